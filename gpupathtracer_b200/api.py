@@ -1,0 +1,379 @@
+"""ctypes binding of libb200pt.so (include/b200pt.h) plus a thin mirror of the reference's host classes.
+
+`Renderer`, `Scene` and `Camera` keep the names, argument meaning and call order of the reference's
+src/core/Renderer.h:12-53, src/core/Scene.h:19-40 and src/math/Camera.h:14-46 so tests read like a
+driver of the reference (Program.cpp:69-152). All compute happens in the CUDA library; there is no
+fallback: a missing library or a missing GPU raises.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200pt.so")
+
+PT_OK = 0
+PT_MICROFACET_GGX, PT_MICROFACET_BECKMANN = 0, 1
+PT_BVH_REFERENCE, PT_BVH_WIDE = 0, 1
+REFERENCE_MAX_DEPTH = 66      # `i > 64`, Iterative.comp:293
+
+
+class PtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libb200pt error {code}: {msg}")
+        self.code = code
+
+
+class pt_config(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_depth", C.c_int32),
+                ("microfacet_model", C.c_int32), ("device", C.c_int32), ("bvh_layout", C.c_int32),
+                ("reserved", C.c_int32 * 6)]
+
+
+class pt_camera(C.Structure):
+    _fields_ = [("lower_left", C.c_float * 3), ("horizontal", C.c_float * 3), ("vertical", C.c_float * 3),
+                ("position", C.c_float * 3), ("u", C.c_float * 3), ("v", C.c_float * 3), ("lens_radius", C.c_float)]
+
+
+class pt_texture(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rgba", C.POINTER(C.c_float))]
+
+
+class pt_counters(C.Structure):
+    _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64),
+                ("frames", C.c_uint64), ("kernel_launches", C.c_uint64)]
+
+
+class pt_bvh_stats(C.Structure):
+    _fields_ = [("n_nodes", C.c_int32), ("n_refs", C.c_int32), ("n_leaves", C.c_int32), ("max_depth", C.c_int32),
+                ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+
+
+# every symbol include/b200pt.h declares: (name, restype, argtypes)
+_P = C.c_void_p
+_F = C.POINTER(C.c_float)
+SYMBOLS = [
+    ("pt_abi_version", C.c_int, []),
+    ("pt_last_error", C.c_char_p, []),
+    ("pt_create", C.c_int, [C.POINTER(pt_config), C.POINTER(_P)]),
+    ("pt_destroy", None, [_P]),
+    ("pt_set_triangles", C.c_int, [_P, _P, C.c_int64]),
+    ("pt_set_materials", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
+    ("pt_set_lights", C.c_int, [_P, _P, C.c_int32, C.c_float]),
+    ("pt_set_environment_color", C.c_int, [_P, _F]),
+    ("pt_set_bvh", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
+    ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
+    ("pt_bvh_build_host", C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(_F), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32), C.POINTER(pt_bvh_stats)]),
+    ("pt_free", None, [_P]),
+    ("pt_get_bvh", C.c_int, [_P, _P, C.POINTER(C.c_int32), _P, C.POINTER(C.c_int32)]),
+    ("pt_assemble_triangles", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_build_light_table", C.c_int, [_P, C.c_int64, _P, C.c_int32, _P, C.c_int32, _F]),
+    ("pt_presubtract_edges", None, [_P, C.c_int64]),
+    ("pt_camera_image_plane", None, [C.c_float, C.c_float, C.c_float, C.c_float, _F, _F, C.POINTER(pt_camera)]),
+    ("pt_set_camera", C.c_int, [_P, C.POINTER(pt_camera)]),
+    ("pt_set_rng", C.c_int, [_P, _P]),
+    ("pt_seed_rng", C.c_int, [_P, C.c_uint64]),
+    ("pt_get_rng", C.c_int, [_P, _P]),
+    ("pt_render_frames", C.c_int, [_P, C.c_int32]),
+    ("pt_reset_samples", C.c_int, [_P]),
+    ("pt_num_samples", C.c_uint32, [_P]),
+    ("pt_synchronize", C.c_int, [_P]),
+    ("pt_download_accum", C.c_int, [_P, _P]),
+    ("pt_accum_device_ptr", _P, [_P]),
+    ("pt_set_accum_device_ptr", C.c_int, [_P, _P]),
+    ("pt_resolve", C.c_int, [_P, C.c_uint32, _P, _P]),
+    ("pt_save_screenshot", C.c_int, [_P, C.c_char_p]),
+    ("pt_trace_closest", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_trace_any", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_trace_closest_device", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_trace_any_device", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_raygen_probe", C.c_int, [_P, C.c_int64, C.c_int64, _P]),
+    ("pt_get_counters", C.c_int, [_P, C.POINTER(pt_counters)]),
+    ("pt_last_device_ms", C.c_float, [_P]),
+    ("pt_set_stage_timing", C.c_int, [_P, C.c_int]),
+    ("pt_get_stage_ms", C.c_int, [_P, _F]),
+    ("pt_stream", _P, [_P]),
+]
+
+_lib = None
+
+
+def load_library():
+    """Load libb200pt.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: run `python -m gpupathtracer_b200.build` (there is no CPU fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, res, args in SYMBOLS:
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+def _check(rc):
+    if rc != PT_OK:
+        raise PtError(rc, load_library().pt_last_error().decode())
+
+
+# ------------------------------------------------------------------------------- host-side scene assembly
+def assemble_triangles(verts, mat_ids):
+    """Scene.cpp:263-292 -> (n,20) float32 with ABSOLUTE positions."""
+    lib = load_library()
+    verts = np.ascontiguousarray(verts, dtype=np.float32)
+    mat_ids = np.ascontiguousarray(mat_ids, dtype=np.uint32)
+    n = verts.shape[0]
+    out = np.zeros((n, 20), dtype=np.float32)
+    rc = lib.pt_assemble_triangles(_ptr(verts), _ptr(mat_ids), n, _ptr(out))
+    if rc != PT_OK:
+        raise PtError(rc, "pt_assemble_triangles")
+    return out
+
+
+def build_light_table(tris_abs, materials):
+    """Scene.cpp:296-331 -> ((L,2) float32 {cumArea, triIndex bits}, totalLightArea)."""
+    lib = load_library()
+    n = tris_abs.shape[0]
+    total = C.c_float(0)
+    mats = np.ascontiguousarray(materials, dtype=np.float32)
+    cnt = lib.pt_build_light_table(_ptr(tris_abs), n, _ptr(mats), mats.shape[0], None, 0, C.byref(total))
+    if cnt < 0:
+        raise PtError(cnt, "pt_build_light_table")
+    out = np.zeros((max(cnt, 1), 2), dtype=np.float32)
+    cnt = lib.pt_build_light_table(_ptr(tris_abs), n, _ptr(mats), mats.shape[0], _ptr(out), cnt, C.byref(total))
+    return out[:cnt], float(total.value)
+
+
+def build_bvh_host(tris_pre, n_threads=0):
+    """This library's SBVH builder on the host (no device needed) -> (nodes (n,8), refs, stats dict)."""
+    lib = load_library()
+    t = np.ascontiguousarray(tris_pre, dtype=np.float32)
+    nodes_p, refs_p = _F(), C.POINTER(C.c_int32)()
+    nn, nr = C.c_int32(), C.c_int32()
+    st = pt_bvh_stats()
+    rc = lib.pt_bvh_build_host(_ptr(t), t.shape[0], n_threads, C.byref(nodes_p), C.byref(nn), C.byref(refs_p), C.byref(nr), C.byref(st))
+    if rc != PT_OK:
+        raise PtError(rc, "pt_bvh_build_host")
+    nodes = np.ctypeslib.as_array(nodes_p, shape=(nn.value, 8)).copy()
+    refs = np.ctypeslib.as_array(refs_p, shape=(nr.value,)).copy()
+    lib.pt_free(nodes_p); lib.pt_free(refs_p)
+    return nodes, refs, {k: getattr(st, k) for k, _ in pt_bvh_stats._fields_}
+
+
+def presubtract_edges(tris_abs):
+    """Scene.cpp:334-337 (returns a copy)."""
+    t = np.ascontiguousarray(tris_abs, dtype=np.float32).copy()
+    load_library().pt_presubtract_edges(_ptr(t), t.shape[0])
+    return t
+
+
+class Camera:
+    """math/Camera.h:14-46. rotation = (yaw, pitch, roll-ignored) as SetRotation (Camera.cpp:33-36)."""
+
+    def __init__(self, aspect, fieldofview, focus, aperture):
+        self.aspect, self.fov, self.focus, self.aperture = float(aspect), float(fieldofview), float(focus), float(aperture)
+        self.position = (0.0, 0.0, 0.0)
+        self.rotation = (0.0, 0.0, 0.0)
+        self.plane = pt_camera()
+
+    def SetPosition(self, p):
+        self.position = tuple(float(x) for x in p)
+
+    def SetRotation(self, r):
+        self.rotation = tuple(float(x) for x in r)
+
+    def GenerateImagePlane(self):
+        load_library().pt_camera_image_plane(self.aspect, self.fov, self.focus, self.aperture, _f3(self.position),
+                                             _f3(self.rotation), C.byref(self.plane))
+        return self.plane
+
+    def as_array(self):
+        p = self.plane
+        return np.array(list(p.lower_left) + list(p.horizontal) + list(p.vertical) + list(p.position) + list(p.u) +
+                        list(p.v) + [p.lens_radius], dtype=np.float32)
+
+
+class Scene:
+    """Host-side result of Scene::LoadScene (Scene.cpp:233-357) for a procedural SceneData."""
+
+    def __init__(self, data):
+        self.data = data
+        self.tris_abs = assemble_triangles(data.verts, data.mat_ids)
+        self.materials = np.ascontiguousarray(data.materials, dtype=np.float32)
+        self.lights, self.total_light_area = build_light_table(self.tris_abs, self.materials)
+        self.tris = presubtract_edges(self.tris_abs)
+        self.env_color = tuple(data.env_color)
+        self.textures = [np.ascontiguousarray(t, dtype=np.float32) for t in data.textures]
+        self.nodes = None
+        self.refs = None
+
+    def set_bvh(self, nodes, refs):
+        self.nodes = np.ascontiguousarray(nodes, dtype=np.float32)
+        self.refs = np.ascontiguousarray(refs, dtype=np.int32)
+
+    def bounds(self):
+        p = self.tris_abs[:, 0:9].reshape(-1, 3)
+        return p.min(axis=0), p.max(axis=0)
+
+
+class Renderer:
+    """src/core/Renderer.h:12-53, headless. Initialize(Window*, scenePath, env) becomes
+    Initialize(width, height, scene) where `scene` is a `Scene`; everything else keeps its name."""
+
+    def __init__(self):
+        self.ctx = None
+        self.lib = load_library()
+        self.width = self.height = 0
+
+    # -- Renderer::Initialize, Renderer.cpp:448-636
+    def Initialize(self, width, height, scene, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=PT_MICROFACET_GGX,
+                   device=0, rng_state=None, seed=None, bvh="given"):
+        cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
+                        device=device, bvh_layout=PT_BVH_REFERENCE)
+        ctx = C.c_void_p()
+        _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
+        self.ctx = ctx
+        self.width, self.height = width, height
+        self.scene = scene
+        _check(self.lib.pt_set_triangles(ctx, _ptr(scene.tris), scene.tris.shape[0]))
+        texs = (pt_texture * max(1, len(scene.textures)))()
+        for i, t in enumerate(scene.textures):
+            texs[i].width, texs[i].height = t.shape[1], t.shape[0]
+            texs[i].rgba = t.ctypes.data_as(C.POINTER(C.c_float))
+        _check(self.lib.pt_set_materials(ctx, _ptr(scene.materials), scene.materials.shape[0],
+                                         C.cast(texs, C.c_void_p), len(scene.textures)))
+        _check(self.lib.pt_set_lights(ctx, _ptr(scene.lights), scene.lights.shape[0], scene.total_light_area))
+        _check(self.lib.pt_set_environment_color(ctx, _f3(scene.env_color)))
+        if bvh == "build" or scene.nodes is None:
+            stats = pt_bvh_stats()
+            _check(self.lib.pt_build_bvh(ctx, C.byref(stats)))
+            self.bvh_stats = stats
+            nodes, refs = self.GetBVH()
+            scene.set_bvh(nodes, refs)
+        else:
+            _check(self.lib.pt_set_bvh(ctx, _ptr(scene.nodes), scene.nodes.shape[0], _ptr(scene.refs), scene.refs.shape[0]))
+        if rng_state is not None:
+            self.SetRNG(rng_state)
+        elif seed is not None:
+            _check(self.lib.pt_seed_rng(ctx, seed))
+        return self
+
+    def GetBVH(self):
+        nn, nr = C.c_int32(), C.c_int32()
+        _check(self.lib.pt_get_bvh(self.ctx, None, C.byref(nn), None, C.byref(nr)))
+        nodes = np.zeros((nn.value, 8), dtype=np.float32)
+        refs = np.zeros(nr.value, dtype=np.int32)
+        _check(self.lib.pt_get_bvh(self.ctx, _ptr(nodes), C.byref(nn), _ptr(refs), C.byref(nr)))
+        return nodes, refs
+
+    def SetRNG(self, state):
+        state = np.ascontiguousarray(state, dtype=np.uint32)
+        assert state.size == self.width * self.height * 4
+        _check(self.lib.pt_set_rng(self.ctx, _ptr(state)))
+
+    def GetRNG(self):
+        out = np.zeros((self.width * self.height, 4), dtype=np.uint32)
+        _check(self.lib.pt_get_rng(self.ctx, _ptr(out)))
+        return out
+
+    # -- Renderer::RenderFrame(const Camera&), Renderer.cpp:651-662: +1 sample per pixel
+    def RenderFrame(self, camera, n_frames=1):
+        _check(self.lib.pt_set_camera(self.ctx, C.byref(camera.plane)))
+        _check(self.lib.pt_render_frames(self.ctx, n_frames))
+
+    def Synchronize(self):
+        _check(self.lib.pt_synchronize(self.ctx))
+
+    def ResetSamples(self):
+        _check(self.lib.pt_reset_samples(self.ctx))
+
+    def GetNumSamples(self):
+        return int(self.lib.pt_num_samples(self.ctx))
+
+    # -- Renderer::Present, Renderer.cpp:681-685 -> headless resolve
+    def Present(self, as_u8=False):
+        n = self.width * self.height
+        if as_u8:
+            out = np.zeros((self.height, self.width, 3), dtype=np.uint8)
+            _check(self.lib.pt_resolve(self.ctx, self.GetNumSamples(), None, _ptr(out)))
+        else:
+            out = np.zeros((self.height, self.width, 3), dtype=np.float32)
+            _check(self.lib.pt_resolve(self.ctx, self.GetNumSamples(), _ptr(out), None))
+        return out
+
+    def SaveScreenshot(self, filename):
+        _check(self.lib.pt_save_screenshot(self.ctx, filename.encode()))
+
+    def DownloadAccum(self):
+        out = np.zeros((self.height, self.width, 4), dtype=np.float32)
+        _check(self.lib.pt_download_accum(self.ctx, _ptr(out)))
+        return out
+
+    def TraceClosest(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        hits = np.zeros((rays.shape[0], 4), dtype=np.float32)
+        _check(self.lib.pt_trace_closest(self.ctx, _ptr(rays), rays.shape[0], _ptr(hits)))
+        return hits
+
+    def TraceAny(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        flags = np.zeros(rays.shape[0], dtype=np.uint8)
+        _check(self.lib.pt_trace_any(self.ctx, _ptr(rays), rays.shape[0], _ptr(flags)))
+        return flags
+
+    def RaygenProbe(self, first, n):
+        out = np.zeros((n, 12), dtype=np.float32)
+        _check(self.lib.pt_raygen_probe(self.ctx, first, n, _ptr(out)))
+        return out
+
+    def Counters(self):
+        c = pt_counters()
+        _check(self.lib.pt_get_counters(self.ctx, C.byref(c)))
+        return {k: int(getattr(c, k)) for k, _ in pt_counters._fields_}
+
+    def LastDeviceMs(self):
+        return float(self.lib.pt_last_device_ms(self.ctx))
+
+    def SetStageTiming(self, on=True):
+        _check(self.lib.pt_set_stage_timing(self.ctx, 1 if on else 0))
+
+    def StageMs(self):
+        out = (C.c_float * 5)()
+        _check(self.lib.pt_get_stage_ms(self.ctx, out))
+        return dict(zip(["raygen", "extend", "shade", "shadow", "tally"], [float(x) for x in out]))
+
+    def ResolveInto(self, host_ptr_u8, num_samples=None):
+        """Present into caller-owned (ideally pinned) host memory: height*width*3 bytes."""
+        _check(self.lib.pt_resolve(self.ctx, num_samples or self.GetNumSamples(), None, C.c_void_p(host_ptr_u8)))
+
+    def AccumDevicePtr(self):
+        return int(self.lib.pt_accum_device_ptr(self.ctx))
+
+    def CleanUp(self):
+        if self.ctx is not None:
+            self.lib.pt_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.CleanUp()
+        except Exception:
+            pass
+
+
+def make_rng_table(n_pixels, seed=0):
+    """Stand-in for Renderer.cpp:545-553 (std::default_random_engine + uniform_int_distribution(129, UINT32_MAX));
+    the table is an INPUT shared by the CUDA path and the oracle."""
+    rng = np.random.default_rng(seed)
+    return rng.integers(129, 2 ** 32, size=(n_pixels, 4), dtype=np.uint64).astype(np.uint32)

@@ -1,0 +1,592 @@
+// pt_api.cu -- implementation of the C ABI declared in include/b200pt.h.
+// Owns the context (device buffers, stream, events) and the host->device re-layout of the scene.
+#include "../../include/b200pt.h"
+#include "pt_kernels.h"
+#include "pt_host.h"
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <cstdarg>
+#include <string>
+#include <vector>
+#include <chrono>
+
+using namespace pt;
+
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
+    g_err = buf;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(PT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr; size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc((void**)&p, (count ? count : 1) * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+struct pt_context {
+    pt_config cfg;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    LaunchDims dims{};
+    float last_ms = 0.0f;
+    pt_counters counters{};
+    uint32_t num_samples = 0;
+
+    // host mirrors (what the reference keeps in triangleVec / nodesVec / referenceVec, Scene.h:23, BVH.h:97-98)
+    std::vector<float> h_tris;
+    HostBvh h_bvh;
+    std::vector<pt_material> h_mats;
+
+    DevBuf<float4> d_tris;
+    DevBuf<BvhPair> d_pairs;
+    DevBuf<LeafTri> d_leaf;
+    DevBuf<MaterialRec> d_mats;
+    DevBuf<TextureRec> d_texrec;
+    std::vector<float4*> d_texels;
+    DevBuf<float2> d_lights;
+    int n_lights = 0, n_textures = 0, n_leaf = 0;
+    float total_light_area = 0.0f;
+    float env[3] = {1.0f, 1.0f, 1.0f};
+
+    CameraRec cam{};
+    bool have_cam = false, have_rng = false;
+
+    DevBuf<uint4> d_rng;
+    DevBuf<float4> d_accum_own;
+    float4* d_accum = nullptr;
+    DevBuf<float4> d_q[2][4];
+    DevBuf<uint4> d_qrng[2];
+    DevBuf<float4> d_shadow[4];
+    DevBuf<float4> d_hits;
+    DevBuf<BounceCounters> d_counters;
+    DevBuf<unsigned long long> d_totals;
+    DevBuf<int> d_cursor;
+    // staging for host-pointer batch entry points
+    DevBuf<float4> d_stage_rays, d_stage_hits;
+    DevBuf<unsigned char> d_stage_flags;
+    DevBuf<float> d_resolve_f32;
+    DevBuf<unsigned char> d_resolve_u8;
+    // per-stage timing (pt_set_stage_timing)
+    bool stage_timing = false;
+    std::vector<cudaEvent_t> stage_events;
+    int stage_frames = 0, stage_events_per_frame = 0;
+};
+
+static SceneDev scene_dev(pt_context* c) {
+    SceneDev s{};
+    s.pairs = c->d_pairs.p; s.leaf_tris = c->d_leaf.p; s.n_leaf_tris = c->n_leaf;
+    s.tris = c->d_tris.p; s.materials = c->d_mats.p; s.textures = c->d_texrec.p; s.n_textures = c->n_textures;
+    s.lights = c->d_lights.p; s.n_lights = c->n_lights; s.total_light_area = c->total_light_area;
+    s.env[0] = c->env[0]; s.env[1] = c->env[1]; s.env[2] = c->env[2];
+    return s;
+}
+
+extern "C" {
+
+int pt_abi_version(void) { return B200PT_ABI_VERSION; }
+const char* pt_last_error(void) { return g_err.c_str(); }
+
+int pt_create(const pt_config* cfg, pt_context** out) {
+    if (!cfg || !out) return fail(PT_ERR_INVALID, "pt_create: null argument");
+    *out = nullptr;
+    if (cfg->width <= 0 || cfg->height <= 0 || (cfg->width % 8) || (cfg->height % 8))
+        return fail(PT_ERR_INVALID, "pt_create: width/height must be positive multiples of 8 (got %dx%d)", cfg->width, cfg->height);
+    if (cfg->max_depth < 1 || cfg->max_depth > 66)
+        return fail(PT_ERR_INVALID, "pt_create: max_depth must be in [1, 66] (got %d)", cfg->max_depth);
+    if (cfg->microfacet_model != PT_MICROFACET_GGX && cfg->microfacet_model != PT_MICROFACET_BECKMANN)
+        return fail(PT_ERR_INVALID, "pt_create: unknown microfacet model %d", cfg->microfacet_model);
+    if (cfg->bvh_layout != PT_BVH_REFERENCE)
+        return fail(PT_ERR_UNSUPPORTED, "pt_create: bvh_layout %d not available in this build", cfg->bvh_layout);
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(PT_ERR_NO_DEVICE, "pt_create: no CUDA device (%s); libb200pt has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count 0");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(PT_ERR_INVALID, "pt_create: device %d of %d", cfg->device, ndev);
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10)
+        return fail(PT_ERR_NO_DEVICE, "pt_create: device %d is sm_%d%d; this library carries sm_100a code only", cfg->device, prop.major, prop.minor);
+    CK(cudaSetDevice(cfg->device));
+    pt_context* c = new pt_context();
+    c->cfg = *cfg;
+    CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CK(cudaEventCreate(&c->ev0));
+    CK(cudaEventCreate(&c->ev1));
+    query_launch_dims(cfg->device, &c->dims);
+    const size_t npx = (size_t)cfg->width * cfg->height;
+    CK(c->d_rng.alloc(npx));
+    CK(c->d_accum_own.alloc(npx));
+    c->d_accum = c->d_accum_own.p;
+    CK(cudaMemsetAsync(c->d_accum, 0, npx * sizeof(float4), c->stream));
+    for (int q = 0; q < 2; q++) {
+        for (int k = 0; k < 4; k++) CK(c->d_q[q][k].alloc(npx));
+        CK(c->d_qrng[q].alloc(npx));
+    }
+    for (int k = 0; k < 4; k++) CK(c->d_shadow[k].alloc(npx));
+    CK(c->d_hits.alloc(npx));
+    CK(c->d_counters.alloc(cfg->max_depth + 2));
+    CK(c->d_totals.alloc(4));
+    CK(cudaMemsetAsync(c->d_totals.p, 0, 4 * sizeof(unsigned long long), c->stream));
+    CK(c->d_cursor.alloc(4));
+    CK(cudaStreamSynchronize(c->stream));
+    *out = c;
+    return PT_OK;
+}
+
+void pt_destroy(pt_context* c) {
+    if (!c) return;
+    cudaSetDevice(c->cfg.device);
+    cudaStreamSynchronize(c->stream);
+    c->d_tris.release(); c->d_pairs.release(); c->d_leaf.release(); c->d_mats.release(); c->d_texrec.release();
+    for (float4* t : c->d_texels) cudaFree(t);
+    c->d_lights.release(); c->d_rng.release(); c->d_accum_own.release();
+    for (int q = 0; q < 2; q++) { for (int k = 0; k < 4; k++) c->d_q[q][k].release(); c->d_qrng[q].release(); }
+    for (int k = 0; k < 4; k++) c->d_shadow[k].release();
+    c->d_hits.release(); c->d_counters.release(); c->d_totals.release(); c->d_cursor.release();
+    c->d_stage_rays.release(); c->d_stage_hits.release(); c->d_stage_flags.release();
+    c->d_resolve_f32.release(); c->d_resolve_u8.release();
+    for (cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+// (re)build the leaf triangle stream from host triangles + reference list
+static int upload_leaf_stream(pt_context* c) {
+    if (c->h_tris.empty() || c->h_bvh.refs.empty()) return PT_OK;
+    const size_t nr = c->h_bvh.refs.size();
+    const int64_t nt = (int64_t)(c->h_tris.size() / 20);
+    std::vector<LeafTri> ls(nr);
+    for (size_t i = 0; i < nr; i++) {
+        int32_t r = c->h_bvh.refs[i];
+        bool last = r < 0;
+        int32_t idx = last ? -r : r;
+        if (idx >= nt) return fail(PT_ERR_INVALID, "BVH reference %d out of range (%lld triangles)", idx, (long long)nt);
+        const float* t = c->h_tris.data() + 20 * (size_t)idx;
+        int32_t id = last ? ~idx : idx;
+        float idf; memcpy(&idf, &id, 4);
+        ls[i].r[0] = make_float4(t[0], t[1], t[2], t[3]);
+        ls[i].r[1] = make_float4(t[4], t[5], t[6], t[7]);
+        ls[i].r[2] = make_float4(t[8], idf, 0.0f, 0.0f);
+    }
+    CK(c->d_leaf.alloc(nr));
+    CK(cudaMemcpyAsync(c->d_leaf.p, ls.data(), nr * sizeof(LeafTri), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->n_leaf = (int)nr;
+    return PT_OK;
+}
+
+int pt_set_triangles(pt_context* c, const float* tris, int64_t n) {
+    if (!c || !tris || n <= 0) return fail(PT_ERR_INVALID, "pt_set_triangles: bad argument");
+    if (n >= (1ll << 30)) return fail(PT_ERR_LIMIT, "pt_set_triangles: too many triangles");
+    CK(cudaSetDevice(c->cfg.device));
+    c->h_tris.assign(tris, tris + 20 * n);
+    CK(c->d_tris.alloc(5 * (size_t)n));
+    CK(cudaMemcpyAsync(c->d_tris.p, tris, 80 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return upload_leaf_stream(c);
+}
+
+int pt_set_materials(pt_context* c, const pt_material* mats, int32_t n_mats, const pt_texture* tex, int32_t n_tex) {
+    if (!c || !mats || n_mats <= 0 || n_tex < 0 || (n_tex > 0 && !tex)) return fail(PT_ERR_INVALID, "pt_set_materials: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    static_assert(sizeof(pt_material) == sizeof(MaterialRec), "material record layout");
+    c->h_mats.assign(mats, mats + n_mats);
+    CK(c->d_mats.alloc(n_mats));
+    CK(cudaMemcpyAsync(c->d_mats.p, mats, sizeof(pt_material) * n_mats, cudaMemcpyHostToDevice, c->stream));
+    for (float4* t : c->d_texels) cudaFree(t);
+    c->d_texels.clear();
+    std::vector<TextureRec> recs(n_tex);
+    for (int i = 0; i < n_tex; i++) {
+        if (tex[i].width <= 0 || tex[i].height <= 0 || !tex[i].rgba) return fail(PT_ERR_INVALID, "pt_set_materials: texture %d invalid", i);
+        size_t cnt = (size_t)tex[i].width * tex[i].height;
+        float4* d = nullptr;
+        CK(cudaMalloc((void**)&d, cnt * sizeof(float4)));
+        c->d_texels.push_back(d);
+        CK(cudaMemcpyAsync(d, tex[i].rgba, cnt * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+        recs[i].width = tex[i].width; recs[i].height = tex[i].height; recs[i].texels = d;
+    }
+    CK(c->d_texrec.alloc(n_tex > 0 ? n_tex : 1));
+    if (n_tex > 0) CK(cudaMemcpyAsync(c->d_texrec.p, recs.data(), sizeof(TextureRec) * n_tex, cudaMemcpyHostToDevice, c->stream));
+    c->n_textures = n_tex;
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
+int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_light_area) {
+    if (!c || !lights || n <= 0) return fail(PT_ERR_INVALID, "pt_set_lights: a scene needs at least one emissive triangle (Iterative.comp:42-61)");
+    CK(cudaSetDevice(c->cfg.device));
+    static_assert(sizeof(pt_light) == sizeof(float2), "light record layout");
+    CK(c->d_lights.alloc(n));
+    CK(cudaMemcpyAsync(c->d_lights.p, lights, sizeof(pt_light) * n, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->n_lights = n; c->total_light_area = total_light_area;
+    return PT_OK;
+}
+
+int pt_set_environment_color(pt_context* c, const float rgb[3]) {
+    if (!c || !rgb) return fail(PT_ERR_INVALID, "pt_set_environment_color: bad argument");
+    c->env[0] = rgb[0]; c->env[1] = rgb[1]; c->env[2] = rgb[2];
+    return PT_OK;
+}
+
+static int install_bvh(pt_context* c) {
+    const float* nodes = c->h_bvh.nodes.data();
+    const int n_nodes = (int)(c->h_bvh.nodes.size() / 8);
+    const int n_pairs = (n_nodes - 1) / 2;
+    std::vector<BvhPair> pairs(n_pairs);
+    auto link_of = [](const float* nd) {
+        int32_t d0; memcpy(&d0, nd + 3, 4);
+        int32_t link = d0 > 0 ? (d0 - 1) / 2 : ~(-d0);
+        float f; memcpy(&f, &link, 4); return f;
+    };
+    for (int pi = 0; pi < n_pairs; pi++) {
+        const float* c0 = nodes + 8 * (size_t)(2 * pi + 1);
+        const float* c1 = c0 + 8;
+        pairs[pi].q[0] = make_float4(c0[0], c0[1], c0[2], link_of(c0));
+        pairs[pi].q[1] = make_float4(c0[4], c0[5], c0[6], 0.0f);
+        pairs[pi].q[2] = make_float4(c1[0], c1[1], c1[2], link_of(c1));
+        pairs[pi].q[3] = make_float4(c1[4], c1[5], c1[6], 0.0f);
+    }
+    CK(c->d_pairs.alloc(n_pairs));
+    CK(cudaMemcpyAsync(c->d_pairs.p, pairs.data(), sizeof(BvhPair) * n_pairs, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return upload_leaf_stream(c);
+}
+
+int pt_set_bvh(pt_context* c, const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs) {
+    if (!c || !nodes || !refs || n_nodes < 3 || n_refs < 1) return fail(PT_ERR_INVALID, "pt_set_bvh: bad argument (the root must be an inner node, BVH.glsl:627)");
+    CK(cudaSetDevice(c->cfg.device));
+    std::string msg; int n_leaves = 0;
+    int64_t nt = c->h_tris.empty() ? -1 : (int64_t)(c->h_tris.size() / 20);
+    int depth = validate_bvh(nodes, n_nodes, refs, n_refs, nt, msg, &n_leaves);
+    if (depth < 0) return fail(PT_ERR_INVALID, "pt_set_bvh: %s", msg.c_str());
+    if (depth >= 64) return fail(PT_ERR_LIMIT, "pt_set_bvh: tree depth %d exceeds the traversal stack (64)", depth);
+    c->h_bvh.nodes.assign(nodes, nodes + 8 * (size_t)n_nodes);
+    c->h_bvh.refs.assign(refs, refs + n_refs);
+    c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = n_leaves;
+    return install_bvh(c);
+}
+
+int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_build_bvh: null context");
+    if (c->h_tris.empty()) return fail(PT_ERR_INVALID, "pt_build_bvh: call pt_set_triangles first");
+    CK(cudaSetDevice(c->cfg.device));
+    std::string msg;
+    HostBvh b;
+    cudaEvent_t dummy; (void)dummy;
+    auto t0 = std::chrono::steady_clock::now();
+    if (!build_sbvh(c->h_tris.data(), (int64_t)(c->h_tris.size() / 20), 0, b, msg)) return fail(PT_ERR_LIMIT, "pt_build_bvh: %s", msg.c_str());
+    auto t1 = std::chrono::steady_clock::now();
+    c->h_bvh = std::move(b);
+    int rc = install_bvh(c);
+    if (rc != PT_OK) return rc;
+    if (stats) {
+        stats->n_nodes = (int)(c->h_bvh.nodes.size() / 8);
+        stats->n_refs = (int)c->h_bvh.refs.size();
+        stats->n_leaves = c->h_bvh.n_leaves;
+        stats->max_depth = c->h_bvh.max_depth;
+        stats->sah_cost = c->h_bvh.sah_cost;
+        stats->build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+    }
+    return PT_OK;
+}
+
+int pt_get_bvh(pt_context* c, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs) {
+    if (!c || !n_nodes || !n_refs) return fail(PT_ERR_INVALID, "pt_get_bvh: bad argument");
+    *n_nodes = (int32_t)(c->h_bvh.nodes.size() / 8);
+    *n_refs = (int32_t)c->h_bvh.refs.size();
+    if (nodes) memcpy(nodes, c->h_bvh.nodes.data(), c->h_bvh.nodes.size() * 4);
+    if (refs) memcpy(refs, c->h_bvh.refs.data(), c->h_bvh.refs.size() * 4);
+    return PT_OK;
+}
+
+int pt_set_camera(pt_context* c, const pt_camera* cam) {
+    if (!c || !cam) return fail(PT_ERR_INVALID, "pt_set_camera: bad argument");
+    static_assert(sizeof(pt_camera) == sizeof(CameraRec), "camera record layout");
+    memcpy(&c->cam, cam, sizeof(CameraRec));
+    c->have_cam = true;
+    return PT_OK;
+}
+
+int pt_set_rng(pt_context* c, const uint32_t* state4) {
+    if (!c || !state4) return fail(PT_ERR_INVALID, "pt_set_rng: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    CK(cudaMemcpyAsync(c->d_rng.p, state4, npx * 16, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->have_rng = true;
+    return PT_OK;
+}
+int pt_seed_rng(pt_context* c, uint64_t seed) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_seed_rng: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    launch_seed_rng(c->d_rng.p, (long long)c->cfg.width * c->cfg.height, seed, c->stream);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(c->stream));
+    c->have_rng = true;
+    return PT_OK;
+}
+int pt_get_rng(pt_context* c, uint32_t* state4) {
+    if (!c || !state4) return fail(PT_ERR_INVALID, "pt_get_rng: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    CK(cudaMemcpyAsync(state4, c->d_rng.p, npx * 16, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
+static int check_scene(pt_context* c, const char* who, bool need_shading) {
+    if (!c->d_pairs.p || !c->d_leaf.p || !c->d_tris.p) return fail(PT_ERR_INVALID, "%s: triangles and BVH must be set first", who);
+    if (need_shading) {
+        if (!c->d_mats.p) return fail(PT_ERR_INVALID, "%s: materials not set", who);
+        if (!c->d_lights.p || c->n_lights < 1) return fail(PT_ERR_INVALID, "%s: light table not set", who);
+        if (!c->have_cam) return fail(PT_ERR_INVALID, "%s: camera not set", who);
+        if (!c->have_rng) return fail(PT_ERR_INVALID, "%s: RNG table not set (pt_set_rng / pt_seed_rng)", who);
+    }
+    return PT_OK;
+}
+
+static FrameParams frame_params(pt_context* c) {
+    FrameParams p{};
+    p.scene = scene_dev(c);
+    p.cam = c->cam;
+    p.width = c->cfg.width; p.height = c->cfg.height;
+    p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model;
+    p.rng_table = c->d_rng.p; p.accum = c->d_accum;
+    for (int q = 0; q < 2; q++) {
+        p.queue[q].q0 = c->d_q[q][0].p; p.queue[q].q1 = c->d_q[q][1].p; p.queue[q].q2 = c->d_q[q][2].p;
+        p.queue[q].q3 = c->d_q[q][3].p; p.queue[q].q4 = c->d_qrng[q].p;
+    }
+    p.shadow.s0 = c->d_shadow[0].p; p.shadow.s1 = c->d_shadow[1].p; p.shadow.s2 = c->d_shadow[2].p; p.shadow.s3 = c->d_shadow[3].p;
+    p.hits = c->d_hits.p;
+    p.counters = c->d_counters.p;
+    p.totals = c->d_totals.p;
+    return p;
+}
+
+int pt_render_frames(pt_context* c, int32_t n_frames) {
+    if (!c || n_frames < 0) return fail(PT_ERR_INVALID, "pt_render_frames: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    int rc = check_scene(c, "pt_render_frames", true);
+    if (rc != PT_OK) return rc;
+    FrameParams p = frame_params(c);
+    CK(cudaEventRecord(c->ev0, c->stream));
+    const int epf = 3 * c->cfg.max_depth + 3;
+    if (c->stage_timing) {
+        while ((int)c->stage_events.size() < epf * n_frames) {
+            cudaEvent_t e; CK(cudaEventCreate(&e)); c->stage_events.push_back(e);
+        }
+        c->stage_frames = n_frames; c->stage_events_per_frame = epf;
+    }
+    for (int f = 0; f < n_frames; f++)
+        c->counters.kernel_launches += launch_frame(p, c->dims, c->stream, c->stage_timing ? c->stage_events.data() + (size_t)f * epf : nullptr);
+    CK(cudaEventRecord(c->ev1, c->stream));
+    CK(cudaGetLastError());
+    c->num_samples += n_frames;
+    c->counters.frames += n_frames;
+    return PT_OK;
+}
+
+int pt_synchronize(pt_context* c) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_synchronize: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
+int pt_reset_samples(pt_context* c) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_reset_samples: null context");
+    CK(cudaSetDevice(c->cfg.device));
+    // glClearTexSubImage(accum, {0,0,0,1}) + numSamples = 0, Renderer.cpp:687-691
+    CK(cudaMemsetAsync(c->d_accum, 0, (size_t)c->cfg.width * c->cfg.height * sizeof(float4), c->stream));
+    c->num_samples = 0;
+    return PT_OK;
+}
+uint32_t pt_num_samples(pt_context* c) { return c ? c->num_samples : 0; }
+
+int pt_download_accum(pt_context* c, float* rgba) {
+    if (!c || !rgba) return fail(PT_ERR_INVALID, "pt_download_accum: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaMemcpyAsync(rgba, c->d_accum, (size_t)c->cfg.width * c->cfg.height * 16, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+void* pt_accum_device_ptr(pt_context* c) { return c ? (void*)c->d_accum : nullptr; }
+int pt_set_accum_device_ptr(pt_context* c, void* dev_rgba) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_set_accum_device_ptr: null context");
+    c->d_accum = dev_rgba ? (float4*)dev_rgba : c->d_accum_own.p;
+    return PT_OK;
+}
+
+int pt_resolve(pt_context* c, uint32_t num_samples, float* rgb_f32, uint8_t* rgb_u8) {
+    if (!c || num_samples == 0) return fail(PT_ERR_INVALID, "pt_resolve: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    float* d_f = nullptr; unsigned char* d_u = nullptr;
+    if (rgb_f32) { CK(c->d_resolve_f32.alloc(npx * 3)); d_f = c->d_resolve_f32.p; }
+    if (rgb_u8) { CK(c->d_resolve_u8.alloc(npx * 3)); d_u = c->d_resolve_u8.p; }
+    launch_resolve(c->d_accum, (long long)npx, num_samples, d_f, d_u, c->stream);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    if (rgb_f32) CK(cudaMemcpyAsync(rgb_f32, d_f, npx * 12, cudaMemcpyDeviceToHost, c->stream));
+    if (rgb_u8) CK(cudaMemcpyAsync(rgb_u8, d_u, npx * 3, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
+int pt_save_screenshot(pt_context* c, const char* path) {
+    if (!c || !path) return fail(PT_ERR_INVALID, "pt_save_screenshot: bad argument");
+    if (c->num_samples == 0) return fail(PT_ERR_INVALID, "pt_save_screenshot: no samples rendered");
+    size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    std::string p(path);
+    bool pfm = p.size() > 4 && p.substr(p.size() - 4) == ".pfm";
+    if (pfm) {
+        std::vector<float> img(npx * 3);
+        int rc = pt_resolve(c, c->num_samples, img.data(), nullptr);
+        if (rc != PT_OK) return rc;
+        if (!write_pfm(path, c->cfg.width, c->cfg.height, img.data())) return fail(PT_ERR_IO, "cannot write %s", path);
+    } else {
+        std::vector<uint8_t> img(npx * 3);
+        int rc = pt_resolve(c, c->num_samples, nullptr, img.data());
+        if (rc != PT_OK) return rc;
+        if (!write_ppm(path, c->cfg.width, c->cfg.height, img.data())) return fail(PT_ERR_IO, "cannot write %s", path);
+    }
+    return PT_OK;
+}
+
+int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* d_hits) {
+    if (!c || !d_rays || !d_hits || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_closest_device: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    int rc = check_scene(c, "pt_trace_closest", false);
+    if (rc != PT_OK) return rc;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    launch_trace_closest(scene_dev(c), (const float4*)d_rays, n, (float4*)d_hits, c->d_cursor.p, c->dims, c->stream);
+    CK(cudaEventRecord(c->ev1, c->stream));
+    CK(cudaGetLastError());
+    c->counters.kernel_launches++;
+    c->counters.closest_rays += (uint64_t)n;
+    return PT_OK;
+}
+int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_flags) {
+    if (!c || !d_rays || !d_flags || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_any_device: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    int rc = check_scene(c, "pt_trace_any", false);
+    if (rc != PT_OK) return rc;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    launch_trace_any(scene_dev(c), (const float4*)d_rays, n, (unsigned char*)d_flags, c->d_cursor.p, c->dims, c->stream);
+    CK(cudaEventRecord(c->ev1, c->stream));
+    CK(cudaGetLastError());
+    c->counters.kernel_launches++;
+    c->counters.shadow_rays += (uint64_t)n;
+    return PT_OK;
+}
+
+int pt_trace_closest(pt_context* c, const float* rays, int64_t n, float* hits) {
+    if (!c || !rays || !hits || n < 0) return fail(PT_ERR_INVALID, "pt_trace_closest: bad argument");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->d_stage_rays.alloc(2 * (size_t)n));
+    CK(c->d_stage_hits.alloc((size_t)n));
+    CK(cudaMemcpyAsync(c->d_stage_rays.p, rays, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    int rc = pt_trace_closest_device(c, c->d_stage_rays.p, n, c->d_stage_hits.p);
+    if (rc != PT_OK) return rc;
+    CK(cudaMemcpyAsync(hits, c->d_stage_hits.p, 16 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+int pt_trace_any(pt_context* c, const float* rays, int64_t n, uint8_t* flags) {
+    if (!c || !rays || !flags || n < 0) return fail(PT_ERR_INVALID, "pt_trace_any: bad argument");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    CK(c->d_stage_rays.alloc(2 * (size_t)n));
+    CK(c->d_stage_flags.alloc((size_t)n));
+    CK(cudaMemcpyAsync(c->d_stage_rays.p, rays, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    int rc = pt_trace_any_device(c, c->d_stage_rays.p, n, c->d_stage_flags.p);
+    if (rc != PT_OK) return rc;
+    CK(cudaMemcpyAsync(flags, c->d_stage_flags.p, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
+int pt_raygen_probe(pt_context* c, int64_t first, int64_t n, float* out) {
+    if (!c || !out || first < 0 || n < 0 || first + n > (int64_t)c->cfg.width * c->cfg.height) return fail(PT_ERR_INVALID, "pt_raygen_probe: bad range");
+    if (!c->have_cam || !c->have_rng) return fail(PT_ERR_INVALID, "pt_raygen_probe: camera and RNG table must be set");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    float4* d = nullptr;
+    CK(cudaMalloc((void**)&d, 48 * (size_t)n));
+    FrameParams p = frame_params(c);
+    launch_raygen_probe(p, first, n, d, c->stream);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(out, d, 48 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    cudaFree(d);
+    return PT_OK;
+}
+
+int pt_get_counters(pt_context* c, pt_counters* out) {
+    if (!c || !out) return fail(PT_ERR_INVALID, "pt_get_counters: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    unsigned long long t[4];
+    CK(cudaMemcpyAsync(t, c->d_totals.p, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    *out = c->counters;
+    out->closest_rays += t[0]; out->shadow_rays += t[1]; out->paths = t[2];
+    return PT_OK;
+}
+
+float pt_last_device_ms(pt_context* c) {
+    if (!c) return -1.0f;
+    cudaSetDevice(c->cfg.device);
+    if (cudaEventSynchronize(c->ev1) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) != cudaSuccess) return -1.0f;
+    return ms;
+}
+int pt_set_stage_timing(pt_context* c, int on) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_set_stage_timing: null context");
+    c->stage_timing = on != 0;
+    c->stage_frames = 0;
+    return PT_OK;
+}
+int pt_get_stage_ms(pt_context* c, float out[5]) {
+    if (!c || !out) return fail(PT_ERR_INVALID, "pt_get_stage_ms: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaStreamSynchronize(c->stream));
+    for (int i = 0; i < 5; i++) out[i] = 0.0f;
+    const int epf = c->stage_events_per_frame;
+    for (int f = 0; f < c->stage_frames; f++) {
+        cudaEvent_t* ev = c->stage_events.data() + (size_t)f * epf;
+        for (int k = 0; k + 1 < epf; k++) {
+            float ms = 0.0f;
+            CK(cudaEventElapsedTime(&ms, ev[k], ev[k + 1]));
+            int stage = (k == 0) ? 0 : (k == epf - 2) ? 4 : 1 + ((k - 1) % 3);
+            out[stage] += ms;
+        }
+    }
+    return PT_OK;
+}
+void* pt_stream(pt_context* c) { return c ? (void*)c->stream : nullptr; }
+}  // extern "C"

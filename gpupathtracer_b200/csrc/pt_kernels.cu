@@ -1,0 +1,374 @@
+// pt_kernels.cu -- the sm_100a kernels of the wavefront path tracer.
+//
+// Stage map to the reference megakernel (src/shaders/Iterative.comp:214-307):
+//   k_raygen   InitRay                      :174-210
+//   k_extend   IfIfClosestHit               common/BVH.glsl:634-767
+//   k_shade    vertex + emission/MIS + NEE sample + BSDF sample + Russian roulette   :236-301
+//   k_shadow   IfIfAnyHit + NEE add + store common/BVH.glsl:769-854, Iterative.comp:278-280,295
+//   k_resolve  Present.frag:13-37
+// Extend and shadow are persistent kernels: one resident grid, warps pull 32-ray packets from a
+// device-side cursor. Shade is a streaming kernel that compacts survivors and shadow items with
+// warp ballots + one atomic per warp.
+#include "pt_kernels.h"
+#include "pt_trace.cuh"
+#include "pt_shade.cuh"
+
+namespace pt {
+
+#define PT_TRACE_THREADS 128
+#define PT_STREAM_THREADS 256
+
+// ------------------------------------------------------------------ fixed ray batches
+template <bool ANY>
+__global__ void __launch_bounds__(PT_TRACE_THREADS)
+k_trace_batch(SceneDev s, const float4* __restrict__ rays, long long n, float4* __restrict__ hits,
+              unsigned char* __restrict__ flags, int* cursor) {
+    const int lane = threadIdx.x & 31;
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        long long i = (long long)base + lane;
+        if (i < n) {
+            float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
+            HitRec h; h.t = rd.w; h.u = 0.0f; h.v = 0.0f; h.tri = -1;
+            bool r = traverse<ANY>(s, xyz(ro), xyz(rd), h);
+            if (ANY) flags[i] = r ? 1 : 0;
+            else hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+        }
+    }
+}
+
+void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
+                          const LaunchDims& dims, cudaStream_t st) {
+    cudaMemsetAsync(cursor, 0, sizeof(int), st);
+    k_trace_batch<false><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, rays, n, hits, nullptr, cursor);
+}
+void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
+                      const LaunchDims& dims, cudaStream_t st) {
+    cudaMemsetAsync(cursor, 0, sizeof(int), st);
+    k_trace_batch<true><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, rays, n, nullptr, flags, cursor);
+}
+
+// ------------------------------------------------------------------ ray generation
+__global__ void __launch_bounds__(PT_STREAM_THREADS)
+k_raygen(FrameParams p) {
+    const int n = p.width * p.height;
+    if (blockIdx.x == 0 && threadIdx.x == 0) p.counters[0].n_paths = n;
+    const PathQueue q = p.queue[0];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int px, py;
+        ray_index_to_morton(i, p.width, px, py);
+        int pix = py * p.width + px;
+        uint4 st = p.rng_table[pix];                         // initRNG, Random.glsl:232-237
+        Rng rng; rng.x = st.x; rng.y = st.y; rng.z = st.z; rng.w = st.w;
+        V3 o, d;
+        init_ray(p.cam, p.width, p.height, px, py, rng, o, d);
+        q.q0[i] = f4(o, 1.0f);
+        q.q1[i] = f4(d, 1.0f);
+        q.q2[i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(pix));
+        q.q3[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        q.q4[i] = make_uint4(rng.x, rng.y, rng.z, rng.w);
+    }
+}
+
+__global__ void k_raygen_probe(FrameParams p, long long first, long long n, float4* out3) {
+    long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int px, py;
+    ray_index_to_morton((int)(first + k), p.width, px, py);
+    int pix = py * p.width + px;
+    uint4 st = p.rng_table[pix];
+    Rng rng; rng.x = st.x; rng.y = st.y; rng.z = st.z; rng.w = st.w;
+    V3 o, d;
+    init_ray(p.cam, p.width, p.height, px, py, rng, o, d);
+    p.rng_table[pix] = make_uint4(rng.x, rng.y, rng.z, rng.w);
+    out3[3 * k + 0] = make_float4(__int_as_float(px), __int_as_float(py), o.x, o.y);
+    out3[3 * k + 1] = make_float4(o.z, d.x, d.y, d.z);
+    out3[3 * k + 2] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+}
+
+// ------------------------------------------------------------------ extend (closest hit)
+__global__ void __launch_bounds__(PT_TRACE_THREADS)
+k_extend(FrameParams p, int bounce, int qi) {
+    const int lane = threadIdx.x & 31;
+    BounceCounters* c = p.counters + bounce;
+    const int n = c->n_paths;
+    const PathQueue q = p.queue[qi];
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&c->fetch_extend, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        if (i < n) {
+            float4 ro = q.q0[i], rd = q.q1[i];
+            HitRec h; h.t = 1e20f; h.u = 0.0f; h.v = 0.0f; h.tri = -1;     // Iterative.comp:232
+            traverse<false>(p.scene, xyz(ro), xyz(rd), h);
+            p.hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+        }
+    }
+}
+
+// ------------------------------------------------------------------ shade
+template <int MODEL>
+__global__ void __launch_bounds__(PT_STREAM_THREADS)
+k_shade(FrameParams p, int bounce, int qi) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    BounceCounters* c = p.counters + bounce;
+    const int n = c->n_paths;
+    const PathQueue qin = p.queue[qi], qout = p.queue[qi ^ 1];
+    const ShadowQueue sq = p.shadow;
+    const SceneDev& s = p.scene;
+    const int warps_total = (gridDim.x * blockDim.x) >> 5;
+    const int warp_id = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const float neePdf = 0.5f / s.total_light_area;             // Iterative.comp:203
+
+    for (int base = warp_id * 32; base < n; base += warps_total * 32) {
+        const int i = base + lane;
+        bool alive = false, has_shadow = false;
+        // outputs
+        V3 vpos = v3(0.0f), newdir = v3(0.0f), thr = v3(0.0f), contrib = v3(0.0f), L = v3(0.0f), ldir = v3(0.0f), lorg = v3(0.0f);
+        float pdf0 = 0.0f, pdf1 = 0.0f, tmax = 0.0f;
+        int pix = 0;
+        Rng rng; rng.x = rng.y = rng.z = rng.w = 0;
+        if (i < n) {
+            float4 a0 = qin.q0[i], a1 = qin.q1[i], a2 = qin.q2[i], a3 = qin.q3[i];
+            uint4 a4 = qin.q4[i];
+            float4 hit = p.hits[i];
+            V3 ro = xyz(a0), rd = xyz(a1);
+            pdf0 = a0.w; pdf1 = a1.w;
+            thr = xyz(a2); pix = __float_as_int(a2.w);
+            contrib = xyz(a3);
+            rng.x = a4.x; rng.y = a4.y; rng.z = a4.z; rng.w = a4.w;
+            int tri = __float_as_int(hit.w);
+            if (tri < 0) {
+                // miss: sky radiance, NOT MIS weighted (Iterative.comp:251-255), store + freeRNG (:262-264)
+                contrib = contrib + thr * v3(s.env[0], s.env[1], s.env[2]);
+                float4 acc = p.accum[pix];
+                p.accum[pix] = make_float4(acc.x + contrib.x, acc.y + contrib.y, acc.z + contrib.z, 1.0f);
+                p.rng_table[pix] = make_uint4(rng.x, rng.y, rng.z, rng.w);
+            } else {
+                // GetInterpolatedVertex, Geometry.glsl:315-337 + Iterative.comp:236-240
+                const float4* tp = s.tris + 5 * (size_t)tri;
+                float4 t2 = __ldg(tp + 2), t3 = __ldg(tp + 3), t4 = __ldg(tp + 4);
+                float hu = hit.y, hv = hit.z, hw = 1.0f - hit.y - hit.z;
+                V3 vnormal = v3(t3.w, t4.x, t4.y);
+                float tu = t2.w * hu + t3.y * hv + t2.y * hw;
+                float tv = t3.x * hu + t3.z * hv + t2.z * hw;
+                uint32_t matId = __float_as_uint(t4.z);
+                vpos = ro + rd * hit.x;
+                vpos = vpos + 0.003f * vnormal;
+                V3 viewDir = -rd;
+
+                Material mat = make_material(s, matId, tu, tv);
+                Interaction it = make_interaction(vnormal, viewDir);
+
+                V3 idt = thr;
+                if (bounce != 0) {                              // Iterative.comp:256-261
+                    float dist = distance(ro, vpos);
+                    float oldMis = mis_weight(pdf0, pdf1);
+                    float g = 0.5f * avdot(vnormal, viewDir) / (dist * dist);
+                    pdf0 = pdf0 * g;
+                    pdf1 = pdf1 * g;
+                    idt = (thr / oldMis) * pdf0 / (pdf0 + pdf1 + neePdf);
+                }
+                contrib = contrib + idt * mat.emission;
+
+                // GenerateLightSample, Iterative.comp:113-147
+                V3 lpos, lnrm; uint32_t lmat;
+                random_light_vertex(s, rng, lpos, lnrm, lmat);
+                float lightPdf = 1.0f / s.total_light_area;
+                float radius = distance(lpos, vpos);
+                tmax = radius - 0.005f;
+                ldir = normalize(lpos - vpos);
+                {
+                    Interaction li = it;
+                    set_incoming(li, ldir);
+                    float bouncePdf = pdf_direction<MODEL>(mat, li) * avdot(lnrm, -ldir) / (radius * radius);
+                    V3 lightThroughput = thr * bsdf<MODEL>(mat, li) * li.ndi * avdot(lnrm, -ldir) *
+                                         mis_weight(lightPdf, bouncePdf) / (lightPdf * radius * radius);
+                    float4 le = __ldg(&s.materials[lmat >> 1].emission_flag);
+                    L = lightThroughput * xyz(le);              // Iterative.comp:279
+                }
+                lorg = vpos + 0.001f * vnormal;
+                has_shadow = true;
+
+                // BSDF sample, Iterative.comp:282-288
+                newdir = importance_sample<MODEL>(mat, it, rng, pdf0, pdf1);
+                thr = thr * (bsdf<MODEL>(mat, it) * it.ndi * mis_weight(pdf0, pdf1) / pdf0);
+
+                // Russian roulette, Iterative.comp:290-301
+                float continuation = gmin(gmax(thr.x, gmax(thr.y, thr.z)), 1.0f);
+                thr = thr / continuation;
+                bool terminate = (rng.next() > continuation) || (bounce > p.max_depth - 2);
+                alive = !terminate;
+                if (terminate) p.rng_table[pix] = make_uint4(rng.x, rng.y, rng.z, rng.w);   // freeRNG
+            }
+        }
+        // ---- compaction: one atomic per warp per queue
+        unsigned m_alive = __ballot_sync(0xffffffffu, alive);
+        unsigned m_shadow = __ballot_sync(0xffffffffu, has_shadow);
+        int base_alive = 0, base_shadow = 0;
+        if (lane == 0) {
+            if (m_alive) base_alive = atomicAdd(&c[1].n_paths, __popc(m_alive));
+            if (m_shadow) base_shadow = atomicAdd(&c->n_shadow, __popc(m_shadow));
+        }
+        base_alive = __shfl_sync(0xffffffffu, base_alive, 0);
+        base_shadow = __shfl_sync(0xffffffffu, base_shadow, 0);
+        int dest = ~pix;
+        if (alive) {
+            int j = base_alive + __popc(m_alive & lt_mask);
+            dest = j;
+            qout.q0[j] = f4(vpos, pdf0);
+            qout.q1[j] = f4(newdir, pdf1);
+            qout.q2[j] = f4(thr, __int_as_float(pix));
+            qout.q4[j] = make_uint4(rng.x, rng.y, rng.z, rng.w);
+            // q3 (contribution) is written by k_shadow once visibility is known
+        }
+        if (has_shadow) {
+            int k = base_shadow + __popc(m_shadow & lt_mask);
+            sq.s0[k] = f4(lorg, tmax);
+            sq.s1[k] = f4(ldir, __int_as_float(dest));
+            sq.s2[k] = f4(L, 0.0f);
+            sq.s3[k] = f4(contrib, 0.0f);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ shadow (any hit) + NEE add + store
+__global__ void __launch_bounds__(PT_TRACE_THREADS)
+k_shadow(FrameParams p, int bounce, int qi_next) {
+    const int lane = threadIdx.x & 31;
+    BounceCounters* c = p.counters + bounce;
+    const int n = c->n_shadow;
+    const ShadowQueue sq = p.shadow;
+    const PathQueue qn = p.queue[qi_next];
+    while (true) {
+        int base = 0;
+        if (lane == 0) base = atomicAdd(&c->fetch_shadow, 32);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        int i = base + lane;
+        if (i < n) {
+            float4 s0 = sq.s0[i], s1 = sq.s1[i];
+            HitRec h; h.t = s0.w; h.u = 0.0f; h.v = 0.0f; h.tri = -1;
+            bool occluded = traverse<true>(p.scene, xyz(s0), xyz(s1), h);
+            float4 s2 = sq.s2[i], s3 = sq.s3[i];
+            V3 contrib = xyz(s3);
+            if (!occluded) contrib = contrib + xyz(s2);        // Iterative.comp:278-280
+            int dest = __float_as_int(s1.w);
+            if (dest >= 0) {
+                qn.q3[dest] = f4(contrib, 0.0f);
+            } else {
+                int pix = ~dest;                                // imageStore, Iterative.comp:295
+                float4 acc = p.accum[pix];
+                p.accum[pix] = make_float4(acc.x + contrib.x, acc.y + contrib.y, acc.z + contrib.z, 1.0f);
+            }
+        }
+    }
+}
+
+__global__ void k_tally(FrameParams p) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long closest = 0, shadow = 0;
+    for (int b = 0; b < p.max_depth; b++) { closest += p.counters[b].n_paths; shadow += p.counters[b].n_shadow; }
+    p.totals[0] += closest; p.totals[1] += shadow; p.totals[2] += (unsigned long long)p.width * p.height;
+}
+
+int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, cudaEvent_t* evs) {
+    // evs (optional): one event recorded before every kernel and one after the last, for per-stage timing
+    int launches = 0;
+    cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 1), st);
+    if (evs) cudaEventRecord(evs[launches], st);
+    k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p); launches++;
+    int qi = 0;
+    for (int b = 0; b < p.max_depth; b++) {
+        if (evs) cudaEventRecord(evs[launches], st);
+        k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi); launches++;
+        if (evs) cudaEventRecord(evs[launches], st);
+        if (p.model == 1) k_shade<1><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, b, qi);
+        else k_shade<0><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, b, qi);
+        launches++;
+        if (evs) cudaEventRecord(evs[launches], st);
+        k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi ^ 1); launches++;
+        qi ^= 1;
+    }
+    if (evs) cudaEventRecord(evs[launches], st);
+    k_tally<<<1, 32, 0, st>>>(p); launches++;
+    if (evs) cudaEventRecord(evs[launches], st);
+    return launches;
+}
+
+void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st) {
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 0) k_raygen_probe<<<blocks, 256, 0, st>>>(p, first, n, out3);
+}
+
+// ------------------------------------------------------------------ RNG table seeding
+// Renderer.cpp:545-553 draws every lane from uniform_int_distribution(129, UINT32_MAX) (HybridTaus
+// needs its Tausworthe lanes > 128). Here: splitmix64 of (seed, pixel, lane), folded into [129, 2^32).
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__global__ void k_seed_rng(uint4* table, long long n, unsigned long long seed) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long a = splitmix64(seed ^ splitmix64((unsigned long long)i * 2 + 0));
+    unsigned long long b = splitmix64(seed ^ splitmix64((unsigned long long)i * 2 + 1));
+    auto lanefix = [](unsigned v) { return v < 129u ? v + 129u : v; };
+    table[i] = make_uint4(lanefix((unsigned)a), lanefix((unsigned)(a >> 32)), lanefix((unsigned)b), lanefix((unsigned)(b >> 32)));
+}
+void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st) {
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 0) k_seed_rng<<<blocks, 256, 0, st>>>(table, n, seed);
+}
+
+// ------------------------------------------------------------------ resolve (Present.frag:13-37)
+__global__ void k_resolve(const float4* __restrict__ accum, long long n, unsigned num_samples, float* rgb_f32,
+                          unsigned char* rgb_u8) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f, W = 11.2f;
+    const float white = ((W * (A * W + C * B) + D * E) / (W * (A * W + B) + D * F)) - E / F;
+    float4 a = accum[i];
+    float in[3] = {a.x, a.y, a.z};
+    for (int c = 0; c < 3; c++) {
+        float color = in[c] / (float)num_samples;
+        color = 1.68f * color;                                 // kExposure, Renderer.cpp:18
+        color *= 2.0f;
+        color = ((color * (A * color + C * B) + D * E) / (color * (A * color + B) + D * F)) - E / F;
+        color /= white;
+        color = powf(color, 1.0f / 2.2f);
+        if (rgb_f32) rgb_f32[3 * i + c] = color;
+        if (rgb_u8) rgb_u8[3 * i + c] = (unsigned char)(gmin(gmax(color, 0.0f), 1.0f) * 255.0f + 0.5f);
+    }
+}
+void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
+                    cudaStream_t st) {
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 0) k_resolve<<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
+}
+
+// occupancy-derived persistent grid sizes
+void query_launch_dims(int device, LaunchDims* out) {
+    cudaDeviceProp prop;
+    cudaGetDeviceProperties(&prop, device);
+    int per_sm_ext = 1, per_sm_shadow = 1, per_sm_shade = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend, PT_TRACE_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow, PT_TRACE_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0>, PT_STREAM_THREADS, 0);
+    int per = per_sm_ext < per_sm_shadow ? per_sm_ext : per_sm_shadow;
+    if (per < 1) per = 1;
+    if (per_sm_shade < 1) per_sm_shade = 1;
+    out->sm_count = prop.multiProcessorCount;
+    out->extend_blocks = prop.multiProcessorCount * per;
+    out->stream_blocks = prop.multiProcessorCount * per_sm_shade;
+}
+
+}  // namespace pt

@@ -1,0 +1,49 @@
+// pt_kernels.h -- launch wrappers of the sm_100a kernels (implemented in pt_kernels.cu).
+#pragma once
+#include "pt_layout.h"
+
+namespace pt {
+
+// Per-frame device counters: one row per bounce. Zeroed once per frame, so no kernel ever has to
+// reset a counter another kernel is still reading.
+struct BounceCounters {
+    int n_paths;      // size of the path queue entering this bounce (written by raygen / previous shade)
+    int n_shadow;     // size of the shadow queue produced by this bounce's shade
+    int fetch_extend; // persistent-kernel work cursors
+    int fetch_shadow;
+};
+
+struct FrameParams {
+    SceneDev scene;
+    CameraRec cam;
+    int width, height;
+    int max_depth;
+    int model;
+    uint4* rng_table;     // per pixel
+    float4* accum;        // per pixel, running sum
+    PathQueue queue[2];
+    ShadowQueue shadow;
+    float4* hits;         // per queue slot
+    BounceCounters* counters;   // [max_depth + 1]
+    unsigned long long* totals; // [0] closest rays, [1] shadow rays, [2] paths
+};
+
+struct LaunchDims { int sm_count; int extend_blocks; int stream_blocks; };
+
+// fixed ray batches (AoS rays: n x {o.xyz, -, d.xyz, tmax})
+void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
+                          const LaunchDims& dims, cudaStream_t st);
+void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
+                      const LaunchDims& dims, cudaStream_t st);
+
+// one frame = raygen + max_depth x (extend, shade, shadow) + tally; returns number of kernels launched
+// kernel k of a frame: 0 = raygen, 1+3b = extend, 2+3b = shade, 3+3b = shadow (bounce b), last = tally
+int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, cudaEvent_t* evs);
+
+void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);
+void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st);
+void query_launch_dims(int device, LaunchDims* out);
+void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
+                    cudaStream_t st);
+
+}  // namespace pt

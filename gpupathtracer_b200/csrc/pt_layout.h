@@ -1,0 +1,71 @@
+// pt_layout.h -- HBM data layout of libb200pt (see DESIGN.md "Data layout in HBM").
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace pt {
+
+// ---- BVH, PT_BVH_REFERENCE layout -------------------------------------------------------------
+// The reference stores one 32-B node per child and addresses sibling pairs at (firstChild,
+// firstChild+1) with firstChild ODD (root = 0, its children = 1,2; BVH.cpp:2224-2255), so every
+// pair straddles a 64-B boundary. Here one 64-B aligned record holds the pair = 4 x 128-bit loads
+// from 2 sectors of one line:
+//   q[0] = {c0.min.xyz, link0}   q[1] = {c0.max.xyz, 0}
+//   q[2] = {c1.min.xyz, link1}   q[3] = {c1.max.xyz, 0}
+// link >= 1 : index of the pair record holding that child's children
+// link <  0 : leaf, ~link = index of its first record in the leaf triangle stream
+// Topology, fp32 boxes, child order and leaf order are those of the reference tree, so traversal
+// visits the same nodes in the same order.
+struct BvhPair { float4 q[4]; };
+
+// ---- leaf triangle stream ----------------------------------------------------------------------
+// The reference walks leaf -> reference list (4 B) -> 80-B triangle. Here the reference list is
+// resolved at upload time into a stream of 48-B intersection records in reference-list order:
+//   r[0] = {p0.xyz, e1.x}  r[1] = {e1.y, e1.z, e2.x, e2.y}  r[2] = {e2.z, id, 0, 0}
+// id = triangle index, stored as ~index when the reference-list entry carried the end-of-leaf
+// marker (negative entry, BVH.cpp:2117). Entry "0" cannot carry the marker in the reference
+// (-0 == 0): that leaf runs on into the next one; the stream reproduces this because the marker
+// is copied, not recomputed.
+struct LeafTri { float4 r[3]; };
+
+// ---- shading tables ------------------------------------------------------------------------------
+// Full reference triangle (5 x vec4, Scene.cpp:339-347 upload) is kept for shading: uv, normal, matId.
+struct MaterialRec { float4 albedo_tex, emission_flag, props_tex; };   // == pt_material
+struct TextureRec { int width, height; const float4* texels; };
+
+struct CameraRec {
+    float lower_left[3], horizontal[3], vertical[3], position[3], u[3], v[3];
+    float lens_radius;
+};
+
+// ---- wavefront path state (SoA of float4 arrays, compacted every bounce, ping-pong) -----------
+//   q0 = {ray.o.xyz, bxdfPdf0}      (ray.o doubles as lastPosition, Iterative.comp:286-288)
+//   q1 = {ray.d.xyz, bxdfPdf1}      (viewDir == -ray.d)
+//   q2 = {throughput.xyz, pixel index}
+//   q3 = {contribution.xyz, bounce i}
+//   q4 = HybridTaus state (uvec4)
+struct PathQueue {
+    float4* q0; float4* q1; float4* q2; float4* q3; uint4* q4;
+};
+
+// One NEE shadow item (64 B): ray + what to do with the answer.
+//   s0 = {o.xyz, tmax}  s1 = {d.xyz, dest}  s2 = {L.xyz (already times Le), 0}  s3 = {contribution.xyz, 0}
+// dest >= 0 : path continues in slot `dest` of the next queue; q3.xyz = contribution (+ L if visible)
+// dest <  0 : path ended by Russian roulette; accum[~dest] += contribution (+ L if visible)
+struct ShadowQueue { float4* s0; float4* s1; float4* s2; float4* s3; };
+
+struct SceneDev {
+    const BvhPair* pairs;
+    const LeafTri* leaf_tris;
+    int n_leaf_tris;
+    const float4* tris;          // n_tris x 5
+    const MaterialRec* materials;
+    const TextureRec* textures;
+    int n_textures;
+    const float2* lights;        // {cumulative area, tri index bits}
+    int n_lights;
+    float total_light_area;
+    float env[3];
+};
+
+}  // namespace pt

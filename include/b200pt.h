@@ -1,0 +1,181 @@
+/* include/b200pt.h -- C ABI of libb200pt.so, the B200-native replacement for the OpenGL hot path of
+ * saadam1n/GPUPathTracer (the src/shaders wavefront stages + the src/core BVH build / flatten / scene
+ * upload). Plain pointers and sizes only; no torch, no C++ types. Every entry point cites the
+ * reference interface it replaces (paths relative to the reference's src/).
+ *
+ * The reference has no FFI: the seam is the four C++ classes Renderer / Scene / BoundingVolumeHierarchy /
+ * Camera driven by main() (Program.cpp:69-152). INTEGRATION.md shows the binding a maintainer adds.
+ *
+ * Conventions: every function returning int returns PT_OK (0) or a negative pt_status and never calls
+ * exit() (the reference prints and exit()s, e.g. Scene.cpp:134,258; BVH.cpp:2146). pt_last_error() returns
+ * the message of the calling thread's last failure. A context is bound to one CUDA device, is driven by
+ * one host thread at a time, and owns all its device memory; host arrays are copied during the call.
+ * There is no CPU fallback: pt_create fails with PT_ERR_NO_DEVICE when no sm_100 device is usable.
+ */
+#ifndef B200PT_H
+#define B200PT_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200PT_ABI_VERSION 1
+
+typedef enum pt_status {
+    PT_OK = 0,
+    PT_ERR_INVALID = -1,      /* bad argument / call order */
+    PT_ERR_NO_DEVICE = -2,    /* no usable CUDA device (the product has no CPU path) */
+    PT_ERR_CUDA = -3,         /* a CUDA runtime call failed; message has the cudaError string */
+    PT_ERR_IO = -4,           /* file could not be read / written */
+    PT_ERR_UNSUPPORTED = -5,
+    PT_ERR_LIMIT = -6         /* e.g. BVH deeper than the traversal stack (reference: exit(-1), BVH.cpp:2144-2147) */
+} pt_status;
+
+typedef struct pt_context pt_context;
+
+/* microfacet model: the reference executes Trowbridge-Reitz (Microfacet.glsl:90-92) and carries Beckmann
+ * as an alternate (Microfacet.glsl:35-55); both are selectable at run time here. */
+enum { PT_MICROFACET_GGX = 0, PT_MICROFACET_BECKMANN = 1 };
+
+/* traversal layout: PT_BVH_REFERENCE keeps the reference tree's topology and fp32 boxes (results are
+ * bit-identical to IfIfClosestHit/IfIfAnyHit); PT_BVH_WIDE is the compressed 8-wide layout. */
+enum { PT_BVH_REFERENCE = 0, PT_BVH_WIDE = 1 };
+
+typedef struct pt_config {
+    int32_t width, height;        /* multiples of 8 (Iterative.comp:163-172); Program.cpp:22-23 hard-codes 1280x720 */
+    int32_t max_depth;            /* max closest-hit rays per path; 66 == the reference's `i > 64` cap (Iterative.comp:293) */
+    int32_t microfacet_model;     /* PT_MICROFACET_* */
+    int32_t device;               /* CUDA device ordinal */
+    int32_t bvh_layout;           /* PT_BVH_* used by pt_render_frames / pt_trace_* */
+    int32_t reserved[6];
+} pt_config;
+
+/* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
+typedef struct pt_camera {
+    float lower_left[3], horizontal[3], vertical[3], position[3], u[3], v[3];
+    float lens_radius;
+} pt_camera;
+
+/* Material k is addressed by matId = 2*k (Scene.cpp:153-158); k = 0 is the sky (Scene.cpp:236-241).
+ * Replaces MaterialInstance{albedoHandle, propertiesHandle, emission, isEmissive} (Scene.h:12-17): bindless
+ * texture handles become indices into the texture array, and the 1x1 RGBA32F "colour textures" of
+ * Texture2D::SetColor (Scene.cpp:97-103) become inline constants (tex index < 0). */
+typedef struct pt_material {
+    float albedo[3];   int32_t albedo_tex;
+    float emission[3]; int32_t is_emissive;
+    float props[3];    int32_t props_tex;      /* props = (unused, roughness source g, metallic b), Scene.cpp:103 */
+} pt_material;
+
+typedef struct pt_texture {        /* RGBA32F, row-major, sampled GL_LINEAR + GL_REPEAT (Texture.cpp:123-131) */
+    int32_t width, height;
+    const float* rgba;
+} pt_texture;
+
+typedef struct pt_light {          /* LightTriangleInfo after the prefix sum, Scene.cpp:296-330 */
+    float cumulative_area;
+    uint32_t tri_index;
+} pt_light;
+
+typedef struct pt_counters {
+    uint64_t closest_rays, shadow_rays, paths, frames;
+    uint64_t kernel_launches;      /* kernels of this library launched since pt_create */
+} pt_counters;
+
+typedef struct pt_bvh_stats {
+    int32_t n_nodes, n_refs, n_leaves, max_depth;
+    float sah_cost;                /* CalculateCost, BVH.cpp:2174-2195 */
+    float build_ms;
+} pt_bvh_stats;
+
+int pt_abi_version(void);
+const char* pt_last_error(void);
+
+/* ---- lifetime: Renderer::Initialize / CleanUp (Renderer.cpp:448-636, :638-647) ---- */
+int pt_create(const pt_config* cfg, pt_context** out);
+void pt_destroy(pt_context* ctx);
+
+/* ---- scene tables: the uploads of Scene::LoadScene (Scene.cpp:339-354) ---- */
+/* tris: n x 20 floats in the CompactTriangle order (math/Triangle.h:13-29) with position1/2 holding the
+ * EDGES e1 = p1-p0, e2 = p2-p0 (Scene.cpp:334-337), i.e. exactly the bytes of the reference's vertexBuf. */
+int pt_set_triangles(pt_context* ctx, const float* tris, int64_t n);
+int pt_set_materials(pt_context* ctx, const pt_material* mats, int32_t n_mats, const pt_texture* tex, int32_t n_tex);
+int pt_set_lights(pt_context* ctx, const pt_light* lights, int32_t n, float total_light_area); /* lightBuf + totalLightArea */
+int pt_set_environment_color(pt_context* ctx, const float rgb[3]);   /* LoadEnvironmnet "GENERATE COLOR", Renderer.cpp:242-260 */
+
+/* ---- BVH: BoundingVolumeHierarchy::BuildBinnedSpatial (BVH.cpp:2197-2293) ---- */
+/* Inject a tree in the reference's serialised form: nodes = n_nodes x {float3 min; int32 data0; float3 max;
+ * int32 data1} (NewLayout, BVH.cpp:2261-2277), refs = the leaf reference list (ConvertIntoLeaf, :2107-2121).
+ * Re-laid out on upload for 128-bit loads; topology, boxes and leaf order are preserved. */
+int pt_set_bvh(pt_context* ctx, const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs);
+/* Build with this library's own SAH/SBVH builder from the triangles given to pt_set_triangles and upload it. */
+int pt_build_bvh(pt_context* ctx, pt_bvh_stats* stats);
+/* The same builder without a context or a device (pure host work): arrays are malloc()ed, release with pt_free. */
+int pt_bvh_build_host(const float* tris, int64_t n, int32_t n_threads, float** nodes, int32_t* n_nodes,
+                      int32_t** refs, int32_t* n_refs, pt_bvh_stats* stats);
+void pt_free(void* p);
+/* Read back the tree in the reference's serialised form (what nodesVec/referenceVec hold, BVH.cpp:2291-2292);
+ * call with NULL arrays to query sizes. */
+int pt_get_bvh(pt_context* ctx, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs);
+
+/* ---- host-side scene assembly (no device work): Scene.cpp:263-337 ---- */
+/* verts: n_tris x 3 x {pos.xyz, normal.xyz, uv.xy} (Vertex, math/Vertex.h), mat_ids: per triangle (first
+ * vertex's, Scene.cpp:289). out_tris_abs: n x 20 floats with ABSOLUTE positions (the form the BVH builder
+ * takes, Scene.cpp:294); geometric normal flipped to agree with the mean vertex normal (Scene.cpp:277-287). */
+int pt_assemble_triangles(const float* verts, const uint32_t* mat_ids, int64_t n_tris, float* out_tris_abs);
+/* emitter list sorted by area + running sum (Scene.cpp:296-331); returns count, writes total area. */
+int pt_build_light_table(const float* tris_abs, int64_t n_tris, const pt_material* mats, int32_t n_mats,
+                         pt_light* out_lights, int32_t capacity, float* total_area);
+/* e1/e2 pre-subtraction in place (Scene.cpp:334-337). */
+void pt_presubtract_edges(float* tris, int64_t n_tris);
+
+/* ---- camera: Camera::GenerateImagePlane (math/Camera.cpp:6-22) + Shader::LoadCamera ---- */
+void pt_camera_image_plane(float aspect, float fov, float focus, float aperture, const float pos[3],
+                           const float rot[3], pt_camera* out);
+int pt_set_camera(pt_context* ctx, const pt_camera* cam);
+
+/* ---- RNG tables: Renderer.cpp:545-553 (uvec4 per pixel, every lane >= 129) ---- */
+int pt_set_rng(pt_context* ctx, const uint32_t* state4);          /* width*height*4 words */
+int pt_seed_rng(pt_context* ctx, uint64_t seed);                   /* generated on the device; seed^rank decorrelates GPUs */
+int pt_get_rng(pt_context* ctx, uint32_t* state4);
+
+/* ---- rendering: Renderer::RenderFrame / ResetSamples / GetNumSamples (Renderer.cpp:651-695) ---- */
+int pt_render_frames(pt_context* ctx, int32_t n_frames);           /* each frame = +1 sample for every pixel */
+int pt_reset_samples(pt_context* ctx);
+uint32_t pt_num_samples(pt_context* ctx);
+int pt_synchronize(pt_context* ctx);
+/* accum = running SUM, RGBA32F, alpha 1 (Iterative.comp:263,295). */
+int pt_download_accum(pt_context* ctx, float* rgba);
+void* pt_accum_device_ptr(pt_context* ctx);                        /* for NCCL reduce across ranks (width*height*4 floats) */
+int pt_set_accum_device_ptr(pt_context* ctx, void* dev_rgba);      /* render into caller-owned device memory */
+/* Renderer::Present (Present.frag:13-37): /numSamples, Uncharted-2, gamma 2.2 -> RGB float and/or 8-bit. */
+int pt_resolve(pt_context* ctx, uint32_t num_samples, float* rgb_f32_or_null, uint8_t* rgb_u8_or_null);
+int pt_save_screenshot(pt_context* ctx, const char* path);         /* Renderer::SaveScreenshot (Renderer.cpp:697-705); .ppm/.pfm */
+
+/* ---- fixed ray batches (parity + microbenchmark entry points) ----
+ * rays: n x 8 floats {o.xyz, unused, d.xyz, tmax}; hits: n x {t, u, v, triId(int32)}; miss = {tmax, 0, 0, -1}.
+ * IfIfClosestHit (common/BVH.glsl:634-767) / IfIfAnyHit (:769-854) over host or device buffers. */
+int pt_trace_closest(pt_context* ctx, const float* rays, int64_t n, float* hits);
+int pt_trace_any(pt_context* ctx, const float* rays, int64_t n, uint8_t* flags);
+int pt_trace_closest_device(pt_context* ctx, const void* d_rays, int64_t n, void* d_hits);
+int pt_trace_any_device(pt_context* ctx, const void* d_rays, int64_t n, void* d_flags);
+
+/* ---- per-stage probes (parity of raygen on its own; rng table is advanced like the shader does) ---- */
+/* out: n x 12 floats {pixel.x, pixel.y (int bits), o.xyz, d.xyz, 0,0,0,0} for ray indices [first, first+n). */
+int pt_raygen_probe(pt_context* ctx, int64_t first, int64_t n, float* out);
+
+int pt_get_counters(pt_context* ctx, pt_counters* out);
+/* CUDA-event milliseconds of the last pt_render_frames / pt_trace_*_device call (device time only). */
+float pt_last_device_ms(pt_context* ctx);
+/* Per-stage device time of the last pt_render_frames call, from CUDA events recorded on the library's stream
+ * between kernels: out = {raygen, extend, shade, shadow, tally} milliseconds summed over the call's frames. */
+int pt_set_stage_timing(pt_context* ctx, int on);
+int pt_get_stage_ms(pt_context* ctx, float out[5]);
+/* cudaStream_t the library launches on (for callers that record their own events). */
+void* pt_stream(pt_context* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

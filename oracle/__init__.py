@@ -1,0 +1,225 @@
+"""oracle -- TEST INFRASTRUCTURE ONLY: ctypes bindings of the CPU checkers.
+
+  oracle/libpt_oracle.so      our CPU restatement of the reference's GLSL path (oracle/pt_oracle.cpp)
+  oracle/_ref/libref_shim.so  the reference's OWN C++ (SBVH builder, AABB, Camera, HybridTaus, tonemap)
+                              compiled in place from /root/reference by oracle/Makefile
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(_HERE, "libpt_oracle.so")
+REF_SO = os.path.join(_HERE, "_ref", "libref_shim.so")
+REFERENCE_ROOT = "/root/reference"
+
+
+def build(ref=True):
+    subprocess.run(["make", "-C", _HERE, "oracle"], check=True, capture_output=True)
+    if ref and os.path.isdir(REFERENCE_ROOT):
+        subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
+
+
+class OrTexture(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("rgba", C.POINTER(C.c_float))]
+
+
+class OrScene(C.Structure):
+    _fields_ = [("nodes", C.c_void_p), ("n_nodes", C.c_int), ("refs", C.c_void_p), ("n_refs", C.c_int),
+                ("tris", C.c_void_p), ("n_tris", C.c_int), ("materials", C.c_void_p), ("n_materials", C.c_int),
+                ("textures", C.POINTER(OrTexture)), ("n_textures", C.c_int), ("lights", C.c_void_p),
+                ("n_lights", C.c_int), ("total_light_area", C.c_float), ("env_color", C.c_float * 3)]
+
+
+class OrCamera(C.Structure):
+    _fields_ = [("lower_left", C.c_float * 3), ("horizontal", C.c_float * 3), ("vertical", C.c_float * 3),
+                ("position", C.c_float * 3), ("u", C.c_float * 3), ("v", C.c_float * 3), ("lens_radius", C.c_float)]
+
+
+class OrConfig(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("max_depth", C.c_int), ("microfacet_model", C.c_int),
+                ("n_threads", C.c_int)]
+
+
+class OrCounters(C.Structure):
+    _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("node_pairs", C.c_uint64),
+                ("leaf_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("paths", C.c_uint64)]
+
+    def as_dict(self):
+        return {k: int(getattr(self, k)) for k, _ in self._fields_}
+
+
+_lib = None
+_ref = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(ORACLE_SO):
+            build(ref=False)
+        _lib = C.CDLL(ORACLE_SO)
+        _lib.or_tonemap.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        _lib.or_slab_test.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        _lib.or_slab_test.restype = C.c_int
+        _lib.or_image_plane.argtypes = [C.c_float] * 4 + [C.c_void_p, C.c_void_p, C.POINTER(OrCamera)]
+        _lib.or_hybrid_taus.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        _lib.or_trace_closest.argtypes = [C.POINTER(OrScene), C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(OrCounters), C.c_int]
+        _lib.or_trace_any.argtypes = [C.POINTER(OrScene), C.c_void_p, C.c_int64, C.c_void_p, C.POINTER(OrCounters), C.c_int]
+        _lib.or_trace_closest_bruteforce.argtypes = [C.POINTER(OrScene), C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+        _lib.or_render.argtypes = [C.POINTER(OrScene), C.POINTER(OrCamera), C.POINTER(OrConfig), C.c_void_p, C.c_void_p,
+                                   C.c_int, C.POINTER(OrCounters)]
+        _lib.or_raygen.argtypes = [C.POINTER(OrCamera), C.POINTER(OrConfig), C.c_float, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
+    return _lib
+
+
+def have_ref():
+    return os.path.exists(REF_SO)
+
+
+def ref():
+    """The reference's own code; None when oracle/_ref has not been built (e.g. no /root/reference)."""
+    global _ref
+    if _ref is None:
+        if not os.path.exists(REF_SO):
+            return None
+        _ref = C.CDLL(REF_SO)
+        _ref.ref_build_sbvh.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int),
+                                        C.POINTER(C.POINTER(C.c_int)), C.POINTER(C.c_int)]
+        _ref.ref_free.argtypes = [C.c_void_p]
+        _ref.ref_camera_image_plane.argtypes = [C.c_float] * 4 + [C.c_void_p, C.c_void_p, C.c_void_p]
+        _ref.ref_aabb_intersect.argtypes = [C.c_void_p] * 4 + [C.c_float, C.c_void_p]
+        _ref.ref_aabb_intersect.restype = C.c_int
+        _ref.ref_aabb_surface_area.argtypes = [C.c_void_p, C.c_void_p]
+        _ref.ref_aabb_surface_area.restype = C.c_float
+        _ref.ref_hybrid_taus.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        _ref.ref_tonemap_uncharted2.argtypes = [C.c_void_p, C.c_void_p]
+    return _ref
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def ref_build_sbvh(tris_abs):
+    """BoundingVolumeHierarchy::BuildBinnedSpatial (BVH.cpp:2197-2293) on absolute-position triangles.
+    Returns (nodes (n,8) float32 in NewLayout, refs int32). stdout of the reference is silenced."""
+    r = ref()
+    assert r is not None, "oracle/_ref/libref_shim.so not built"
+    t = np.ascontiguousarray(tris_abs, dtype=np.float32)
+    nodes_p, refs_p = C.POINTER(C.c_float)(), C.POINTER(C.c_int)()
+    nn, nr = C.c_int(), C.c_int()
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(1)
+    os.dup2(devnull, 1)
+    try:
+        rc = r.ref_build_sbvh(_p(t), t.shape[0], C.byref(nodes_p), C.byref(nn), C.byref(refs_p), C.byref(nr))
+    finally:
+        os.dup2(saved, 1)
+        os.close(saved)
+        os.close(devnull)
+    assert rc == 0
+    nodes = np.ctypeslib.as_array(nodes_p, shape=(nn.value, 8)).copy()
+    refs = np.ctypeslib.as_array(refs_p, shape=(nr.value,)).astype(np.int32).copy()
+    r.ref_free(nodes_p)
+    r.ref_free(refs_p)
+    return nodes, refs
+
+
+class Oracle:
+    """Scene tables + entry points of libpt_oracle.so. `scene` is a gpupathtracer_b200.Scene-like object
+    exposing tris (pre-subtracted), materials, lights, total_light_area, env_color, textures, nodes, refs."""
+
+    def __init__(self, scene, nodes=None, refs=None):
+        self.l = lib()
+        self.tris = np.ascontiguousarray(scene.tris, dtype=np.float32)
+        self.materials = np.ascontiguousarray(scene.materials, dtype=np.float32)
+        self.lights = np.ascontiguousarray(scene.lights, dtype=np.float32)
+        self.nodes = np.ascontiguousarray(nodes if nodes is not None else scene.nodes, dtype=np.float32)
+        self.refs = np.ascontiguousarray(refs if refs is not None else scene.refs, dtype=np.int32)
+        self.textures = [np.ascontiguousarray(t, dtype=np.float32) for t in getattr(scene, "textures", [])]
+        self.tex_arr = (OrTexture * max(1, len(self.textures)))()
+        for i, t in enumerate(self.textures):
+            self.tex_arr[i].width, self.tex_arr[i].height = t.shape[1], t.shape[0]
+            self.tex_arr[i].rgba = t.ctypes.data_as(C.POINTER(C.c_float))
+        s = OrScene()
+        s.nodes, s.n_nodes = _p(self.nodes), self.nodes.shape[0]
+        s.refs, s.n_refs = _p(self.refs), self.refs.shape[0]
+        s.tris, s.n_tris = _p(self.tris), self.tris.shape[0]
+        s.materials, s.n_materials = _p(self.materials), self.materials.shape[0]
+        s.textures, s.n_textures = self.tex_arr, len(self.textures)
+        s.lights, s.n_lights = _p(self.lights), self.lights.shape[0]
+        s.total_light_area = float(scene.total_light_area)
+        s.env_color = (C.c_float * 3)(*scene.env_color)
+        self.s = s
+
+    def trace_closest(self, rays, n_threads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        hits = np.zeros((rays.shape[0], 4), dtype=np.float32)
+        c = OrCounters()
+        self.l.or_trace_closest(C.byref(self.s), _p(rays), rays.shape[0], _p(hits), C.byref(c), n_threads)
+        return hits, c.as_dict()
+
+    def trace_any(self, rays, n_threads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        flags = np.zeros(rays.shape[0], dtype=np.uint8)
+        c = OrCounters()
+        self.l.or_trace_any(C.byref(self.s), _p(rays), rays.shape[0], _p(flags), C.byref(c), n_threads)
+        return flags, c.as_dict()
+
+    def trace_closest_bruteforce(self, rays, n_threads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        hits = np.zeros((rays.shape[0], 4), dtype=np.float32)
+        self.l.or_trace_closest_bruteforce(C.byref(self.s), _p(rays), rays.shape[0], _p(hits), n_threads)
+        return hits
+
+    @staticmethod
+    def camera(cam_array):
+        c = OrCamera()
+        a = np.asarray(cam_array, dtype=np.float32)
+        for i, name in enumerate(["lower_left", "horizontal", "vertical", "position", "u", "v"]):
+            setattr(c, name, (C.c_float * 3)(*a[3 * i:3 * i + 3]))
+        c.lens_radius = float(a[18])
+        return c
+
+    def render(self, cam_array, width, height, rng, accum, n_frames=1, max_depth=66, model=0, n_threads=0):
+        """In place on rng (px,4) uint32 and accum (h,w,4) float32. Returns counters."""
+        cam = self.camera(cam_array)
+        cfg = OrConfig(width, height, max_depth, model, n_threads)
+        c = OrCounters()
+        assert rng.dtype == np.uint32 and rng.flags.c_contiguous and accum.dtype == np.float32 and accum.flags.c_contiguous
+        self.l.or_render(C.byref(self.s), C.byref(cam), C.byref(cfg), _p(rng), _p(accum), n_frames, C.byref(c))
+        return c.as_dict()
+
+    def raygen(self, cam_array, width, height, rng, first, n):
+        cam = self.camera(cam_array)
+        cfg = OrConfig(width, height, 66, 0, 1)
+        out = np.zeros((n, 12), dtype=np.float32)
+        self.l.or_raygen(C.byref(cam), C.byref(cfg), float(self.s.total_light_area), _p(rng), first, n, _p(out))
+        return out
+
+
+def hybrid_taus(state4, n):
+    st = np.ascontiguousarray(state4, dtype=np.uint32).copy()
+    out = np.zeros(n, dtype=np.float32)
+    lib().or_hybrid_taus(_p(st), n, _p(out))
+    return out, st
+
+
+def image_plane(aspect, fov, focus, aperture, pos, rot):
+    c = OrCamera()
+    p = np.asarray(pos, dtype=np.float32); r = np.asarray(rot, dtype=np.float32)
+    lib().or_image_plane(aspect, fov, focus, aperture, _p(p), _p(r), C.byref(c))
+    return np.array(list(c.lower_left) + list(c.horizontal) + list(c.vertical) + list(c.position) + list(c.u) +
+                    list(c.v) + [c.lens_radius], dtype=np.float32)
+
+
+def tonemap(rgb_sum, num_samples):
+    a = np.ascontiguousarray(rgb_sum, dtype=np.float32).reshape(-1, 3)
+    out = np.zeros_like(a)
+    for i in range(a.shape[0]):
+        lib().or_tonemap(_p(a[i:i + 1]), num_samples, _p(out[i:i + 1]))
+    return out

@@ -1,0 +1,113 @@
+/* oracle/pt_oracle.h -- TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU restatement of the reference's live GLSL path-tracing path (saadam1n/GPUPathTracer,
+ * src/shaders/Iterative.comp + common/*.glsl) used as the parity checker for the CUDA
+ * kernels. Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+ * reference legs may load this library; the product (libb200pt.so) never does.
+ *
+ * PARITY STATUS: the reference ships no tests, golden vectors or known-answer fixtures
+ * (SURVEY.md section 4), and its GLSL cannot execute on this box (no GL stack), so the
+ * shader restatement is "parity unpinned" by the reference's own tests. What IS pinned,
+ * against the reference's own C++ compiled in place (oracle/_ref/libref_shim.so, see
+ * oracle/Makefile and tests/test_oracle_vs_ref.py):
+ *   - HybridTaus            vs Renderer.cpp:764-782   (bit-exact)
+ *   - slab test             vs math/AABB.cpp:102-113  (bit-exact on NaN-free inputs)
+ *   - image plane           vs math/Camera.cpp:6-22   (bit-exact)
+ *   - Uncharted-2 tonemap   vs Renderer.cpp:980-994   (bit-exact)
+ *   - the BVH it traverses  IS the reference builder's output (BVH.cpp:2197-2293)
+ *
+ * Float mode (stated, because GLSL does not pin one): IEEE-754 binary32, every operation
+ * separately rounded (built with -ffp-contract=off -fno-fast-math), division and sqrt
+ * correctly rounded, GLSL min()/max() = fminf()/fmaxf() (IEEE minNum/maxNum, which is what
+ * NVIDIA's FMNMX executes; identical to glm's ternaries whenever no operand is NaN),
+ * normalize(v) = v * (1/sqrt(dot(v,v))) and mix(x,y,a) = x*(1-a)+y*a as in glm.
+ */
+#ifndef PT_ORACLE_H
+#define PT_ORACLE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Scene tables exactly as the reference uploads them. */
+typedef struct OrTexture {
+    int width, height;     /* RGBA32F texels, row-major, GL_REPEAT + GL_LINEAR (Texture.cpp:123-131) */
+    const float* rgba;
+} OrTexture;
+
+typedef struct OrScene {
+    const float* nodes;    /* n_nodes x 8 floats: {min.xyz, data0(int bits), max.xyz, data1} BVH.cpp:2261-2277 */
+    int n_nodes;
+    const int32_t* refs;   /* reference list, negative = last of leaf (BVH.cpp:2107-2121) */
+    int n_refs;
+    const float* tris;     /* n_tris x 20 floats, 5 x vec4 layout, e1/e2 pre-subtracted (Scene.cpp:334-337) */
+    int n_tris;
+    /* material k (matId = 2k, Scene.cpp:153-158): 12 floats
+     *   [albedo.rgb, albedo_tex(int bits, <0: constant colour)]
+     *   [emission.rgb, isEmissive(int bits)]
+     *   [props.r, props.g = roughness source, props.b = metallic, props_tex(int bits, <0: constant)]
+     * a constant colour stands for the reference's 1x1 RGBA32F texture (Texture2D::SetColor). */
+    const float* materials;
+    int n_materials;
+    const OrTexture* textures;
+    int n_textures;
+    const float* lights;   /* n_lights x {float cumulativeArea; uint32 triIndex} (Scene.cpp:296-331) */
+    int n_lights;
+    float total_light_area;
+    float env_color[3];    /* "GENERATE COLOR x" constant cubemap (Renderer.cpp:242-260) */
+} OrScene;
+
+/* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
+typedef struct OrCamera {
+    float lower_left[3], horizontal[3], vertical[3], position[3], u[3], v[3];
+    float lens_radius;
+} OrCamera;
+
+typedef struct OrConfig {
+    int width, height;     /* multiples of 8 (Iterative.comp:163-172) */
+    int max_depth;         /* max closest-hit rays per path; reference = 66 (`i > 64`, Iterative.comp:293) */
+    int microfacet_model;  /* 0 = Trowbridge-Reitz (live, Microfacet.glsl:90-92), 1 = Beckmann (:35-55) */
+    int n_threads;         /* host threads; <=0: hardware_concurrency */
+} OrConfig;
+
+typedef struct OrCounters {
+    uint64_t closest_rays, shadow_rays;
+    uint64_t node_pairs, leaf_visits, tri_tests;   /* summed over both ray kinds */
+    uint64_t paths;
+} OrCounters;
+
+/* ---- scalar pieces ---- */
+void or_hybrid_taus(uint32_t state[4], int n, float* out);            /* Random.glsl:47-70 */
+void or_image_plane(float aspect, float fov, float focus, float aperture, const float pos[3],
+                    const float rot[3], OrCamera* cam);                /* Camera.cpp:4-22 */
+int or_slab_test(const float bmin[3], const float bmax[3], const float iorg[3], const float idir[3],
+                 float tcur, float dist2[2]);                          /* BVH.glsl:379-391 */
+void or_tonemap(const float rgb_sum[3], int num_samples, float out_rgb[3]); /* Present.frag:13-37 */
+
+/* ---- fixed ray batches: rays[n][8] = {o.xyz, tmin(ignored), d.xyz, tmax} ---- */
+/* hits[n][4] = {t, u, v, triId as int bits}; miss: t = tmax given, triId = -1. BVH.glsl:634-767 */
+void or_trace_closest(const OrScene* s, const float* rays, int64_t n, float* hits, OrCounters* c, int n_threads);
+/* flags[n] = 1 if occluded within (0, tmax). BVH.glsl:769-854 */
+void or_trace_any(const OrScene* s, const float* rays, int64_t n, uint8_t* flags, OrCounters* c, int n_threads);
+
+/* ---- whole frames: n_frames x (1 path per pixel), Iterative.comp:214-307 ----
+ * rng[px][4] persistent per-pixel HybridTaus state (read, advanced, written back: Random.glsl:232-242)
+ * accum[px][4] running SUM of radiance (alpha forced to 1), Iterative.comp:263,295 */
+void or_render(const OrScene* s, const OrCamera* cam, const OrConfig* cfg, uint32_t* rng, float* accum,
+               int n_frames, OrCounters* c);
+
+/* ---- per-stage probes for wavefront-kernel parity (same code paths as or_render) ---- */
+/* ray generation for ray index range [first, first+n): out[n][12] =
+ * {pixel.x, pixel.y (int bits), o.xyz, d.xyz, 4 pad}; advances rng of the touched pixels. Iterative.comp:174-210 */
+void or_raygen(const OrCamera* cam, const OrConfig* cfg, const float total_light_area, uint32_t* rng,
+               int64_t first, int64_t n, float* out);
+
+/* Brute force over all triangles with the same triangle test (no BVH): used by tests to classify
+ * mismatches of conservative (wide/quantised) traversal as "reference box-cull miss" or "tie". */
+void or_trace_closest_bruteforce(const OrScene* s, const float* rays, int64_t n, float* hits, int n_threads);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
