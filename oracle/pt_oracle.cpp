@@ -205,10 +205,12 @@ void parallel_for(int64_t n, int n_threads, F f) {
     for (auto& t : th) t.join();
 }
 
-void add_counters(OrCounters* c, const Cnt& k, uint64_t closest, uint64_t shadow, uint64_t paths) {
+void add_counters(OrCounters* c, const Cnt& k, uint64_t closest, uint64_t shadow, uint64_t paths,
+                  const Cnt* shadowShare = nullptr) {
     if (!c) return;
     // callers serialise this
     c->node_pairs += k.pairs; c->leaf_visits += k.leaves; c->tri_tests += k.tris;
+    if (shadowShare) { c->shadow_node_pairs += shadowShare->pairs; c->shadow_tri_tests += shadowShare->tris; }
     c->closest_rays += closest; c->shadow_rays += shadow; c->paths += paths;
 }
 
@@ -483,7 +485,7 @@ void init_ray(const OrCamera& cam, const OrConfig& cfg, float totalLightArea, in
 
 // One path = the body of main()'s while(true) until the path is stored. Iterative.comp:225-303
 void trace_path(const OrScene& s, const OrCamera& cam, const OrConfig& cfg, int rayIndex, uint32_t* rngTable,
-                float* accum, Cnt& cnt, uint64_t& nClosest, uint64_t& nShadow) {
+                float* accum, Cnt& cnt, Cnt& scnt, uint64_t& nClosest, uint64_t& nShadow) {
     Path p;
     ray_index_to_morton(rayIndex, cfg.width, p.px, p.py);
     size_t pix = (size_t)p.py * cfg.width + p.px;
@@ -530,7 +532,7 @@ void trace_path(const OrScene& s, const OrCamera& cam, const OrConfig& cfg, int 
         Ray lightRay = light_sample(s, model, vpos, vnormal, mat, it, rng, tmax, p.throughput, lightThroughput, lightMat);
         Hit lh; lh.t = tmax; lh.u = lh.v = 0; lh.tri = -1;
         nShadow++;
-        if (!any_hit(s, lightRay, lh, cnt)) {
+        if (!any_hit(s, lightRay, lh, scnt)) {
             const float* lm = s.materials + 12 * (size_t)(lightMat >> 1);
             p.contribution = p.contribution + lightThroughput * v3(lm[4], lm[5], lm[6]);
         }
@@ -642,7 +644,7 @@ void or_trace_any(const OrScene* s, const float* rays, int64_t n, uint8_t* flags
             flags[i] = any_hit(*s, ray, h, k) ? 1 : 0;
         }
         while (lock.test_and_set()) {}
-        add_counters(c, k, 0, (uint64_t)(e - b), 0);
+        add_counters(c, k, 0, (uint64_t)(e - b), 0, &k);
         lock.clear();
     });
 }
@@ -667,10 +669,11 @@ void or_render(const OrScene* s, const OrCamera* cam, const OrConfig* cfg, uint3
     for (int f = 0; f < n_frames; f++) {
         // one dispatch: globalRayCount = width*height paths, one per pixel (Iterative.comp:149,175-178)
         parallel_for(npx, cfg->n_threads, [&](int, int64_t b, int64_t e) {
-            Cnt k; uint64_t nc = 0, ns = 0;
-            for (int64_t i = b; i < e; i++) trace_path(*s, *cam, *cfg, (int)i, rng, accum, k, nc, ns);
+            Cnt k, ks; uint64_t nc = 0, ns = 0;
+            for (int64_t i = b; i < e; i++) trace_path(*s, *cam, *cfg, (int)i, rng, accum, k, ks, nc, ns);
+            k.pairs += ks.pairs; k.leaves += ks.leaves; k.tris += ks.tris;
             while (lock.test_and_set()) {}
-            add_counters(c, k, nc, ns, (uint64_t)(e - b));
+            add_counters(c, k, nc, ns, (uint64_t)(e - b), &ks);
             lock.clear();
         });
     }

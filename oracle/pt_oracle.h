@@ -75,6 +75,7 @@ typedef struct OrCounters {
     uint64_t closest_rays, shadow_rays;
     uint64_t node_pairs, leaf_visits, tri_tests;   /* summed over both ray kinds */
     uint64_t paths;
+    uint64_t shadow_node_pairs, shadow_tri_tests;  /* the any-hit share of node_pairs / tri_tests */
 } OrCounters;
 
 /* ---- scalar pieces ---- */
