@@ -24,7 +24,7 @@ if ROOT not in sys.path:
 WIDTH, HEIGHT, MAX_DEPTH, TRIS = 1920, 1080, 5, 262144
 METRIC = "Mrays/s (closest-hit + shadow rays), 1080p atrium-262k path tracing, depth 5, NEE + RR"
 # algorithmic bytes of the HBM data layout: ray in 32 B, hit out 16 B, node pair 64 B, leaf triangle 48 B
-B_RAY_IN, B_HIT_OUT, B_PAIR, B_TRI, B_FLAG_OUT = 32, 16, 64, 48, 4
+B_RAY_IN, B_HIT_OUT, B_PAIR, B_TRI, B_FLAG_OUT = 32, 16, 64, 40, 4
 
 
 def measured_peaks():

@@ -187,6 +187,7 @@ static int upload_leaf_stream(pt_context* c) {
         ls[i].r[0] = make_float4(t[0], t[1], t[2], t[3]);
         ls[i].r[1] = make_float4(t[4], t[5], t[6], t[7]);
         ls[i].r[2] = make_float4(t[8], idf, 0.0f, 0.0f);
+        ls[i].r[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
     CK(c->d_leaf.alloc(nr));
     CK(cudaMemcpyAsync(c->d_leaf.p, ls.data(), nr * sizeof(LeafTri), cudaMemcpyHostToDevice, c->stream));

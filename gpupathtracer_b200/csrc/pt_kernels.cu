@@ -12,6 +12,7 @@
 #include "pt_kernels.h"
 #include "pt_trace.cuh"
 #include "pt_shade.cuh"
+#include <cstdlib>
 
 namespace pt {
 
@@ -19,36 +20,37 @@ namespace pt {
 #define PT_STREAM_THREADS 256
 
 // ------------------------------------------------------------------ fixed ray batches
+struct BatchIO {
+    const float4* rays; float4* hits; unsigned char* flags; int n; int* cur;
+    __device__ __forceinline__ int count() const { return n; }
+    __device__ __forceinline__ int* cursor() const { return cur; }
+    __device__ __forceinline__ void load(int i, V3& o, V3& d, float& tmax) const {
+        float4 ro = __ldg(rays + 2 * (size_t)i), rd = __ldg(rays + 2 * (size_t)i + 1);
+        o = xyz(ro); d = xyz(rd); tmax = rd.w;
+    }
+    __device__ __forceinline__ void store(int i, const HitRec& h, bool result) const {
+        if (flags) flags[i] = result ? 1 : 0;
+        else hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+    }
+};
+
 template <bool ANY>
 __global__ void __launch_bounds__(PT_TRACE_THREADS)
-k_trace_batch(SceneDev s, const float4* __restrict__ rays, long long n, float4* __restrict__ hits,
-              unsigned char* __restrict__ flags, int* cursor) {
-    const int lane = threadIdx.x & 31;
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(cursor, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        long long i = (long long)base + lane;
-        if (i < n) {
-            float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
-            HitRec h; h.t = rd.w; h.u = 0.0f; h.v = 0.0f; h.tri = -1;
-            bool r = traverse<ANY>(s, xyz(ro), xyz(rd), h);
-            if (ANY) flags[i] = r ? 1 : 0;
-            else hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
-        }
-    }
+k_trace_batch(SceneDev s, BatchIO io, int leaf_thresh, int fetch_thresh) {
+    trace_persistent<ANY>(s, io, leaf_thresh, fetch_thresh);
 }
 
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
                           const LaunchDims& dims, cudaStream_t st) {
     cudaMemsetAsync(cursor, 0, sizeof(int), st);
-    k_trace_batch<false><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, rays, n, hits, nullptr, cursor);
+    BatchIO io{rays, hits, nullptr, (int)n, cursor};
+    k_trace_batch<false><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
                       const LaunchDims& dims, cudaStream_t st) {
     cudaMemsetAsync(cursor, 0, sizeof(int), st);
-    k_trace_batch<true><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, rays, n, nullptr, flags, cursor);
+    BatchIO io{rays, nullptr, flags, (int)n, cursor};
+    k_trace_batch<true><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 // ------------------------------------------------------------------ ray generation
@@ -90,25 +92,23 @@ __global__ void k_raygen_probe(FrameParams p, long long first, long long n, floa
 }
 
 // ------------------------------------------------------------------ extend (closest hit)
-__global__ void __launch_bounds__(PT_TRACE_THREADS)
-k_extend(FrameParams p, int bounce, int qi) {
-    const int lane = threadIdx.x & 31;
-    BounceCounters* c = p.counters + bounce;
-    const int n = c->n_paths;
-    const PathQueue q = p.queue[qi];
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&c->fetch_extend, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
-            float4 ro = q.q0[i], rd = q.q1[i];
-            HitRec h; h.t = 1e20f; h.u = 0.0f; h.v = 0.0f; h.tri = -1;     // Iterative.comp:232
-            traverse<false>(p.scene, xyz(ro), xyz(rd), h);
-            p.hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
-        }
+struct ExtendIO {
+    PathQueue q; float4* hits; BounceCounters* c;
+    __device__ __forceinline__ int count() const { return c->n_paths; }
+    __device__ __forceinline__ int* cursor() const { return &c->fetch_extend; }
+    __device__ __forceinline__ void load(int i, V3& o, V3& d, float& tmax) const {
+        float4 ro = q.q0[i], rd = q.q1[i];
+        o = xyz(ro); d = xyz(rd); tmax = 1e20f;                      // Iterative.comp:232
     }
+    __device__ __forceinline__ void store(int i, const HitRec& h, bool) const {
+        hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+    }
+};
+
+__global__ void __launch_bounds__(PT_TRACE_THREADS)
+k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
+    ExtendIO io{p.queue[qi], p.hits, p.counters + bounce};
+    trace_persistent<false>(p.scene, io, leaf_thresh, fetch_thresh);
 }
 
 // ------------------------------------------------------------------ shade
@@ -239,36 +239,33 @@ k_shade(FrameParams p, int bounce, int qi) {
 }
 
 // ------------------------------------------------------------------ shadow (any hit) + NEE add + store
-__global__ void __launch_bounds__(PT_TRACE_THREADS)
-k_shadow(FrameParams p, int bounce, int qi_next) {
-    const int lane = threadIdx.x & 31;
-    BounceCounters* c = p.counters + bounce;
-    const int n = c->n_shadow;
-    const ShadowQueue sq = p.shadow;
-    const PathQueue qn = p.queue[qi_next];
-    while (true) {
-        int base = 0;
-        if (lane == 0) base = atomicAdd(&c->fetch_shadow, 32);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        int i = base + lane;
-        if (i < n) {
-            float4 s0 = sq.s0[i], s1 = sq.s1[i];
-            HitRec h; h.t = s0.w; h.u = 0.0f; h.v = 0.0f; h.tri = -1;
-            bool occluded = traverse<true>(p.scene, xyz(s0), xyz(s1), h);
-            float4 s2 = sq.s2[i], s3 = sq.s3[i];
-            V3 contrib = xyz(s3);
-            if (!occluded) contrib = contrib + xyz(s2);        // Iterative.comp:278-280
-            int dest = __float_as_int(s1.w);
-            if (dest >= 0) {
-                qn.q3[dest] = f4(contrib, 0.0f);
-            } else {
-                int pix = ~dest;                                // imageStore, Iterative.comp:295
-                float4 acc = p.accum[pix];
-                p.accum[pix] = make_float4(acc.x + contrib.x, acc.y + contrib.y, acc.z + contrib.z, 1.0f);
-            }
+struct ShadowIO {
+    ShadowQueue sq; PathQueue qn; float4* accum; BounceCounters* c;
+    __device__ __forceinline__ int count() const { return c->n_shadow; }
+    __device__ __forceinline__ int* cursor() const { return &c->fetch_shadow; }
+    __device__ __forceinline__ void load(int i, V3& o, V3& d, float& tmax) const {
+        float4 s0 = sq.s0[i], s1 = sq.s1[i];
+        o = xyz(s0); d = xyz(s1); tmax = s0.w;
+    }
+    __device__ __forceinline__ void store(int i, const HitRec&, bool occluded) const {
+        float4 s2 = sq.s2[i], s3 = sq.s3[i];
+        int dest = __float_as_int(sq.s1[i].w);
+        V3 contrib = xyz(s3);
+        if (!occluded) contrib = contrib + xyz(s2);                  // Iterative.comp:278-280
+        if (dest >= 0) {
+            qn.q3[dest] = f4(contrib, 0.0f);
+        } else {
+            int pix = ~dest;                                         // imageStore, Iterative.comp:295
+            float4 acc = accum[pix];
+            accum[pix] = make_float4(acc.x + contrib.x, acc.y + contrib.y, acc.z + contrib.z, 1.0f);
         }
     }
+};
+
+__global__ void __launch_bounds__(PT_TRACE_THREADS)
+k_shadow(FrameParams p, int bounce, int qi_next, int leaf_thresh, int fetch_thresh) {
+    ShadowIO io{p.shadow, p.queue[qi_next], p.accum, p.counters + bounce};
+    trace_persistent<true>(p.scene, io, leaf_thresh, fetch_thresh);
 }
 
 __global__ void k_tally(FrameParams p) {
@@ -287,13 +284,13 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
     int qi = 0;
     for (int b = 0; b < p.max_depth; b++) {
         if (evs) cudaEventRecord(evs[launches], st);
-        k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi); launches++;
+        k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
         if (p.model == 1) k_shade<1><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, b, qi);
         else k_shade<0><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, b, qi);
         launches++;
         if (evs) cudaEventRecord(evs[launches], st);
-        k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi ^ 1); launches++;
+        k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi ^ 1, dims.leaf_thresh, dims.fetch_thresh); launches++;
         qi ^= 1;
     }
     if (evs) cudaEventRecord(evs[launches], st);
@@ -369,6 +366,11 @@ void query_launch_dims(int device, LaunchDims* out) {
     out->sm_count = prop.multiProcessorCount;
     out->extend_blocks = prop.multiProcessorCount * per;
     out->stream_blocks = prop.multiProcessorCount * per_sm_shade;
+    // warp-scheduling thresholds (see pt_trace.cuh); env overrides exist for tuning runs only
+    out->leaf_thresh = 8; out->fetch_thresh = 12;
+    if (const char* e = getenv("PT_LEAF_THRESH")) out->leaf_thresh = atoi(e);
+    if (const char* e = getenv("PT_FETCH_THRESH")) out->fetch_thresh = atoi(e);
+    if (const char* e = getenv("PT_BLOCKS_PER_SM")) out->extend_blocks = prop.multiProcessorCount * atoi(e);
 }
 
 }  // namespace pt

@@ -8,7 +8,7 @@ namespace pt {
 // ---- BVH, PT_BVH_REFERENCE layout -------------------------------------------------------------
 // The reference stores one 32-B node per child and addresses sibling pairs at (firstChild,
 // firstChild+1) with firstChild ODD (root = 0, its children = 1,2; BVH.cpp:2224-2255), so every
-// pair straddles a 64-B boundary. Here one 64-B aligned record holds the pair = 4 x 128-bit loads
+// pair straddles a 64-B boundary. Here one 64-B aligned record holds the pair = 2 x 256-bit loads
 // from 2 sectors of one line:
 //   q[0] = {c0.min.xyz, link0}   q[1] = {c0.max.xyz, 0}
 //   q[2] = {c1.min.xyz, link1}   q[3] = {c1.max.xyz, 0}
@@ -20,13 +20,14 @@ struct BvhPair { float4 q[4]; };
 
 // ---- leaf triangle stream ----------------------------------------------------------------------
 // The reference walks leaf -> reference list (4 B) -> 80-B triangle. Here the reference list is
-// resolved at upload time into a stream of 48-B intersection records in reference-list order:
-//   r[0] = {p0.xyz, e1.x}  r[1] = {e1.y, e1.z, e2.x, e2.y}  r[2] = {e2.z, id, 0, 0}
+// resolved at upload time into a stream of 64-B (2 x 256-bit loads, 32-B aligned) intersection records in
+// reference-list order; 40 B are used, the rest is padding that keeps every record inside one 128-B line:
+//   r[0] = {p0.xyz, e1.x}  r[1] = {e1.y, e1.z, e2.x, e2.y}  r[2] = {e2.z, id, 0, 0}  r[3] = 0
 // id = triangle index, stored as ~index when the reference-list entry carried the end-of-leaf
 // marker (negative entry, BVH.cpp:2117). Entry "0" cannot carry the marker in the reference
 // (-0 == 0): that leaf runs on into the next one; the stream reproduces this because the marker
 // is copied, not recomputed.
-struct LeafTri { float4 r[3]; };
+struct LeafTri { float4 r[4]; };
 
 // ---- shading tables ------------------------------------------------------------------------------
 // Full reference triangle (5 x vec4, Scene.cpp:339-347 upload) is kept for shading: uv, normal, matId.

@@ -46,7 +46,19 @@ __host__ __device__ __forceinline__ float avdot(V3 a, V3 b) { return fabsf(dot(a
 __device__ __forceinline__ V3 xyz(float4 v) { return v3(v.x, v.y, v.z); }
 __device__ __forceinline__ float4 f4(V3 v, float w) { return make_float4(v.x, v.y, v.z, w); }
 
-// 128-bit read-only loads (LDG.E.128.CONSTANT) and streaming stores
+// 128-bit read-only loads (LDG.E.128.CONSTANT)
 __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
+
+// 256-bit read-only load (LDG.E.256.CONSTANT, new with sm_100): one request and one L1 data-pipe wavefront
+// per lane for a 32-B half record instead of two. The traversal kernels are bound by exactly that pipe
+// (l1tex__data_pipe_lsu_wavefronts ~ 89 % of peak with 128-bit loads, profiles/), so record loads use this.
+struct F8 { float4 lo, hi; };
+__device__ __forceinline__ F8 ldg256(const void* p) {
+    F8 r;
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
+        : "l"(p));
+    return r;
+}
 
 }  // namespace pt

@@ -1,7 +1,16 @@
 // pt_trace.cuh -- closest-hit / any-hit traversal of the PT_BVH_REFERENCE layout.
 // Replaces IfIfClosestHit (common/BVH.glsl:634-767), IfIfAnyHit (:769-854), IntersectNodeFast (:379-391),
 // IntersectLeaf (:420-437) and IntersectTriangleMT (common/Geometry.glsl:198-225) of the reference.
-// Same node visit order and the same arithmetic (see pt_math.cuh), hence the same (triId, t, u, v).
+//
+// Per RAY, the sequence of node visits, triangle tests and arithmetic is exactly the reference's, hence
+// the same (triId, t, u, v) bit for bit. What is different is how a WARP schedules its 32 rays:
+//   * a ray's next operation is either an INNER step (one sibling-pair test) or a LEAF step (one
+//     triangle test). Instead of running "inner block; leaf block" every iteration (the shader's if-if
+//     loop, which executes the expensive leaf block at ~5 % lane utilisation almost every time), the warp
+//     votes: leaf steps run only when at least `leaf_thresh` lanes wait at a leaf or no lane has an inner
+//     step left. Waiting does not change a ray's own sequence, so results cannot change;
+//   * persistent threads with dynamic fetch: lanes whose ray has finished pull new rays from a device
+//     cursor (one atomic per warp, ballot + popc ranks) once `fetch_thresh` lanes are idle.
 #pragma once
 #include "pt_math.cuh"
 #include "pt_layout.h"
@@ -12,7 +21,7 @@ namespace pt {
 
 struct HitRec { float t, u, v; int tri; };
 
-// slab test of one child; returns t_entry
+// slab test of one child (IntersectNodeFast); returns t_entry
 __device__ __forceinline__ float slab_test(float4 bmin, float4 bmax, V3 inv, V3 oinv, float tcur, bool& hit) {
     float ax = bmin.x * inv.x + oinv.x, ay = bmin.y * inv.y + oinv.y, az = bmin.z * inv.z + oinv.z;
     float bx = bmax.x * inv.x + oinv.x, by = bmax.y * inv.y + oinv.y, bz = bmax.z * inv.z + oinv.z;
@@ -24,9 +33,10 @@ __device__ __forceinline__ float slab_test(float4 bmin, float4 bmax, V3 inv, V3 
 
 // Moeller-Trumbore with pre-subtracted edges; strict bounds as in the shader
 __device__ __forceinline__ bool tri_test(const LeafTri* __restrict__ rec, V3 o, V3 d, HitRec& h, bool& last) {
-    float4 r0 = __ldg(&rec->r[0]);
-    float4 r1 = __ldg(&rec->r[1]);
-    float4 r2 = __ldg(&rec->r[2]);
+    F8 lo = ldg256(&rec->r[0]);
+    float2 tail = __ldg(reinterpret_cast<const float2*>(&rec->r[2]));
+    float4 r0 = lo.lo, r1 = lo.hi;
+    float4 r2 = make_float4(tail.x, tail.y, 0.0f, 0.0f);
     V3 p0 = v3(r0.x, r0.y, r0.z);
     V3 v01 = v3(r0.w, r1.x, r1.y);
     V3 v02 = v3(r1.z, r1.w, r2.x);
@@ -48,50 +58,113 @@ __device__ __forceinline__ bool tri_test(const LeafTri* __restrict__ rec, V3 o, 
     return false;
 }
 
-// ANY = false: closest hit (near child first, far child pushed).
-// ANY = true : stops after the first LEAF that produced a hit (the leaf itself is fully tested).
-template <bool ANY>
-__device__ __forceinline__ bool traverse(const SceneDev& s, V3 o, V3 d, HitRec& h) {
-    V3 inv = v3(1.0f) / d;
-    V3 oinv = -o * inv;
-    int stack[PT_STACK_SIZE];
-    int sp = 0;
-    int current = 0;          // pair record of the root's children (RootFirstChild, BVH.glsl:627)
-    bool result = false;
-    while (true) {
-        if (current >= 0) {
-            const float4* q = s.pairs[current].q;
-            float4 a0 = __ldg(q + 0), a1 = __ldg(q + 1), b0 = __ldg(q + 2), b1 = __ldg(q + 3);
-            bool hit0, hit1;
-            float d0 = slab_test(a0, a1, inv, oinv, h.t, hit0);
-            float d1 = slab_test(b0, b1, inv, oinv, h.t, hit1);
-            int sub0 = __float_as_int(a0.w), sub1 = __float_as_int(b0.w);
-            if (hit0 && hit1) {
-                bool swap = ANY ? false : (d0 > d1);
-                current = swap ? sub1 : sub0;
-                stack[sp++] = swap ? sub0 : sub1;
-            } else if (hit0 != hit1) {
-                current = hit0 ? sub0 : sub1;
-            } else {
-                if (sp == 0) break;
-                current = stack[--sp];
-            }
+// Per-lane traversal state machine. `current` >= 0: pair record to test next (inner step);
+// `current` < 0: ~current = next record of the leaf triangle stream to test (leaf step).
+struct Traverser {
+    V3 o, d, inv, oinv;
+    HitRec h;
+    int current, sp;
+    bool result;          // "some triangle of the current leaf was accepted"
+
+    __device__ __forceinline__ void begin(V3 org, V3 dir, float tmax) {
+        o = org; d = dir;
+        inv = v3(1.0f) / d;
+        oinv = -o * inv;
+        h.t = tmax; h.u = 0.0f; h.v = 0.0f; h.tri = -1;
+        current = 0;      // pair record of the root's children (RootFirstChild, BVH.glsl:627)
+        sp = 0;
+        result = false;
+    }
+    // returns true when the ray is finished
+    __device__ __forceinline__ bool pop(const int* stack) {
+        if (sp == 0) return true;
+        current = stack[--sp];
+        return false;
+    }
+    template <bool ANY>
+    __device__ __forceinline__ bool inner_step(const SceneDev& s, int* stack) {
+        const float4* q = s.pairs[current].q;
+        F8 ca = ldg256(q), cb = ldg256(q + 2);
+        float4 a0 = ca.lo, a1 = ca.hi, b0 = cb.lo, b1 = cb.hi;
+        bool hit0, hit1;
+        float d0 = slab_test(a0, a1, inv, oinv, h.t, hit0);
+        float d1 = slab_test(b0, b1, inv, oinv, h.t, hit1);
+        int sub0 = __float_as_int(a0.w), sub1 = __float_as_int(b0.w);
+        if (hit0 && hit1) {
+            bool swap = ANY ? false : (d0 > d1);      // near child first for closest hit only
+            current = swap ? sub1 : sub0;
+            stack[sp++] = swap ? sub0 : sub1;
+            return false;
         }
-        if (current < 0) {
-            const LeafTri* rec = s.leaf_tris + (~current);
-            const LeafTri* end = s.leaf_tris + s.n_leaf_tris;
-            bool last = false;
-            while (!last && rec < end) {
-                bool hit = tri_test(rec, o, d, h, last);
-                result = result || hit;
-                ++rec;
+        if (hit0 != hit1) { current = hit0 ? sub0 : sub1; return false; }
+        return pop(stack);
+    }
+    // one triangle of the current leaf; the leaf is always tested to its end marker (IntersectLeaf)
+    template <bool ANY>
+    __device__ __forceinline__ bool leaf_step(const SceneDev& s, const int* stack) {
+        int ri = ~current;
+        bool last;
+        bool hit = tri_test(s.leaf_tris + ri, o, d, h, last);
+        result = result || hit;
+        if (!last && ri + 1 < s.n_leaf_tris) { current = ~(ri + 1); return false; }
+        if (ANY && result) return true;                // IfIfAnyHit returns after the first leaf that hit
+        return pop(stack);
+    }
+};
+
+// The warp-scheduled persistent traversal loop. IO supplies:
+//   int  count() const;  int* cursor() const;
+//   void load(int i, V3& o, V3& d, float& tmax) const;
+//   void store(int i, const HitRec& h, bool result) const;
+template <bool ANY, class IO>
+__device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io, int leaf_thresh, int fetch_thresh) {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n = io.count();
+    int* cursor = io.cursor();
+    Traverser tr;
+    int stack[PT_STACK_SIZE];   // per-lane traversal stack (local memory, L1-resident)
+    bool active = false, exhausted = false;
+    int ridx = -1;
+    tr.current = 0; tr.sp = 0;
+    while (true) {
+        // ---- refill idle lanes
+        unsigned m_idle = __ballot_sync(FULL, !active);
+        if (!exhausted && (m_idle == FULL || __popc(m_idle) >= fetch_thresh)) {
+            int cnt = __popc(m_idle), base = 0;
+            int leader = __ffs(m_idle) - 1;
+            if (lane == leader) base = atomicAdd(cursor, cnt);
+            base = __shfl_sync(FULL, base, leader);
+            if (!active) {
+                int my = base + __popc(m_idle & lt_mask);
+                if (my < n) {
+                    V3 o, d; float tmax;
+                    io.load(my, o, d, tmax);
+                    tr.begin(o, d, tmax);
+                    ridx = my;
+                    active = true;
+                }
             }
-            if (ANY && result) return true;
-            if (sp == 0) break;
-            current = stack[--sp];
+            if (base + cnt >= n) exhausted = true;
+        }
+        // ---- vote on the phase
+        bool at_leaf = active && tr.current < 0;
+        unsigned m_leaf = __ballot_sync(FULL, at_leaf);
+        unsigned m_active = __ballot_sync(FULL, active);
+        if (m_active == 0) { if (exhausted) break; else continue; }
+        unsigned m_inner = m_active & ~m_leaf;
+        bool done = false;
+        if (m_inner != 0 && __popc(m_leaf) < leaf_thresh) {
+            if (active && !at_leaf) done = tr.template inner_step<ANY>(s, stack);
+        } else {
+            if (at_leaf) done = tr.template leaf_step<ANY>(s, stack);
+        }
+        if (done) {
+            io.store(ridx, tr.h, tr.result);
+            active = false;
         }
     }
-    return result;
 }
 
 }  // namespace pt

@@ -171,6 +171,16 @@ class Oracle:
         self.l.or_trace_any(C.byref(self.s), _p(rays), rays.shape[0], _p(flags), C.byref(c), n_threads)
         return flags, c.as_dict()
 
+    def trace_ops(self, rays, any_hit=False):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        n = rays.shape[0]
+        self.l.or_trace_ops.restype = C.c_int64
+        self.l.or_trace_ops.argtypes = [C.POINTER(OrScene), C.c_void_p, C.c_int64, C.c_int, C.c_void_p, C.c_void_p]
+        total = self.l.or_trace_ops(C.byref(self.s), _p(rays), n, int(any_hit), None, None)
+        ops = np.zeros(total, dtype=np.uint8); off = np.zeros(n + 1, dtype=np.int64)
+        self.l.or_trace_ops(C.byref(self.s), _p(rays), n, int(any_hit), _p(ops), _p(off))
+        return ops, off
+
     def trace_closest_bruteforce(self, rays, n_threads=0):
         rays = np.ascontiguousarray(rays, dtype=np.float32)
         hits = np.zeros((rays.shape[0], 4), dtype=np.float32)

@@ -62,7 +62,7 @@ struct Rng {
 
 // ---------------------------------------------------------------- traversal
 struct Hit { float t, u, v; int tri; };
-struct Cnt { uint64_t pairs = 0, leaves = 0, tris = 0; };
+struct Cnt { uint64_t pairs = 0, leaves = 0, tris = 0; std::vector<uint8_t>* ops = nullptr; };   // ops: optional per-step trace (0 = pair test, 1 = triangle test)
 
 // IntersectNodeFast, BVH.glsl:379-391. iray = {o' = -o/d, 1/d}.
 inline float slab(const float* node, const Ray& iray, float tcur, bool& hit) {
@@ -105,11 +105,13 @@ inline void leaf(const OrScene& s, int leafv, const Ray& ray, Hit& h, bool& resu
     int i = -leafv;
     bool iterating = true;
     c.leaves++;
+    if (c.ops) c.ops->push_back(2);   // leaf entered
     while (iterating) {
         if (i >= s.n_refs) break;
         int index = s.refs[i++];
         if (index < 0) { index = -index; iterating = false; }
         c.tris++;
+        if (c.ops) c.ops->push_back(1);
         bool hit = tri_mt(s.tris + 20 * (size_t)index, ray, h, index);
         result = result || hit;
     }
@@ -130,6 +132,7 @@ bool closest_hit(const OrScene& s, const Ray& ray, Hit& h, Cnt& c) {
             const float* c0 = s.nodes + 8 * (size_t)current;
             const float* c1 = c0 + 8;
             c.pairs++;
+            if (c.ops) c.ops->push_back(0);
             int sub0 = fbs(c0[3]); bool hit0; float d0 = slab(c0, iray, h.t, hit0);
             int sub1 = fbs(c1[3]); bool hit1; float d1 = slab(c1, iray, h.t, hit1);
             if (hit0 && hit1) {
@@ -164,6 +167,7 @@ bool any_hit(const OrScene& s, const Ray& ray, Hit& h, Cnt& c) {
             const float* c0 = s.nodes + 8 * (size_t)current;
             const float* c1 = c0 + 8;
             c.pairs++;
+            if (c.ops) c.ops->push_back(0);
             int sub0 = fbs(c0[3]); bool hit0; slab(c0, iray, h.t, hit0);
             int sub1 = fbs(c1[3]); bool hit1; slab(c1, iray, h.t, hit1);
             if (hit0 && hit1) {
@@ -647,6 +651,27 @@ void or_trace_any(const OrScene* s, const float* rays, int64_t n, uint8_t* flags
         add_counters(c, k, 0, (uint64_t)(e - b), 0, &k);
         lock.clear();
     });
+}
+
+// Per-ray operation trace for scheduling studies (tools/simulate_warp.py): ops = concatenated step codes
+// (0 = sibling-pair test, 1 = triangle test, 2 = leaf entered), offsets[n+1] = start of each ray's steps. Returns total steps
+// (call with ops == NULL to size the buffer).
+int64_t or_trace_ops(const OrScene* s, const float* rays, int64_t n, int any, uint8_t* ops, int64_t* offsets) {
+    std::vector<uint8_t> v;
+    Cnt k; k.ops = &v;
+    int64_t total = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const float* r = rays + 8 * i;
+        Ray ray; ray.origin = ld3(r); ray.direction = ld3(r + 4);
+        Hit h; h.t = r[7]; h.u = 0; h.v = 0; h.tri = -1;
+        v.clear();
+        if (any) any_hit(*s, ray, h, k); else closest_hit(*s, ray, h, k);
+        if (offsets) offsets[i] = total;
+        if (ops) std::memcpy(ops + total, v.data(), v.size());
+        total += (int64_t)v.size();
+    }
+    if (offsets) offsets[n] = total;
+    return total;
 }
 
 void or_trace_closest_bruteforce(const OrScene* s, const float* rays, int64_t n, float* hits, int n_threads) {

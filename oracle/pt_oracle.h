@@ -108,6 +108,9 @@ void or_raygen(const OrCamera* cam, const OrConfig* cfg, const float total_light
  * mismatches of conservative (wide/quantised) traversal as "reference box-cull miss" or "tie". */
 void or_trace_closest_bruteforce(const OrScene* s, const float* rays, int64_t n, float* hits, int n_threads);
 
+/* per-ray step trace (0 = pair test, 1 = triangle test) for warp-scheduling studies; returns total steps */
+int64_t or_trace_ops(const OrScene* s, const float* rays, int64_t n, int any, uint8_t* ops, int64_t* offsets);
+
 #ifdef __cplusplus
 }
 #endif
