@@ -1,0 +1,89 @@
+// include/b200pt_renderer.hpp -- header-only C++ facade over the C ABI (b200pt.h) with the reference's own class shape:
+// the eight public methods of `Renderer` (src/core/Renderer.h:14-24) keep their names and meaning, headless.
+// A maintainer of the reference swaps `#include "core/Renderer.h"` for this header in Program.cpp.
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#include "b200pt.h"
+
+namespace b200pt {
+
+// Stand-in for misc/Window.h: the renderer only reads Width/Height (Renderer.cpp:450-451).
+struct Window { uint32_t Width = 1280, Height = 720; };
+
+// math/Camera.h:14-46, same constructor and setters; GenerateImagePlane fills the 7 uniforms of Shader::LoadCamera.
+class Camera {
+public:
+    Camera(float aspect, float fieldofview, float focus, float aperture)
+        : aspect_(aspect), fov_(fieldofview), focus_(focus), aperture_(aperture) {}
+    void SetPosition(const float p[3]) { for (int i = 0; i < 3; i++) pos_[i] = p[i]; }
+    void SetRotation(const float r[3]) { for (int i = 0; i < 3; i++) rot_[i] = r[i]; }
+    void GenerateImagePlane() { pt_camera_image_plane(aspect_, fov_, focus_, aperture_, pos_, rot_, &plane_); }
+    const pt_camera& Plane() const { return plane_; }
+private:
+    float aspect_, fov_, focus_, aperture_;
+    float pos_[3] = {0, 0, 0}, rot_[3] = {0, 0, 0};
+    pt_camera plane_{};
+};
+
+// What Scene::LoadScene (Scene.cpp:233-357) leaves behind, as plain arrays.
+struct SceneArrays {
+    std::vector<float> verts;            // n_tris x 3 x {pos, normal, uv}
+    std::vector<uint32_t> mat_ids;       // per triangle, = 2 * material index
+    std::vector<pt_material> materials;  // [0] = sky (Scene.cpp:236-241)
+    std::vector<pt_texture> textures;
+    float env_color[3] = {1, 1, 1};      // "GENERATE COLOR WHITE"
+};
+
+class Renderer {
+public:
+    ~Renderer() { CleanUp(); }
+
+    // Renderer::Initialize(Window*, scenePath, env) (Renderer.cpp:448-636): scene assembly, BVH build, uploads, RNG tables.
+    void Initialize(const Window* window, const SceneArrays& scene, int max_depth = 66, uint64_t seed = 0) {
+        pt_config cfg{};
+        cfg.width = (int32_t)window->Width; cfg.height = (int32_t)window->Height;
+        cfg.max_depth = max_depth; cfg.microfacet_model = PT_MICROFACET_GGX; cfg.device = 0; cfg.bvh_layout = PT_BVH_REFERENCE;
+        check(pt_create(&cfg, &ctx_));
+        const int64_t n = (int64_t)scene.mat_ids.size();
+        std::vector<float> tris((size_t)n * 20);
+        check(pt_assemble_triangles(scene.verts.data(), scene.mat_ids.data(), n, tris.data()));           // Scene.cpp:263-292
+        float total = 0.0f;
+        int nl = pt_build_light_table(tris.data(), n, scene.materials.data(), (int32_t)scene.materials.size(), nullptr, 0, &total);
+        if (nl < 1) throw std::runtime_error("scene has no emissive triangle (Iterative.comp:42-61 needs one)");
+        std::vector<pt_light> lights((size_t)nl);
+        pt_build_light_table(tris.data(), n, scene.materials.data(), (int32_t)scene.materials.size(), lights.data(), nl, &total);
+        pt_presubtract_edges(tris.data(), n);                                                                // Scene.cpp:334-337
+        check(pt_set_triangles(ctx_, tris.data(), n));
+        check(pt_set_materials(ctx_, scene.materials.data(), (int32_t)scene.materials.size(), scene.textures.data(),
+                               (int32_t)scene.textures.size()));
+        check(pt_set_lights(ctx_, lights.data(), nl, total));
+        check(pt_set_environment_color(ctx_, scene.env_color));
+        check(pt_build_bvh(ctx_, &bvh_stats_));                                                              // Scene.cpp:294
+        check(pt_seed_rng(ctx_, seed));                                                                      // Renderer.cpp:545-553
+        width_ = window->Width; height_ = window->Height;
+    }
+    void RenderFrame(const Camera& camera) {                      // Renderer.cpp:651-662
+        check(pt_set_camera(ctx_, &camera.Plane()));
+        check(pt_render_frames(ctx_, 1));
+    }
+    // Renderer::Present (Renderer.cpp:681-685): headless resolve into a host buffer (width*height*3 bytes, row 0 = bottom).
+    void Present(uint8_t* rgb8) { check(pt_resolve(ctx_, pt_num_samples(ctx_), nullptr, rgb8)); }
+    void ResetSamples() { check(pt_reset_samples(ctx_)); }        // Renderer.cpp:687-691
+    uint32_t GetNumSamples() { return pt_num_samples(ctx_); }     // Renderer.cpp:693-695
+    void SaveScreenshot(const std::string& filename) { check(pt_save_screenshot(ctx_, filename.c_str())); }   // :697-705
+    void CleanUp() { if (ctx_) { pt_destroy(ctx_); ctx_ = nullptr; } }                                       // :638-647
+    // Renderer::RenderReference (the stale CPU renderer, Renderer.cpp:1075-1187) has no counterpart: out of scope.
+    const pt_bvh_stats& BvhStats() const { return bvh_stats_; }
+    pt_context* Context() { return ctx_; }
+
+private:
+    static void check(int rc) { if (rc != PT_OK) throw std::runtime_error(pt_last_error()); }
+    pt_context* ctx_ = nullptr;
+    pt_bvh_stats bvh_stats_{};
+    uint32_t width_ = 0, height_ = 0;
+};
+
+}  // namespace b200pt
