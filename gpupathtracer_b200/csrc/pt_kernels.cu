@@ -18,6 +18,7 @@ namespace pt {
 
 #define PT_TRACE_THREADS 128
 #define PT_STREAM_THREADS 256
+#define PT_SHADE_THREADS 128
 
 // ------------------------------------------------------------------ fixed ray batches
 struct BatchIO {
@@ -113,7 +114,7 @@ k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
 
 // ------------------------------------------------------------------ shade
 template <int MODEL>
-__global__ void __launch_bounds__(PT_STREAM_THREADS)
+__global__ void __launch_bounds__(PT_SHADE_THREADS, 6)
 k_shade(FrameParams p, int bounce, int qi) {
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -286,8 +287,8 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
         if (evs) cudaEventRecord(evs[launches], st);
         k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
-        if (p.model == 1) k_shade<1><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, b, qi);
-        else k_shade<0><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, b, qi);
+        if (p.model == 1) k_shade<1><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
+        else k_shade<0><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
         launches++;
         if (evs) cudaEventRecord(evs[launches], st);
         k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi ^ 1, dims.leaf_thresh, dims.fetch_thresh); launches++;
@@ -359,13 +360,14 @@ void query_launch_dims(int device, LaunchDims* out) {
     int per_sm_ext = 1, per_sm_shadow = 1, per_sm_shade = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend, PT_TRACE_THREADS, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow, PT_TRACE_THREADS, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0>, PT_STREAM_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0>, PT_SHADE_THREADS, 0);
     int per = per_sm_ext < per_sm_shadow ? per_sm_ext : per_sm_shadow;
     if (per < 1) per = 1;
     if (per_sm_shade < 1) per_sm_shade = 1;
     out->sm_count = prop.multiProcessorCount;
     out->extend_blocks = prop.multiProcessorCount * per;
-    out->stream_blocks = prop.multiProcessorCount * per_sm_shade;
+    out->shade_blocks = prop.multiProcessorCount * per_sm_shade;
+    out->stream_blocks = prop.multiProcessorCount * 4;
     // warp-scheduling thresholds (see pt_trace.cuh); env overrides exist for tuning runs only
     out->leaf_thresh = 8; out->fetch_thresh = 12;
     if (const char* e = getenv("PT_LEAF_THRESH")) out->leaf_thresh = atoi(e);
