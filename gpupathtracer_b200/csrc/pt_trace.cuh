@@ -91,7 +91,10 @@ struct Traverser {
         float d1 = slab_test(b0, b1, inv, oinv, h.t, hit1);
         int sub0 = __float_as_int(a0.w), sub1 = __float_as_int(b0.w);
         if (hit0 && hit1) {
-            bool swap = ANY ? false : (d0 > d1);      // near child first for closest hit only
+            // Near child first. For ANY this differs from IfIfAnyHit's fixed order (BVH.glsl:806-812) but cannot
+            // change the flag: until the first accepted triangle h.t stays at tmax, so which leaves are reachable
+            // does not depend on the visiting order, and the answer is "some reachable leaf holds a hit".
+            bool swap = d0 > d1;
             current = swap ? sub1 : sub0;
             stack[sp++] = swap ? sub0 : sub1;
             return false;
