@@ -23,6 +23,23 @@ if ROOT not in sys.path:
 
 WIDTH, HEIGHT, MAX_DEPTH, TRIS = 1920, 1080, 5, 262144
 METRIC = "Mrays/s (closest-hit + shadow rays), 1080p atrium-262k path tracing, depth 5, NEE + RR"
+
+# BASELINE.json configs -> workloads. The default (and the driver's) run is configs[1] = "atrium"; the others are
+# selected with --workload and recorded under profiles/ by tools/run_configs.py.
+WORKLOADS = {
+    "atrium": dict(kind="pt", width=1920, height=1080, depth=5, model=0, tris=262144, seed=2, aperture=0.0, glossy=False,
+                   desc="atrium-262144 1080p depth-5 NEE+RR (BASELINE.json configs[1], procedural stand-in for Sponza)"),
+    "bathroom": dict(kind="pt", width=1920, height=1080, depth=5, model=1, tris=1000000, seed=3, aperture=0.5, glossy=True,
+                     desc="glossy interior ~1.0 M triangles, Beckmann microfacet + thin-lens DOF (lens radius 0.25), 1080p depth-5 "
+                          "(BASELINE.json configs[2], procedural stand-in for Salle de Bain)"),
+    "4k": dict(kind="pt", width=4096, height=2160, depth=5, model=0, tris=262144, seed=2, aperture=0.0, glossy=False,
+               desc="atrium-262144 4096x2160 depth-5 NEE+RR, samples split over the GPUs + NCCL reduce (BASELINE.json configs[4])"),
+    "micro": dict(kind="rays", n_rays=1 << 24, desc="16 777 216 random rays (origins uniform in the AABB, directions uniform on the "
+                  "sphere, unsorted) vs 8 nested displaced shells = 10 010 896 triangles: closest-hit + shadow any-hit "
+                  "(BASELINE.json configs[3])"),
+    "bunny": dict(kind="primary", width=1280, height=720,
+                  desc="bunny-like 69 196-triangle mesh: SAH/SBVH build + 1 spp primary closest-hit at 1280x720 (BASELINE.json configs[0])"),
+}
 # algorithmic bytes of the HBM data layout: ray in 32 B, hit out 16 B, node pair 64 B, leaf triangle 48 B
 B_RAY_IN, B_HIT_OUT, B_PAIR, B_TRI, B_FLAG_OUT = 32, 16, 64, 40, 4
 
@@ -69,35 +86,46 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def build_scene():
+def build_scene(wl=None):
     from gpupathtracer_b200 import Scene, scenes
-    data = scenes.atrium(target_tris=TRIS, seed=2)
+    wl = wl or WORKLOADS["atrium"]
+    data = scenes.atrium(target_tris=wl["tris"], seed=wl["seed"], aperture=wl["aperture"], glossy=wl["glossy"])
     return Scene(data)
 
 
-def make_camera(scene, w, h):
+def make_camera(scene, w, h, aspect=None):
     from gpupathtracer_b200 import Camera
     c = scene.data.camera
-    cam = Camera(WIDTH / HEIGHT, c["fov"], c["focus"], c["aperture"])
+    cam = Camera(aspect or (w / h), c["fov"], c["focus"], c["aperture"])
     cam.SetPosition(c["pos"]); cam.SetRotation(c["rot"]); cam.GenerateImagePlane()
     return cam
 
 
-def cpu_reference_run(scene, steps, warmup, w, h, threads=0):
+def traffic_for(workload, kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture (profiles/traffic.json), or None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f).get(workload, {}).get(kernel)
+
+
+def cpu_reference_run(scene, steps, warmup, w, h, wl, threads=0):
     """The reference's algorithm (CPU restatement, oracle/) on a bounded sample of the workload: the same scene,
     camera, depth and estimator at w x h pixels, 1 frame per step. Returns (Mrays/s, samples/s, ms/step, counters)."""
     import oracle
     from gpupathtracer_b200 import make_rng_table
     o = oracle.Oracle(scene)
-    cam = make_camera(scene, w, h).as_array()
+    cam = make_camera(scene, w, h, aspect=wl["width"] / wl["height"]).as_array()
     rng = make_rng_table(w * h, 1234)
     acc = np.zeros((h, w, 4), np.float32)
+    kw = dict(n_frames=1, max_depth=wl["depth"], model=wl["model"], n_threads=threads)
     for _ in range(warmup):
-        o.render(cam, w, h, rng, acc, n_frames=1, max_depth=MAX_DEPTH, n_threads=threads)
+        o.render(cam, w, h, rng, acc, **kw)
     tot = {"closest_rays": 0, "shadow_rays": 0, "node_pairs": 0, "tri_tests": 0, "shadow_node_pairs": 0, "shadow_tri_tests": 0}
     t0 = time.perf_counter()
     for _ in range(steps):
-        c = o.render(cam, w, h, rng, acc, n_frames=1, max_depth=MAX_DEPTH, n_threads=threads)
+        c = o.render(cam, w, h, rng, acc, **kw)
         for k in tot:
             tot[k] += c[k]
     dt = time.perf_counter() - t0
@@ -105,88 +133,175 @@ def cpu_reference_run(scene, steps, warmup, w, h, threads=0):
     return rays / dt / 1e6, steps * w * h / dt, dt / steps * 1e3, tot
 
 
+def metric_name(name, wl):
+    if name == "atrium":
+        return METRIC
+    if wl["kind"] == "pt":
+        return f"Mrays/s (closest-hit + shadow rays), {name} path tracing {wl['width']}x{wl['height']} depth {wl['depth']}, NEE + RR"
+    if wl["kind"] == "rays":
+        return "Mrays/s (closest-hit + shadow any-hit), 16M random rays vs 10M-triangle mesh"
+    return "Mrays/s (primary closest-hit), bunny-69k 1280x720 1 spp (+ BVH build ms)"
+
+
+CPU_SAMPLE = (480, 272)
+
+
+def micro_scene_and_rays(n_rays, seed):
+    from gpupathtracer_b200 import Scene, scenes
+    scene = Scene(scenes.shells())
+    lo, hi = scene.bounds()
+    closest = scenes.random_rays(n_rays, lo, hi, seed=seed)
+    anyr = closest.copy()
+    diag = float(np.linalg.norm(hi - lo))
+    anyr[:, 7] = np.random.default_rng(seed + 1).uniform(0, diag, size=n_rays).astype(np.float32)
+    return scene, closest, anyr
+
+
+def bytes_per_ray(c, n, out_bytes):
+    """B_ray = 32 (ray in) + out + pairs/ray * 64 + tris/ray * 40 on the tree the kernel traverses."""
+    pairs, tris = c["node_pairs"] / n, c["tri_tests"] / n
+    return B_RAY_IN + out_bytes + pairs * B_PAIR + tris * B_TRI, pairs, tris
+
+
 def run_reference(args):
+    """--impl reference: the reference's algorithm on the host cores (oracle/, all threads), bounded sample."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    scene = build_scene()
-    from gpupathtracer_b200 import build_bvh_host
     import oracle
-    if oracle.have_ref():
-        nodes, refs = oracle.ref_build_sbvh(scene.tris_abs)      # the reference's own builder
-        tree = "reference BuildBinnedSpatial (oracle/_ref)"
-    else:
-        nodes, refs, _ = build_bvh_host(scene.tris)
-        tree = "libb200pt host builder (oracle/_ref absent)"
-    scene.set_bvh(nodes, refs)
+    from gpupathtracer_b200 import build_bvh_host
+    wl = WORKLOADS[args.workload]
     cores = os.cpu_count() or 1
-    w, h = 480, 272
-    mrays, sps, ms, tot = cpu_reference_run(scene, args.steps, args.warmup, w, h)
-    line = {
-        "impl": "reference", "metric": METRIC, "value": mrays, "unit": "Mrays/s", "samples_per_s": sps,
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"atrium-{TRIS} 1080p depth-{MAX_DEPTH} NEE+RR", "tree": tree},
-        "cpu_baseline": {"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": "port",
-                         "sample": f"{w}x{h} px of the same camera/scene, 1 frame per step (the GLSL megakernel restated in C++; "
-                                   "reference GLSL via a GL stack: unavailable on this box)"},
-        "e2e": {"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }
+    base = {"impl": "reference", "metric": metric_name(args.workload, wl), "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic"}
+
+    def ref_tree(scene):
+        if oracle.have_ref():
+            t0 = time.perf_counter()
+            nodes, refs = oracle.ref_build_sbvh(scene.tris_abs)      # the reference's own builder, single-threaded as shipped
+            return nodes, refs, "reference BuildBinnedSpatial (oracle/_ref)", (time.perf_counter() - t0) * 1e3
+        t0 = time.perf_counter()
+        nodes, refs, _ = build_bvh_host(scene.tris)
+        return nodes, refs, "libb200pt host builder (oracle/_ref absent)", (time.perf_counter() - t0) * 1e3
+
+    if wl["kind"] == "pt":
+        scene = build_scene(wl)
+        nodes, refs, tree, _ = ref_tree(scene)
+        scene.set_bvh(nodes, refs)
+        w, h = CPU_SAMPLE
+        mrays, sps, ms, tot = cpu_reference_run(scene, args.steps, args.warmup, w, h, wl)
+        sample = (f"{w}x{h} px of the same camera/scene, 1 frame per step (the GLSL megakernel restated in C++; "
+                  "reference GLSL via a GL stack: unavailable on this box)")
+        extra = {"samples_per_s": sps}
+    elif wl["kind"] == "rays":
+        n = 1 << 20
+        scene, closest, anyr = micro_scene_and_rays(n, 0xB200)
+        nodes, refs, _ = build_bvh_host(scene.tris)                  # the reference builder needs minutes at 10 M triangles
+        tree = "libb200pt host builder"
+        scene.set_bvh(nodes, refs)
+        o = oracle.Oracle(scene)
+        for _ in range(args.warmup):
+            o.trace_closest(closest[:1 << 16])
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            o.trace_closest(closest); o.trace_any(anyr)
+        dt = time.perf_counter() - t0
+        mrays, ms = 2 * n * args.steps / dt / 1e6, dt / args.steps * 1e3
+        sample = f"first {n} closest-hit + {n} any-hit rays of the same batch per step"
+        extra = {}
+    else:
+        from gpupathtracer_b200 import Scene, scenes
+        scene = Scene(scenes.bunny_like(seed=1))
+        nodes, refs, tree, build_ms = ref_tree(scene)
+        scene.set_bvh(nodes, refs)
+        o = oracle.Oracle(scene)
+        w, h = wl["width"], wl["height"]
+        from gpupathtracer_b200 import make_rng_table
+        rng = make_rng_table(w * h, 1)
+        cam = make_camera(scene, w, h).as_array()
+        rays = np.zeros((w * h, 8), np.float32)
+        pr = o.raygen(cam, w, h, rng, 0, w * h)
+        rays[:, 0:3] = pr[:, 2:5]; rays[:, 4:7] = pr[:, 5:8]; rays[:, 7] = 1e20
+        for _ in range(args.warmup):
+            o.trace_closest(rays[:1 << 16])
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            o.trace_closest(rays)
+        dt = time.perf_counter() - t0
+        mrays, ms = w * h * args.steps / dt / 1e6, dt / args.steps * 1e3
+        sample = "all 921 600 primary rays per step"
+        extra = {"bvh_build_ms": build_ms, "bvh_builder": tree}
+    line = dict(base, value=mrays, ms_per_step=ms, config={"workload": wl["desc"], "tree": tree},
+                cpu_baseline={"value": mrays, "unit": "Mrays/s", "cores": cores, "kind": "port", "sample": sample},
+                e2e={"value": mrays, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, **extra)
     print(json.dumps(line))
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=64)
-    ap.add_argument("--warmup", type=int, default=4)
-    ap.add_argument("--impl", default="ours")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
-    args = ap.parse_args()
-    if args.impl == "reference":
-        return run_reference(args)
+class Dist:
+    """torch.distributed plumbing shared by the workloads (one process per GPU, NCCL)."""
 
-    import torch
-    import torch.distributed as dist
+    def __init__(self):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+
+    def barrier(self, r=None):
+        if r is not None:
+            r.Synchronize()
+        self.torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+
+    def max_sum(self, values):
+        """values: list of floats; element 0 is reduced with MAX (time), the rest with SUM (work)."""
+        t = self.torch.tensor(values, dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            tmax = t.clone(); self.dist.all_reduce(tmax, op=self.dist.ReduceOp.MAX)
+            tsum = t.clone(); self.dist.all_reduce(tsum, op=self.dist.ReduceOp.SUM)
+            return [float(tmax[0])] + [float(x) for x in tsum[1:]]
+        return [float(x) for x in t]
+
+    def close(self):
+        if self.world > 1:
+            self.dist.destroy_process_group()
+
+
+def run_pathtrace(args, name, wl):
+    d = Dist()
+    torch, dist, world, rank, local = d.torch, d.dist, d.world, d.rank, d.local
     from gpupathtracer_b200 import Renderer
-
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-
-    scene = build_scene()
+    W, H, depth = wl["width"], wl["height"], wl["depth"]
+    scene = build_scene(wl)
     t0 = time.perf_counter()
-    r = Renderer().Initialize(WIDTH, HEIGHT, scene, max_depth=MAX_DEPTH, device=local, seed=0xB200 ^ (rank * 0x9E3779B9),
-                              bvh="build")
+    r = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
+                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh="build")
     init_s = time.perf_counter() - t0
-    cam = make_camera(scene, WIDTH, HEIGHT)
+    cam = make_camera(scene, W, H)
     # accumulation buffer owned by torch so NCCL can reduce it in place
-    accum = torch.zeros((HEIGHT, WIDTH, 4), dtype=torch.float32, device="cuda")
+    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
     r.lib.pt_set_accum_device_ptr(r.ctx, accum.data_ptr())
-    pinned = torch.empty((HEIGHT, WIDTH, 3), dtype=torch.uint8).pin_memory()
-
-    def barrier():
-        r.Synchronize()
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
+    pinned = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    warmup = max(args.warmup, 3)
 
     # ---- warm-up
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         r.RenderFrame(cam, 1)
     if world > 1:
         r.Synchronize(); dist.reduce(accum, dst=0); torch.cuda.synchronize()
-    barrier()
+    d.barrier(r)
 
     # ---- timed region: K frames, device time from CUDA events on the library's stream (+ the reduce for N > 1)
     r.ResetSamples(); r.Synchronize()
     c0 = r.Counters()
-    r.SetStageTiming(True)
     sampler = ClockSampler(local); sampler.start()
-    barrier()
+    d.barrier(r)
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     r.RenderFrame(cam, args.steps)                 # K frames back to back; all inputs already resident in HBM
     r.Synchronize()
@@ -195,87 +310,280 @@ def main():
     if world > 1:
         ev0.record(); dist.reduce(accum, dst=0); ev1.record(); torch.cuda.synchronize()
         ms_reduce = ev0.elapsed_time(ev1)
-    barrier()
+    d.barrier(r)
     clocks = sampler.result()
+    c1 = r.Counters()
+    # per-kernel durations: a second pass with the frame as ONE launch sequence (no overlapping slices), CUDA events
+    # between kernels on the library's stream
+    stage_frames = min(args.steps, 16)
+    r.SetStageTiming(True)
+    r.RenderFrame(cam, stage_frames); r.Synchronize()
     stage = r.StageMs()
     r.SetStageTiming(False)
-    c1 = r.Counters()
-    ms_total = ms_render + ms_reduce
-    t = torch.tensor([ms_total, float(c1["closest_rays"] - c0["closest_rays"]), float(c1["shadow_rays"] - c0["shadow_rays"])],
-                     dtype=torch.float64, device="cuda")
-    if world > 1:
-        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
-        tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        ms_total = float(tmax[0]); closest = float(tsum[1]); shadow = float(tsum[2])
-    else:
-        closest, shadow = float(t[1]), float(t[2])
+    cs = r.Counters()
+    closest_stage = float(cs["closest_rays"] - c1["closest_rays"])
+    ms_total, closest, shadow = d.max_sum([ms_render + ms_reduce, float(c1["closest_rays"] - c0["closest_rays"]),
+                                           float(c1["shadow_rays"] - c0["shadow_rays"])])
     rays = closest + shadow
     value = rays / (ms_total * 1e-3) / 1e6
-    samples_per_s = world * args.steps * WIDTH * HEIGHT / (ms_total * 1e-3)
+    samples_per_s = world * args.steps * W * H / (ms_total * 1e-3)
 
     # ---- end to end through the public API with host buffers: camera in (H2D), presented 8-bit frame out (D2H)
-    barrier()
+    d.barrier(r)
     c2 = r.Counters()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        cam.GenerateImagePlane()
+    for i in range(args.steps):
+        cam.GenerateImagePlane()                   # host: Camera::GenerateImagePlane; H2D: the 76 B of camera uniforms
         r.RenderFrame(cam, 1)
-        r.ResolveInto(pinned.data_ptr())           # Present(): /numSamples + tonemap + D2H into pinned host memory
-    barrier()
+        r.PresentAsync(pinned[i & 1].data_ptr())   # Present(): /numSamples + tonemap, D2H into pinned host memory (double-buffered)
+    d.barrier(r)                                   # all K presented frames are in host memory here
     e2e_s = time.perf_counter() - t0
     c3 = r.Counters()
-    e2e = torch.tensor([e2e_s, float(c3["closest_rays"] - c2["closest_rays"] + c3["shadow_rays"] - c2["shadow_rays"])],
-                       dtype=torch.float64, device="cuda")
-    if world > 1:
-        emax = e2e.clone(); dist.all_reduce(emax, op=dist.ReduceOp.MAX)
-        esum = e2e.clone(); dist.all_reduce(esum, op=dist.ReduceOp.SUM)
-        e2e_s, e2e_rays = float(emax[0]), float(esum[1])
-    else:
-        e2e_rays = float(e2e[1])
+    e2e_s, e2e_rays = d.max_sum([e2e_s, float(c3["closest_rays"] - c2["closest_rays"] + c3["shadow_rays"] - c2["shadow_rays"])])
     e2e_value = e2e_rays / e2e_s / 1e6
 
     if rank == 0:
         peak, which = measured_peaks()
         line = {
-            "metric": METRIC, "value": value, "unit": "Mrays/s", "samples_per_s": samples_per_s,
-            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps,
+            "metric": metric_name(name, wl), "value": value, "unit": "Mrays/s", "samples_per_s": samples_per_s,
+            "n_gpus": world, "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"atrium-{TRIS} 1080p depth-{MAX_DEPTH} NEE+RR (BASELINE.json configs[1], procedural stand-in for Sponza)",
-                       "width": WIDTH, "height": HEIGHT, "max_depth": MAX_DEPTH, "triangles": scene.tris.shape[0],
-                       "microfacet": "ggx", "bvh": "own SBVH builder, reference layout",
-                       "l2": "per-step working set (path state + queues + accum, ~0.5 GB) exceeds the 126 MB L2",
+            "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
+                       "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
+                       "bvh": "own SBVH builder, reference layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
+                       "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
+                       "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
                        "parallelism": f"samples split over {world} GPU(s), 1 NCCL reduce of the accumulation buffer per {args.steps}-frame batch",
                        "init_s": init_s},
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": WIDTH * HEIGHT * 3,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": W * H * 3,
                     "ms_per_step": e2e_s / args.steps * 1e3},
             "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]),
             "clocks": clocks,
-            "stage_ms_per_step": {k: v / args.steps for k, v in stage.items()},
+            "stage_ms_per_step": {k: v / stage_frames for k, v in stage.items()},
+            "stage_note": f"per-kernel times from a separate {stage_frames}-frame pass without slice overlap; their sum exceeds "
+                          "ms_per_step because the timed region overlaps slices",
             "ms_reduce": ms_reduce,
         }
         # ---- CPU baseline (bounded sample) + visit counts for the algorithmic-bytes figure
         if world == 1 and not args.no_cpu_baseline:
-            w, h = 480, 272
-            mrays, sps, ms, tot = cpu_reference_run(scene, 4, 1, w, h)
+            w, h = CPU_SAMPLE
+            mrays, sps, ms, tot = cpu_reference_run(scene, 4, 1, w, h, wl)
             line["cpu_baseline"] = {"value": mrays, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
                                     "sample": f"{w}x{h} px of the same camera/scene/tree, 4 frames, all host cores",
                                     "samples_per_s": sps}
-            n_c, n_s = tot["closest_rays"], tot["shadow_rays"]
+            n_c = tot["closest_rays"]
             pairs_c = (tot["node_pairs"] - tot["shadow_node_pairs"]) / n_c
             tris_c = (tot["tri_tests"] - tot["shadow_tri_tests"]) / n_c
             b_ray = B_RAY_IN + B_HIT_OUT + pairs_c * B_PAIR + tris_c * B_TRI
             ext_s = stage["extend"] * 1e-3
-            achieved = closest * b_ray / ext_s / 1e9 if ext_s > 0 else None
+            launches = stage_frames * depth
+            achieved = closest_stage * b_ray / ext_s / 1e9 if ext_s > 0 else None
             line["roofline"] = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": which,
+                                "frac": achieved / peak if achieved else None, "traffic": traffic_for(name, "k_extend"),
+                                "algorithmic_bytes_per_launch": closest_stage * b_ray / launches, "peak_source": which,
                                 "bytes_per_ray": b_ray, "pairs_per_ray": pairs_c, "tris_per_ray": tris_c,
-                                "launches": args.steps * MAX_DEPTH,
-                                "avg_launch_ms": stage["extend"] / (args.steps * MAX_DEPTH),
-                                "note": "scene (~35 MB) is L2-resident: HBM fraction is a lower bound story, see DESIGN.md"}
+                                "launches": launches, "avg_launch_ms": stage["extend"] / launches,
+                                "note": "scene (~50 MB) is L2-resident: algorithmic bytes are served by L1/L2, the binding limit is the "
+                                        "L1 data pipe (DESIGN.md 4); the HBM-bound case is --workload micro"}
         print(json.dumps(line))
     r.CleanUp()
-    if world > 1:
-        dist.destroy_process_group()
+    d.close()
+
+
+def run_micro(args, name, wl):
+    """configs[3]: fixed ray batches against a scene far larger than L2 -- the HBM-bound case."""
+    d = Dist()
+    torch, world, rank, local = d.torch, d.world, d.rank, d.local
+    from gpupathtracer_b200 import Renderer
+    n = wl["n_rays"]
+    scene, closest, anyr = micro_scene_and_rays(n, 0xB200 + 7 * rank)
+    t0 = time.perf_counter()
+    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh="build")
+    init_s = time.perf_counter() - t0
+    d_closest = torch.from_numpy(closest).cuda()
+    d_any = torch.from_numpy(anyr).cuda()
+    d_hits = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    d_flags = torch.empty((n,), dtype=torch.uint8, device="cuda")
+    h_closest = torch.from_numpy(closest).pin_memory()
+    h_any = torch.from_numpy(anyr).pin_memory()
+    h_hits = torch.empty((n, 4), dtype=torch.float32).pin_memory()
+    h_flags = torch.empty((n,), dtype=torch.uint8).pin_memory()
+    torch.cuda.synchronize()
+    warmup = max(args.warmup, 3)
+    steps = args.steps
+
+    def step_device():
+        r.TraceClosestDevice(d_closest.data_ptr(), n, d_hits.data_ptr()); ms_c = r.LastDeviceMs()
+        r.TraceAnyDevice(d_any.data_ptr(), n, d_flags.data_ptr()); ms_a = r.LastDeviceMs()
+        return ms_c, ms_a
+
+    for _ in range(warmup):
+        step_device()
+    d.barrier(r)
+    c0 = r.Counters()
+    sampler = ClockSampler(local); sampler.start()
+    ms_c = ms_a = 0.0
+    for _ in range(steps):                         # rays (2 x 512 MB) and tree (1.2 GB) are far larger than L2
+        a, b = step_device(); ms_c += a; ms_a += b
+    d.barrier(r)
+    clocks = sampler.result()
+    c1 = r.Counters()
+    ms_total, rays = d.max_sum([ms_c + ms_a, 2.0 * n * steps])
+    value = rays / (ms_total * 1e-3) / 1e6
+
+    # ---- end to end: host ray batches in (pinned), hits / flags out, through pt_trace_closest / pt_trace_any
+    d.barrier(r)
+    t0 = time.perf_counter()
+    e2e_steps = min(steps, 4)
+    for _ in range(e2e_steps):
+        r.TraceClosestHost(h_closest.data_ptr(), n, h_hits.data_ptr())
+        r.TraceAnyHost(h_any.data_ptr(), n, h_flags.data_ptr())
+    d.barrier(r)
+    e2e_s, e2e_rays = d.max_sum([time.perf_counter() - t0, 2.0 * n * e2e_steps])
+
+    if rank == 0:
+        peak, which = measured_peaks()
+        hits = d_hits.cpu().numpy()
+        line = {
+            "metric": metric_name(name, wl), "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "rays_per_step": 2 * n,
+                       "bvh": "own SBVH builder, reference layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
+                       "bvh_nodes": int(r.bvh_stats.n_nodes), "bvh_refs": int(r.bvh_stats.n_refs),
+                       "l2": "ray batches (2 x 512 MB) and tree + leaf stream (~1.2 GB) exceed the 126 MB L2",
+                       "parallelism": f"{world} independent replica(s), each with its own 16M-ray batch; no collective", "init_s": init_s},
+            "closest_mrays_s": n * steps / (ms_c * 1e-3) / 1e6, "any_mrays_s": n * steps / (ms_a * 1e-3) / 1e6,
+            "hit_fraction": float((hits[:, 3].view(np.int32) >= 0).mean()),
+            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 2 * n * 32, "d2h_bytes_per_step": n * 16 + n,
+                    "ms_per_step": e2e_s / e2e_steps * 1e3},
+            "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]),
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            import oracle
+            o = oracle.Oracle(scene)
+            m = 1 << 19
+            t0 = time.perf_counter()
+            want, cc = o.trace_closest(closest[:m])
+            wflag, ca = o.trace_any(anyr[:m])
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": 2 * m / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
+                                    "sample": f"first {m} closest-hit + {m} any-hit rays of the same batch, all host cores"}
+            line["parity_on_sample"] = {"closest_bit_exact": bool(np.array_equal(want.view(np.uint32), hits[:m].view(np.uint32))),
+                                        "any_bit_exact": bool(np.array_equal(wflag, d_flags[:m].cpu().numpy()))}
+            b_ray, pairs, tris = bytes_per_ray(cc, m, B_HIT_OUT)
+            achieved = n * b_ray / (ms_c / steps * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                                "frac": achieved / peak, "traffic": traffic_for(name, "k_trace_batch<false>"),
+                                "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
+                                "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": steps, "avg_launch_ms": ms_c / steps}
+        print(json.dumps(line))
+    r.CleanUp()
+    d.close()
+
+
+def run_primary(args, name, wl):
+    """configs[0]: BVH build + 1 spp primary closest-hit at 1280x720."""
+    d = Dist()
+    torch, world, rank, local = d.torch, d.world, d.rank, d.local
+    from gpupathtracer_b200 import Renderer, Scene, scenes, build_bvh_host
+    W, H = wl["width"], wl["height"]
+    scene = Scene(scenes.bunny_like(seed=1))
+    builds = []
+    for _ in range(3):
+        _, _, st = build_bvh_host(scene.tris)
+        builds.append(st["build_ms"])
+    r = Renderer().Initialize(W, H, scene, max_depth=1, device=local, seed=0xB200 + rank, bvh="build")
+    cam = make_camera(scene, W, H)
+    r.lib.pt_set_camera(r.ctx, cam.plane)
+    n = W * H
+    pr = r.RaygenProbe(0, n)
+    rays = np.zeros((n, 8), np.float32)
+    rays[:, 0:3] = pr[:, 2:5]; rays[:, 4:7] = pr[:, 5:8]; rays[:, 7] = 1e20
+    d_rays = torch.from_numpy(rays).cuda()
+    d_hits = torch.empty((n, 4), dtype=torch.float32, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    h_rays = torch.from_numpy(rays).pin_memory(); h_hits = torch.empty((n, 4), dtype=torch.float32).pin_memory()
+    torch.cuda.synchronize()
+    warmup = max(args.warmup, 3)
+    for _ in range(warmup):
+        r.TraceClosestDevice(d_rays.data_ptr(), n, d_hits.data_ptr())
+    d.barrier(r)
+    sampler = ClockSampler(local); sampler.start()
+    ms = 0.0
+    c0 = r.Counters()
+    for _ in range(args.steps):
+        flush.zero_(); torch.cuda.synchronize()    # 256 MB write between timed launches: L2 flushed
+        r.TraceClosestDevice(d_rays.data_ptr(), n, d_hits.data_ptr()); ms += r.LastDeviceMs()
+    d.barrier(r)
+    clocks = sampler.result()
+    c1 = r.Counters()
+    ms_total, rays_total = d.max_sum([ms, float(n * args.steps)])
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        r.TraceClosestHost(h_rays.data_ptr(), n, h_hits.data_ptr())
+    d.barrier(r)
+    e2e_s, e2e_rays = d.max_sum([time.perf_counter() - t0, float(n * args.steps)])
+    if rank == 0:
+        peak, which = measured_peaks()
+        hits = d_hits.cpu().numpy()
+        line = {
+            "metric": metric_name(name, wl), "value": rays_total / (ms_total * 1e-3) / 1e6, "unit": "Mrays/s", "n_gpus": world,
+            "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "width": W, "height": H,
+                       "bvh": "own SBVH builder (host, all cores), reference layout", "l2": "256 MB flush between timed launches"},
+            "bvh_build_ms": {"ours_host_all_cores_best_of_3": min(builds), "nodes": int(r.bvh_stats.n_nodes), "refs": int(r.bvh_stats.n_refs),
+                             "sah_cost": float(r.bvh_stats.sah_cost)},
+            "hit_fraction": float((hits[:, 3].view(np.int32) >= 0).mean()),
+            "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,
+                    "ms_per_step": e2e_s / args.steps * 1e3},
+            "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]),
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            import oracle
+            o = oracle.Oracle(scene)
+            t0 = time.perf_counter()
+            want, cc = o.trace_closest(rays)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": n / dt / 1e6, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": "port",
+                                    "sample": "all 921 600 primary rays, same tree, all host cores"}
+            line["parity_on_sample"] = {"closest_bit_exact": bool(np.array_equal(want.view(np.uint32), hits.view(np.uint32)))}
+            if oracle.have_ref():
+                t0 = time.perf_counter()
+                oracle.ref_build_sbvh(scene.tris_abs)
+                line["bvh_build_ms"]["reference_BuildBinnedSpatial_1_thread"] = (time.perf_counter() - t0) * 1e3
+            b_ray, pairs, tris = bytes_per_ray(cc, n, B_HIT_OUT)
+            achieved = n * b_ray / (ms_total / args.steps * 1e-3) / 1e9
+            line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                                "frac": achieved / peak, "traffic": traffic_for(name, "k_trace_batch<false>"),
+                                "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
+                                "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": args.steps, "avg_launch_ms": ms_total / args.steps,
+                                "note": "coherent primary rays on a 10 MB tree: L1/L2-resident, issue-slot bound (DESIGN.md 4)"}
+        print(json.dumps(line))
+    r.CleanUp()
+    d.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.steps is None:
+        args.steps = {"pt": 64, "rays": 8, "primary": 32}[wl["kind"]] if args.impl != "reference" else 3
+        if args.workload == "4k":
+            args.steps = 16
+    if args.impl == "reference":
+        return run_reference(args)
+    {"pt": run_pathtrace, "rays": run_micro, "primary": run_primary}[wl["kind"]](args, args.workload, wl)
 
 
 if __name__ == "__main__":

@@ -27,7 +27,7 @@ class PtError(RuntimeError):
 class pt_config(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_depth", C.c_int32),
                 ("microfacet_model", C.c_int32), ("device", C.c_int32), ("bvh_layout", C.c_int32),
-                ("reserved", C.c_int32 * 6)]
+                ("n_slices", C.c_int32), ("reserved", C.c_int32 * 5)]
 
 
 class pt_camera(C.Structure):
@@ -82,6 +82,7 @@ SYMBOLS = [
     ("pt_accum_device_ptr", _P, [_P]),
     ("pt_set_accum_device_ptr", C.c_int, [_P, _P]),
     ("pt_resolve", C.c_int, [_P, C.c_uint32, _P, _P]),
+    ("pt_present_async", C.c_int, [_P, C.c_uint32, _P]),
     ("pt_save_screenshot", C.c_int, [_P, C.c_char_p]),
     ("pt_trace_closest", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_trace_any", C.c_int, [_P, _P, C.c_int64, _P]),
@@ -238,9 +239,9 @@ class Renderer:
 
     # -- Renderer::Initialize, Renderer.cpp:448-636
     def Initialize(self, width, height, scene, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=PT_MICROFACET_GGX,
-                   device=0, rng_state=None, seed=None, bvh="given"):
+                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0):
         cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
-                        device=device, bvh_layout=PT_BVH_REFERENCE)
+                        device=device, bvh_layout=PT_BVH_REFERENCE, n_slices=n_slices)
         ctx = C.c_void_p()
         _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
         self.ctx = ctx
@@ -332,6 +333,20 @@ class Renderer:
         _check(self.lib.pt_trace_any(self.ctx, _ptr(rays), rays.shape[0], _ptr(flags)))
         return flags
 
+    def TraceClosestDevice(self, d_rays, n, d_hits):
+        """Device-resident batch (raw device pointers); asynchronous on the library's stream."""
+        _check(self.lib.pt_trace_closest_device(self.ctx, C.c_void_p(d_rays), n, C.c_void_p(d_hits)))
+
+    def TraceAnyDevice(self, d_rays, n, d_flags):
+        _check(self.lib.pt_trace_any_device(self.ctx, C.c_void_p(d_rays), n, C.c_void_p(d_flags)))
+
+    def TraceClosestHost(self, h_rays, n, h_hits):
+        """Host batch given as raw (ideally pinned) host pointers: H2D, trace, D2H, synchronous."""
+        _check(self.lib.pt_trace_closest(self.ctx, C.c_void_p(h_rays), n, C.c_void_p(h_hits)))
+
+    def TraceAnyHost(self, h_rays, n, h_flags):
+        _check(self.lib.pt_trace_any(self.ctx, C.c_void_p(h_rays), n, C.c_void_p(h_flags)))
+
     def RaygenProbe(self, first, n):
         out = np.zeros((n, 12), dtype=np.float32)
         _check(self.lib.pt_raygen_probe(self.ctx, first, n, _ptr(out)))
@@ -356,6 +371,10 @@ class Renderer:
     def ResolveInto(self, host_ptr_u8, num_samples=None):
         """Present into caller-owned (ideally pinned) host memory: height*width*3 bytes."""
         _check(self.lib.pt_resolve(self.ctx, num_samples or self.GetNumSamples(), None, C.c_void_p(host_ptr_u8)))
+
+    def PresentAsync(self, host_ptr_u8, num_samples=None):
+        """Present() whose D2H copy overlaps the next frame (pt_present_async); complete after Synchronize()."""
+        _check(self.lib.pt_present_async(self.ctx, num_samples or self.GetNumSamples(), C.c_void_p(host_ptr_u8)))
 
     def AccumDevicePtr(self):
         return int(self.lib.pt_accum_device_ptr(self.ctx))

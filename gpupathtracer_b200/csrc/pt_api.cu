@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include <chrono>
+#include <cstdlib>
 
 using namespace pt;
 
@@ -45,6 +46,24 @@ struct pt_context {
     pt_config cfg;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // A frame is cut into n_slices ranges of ray indices (pixel-disjoint, so RNG table and accum need no
+    // synchronisation); every slice runs its own raygen -> (extend, shade, shadow)* sequence on its own stream,
+    // so the drain phase of one slice's persistent kernel is filled by another slice's kernels.
+    // Inside a slice, shadow(b) and extend(b+1) run concurrently on two streams (enqueue_frame_dag). The whole
+    // fork/join structure of `g` consecutive frames is captured once into a CUDA graph and replayed.
+    int n_slices = 1, slice_size = 0;
+    std::vector<SliceStreams> slice_streams;
+    std::vector<cudaEvent_t> slice_done;      // 2 per slice (streams a and b)
+    cudaEvent_t ev_fork = nullptr;
+    bool use_graph = true;
+    struct FrameGraph { cudaGraphExec_t exec = nullptr; int launches = 0; };
+    FrameGraph graph;                          // one frame, all slices
+    DevBuf<CameraRec> d_cam;
+    // pt_present_async: double-buffered resolve target + copy stream
+    cudaStream_t copy_stream = nullptr;
+    DevBuf<unsigned char> d_present[2];
+    cudaEvent_t ev_resolved = nullptr, ev_copied[2] = {nullptr, nullptr};
+    int present_turn = 0;
     LaunchDims dims{};
     float last_ms = 0.0f;
     pt_counters counters{};
@@ -90,6 +109,11 @@ struct pt_context {
     int stage_frames = 0, stage_events_per_frame = 0;
 };
 
+static void invalidate_graphs(pt_context* c) {
+    if (c->graph.exec) cudaGraphExecDestroy(c->graph.exec);
+    c->graph.exec = nullptr; c->graph.launches = 0;
+}
+
 static SceneDev scene_dev(pt_context* c) {
     SceneDev s{};
     s.pairs = c->d_pairs.p; s.leaf_tris = c->d_leaf.p; s.n_leaf_tris = c->n_leaf;
@@ -133,6 +157,32 @@ int pt_create(const pt_config* cfg, pt_context** out) {
     CK(cudaEventCreate(&c->ev1));
     query_launch_dims(cfg->device, &c->dims);
     const size_t npx = (size_t)cfg->width * cfg->height;
+    {
+        int want = cfg->n_slices > 0 ? cfg->n_slices : 3;
+        if (const char* e = getenv("PT_SLICES")) want = atoi(e);
+        if (want < 1) want = 1;
+        if (want > 16) want = 16;
+        size_t sz = (npx + want - 1) / want;
+        sz = (sz + 63) / 64 * 64;                               // whole 8x8 Morton tiles (Iterative.comp:163-172)
+        c->slice_size = (int)sz;
+        c->n_slices = (int)((npx + sz - 1) / sz);
+        c->slice_streams.resize(c->n_slices); c->slice_done.resize(2 * c->n_slices);
+        for (int s = 0; s < c->n_slices; s++) {
+            SliceStreams& ss = c->slice_streams[s];
+            CK(cudaStreamCreateWithFlags(&ss.a, cudaStreamNonBlocking));
+            CK(cudaStreamCreateWithFlags(&ss.b, cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&ss.ev_shade, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&ss.ev_shadow, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&c->slice_done[2 * s], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&c->slice_done[2 * s + 1], cudaEventDisableTiming));
+        }
+        CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+        if (const char* e = getenv("PT_NO_GRAPH")) c->use_graph = atoi(e) == 0;
+        CK(c->d_cam.alloc(1));
+        CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&c->ev_resolved, cudaEventDisableTiming));
+        for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming));
+    }
     CK(c->d_rng.alloc(npx));
     CK(c->d_accum_own.alloc(npx));
     c->d_accum = c->d_accum_own.p;
@@ -143,7 +193,7 @@ int pt_create(const pt_config* cfg, pt_context** out) {
     }
     for (int k = 0; k < 4; k++) CK(c->d_shadow[k].alloc(npx));
     CK(c->d_hits.alloc(npx));
-    CK(c->d_counters.alloc(cfg->max_depth + 2));
+    CK(c->d_counters.alloc((size_t)2 * c->n_slices * (cfg->max_depth + 2)));   // 2 blocks per slice: frame parity
     CK(c->d_totals.alloc(4));
     CK(cudaMemsetAsync(c->d_totals.p, 0, 4 * sizeof(unsigned long long), c->stream));
     CK(c->d_cursor.alloc(4));
@@ -166,6 +216,18 @@ void pt_destroy(pt_context* c) {
     c->d_resolve_f32.release(); c->d_resolve_u8.release();
     for (cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
+    for (SliceStreams& ss : c->slice_streams) {
+        cudaStreamSynchronize(ss.a); cudaStreamSynchronize(ss.b);
+        cudaStreamDestroy(ss.a); cudaStreamDestroy(ss.b);
+        cudaEventDestroy(ss.ev_shade); cudaEventDestroy(ss.ev_shadow);
+    }
+    for (cudaEvent_t e : c->slice_done) cudaEventDestroy(e);
+    if (c->graph.exec) cudaGraphExecDestroy(c->graph.exec);
+    c->d_cam.release();
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->ev_resolved) cudaEventDestroy(c->ev_resolved);
+    for (int k = 0; k < 2; k++) { if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); c->d_present[k].release(); }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -200,6 +262,7 @@ int pt_set_triangles(pt_context* c, const float* tris, int64_t n) {
     if (!c || !tris || n <= 0) return fail(PT_ERR_INVALID, "pt_set_triangles: bad argument");
     if (n >= (1ll << 30)) return fail(PT_ERR_LIMIT, "pt_set_triangles: too many triangles");
     CK(cudaSetDevice(c->cfg.device));
+    invalidate_graphs(c);
     c->h_tris.assign(tris, tris + 20 * n);
     CK(c->d_tris.alloc(5 * (size_t)n));
     CK(cudaMemcpyAsync(c->d_tris.p, tris, 80 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
@@ -211,6 +274,7 @@ int pt_set_materials(pt_context* c, const pt_material* mats, int32_t n_mats, con
     if (!c || !mats || n_mats <= 0 || n_tex < 0 || (n_tex > 0 && !tex)) return fail(PT_ERR_INVALID, "pt_set_materials: bad argument");
     CK(cudaSetDevice(c->cfg.device));
     static_assert(sizeof(pt_material) == sizeof(MaterialRec), "material record layout");
+    invalidate_graphs(c);
     c->h_mats.assign(mats, mats + n_mats);
     CK(c->d_mats.alloc(n_mats));
     CK(cudaMemcpyAsync(c->d_mats.p, mats, sizeof(pt_material) * n_mats, cudaMemcpyHostToDevice, c->stream));
@@ -237,6 +301,7 @@ int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_
     if (!c || !lights || n <= 0) return fail(PT_ERR_INVALID, "pt_set_lights: a scene needs at least one emissive triangle (Iterative.comp:42-61)");
     CK(cudaSetDevice(c->cfg.device));
     static_assert(sizeof(pt_light) == sizeof(float2), "light record layout");
+    invalidate_graphs(c);
     CK(c->d_lights.alloc(n));
     CK(cudaMemcpyAsync(c->d_lights.p, lights, sizeof(pt_light) * n, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -246,11 +311,13 @@ int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_
 
 int pt_set_environment_color(pt_context* c, const float rgb[3]) {
     if (!c || !rgb) return fail(PT_ERR_INVALID, "pt_set_environment_color: bad argument");
+    invalidate_graphs(c);
     c->env[0] = rgb[0]; c->env[1] = rgb[1]; c->env[2] = rgb[2];
     return PT_OK;
 }
 
 static int install_bvh(pt_context* c) {
+    invalidate_graphs(c);
     const float* nodes = c->h_bvh.nodes.data();
     const int n_nodes = (int)(c->h_bvh.nodes.size() / 8);
     const int n_pairs = (n_nodes - 1) / 2;
@@ -325,6 +392,9 @@ int pt_set_camera(pt_context* c, const pt_camera* cam) {
     if (!c || !cam) return fail(PT_ERR_INVALID, "pt_set_camera: bad argument");
     static_assert(sizeof(pt_camera) == sizeof(CameraRec), "camera record layout");
     memcpy(&c->cam, cam, sizeof(CameraRec));
+    CK(cudaSetDevice(c->cfg.device));
+    // 76 bytes of uniforms (Shader::LoadCamera); stream-ordered, so frames already queued keep their camera
+    CK(cudaMemcpyAsync(c->d_cam.p, &c->cam, sizeof(CameraRec), cudaMemcpyHostToDevice, c->stream));
     c->have_cam = true;
     return PT_OK;
 }
@@ -368,22 +438,64 @@ static int check_scene(pt_context* c, const char* who, bool need_shading) {
     return PT_OK;
 }
 
-static FrameParams frame_params(pt_context* c) {
+// parameters of the launch sequence that owns ray indices [first, first + count); counter block `block`
+static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, int block = 0) {
     FrameParams p{};
     p.scene = scene_dev(c);
-    p.cam = c->cam;
+    p.cam = c->d_cam.p;
     p.width = c->cfg.width; p.height = c->cfg.height;
+    p.slice_first = first; p.slice_count = count < 0 ? c->cfg.width * c->cfg.height : count;
     p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model;
     p.rng_table = c->d_rng.p; p.accum = c->d_accum;
+    const size_t o = (size_t)first;                              // the slice's sub-range of every per-path array
     for (int q = 0; q < 2; q++) {
-        p.queue[q].q0 = c->d_q[q][0].p; p.queue[q].q1 = c->d_q[q][1].p; p.queue[q].q2 = c->d_q[q][2].p;
-        p.queue[q].q3 = c->d_q[q][3].p; p.queue[q].q4 = c->d_qrng[q].p;
+        p.queue[q].q0 = c->d_q[q][0].p + o; p.queue[q].q1 = c->d_q[q][1].p + o; p.queue[q].q2 = c->d_q[q][2].p + o;
+        p.queue[q].q3 = c->d_q[q][3].p + o; p.queue[q].q4 = c->d_qrng[q].p + o;
     }
-    p.shadow.s0 = c->d_shadow[0].p; p.shadow.s1 = c->d_shadow[1].p; p.shadow.s2 = c->d_shadow[2].p; p.shadow.s3 = c->d_shadow[3].p;
-    p.hits = c->d_hits.p;
-    p.counters = c->d_counters.p;
+    p.shadow.s0 = c->d_shadow[0].p + o; p.shadow.s1 = c->d_shadow[1].p + o; p.shadow.s2 = c->d_shadow[2].p + o; p.shadow.s3 = c->d_shadow[3].p + o;
+    p.hits = c->d_hits.p + o;
+    p.counters = c->d_counters.p + (size_t)block * (c->cfg.max_depth + 2);
     p.totals = c->d_totals.p;
     return p;
+}
+
+
+
+// `g` consecutive frames of every slice between a fork from and a join into the main stream. Slices advance through
+// their frames independently; stream-capturable (every cross-stream edge is an event).
+static int enqueue_frames(pt_context* c, int g) {
+    const int npx = c->cfg.width * c->cfg.height;
+    int launches = 0;
+    cudaEventRecord(c->ev_fork, c->stream);
+    for (int s = 0; s < c->n_slices; s++) cudaStreamWaitEvent(c->slice_streams[s].a, c->ev_fork, 0);
+    for (int f = 0; f < g; f++)
+        for (int s = 0; s < c->n_slices; s++) {
+            int first = s * c->slice_size;
+            int count = npx - first < c->slice_size ? npx - first : c->slice_size;
+            FrameParams p = frame_params(c, first, count, 2 * s + (f & 1));
+            launches += enqueue_frame_dag(p, c->dims, c->slice_streams[s], f > 0);
+        }
+    for (int s = 0; s < c->n_slices; s++) {
+        cudaEventRecord(c->slice_done[2 * s], c->slice_streams[s].a);
+        cudaEventRecord(c->slice_done[2 * s + 1], c->slice_streams[s].b);
+        cudaStreamWaitEvent(c->stream, c->slice_done[2 * s], 0);
+        cudaStreamWaitEvent(c->stream, c->slice_done[2 * s + 1], 0);
+    }
+    return launches;
+}
+
+static int ensure_graph(pt_context* c) {
+    if (c->graph.exec) return PT_OK;
+    cudaGraph_t graph = nullptr;
+    CK(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+    int launches = enqueue_frames(c, 1);
+    cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+    if (e != cudaSuccess || !graph) { cudaGetLastError(); return fail(PT_ERR_CUDA, "frame graph capture failed: %s", cudaGetErrorString(e)); }
+    e = cudaGraphInstantiate(&c->graph.exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (e != cudaSuccess) { c->graph.exec = nullptr; return fail(PT_ERR_CUDA, "cudaGraphInstantiate failed: %s", cudaGetErrorString(e)); }
+    c->graph.launches = launches;
+    return PT_OK;
 }
 
 int pt_render_frames(pt_context* c, int32_t n_frames) {
@@ -391,17 +503,29 @@ int pt_render_frames(pt_context* c, int32_t n_frames) {
     CK(cudaSetDevice(c->cfg.device));
     int rc = check_scene(c, "pt_render_frames", true);
     if (rc != PT_OK) return rc;
-    FrameParams p = frame_params(c);
     CK(cudaEventRecord(c->ev0, c->stream));
     const int epf = 3 * c->cfg.max_depth + 3;
     if (c->stage_timing) {
-        while ((int)c->stage_events.size() < epf * n_frames) {
-            cudaEvent_t e; CK(cudaEventCreate(&e)); c->stage_events.push_back(e);
+        // one launch sequence for the whole frame on the main stream (per-stage events need kernels that do not overlap)
+        FrameParams p = frame_params(c);
+        if (c->stage_timing) {
+            while ((int)c->stage_events.size() < epf * n_frames) {
+                cudaEvent_t e; CK(cudaEventCreate(&e)); c->stage_events.push_back(e);
+            }
+            c->stage_frames = n_frames; c->stage_events_per_frame = epf;
         }
-        c->stage_frames = n_frames; c->stage_events_per_frame = epf;
+        for (int f = 0; f < n_frames; f++)
+            c->counters.kernel_launches += launch_frame(p, c->dims, c->stream, c->stage_timing ? c->stage_events.data() + (size_t)f * epf : nullptr);
+    } else if (c->use_graph && n_frames == 1) {
+        // the interactive case (one RenderFrame per Present): replay the captured fork/join DAG of one frame
+        int rc2 = ensure_graph(c);
+        if (rc2 != PT_OK) return rc2;
+        CK(cudaGraphLaunch(c->graph.exec, c->stream));
+        c->counters.kernel_launches += c->graph.launches;
+    } else {
+        // batches: slices run through all their frames without a join in between (measured faster than replaying graphs)
+        c->counters.kernel_launches += enqueue_frames(c, n_frames);
     }
-    for (int f = 0; f < n_frames; f++)
-        c->counters.kernel_launches += launch_frame(p, c->dims, c->stream, c->stage_timing ? c->stage_events.data() + (size_t)f * epf : nullptr);
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaGetLastError());
     c->num_samples += n_frames;
@@ -413,6 +537,7 @@ int pt_synchronize(pt_context* c) {
     if (!c) return fail(PT_ERR_INVALID, "pt_synchronize: null context");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(c->copy_stream));
     return PT_OK;
 }
 
@@ -436,6 +561,7 @@ int pt_download_accum(pt_context* c, float* rgba) {
 void* pt_accum_device_ptr(pt_context* c) { return c ? (void*)c->d_accum : nullptr; }
 int pt_set_accum_device_ptr(pt_context* c, void* dev_rgba) {
     if (!c) return fail(PT_ERR_INVALID, "pt_set_accum_device_ptr: null context");
+    invalidate_graphs(c);
     c->d_accum = dev_rgba ? (float4*)dev_rgba : c->d_accum_own.p;
     return PT_OK;
 }
@@ -453,6 +579,23 @@ int pt_resolve(pt_context* c, uint32_t num_samples, float* rgb_f32, uint8_t* rgb
     if (rgb_f32) CK(cudaMemcpyAsync(rgb_f32, d_f, npx * 12, cudaMemcpyDeviceToHost, c->stream));
     if (rgb_u8) CK(cudaMemcpyAsync(rgb_u8, d_u, npx * 3, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
+int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) {
+    if (!c || num_samples == 0 || !host_rgb_u8) return fail(PT_ERR_INVALID, "pt_present_async: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    const size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    const int k = c->present_turn; c->present_turn ^= 1;
+    CK(c->d_present[k].alloc(npx * 3));
+    CK(cudaStreamWaitEvent(c->stream, c->ev_copied[k], 0));          // the copy that last used this buffer (no-op the first time)
+    launch_resolve(c->d_accum, (long long)npx, num_samples, nullptr, c->d_present[k].p, c->stream);
+    c->counters.kernel_launches++;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev_resolved, c->stream));
+    CK(cudaStreamWaitEvent(c->copy_stream, c->ev_resolved, 0));
+    CK(cudaMemcpyAsync(host_rgb_u8, c->d_present[k].p, npx * 3, cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaEventRecord(c->ev_copied[k], c->copy_stream));
     return PT_OK;
 }
 

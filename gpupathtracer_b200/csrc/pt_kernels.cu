@@ -57,17 +57,17 @@ void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsign
 // ------------------------------------------------------------------ ray generation
 __global__ void __launch_bounds__(PT_STREAM_THREADS)
 k_raygen(FrameParams p) {
-    const int n = p.width * p.height;
+    const int n = p.slice_count;
     if (blockIdx.x == 0 && threadIdx.x == 0) p.counters[0].n_paths = n;
     const PathQueue q = p.queue[0];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         int px, py;
-        ray_index_to_morton(i, p.width, px, py);
+        ray_index_to_morton(p.slice_first + i, p.width, px, py);
         int pix = py * p.width + px;
         uint4 st = p.rng_table[pix];                         // initRNG, Random.glsl:232-237
         Rng rng; rng.x = st.x; rng.y = st.y; rng.z = st.z; rng.w = st.w;
         V3 o, d;
-        init_ray(p.cam, p.width, p.height, px, py, rng, o, d);
+        init_ray(*p.cam, p.width, p.height, px, py, rng, o, d);
         q.q0[i] = f4(o, 1.0f);
         q.q1[i] = f4(d, 1.0f);
         q.q2[i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(pix));
@@ -85,7 +85,7 @@ __global__ void k_raygen_probe(FrameParams p, long long first, long long n, floa
     uint4 st = p.rng_table[pix];
     Rng rng; rng.x = st.x; rng.y = st.y; rng.z = st.z; rng.w = st.w;
     V3 o, d;
-    init_ray(p.cam, p.width, p.height, px, py, rng, o, d);
+    init_ray(*p.cam, p.width, p.height, px, py, rng, o, d);
     p.rng_table[pix] = make_uint4(rng.x, rng.y, rng.z, rng.w);
     out3[3 * k + 0] = make_float4(__int_as_float(px), __int_as_float(py), o.x, o.y);
     out3[3 * k + 1] = make_float4(o.z, d.x, d.y, d.z);
@@ -273,13 +273,14 @@ __global__ void k_tally(FrameParams p) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     unsigned long long closest = 0, shadow = 0;
     for (int b = 0; b < p.max_depth; b++) { closest += p.counters[b].n_paths; shadow += p.counters[b].n_shadow; }
-    p.totals[0] += closest; p.totals[1] += shadow; p.totals[2] += (unsigned long long)p.width * p.height;
+    // slices of one frame tally concurrently from different streams
+    atomicAdd(&p.totals[0], closest); atomicAdd(&p.totals[1], shadow); atomicAdd(&p.totals[2], (unsigned long long)p.slice_count);
 }
 
 int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, cudaEvent_t* evs) {
     // evs (optional): one event recorded before every kernel and one after the last, for per-stage timing
     int launches = 0;
-    cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 1), st);
+    cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), st);
     if (evs) cudaEventRecord(evs[launches], st);
     k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p); launches++;
     int qi = 0;
@@ -297,6 +298,33 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
     if (evs) cudaEventRecord(evs[launches], st);
     k_tally<<<1, 32, 0, st>>>(p); launches++;
     if (evs) cudaEventRecord(evs[launches], st);
+    return launches;
+}
+
+int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceStreams& ss, bool wait_prev) {
+    int launches = 0;
+    cudaStream_t A = ss.a, B = ss.b;
+    cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), A);
+    k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, A>>>(p); launches++;
+    k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, A>>>(p, 0, 0, dims.leaf_thresh, dims.fetch_thresh); launches++;
+    // shade(0) rewrites the shadow queue and accum pixels the previous frame's last shadow kernel may still be using
+    if (wait_prev) cudaStreamWaitEvent(A, ss.ev_shadow, 0);
+    int qi = 0;
+    for (int b = 0; b < p.max_depth; b++) {
+        if (p.model == 1) k_shade<1><<<dims.shade_blocks, PT_SHADE_THREADS, 0, A>>>(p, b, qi);
+        else k_shade<0><<<dims.shade_blocks, PT_SHADE_THREADS, 0, A>>>(p, b, qi);
+        launches++;
+        cudaEventRecord(ss.ev_shade, A);
+        cudaStreamWaitEvent(B, ss.ev_shade, 0);
+        k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, B>>>(p, b, qi ^ 1, dims.leaf_thresh, dims.fetch_thresh); launches++;
+        if (b + 1 == p.max_depth) { k_tally<<<1, 32, 0, B>>>(p); launches++; }
+        cudaEventRecord(ss.ev_shadow, B);
+        qi ^= 1;
+        if (b + 1 < p.max_depth) {
+            k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, A>>>(p, b + 1, qi, dims.leaf_thresh, dims.fetch_thresh); launches++;
+            cudaStreamWaitEvent(A, ss.ev_shadow, 0);         // shade(b+1) reuses the shadow queue and reads q3 written by shadow(b)
+        }
+    }
     return launches;
 }
 

@@ -15,16 +15,17 @@ struct BounceCounters {
 
 struct FrameParams {
     SceneDev scene;
-    CameraRec cam;
+    const CameraRec* cam;    // device copy of the camera uniforms (so a captured graph sees camera updates)
     int width, height;
+    int slice_first, slice_count;   // this launch sequence owns ray indices [slice_first, slice_first + slice_count)
     int max_depth;
     int model;
     uint4* rng_table;     // per pixel
     float4* accum;        // per pixel, running sum
     PathQueue queue[2];
     ShadowQueue shadow;
-    float4* hits;         // per queue slot
-    BounceCounters* counters;   // [max_depth + 1]
+    float4* hits;         // per queue slot (queue, shadow and hit pointers are already offset to the slice's sub-range)
+    BounceCounters* counters;   // [max_depth + 2], one block per slice
     unsigned long long* totals; // [0] closest rays, [1] shadow rays, [2] paths
 };
 
@@ -39,6 +40,13 @@ void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsign
 // one frame = raygen + max_depth x (extend, shade, shadow) + tally; returns number of kernels launched
 // kernel k of a frame: 0 = raygen, 1+3b = extend, 2+3b = shade, 3+3b = shadow (bounce b), last = tally
 int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, cudaEvent_t* evs);
+
+// The same frame as a dependency graph on two streams: shadow(b) (NEE visibility of bounce b) and extend(b+1)
+// (closest hit of the next bounce) only depend on shade(b), so they run concurrently, shadow on `b`, everything
+// else on `a`. Safe to capture into a CUDA graph (cross-stream edges are events). `wait_prev`: the previous frame
+// of this slice was enqueued on the same streams without an intervening join (its last shadow may still run).
+struct SliceStreams { cudaStream_t a, b; cudaEvent_t ev_shade, ev_shadow; };
+int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceStreams& ss, bool wait_prev);
 
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);
 void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st);

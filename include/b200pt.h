@@ -49,7 +49,10 @@ typedef struct pt_config {
     int32_t microfacet_model;     /* PT_MICROFACET_* */
     int32_t device;               /* CUDA device ordinal */
     int32_t bvh_layout;           /* PT_BVH_* used by pt_render_frames / pt_trace_* */
-    int32_t reserved[6];
+    int32_t n_slices;             /* a frame is rendered as this many pixel-disjoint slices on concurrent streams so that
+                                     one slice's kernels fill the drain phase of another's; 0 = default (3). Results do
+                                     not depend on it (every pixel keeps its own RNG sequence). */
+    int32_t reserved[5];
 } pt_config;
 
 /* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
@@ -151,6 +154,11 @@ void* pt_accum_device_ptr(pt_context* ctx);                        /* for NCCL r
 int pt_set_accum_device_ptr(pt_context* ctx, void* dev_rgba);      /* render into caller-owned device memory */
 /* Renderer::Present (Present.frag:13-37): /numSamples, Uncharted-2, gamma 2.2 -> RGB float and/or 8-bit. */
 int pt_resolve(pt_context* ctx, uint32_t num_samples, float* rgb_f32_or_null, uint8_t* rgb_u8_or_null);
+/* Present without the stall of a swap: the resolve kernel is queued behind the frames rendered so far and its 8-bit image
+ * is copied to host_rgb_u8 (width*height*3 bytes, pinned memory for a truly asynchronous copy) on a separate copy stream,
+ * so the next RenderFrame overlaps the transfer. The image is complete after pt_synchronize. Device-side the target is
+ * double-buffered: at most two presents are in flight. */
+int pt_present_async(pt_context* ctx, uint32_t num_samples, uint8_t* host_rgb_u8);
 int pt_save_screenshot(pt_context* ctx, const char* path);         /* Renderer::SaveScreenshot (Renderer.cpp:697-705); .ppm/.pfm */
 
 /* ---- fixed ray batches (parity + microbenchmark entry points) ----
