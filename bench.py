@@ -273,6 +273,9 @@ class Dist:
             self.dist.destroy_process_group()
 
 
+LAYOUTS = {"reference": 0, "wide": 1, "wide4": 2}
+
+
 def run_pathtrace(args, name, wl):
     d = Dist()
     torch, dist, world, rank, local = d.torch, d.dist, d.world, d.rank, d.local
@@ -281,7 +284,7 @@ def run_pathtrace(args, name, wl):
     scene = build_scene(wl)
     t0 = time.perf_counter()
     r = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
-                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh="build")
+                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh="build", bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     cam = make_camera(scene, W, H)
     # accumulation buffer owned by torch so NCCL can reduce it in place
@@ -350,7 +353,7 @@ def run_pathtrace(args, name, wl):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
                        "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
-                       "bvh": "own SBVH builder, reference layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
+                       "bvh": f"own SBVH builder, {args.bvh} layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
                        "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
                        "parallelism": f"samples split over {world} GPU(s), 1 NCCL reduce of the accumulation buffer per {args.steps}-frame batch",
@@ -398,7 +401,7 @@ def run_micro(args, name, wl):
     n = wl["n_rays"]
     scene, closest, anyr = micro_scene_and_rays(n, 0xB200 + 7 * rank)
     t0 = time.perf_counter()
-    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh="build")
+    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh="build", bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     d_closest = torch.from_numpy(closest).cuda()
     d_any = torch.from_numpy(anyr).cuda()
@@ -449,7 +452,7 @@ def run_micro(args, name, wl):
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "rays_per_step": 2 * n,
-                       "bvh": "own SBVH builder, reference layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
+                       "bvh": f"own SBVH builder, {args.bvh} layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "bvh_nodes": int(r.bvh_stats.n_nodes), "bvh_refs": int(r.bvh_stats.n_refs),
                        "l2": "ray batches (2 x 512 MB) and tree + leaf stream (~1.2 GB) exceed the 126 MB L2",
                        "parallelism": f"{world} independent replica(s), each with its own 16M-ray batch; no collective", "init_s": init_s},
@@ -494,7 +497,7 @@ def run_primary(args, name, wl):
     for _ in range(3):
         _, _, st = build_bvh_host(scene.tris)
         builds.append(st["build_ms"])
-    r = Renderer().Initialize(W, H, scene, max_depth=1, device=local, seed=0xB200 + rank, bvh="build")
+    r = Renderer().Initialize(W, H, scene, max_depth=1, device=local, seed=0xB200 + rank, bvh="build", bvh_layout=LAYOUTS[args.bvh])
     cam = make_camera(scene, W, H)
     r.lib.pt_set_camera(r.ctx, cam.plane)
     n = W * H
@@ -575,6 +578,8 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--bvh", default="reference", choices=["reference", "wide", "wide4"],
+                    help="device BVH layout: the reference's binary fp32 tree (bit-exact) or the compressed 8-/4-wide collapse of it")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.steps is None:

@@ -14,7 +14,7 @@ LIB_PATH = os.path.join(_HERE, "libb200pt.so")
 
 PT_OK = 0
 PT_MICROFACET_GGX, PT_MICROFACET_BECKMANN = 0, 1
-PT_BVH_REFERENCE, PT_BVH_WIDE = 0, 1
+PT_BVH_REFERENCE, PT_BVH_WIDE, PT_BVH_WIDE4 = 0, 1, 2
 REFERENCE_MAX_DEPTH = 66      # `i > 64`, Iterative.comp:293
 
 
@@ -65,6 +65,9 @@ SYMBOLS = [
     ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_bvh_build_host", C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(_F), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32), C.POINTER(pt_bvh_stats)]),
     ("pt_free", None, [_P]),
+    ("pt_bvh_collapse_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, C.c_int32, C.POINTER(C.POINTER(C.c_uint8)),
+                                       C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)),
+                                       C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     ("pt_get_bvh", C.c_int, [_P, _P, C.POINTER(C.c_int32), _P, C.POINTER(C.c_int32)]),
     ("pt_assemble_triangles", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_build_light_table", C.c_int, [_P, C.c_int64, _P, C.c_int32, _P, C.c_int32, _F]),
@@ -172,6 +175,23 @@ def build_bvh_host(tris_pre, n_threads=0):
     return nodes, refs, {k: getattr(st, k) for k, _ in pt_bvh_stats._fields_}
 
 
+def collapse_bvh_host(nodes, refs, tris_pre, width=8):
+    """Reference-form tree -> compressed wide layout (host only). Returns (node_bytes (n, node_size) uint8, tri_ids, depth)."""
+    lib = load_library()
+    nodes = np.ascontiguousarray(nodes, dtype=np.float32); refs = np.ascontiguousarray(refs, dtype=np.int32)
+    t = np.ascontiguousarray(tris_pre, dtype=np.float32)
+    nb, ids = C.POINTER(C.c_uint8)(), C.POINTER(C.c_int32)()
+    n_wide, n_ids, size, depth = C.c_int64(), C.c_int64(), C.c_int32(), C.c_int32()
+    rc = lib.pt_bvh_collapse_host(_ptr(nodes), nodes.shape[0], _ptr(refs), refs.shape[0], _ptr(t), t.shape[0], width,
+                                  C.byref(nb), C.byref(n_wide), C.byref(size), C.byref(ids), C.byref(n_ids), C.byref(depth))
+    if rc != PT_OK:
+        raise PtError(rc, "pt_bvh_collapse_host")
+    node_bytes = np.ctypeslib.as_array(nb, shape=(n_wide.value, size.value)).copy()
+    tri_ids = np.ctypeslib.as_array(ids, shape=(max(n_ids.value, 1),))[:n_ids.value].copy()
+    lib.pt_free(nb); lib.pt_free(ids)
+    return node_bytes, tri_ids, depth.value
+
+
 def presubtract_edges(tris_abs):
     """Scene.cpp:334-337 (returns a copy)."""
     t = np.ascontiguousarray(tris_abs, dtype=np.float32).copy()
@@ -239,9 +259,9 @@ class Renderer:
 
     # -- Renderer::Initialize, Renderer.cpp:448-636
     def Initialize(self, width, height, scene, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=PT_MICROFACET_GGX,
-                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0):
+                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0, bvh_layout=PT_BVH_REFERENCE):
         cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
-                        device=device, bvh_layout=PT_BVH_REFERENCE, n_slices=n_slices)
+                        device=device, bvh_layout=bvh_layout, n_slices=n_slices)
         ctx = C.c_void_p()
         _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
         self.ctx = ctx

@@ -77,6 +77,10 @@ struct pt_context {
     DevBuf<float4> d_tris;
     DevBuf<BvhPair> d_pairs;
     DevBuf<LeafTri> d_leaf;
+    DevBuf<unsigned char> d_wide;          // PT_BVH_WIDE / PT_BVH_WIDE4 node bytes
+    DevBuf<LeafTri> d_wide_tris;
+    WideBvh h_wide;
+    float wide_ms = 0.0f;
     DevBuf<MaterialRec> d_mats;
     DevBuf<TextureRec> d_texrec;
     std::vector<float4*> d_texels;
@@ -117,6 +121,7 @@ static void invalidate_graphs(pt_context* c) {
 static SceneDev scene_dev(pt_context* c) {
     SceneDev s{};
     s.pairs = c->d_pairs.p; s.leaf_tris = c->d_leaf.p; s.n_leaf_tris = c->n_leaf;
+    s.wide_nodes = c->d_wide.p; s.wide_tris = c->d_wide_tris.p;
     s.tris = c->d_tris.p; s.materials = c->d_mats.p; s.textures = c->d_texrec.p; s.n_textures = c->n_textures;
     s.lights = c->d_lights.p; s.n_lights = c->n_lights; s.total_light_area = c->total_light_area;
     s.env[0] = c->env[0]; s.env[1] = c->env[1]; s.env[2] = c->env[2];
@@ -137,8 +142,8 @@ int pt_create(const pt_config* cfg, pt_context** out) {
         return fail(PT_ERR_INVALID, "pt_create: max_depth must be in [1, 66] (got %d)", cfg->max_depth);
     if (cfg->microfacet_model != PT_MICROFACET_GGX && cfg->microfacet_model != PT_MICROFACET_BECKMANN)
         return fail(PT_ERR_INVALID, "pt_create: unknown microfacet model %d", cfg->microfacet_model);
-    if (cfg->bvh_layout != PT_BVH_REFERENCE)
-        return fail(PT_ERR_UNSUPPORTED, "pt_create: bvh_layout %d not available in this build", cfg->bvh_layout);
+    if (cfg->bvh_layout != PT_BVH_REFERENCE && cfg->bvh_layout != PT_BVH_WIDE && cfg->bvh_layout != PT_BVH_WIDE4)
+        return fail(PT_ERR_INVALID, "pt_create: unknown bvh_layout %d", cfg->bvh_layout);
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
     if (e != cudaSuccess || ndev == 0)
@@ -155,7 +160,7 @@ int pt_create(const pt_config* cfg, pt_context** out) {
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&c->ev0));
     CK(cudaEventCreate(&c->ev1));
-    query_launch_dims(cfg->device, &c->dims);
+    query_launch_dims(cfg->device, cfg->bvh_layout == PT_BVH_WIDE ? 8 : cfg->bvh_layout == PT_BVH_WIDE4 ? 4 : 0, &c->dims);
     const size_t npx = (size_t)cfg->width * cfg->height;
     {
         int want = cfg->n_slices > 0 ? cfg->n_slices : 3;
@@ -206,6 +211,7 @@ void pt_destroy(pt_context* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
+    c->d_wide.release(); c->d_wide_tris.release();
     c->d_tris.release(); c->d_pairs.release(); c->d_leaf.release(); c->d_mats.release(); c->d_texrec.release();
     for (float4* t : c->d_texels) cudaFree(t);
     c->d_lights.release(); c->d_rng.release(); c->d_accum_own.release();
@@ -232,6 +238,33 @@ void pt_destroy(pt_context* c) {
     delete c;
 }
 
+// PT_BVH_WIDE: collapse the reference-form tree into 8-wide quantised nodes + their own leaf triangle stream
+static int upload_wide(pt_context* c) {
+    std::string msg;
+    auto t0 = std::chrono::steady_clock::now();
+    if (!build_wide_bvh(c->h_bvh, c->h_tris.data(), (int64_t)(c->h_tris.size() / 20), c->dims.wide, c->h_wide, msg))
+        return fail(PT_ERR_LIMIT, "wide BVH: %s", msg.c_str());
+    c->wide_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    static_assert(sizeof(WideNodeHost) == sizeof(WideNode), "wide node layout");
+    const size_t nb = c->h_wide.bytes.size(), nt = c->h_wide.tri_ids.size();
+    std::vector<LeafTri> ls(nt ? nt : 1);
+    for (size_t i = 0; i < nt; i++) {
+        int32_t id = c->h_wide.tri_ids[i];
+        const float* t = c->h_tris.data() + 20 * (size_t)id;
+        float idf; memcpy(&idf, &id, 4);
+        ls[i].r[0] = make_float4(t[0], t[1], t[2], t[3]);
+        ls[i].r[1] = make_float4(t[4], t[5], t[6], t[7]);
+        ls[i].r[2] = make_float4(t[8], idf, 0.0f, 0.0f);
+        ls[i].r[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+    CK(c->d_wide.alloc(nb));
+    CK(c->d_wide_tris.alloc(ls.size()));
+    CK(cudaMemcpyAsync(c->d_wide.p, c->h_wide.bytes.data(), nb, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->d_wide_tris.p, ls.data(), ls.size() * sizeof(LeafTri), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return PT_OK;
+}
+
 // (re)build the leaf triangle stream from host triangles + reference list
 static int upload_leaf_stream(pt_context* c) {
     if (c->h_tris.empty() || c->h_bvh.refs.empty()) return PT_OK;
@@ -255,6 +288,7 @@ static int upload_leaf_stream(pt_context* c) {
     CK(cudaMemcpyAsync(c->d_leaf.p, ls.data(), nr * sizeof(LeafTri), cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     c->n_leaf = (int)nr;
+    if (c->cfg.bvh_layout != PT_BVH_REFERENCE) return upload_wide(c);
     return PT_OK;
 }
 

@@ -11,6 +11,7 @@
 // warp ballots + one atomic per warp.
 #include "pt_kernels.h"
 #include "pt_trace.cuh"
+#include "pt_trace_wide.cuh"
 #include "pt_shade.cuh"
 #include <cstdlib>
 
@@ -35,23 +36,27 @@ struct BatchIO {
     }
 };
 
-template <bool ANY>
+template <bool ANY, class TR>
 __global__ void __launch_bounds__(PT_TRACE_THREADS)
 k_trace_batch(SceneDev s, BatchIO io, int leaf_thresh, int fetch_thresh) {
-    trace_persistent<ANY>(s, io, leaf_thresh, fetch_thresh);
+    trace_persistent<ANY, TR>(s, io, leaf_thresh, fetch_thresh);
 }
 
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
                           const LaunchDims& dims, cudaStream_t st) {
     cudaMemsetAsync(cursor, 0, sizeof(int), st);
     BatchIO io{rays, hits, nullptr, (int)n, cursor};
-    k_trace_batch<false><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    if (dims.wide == 8) k_trace_batch<false, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.wide == 4) k_trace_batch<false, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else k_trace_batch<false, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
                       const LaunchDims& dims, cudaStream_t st) {
     cudaMemsetAsync(cursor, 0, sizeof(int), st);
     BatchIO io{rays, nullptr, flags, (int)n, cursor};
-    k_trace_batch<true><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    if (dims.wide == 8) k_trace_batch<true, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.wide == 4) k_trace_batch<true, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else k_trace_batch<true, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 // ------------------------------------------------------------------ ray generation
@@ -106,10 +111,16 @@ struct ExtendIO {
     }
 };
 
+template <class TR>
 __global__ void __launch_bounds__(PT_TRACE_THREADS)
 k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
     ExtendIO io{p.queue[qi], p.hits, p.counters + bounce};
-    trace_persistent<false>(p.scene, io, leaf_thresh, fetch_thresh);
+    trace_persistent<false, TR>(p.scene, io, leaf_thresh, fetch_thresh);
+}
+static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
+    if (dims.wide == 8) k_extend<WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.wide == 4) k_extend<WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+    else k_extend<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 // ------------------------------------------------------------------ shade
@@ -263,10 +274,16 @@ struct ShadowIO {
     }
 };
 
+template <class TR>
 __global__ void __launch_bounds__(PT_TRACE_THREADS)
 k_shadow(FrameParams p, int bounce, int qi_next, int leaf_thresh, int fetch_thresh) {
     ShadowIO io{p.shadow, p.queue[qi_next], p.accum, p.counters + bounce};
-    trace_persistent<true>(p.scene, io, leaf_thresh, fetch_thresh);
+    trace_persistent<true, TR>(p.scene, io, leaf_thresh, fetch_thresh);
+}
+static void launch_shadow(const FrameParams& p, int b, int qi_next, const LaunchDims& dims, cudaStream_t st) {
+    if (dims.wide == 8) k_shadow<WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.wide == 4) k_shadow<WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+    else k_shadow<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 __global__ void k_tally(FrameParams p) {
@@ -286,13 +303,13 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
     int qi = 0;
     for (int b = 0; b < p.max_depth; b++) {
         if (evs) cudaEventRecord(evs[launches], st);
-        k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh); launches++;
+        launch_extend(p, b, qi, dims, st); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
         if (p.model == 1) k_shade<1><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
         else k_shade<0><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
         launches++;
         if (evs) cudaEventRecord(evs[launches], st);
-        k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi ^ 1, dims.leaf_thresh, dims.fetch_thresh); launches++;
+        launch_shadow(p, b, qi ^ 1, dims, st); launches++;
         qi ^= 1;
     }
     if (evs) cudaEventRecord(evs[launches], st);
@@ -306,7 +323,7 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
     cudaStream_t A = ss.a, B = ss.b;
     cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), A);
     k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, A>>>(p); launches++;
-    k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, A>>>(p, 0, 0, dims.leaf_thresh, dims.fetch_thresh); launches++;
+    launch_extend(p, 0, 0, dims, A); launches++;
     // shade(0) rewrites the shadow queue and accum pixels the previous frame's last shadow kernel may still be using
     if (wait_prev) cudaStreamWaitEvent(A, ss.ev_shadow, 0);
     int qi = 0;
@@ -316,12 +333,12 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
         launches++;
         cudaEventRecord(ss.ev_shade, A);
         cudaStreamWaitEvent(B, ss.ev_shade, 0);
-        k_shadow<<<dims.extend_blocks, PT_TRACE_THREADS, 0, B>>>(p, b, qi ^ 1, dims.leaf_thresh, dims.fetch_thresh); launches++;
+        launch_shadow(p, b, qi ^ 1, dims, B); launches++;
         if (b + 1 == p.max_depth) { k_tally<<<1, 32, 0, B>>>(p); launches++; }
         cudaEventRecord(ss.ev_shadow, B);
         qi ^= 1;
         if (b + 1 < p.max_depth) {
-            k_extend<<<dims.extend_blocks, PT_TRACE_THREADS, 0, A>>>(p, b + 1, qi, dims.leaf_thresh, dims.fetch_thresh); launches++;
+            launch_extend(p, b + 1, qi, dims, A); launches++;
             cudaStreamWaitEvent(A, ss.ev_shadow, 0);         // shade(b+1) reuses the shadow queue and reads q3 written by shadow(b)
         }
     }
@@ -382,12 +399,21 @@ void launch_resolve(const float4* accum, long long n, unsigned num_samples, floa
 }
 
 // occupancy-derived persistent grid sizes
-void query_launch_dims(int device, LaunchDims* out) {
+void query_launch_dims(int device, int wide, LaunchDims* out) {
     cudaDeviceProp prop;
     cudaGetDeviceProperties(&prop, device);
     int per_sm_ext = 1, per_sm_shadow = 1, per_sm_shade = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend, PT_TRACE_THREADS, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow, PT_TRACE_THREADS, 0);
+    out->wide = wide;
+    if (wide == 8) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<WideTraverser<8>>, PT_TRACE_THREADS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<WideTraverser<8>>, PT_TRACE_THREADS, 0);
+    } else if (wide == 4) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<WideTraverser<4>>, PT_TRACE_THREADS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<WideTraverser<4>>, PT_TRACE_THREADS, 0);
+    } else {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<Traverser>, PT_TRACE_THREADS, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<Traverser>, PT_TRACE_THREADS, 0);
+    }
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0>, PT_SHADE_THREADS, 0);
     int per = per_sm_ext < per_sm_shadow ? per_sm_ext : per_sm_shadow;
     if (per < 1) per = 1;

@@ -29,7 +29,7 @@ struct FrameParams {
     unsigned long long* totals; // [0] closest rays, [1] shadow rays, [2] paths
 };
 
-struct LaunchDims { int sm_count; int extend_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; };
+struct LaunchDims { int sm_count; int extend_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; int wide; };
 
 // fixed ray batches (AoS rays: n x {o.xyz, -, d.xyz, tmax})
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
@@ -50,7 +50,7 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
 
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);
 void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st);
-void query_launch_dims(int device, LaunchDims* out);
+void query_launch_dims(int device, int wide, LaunchDims* out);
 void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
                     cudaStream_t st);
 

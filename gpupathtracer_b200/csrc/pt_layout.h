@@ -29,6 +29,17 @@ struct BvhPair { float4 q[4]; };
 // is copied, not recomputed.
 struct LeafTri { float4 r[4]; };
 
+// ---- BVH, PT_BVH_WIDE layout ----------------------------------------------------------------------
+// 8-wide node, child boxes quantised to 8 bits per plane on a per-node power-of-two grid; 96 B, 32-B aligned =
+// 3 x 256-bit loads (an 80-B record would need 5 x 128-bit loads: the traversal kernels are bound by L1 tag
+// lookups per lane, not by bytes). Field-for-field WideNodeHost (pt_host.h):
+//   w0 = {p.x, p.y, p.z, ex|ey<<8|ez<<16|imask<<24, child_base, tri_base, meta[0..3], meta[4..7]}
+//   w1 = {qlo_x[0..3], qlo_x[4..7], qlo_y.., qlo_y.., qlo_z.., qlo_z.., qhi_x.., qhi_x..}
+//   w2 = {qhi_y.., qhi_y.., qhi_z.., qhi_z.., pad x 4}
+// Leaves (1-3 triangles per slot, at most 24 per node) index a second LeafTri stream in node order.
+// PT_BVH_WIDE4: the same scheme with 4 children in 64 B = 2 x 256-bit loads (WideNode4Host).
+struct WideNode { uint4 w[6]; };
+
 // ---- shading tables ------------------------------------------------------------------------------
 // Full reference triangle (5 x vec4, Scene.cpp:339-347 upload) is kept for shading: uv, normal, matId.
 struct MaterialRec { float4 albedo_tex, emission_flag, props_tex; };   // == pt_material
@@ -59,6 +70,8 @@ struct SceneDev {
     const BvhPair* pairs;
     const LeafTri* leaf_tris;
     int n_leaf_tris;
+    const void* wide_nodes;      // PT_BVH_WIDE (96-B nodes) / PT_BVH_WIDE4 (64-B nodes)
+    const LeafTri* wide_tris;
     const float4* tris;          // n_tris x 5
     const MaterialRec* materials;
     const TextureRec* textures;

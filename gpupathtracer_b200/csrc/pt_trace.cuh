@@ -61,6 +61,8 @@ __device__ __forceinline__ bool tri_test(const LeafTri* __restrict__ rec, V3 o, 
 // Per-lane traversal state machine. `current` >= 0: pair record to test next (inner step);
 // `current` < 0: ~current = next record of the leaf triangle stream to test (leaf step).
 struct Traverser {
+    typedef int StackEntry;
+    static const int kStack = PT_STACK_SIZE;
     V3 o, d, inv, oinv;
     HitRec h;
     int current, sp;
@@ -75,6 +77,8 @@ struct Traverser {
         sp = 0;
         result = false;
     }
+    __device__ __forceinline__ void idle() { current = 0; sp = 0; }
+    __device__ __forceinline__ bool at_leaf() const { return current < 0; }
     // returns true when the ray is finished
     __device__ __forceinline__ bool pop(const int* stack) {
         if (sp == 0) return true;
@@ -119,18 +123,18 @@ struct Traverser {
 //   int  count() const;  int* cursor() const;
 //   void load(int i, V3& o, V3& d, float& tmax) const;
 //   void store(int i, const HitRec& h, bool result) const;
-template <bool ANY, class IO>
+template <bool ANY, class TR, class IO>
 __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io, int leaf_thresh, int fetch_thresh) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int n = io.count();
     int* cursor = io.cursor();
-    Traverser tr;
-    int stack[PT_STACK_SIZE];   // per-lane traversal stack (local memory, L1-resident)
+    TR tr;
+    typename TR::StackEntry stack[TR::kStack];   // per-lane traversal stack (local memory, L1-resident)
     bool active = false, exhausted = false;
     int ridx = -1;
-    tr.current = 0; tr.sp = 0;
+    tr.idle();
     while (true) {
         // ---- refill idle lanes
         unsigned m_idle = __ballot_sync(FULL, !active);
@@ -152,7 +156,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io
             if (base + cnt >= n) exhausted = true;
         }
         // ---- vote on the phase
-        bool at_leaf = active && tr.current < 0;
+        bool at_leaf = active && tr.at_leaf();
         unsigned m_leaf = __ballot_sync(FULL, at_leaf);
         unsigned m_active = __ballot_sync(FULL, active);
         if (m_active == 0) { if (exhausted) break; else continue; }

@@ -40,8 +40,11 @@ typedef struct pt_context pt_context;
 enum { PT_MICROFACET_GGX = 0, PT_MICROFACET_BECKMANN = 1 };
 
 /* traversal layout: PT_BVH_REFERENCE keeps the reference tree's topology and fp32 boxes (results are
- * bit-identical to IfIfClosestHit/IfIfAnyHit); PT_BVH_WIDE is the compressed 8-wide layout. */
-enum { PT_BVH_REFERENCE = 0, PT_BVH_WIDE = 1 };
+ * bit-identical to IfIfClosestHit/IfIfAnyHit). PT_BVH_WIDE / PT_BVH_WIDE4 collapse that tree into 8- / 4-wide nodes
+ * with 8-bit quantised child boxes (96 B / 64 B per node): same triangles, same triangle test, conservative boxes --
+ * (t,u,v) are bit-identical whenever the same triangle is reported; the reported triangle differs for the ~1e-6 of
+ * rays whose hit the reference's fp32 slab test culls or that tie in t. Faster once the tree outgrows L2. */
+enum { PT_BVH_REFERENCE = 0, PT_BVH_WIDE = 1, PT_BVH_WIDE4 = 2 };
 
 typedef struct pt_config {
     int32_t width, height;        /* multiples of 8 (Iterative.comp:163-172); Program.cpp:22-23 hard-codes 1280x720 */
@@ -118,6 +121,14 @@ int pt_build_bvh(pt_context* ctx, pt_bvh_stats* stats);
 int pt_bvh_build_host(const float* tris, int64_t n, int32_t n_threads, float** nodes, int32_t* n_nodes,
                       int32_t** refs, int32_t* n_refs, pt_bvh_stats* stats);
 void pt_free(void* p);
+/* Collapse a reference-form tree into the compressed wide layout used by PT_BVH_WIDE (width 8, 96-B nodes) or
+ * PT_BVH_WIDE4 (width 4, 64-B nodes) without a device: node_bytes = n_wide x node_size bytes exactly as uploaded
+ * (layout: gpupathtracer_b200/csrc/pt_host.h WideNodeHost / WideNode4Host), tri_ids = triangle index per entry of the
+ * wide leaf stream. The reference has no counterpart (its device tree is the binary NewLayout array, BVH.cpp:2261-2277);
+ * north_star item (1) asks for it. Arrays are malloc()ed, release with pt_free. */
+int pt_bvh_collapse_host(const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs, const float* tris,
+                         int64_t n_tris, int32_t width, uint8_t** node_bytes, int64_t* n_wide, int32_t* node_size,
+                         int32_t** tri_ids, int64_t* n_tri_ids, int32_t* depth);
 /* Read back the tree in the reference's serialised form (what nodesVec/referenceVec hold, BVH.cpp:2291-2292);
  * call with NULL arrays to query sizes. */
 int pt_get_bvh(pt_context* ctx, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs);
