@@ -49,6 +49,11 @@ class pt_bvh_stats(C.Structure):
                 ("sah_cost", C.c_float), ("build_ms", C.c_float)]
 
 
+class pt_scene_txt(C.Structure):
+    _fields_ = [("scene_path", C.c_char * 1024), ("environment", C.c_char * 1024),
+                ("camera_position", C.c_float * 3), ("camera_rotation", C.c_float * 3)]
+
+
 # every symbol include/b200pt.h declares: (name, restype, argtypes)
 _P = C.c_void_p
 _F = C.POINTER(C.c_float)
@@ -68,6 +73,20 @@ SYMBOLS = [
     ("pt_bvh_collapse_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, C.c_int32, C.POINTER(C.POINTER(C.c_uint8)),
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)),
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
+    ("pt_scene_file_load_obj", C.c_int, [C.c_char_p, C.POINTER(_P)]),
+    ("pt_scene_file_free", None, [_P]),
+    ("pt_scene_file_num_triangles", C.c_int64, [_P]),
+    ("pt_scene_file_vertices", _F, [_P]),
+    ("pt_scene_file_material_ids", C.POINTER(C.c_uint32), [_P]),
+    ("pt_scene_file_num_materials", C.c_int32, [_P]),
+    ("pt_scene_file_materials", _F, [_P]),
+    ("pt_scene_file_texture_path", C.c_char_p, [_P, C.c_int32]),
+    ("pt_scene_file_num_shapes", C.c_int32, [_P]),
+    ("pt_scene_file_warnings", C.c_char_p, [_P]),
+    ("pt_image_load", C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(_F)]),
+    ("pt_scene_txt_read", C.c_int, [C.c_char_p, _P]),
+    ("pt_parse_environment", C.c_int, [C.c_char_p, _F]),
+    ("pt_load_scene", C.c_int, [_P, C.c_char_p, C.c_char_p, C.POINTER(pt_bvh_stats)]),
     ("pt_get_bvh", C.c_int, [_P, _P, C.POINTER(C.c_int32), _P, C.POINTER(C.c_int32)]),
     ("pt_assemble_triangles", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_build_light_table", C.c_int, [_P, C.c_int64, _P, C.c_int32, _P, C.c_int32, _F]),
@@ -192,6 +211,67 @@ def collapse_bvh_host(nodes, refs, tris_pre, width=8):
     return node_bytes, tri_ids, depth.value
 
 
+def load_obj(path):
+    """LoadOBJ (Scene.cpp:120-231) through libb200pt's own parser -> dict(verts (n,3,8), mat_ids (n,), materials (m,12),
+    texture_paths [m], n_shapes, warnings)."""
+    lib = load_library()
+    h = C.c_void_p()
+    _check(lib.pt_scene_file_load_obj(path.encode(), C.byref(h)))
+    try:
+        n = lib.pt_scene_file_num_triangles(h)
+        m = lib.pt_scene_file_num_materials(h)
+        verts = np.ctypeslib.as_array(lib.pt_scene_file_vertices(h), shape=(n, 3, 8)).copy()
+        mat_ids = np.ctypeslib.as_array(lib.pt_scene_file_material_ids(h), shape=(n,)).copy()
+        mats = np.ctypeslib.as_array(lib.pt_scene_file_materials(h), shape=(m, 12)).copy()
+        tex = [lib.pt_scene_file_texture_path(h, i).decode() for i in range(m)]
+        return dict(verts=verts, mat_ids=mat_ids, materials=mats, texture_paths=tex,
+                    n_shapes=int(lib.pt_scene_file_num_shapes(h)), warnings=lib.pt_scene_file_warnings(h).decode())
+    finally:
+        lib.pt_scene_file_free(h)
+
+
+def load_image(path):
+    """map_Kd decoder -> (h, w, 4) float32."""
+    lib = load_library()
+    w, h, p = C.c_int32(), C.c_int32(), _F()
+    _check(lib.pt_image_load(path.encode(), C.byref(w), C.byref(h), C.byref(p)))
+    out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
+    lib.pt_free(p)
+    return out
+
+
+def scene_data_from_obj(path, camera=None, env_color=(1.0, 1.0, 1.0)):
+    """The file the reference would load (Scene::LoadScene) as a `scenes.SceneData`, textures decoded and bound the way
+    pt_load_scene does it -- so the oracle and the per-array upload path can be fed from an .obj too."""
+    from .scenes import SceneData
+    d = load_obj(path)
+    mats = d["materials"].copy()
+    textures = []
+    for m, tp in enumerate(d["texture_paths"]):
+        if not tp:
+            continue
+        try:
+            img = load_image(tp)
+        except PtError:
+            continue
+        textures.append(img)
+        mats.view(np.int32)[m, 3] = len(textures) - 1
+    return SceneData(os.path.basename(path), d["verts"], d["mat_ids"], mats, tuple(env_color), camera or {}, textures)
+
+
+def read_scene_txt(path):
+    """scene.txt (Program.cpp:70-84) -> (scene_path, environment, camera position, camera rotation)."""
+    st = pt_scene_txt()
+    _check(load_library().pt_scene_txt_read(path.encode(), C.byref(st)))
+    return st.scene_path.decode(), st.environment.decode(), tuple(st.camera_position), tuple(st.camera_rotation)
+
+
+def parse_environment(args):
+    rgb = (C.c_float * 3)()
+    _check(load_library().pt_parse_environment(args.encode(), rgb))
+    return tuple(rgb)
+
+
 def presubtract_edges(tris_abs):
     """Scene.cpp:334-337 (returns a copy)."""
     t = np.ascontiguousarray(tris_abs, dtype=np.float32).copy()
@@ -288,6 +368,21 @@ class Renderer:
             self.SetRNG(rng_state)
         elif seed is not None:
             _check(self.lib.pt_seed_rng(ctx, seed))
+        return self
+
+    def InitializeFromFile(self, width, height, scene_path, env="GENERATE COLOR WHITE", max_depth=REFERENCE_MAX_DEPTH,
+                           microfacet_model=PT_MICROFACET_GGX, device=0, seed=1, bvh_layout=PT_BVH_REFERENCE, n_slices=0):
+        """Renderer::Initialize(Window*, scenePath, env) (Renderer.cpp:448-636) with the window reduced to its size."""
+        cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
+                        device=device, bvh_layout=bvh_layout, n_slices=n_slices)
+        ctx = C.c_void_p()
+        _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
+        self.ctx = ctx
+        self.width, self.height = width, height
+        stats = pt_bvh_stats()
+        _check(self.lib.pt_load_scene(ctx, scene_path.encode(), env.encode(), C.byref(stats)))
+        self.bvh_stats = stats
+        _check(self.lib.pt_seed_rng(ctx, seed))
         return self
 
     def GetBVH(self):

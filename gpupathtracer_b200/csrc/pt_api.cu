@@ -15,6 +15,7 @@
 using namespace pt;
 
 static thread_local std::string g_err;
+namespace pt { void set_last_error(const char* msg) { g_err = msg ? msg : ""; } }
 
 static int fail(int code, const char* fmt, ...) {
     char buf[1024];
@@ -411,6 +412,49 @@ int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
         stats->build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
     }
     return PT_OK;
+}
+
+// Renderer::Initialize's scene half (Renderer.cpp:519-523 -> Scene::LoadScene, Scene.cpp:233-357) from files
+int pt_load_scene(pt_context* c, const char* scene_path, const char* environment, pt_bvh_stats* stats) {
+    if (!c || !scene_path) return fail(PT_ERR_INVALID, "pt_load_scene: bad argument");
+    std::string path(scene_path);
+    size_t dot = path.find_last_of('.');
+    if (dot == std::string::npos || path.substr(dot + 1) != "obj")
+        return fail(PT_ERR_UNSUPPORTED, "Unsupported file type: %s (the reference's only live loader is .obj, Scene.cpp:248-259)", scene_path);
+    float env[3] = {1.0f, 1.0f, 1.0f};
+    if (environment) { int rc = pt_parse_environment(environment, env); if (rc != PT_OK) return rc; }
+    pt_scene_file* sf = nullptr;
+    int rc = pt_scene_file_load_obj(scene_path, &sf);
+    if (rc != PT_OK) return rc;
+    const int64_t n = pt_scene_file_num_triangles(sf);
+    std::vector<pt_material> mats(pt_scene_file_materials(sf), pt_scene_file_materials(sf) + pt_scene_file_num_materials(sf));
+    // map_Kd images -> RGBA32F textures; a file that cannot be decoded leaves the material on its Kd colour
+    std::vector<std::vector<float>> texels; std::vector<pt_texture> tex;
+    for (size_t m = 0; m < mats.size(); m++) {
+        std::string tp = pt_scene_file_texture_path(sf, (int32_t)m);
+        if (tp.empty()) continue;
+        int w = 0, h = 0; std::vector<float> px;
+        if (!load_image_rgba32f(tp, w, h, px)) continue;
+        texels.push_back(std::move(px));
+        mats[m].albedo_tex = (int32_t)texels.size() - 1;
+        pt_texture t; t.width = w; t.height = h; t.rgba = nullptr; tex.push_back(t);
+    }
+    for (size_t i = 0; i < tex.size(); i++) tex[i].rgba = texels[i].data();
+    std::vector<float> tris((size_t)n * 20);
+    rc = pt_assemble_triangles(pt_scene_file_vertices(sf), pt_scene_file_material_ids(sf), n, tris.data());
+    pt_scene_file_free(sf);
+    if (rc != PT_OK) return fail(rc, "pt_load_scene: triangle assembly failed");
+    float total = 0.0f;
+    int nl = pt_build_light_table(tris.data(), n, mats.data(), (int32_t)mats.size(), nullptr, 0, &total);
+    if (nl <= 0) return fail(PT_ERR_INVALID, "pt_load_scene: %s has no emissive triangle (a material needs Ke > 0; the reference samples garbage then, Iterative.comp:42-61)", scene_path);
+    std::vector<pt_light> lights(nl);
+    pt_build_light_table(tris.data(), n, mats.data(), (int32_t)mats.size(), lights.data(), nl, &total);
+    pt_presubtract_edges(tris.data(), n);
+    if ((rc = pt_set_triangles(c, tris.data(), n)) != PT_OK) return rc;
+    if ((rc = pt_set_materials(c, mats.data(), (int32_t)mats.size(), tex.empty() ? nullptr : tex.data(), (int32_t)tex.size())) != PT_OK) return rc;
+    if ((rc = pt_set_lights(c, lights.data(), nl, total)) != PT_OK) return rc;
+    if ((rc = pt_set_environment_color(c, env)) != PT_OK) return rc;
+    return pt_build_bvh(c, stats);
 }
 
 int pt_get_bvh(pt_context* c, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs) {

@@ -58,6 +58,12 @@ struct WideBvh {
 };
 bool build_wide_bvh(const HostBvh& in, const float* tris_pre, int64_t n_tris, int width, WideBvh& out, std::string& msg);
 
+// pt_obj.cpp: Wavefront .obj/.mtl with the reference's material rules (Scene.cpp:120-231)
+struct SceneFile;
+bool load_obj_file(const std::string& path, SceneFile& out, std::string& err);
+bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<float>& rgba);
+void set_last_error(const char* msg);       // message returned by pt_last_error() on this thread
+
 bool write_ppm(const char* path, int w, int h, const uint8_t* rgb);
 bool write_pfm(const char* path, int w, int h, const float* rgb);
 

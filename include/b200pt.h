@@ -144,6 +144,39 @@ int pt_build_light_table(const float* tris_abs, int64_t n_tris, const pt_materia
 /* e1/e2 pre-subtraction in place (Scene.cpp:334-337). */
 void pt_presubtract_edges(float* tris, int64_t n_tris);
 
+/* ---- scene files: Scene::LoadScene / LoadOBJ (Scene.cpp:120-259), scene.txt (Program.cpp:70-84) ----
+ * Own .obj/.mtl reader that follows tinyobjloader's behaviour for what the reference consumes (shapes at g/o, per-face
+ * usemtl, quads cut along the shorter diagonal, missing normal (0,1,0) / texcoord (0,0)) and the reference's material
+ * rules (matId = 2*(1 + .mtl index), sky = 0, every triangle of a shape takes the shape's FIRST face's material,
+ * roughness = sqrt(2/(Ns+2)), metallic = max(Ks) > 0.3, emissive = sum(Ke) > 1e-5). Host only. */
+typedef struct pt_scene_file pt_scene_file;
+int pt_scene_file_load_obj(const char* obj_path, pt_scene_file** out);
+void pt_scene_file_free(pt_scene_file* sf);
+int64_t pt_scene_file_num_triangles(const pt_scene_file* sf);
+const float* pt_scene_file_vertices(const pt_scene_file* sf);          /* n_tris x 3 x {pos.xyz, normal.xyz, uv.xy} */
+const uint32_t* pt_scene_file_material_ids(const pt_scene_file* sf);   /* per triangle */
+int32_t pt_scene_file_num_materials(const pt_scene_file* sf);          /* sky included */
+const pt_material* pt_scene_file_materials(const pt_scene_file* sf);   /* albedo_tex = -1: see texture_path */
+const char* pt_scene_file_texture_path(const pt_scene_file* sf, int32_t material);   /* folder + map_Kd, "" if none */
+int32_t pt_scene_file_num_shapes(const pt_scene_file* sf);
+const char* pt_scene_file_warnings(const pt_scene_file* sf);
+/* map_Kd image -> RGBA32F texels (byte / 255, rows in file order; Texture2D::LoadTexture, Texture.cpp:146-156, decodes
+ * through SOIL2 -- here: .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
+int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgba);
+/* scene.txt: line 1 scene path, line 2 environment string, then camera position xyz and rotation (yaw pitch roll). */
+typedef struct pt_scene_txt {
+    char scene_path[1024];
+    char environment[1024];
+    float camera_position[3], camera_rotation[3];
+} pt_scene_txt;
+int pt_scene_txt_read(const char* path, pt_scene_txt* out);
+/* LoadEnvironmnet (Renderer.cpp:236-260): "GENERATE COLOR BLACK|WHITE" (anything else after COLOR: red, as the reference).
+ * HDR equirect / 6-face lists go through raster passes in the reference and return PT_ERR_UNSUPPORTED here. */
+int pt_parse_environment(const char* args, float rgb[3]);
+/* Everything Renderer::Initialize does with a scene path: parse, assemble triangles, light table, edge pre-subtraction,
+ * textures (map_Kd as .ppm/.bmp/.tga; other formats keep the Kd colour), uploads, BVH build. environment may be NULL. */
+int pt_load_scene(pt_context* ctx, const char* scene_path, const char* environment, pt_bvh_stats* stats_or_null);
+
 /* ---- camera: Camera::GenerateImagePlane (math/Camera.cpp:6-22) + Shader::LoadCamera ---- */
 void pt_camera_image_plane(float aspect, float fov, float focus, float aperture, const float pos[3],
                            const float rot[3], pt_camera* out);

@@ -234,3 +234,39 @@ def tonemap(rgb_sum, num_samples):
     for i in range(a.shape[0]):
         lib().or_tonemap(_p(a[i:i + 1]), num_samples, _p(out[i:i + 1]))
     return out
+
+
+# ---------------------------------------------------------------- tinyobjloader (the reference's .obj parser), compiled in place
+TINYOBJ_SO = os.path.join(_HERE, "_ref", "libref_tinyobj.so")
+
+
+def have_tinyobj():
+    return os.path.exists(TINYOBJ_SO)
+
+
+def ref_tinyobj_load(path):
+    """tinyobj::ObjReader (extern/tinyobjloader, as configured at Scene.cpp:125-136) -> raw arrays: corner_idx (c,3)
+    [vertex, normal, texcoord], face_mat (f,), shape_first_face (s+1,), v (nv,3), vn, vt (nvt,2), materials (m,11)
+    [Kd, Ks, Ke, Ns, illum], texnames [m]."""
+    l = C.CDLL(TINYOBJ_SO)
+    I, F = C.POINTER(C.c_int), C.POINTER(C.c_float)
+    nc, nf, ns, nv, nvn, nvt, nm = (C.c_int() for _ in range(7))
+    ci, fm, sf, v, vn, vt, mf, names = I(), I(), I(), F(), F(), F(), F(), C.c_char_p()
+    l.ref_tinyobj_load.argtypes = [C.c_char_p] + [C.c_void_p] * 15
+    l.ref_tinyobj_free.argtypes = [C.c_void_p]
+    rc = l.ref_tinyobj_load(path.encode(), C.byref(nc), C.byref(ci), C.byref(nf), C.byref(fm), C.byref(ns), C.byref(sf),
+                            C.byref(nv), C.byref(v), C.byref(nvn), C.byref(vn), C.byref(nvt), C.byref(vt), C.byref(nm),
+                            C.byref(mf), C.byref(names))
+    if rc != 0:
+        raise RuntimeError(f"tinyobj could not parse {path}")
+
+    def arr(p, shape, dt):
+        n = int(np.prod(shape))
+        return (np.ctypeslib.as_array(p, shape=(max(n, 1),))[:n].astype(dt).reshape(shape)).copy()
+    out = dict(corner_idx=arr(ci, (nc.value, 3), np.int32), face_mat=arr(fm, (nf.value,), np.int32),
+               shape_first_face=arr(sf, (ns.value + 1,), np.int32), v=arr(v, (nv.value, 3), np.float32),
+               vn=arr(vn, (nvn.value, 3), np.float32), vt=arr(vt, (nvt.value, 2), np.float32),
+               materials=arr(mf, (nm.value, 11), np.float32), texnames=names.value.decode().split("\n")[:nm.value])
+    for p in (ci, fm, sf, v, vn, vt, mf):
+        l.ref_tinyobj_free(p)
+    return out
