@@ -156,9 +156,11 @@ def test_room_scene_data_feeds_the_oracle():
     assert s.lights.shape[0] == 4 and s.total_light_area > 0.36
     nodes, refs, _ = build_bvh_host(s.tris)
     s.set_bvh(nodes, refs)
-    rays = np.zeros((1, 8), np.float32); rays[0, 0:3] = (0.1, 1, 0.05); rays[0, 4:7] = (0, 1, 0); rays[0, 7] = 1e20
+    # (an exactly axis-parallel ray misses everything in the reference's slab test: 0 * inf; tilt it)
+    d = np.array([0.01, 1.0, 0.02]); d /= np.linalg.norm(d)
+    rays = np.zeros((1, 8), np.float32); rays[0, 0:3] = (0.1, 1, 0.05); rays[0, 4:7] = d; rays[0, 7] = 1e20
     hit, _ = oracle.Oracle(s).trace_closest(rays)
-    assert abs(hit[0, 0] - 0.99) < 1e-5                                              # straight up: the lamp at y = 1.99
+    assert abs(hit[0, 0] - 0.99 / d[1]) < 1e-5                                       # upwards: the lamp at y = 1.99
 
 
 @pytest.mark.gpu
