@@ -65,12 +65,28 @@ public:
         check(pt_seed_rng(ctx_, seed));                                                                      // Renderer.cpp:545-553
         width_ = window->Width; height_ = window->Height;
     }
+    // The reference's own signature: Initialize(Window*, scenePath, env) (Renderer.cpp:448, called at Program.cpp:81).
+    // scenePath is an .obj (the only live loader, Scene.cpp:248-259), env e.g. "GENERATE COLOR WHITE".
+    void Initialize(const Window* window, const char* scenePath, const std::string& env, int max_depth = 66, uint64_t seed = 0,
+                    int bvh_layout = PT_BVH_REFERENCE) {
+        pt_config cfg{};
+        cfg.width = (int32_t)window->Width; cfg.height = (int32_t)window->Height;
+        cfg.max_depth = max_depth; cfg.microfacet_model = PT_MICROFACET_GGX; cfg.device = 0; cfg.bvh_layout = bvh_layout;
+        check(pt_create(&cfg, &ctx_));
+        check(pt_load_scene(ctx_, scenePath, env.c_str(), &bvh_stats_));                                    // Scene::LoadScene
+        check(pt_seed_rng(ctx_, seed));
+        width_ = window->Width; height_ = window->Height;
+    }
     void RenderFrame(const Camera& camera) {                      // Renderer.cpp:651-662
         check(pt_set_camera(ctx_, &camera.Plane()));
         check(pt_render_frames(ctx_, 1));
     }
     // Renderer::Present (Renderer.cpp:681-685): headless resolve into a host buffer (width*height*3 bytes, row 0 = bottom).
     void Present(uint8_t* rgb8) { check(pt_resolve(ctx_, pt_num_samples(ctx_), nullptr, rgb8)); }
+    // The same without stalling the render stream: the copy to (pinned) host memory overlaps the next RenderFrame;
+    // the image is complete after Synchronize(). At most two presents in flight.
+    void PresentAsync(uint8_t* rgb8) { check(pt_present_async(ctx_, pt_num_samples(ctx_), rgb8)); }
+    void Synchronize() { check(pt_synchronize(ctx_)); }
     void ResetSamples() { check(pt_reset_samples(ctx_)); }        // Renderer.cpp:687-691
     uint32_t GetNumSamples() { return pt_num_samples(ctx_); }     // Renderer.cpp:693-695
     void SaveScreenshot(const std::string& filename) { check(pt_save_screenshot(ctx_, filename.c_str())); }   // :697-705
