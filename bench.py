@@ -501,6 +501,27 @@ def run_primary(args, name, wl):
     cam = make_camera(scene, W, H)
     r.lib.pt_set_camera(r.ctx, cam.plane)
     n = W * H
+    # the device builder (Morton LBVH): build time and what its tree costs to traverse
+    dev = {}
+    if args.bvh == "reference":
+        s2 = Scene(scene.data)
+        r2 = Renderer().Initialize(W, H, s2, max_depth=1, device=local, seed=1, bvh="device")
+        dev_builds = [float(r2.bvh_stats.build_ms)]
+        import ctypes as C
+        from gpupathtracer_b200.api import pt_bvh_stats
+        for _ in range(4):
+            st = pt_bvh_stats(); r2.lib.pt_build_bvh_device(r2.ctx, C.byref(st)); dev_builds.append(float(st.build_ms)); tot = float(st.total_ms)
+        dev = {"device_lbvh_kernels_best_of_5": min(dev_builds), "device_lbvh_total_with_readback_and_install": tot,
+               "device_lbvh_sah_cost": float(r2.bvh_stats.sah_cost), "device_lbvh_depth": int(r2.bvh_stats.max_depth)}
+        r2.lib.pt_set_camera(r2.ctx, cam.plane)
+        pr2 = r2.RaygenProbe(0, n)
+        rays2 = np.zeros((n, 8), np.float32); rays2[:, 0:3] = pr2[:, 2:5]; rays2[:, 4:7] = pr2[:, 5:8]; rays2[:, 7] = 1e20
+        d2 = torch.from_numpy(rays2).cuda(); h2 = torch.empty((n, 4), dtype=torch.float32, device="cuda"); torch.cuda.synchronize()
+        ms2 = []
+        for _ in range(8):
+            r2.TraceClosestDevice(d2.data_ptr(), n, h2.data_ptr()); ms2.append(r2.LastDeviceMs())
+        dev["device_lbvh_primary_mrays_s"] = n / min(ms2) / 1e3
+        r2.CleanUp()
     pr = r.RaygenProbe(0, n)
     rays = np.zeros((n, 8), np.float32)
     rays[:, 0:3] = pr[:, 2:5]; rays[:, 4:7] = pr[:, 5:8]; rays[:, 7] = 1e20
@@ -537,7 +558,7 @@ def run_primary(args, name, wl):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "width": W, "height": H,
                        "bvh": "own SBVH builder (host, all cores), reference layout", "l2": "256 MB flush between timed launches"},
-            "bvh_build_ms": {"ours_host_all_cores_best_of_3": min(builds), "nodes": int(r.bvh_stats.n_nodes), "refs": int(r.bvh_stats.n_refs),
+            "bvh_build_ms": {**dev, "ours_host_all_cores_best_of_3": min(builds), "nodes": int(r.bvh_stats.n_nodes), "refs": int(r.bvh_stats.n_refs),
                              "sah_cost": float(r.bvh_stats.sah_cost)},
             "hit_fraction": float((hits[:, 3].view(np.int32) >= 0).mean()),
             "e2e": {"value": e2e_rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": n * 32, "d2h_bytes_per_step": n * 16,

@@ -46,7 +46,7 @@ class pt_counters(C.Structure):
 
 class pt_bvh_stats(C.Structure):
     _fields_ = [("n_nodes", C.c_int32), ("n_refs", C.c_int32), ("n_leaves", C.c_int32), ("max_depth", C.c_int32),
-                ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+                ("sah_cost", C.c_float), ("build_ms", C.c_float), ("total_ms", C.c_float)]
 
 
 class pt_scene_txt(C.Structure):
@@ -68,6 +68,7 @@ SYMBOLS = [
     ("pt_set_environment_color", C.c_int, [_P, _F]),
     ("pt_set_bvh", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
     ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
+    ("pt_build_bvh_device", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_bvh_build_host", C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(_F), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32), C.POINTER(pt_bvh_stats)]),
     ("pt_free", None, [_P]),
     ("pt_bvh_collapse_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, C.c_int32, C.POINTER(C.POINTER(C.c_uint8)),
@@ -356,7 +357,13 @@ class Renderer:
                                          C.cast(texs, C.c_void_p), len(scene.textures)))
         _check(self.lib.pt_set_lights(ctx, _ptr(scene.lights), scene.lights.shape[0], scene.total_light_area))
         _check(self.lib.pt_set_environment_color(ctx, _f3(scene.env_color)))
-        if bvh == "build" or scene.nodes is None:
+        if bvh == "device":
+            stats = pt_bvh_stats()
+            _check(self.lib.pt_build_bvh_device(ctx, C.byref(stats)))
+            self.bvh_stats = stats
+            nodes, refs = self.GetBVH()
+            scene.set_bvh(nodes, refs)
+        elif bvh == "build" or scene.nodes is None:
             stats = pt_bvh_stats()
             _check(self.lib.pt_build_bvh(ctx, C.byref(stats)))
             self.bvh_stats = stats

@@ -410,6 +410,46 @@ int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
         stats->max_depth = c->h_bvh.max_depth;
         stats->sah_cost = c->h_bvh.sah_cost;
         stats->build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+        stats->total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return PT_OK;
+}
+
+// The device builder (pt_bvh_gpu.cu): Morton LBVH, one triangle per leaf, reference serialised form
+int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_build_bvh_device: null context");
+    if (c->h_tris.empty() || !c->d_tris.p) return fail(PT_ERR_INVALID, "pt_build_bvh_device: call pt_set_triangles first");
+    const int64_t n = (int64_t)(c->h_tris.size() / 20);
+    if (n < 2 || n > (1 << 29)) return fail(PT_ERR_LIMIT, "pt_build_bvh_device: 2 .. 2^29 triangles");
+    CK(cudaSetDevice(c->cfg.device));
+    auto t0 = std::chrono::steady_clock::now();
+    DevBuf<float4> d_nodes; DevBuf<int> d_refs;
+    CK(d_nodes.alloc(2 * (size_t)(2 * n - 1)));
+    CK(d_refs.alloc((size_t)n));
+    float kernel_ms = 0.0f;
+    int launches = build_lbvh_device(c->d_tris.p, (int)n, d_nodes.p, d_refs.p, c->stream, &kernel_ms);
+    if (launches < 0) { d_nodes.release(); d_refs.release(); return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches))); }
+    c->counters.kernel_launches += launches;
+    HostBvh b;
+    b.nodes.resize(8 * (size_t)(2 * n - 1)); b.refs.resize((size_t)n);
+    CK(cudaMemcpyAsync(b.nodes.data(), d_nodes.p, b.nodes.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(b.refs.data(), d_refs.p, b.refs.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    d_nodes.release(); d_refs.release();
+    std::string msg; int n_leaves = 0;
+    int depth = validate_bvh(b.nodes.data(), (int)(2 * n - 1), b.refs.data(), (int)n, n, msg, &n_leaves);
+    if (depth < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: built tree is invalid: %s", msg.c_str());
+    if (depth >= 64) return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (64); use pt_build_bvh", depth);
+    b.max_depth = depth; b.n_leaves = n_leaves;
+    b.sah_cost = bvh_sah_cost(b.nodes.data(), (int)(2 * n - 1), b.refs.data(), (int)n);
+    c->h_bvh = std::move(b);
+    int rc = install_bvh(c);
+    if (rc != PT_OK) return rc;
+    if (stats) {
+        stats->n_nodes = (int)(2 * n - 1); stats->n_refs = (int)n; stats->n_leaves = n_leaves; stats->max_depth = depth;
+        stats->sah_cost = c->h_bvh.sah_cost;
+        stats->build_ms = kernel_ms;        // device time of the build kernels; wall time incl. read-back + install below
+        stats->total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
     return PT_OK;
 }

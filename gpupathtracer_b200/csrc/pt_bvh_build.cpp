@@ -400,6 +400,7 @@ int pt_bvh_build_host(const float* tris, int64_t n, int32_t n_threads, float** n
     if (stats) {
         stats->n_nodes = *n_nodes; stats->n_refs = *n_refs; stats->n_leaves = b.n_leaves; stats->max_depth = b.max_depth;
         stats->sah_cost = b.sah_cost; stats->build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+        stats->total_ms = stats->build_ms;
     }
     return PT_OK;
 }
