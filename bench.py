@@ -284,7 +284,8 @@ def run_pathtrace(args, name, wl):
     scene = build_scene(wl)
     t0 = time.perf_counter()
     r = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
-                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh="build", bvh_layout=LAYOUTS[args.bvh])
+                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh="device" if args.builder == "device" else "build",
+                              bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     cam = make_camera(scene, W, H)
     # accumulation buffer owned by torch so NCCL can reduce it in place
@@ -353,7 +354,8 @@ def run_pathtrace(args, name, wl):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
                        "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
-                       "bvh": f"own SBVH builder, {args.bvh} layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
+                       "bvh": f"{'device LBVH' if args.builder == 'device' else 'own SBVH'} builder, {args.bvh} layout",
+                       "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
                        "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
                        "parallelism": f"samples split over {world} GPU(s), 1 NCCL reduce of the accumulation buffer per {args.steps}-frame batch",
@@ -401,7 +403,8 @@ def run_micro(args, name, wl):
     n = wl["n_rays"]
     scene, closest, anyr = micro_scene_and_rays(n, 0xB200 + 7 * rank)
     t0 = time.perf_counter()
-    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh="build", bvh_layout=LAYOUTS[args.bvh])
+    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh="device" if args.builder == "device" else "build",
+                              bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     d_closest = torch.from_numpy(closest).cuda()
     d_any = torch.from_numpy(anyr).cuda()
@@ -452,7 +455,8 @@ def run_micro(args, name, wl):
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "rays_per_step": 2 * n,
-                       "bvh": f"own SBVH builder, {args.bvh} layout", "bvh_build_ms": float(r.bvh_stats.build_ms),
+                       "bvh": f"{'device LBVH' if args.builder == 'device' else 'own SBVH'} builder, {args.bvh} layout",
+                       "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "bvh_nodes": int(r.bvh_stats.n_nodes), "bvh_refs": int(r.bvh_stats.n_refs),
                        "l2": "ray batches (2 x 512 MB) and tree + leaf stream (~1.2 GB) exceed the 126 MB L2",
                        "parallelism": f"{world} independent replica(s), each with its own 16M-ray batch; no collective", "init_s": init_s},
@@ -511,7 +515,7 @@ def run_primary(args, name, wl):
         from gpupathtracer_b200.api import pt_bvh_stats
         for _ in range(4):
             st = pt_bvh_stats(); r2.lib.pt_build_bvh_device(r2.ctx, C.byref(st)); dev_builds.append(float(st.build_ms)); tot = float(st.total_ms)
-        dev = {"device_lbvh_kernels_best_of_5": min(dev_builds), "device_lbvh_total_with_readback_and_install": tot,
+        dev = {"device_lbvh_kernels_best_of_5": min(dev_builds), "device_lbvh_total_call_ms": tot,
                "device_lbvh_sah_cost": float(r2.bvh_stats.sah_cost), "device_lbvh_depth": int(r2.bvh_stats.max_depth)}
         r2.lib.pt_set_camera(r2.ctx, cam.plane)
         pr2 = r2.RaygenProbe(0, n)
@@ -599,6 +603,8 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--builder", default="host", choices=["host", "device"],
+                    help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels")
     ap.add_argument("--bvh", default="reference", choices=["reference", "wide", "wide4"],
                     help="device BVH layout: the reference's binary fp32 tree (bit-exact) or the compressed 8-/4-wide collapse of it")
     args = ap.parse_args()

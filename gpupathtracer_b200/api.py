@@ -88,6 +88,7 @@ SYMBOLS = [
     ("pt_scene_txt_read", C.c_int, [C.c_char_p, _P]),
     ("pt_parse_environment", C.c_int, [C.c_char_p, _F]),
     ("pt_load_scene", C.c_int, [_P, C.c_char_p, C.c_char_p, C.POINTER(pt_bvh_stats)]),
+    ("pt_bvh_sah_cost", C.c_float, [_P, C.c_int32, _P, C.c_int32]),
     ("pt_get_bvh", C.c_int, [_P, _P, C.POINTER(C.c_int32), _P, C.POINTER(C.c_int32)]),
     ("pt_assemble_triangles", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_build_light_table", C.c_int, [_P, C.c_int64, _P, C.c_int32, _P, C.c_int32, _F]),
@@ -361,8 +362,9 @@ class Renderer:
             stats = pt_bvh_stats()
             _check(self.lib.pt_build_bvh_device(ctx, C.byref(stats)))
             self.bvh_stats = stats
-            nodes, refs = self.GetBVH()
+            nodes, refs = self.GetBVH()            # reads the serialised tree back from the device
             scene.set_bvh(nodes, refs)
+            stats.sah_cost = self.lib.pt_bvh_sah_cost(_ptr(scene.nodes), scene.nodes.shape[0], _ptr(scene.refs), scene.refs.shape[0])
         elif bvh == "build" or scene.nodes is None:
             stats = pt_bvh_stats()
             _check(self.lib.pt_build_bvh(ctx, C.byref(stats)))

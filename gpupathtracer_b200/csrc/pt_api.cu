@@ -81,6 +81,9 @@ struct pt_context {
     DevBuf<unsigned char> d_wide;          // PT_BVH_WIDE / PT_BVH_WIDE4 node bytes
     DevBuf<LeafTri> d_wide_tris;
     WideBvh h_wide;
+    // device builder: serialised tree kept on the device, host mirror fetched on demand
+    DevBuf<float4> d_ser_nodes; DevBuf<int> d_ser_refs;
+    bool host_bvh_stale = false; int64_t ser_nodes = 0, ser_refs = 0;
     float wide_ms = 0.0f;
     DevBuf<MaterialRec> d_mats;
     DevBuf<TextureRec> d_texrec;
@@ -212,7 +215,7 @@ void pt_destroy(pt_context* c) {
     if (!c) return;
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
-    c->d_wide.release(); c->d_wide_tris.release();
+    c->d_wide.release(); c->d_wide_tris.release(); c->d_ser_nodes.release(); c->d_ser_refs.release();
     c->d_tris.release(); c->d_pairs.release(); c->d_leaf.release(); c->d_mats.release(); c->d_texrec.release();
     for (float4* t : c->d_texels) cudaFree(t);
     c->d_lights.release(); c->d_rng.release(); c->d_accum_own.release();
@@ -237,6 +240,21 @@ void pt_destroy(pt_context* c) {
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     cudaStreamDestroy(c->stream);
     delete c;
+}
+
+// host mirror of a device-built tree (nodesVec / referenceVec of the reference), fetched when first needed
+static int ensure_host_bvh(pt_context* c) {
+    if (!c->host_bvh_stale) return PT_OK;
+    HostBvh b;
+    b.nodes.resize(8 * (size_t)c->ser_nodes); b.refs.resize((size_t)c->ser_refs);
+    CK(cudaMemcpyAsync(b.nodes.data(), c->d_ser_nodes.p, b.nodes.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(b.refs.data(), c->d_ser_refs.p, b.refs.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    b.max_depth = c->h_bvh.max_depth; b.n_leaves = c->h_bvh.n_leaves;
+    b.sah_cost = bvh_sah_cost(b.nodes.data(), (int)c->ser_nodes, b.refs.data(), (int)c->ser_refs);
+    c->h_bvh = std::move(b);
+    c->host_bvh_stale = false;
+    return PT_OK;
 }
 
 // PT_BVH_WIDE: collapse the reference-form tree into 8-wide quantised nodes + their own leaf triangle stream
@@ -268,6 +286,7 @@ static int upload_wide(pt_context* c) {
 
 // (re)build the leaf triangle stream from host triangles + reference list
 static int upload_leaf_stream(pt_context* c) {
+    { int rc = ensure_host_bvh(c); if (rc != PT_OK) return rc; }
     if (c->h_tris.empty() || c->h_bvh.refs.empty()) return PT_OK;
     const size_t nr = c->h_bvh.refs.size();
     const int64_t nt = (int64_t)(c->h_tris.size() / 20);
@@ -353,6 +372,7 @@ int pt_set_environment_color(pt_context* c, const float rgb[3]) {
 
 static int install_bvh(pt_context* c) {
     invalidate_graphs(c);
+    c->host_bvh_stale = false;                                    // the host tree is the authority again
     const float* nodes = c->h_bvh.nodes.data();
     const int n_nodes = (int)(c->h_bvh.nodes.size() / 8);
     const int n_pairs = (n_nodes - 1) / 2;
@@ -423,32 +443,35 @@ int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) {
     if (n < 2 || n > (1 << 29)) return fail(PT_ERR_LIMIT, "pt_build_bvh_device: 2 .. 2^29 triangles");
     CK(cudaSetDevice(c->cfg.device));
     auto t0 = std::chrono::steady_clock::now();
-    DevBuf<float4> d_nodes; DevBuf<int> d_refs;
-    CK(d_nodes.alloc(2 * (size_t)(2 * n - 1)));
-    CK(d_refs.alloc((size_t)n));
-    float kernel_ms = 0.0f;
-    int launches = build_lbvh_device(c->d_tris.p, (int)n, d_nodes.p, d_refs.p, c->stream, &kernel_ms);
-    if (launches < 0) { d_nodes.release(); d_refs.release(); return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches))); }
+    invalidate_graphs(c);
+    // the serialised tree stays on the device (read back only when somebody asks for it: pt_get_bvh, wide collapse);
+    // the traversal layout (pair records + leaf stream) is written by the build kernels themselves
+    CK(c->d_ser_nodes.alloc(2 * (size_t)(2 * n - 1)));
+    CK(c->d_ser_refs.alloc((size_t)n));
+    CK(c->d_pairs.alloc((size_t)(n - 1)));
+    CK(c->d_leaf.alloc((size_t)n));
+    float kernel_ms = 0.0f; int depth = 0;
+    int launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
+                                     c->stream, &kernel_ms);
+    if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
     c->counters.kernel_launches += launches;
-    HostBvh b;
-    b.nodes.resize(8 * (size_t)(2 * n - 1)); b.refs.resize((size_t)n);
-    CK(cudaMemcpyAsync(b.nodes.data(), d_nodes.p, b.nodes.size() * 4, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaMemcpyAsync(b.refs.data(), d_refs.p, b.refs.size() * 4, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    d_nodes.release(); d_refs.release();
-    std::string msg; int n_leaves = 0;
-    int depth = validate_bvh(b.nodes.data(), (int)(2 * n - 1), b.refs.data(), (int)n, n, msg, &n_leaves);
-    if (depth < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: built tree is invalid: %s", msg.c_str());
-    if (depth >= 64) return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (64); use pt_build_bvh", depth);
-    b.max_depth = depth; b.n_leaves = n_leaves;
-    b.sah_cost = bvh_sah_cost(b.nodes.data(), (int)(2 * n - 1), b.refs.data(), (int)n);
-    c->h_bvh = std::move(b);
-    int rc = install_bvh(c);
-    if (rc != PT_OK) return rc;
+    if (depth >= 64) {
+        c->d_pairs.release(); c->d_leaf.release();
+        return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (64); use pt_build_bvh", depth);
+    }
+    c->n_leaf = (int)n;
+    c->h_bvh = HostBvh();
+    c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = (int)n;
+    c->host_bvh_stale = true; c->ser_nodes = 2 * n - 1; c->ser_refs = n;
+    if (c->cfg.bvh_layout != PT_BVH_REFERENCE) {                 // the wide collapse runs on the host
+        int rc = ensure_host_bvh(c);
+        if (rc != PT_OK) return rc;
+        if ((rc = upload_wide(c)) != PT_OK) return rc;
+    }
     if (stats) {
-        stats->n_nodes = (int)(2 * n - 1); stats->n_refs = (int)n; stats->n_leaves = n_leaves; stats->max_depth = depth;
-        stats->sah_cost = c->h_bvh.sah_cost;
-        stats->build_ms = kernel_ms;        // device time of the build kernels; wall time incl. read-back + install below
+        stats->n_nodes = (int)(2 * n - 1); stats->n_refs = (int)n; stats->n_leaves = (int)n; stats->max_depth = depth;
+        stats->sah_cost = c->host_bvh_stale ? 0.0f : c->h_bvh.sah_cost;     // known once the tree has been read back
+        stats->build_ms = kernel_ms;        // CUDA-event time of the build kernels (the tree is usable at that point)
         stats->total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
     return PT_OK;
@@ -499,6 +522,7 @@ int pt_load_scene(pt_context* c, const char* scene_path, const char* environment
 
 int pt_get_bvh(pt_context* c, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs) {
     if (!c || !n_nodes || !n_refs) return fail(PT_ERR_INVALID, "pt_get_bvh: bad argument");
+    { CK(cudaSetDevice(c->cfg.device)); int rc = ensure_host_bvh(c); if (rc != PT_OK) return rc; }
     *n_nodes = (int32_t)(c->h_bvh.nodes.size() / 8);
     *n_refs = (int32_t)c->h_bvh.refs.size();
     if (nodes) memcpy(nodes, c->h_bvh.nodes.data(), c->h_bvh.nodes.size() * 4);

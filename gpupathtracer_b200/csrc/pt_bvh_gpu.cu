@@ -240,10 +240,20 @@ __device__ __forceinline__ float box_area(float4 lo, float4 hi) {
 // (BVH.cpp:2240-2247); leaf l owns reference-list entry l = -(triangle index), the negated "last of leaf" entry (:2117)
 __global__ void k_emit(const int* __restrict__ vals, int n, const int2* __restrict__ children, const float4* __restrict__ leaf_lo,
                        const float4* __restrict__ leaf_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi,
-                       float4* nodes /* 2 float4 per node */, int* refs) {
+                       float4* nodes /* 2 float4 per node */, int* refs, const float4* __restrict__ tris, BvhPair* pairs, LeafTri* leaf) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     refs[i] = -vals[i];
+    if (leaf) {
+        // what upload_leaf_stream does on the host: intersection record of the leaf's triangle; the end-of-leaf marker is
+        // the sign of the reference-list entry, which triangle 0 cannot carry (-0 == 0, BVH.cpp:2117)
+        const int tri = vals[i];
+        const float4* t = tris + 5 * (size_t)tri;
+        float4 t0 = t[0], t1 = t[1], t2 = t[2];
+        leaf[i].r[0] = t0; leaf[i].r[1] = t1;
+        leaf[i].r[2] = make_float4(t2.x, __int_as_float(tri > 0 ? ~tri : tri), 0.0f, 0.0f);
+        leaf[i].r[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
     if (i >= n - 1) return;
     int2 c = children[i];
     float4 lo0 = c.x < 0 ? leaf_lo[~c.x] : inner_lo[c.x], hi0 = c.x < 0 ? leaf_hi[~c.x] : inner_hi[c.x];
@@ -258,24 +268,46 @@ __global__ void k_emit(const int* __restrict__ vals, int n, const int2* __restri
     nodes[at + 1] = make_float4(hi0.x, hi0.y, hi0.z, 0.0f);
     nodes[at + 2] = make_float4(lo1.x, lo1.y, lo1.z, __int_as_float(link1));
     nodes[at + 3] = make_float4(hi1.x, hi1.y, hi1.z, 0.0f);
+    if (pairs) {
+        // install_bvh's re-layout: one 64-B record per sibling pair; link = pair index of an inner child, ~leaf-stream offset of a leaf
+        int p0 = link0 > 0 ? (link0 - 1) / 2 : ~(-link0), p1 = link1 > 0 ? (link1 - 1) / 2 : ~(-link1);
+        pairs[i].q[0] = make_float4(lo0.x, lo0.y, lo0.z, __int_as_float(p0));
+        pairs[i].q[1] = make_float4(hi0.x, hi0.y, hi0.z, 0.0f);
+        pairs[i].q[2] = make_float4(lo1.x, lo1.y, lo1.z, __int_as_float(p1));
+        pairs[i].q[3] = make_float4(hi1.x, hi1.y, hi1.z, 0.0f);
+    }
     if (i == 0) {
         nodes[0] = make_float4(inner_lo[0].x, inner_lo[0].y, inner_lo[0].z, __int_as_float(1));
         nodes[1] = make_float4(inner_hi[0].x, inner_hi[0].y, inner_hi[0].z, 0.0f);
     }
 }
 
+// depth of the tree = longest leaf-to-root climb
+__global__ void k_depth(const int* __restrict__ parent_inner, const int* __restrict__ parent_leaf, int n, int* max_depth) {
+    int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n) return;
+    int d = 0;
+    for (int cur = parent_leaf[l]; cur >= 0; cur = parent_inner[cur]) d++;
+    d = max(d, __shfl_xor_sync(0xffffffffu, d, 16)); d = max(d, __shfl_xor_sync(0xffffffffu, d, 8));
+    d = max(d, __shfl_xor_sync(0xffffffffu, d, 4)); d = max(d, __shfl_xor_sync(0xffffffffu, d, 2));
+    d = max(d, __shfl_xor_sync(0xffffffffu, d, 1));
+    if ((threadIdx.x & 31) == 0) atomicMax(max_depth, d);
+}
+
 // ---------------------------------------------------------------- driver
 #define BCK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { err = e__; goto done; } } while (0)
 
-// d_tris: n x 5 float4 (device). d_nodes: 2 * (2n - 1) float4, d_refs: n ints (device, caller-owned).
+// d_tris: n x 5 float4 (device). d_nodes: 2 * (2n - 1) float4, d_refs: n ints (device, caller-owned). d_pairs (n - 1) /
+// d_leaf (n): optional, the traversal layout of pt_layout.h written directly. *depth: depth of the tree.
 // Returns the number of kernels launched (> 0) or -(cudaError) on failure; *kernel_ms = device time of the build.
-int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, cudaStream_t st, float* kernel_ms) {
+int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
+                      cudaStream_t st, float* kernel_ms) {
     cudaError_t err = cudaSuccess;
     int launches = 0;
     const int n_blocks = (n + SORT_TILE - 1) / SORT_TILE;
     const int grid_n = (n + BVH_THREADS - 1) / BVH_THREADS;
     unsigned *bounds = nullptr, *keys[2] = {nullptr, nullptr}, *hist = nullptr, *flags = nullptr;
-    int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr;
+    int *vals[2] = {nullptr, nullptr}, *parent_inner = nullptr, *parent_leaf = nullptr, *d_depth = nullptr;
     int2* children = nullptr;
     float4 *leaf_lo = nullptr, *leaf_hi = nullptr, *inner_lo = nullptr, *inner_hi = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
@@ -291,6 +323,8 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
     BCK(cudaMalloc((void**)&inner_lo, (size_t)n * 16)); BCK(cudaMalloc((void**)&inner_hi, (size_t)n * 16));
     BCK(cudaMemcpyAsync(bounds, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice, st));
     BCK(cudaMemsetAsync(flags, 0, (size_t)n * 4, st));
+    BCK(cudaMalloc((void**)&d_depth, 4));
+    BCK(cudaMemsetAsync(d_depth, 0, 4, st));
     BCK(cudaEventRecord(e0, st));
     k_scene_bounds<<<min(grid_n, 148 * 8), BVH_THREADS, 0, st>>>(d_tris, n, bounds); launches++;
     k_morton<<<grid_n, BVH_THREADS, 0, st>>>(d_tris, n, bounds, keys[0], vals[0]); launches++;
@@ -303,14 +337,16 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
     // 4 passes: the sorted arrays are back in buffer 0
     k_hierarchy<<<grid_n, BVH_THREADS, 0, st>>>(keys[0], n, children, parent_inner, parent_leaf); launches++;
     k_fit<<<grid_n, BVH_THREADS, 0, st>>>(d_tris, vals[0], n, children, parent_inner, parent_leaf, leaf_lo, leaf_hi, inner_lo, inner_hi, flags); launches++;
-    k_emit<<<grid_n, BVH_THREADS, 0, st>>>(vals[0], n, children, leaf_lo, leaf_hi, inner_lo, inner_hi, d_nodes, d_refs); launches++;
+    k_emit<<<grid_n, BVH_THREADS, 0, st>>>(vals[0], n, children, leaf_lo, leaf_hi, inner_lo, inner_hi, d_nodes, d_refs, d_tris, d_pairs, d_leaf); launches++;
+    k_depth<<<grid_n, BVH_THREADS, 0, st>>>(parent_inner, parent_leaf, n, d_depth); launches++;
     BCK(cudaEventRecord(e1, st));
+    if (depth) BCK(cudaMemcpyAsync(depth, d_depth, 4, cudaMemcpyDeviceToHost, st));
     BCK(cudaGetLastError());
     BCK(cudaStreamSynchronize(st));
     if (kernel_ms) BCK(cudaEventElapsedTime(kernel_ms, e0, e1));
 done:
     cudaFree(bounds); cudaFree(keys[0]); cudaFree(keys[1]); cudaFree(vals[0]); cudaFree(vals[1]); cudaFree(hist); cudaFree(flags);
-    cudaFree(parent_inner); cudaFree(parent_leaf); cudaFree(children);
+    cudaFree(parent_inner); cudaFree(parent_leaf); cudaFree(children); cudaFree(d_depth);
     cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(inner_lo); cudaFree(inner_hi);
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);

@@ -174,3 +174,8 @@ void pt_camera_image_plane(float aspect, float fov, float focus, float aperture,
 }
 
 }  // extern "C"
+
+extern "C" float pt_bvh_sah_cost(const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs) {
+    if (!nodes || !refs || n_nodes < 1) return -1.0f;
+    return pt::bvh_sah_cost(nodes, n_nodes, refs, n_refs);
+}

@@ -49,7 +49,8 @@ struct SliceStreams { cudaStream_t a, b; cudaEvent_t ev_shade, ev_shadow; };
 int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceStreams& ss, bool wait_prev);
 
 // pt_bvh_gpu.cu: LBVH on the device, output in the reference's serialised form
-int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, cudaStream_t st, float* kernel_ms);
+int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
+                      cudaStream_t st, float* kernel_ms);
 
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);
 void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st);

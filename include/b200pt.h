@@ -135,6 +135,9 @@ void pt_free(void* p);
 int pt_bvh_collapse_host(const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs, const float* tris,
                          int64_t n_tris, int32_t width, uint8_t** node_bytes, int64_t* n_wide, int32_t* node_size,
                          int32_t** tri_ids, int64_t* n_tri_ids, int32_t* depth);
+/* SAH cost of a serialised tree with the reference's constants (CalculateCost, BVH.cpp:2174-2195; traversal 1.23,
+ * intersection 5.33), relative to the root's surface area. */
+float pt_bvh_sah_cost(const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs);
 /* Read back the tree in the reference's serialised form (what nodesVec/referenceVec hold, BVH.cpp:2291-2292);
  * call with NULL arrays to query sizes. */
 int pt_get_bvh(pt_context* ctx, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs);
