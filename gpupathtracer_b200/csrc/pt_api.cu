@@ -90,6 +90,7 @@ struct pt_context {
     std::vector<float4*> d_texels;
     DevBuf<float2> d_lights;
     int n_lights = 0, n_textures = 0, n_leaf = 0;
+    int top_pairs = 0;                     // pair records [0, top_pairs) are the breadth-first top of the tree
     float total_light_area = 0.0f;
     float env[3] = {1.0f, 1.0f, 1.0f};
 
@@ -124,7 +125,7 @@ static void invalidate_graphs(pt_context* c) {
 
 static SceneDev scene_dev(pt_context* c) {
     SceneDev s{};
-    s.pairs = c->d_pairs.p; s.leaf_tris = c->d_leaf.p; s.n_leaf_tris = c->n_leaf;
+    s.pairs = c->d_pairs.p; s.leaf_tris = c->d_leaf.p; s.n_leaf_tris = c->n_leaf; s.top_pairs = c->top_pairs;
     s.wide_nodes = c->d_wide.p; s.wide_tris = c->d_wide_tris.p;
     s.tris = c->d_tris.p; s.materials = c->d_mats.p; s.textures = c->d_texrec.p; s.n_textures = c->n_textures;
     s.lights = c->d_lights.p; s.n_lights = c->n_lights; s.total_light_area = c->total_light_area;
@@ -390,6 +391,37 @@ static int install_bvh(pt_context* c) {
         pairs[pi].q[2] = make_float4(c1[0], c1[1], c1[2], link_of(c1));
         pairs[pi].q[3] = make_float4(c1[4], c1[5], c1[6], 0.0f);
     }
+    // PT_SMEM_TOP = K: move the K pair records nearest the root to the front, breadth-first, so that a CTA can stage
+    // records [0, K) in shared memory with one contiguous copy. Only indices change; what a ray visits does not.
+    c->top_pairs = 0;
+    if (c->dims.top_pairs > 0 && n_pairs > 1) {
+        const int K = c->dims.top_pairs < n_pairs ? c->dims.top_pairs : n_pairs;
+        auto link_i = [](float f) { int32_t v; memcpy(&v, &f, 4); return v; };
+        std::vector<int> order; order.reserve(n_pairs);
+        std::vector<char> taken(n_pairs, 0);
+        order.push_back(0); taken[0] = 1;
+        for (size_t head = 0; head < order.size() && (int)order.size() < K; head++) {
+            const BvhPair& pr = pairs[order[head]];
+            for (int k = 0; k < 2 && (int)order.size() < K; k++) {
+                int32_t l = link_i(pr.q[2 * k].w);
+                if (l >= 1 && !taken[l]) { order.push_back(l); taken[l] = 1; }
+            }
+        }
+        for (int i = 0; i < n_pairs; i++) if (!taken[i]) order.push_back(i);
+        std::vector<int> new_index(n_pairs);
+        for (int i = 0; i < n_pairs; i++) new_index[order[i]] = i;
+        std::vector<BvhPair> re(n_pairs);
+        for (int i = 0; i < n_pairs; i++) {
+            BvhPair pr = pairs[order[i]];
+            for (int k = 0; k < 2; k++) {
+                int32_t l = link_i(pr.q[2 * k].w);
+                if (l >= 1) { int32_t nl = new_index[l]; memcpy(&pr.q[2 * k].w, &nl, 4); }
+            }
+            re[i] = pr;
+        }
+        pairs.swap(re);
+        c->top_pairs = K;
+    }
     CK(c->d_pairs.alloc(n_pairs));
     CK(cudaMemcpyAsync(c->d_pairs.p, pairs.data(), sizeof(BvhPair) * n_pairs, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -460,6 +492,7 @@ int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) {
         return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (64); use pt_build_bvh", depth);
     }
     c->n_leaf = (int)n;
+    c->top_pairs = 0;                                             // Karras order: the top levels are not contiguous
     c->h_bvh = HostBvh();
     c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = (int)n;
     c->host_bvh_stale = true; c->ser_nodes = 2 * n - 1; c->ser_refs = n;

@@ -48,7 +48,7 @@ void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, fl
     BatchIO io{rays, hits, nullptr, (int)n, cursor};
     if (dims.wide == 8) k_trace_batch<false, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_trace_batch<false, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
-    else k_trace_batch<false, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else k_trace_batch<false, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
                       const LaunchDims& dims, cudaStream_t st) {
@@ -56,7 +56,7 @@ void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsign
     BatchIO io{rays, nullptr, flags, (int)n, cursor};
     if (dims.wide == 8) k_trace_batch<true, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_trace_batch<true, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
-    else k_trace_batch<true, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else k_trace_batch<true, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 // ------------------------------------------------------------------ ray generation
@@ -120,7 +120,7 @@ k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
 static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
     if (dims.wide == 8) k_extend<WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_extend<WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
-    else k_extend<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+    else k_extend<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 // ------------------------------------------------------------------ shade
@@ -283,7 +283,7 @@ k_shadow(FrameParams p, int bounce, int qi_next, int leaf_thresh, int fetch_thre
 static void launch_shadow(const FrameParams& p, int b, int qi_next, const LaunchDims& dims, cudaStream_t st) {
     if (dims.wide == 8) k_shadow<WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_shadow<WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
-    else k_shadow<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+    else k_shadow<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 __global__ void k_tally(FrameParams p) {
@@ -404,6 +404,7 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
     cudaGetDeviceProperties(&prop, device);
     int per_sm_ext = 1, per_sm_shadow = 1, per_sm_shade = 1;
     out->wide = wide;
+    out->top_pairs = 0;
     if (wide == 8) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<WideTraverser<8>>, PT_TRACE_THREADS, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<WideTraverser<8>>, PT_TRACE_THREADS, 0);
@@ -411,8 +412,12 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<WideTraverser<4>>, PT_TRACE_THREADS, 0);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<WideTraverser<4>>, PT_TRACE_THREADS, 0);
     } else {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<Traverser>, PT_TRACE_THREADS, 0);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<Traverser>, PT_TRACE_THREADS, 0);
+        out->top_pairs = 0;
+        if (const char* e = getenv("PT_SMEM_TOP")) out->top_pairs = atoi(e);
+        if (out->top_pairs < 0) out->top_pairs = 0;
+        if (out->top_pairs > 700) out->top_pairs = 700;                      // 44.8 KB: below the 48-KB dynamic limit without opt-in
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);
     }
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0>, PT_SHADE_THREADS, 0);
     int per = per_sm_ext < per_sm_shadow ? per_sm_ext : per_sm_shadow;

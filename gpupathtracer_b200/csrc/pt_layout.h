@@ -70,6 +70,7 @@ struct SceneDev {
     const BvhPair* pairs;
     const LeafTri* leaf_tris;
     int n_leaf_tris;
+    int top_pairs;               // pair records [0, top_pairs) = the top levels in breadth-first order, staged in shared memory
     const void* wide_nodes;      // PT_BVH_WIDE (96-B nodes) / PT_BVH_WIDE4 (64-B nodes)
     const LeafTri* wide_tris;
     const float4* tris;          // n_tris x 5

@@ -77,6 +77,13 @@ struct Traverser {
         sp = 0;
         result = false;
     }
+    // Stage the top of the tree (pair records [0, top_pairs), breadth-first) in shared memory, once per CTA.
+    static __device__ __forceinline__ void prologue(const SceneDev& s) {
+        extern __shared__ float4 s_top[];
+        const float4* src = reinterpret_cast<const float4*>(s.pairs);
+        for (int i = threadIdx.x; i < 4 * s.top_pairs; i += blockDim.x) s_top[i] = __ldg(src + i);
+        __syncthreads();
+    }
     __device__ __forceinline__ void idle() { current = 0; sp = 0; }
     __device__ __forceinline__ bool at_leaf() const { return current < 0; }
     // returns true when the ray is finished
@@ -87,9 +94,16 @@ struct Traverser {
     }
     template <bool ANY>
     __device__ __forceinline__ bool inner_step(const SceneDev& s, int* stack) {
-        const float4* q = s.pairs[current].q;
-        F8 ca = ldg256(q), cb = ldg256(q + 2);
-        float4 a0 = ca.lo, a1 = ca.hi, b0 = cb.lo, b1 = cb.hi;
+        float4 a0, a1, b0, b1;
+        if (current < s.top_pairs) {
+            extern __shared__ float4 s_top[];
+            const float4* q = s_top + 4 * current;
+            a0 = q[0]; a1 = q[1]; b0 = q[2]; b1 = q[3];
+        } else {
+            const float4* q = s.pairs[current].q;
+            F8 ca = ldg256(q), cb = ldg256(q + 2);
+            a0 = ca.lo; a1 = ca.hi; b0 = cb.lo; b1 = cb.hi;
+        }
         bool hit0, hit1;
         float d0 = slab_test(a0, a1, inv, oinv, h.t, hit0);
         float d1 = slab_test(b0, b1, inv, oinv, h.t, hit1);
@@ -130,6 +144,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io
     const unsigned lt_mask = (1u << lane) - 1u;
     const int n = io.count();
     int* cursor = io.cursor();
+    TR::prologue(s);
     TR tr;
     typename TR::StackEntry stack[TR::kStack];   // per-lane traversal stack (local memory, L1-resident)
     bool active = false, exhausted = false;

@@ -60,6 +60,7 @@ struct WideTraverser {
     unsigned octinv;
     bool result;
 
+    static __device__ __forceinline__ void prologue(const SceneDev&) {}
     __device__ __forceinline__ void idle() { G = make_uint2(0, 0); T = make_uint2(0, 0); sp = 0; }
     __device__ __forceinline__ void begin(V3 org, V3 dir, float tmax) {
         o = org; d = dir;
