@@ -114,7 +114,13 @@ struct Traverser {
             // does not depend on the visiting order, and the answer is "some reachable leaf holds a hit".
             bool swap = d0 > d1;
             current = swap ? sub1 : sub0;
-            stack[sp++] = swap ? sub0 : sub1;
+            const int far_child = swap ? sub0 : sub1;
+            stack[sp++] = far_child;
+#ifdef PT_PREFETCH_FAR   // measured (build with PT_NVCC_EXTRA=-DPT_PREFETCH_FAR): atrium 3.03 -> 2.85 Grays/s, 10M-triangle batch 2.40 -> 1.91:
+                         // the prefetch costs an L1 tag look-up on a pipe that is already the bottleneck, and half the pushed nodes are culled
+            if (far_child >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(s.pairs + far_child));
+            else asm volatile("prefetch.global.L1 [%0];" :: "l"(s.leaf_tris + ~far_child));
+#endif
             return false;
         }
         if (hit0 != hit1) { current = hit0 ? sub0 : sub1; return false; }
