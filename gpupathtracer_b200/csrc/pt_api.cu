@@ -62,6 +62,9 @@ struct pt_context {
     DevBuf<CameraRec> d_cam;
     // pt_present_async: double-buffered resolve target + copy stream
     cudaStream_t copy_stream = nullptr;
+    // host-batch pipeline (trace_host)
+    cudaStream_t in_stream = nullptr;
+    cudaEvent_t ev_h_in[2] = {nullptr, nullptr}, ev_h_done[2] = {nullptr, nullptr}, ev_h_out[2] = {nullptr, nullptr};
     DevBuf<unsigned char> d_present[2];
     cudaEvent_t ev_resolved = nullptr, ev_copied[2] = {nullptr, nullptr};
     int present_turn = 0;
@@ -236,6 +239,12 @@ void pt_destroy(pt_context* c) {
     if (c->graph.exec) cudaGraphExecDestroy(c->graph.exec);
     c->d_cam.release();
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    if (c->in_stream) { cudaStreamSynchronize(c->in_stream); cudaStreamDestroy(c->in_stream); }
+    for (int k = 0; k < 2; k++) {
+        if (c->ev_h_in[k]) cudaEventDestroy(c->ev_h_in[k]);
+        if (c->ev_h_done[k]) cudaEventDestroy(c->ev_h_done[k]);
+        if (c->ev_h_out[k]) cudaEventDestroy(c->ev_h_out[k]);
+    }
     if (c->ev_resolved) cudaEventDestroy(c->ev_resolved);
     for (int k = 0; k < 2; k++) { if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); c->d_present[k].release(); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -821,31 +830,70 @@ int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_fl
     return PT_OK;
 }
 
-int pt_trace_closest(pt_context* c, const float* rays, int64_t n, float* hits) {
-    if (!c || !rays || !hits || n < 0) return fail(PT_ERR_INVALID, "pt_trace_closest: bad argument");
-    if (n == 0) return PT_OK;
+// Host batches: chunks of kHostChunk rays flow through a three-stage pipeline -- H2D on `in_stream`, the traversal
+// kernel on the render stream, D2H on `copy_stream` -- with double-buffered staging, so a 16 M-ray batch costs about
+// max(PCIe in, kernel, PCIe out) instead of their sum (pinned host memory makes the copies truly asynchronous).
+static const int64_t kHostChunk = 1 << 21;
+
+static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, size_t out_bytes, bool any) {
     CK(cudaSetDevice(c->cfg.device));
-    CK(c->d_stage_rays.alloc(2 * (size_t)n));
-    CK(c->d_stage_hits.alloc((size_t)n));
-    CK(cudaMemcpyAsync(c->d_stage_rays.p, rays, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-    int rc = pt_trace_closest_device(c, c->d_stage_rays.p, n, c->d_stage_hits.p);
+    int rc = check_scene(c, any ? "pt_trace_any" : "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
-    CK(cudaMemcpyAsync(hits, c->d_stage_hits.p, 16 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    const int64_t chunk = n < kHostChunk ? n : kHostChunk;
+    CK(c->d_stage_rays.alloc(2 * 2 * (size_t)chunk));                 // 2 buffers x 2 float4 per ray
+    if (any) CK(c->d_stage_flags.alloc(2 * (size_t)chunk)); else CK(c->d_stage_hits.alloc(2 * (size_t)chunk));
+    if (!c->in_stream) {
+        CK(cudaStreamCreateWithFlags(&c->in_stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; k++) {
+            CK(cudaEventCreateWithFlags(&c->ev_h_in[k], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&c->ev_h_done[k], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&c->ev_h_out[k], cudaEventDisableTiming));
+        }
+    }
+    CK(cudaEventRecord(c->ev0, c->stream));
+    int k = 0;
+    for (int64_t first = 0; first < n; first += chunk, k ^= 1) {
+        const int64_t m = n - first < chunk ? n - first : chunk;
+        float4* d_rays = c->d_stage_rays.p + (size_t)k * 2 * chunk;
+        CK(cudaStreamWaitEvent(c->in_stream, c->ev_h_done[k], 0));    // the kernel that last read this ray buffer
+        CK(cudaMemcpyAsync(d_rays, rays + 8 * first, 32 * (size_t)m, cudaMemcpyHostToDevice, c->in_stream));
+        CK(cudaEventRecord(c->ev_h_in[k], c->in_stream));
+        CK(cudaStreamWaitEvent(c->stream, c->ev_h_in[k], 0));
+        CK(cudaStreamWaitEvent(c->stream, c->ev_h_out[k], 0));        // the copy that last read this result buffer
+        if (any) {
+            unsigned char* d_out = c->d_stage_flags.p + (size_t)k * chunk;
+            launch_trace_any(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream);
+            CK(cudaEventRecord(c->ev_h_done[k], c->stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->ev_h_done[k], 0));
+            CK(cudaMemcpyAsync((unsigned char*)out + first, d_out, (size_t)m, cudaMemcpyDeviceToHost, c->copy_stream));
+            c->counters.shadow_rays += (uint64_t)m;
+        } else {
+            float4* d_out = c->d_stage_hits.p + (size_t)k * chunk;
+            launch_trace_closest(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream);
+            CK(cudaEventRecord(c->ev_h_done[k], c->stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->ev_h_done[k], 0));
+            CK(cudaMemcpyAsync((char*)out + out_bytes * first, d_out, out_bytes * (size_t)m, cudaMemcpyDeviceToHost, c->copy_stream));
+            c->counters.closest_rays += (uint64_t)m;
+        }
+        CK(cudaEventRecord(c->ev_h_out[k], c->copy_stream));
+        c->counters.kernel_launches++;
+    }
+    CK(cudaEventRecord(c->ev1, c->stream));
+    CK(cudaGetLastError());
     CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(c->copy_stream));
     return PT_OK;
 }
-int pt_trace_any(pt_context* c, const float* rays, int64_t n, uint8_t* flags) {
-    if (!c || !rays || !flags || n < 0) return fail(PT_ERR_INVALID, "pt_trace_any: bad argument");
+
+int pt_trace_closest(pt_context* c, const float* rays, int64_t n, float* hits) {
+    if (!c || !rays || !hits || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_closest: bad argument");
     if (n == 0) return PT_OK;
-    CK(cudaSetDevice(c->cfg.device));
-    CK(c->d_stage_rays.alloc(2 * (size_t)n));
-    CK(c->d_stage_flags.alloc((size_t)n));
-    CK(cudaMemcpyAsync(c->d_stage_rays.p, rays, 32 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
-    int rc = pt_trace_any_device(c, c->d_stage_rays.p, n, c->d_stage_flags.p);
-    if (rc != PT_OK) return rc;
-    CK(cudaMemcpyAsync(flags, c->d_stage_flags.p, (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    return PT_OK;
+    return trace_host(c, rays, n, hits, 16, false);
+}
+int pt_trace_any(pt_context* c, const float* rays, int64_t n, uint8_t* flags) {
+    if (!c || !rays || !flags || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_any: bad argument");
+    if (n == 0) return PT_OK;
+    return trace_host(c, rays, n, flags, 1, true);
 }
 
 int pt_raygen_probe(pt_context* c, int64_t first, int64_t n, float* out) {

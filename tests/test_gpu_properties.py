@@ -130,3 +130,24 @@ def test_device_built_bvh(name):
     same = got[:, 3].view(np.int32) == other[:, 3].view(np.int32)
     assert same.mean() > 1 - 1e-4                                # a different tree: only box-culling edge cases and ties differ
     assert np.array_equal(got[same, :3].view(np.uint32), other[same, :3].view(np.uint32))
+
+
+def test_host_batches_larger_than_one_pipeline_chunk():
+    """pt_trace_closest / pt_trace_any stream host batches through the device in 2 M-ray chunks (H2D, kernel, D2H
+    overlapped, double-buffered staging): 2.5 chunks with a ragged tail must give the oracle's bits."""
+    from common import mixed_rays
+    s = get_scene("cornell")
+    n = (1 << 21) * 2 + 777_777
+    rays = mixed_rays(s, n, seed=31)
+    anyr = mixed_rays(s, n, seed=32, any_hit=True)
+    o = oracle.Oracle(s)
+    want, _ = o.trace_closest(rays)
+    wflag, _ = o.trace_any(anyr)
+    r = Renderer().Initialize(64, 64, s)
+    got = r.TraceClosest(rays)
+    gflag = r.TraceAny(anyr)
+    c = r.Counters()
+    r.CleanUp()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(gflag, wflag)
+    assert c["closest_rays"] == n and c["shadow_rays"] == n
