@@ -14,7 +14,8 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
-#include <deque>
+#include <atomic>
+#include <thread>
 #include <cstdlib>
 
 namespace pt {
@@ -23,7 +24,7 @@ namespace {
 struct BNode {
     float lo[3], hi[3];
     int left = -1, right = -1;         // both -1: leaf
-    std::vector<int> tris;
+    int tri_first = 0, tri_count = 0;  // leaf: range in Collapser::leaf_tris
 };
 
 inline float box_area(const float* lo, const float* hi) {
@@ -36,6 +37,8 @@ struct Collapser {
     const HostBvh& in;
     const float* tris;                  // n x 20, pre-subtracted edges
     std::vector<BNode> b;
+    std::vector<int> leaf_tris;         // triangle ids of all leaves, one contiguous range per leaf
+    std::vector<int> big_leaves;        // leaves with more than 3 triangles (split_big_leaf)
 
     int32_t data0(int i) const { int32_t d; std::memcpy(&d, in.nodes.data() + 8 * (size_t)i + 3, 4); return d; }
 
@@ -50,37 +53,49 @@ struct Collapser {
         }
     }
 
-    // reference-form tree -> pointer-free binary nodes; leaves keep their triangle lists
-    int import(int i) {
-        int me = (int)b.size();
-        b.emplace_back();
-        const float* nd = in.nodes.data() + 8 * (size_t)i;
-        for (int k = 0; k < 3; k++) { b[me].lo[k] = nd[k]; b[me].hi[k] = nd[4 + k]; }
-        int32_t d0 = data0(i);
-        if (d0 > 0) {
-            int l = import(d0); b[me].left = l;
-            int r = import(d0 + 1); b[me].right = r;
-        } else {
-            // IntersectLeaf (BVH.glsl:420-437): walk until the negated entry; entry 0 cannot carry the marker, so
-            // that leaf runs on into the next one -- reproduced, those triangles are tested by the reference too
-            std::vector<int> t;
-            for (size_t k = (size_t)(-d0); k < in.refs.size(); k++) {
-                int32_t r = in.refs[k];
-                t.push_back(r < 0 ? -r : r);
-                if (r < 0) break;
+    // reference-form tree -> pointer-free binary nodes (pre-order, explicit stack: the serialised tree may be deep);
+    // leaves keep their triangle lists
+    int import_tree() {
+        struct Todo { int ser, parent; bool right; };
+        std::vector<Todo> stack;
+        stack.push_back({0, -1, false});
+        while (!stack.empty()) {
+            Todo td = stack.back(); stack.pop_back();
+            int me = (int)b.size();
+            b.emplace_back();
+            BNode& x = b[me];
+            if (td.parent >= 0) { if (td.right) b[td.parent].right = me; else b[td.parent].left = me; }
+            const float* nd = in.nodes.data() + 8 * (size_t)td.ser;
+            for (int k = 0; k < 3; k++) { x.lo[k] = nd[k]; x.hi[k] = nd[4 + k]; }
+            int32_t d0 = data0(td.ser);
+            if (d0 > 0) {
+                stack.push_back({d0 + 1, me, true});
+                stack.push_back({d0, me, false});
+            } else {
+                // IntersectLeaf (BVH.glsl:420-437): walk until the negated entry; entry 0 cannot carry the marker, so
+                // that leaf runs on into the next one -- reproduced, those triangles are tested by the reference too
+                size_t first = leaf_tris.size();
+                for (size_t k = (size_t)(-d0); k < in.refs.size(); k++) {
+                    int32_t r = in.refs[k];
+                    leaf_tris.push_back(r < 0 ? -r : r);
+                    if (r < 0) break;
+                }
+                if (leaf_tris.size() - first > 1) {
+                    std::sort(leaf_tris.begin() + first, leaf_tris.end());
+                    leaf_tris.erase(std::unique(leaf_tris.begin() + first, leaf_tris.end()), leaf_tris.end());
+                }
+                x.tri_first = (int)first; x.tri_count = (int)(leaf_tris.size() - first);
+                if (x.tri_count > 3) big_leaves.push_back(me);
             }
-            std::sort(t.begin(), t.end());
-            t.erase(std::unique(t.begin(), t.end()), t.end());
-            b[me].tris = std::move(t);
         }
-        return me;
+        return 0;
     }
 
     // a wide leaf slot holds at most 3 triangles: larger leaves become small median-split subtrees
     void split_big_leaf(int me) {
-        if (b[me].left >= 0 || b[me].tris.size() <= 3) return;
-        std::vector<int> t = std::move(b[me].tris);
-        b[me].tris.clear();
+        if (b[me].left >= 0 || b[me].tri_count <= 3) return;
+        std::vector<int> t(leaf_tris.begin() + b[me].tri_first, leaf_tris.begin() + b[me].tri_first + b[me].tri_count);
+        b[me].tri_count = 0;
         int ax = 0; float ext = -1.0f;
         for (int k = 0; k < 3; k++) if (b[me].hi[k] - b[me].lo[k] > ext) { ext = b[me].hi[k] - b[me].lo[k]; ax = k; }
         std::vector<std::pair<float, int>> key;
@@ -95,11 +110,13 @@ struct Collapser {
             int c = (int)b.size(); b.emplace_back(); kids[side] = c;
             for (int k = 0; k < 3; k++) { b[c].lo[k] = FLT_MAX; b[c].hi[k] = -FLT_MAX; }
             size_t from = side ? half : 0, to = side ? key.size() : half;
+            b[c].tri_first = (int)leaf_tris.size();
             for (size_t q = from; q < to; q++) {
                 float lo[3], hi[3]; tri_bounds(key[q].second, b[me].lo, b[me].hi, lo, hi);
                 for (int k = 0; k < 3; k++) { b[c].lo[k] = std::min(b[c].lo[k], lo[k]); b[c].hi[k] = std::max(b[c].hi[k], hi[k]); }
-                b[c].tris.push_back(key[q].second);
+                leaf_tris.push_back(key[q].second);
             }
+            b[c].tri_count = (int)(to - from);
         }
         b[me].left = kids[0]; b[me].right = kids[1];
         split_big_leaf(kids[0]); split_big_leaf(kids[1]);
@@ -145,25 +162,27 @@ static void serialise(const NodeRec& r, int width, uint8_t* dst) {
     }
 }
 
-bool build_wide_bvh(const HostBvh& in, const float* tris_pre, int64_t n_tris, int width, WideBvh& out, std::string& msg) {
-    (void)n_tris;
-    if (width != 4 && width != 8) { msg = "wide BVH width must be 4 or 8"; return false; }
-    if (in.nodes.size() < 24) { msg = "wide collapse needs a tree whose root is an inner node"; return false; }
-    Collapser c{in, tris_pre, {}};
-    c.b.reserve(in.nodes.size() / 8 + 16);
-    int root = c.import(0);
-    for (size_t i = 0, n0 = c.b.size(); i < n0; i++) c.split_big_leaf((int)i);
-    const std::vector<BNode>& b = c.b;
-
-    std::vector<NodeRec> recs;
-    out.tri_ids.clear(); out.depth = 0; out.width = width; out.node_size = width == 8 ? 96 : 64;
+// Breadth-first emission of wide nodes below a set of binary subtree roots. One Emitter is private to one thread:
+// node and triangle indices are local and rebased when the pieces are concatenated.
+struct alignas(128) Emitter {
     struct Item { int wide, bin, depth; };
-    std::deque<Item> queue;
-    recs.emplace_back();
-    queue.push_back({0, root, 0});
-    while (!queue.empty()) {
-        Item it = queue.front(); queue.pop_front();
-        out.depth = std::max(out.depth, it.depth);
+    const std::vector<BNode>& b;
+    const std::vector<int>& leaf_tris;
+    int width;
+    std::vector<NodeRec> recs;
+    std::vector<int> tri_ids;
+    std::vector<Item> queue; size_t head = 0;
+    int depth = 0;
+    bool bad_leaf = false;
+
+    Emitter(const std::vector<BNode>& b_, const std::vector<int>& lt, int w) : b(b_), leaf_tris(lt), width(w) {}
+    bool empty() const { return head == queue.size(); }
+    size_t pending() const { return queue.size() - head; }
+    void seed(int bin, int d) { queue.push_back({(int)recs.size(), bin, d}); recs.emplace_back(); }
+
+    void step() {
+        Item it = queue[head++];
+        depth = std::max(depth, it.depth);
         // ---- gather up to `width` children: repeatedly open the inner child with the largest surface area
         int kids[8]; int nk = 0;
         kids[nk++] = b[it.bin].left; kids[nk++] = b[it.bin].right;
@@ -208,9 +227,10 @@ bool build_wide_bvh(const HostBvh& in, const float* tris_pre, int64_t n_tris, in
         for (int k = 0; k < nk; k++) kid_in_slot[slot_of[k]] = kids[k];
 
         NodeRec w; std::memset(&w, 0, sizeof(w));
-        for (int a = 0; a < 3; a++) { w.p[a] = lo[a]; w.e[a] = grid_exponent(hi[a] - lo[a]); }
+        double scale[3];
+        for (int a = 0; a < 3; a++) { w.p[a] = lo[a]; w.e[a] = grid_exponent(hi[a] - lo[a]); scale[a] = std::ldexp(1.0, (int)w.e[a] - 127); }
         w.child_base = (uint32_t)recs.size();
-        w.tri_base = (uint32_t)out.tri_ids.size();
+        w.tri_base = (uint32_t)tri_ids.size();
         int tri_off = 0;
         for (int s = 0; s < 8; s++) {
             int kid = kid_in_slot[s];
@@ -218,34 +238,105 @@ bool build_wide_bvh(const HostBvh& in, const float* tris_pre, int64_t n_tris, in
             const int k = w.n++;                              // position in the node's child arrays
             const BNode& x = b[kid];
             for (int a = 0; a < 3; a++) {
-                double scale = std::ldexp(1.0, (int)w.e[a] - 127);
-                double ql = std::floor(((double)x.lo[a] - (double)w.p[a]) / scale);
-                double qh = std::ceil(((double)x.hi[a] - (double)w.p[a]) / scale);
+                double ql = std::floor(((double)x.lo[a] - (double)w.p[a]) / scale[a]);
+                double qh = std::ceil(((double)x.hi[a] - (double)w.p[a]) / scale[a]);
                 ql = std::min(std::max(ql, 0.0), 255.0); qh = std::min(std::max(qh, 0.0), 255.0);
                 // the kernel evaluates p + scale * q in fp32: make sure that still encloses the fp32 box
-                while (ql > 0.0 && w.p[a] + (float)scale * (float)ql > x.lo[a]) ql -= 1.0;
-                while (qh < 255.0 && w.p[a] + (float)scale * (float)qh < x.hi[a]) qh += 1.0;
+                while (ql > 0.0 && w.p[a] + (float)scale[a] * (float)ql > x.lo[a]) ql -= 1.0;
+                while (qh < 255.0 && w.p[a] + (float)scale[a] * (float)qh < x.hi[a]) qh += 1.0;
                 w.qlo[a][k] = (uint8_t)ql; w.qhi[a][k] = (uint8_t)qh;
             }
             if (x.left >= 0) {
                 w.imask |= (uint8_t)(1u << s);
                 w.meta[k] = (uint8_t)((1u << 5) | (24 + s));
-                queue.push_back({(int)recs.size(), kid, it.depth + 1});     // inner children: contiguous, slot order
-                recs.emplace_back();
+                seed(kid, it.depth + 1);                      // inner children: contiguous, slot order
             } else {
-                int cnt = (int)x.tris.size();                // 1..3 after split_big_leaf
-                if (cnt < 1 || cnt > 3) { msg = "internal: leaf with an unsupported triangle count"; return false; }
+                int cnt = x.tri_count;                        // 1..3 after split_big_leaf
+                if (cnt < 1 || cnt > 3) { bad_leaf = true; cnt = std::min(std::max(cnt, 1), 3); }
                 w.meta[k] = (uint8_t)((((1u << cnt) - 1u) << 5) | (unsigned)tri_off);
-                for (int id : x.tris) out.tri_ids.push_back(id);
+                for (int q = 0; q < cnt; q++) tri_ids.push_back(leaf_tris[(size_t)x.tri_first + q]);
                 tri_off += cnt;
             }
         }
         recs[it.wide] = w;
     }
+};
+
+// Node order: the top of the tree breadth-first until kFrontier subtrees are open, then each of those subtrees
+// breadth-first in its own block (emitted by a pool of threads; the order does not depend on the thread count).
+bool build_wide_bvh(const HostBvh& in, const float* tris_pre, int64_t n_tris, int width, WideBvh& out, std::string& msg) {
+    (void)n_tris;
+    if (width != 4 && width != 8) { msg = "wide BVH width must be 4 or 8"; return false; }
+    if (in.nodes.size() < 24) { msg = "wide collapse needs a tree whose root is an inner node"; return false; }
+    Collapser c{in, tris_pre, {}, {}, {}};
+    c.b.reserve(in.nodes.size() / 8 + 16);
+    c.leaf_tris.reserve(in.refs.size());
+    int root = c.import_tree();
+    for (int leaf : c.big_leaves) c.split_big_leaf(leaf);
+
+    out.tri_ids.clear(); out.depth = 0; out.width = width; out.node_size = width == 8 ? 96 : 64;
+    constexpr size_t kFrontier = 1024;
+    Emitter top(c.b, c.leaf_tris, width);
+    top.seed(root, 0);
+    while (!top.empty() && top.pending() < kFrontier) top.step();
+    const size_t n_sub = top.pending();
+    std::vector<Emitter> sub;
+    sub.reserve(n_sub);
+    for (size_t k = 0; k < n_sub; k++) {
+        sub.emplace_back(c.b, c.leaf_tris, width);
+        sub.back().seed(top.queue[top.head + k].bin, top.queue[top.head + k].depth);
+    }
+    {
+        std::atomic<size_t> next{0};
+        auto work = [&]() { for (size_t k; (k = next.fetch_add(1)) < n_sub;) while (!sub[k].empty()) sub[k].step(); };
+        int n_threads = (int)std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), std::max<size_t>(n_sub / 4, 1));
+        std::vector<std::thread> pool;
+        for (int t = 1; t < n_threads; t++) pool.emplace_back(work);
+        work();
+        for (auto& t : pool) t.join();
+    }
+    // ---- concatenate: sub[k].recs[0] is the node the top already allocated; the rest forms block k
+    std::vector<size_t> node_off(n_sub + 1), tri_off(n_sub + 1);
+    node_off[0] = top.recs.size(); tri_off[0] = top.tri_ids.size();
+    bool bad = top.bad_leaf; out.depth = top.depth;
+    for (size_t k = 0; k < n_sub; k++) {
+        node_off[k + 1] = node_off[k] + sub[k].recs.size() - 1;
+        tri_off[k + 1] = tri_off[k] + sub[k].tri_ids.size();
+        bad = bad || sub[k].bad_leaf; out.depth = std::max(out.depth, sub[k].depth);
+    }
+    if (bad) { msg = "internal: leaf with an unsupported triangle count"; return false; }
     if (out.depth >= 30) { msg = "wide tree too deep for the traversal stack"; return false; }
-    out.n_nodes = (int64_t)recs.size();
+    if (node_off[n_sub] >= (size_t)1 << 31 || tri_off[n_sub] >= (size_t)1 << 31) { msg = "wide tree exceeds 2^31 nodes or triangle slots"; return false; }
+    out.n_nodes = (int64_t)node_off[n_sub];
     out.bytes.assign((size_t)out.n_nodes * out.node_size, 0);
-    for (int64_t i = 0; i < out.n_nodes; i++) serialise(recs[i], width, out.bytes.data() + (size_t)i * out.node_size);
+    out.tri_ids.resize(tri_off[n_sub]);
+    std::copy(top.tri_ids.begin(), top.tri_ids.end(), out.tri_ids.begin());
+    {
+        const size_t n_top = top.recs.size();
+        std::atomic<size_t> next{0};
+        auto work = [&]() {
+            for (size_t k; (k = next.fetch_add(1)) < n_sub + 1;) {
+                if (k == n_sub) {        // the top block; its last n_sub nodes (the open subtrees) are written below
+                    for (size_t i = 0; i + n_sub < n_top; i++) serialise(top.recs[i], width, out.bytes.data() + i * out.node_size);
+                    continue;
+                }
+                Emitter& e = sub[k];
+                for (size_t i = 0; i < e.recs.size(); i++) {
+                    NodeRec r = e.recs[i];
+                    r.child_base = (uint32_t)(r.child_base - 1 + node_off[k]);
+                    r.tri_base = (uint32_t)(r.tri_base + tri_off[k]);
+                    size_t at = i == 0 ? (size_t)top.queue[top.head + k].wide : node_off[k] + i - 1;
+                    serialise(r, width, out.bytes.data() + at * out.node_size);
+                }
+                std::copy(e.tri_ids.begin(), e.tri_ids.end(), out.tri_ids.begin() + tri_off[k]);
+            }
+        };
+        int n_threads = (int)std::max(1u, std::thread::hardware_concurrency());
+        std::vector<std::thread> pool;
+        for (int t = 1; t < n_threads; t++) pool.emplace_back(work);
+        work();
+        for (auto& t : pool) t.join();
+    }
     return true;
 }
 
