@@ -66,6 +66,12 @@ SYMBOLS = [
     ("pt_set_materials", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
     ("pt_set_lights", C.c_int, [_P, _P, C.c_int32, C.c_float]),
     ("pt_set_environment_color", C.c_int, [_P, _F]),
+    ("pt_set_environment_cubemap", C.c_int, [_P, _P, C.c_int32]),
+    ("pt_set_environment_equirect", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32]),
+    ("pt_environment_size", C.c_int32, [_P]),
+    ("pt_download_environment", C.c_int, [_P, _P]),
+    ("pt_load_environment", C.c_int, [_P, C.c_char_p]),
+    ("pt_image_load_hdr", C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(_F)]),
     ("pt_set_bvh", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
     ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_build_bvh_device", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
@@ -242,6 +248,16 @@ def load_image(path):
     return out
 
 
+def load_hdr(path):
+    """Radiance .hdr as stbi_loadf(path, .., 4) returns it (Renderer.cpp:265) -> (h, w, 4) float32."""
+    lib = load_library()
+    w, h, p = C.c_int32(), C.c_int32(), _F()
+    _check(lib.pt_image_load_hdr(path.encode(), C.byref(w), C.byref(h), C.byref(p)))
+    out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
+    lib.pt_free(p)
+    return out
+
+
 def scene_data_from_obj(path, camera=None, env_color=(1.0, 1.0, 1.0)):
     """The file the reference would load (Scene::LoadScene) as a `scenes.SceneData`, textures decoded and bound the way
     pt_load_scene does it -- so the oracle and the per-array upload path can be fed from an .obj too."""
@@ -317,6 +333,7 @@ class Scene:
         self.lights, self.total_light_area = build_light_table(self.tris_abs, self.materials)
         self.tris = presubtract_edges(self.tris_abs)
         self.env_color = tuple(data.env_color)
+        self.env_cubemap = None       # (6, S, S, 4) float32: +X -X +Y -Y +Z -Z faces, replaces env_color when set
         self.textures = [np.ascontiguousarray(t, dtype=np.float32) for t in data.textures]
         self.nodes = None
         self.refs = None
@@ -358,6 +375,8 @@ class Renderer:
                                          C.cast(texs, C.c_void_p), len(scene.textures)))
         _check(self.lib.pt_set_lights(ctx, _ptr(scene.lights), scene.lights.shape[0], scene.total_light_area))
         _check(self.lib.pt_set_environment_color(ctx, _f3(scene.env_color)))
+        if getattr(scene, "env_cubemap", None) is not None:
+            self.SetEnvironmentCubemap(scene.env_cubemap)
         if bvh == "device":
             stats = pt_bvh_stats()
             _check(self.lib.pt_build_bvh_device(ctx, C.byref(stats)))
@@ -393,6 +412,28 @@ class Renderer:
         self.bvh_stats = stats
         _check(self.lib.pt_seed_rng(ctx, seed))
         return self
+
+    # -- LoadEnvironmnet, Renderer.cpp:236-323
+    def SetEnvironmentCubemap(self, faces):
+        faces = np.ascontiguousarray(faces, dtype=np.float32)
+        assert faces.ndim == 4 and faces.shape[0] == 6 and faces.shape[1] == faces.shape[2] and faces.shape[3] == 4
+        _check(self.lib.pt_set_environment_cubemap(self.ctx, _ptr(faces), faces.shape[1]))
+
+    def SetEnvironmentEquirect(self, rgba, cube_size=1024):
+        rgba = np.ascontiguousarray(rgba, dtype=np.float32)
+        assert rgba.ndim == 3 and rgba.shape[2] == 4
+        _check(self.lib.pt_set_environment_equirect(self.ctx, _ptr(rgba), rgba.shape[1], rgba.shape[0], cube_size))
+
+    def LoadEnvironment(self, args):
+        _check(self.lib.pt_load_environment(self.ctx, args.encode()))
+
+    def GetEnvironment(self):
+        n = self.lib.pt_environment_size(self.ctx)
+        if n == 0:
+            return None
+        out = np.zeros((6, n, n, 4), dtype=np.float32)
+        _check(self.lib.pt_download_environment(self.ctx, _ptr(out)))
+        return out
 
     def GetBVH(self):
         nn, nr = C.c_int32(), C.c_int32()

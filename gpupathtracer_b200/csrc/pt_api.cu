@@ -96,6 +96,7 @@ struct pt_context {
     int top_pairs = 0;                     // pair records [0, top_pairs) are the breadth-first top of the tree
     float total_light_area = 0.0f;
     float env[3] = {1.0f, 1.0f, 1.0f};
+    DevBuf<float4> d_env; int env_size = 0;      // cubemap faces, 0: constant colour
 
     CameraRec cam{};
     bool have_cam = false, have_rng = false;
@@ -133,6 +134,7 @@ static SceneDev scene_dev(pt_context* c) {
     s.tris = c->d_tris.p; s.materials = c->d_mats.p; s.textures = c->d_texrec.p; s.n_textures = c->n_textures;
     s.lights = c->d_lights.p; s.n_lights = c->n_lights; s.total_light_area = c->total_light_area;
     s.env[0] = c->env[0]; s.env[1] = c->env[1]; s.env[2] = c->env[2];
+    s.env_faces = c->d_env.p; s.env_size = c->env_size;
     return s;
 }
 
@@ -222,7 +224,7 @@ void pt_destroy(pt_context* c) {
     c->d_wide.release(); c->d_wide_tris.release(); c->d_ser_nodes.release(); c->d_ser_refs.release();
     c->d_tris.release(); c->d_pairs.release(); c->d_leaf.release(); c->d_mats.release(); c->d_texrec.release();
     for (float4* t : c->d_texels) cudaFree(t);
-    c->d_lights.release(); c->d_rng.release(); c->d_accum_own.release();
+    c->d_lights.release(); c->d_env.release(); c->d_rng.release(); c->d_accum_own.release();
     for (int q = 0; q < 2; q++) { for (int k = 0; k < 4; k++) c->d_q[q][k].release(); c->d_qrng[q].release(); }
     for (int k = 0; k < 4; k++) c->d_shadow[k].release();
     c->d_hits.release(); c->d_counters.release(); c->d_totals.release(); c->d_cursor.release();
@@ -377,7 +379,93 @@ int pt_set_environment_color(pt_context* c, const float rgb[3]) {
     if (!c || !rgb) return fail(PT_ERR_INVALID, "pt_set_environment_color: bad argument");
     invalidate_graphs(c);
     c->env[0] = rgb[0]; c->env[1] = rgb[1]; c->env[2] = rgb[2];
+    if (c->env_size) { CK(cudaSetDevice(c->cfg.device)); CK(cudaDeviceSynchronize()); c->d_env.release(); c->env_size = 0; }
     return PT_OK;
+}
+
+int pt_set_environment_cubemap(pt_context* c, const float* faces, int32_t size) {
+    if (!c || !faces || size < 1 || size > 16384) return fail(PT_ERR_INVALID, "pt_set_environment_cubemap: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaDeviceSynchronize());
+    invalidate_graphs(c);
+    CK(c->d_env.alloc(6 * (size_t)size * size));
+    CK(cudaMemcpy(c->d_env.p, faces, 6 * (size_t)size * size * sizeof(float4), cudaMemcpyHostToDevice));
+    c->env_size = size;
+    return PT_OK;
+}
+
+int pt_set_environment_equirect(pt_context* c, const float* rgba, int32_t width, int32_t height, int32_t cube_size) {
+    if (!c || !rgba || width < 1 || height < 1 || cube_size < 1 || cube_size > 16384)
+        return fail(PT_ERR_INVALID, "pt_set_environment_equirect: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaDeviceSynchronize());
+    invalidate_graphs(c);
+    DevBuf<float4> src;
+    CK(src.alloc((size_t)width * height));
+    cudaError_t e = cudaMemcpy(src.p, rgba, (size_t)width * height * sizeof(float4), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = c->d_env.alloc(6 * (size_t)cube_size * cube_size);
+    if (e == cudaSuccess) {
+        launch_equirect_to_cube(src.p, width, height, c->d_env.p, cube_size, c->stream);
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    }
+    src.release();
+    if (e != cudaSuccess) { c->env_size = 0; return fail(PT_ERR_CUDA, "pt_set_environment_equirect: %s", cudaGetErrorString(e)); }
+    c->env_size = cube_size;
+    return PT_OK;
+}
+
+int32_t pt_environment_size(pt_context* c) { return c ? c->env_size : 0; }
+
+int pt_download_environment(pt_context* c, float* faces) {
+    if (!c || !faces) return fail(PT_ERR_INVALID, "pt_download_environment: bad argument");
+    if (!c->env_size) return fail(PT_ERR_INVALID, "pt_download_environment: the environment is a constant colour");
+    CK(cudaSetDevice(c->cfg.device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(faces, c->d_env.p, 6 * (size_t)c->env_size * c->env_size * sizeof(float4), cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+// LoadEnvironmnet (Renderer.cpp:236-323): "GENERATE COLOR x" | *.hdr (equirect -> 1024^2 cubemap) | text file naming six faces
+int pt_load_environment(pt_context* c, const char* args) {
+    if (!c || !args) return fail(PT_ERR_INVALID, "pt_load_environment: bad argument");
+    std::string a = args;
+    std::string ext = a.substr(a.find_last_of('.') + 1);       // npos + 1 == 0: the whole string, as in the reference
+    if (a.find_first_of("GENERATE") == 0) {
+        float rgb[3]; int rc = pt_parse_environment(args, rgb);
+        if (rc != PT_OK) return rc;
+        return pt_set_environment_color(c, rgb);
+    }
+    if (ext == "hdr") {
+        int w = 0, h = 0; std::vector<float> px; std::string err;
+        if (!load_hdr_rgba32f(a, w, h, px, err)) return fail(PT_ERR_IO, "pt_load_environment: %s", err.c_str());
+        return pt_set_environment_equirect(c, px.data(), w, h, 1024);
+    }
+    if (ext == "jpg") return fail(PT_ERR_UNSUPPORTED, "pt_load_environment: %s: no JPEG decoder in this build (convert to .hdr)", args);
+    // TextureCubemap::LoadTexture (Texture.cpp:245-276): six lines (those starting with '#' skipped), paths relative
+    // to the list's folder, order +X -X +Y -Y +Z -Z, each decoded to RGBA bytes -> normalised floats
+    std::string path = a;
+    for (char& ch : path) if (ch == '\\') ch = '/';
+    std::string folder = path.substr(0, path.find_last_of('/') + 1);
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return fail(PT_ERR_IO, "pt_load_environment: cannot open %s", path.c_str());
+    std::vector<std::string> lines; { std::string cur; int ch; while ((ch = fgetc(f)) != EOF) { if (ch == '\n') { lines.push_back(cur); cur.clear(); } else cur.push_back((char)ch); } if (!cur.empty()) lines.push_back(cur); }
+    fclose(f);
+    std::vector<float> faces; int size = 0, got = 0;
+    for (size_t li = 0; li < lines.size() && got < 6; li++) {
+        std::string fp = lines[li];
+        if (!fp.empty() && fp.back() == '\r') fp.pop_back();
+        if (fp.empty()) return fail(PT_ERR_INVALID, "pt_load_environment: %s: empty line in the face list", path.c_str());
+        if (fp.front() == '#') continue;
+        int w = 0, h = 0; std::vector<float> px;
+        if (!load_image_rgba32f(folder + fp, w, h, px)) return fail(PT_ERR_IO, "pt_load_environment: cannot decode %s (supported: .ppm, .bmp, .tga)", (folder + fp).c_str());
+        if (w != h || (got && w != size)) return fail(PT_ERR_INVALID, "pt_load_environment: cube faces must be square and of one size (%s is %dx%d)", fp.c_str(), w, h);
+        size = w;
+        faces.insert(faces.end(), px.begin(), px.end());
+        got++;
+    }
+    if (got != 6) return fail(PT_ERR_INVALID, "pt_load_environment: %s names %d faces, 6 needed", path.c_str(), got);
+    return pt_set_environment_cubemap(c, faces.data(), size);
 }
 
 static int install_bvh(pt_context* c) {
@@ -526,8 +614,10 @@ int pt_load_scene(pt_context* c, const char* scene_path, const char* environment
     size_t dot = path.find_last_of('.');
     if (dot == std::string::npos || path.substr(dot + 1) != "obj")
         return fail(PT_ERR_UNSUPPORTED, "Unsupported file type: %s (the reference's only live loader is .obj, Scene.cpp:248-259)", scene_path);
-    float env[3] = {1.0f, 1.0f, 1.0f};
-    if (environment) { int rc = pt_parse_environment(environment, env); if (rc != PT_OK) return rc; }
+    {
+        int rc = pt_load_environment(c, environment ? environment : "GENERATE COLOR WHITE");
+        if (rc != PT_OK) return rc;
+    }
     pt_scene_file* sf = nullptr;
     int rc = pt_scene_file_load_obj(scene_path, &sf);
     if (rc != PT_OK) return rc;
@@ -558,7 +648,6 @@ int pt_load_scene(pt_context* c, const char* scene_path, const char* environment
     if ((rc = pt_set_triangles(c, tris.data(), n)) != PT_OK) return rc;
     if ((rc = pt_set_materials(c, mats.data(), (int32_t)mats.size(), tex.empty() ? nullptr : tex.data(), (int32_t)tex.size())) != PT_OK) return rc;
     if ((rc = pt_set_lights(c, lights.data(), nl, total)) != PT_OK) return rc;
-    if ((rc = pt_set_environment_color(c, env)) != PT_OK) return rc;
     return pt_build_bvh(c, stats);
 }
 

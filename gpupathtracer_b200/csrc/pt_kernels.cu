@@ -158,7 +158,7 @@ k_shade(FrameParams p, int bounce, int qi) {
             int tri = __float_as_int(hit.w);
             if (tri < 0) {
                 // miss: sky radiance, NOT MIS weighted (Iterative.comp:251-255), store + freeRNG (:262-264)
-                contrib = contrib + thr * v3(s.env[0], s.env[1], s.env[2]);
+                contrib = contrib + thr * sample_environment(s, rd);
                 float4 acc = p.accum[pix];
                 p.accum[pix] = make_float4(acc.x + contrib.x, acc.y + contrib.y, acc.z + contrib.z, 1.0f);
                 p.rng_table[pix] = make_uint4(rng.x, rng.y, rng.z, rng.w);
@@ -396,6 +396,44 @@ void launch_resolve(const float4* accum, long long n, unsigned num_samples, floa
                     cudaStream_t st) {
     int blocks = (int)((n + 255) / 256);
     if (blocks > 0) k_resolve<<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
+}
+
+// ------------------------------------------------------------------ equirectangular -> cubemap
+// LoadEnvironmnet, .hdr branch (Renderer.cpp:262-312): the reference draws a unit cube six times with a 90-degree
+// projection (glm::perspective(radians(90), 1, ..): focal length 1) and the six lookAt views of :286-294 into the faces of
+// an RGB32F cubemap; EquirectangularConverter.vert passes sampleCoords = -position, EquirectangularConverter.frag:9-19
+// looks the equirect image up at (atan(v.z, v.x), asin(v.y)) * (0.1591, 0.3183) + 0.5 of the normalised vector
+// (GL_LINEAR, CLAMP_TO_EDGE, row 0 of the file = t 0). Per face texel that is: position on the cube face
+// p = f + nx * s + ny * u with (nx, ny) the NDC of the texel centre and (s, u, f) the lookAt basis; colour =
+// equirect(normalize(-p)); alpha reads back as 1 (RGB32F storage).
+__global__ void k_equirect_to_cube(const float4* __restrict__ src, int w, int h, float4* __restrict__ faces, int n) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= 6ll * n * n) return;
+    int face = (int)(i / ((long long)n * n));
+    int py = (int)((i / n) % n), px = (int)(i % n);
+    const float centre[6][3] = {{1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+    const float upv[6][3] = {{0, -1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}, {0, -1, 0}, {0, -1, 0}};
+    V3 f = v3(centre[face][0], centre[face][1], centre[face][2]);
+    V3 up = v3(upv[face][0], upv[face][1], upv[face][2]);
+    V3 sv = cross(f, up), uv = cross(sv, f);                       // glm::lookAt, axis-aligned: already unit length
+    float nx = ((float)px + 0.5f) / (float)n * 2.0f - 1.0f, ny = ((float)py + 0.5f) / (float)n * 2.0f - 1.0f;
+    V3 p = f + sv * nx + uv * ny;
+    V3 d = normalize(-p);
+    float tu = atan2f(d.z, d.x) * 0.1591f + 0.5f, tv = asinf(d.y) * 0.3183f + 0.5f;
+    float x = tu * (float)w - 0.5f, y = tv * (float)h - 0.5f;
+    float fx = floorf(x), fy = floorf(y);
+    float wx = x - fx, wy = y - fy;
+    int x0 = min(max((int)fx, 0), w - 1), x1 = min(max((int)fx + 1, 0), w - 1);
+    int y0 = min(max((int)fy, 0), h - 1), y1 = min(max((int)fy + 1, 0), h - 1);
+    float4 a = __ldg(src + (size_t)y0 * w + x0), b = __ldg(src + (size_t)y0 * w + x1);
+    float4 c = __ldg(src + (size_t)y1 * w + x0), e = __ldg(src + (size_t)y1 * w + x1);
+    faces[i] = make_float4(mixf(mixf(a.x, b.x, wx), mixf(c.x, e.x, wx), wy), mixf(mixf(a.y, b.y, wx), mixf(c.y, e.y, wx), wy),
+                           mixf(mixf(a.z, b.z, wx), mixf(c.z, e.z, wx), wy), 1.0f);
+}
+void launch_equirect_to_cube(const float4* src, int w, int h, float4* faces, int n, cudaStream_t st) {
+    long long total = 6ll * n * n;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 0) k_equirect_to_cube<<<blocks, 256, 0, st>>>(src, w, h, faces, n);
 }
 
 // occupancy-derived persistent grid sizes

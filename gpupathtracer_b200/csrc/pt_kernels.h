@@ -57,5 +57,6 @@ void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStr
 void query_launch_dims(int device, int wide, LaunchDims* out);
 void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
                     cudaStream_t st);
+void launch_equirect_to_cube(const float4* src, int w, int h, float4* faces, int n, cudaStream_t st);
 
 }  // namespace pt

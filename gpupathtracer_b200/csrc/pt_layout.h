@@ -80,7 +80,9 @@ struct SceneDev {
     const float2* lights;        // {cumulative area, tri index bits}
     int n_lights;
     float total_light_area;
-    float env[3];
+    float env[3];                // constant environment ("GENERATE COLOR"), used when env_size == 0
+    const float4* env_faces;     // cubemap: 6 x env_size x env_size RGBA32F, faces +X -X +Y -Y +Z -Z, rows as uploaded
+    int env_size;
 };
 
 }  // namespace pt

@@ -598,7 +598,7 @@ int pt_parse_environment(const char* args, float rgb[3]) {
     std::string cmd, arg0, arg1;
     parser >> cmd >> arg0 >> arg1;
     if (cmd != "GENERATE" || arg0 != "COLOR") {
-        pt::set_last_error("environment: only \"GENERATE COLOR <BLACK|WHITE>\" is supported (HDR equirect / 6-face lists need the reference's raster passes)");
+        pt::set_last_error("environment: a string whose first character is one of \"GENERATE\" is taken as a command (find_first_of, Renderer.cpp:238) and the only command is \"GENERATE COLOR <BLACK|WHITE>\"");
         return PT_ERR_UNSUPPORTED;
     }
     if (arg1 == "BLACK") { rgb[0] = rgb[1] = rgb[2] = 0.0f; }

@@ -57,6 +57,32 @@ __device__ inline float4 sample_texture(const TextureRec& t, float u, float v) {
     return r;
 }
 
+// texture(samplerCube(sky), d).xyz, Iterative.comp:251. Face and (s, t) by the OpenGL cube-map table (major axis; ties,
+// which GL leaves to the implementation, go to x, then y), then GL_LINEAR with CLAMP_TO_EDGE inside that face
+// (Renderer.cpp:318-322; seamless filtering is never enabled), float weights. The reference's CPU twin of the lookup is
+// TextureCubemap::Sample (Texture.cpp:278-340, nearest texel, y negated).
+__device__ inline V3 sample_environment(const SceneDev& s, V3 d) {
+    if (s.env_size == 0) return v3(s.env[0], s.env[1], s.env[2]);
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    int face; float sc, tc, ma;
+    if (ax >= ay && ax >= az) { face = d.x > 0.0f ? 0 : 1; ma = ax; sc = d.x > 0.0f ? -d.z : d.z; tc = -d.y; }
+    else if (ay >= az)        { face = d.y > 0.0f ? 2 : 3; ma = ay; sc = d.x; tc = d.y > 0.0f ? d.z : -d.z; }
+    else                      { face = d.z > 0.0f ? 4 : 5; ma = az; sc = d.z > 0.0f ? d.x : -d.x; tc = -d.y; }
+    const int n = s.env_size;
+    float u = 0.5f * (sc / ma + 1.0f), v = 0.5f * (tc / ma + 1.0f);
+    float x = u * (float)n - 0.5f, y = v * (float)n - 0.5f;
+    float fx = floorf(x), fy = floorf(y);
+    float wx = x - fx, wy = y - fy;
+    int x0 = min(max((int)fx, 0), n - 1), x1 = min(max((int)fx + 1, 0), n - 1);
+    int y0 = min(max((int)fy, 0), n - 1), y1 = min(max((int)fy + 1, 0), n - 1);
+    const float4* f = s.env_faces + (size_t)face * n * n;
+    float4 a = __ldg(f + (size_t)y0 * n + x0), b = __ldg(f + (size_t)y0 * n + x1);
+    float4 c = __ldg(f + (size_t)y1 * n + x0), e = __ldg(f + (size_t)y1 * n + x1);
+    return v3(mixf(mixf(a.x, b.x, wx), mixf(c.x, e.x, wx), wy),
+              mixf(mixf(a.y, b.y, wx), mixf(c.y, e.y, wx), wy),
+              mixf(mixf(a.z, b.z, wx), mixf(c.z, e.z, wx), wy));
+}
+
 // ConstructMaterialInstance, Material.glsl:39-54
 __device__ inline Material make_material(const SceneDev& s, uint32_t matId, float tu, float tv) {
     const MaterialRec* m = s.materials + (matId >> 1);

@@ -110,6 +110,20 @@ int pt_set_triangles(pt_context* ctx, const float* tris, int64_t n);
 int pt_set_materials(pt_context* ctx, const pt_material* mats, int32_t n_mats, const pt_texture* tex, int32_t n_tex);
 int pt_set_lights(pt_context* ctx, const pt_light* lights, int32_t n, float total_light_area); /* lightBuf + totalLightArea */
 int pt_set_environment_color(pt_context* ctx, const float rgb[3]);   /* LoadEnvironmnet "GENERATE COLOR", Renderer.cpp:242-260 */
+/* Environment cubemap sampled on a miss (Iterative.comp:251: texture(samplerCube, ray.direction)): six size x size
+ * RGBA32F faces in the order +X -X +Y -Y +Z -Z, rows as they would be handed to glTexImage2D; looked up with the
+ * OpenGL cube-map face table, GL_LINEAR, CLAMP_TO_EDGE per face (Renderer.cpp:318-322). */
+int pt_set_environment_cubemap(pt_context* ctx, const float* faces_rgba, int32_t size);
+/* The .hdr branch of LoadEnvironmnet (Renderer.cpp:262-312) as one kernel: the six 90-degree raster passes over
+ * EquirectangularConverter.vert/.frag written out per face texel. rgba = width x height RGBA32F, row 0 = top of the
+ * file (stbi_loadf order); cube_size is 1024 in the reference. */
+int pt_set_environment_equirect(pt_context* ctx, const float* rgba, int32_t width, int32_t height, int32_t cube_size);
+int32_t pt_environment_size(pt_context* ctx);                        /* 0: constant colour */
+int pt_download_environment(pt_context* ctx, float* faces_rgba);     /* 6 x size x size x 4 floats */
+/* All of LoadEnvironmnet: "GENERATE COLOR x" | path ending in .hdr (Radiance RGBE, equirect -> 1024^2 cubemap) | text
+ * file naming six face images (TextureCubemap::LoadTexture, Texture.cpp:245-276; faces as .ppm/.bmp/.tga).
+ * ".jpg" (stbi_loadf + gamma 2.2 in the reference) returns PT_ERR_UNSUPPORTED: no JPEG decoder here. */
+int pt_load_environment(pt_context* ctx, const char* args);
 
 /* ---- BVH: BoundingVolumeHierarchy::BuildBinnedSpatial (BVH.cpp:2197-2293) ---- */
 /* Inject a tree in the reference's serialised form: nodes = n_nodes x {float3 min; int32 data0; float3 max;
@@ -172,6 +186,9 @@ const char* pt_scene_file_warnings(const pt_scene_file* sf);
 /* map_Kd image -> RGBA32F texels (byte / 255, rows in file order; Texture2D::LoadTexture, Texture.cpp:146-156, decodes
  * through SOIL2 -- here: .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
 int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgba);
+/* Radiance .hdr -> RGBA32F as stbi_loadf(path, .., 4) returns it (Renderer.cpp:265): byte * 2^(e-136), alpha 1, rows in
+ * file order. *rgba is malloc()ed, release with pt_free. */
+int pt_image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba);
 /* scene.txt: line 1 scene path, line 2 environment string, then camera position xyz and rotation (yaw pitch roll). */
 typedef struct pt_scene_txt {
     char scene_path[1024];
@@ -179,11 +196,14 @@ typedef struct pt_scene_txt {
     float camera_position[3], camera_rotation[3];
 } pt_scene_txt;
 int pt_scene_txt_read(const char* path, pt_scene_txt* out);
-/* LoadEnvironmnet (Renderer.cpp:236-260): "GENERATE COLOR BLACK|WHITE" (anything else after COLOR: red, as the reference).
- * HDR equirect / 6-face lists go through raster passes in the reference and return PT_ERR_UNSUPPORTED here. */
+/* The "GENERATE COLOR BLACK|WHITE" branch of LoadEnvironmnet (Renderer.cpp:236-260; anything else after COLOR: red, as
+ * the reference). Like the reference (find_first_of, :238) any string whose first character is one of G,E,N,R,A,T is
+ * taken as a command; a command other than GENERATE COLOR returns PT_ERR_UNSUPPORTED (the reference leaves the
+ * cubemap without storage). */
 int pt_parse_environment(const char* args, float rgb[3]);
 /* Everything Renderer::Initialize does with a scene path: parse, assemble triangles, light table, edge pre-subtraction,
- * textures (map_Kd as .ppm/.bmp/.tga; other formats keep the Kd colour), uploads, BVH build. environment may be NULL. */
+ * textures (map_Kd as .ppm/.bmp/.tga; other formats keep the Kd colour), uploads, BVH build. environment goes through
+ * pt_load_environment; NULL = "GENERATE COLOR WHITE". */
 int pt_load_scene(pt_context* ctx, const char* scene_path, const char* environment, pt_bvh_stats* stats_or_null);
 
 /* ---- camera: Camera::GenerateImagePlane (math/Camera.cpp:6-22) + Shader::LoadCamera ---- */

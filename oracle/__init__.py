@@ -31,7 +31,8 @@ class OrScene(C.Structure):
     _fields_ = [("nodes", C.c_void_p), ("n_nodes", C.c_int), ("refs", C.c_void_p), ("n_refs", C.c_int),
                 ("tris", C.c_void_p), ("n_tris", C.c_int), ("materials", C.c_void_p), ("n_materials", C.c_int),
                 ("textures", C.POINTER(OrTexture)), ("n_textures", C.c_int), ("lights", C.c_void_p),
-                ("n_lights", C.c_int), ("total_light_area", C.c_float), ("env_color", C.c_float * 3)]
+                ("n_lights", C.c_int), ("total_light_area", C.c_float), ("env_color", C.c_float * 3),
+                ("env_faces", C.c_void_p), ("env_size", C.c_int)]
 
 
 class OrCamera(C.Structure):
@@ -73,6 +74,8 @@ def lib():
         _lib.or_trace_closest_bruteforce.argtypes = [C.POINTER(OrScene), C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
         _lib.or_render.argtypes = [C.POINTER(OrScene), C.POINTER(OrCamera), C.POINTER(OrConfig), C.c_void_p, C.c_void_p,
                                    C.c_int, C.POINTER(OrCounters)]
+        _lib.or_sample_environment.argtypes = [C.POINTER(OrScene), C.c_void_p, C.c_int64, C.c_void_p]
+        _lib.or_equirect_to_cube.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
         _lib.or_raygen.argtypes = [C.POINTER(OrCamera), C.POINTER(OrConfig), C.c_float, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
     return _lib
 
@@ -155,7 +158,20 @@ class Oracle:
         s.lights, s.n_lights = _p(self.lights), self.lights.shape[0]
         s.total_light_area = float(scene.total_light_area)
         s.env_color = (C.c_float * 3)(*scene.env_color)
+        cube = getattr(scene, "env_cubemap", None)
+        if cube is not None:
+            self.env_faces = np.ascontiguousarray(cube, dtype=np.float32)
+            assert self.env_faces.shape[0] == 6 and self.env_faces.shape[1] == self.env_faces.shape[2]
+            s.env_faces, s.env_size = _p(self.env_faces), self.env_faces.shape[1]
+        else:
+            s.env_faces, s.env_size = None, 0
         self.s = s
+
+    def sample_environment(self, dirs):
+        dirs = np.ascontiguousarray(dirs, dtype=np.float32)
+        out = np.zeros((dirs.shape[0], 3), dtype=np.float32)
+        self.l.or_sample_environment(C.byref(self.s), _p(dirs), C.c_int64(dirs.shape[0]), _p(out))
+        return out
 
     def trace_closest(self, rays, n_threads=0):
         rays = np.ascontiguousarray(rays, dtype=np.float32)
@@ -237,6 +253,47 @@ def tonemap(rgb_sum, num_samples):
 
 
 # ---------------------------------------------------------------- tinyobjloader (the reference's .obj parser), compiled in place
+def equirect_to_cube(rgba, size):
+    """LoadEnvironmnet's .hdr branch (Renderer.cpp:262-312) on the CPU: (h, w, 4) float32 -> (6, size, size, 4)."""
+    rgba = np.ascontiguousarray(rgba, dtype=np.float32)
+    out = np.zeros((6, size, size, 4), dtype=np.float32)
+    lib().or_equirect_to_cube(_p(rgba), rgba.shape[1], rgba.shape[0], size, _p(out))
+    return out
+
+
+STBI_SO = os.path.join(_HERE, "_ref", "libref_stbi.so")
+
+
+def have_stbi():
+    return os.path.exists(STBI_SO)
+
+
+def ref_stbi_loadf(path):
+    """stbi_loadf(path, &w, &h, &c, 4) of the stb_image vendored in the reference's SOIL2 -> (h, w, 4) float32."""
+    l = C.CDLL(STBI_SO)
+    w, h, p = C.c_int(), C.c_int(), C.POINTER(C.c_float)()
+    l.ref_stbi_loadf.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    l.ref_stbi_free.argtypes = [C.c_void_p]
+    if l.ref_stbi_loadf(path.encode(), C.byref(w), C.byref(h), C.byref(p)) != 0:
+        return None
+    out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
+    l.ref_stbi_free(p)
+    return out
+
+
+def ref_stbi_load(path):
+    """stbi_load(path, &w, &h, &c, 4) (what SOIL_load_image(.., SOIL_LOAD_RGBA) yields) -> (h, w, 4) uint8."""
+    l = C.CDLL(STBI_SO)
+    w, h, p = C.c_int(), C.c_int(), C.POINTER(C.c_uint8)()
+    l.ref_stbi_load.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    l.ref_stbi_free.argtypes = [C.c_void_p]
+    if l.ref_stbi_load(path.encode(), C.byref(w), C.byref(h), C.byref(p)) != 0:
+        return None
+    out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
+    l.ref_stbi_free(p)
+    return out
+
+
 TINYOBJ_SO = os.path.join(_HERE, "_ref", "libref_tinyobj.so")
 
 

@@ -244,6 +244,42 @@ void sample_texture(const OrTexture& t, float u, float v, float out[4]) {
     }
 }
 
+// GL_LINEAR + CLAMP_TO_EDGE lookup in a w x h RGBA32F image, float weights
+void sample_clamped(const float* img, int w, int h, float u, float v, float out[4]) {
+    float x = u * (float)w - 0.5f, y = v * (float)h - 0.5f;
+    float fx = floorf(x), fy = floorf(y);
+    float ax = x - fx, ay = y - fy;
+    auto clampi = [](int i, int n) { return i < 0 ? 0 : (i > n - 1 ? n - 1 : i); };
+    int x0 = clampi((int)fx, w), x1 = clampi((int)fx + 1, w);
+    int y0 = clampi((int)fy, h), y1 = clampi((int)fy + 1, h);
+    for (int c = 0; c < 4; c++) {
+        float a = img[4 * ((size_t)y0 * w + x0) + c], b = img[4 * ((size_t)y0 * w + x1) + c];
+        float d = img[4 * ((size_t)y1 * w + x0) + c], e = img[4 * ((size_t)y1 * w + x1) + c];
+        out[c] = mixf(mixf(a, b, ax), mixf(d, e, ax), ay);
+    }
+}
+
+// texture(samplerCube(fbu(materialInstance[0].xy)), ray.direction).xyz, Iterative.comp:251. OpenGL 4.3 core, 8.13
+// "Cube Map Texture Selection", table 8.19:  major axis  target  sc   tc   ma
+//                                              +rx        +X     -rz  -ry  rx      -rx  -X  +rz  -ry  rx
+//                                              +ry        +Y     +rx  +rz  ry      -ry  -Y  +rx  -rz  ry
+//                                              +rz        +Z     +rx  -ry  rz      -rz  -Z  -rx  -ry  rz
+// s = (sc/|ma| + 1)/2, t = (tc/|ma| + 1)/2; then an ordinary 2-D lookup in that face with the cubemap's sampler
+// state (LINEAR, CLAMP_TO_EDGE: Renderer.cpp:318-322; GL_TEXTURE_CUBE_MAP_SEAMLESS is never enabled). Ties between
+// axes are implementation-defined in GL; here x wins over y wins over z.
+V3 sample_environment(const OrScene& s, V3 d) {
+    if (s.env_size == 0) return v3(s.env_color[0], s.env_color[1], s.env_color[2]);
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    int face; float sc, tc, ma;
+    if (ax >= ay && ax >= az) { face = d.x > 0.0f ? 0 : 1; ma = ax; sc = d.x > 0.0f ? -d.z : d.z; tc = -d.y; }
+    else if (ay >= az)        { face = d.y > 0.0f ? 2 : 3; ma = ay; sc = d.x; tc = d.y > 0.0f ? d.z : -d.z; }
+    else                      { face = d.z > 0.0f ? 4 : 5; ma = az; sc = d.z > 0.0f ? d.x : -d.x; tc = -d.y; }
+    float u = 0.5f * (sc / ma + 1.0f), v = 0.5f * (tc / ma + 1.0f);
+    float out[4];
+    sample_clamped(s.env_faces + 4 * (size_t)face * s.env_size * s.env_size, s.env_size, s.env_size, u, v, out);
+    return v3(out[0], out[1], out[2]);
+}
+
 // ConstructMaterialInstance, Material.glsl:39-54
 Material make_material(const OrScene& s, uint32_t matId, float tu, float tv) {
     const float* m = s.materials + 12 * (size_t)(matId >> 1);
@@ -505,7 +541,7 @@ void trace_path(const OrScene& s, const OrCamera& cam, const OrConfig& cfg, int 
         bool miss = !closest_hit(s, p.ray, hit, cnt);
         if (miss) {
             // Iterative.comp:251-255,260-265: sky radiance is NOT MIS-weighted (throughput as is)
-            p.contribution = p.contribution + p.throughput * ld3(s.env_color);
+            p.contribution = p.contribution + p.throughput * sample_environment(s, p.ray.direction);
             break;
         }
         // GetInterpolatedVertex, Geometry.glsl:315-337 + Iterative.comp:236-240
@@ -615,6 +651,43 @@ void or_tonemap(const float rgb_sum[3], int num_samples, float out_rgb[3]) {
         color /= white;
         out_rgb[c] = powf(color, 1.0f / 2.2f);
     }
+}
+
+void or_sample_environment(const OrScene* s, const float* dirs, int64_t n, float* rgb) {
+    for (int64_t i = 0; i < n; i++) {
+        V3 c = sample_environment(*s, ld3(dirs + 3 * i));
+        rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+    }
+}
+
+// LoadEnvironmnet, .hdr branch (Renderer.cpp:262-312). Per face i the reference rasterises a unit cube with
+// captureProjection = perspective(90 deg, 1, 0.1, 10) and captureViews[i] = lookAt(0, centre_i, up_i) (:286-294);
+// EquirectangularConverter.vert hands the fragment sampleCoords = -position, the fragment shader
+// (EquirectangularConverter.frag:9-19) reads hdrTex at (atan(v.z, v.x), asin(v.y)) * (0.1591, 0.3183) + 0.5 of the
+// normalised vector. The fragment at window (px + .5, py + .5) sees the cube point f + nx*s + ny*u with the lookAt basis
+// s = normalize(cross(f, up)), u = cross(s, f) (glm::lookAtRH) and nx = (px + .5)/size*2 - 1; it lands in texel
+// (px, py) of face i. hdrTex: GL_LINEAR, CLAMP_TO_EDGE (:269-272), row 0 of the stbi image at t = 0. The cubemap's
+// storage is RGB32F (:282): alpha reads back as 1.
+void or_equirect_to_cube(const float* rgba, int width, int height, int size, float* faces) {
+    const float centre[6][3] = {{1, 0, 0}, {-1, 0, 0}, {0, 1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}};
+    const float upv[6][3] = {{0, -1, 0}, {0, -1, 0}, {0, 0, 1}, {0, 0, -1}, {0, -1, 0}, {0, -1, 0}};
+    parallel_for((int64_t)6 * size, 0, [&](int, int64_t b, int64_t e) {
+        for (int64_t row = b; row < e; row++) {
+            int face = (int)(row / size), py = (int)(row % size);
+            V3 f = ld3(centre[face]), up = ld3(upv[face]);
+            V3 sv = cross(f, up), uv = cross(sv, f);
+            for (int px = 0; px < size; px++) {
+                float nx = ((float)px + 0.5f) / (float)size * 2.0f - 1.0f, ny = ((float)py + 0.5f) / (float)size * 2.0f - 1.0f;
+                V3 p = f + sv * nx + uv * ny;
+                V3 d = normalize(-p);
+                float tu = atan2f(d.z, d.x) * 0.1591f + 0.5f, tv = asinf(d.y) * 0.3183f + 0.5f;
+                float out[4];
+                sample_clamped(rgba, width, height, tu, tv, out);
+                float* o = faces + 4 * (((size_t)face * size + py) * size + px);
+                o[0] = out[0]; o[1] = out[1]; o[2] = out[2]; o[3] = 1.0f;
+            }
+        }
+    });
 }
 
 static OrCounters g_dummy;

@@ -55,7 +55,9 @@ typedef struct OrScene {
     const float* lights;   /* n_lights x {float cumulativeArea; uint32 triIndex} (Scene.cpp:296-331) */
     int n_lights;
     float total_light_area;
-    float env_color[3];    /* "GENERATE COLOR x" constant cubemap (Renderer.cpp:242-260) */
+    float env_color[3];    /* "GENERATE COLOR x" constant cubemap (Renderer.cpp:242-260), used when env_size == 0 */
+    const float* env_faces; /* cubemap: 6 x env_size x env_size x RGBA32F, +X -X +Y -Y +Z -Z, rows as uploaded */
+    int env_size;
 } OrScene;
 
 /* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
@@ -85,6 +87,10 @@ void or_image_plane(float aspect, float fov, float focus, float aperture, const 
 int or_slab_test(const float bmin[3], const float bmax[3], const float iorg[3], const float idir[3],
                  float tcur, float dist2[2]);                          /* BVH.glsl:379-391 */
 void or_tonemap(const float rgb_sum[3], int num_samples, float out_rgb[3]); /* Present.frag:13-37 */
+/* texture(samplerCube, d).xyz as Iterative.comp:251 samples the sky: GL cube-map face table, GL_LINEAR, CLAMP_TO_EDGE */
+void or_sample_environment(const OrScene* s, const float* dirs, int64_t n, float* rgb);
+/* LoadEnvironmnet's six raster passes over EquirectangularConverter.vert/.frag (Renderer.cpp:262-312), per face texel */
+void or_equirect_to_cube(const float* rgba, int width, int height, int size, float* faces);
 
 /* ---- fixed ray batches: rays[n][8] = {o.xyz, tmin(ignored), d.xyz, tmax} ---- */
 /* hits[n][4] = {t, u, v, triId as int bits}; miss: t = tmax given, triId = -1. BVH.glsl:634-767 */

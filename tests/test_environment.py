@@ -1,0 +1,318 @@
+"""Environment maps: LoadEnvironmnet (Renderer.cpp:236-323), the miss-branch cubemap lookup
+(Iterative.comp:251), the Radiance .hdr reader behind stbi_loadf, the equirect -> cubemap conversion.
+
+CPU part: own .hdr reader against an independent numpy decode, the committed stb_image result and (when oracle/_ref is
+built) stb_image itself; the oracle's cube lookup and conversion against hand-derived OpenGL conventions.
+GPU part (-m gpu): device conversion and device render against the oracle."""
+import copy
+import os
+import struct
+import numpy as np
+import pytest
+
+import oracle
+from gpupathtracer_b200 import api
+from common import GOLDEN, get_scene, make_camera, rel_mse
+
+ENV = os.path.join(GOLDEN, "env")
+
+
+# ------------------------------------------------------------------------------------------------ .hdr writer (test side)
+def _rle_plane(vals):
+    """One byte plane of a scanline in Radiance's new RLE: runs (128+n, value) for n >= 3 equal bytes, dumps otherwise."""
+    out, i, n = bytearray(), 0, len(vals)
+    while i < n:
+        run = 1
+        while i + run < n and run < 127 and vals[i + run] == vals[i]:
+            run += 1
+        if run >= 3:
+            out += bytes([128 + run, vals[i]]); i += run
+            continue
+        j = i
+        while j < n and j - i < 128:
+            r = 1
+            while j + r < n and r < 3 and vals[j + r] == vals[j]:
+                r += 1
+            if r >= 3:
+                break
+            j += 1
+        out += bytes([j - i]) + bytes(vals[i:j]); i = j
+    return bytes(out)
+
+
+def write_hdr(path, rgbe, rle=True, signature=b"#?RADIANCE", extra_header=(b"EXPOSURE=1.0",)):
+    h, w, _ = rgbe.shape
+    with open(path, "wb") as f:
+        f.write(signature + b"\n")
+        for line in extra_header:
+            f.write(line + b"\n")
+        f.write(b"FORMAT=32-bit_rle_rgbe\n\n")
+        f.write(b"-Y %d +X %d\n" % (h, w))
+        for j in range(h):
+            if rle and 8 <= w < 32768:
+                f.write(bytes([2, 2, w >> 8, w & 255]))
+                for k in range(4):
+                    f.write(_rle_plane(list(int(v) for v in rgbe[j, :, k])))
+            else:
+                f.write(rgbe[j].astype(np.uint8).tobytes())
+
+
+def decode_rgbe(rgbe):
+    """byte * 2^(e - 136), e == 0 -> 0, alpha 1 (stbi__hdr_convert)."""
+    e = rgbe[..., 3].astype(np.int32)
+    scale = np.where(e != 0, np.ldexp(np.float32(1.0), e - 136), np.float32(0.0)).astype(np.float32)
+    out = np.ones(rgbe.shape[:2] + (4,), np.float32)
+    out[..., :3] = rgbe[..., :3].astype(np.float32) * scale[..., None]
+    return out
+
+
+def random_rgbe(h, w, seed):
+    rng = np.random.default_rng(seed)
+    img = rng.integers(0, 256, size=(h, w, 4), dtype=np.uint8)
+    img[..., 3] = rng.integers(120, 140, size=(h, w), dtype=np.uint8)
+    img[:, : w // 3, :] = img[:, :1, :]                 # long runs
+    img[h // 2, w // 2:, 3] = 0                          # zero exponent -> black
+    img[..., 0] |= 128                                   # a valid normalised pixel can never start with (2, 2)
+    return img
+
+
+@pytest.mark.parametrize("w,h,rle,sig", [(16, 6, True, b"#?RADIANCE"), (40, 5, True, b"#?RGBE"), (200, 3, True, b"#?RADIANCE"),
+                                         (5, 7, True, b"#?RADIANCE"), (24, 4, False, b"#?RADIANCE")])
+def test_hdr_reader(tmp_path, w, h, rle, sig):
+    rgbe = random_rgbe(h, w, seed=w * 31 + h)
+    p = str(tmp_path / "t.hdr")
+    write_hdr(p, rgbe, rle=rle, signature=sig)
+    got = api.load_hdr(p)
+    assert got.shape == (h, w, 4)
+    assert np.array_equal(got, decode_rgbe(rgbe))
+    if oracle.have_stbi():
+        assert np.array_equal(got, oracle.ref_stbi_loadf(p))
+
+
+def test_hdr_reader_committed_fixture():
+    """tests/golden/env/sky.hdr + the stbi_loadf result recorded from the reference's stb_image (tools/make_env_golden.py)."""
+    got = api.load_hdr(os.path.join(ENV, "sky.hdr"))
+    want = np.load(os.path.join(ENV, "sky_stbi.npy"))
+    assert got.shape == want.shape and np.array_equal(got, want)
+
+
+def test_hdr_reader_refuses_what_stb_refuses(tmp_path):
+    bad = tmp_path / "bad.hdr"
+    bad.write_bytes(b"#?RADIANCE\nFORMAT=32-bit_rle_xyze\n\n-Y 2 +X 2\n" + bytes(16))
+    with pytest.raises(api.PtError):
+        api.load_hdr(str(bad))
+    flipped = tmp_path / "flipped.hdr"
+    flipped.write_bytes(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n+Y 2 +X 2\n" + bytes(16))
+    with pytest.raises(api.PtError):
+        api.load_hdr(str(flipped))
+    not_hdr = tmp_path / "x.hdr"
+    not_hdr.write_bytes(b"P6\n1 1\n255\n\x00\x00\x00")
+    with pytest.raises(api.PtError):
+        api.load_hdr(str(not_hdr))
+    if oracle.have_stbi():
+        assert oracle.ref_stbi_loadf(str(bad)) is None and oracle.ref_stbi_loadf(str(flipped)) is None
+
+
+# ------------------------------------------------------------------------------------------------ cube lookup (oracle)
+def _coded_cube(n):
+    """texel (face, y, x) = (face, x, y, 1): a bilinear lookup returns the continuous texel coordinates."""
+    f = np.zeros((6, n, n, 4), np.float32)
+    for face in range(6):
+        f[face, :, :, 0] = face
+        f[face, :, :, 1] = np.arange(n, dtype=np.float32)[None, :]
+        f[face, :, :, 2] = np.arange(n, dtype=np.float32)[:, None]
+    f[..., 3] = 1.0
+    return f
+
+
+def _env_oracle(cube):
+    s = copy.copy(get_scene("soup_small"))
+    s.env_cubemap = cube
+    return oracle.Oracle(s), s
+
+
+def test_cube_lookup_follows_the_gl_face_table():
+    n = 16
+    o, _ = _env_oracle(_coded_cube(n))
+    # (direction, face, sc, tc, ma) straight from OpenGL 4.3 table 8.19
+    cases = [((1.0, 0.5, 0.25), 0, -0.25, -0.5, 1.0), ((-2.0, 0.5, 0.25), 1, 0.25, -0.5, 2.0),
+             ((0.3, 1.5, -0.6), 2, 0.3, -0.6, 1.5), ((0.3, -1.5, -0.6), 3, 0.3, 0.6, 1.5),
+             ((0.2, -0.7, 4.0), 4, 0.2, 0.7, 4.0), ((0.2, -0.7, -4.0), 5, -0.2, 0.7, 4.0)]
+    dirs = np.array([c[0] for c in cases], np.float32)
+    got = o.sample_environment(dirs)
+    for (d, face, sc, tc, ma), g in zip(cases, got):
+        s, t = 0.5 * (sc / ma + 1.0), 0.5 * (tc / ma + 1.0)
+        assert g[0] == face
+        assert abs(g[1] - (s * n - 0.5)) < 1e-4 and abs(g[2] - (t * n - 0.5)) < 1e-4
+
+
+def test_cube_lookup_clamps_at_face_edges_and_is_scale_invariant():
+    n = 8
+    o, _ = _env_oracle(_coded_cube(n))
+    got = o.sample_environment(np.array([(1.0, 0.999999, 0.0), (1.0, -0.999999, 0.0), (3.0, 0.3, -0.9), (30.0, 3.0, -9.0)], np.float32))
+    assert got[0][0] == 0 and abs(got[0][2] - 0.0) < 1e-3          # tc = -ry -> t near 0: clamped to row 0, not wrapped
+    assert got[1][0] == 0 and abs(got[1][2] - (n - 1)) < 1e-3
+    np.testing.assert_allclose(got[2], got[3], rtol=0, atol=1e-5)
+
+
+def test_constant_colour_environment_is_unchanged():
+    s = get_scene("soup_small")
+    got = oracle.Oracle(s).sample_environment(np.array([(0.0, 1.0, 0.0), (0.3, -0.2, 0.9)], np.float32))
+    assert np.array_equal(got, np.array([s.env_color, s.env_color], np.float32))
+
+
+# ------------------------------------------------------------------------------------------------ equirect -> cube (oracle)
+def _smooth_equirect(w, h):
+    """HDR-ish image that is an analytic function of the texture coordinate."""
+    u = (np.arange(w, dtype=np.float64) + 0.5) / w
+    v = (np.arange(h, dtype=np.float64) + 0.5) / h
+    U, V = np.meshgrid(u, v)
+    img = np.ones((h, w, 4), np.float32)
+    img[..., 0] = 2.0 + np.sin(2 * np.pi * U) * np.cos(np.pi * V)
+    img[..., 1] = 0.5 + V
+    img[..., 2] = 8.0 * np.exp(-20.0 * ((U - 0.25) ** 2 + (V - 0.7) ** 2))
+    return img
+
+
+def _glm_look_at(center, up):
+    f = np.array(center, np.float64); f /= np.linalg.norm(f)
+    s = np.cross(f, np.array(up, np.float64)); s /= np.linalg.norm(s)
+    u = np.cross(s, f)
+    m = np.eye(4)
+    m[0, :3], m[1, :3], m[2, :3] = s, u, -f
+    return m
+
+
+def test_equirect_conversion_matches_an_unprojection_of_the_raster_passes():
+    """Independent derivation: build captureProjection / captureViews as matrices (Renderer.cpp:279,286-294), un-project
+    every texel centre to the cube, negate (EquirectangularConverter.vert), evaluate the analytic image there."""
+    w, h, n = 256, 128, 16
+    img = _smooth_equirect(w, h)
+    got = oracle.equirect_to_cube(img, n)
+    assert got.shape == (6, n, n, 4) and np.all(got[..., 3] == 1.0)
+    t = np.tan(np.radians(90.0) / 2)
+    near, far = 0.1, 10.0
+    proj = np.array([[1 / t, 0, 0, 0], [0, 1 / t, 0, 0], [0, 0, -(far + near) / (far - near), -2 * far * near / (far - near)], [0, 0, -1, 0]])
+    views = [((1, 0, 0), (0, -1, 0)), ((-1, 0, 0), (0, -1, 0)), ((0, 1, 0), (0, 0, 1)), ((0, -1, 0), (0, 0, -1)),
+             ((0, 0, 1), (0, -1, 0)), ((0, 0, -1), (0, -1, 0))]
+    worst = 0.0
+    for face, (c, up) in enumerate(views):
+        inv = np.linalg.inv(proj @ _glm_look_at(c, up))
+        for py in range(n):
+            for px in range(n):
+                ndc = np.array([(px + 0.5) / n * 2 - 1, (py + 0.5) / n * 2 - 1, 0.0, 1.0])
+                p = inv @ ndc; p = p[:3] / p[3]                       # a point on the view ray through the texel
+                d = -p / np.linalg.norm(p)
+                U = np.arctan2(d[2], d[0]) * 0.1591 + 0.5
+                V = np.arcsin(d[1]) * 0.3183 + 0.5
+                want = (2.0 + np.sin(2 * np.pi * U) * np.cos(np.pi * V), 0.5 + V,
+                        8.0 * np.exp(-20.0 * ((U - 0.25) ** 2 + (V - 0.7) ** 2)))
+                worst = max(worst, float(np.max(np.abs(got[face, py, px, :3] - want))))
+    assert worst < 2e-2, worst           # bilinear reconstruction error of the 256x128 image, not a convention error
+
+
+def test_cube_lookup_of_converted_map_returns_the_negated_direction():
+    """Consequence of sampleCoords = -position: texture(cube, r) ~ equirect(-r)."""
+    w, h, n = 512, 256, 128
+    img = _smooth_equirect(w, h)
+    cube = oracle.equirect_to_cube(img, n)
+    o, _ = _env_oracle(cube)
+    rng = np.random.default_rng(5)
+    d = rng.normal(size=(2000, 3)); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    got = o.sample_environment(d.astype(np.float32))
+    m = -d
+    U = np.arctan2(m[:, 2], m[:, 0]) * 0.1591 + 0.5
+    V = np.arcsin(m[:, 1]) * 0.3183 + 0.5
+    seam = np.abs(U - 0.5) > 0.47                                     # atan wrap: CLAMP_TO_EDGE smears the seam texels
+    want_g = 0.5 + V
+    assert np.max(np.abs(got[~seam, 1] - want_g[~seam])) < 5e-3
+
+
+# ------------------------------------------------------------------------------------------------ device (-m gpu)
+def _noise_equirect(w, h, seed):
+    rng = np.random.default_rng(seed)
+    img = np.ones((h, w, 4), np.float32)
+    img[..., :3] = rng.gamma(0.5, 2.0, size=(h, w, 3)).astype(np.float32)
+    return img
+
+
+@pytest.mark.gpu
+def test_device_conversion_matches_oracle():
+    from gpupathtracer_b200 import Renderer
+    s = get_scene("soup_small")
+    r = Renderer().Initialize(64, 64, s, seed=1)
+    for (w, h, n, img) in [(64, 32, 32, _noise_equirect(64, 32, 1)), (256, 128, 64, _smooth_equirect(256, 128)),
+                           (7, 5, 9, _noise_equirect(7, 5, 2))]:
+        r.SetEnvironmentEquirect(img, cube_size=n)
+        got = r.GetEnvironment()
+        want = oracle.equirect_to_cube(img, n)
+        assert got.shape == want.shape
+        # atan2f / asinf differ by <= 2 ulp between CUDA and glibc: texel coordinate off by ~1e-5, times local contrast
+        tol = 2e-4 * float(img[..., :3].max())
+        assert np.max(np.abs(got - want)) < tol
+        assert np.mean(got == want) > 0.5
+    r.SetEnvironmentCubemap(want)
+    assert np.array_equal(r.GetEnvironment(), want)
+    r.CleanUp()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,depth", [("soup_small", 5), ("cornell_small", 4)])
+def test_frames_with_cubemap_match_oracle(name, depth):
+    from gpupathtracer_b200 import Renderer, make_rng_table
+    s = copy.copy(get_scene(name))
+    s.env_cubemap = oracle.equirect_to_cube(_smooth_equirect(128, 64), 32)
+    w, h, frames = 64, 64, 4
+    cam = make_camera(s.data, w, h)
+    rng = make_rng_table(w * h, 21)
+    r = Renderer().Initialize(w, h, s, max_depth=depth, rng_state=rng)
+    r.RenderFrame(cam, frames)
+    got = r.DownloadAccum()
+    r.CleanUp()
+    rng_o = rng.copy()
+    want = np.zeros((h, w, 4), np.float32)
+    oracle.Oracle(s).render(cam.as_array(), w, h, rng_o, want, n_frames=frames, max_depth=depth)
+    fin = np.isfinite(want[..., :3]).all(axis=2) & np.isfinite(got[..., :3]).all(axis=2)
+    close = np.isclose(got[..., :3], want[..., :3], rtol=1e-4, atol=1e-6).all(axis=2)
+    frac = float((close & fin).sum()) / float(fin.sum())
+    assert frac > 0.995, f"only {frac:.5f} of pixels agree to 1e-4"
+    assert rel_mse(got[..., :3], want[..., :3]) < 1e-3
+    # and the environment really is what lights the image: a black map gives a different picture
+    s2 = copy.copy(s); s2.env_cubemap = np.zeros_like(s.env_cubemap)
+    dark = np.zeros((h, w, 4), np.float32)
+    oracle.Oracle(s2).render(cam.as_array(), w, h, rng.copy(), dark, n_frames=frames, max_depth=depth)
+    if name == "soup_small":
+        assert float(np.nansum(want[..., :3])) > 1.5 * float(np.nansum(dark[..., :3]))
+
+
+@pytest.mark.gpu
+def test_load_environment_strings(tmp_path):
+    from gpupathtracer_b200 import Renderer
+    s = get_scene("soup_small")
+    r = Renderer().Initialize(64, 64, s, seed=1)
+    # six-face list (TextureCubemap::LoadTexture): comments skipped, paths relative to the list, byte / 255
+    rng = np.random.default_rng(3)
+    faces = rng.integers(0, 256, size=(6, 4, 4, 3), dtype=np.uint8)
+    lines = ["# +X -X +Y -Y +Z -Z"]
+    for i in range(6):
+        with open(tmp_path / f"f{i}.ppm", "wb") as f:
+            f.write(b"P6\n4 4\n255\n" + faces[i].tobytes())
+        lines.append(f"f{i}.ppm")
+    (tmp_path / "sky.txt").write_text("\n".join(lines) + "\n")
+    r.LoadEnvironment(str(tmp_path / "sky.txt"))
+    got = r.GetEnvironment()
+    assert got.shape == (6, 4, 4, 4)
+    assert np.array_equal(got[..., :3], faces.astype(np.float32) / np.float32(255.0)) and np.all(got[..., 3] == 1.0)
+    # .hdr -> 1024^2 cubemap, as the reference
+    r.LoadEnvironment(os.path.join(ENV, "sky.hdr"))
+    got = r.GetEnvironment()
+    assert got.shape == (6, 1024, 1024, 4)
+    want = oracle.equirect_to_cube(np.load(os.path.join(ENV, "sky_stbi.npy")), 1024)
+    assert np.max(np.abs(got - want)) < 2e-4 * float(want.max())
+    r.LoadEnvironment("GENERATE COLOR BLACK")
+    assert r.GetEnvironment() is None
+    with pytest.raises(api.PtError):
+        r.LoadEnvironment("Textures/sky.hdr")       # first character in "GENERATE": a command, as in the reference
+    with pytest.raises(api.PtError):
+        r.LoadEnvironment(str(tmp_path / "missing.txt"))
+    r.CleanUp()
