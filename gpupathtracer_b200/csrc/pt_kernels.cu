@@ -419,6 +419,7 @@ __global__ void k_equirect_to_cube(const float4* __restrict__ src, int w, int h,
     float nx = ((float)px + 0.5f) / (float)n * 2.0f - 1.0f, ny = ((float)py + 0.5f) / (float)n * 2.0f - 1.0f;
     V3 p = f + sv * nx + uv * ny;
     V3 d = normalize(-p);
+    if (d.z == 0.0f) d.z = 0.0f;      // -0 -> +0: the seam column of odd-sized faces must not depend on atan2f(-0, x < 0)
     float tu = atan2f(d.z, d.x) * 0.1591f + 0.5f, tv = asinf(d.y) * 0.3183f + 0.5f;
     float x = tu * (float)w - 0.5f, y = tv * (float)h - 0.5f;
     float fx = floorf(x), fy = floorf(y);

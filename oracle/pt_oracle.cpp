@@ -680,6 +680,7 @@ void or_equirect_to_cube(const float* rgba, int width, int height, int size, flo
                 float nx = ((float)px + 0.5f) / (float)size * 2.0f - 1.0f, ny = ((float)py + 0.5f) / (float)size * 2.0f - 1.0f;
                 V3 p = f + sv * nx + uv * ny;
                 V3 d = normalize(-p);
+                if (d.z == 0.0f) d.z = 0.0f;      // -0 -> +0, see k_equirect_to_cube (GLSL leaves atan(-0, x < 0) open)
                 float tu = atan2f(d.z, d.x) * 0.1591f + 0.5f, tv = asinf(d.y) * 0.3183f + 0.5f;
                 float out[4];
                 sample_clamped(rgba, width, height, tu, tv, out);
