@@ -71,6 +71,7 @@ SYMBOLS = [
     ("pt_environment_size", C.c_int32, [_P]),
     ("pt_download_environment", C.c_int, [_P, _P]),
     ("pt_load_environment", C.c_int, [_P, C.c_char_p]),
+    ("pt_image_save_png", C.c_int, [C.c_char_p, C.c_int32, C.c_int32, _P]),
     ("pt_image_load_hdr", C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(_F)]),
     ("pt_set_bvh", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
     ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
@@ -246,6 +247,13 @@ def load_image(path):
     out = np.ctypeslib.as_array(p, shape=(h.value, w.value, 4)).copy()
     lib.pt_free(p)
     return out
+
+
+def save_png(path, rgb8):
+    """(h, w, 3) uint8, row 0 on top -> 8-bit RGB PNG (the format of Renderer::SaveScreenshot)."""
+    rgb8 = np.ascontiguousarray(rgb8, dtype=np.uint8)
+    assert rgb8.ndim == 3 and rgb8.shape[2] == 3
+    _check(load_library().pt_image_save_png(path.encode(), rgb8.shape[1], rgb8.shape[0], _ptr(rgb8)))
 
 
 def load_hdr(path):

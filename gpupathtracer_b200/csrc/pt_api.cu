@@ -887,7 +887,13 @@ int pt_save_screenshot(pt_context* c, const char* path) {
         std::vector<uint8_t> img(npx * 3);
         int rc = pt_resolve(c, c->num_samples, nullptr, img.data());
         if (rc != PT_OK) return rc;
-        if (!write_ppm(path, c->cfg.width, c->cfg.height, img.data())) return fail(PT_ERR_IO, "cannot write %s", path);
+        if (p.size() > 4 && p.substr(p.size() - 4) == ".png") {
+            // the reference's format (SOIL_SAVE_TYPE_PNG); image row 0 is the bottom row of its GL framebuffer, PNG is top-down
+            std::vector<uint8_t> flip(npx * 3);
+            const size_t row = 3 * (size_t)c->cfg.width;
+            for (int y = 0; y < c->cfg.height; y++) memcpy(&flip[(size_t)y * row], &img[(size_t)(c->cfg.height - 1 - y) * row], row);
+            if (!write_png_rgb8(path, c->cfg.width, c->cfg.height, flip.data())) return fail(PT_ERR_IO, "cannot write %s", path);
+        } else if (!write_ppm(path, c->cfg.width, c->cfg.height, img.data())) return fail(PT_ERR_IO, "cannot write %s", path);
     }
     return PT_OK;
 }

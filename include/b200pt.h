@@ -184,8 +184,10 @@ const char* pt_scene_file_texture_path(const pt_scene_file* sf, int32_t material
 int32_t pt_scene_file_num_shapes(const pt_scene_file* sf);
 const char* pt_scene_file_warnings(const pt_scene_file* sf);
 /* map_Kd image -> RGBA32F texels (byte / 255, rows in file order; Texture2D::LoadTexture, Texture.cpp:146-156, decodes
- * through SOIL2 -- here: .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
+ * through SOIL2 -- here: .png (all colour types / depths / Adam7, as stb_image reads them), .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
 int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgba);
+/* 8-bit RGB PNG, rows top-down (filter 0, stored deflate blocks): the format of Renderer::SaveScreenshot (Renderer.cpp:698). */
+int pt_image_save_png(const char* path, int32_t width, int32_t height, const uint8_t* rgb_top_down);
 /* Radiance .hdr -> RGBA32F as stbi_loadf(path, .., 4) returns it (Renderer.cpp:265): byte * 2^(e-136), alpha 1, rows in
  * file order. *rgba is malloc()ed, release with pt_free. */
 int pt_image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba);
@@ -232,7 +234,7 @@ int pt_resolve(pt_context* ctx, uint32_t num_samples, float* rgb_f32_or_null, ui
  * so the next RenderFrame overlaps the transfer. The image is complete after pt_synchronize. Device-side the target is
  * double-buffered: at most two presents are in flight. */
 int pt_present_async(pt_context* ctx, uint32_t num_samples, uint8_t* host_rgb_u8);
-int pt_save_screenshot(pt_context* ctx, const char* path);         /* Renderer::SaveScreenshot (Renderer.cpp:697-705); .ppm/.pfm */
+int pt_save_screenshot(pt_context* ctx, const char* path);         /* Renderer::SaveScreenshot (Renderer.cpp:697-705); .png (as the reference) / .ppm / .pfm by extension */
 
 /* ---- fixed ray batches (parity + microbenchmark entry points) ----
  * rays: n x 8 floats {o.xyz, unused, d.xyz, tmax}; hits: n x {t, u, v, triId(int32)}; miss = {tmax, 0, 0, -1}.

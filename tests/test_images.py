@@ -1,0 +1,226 @@
+"""PNG reader (map_Kd textures, cube faces: SOIL_load_image(.., SOIL_LOAD_RGBA) = stbi_load(.., 4), Texture.cpp:146-156,:262)
+and PNG writer (Renderer::SaveScreenshot, Renderer.cpp:697-705). CPU only.
+
+The PNG files are produced here from numpy arrays by a small encoder (zlib from the standard library, every filter type,
+Adam7), so the expected pixels are known without any decoder; when oracle/_ref is built the reference's own stb_image is a
+second, byte-for-byte witness, and its output for the committed fixture travels as tests/golden/png/*.npy."""
+import os
+import struct
+import zlib
+import numpy as np
+import pytest
+
+import oracle
+from gpupathtracer_b200 import api
+from common import GOLDEN
+
+PNG = os.path.join(GOLDEN, "png")
+
+
+# ------------------------------------------------------------------------------------------------ test-side PNG encoder
+def _chunk(kind, data):
+    return struct.pack(">I", len(data)) + kind + data + struct.pack(">I", zlib.crc32(kind + data) & 0xffffffff)
+
+
+def _pack_rows(samples, depth):
+    """samples (h, w, c) of unsigned ints at `depth` bits -> list of bytes rows."""
+    h, w, c = samples.shape
+    rows = []
+    for y in range(h):
+        flat = samples[y].reshape(-1)
+        if depth == 16:
+            rows.append(flat.astype(">u2").tobytes())
+        elif depth == 8:
+            rows.append(flat.astype(np.uint8).tobytes())
+        else:
+            bits = np.zeros(((flat.size * depth + 7) // 8) * 8, np.uint8)
+            for k in range(depth):
+                bits[np.arange(flat.size) * depth + k] = (flat >> (depth - 1 - k)) & 1
+            rows.append(np.packbits(bits).tobytes())
+    return rows
+
+
+def _filter_rows(rows, bpp, kinds):
+    out, prev = bytearray(), None
+    for y, row in enumerate(rows):
+        kind = kinds[y % len(kinds)]
+        cur = np.frombuffer(row, np.uint8).astype(np.int32)
+        up = np.frombuffer(prev, np.uint8).astype(np.int32) if prev is not None else np.zeros_like(cur)
+        left = np.concatenate([np.zeros(bpp, np.int32), cur[:-bpp]]) if cur.size > bpp else np.zeros_like(cur)
+        ul = np.concatenate([np.zeros(bpp, np.int32), up[:-bpp]]) if cur.size > bpp else np.zeros_like(cur)
+        if kind == 0:
+            pred = np.zeros_like(cur)
+        elif kind == 1:
+            pred = left
+        elif kind == 2:
+            pred = up
+        elif kind == 3:
+            pred = (left + up) // 2
+        else:
+            p = left + up - ul
+            pa, pb, pc = np.abs(p - left), np.abs(p - up), np.abs(p - ul)
+            pred = np.where((pa <= pb) & (pa <= pc), left, np.where(pb <= pc, up, ul))
+        out.append(kind)
+        out += ((cur - pred) & 255).astype(np.uint8).tobytes()
+        prev = row
+    return bytes(out)
+
+
+def write_png(path, samples, color, depth, palette=None, trns=None, interlace=False, kinds=(0, 1, 2, 3, 4), level=6,
+              idat_split=0, extra=()):
+    h, w, c = samples.shape
+    bpp = max(1, c * depth // 8)
+    body = b""
+    if interlace:
+        xs, ys, dx, dy = (0, 4, 0, 2, 0, 1, 0), (0, 0, 4, 0, 2, 0, 1), (8, 8, 4, 4, 2, 2, 1), (8, 8, 8, 4, 4, 2, 2)
+        for p in range(7):
+            sub = samples[ys[p]::dy[p], xs[p]::dx[p]]
+            if sub.shape[0] and sub.shape[1]:
+                body += _filter_rows(_pack_rows(sub, depth), bpp, kinds)
+    else:
+        body = _filter_rows(_pack_rows(samples, depth), bpp, kinds)
+    z = zlib.compress(body, level)
+    out = b"\x89PNG\r\n\x1a\n" + _chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, depth, color, 0, 0, 1 if interlace else 0))
+    for kind, data in extra:
+        out += _chunk(kind, data)
+    if palette is not None:
+        out += _chunk(b"PLTE", np.asarray(palette, np.uint8).tobytes())
+    if trns is not None:
+        out += _chunk(b"tRNS", trns)
+    if idat_split:
+        for i in range(0, len(z), idat_split):
+            out += _chunk(b"IDAT", z[i:i + idat_split])
+    else:
+        out += _chunk(b"IDAT", z)
+    out += _chunk(b"IEND", b"")
+    with open(path, "wb") as f:
+        f.write(out)
+
+
+def expected_rgba8(samples, color, depth, palette=None, trns=None):
+    h, w, c = samples.shape
+    maxv = (1 << depth) - 1
+
+    def to8(v):
+        return (v >> 8) if depth == 16 else (v if depth == 8 else v * (255 // maxv))
+    out = np.full((h, w, 4), 255, np.uint8)
+    if color == 3:
+        pal = np.asarray(palette, np.uint8).reshape(-1, 3)
+        out[..., :3] = pal[samples[..., 0]]
+        if trns is not None:
+            alpha = np.full(256, 255, np.uint8); alpha[:len(trns)] = np.frombuffer(trns, np.uint8)
+            out[..., 3] = alpha[samples[..., 0]]
+    elif color in (0, 4):
+        out[..., 0] = out[..., 1] = out[..., 2] = to8(samples[..., 0])
+        if color == 4:
+            out[..., 3] = to8(samples[..., 1])
+        elif trns is not None:
+            key = struct.unpack(">H", trns[:2])[0]
+            out[..., 3] = np.where(samples[..., 0] == key, 0, 255)
+    else:
+        out[..., :3] = to8(samples[..., :3])
+        if color == 6:
+            out[..., 3] = to8(samples[..., 3])
+        elif trns is not None:
+            key = np.array(struct.unpack(">HHH", trns[:6]))
+            out[..., 3] = np.where((samples[..., :3] == key).all(axis=2), 0, 255)
+    return out
+
+
+CASES = [  # (name, color, depth, channels, interlace, w, h)
+    ("rgb8", 2, 8, 3, False, 37, 19), ("rgba8", 6, 8, 4, False, 16, 16), ("grey8", 0, 8, 1, False, 33, 9),
+    ("ga8", 4, 8, 2, False, 12, 21), ("rgb16", 2, 16, 3, False, 11, 13), ("rgba16", 6, 16, 4, True, 23, 17),
+    ("grey1", 0, 1, 1, False, 43, 7), ("grey2", 0, 2, 1, True, 21, 11), ("grey4", 0, 4, 1, False, 17, 5),
+    ("grey16", 0, 16, 1, False, 9, 9), ("pal8", 3, 8, 1, False, 31, 14), ("pal4", 3, 4, 1, True, 29, 10),
+    ("pal1", 3, 1, 1, False, 19, 6), ("rgb8_adam7", 2, 8, 3, True, 40, 27), ("rgb8_tiny", 2, 8, 3, True, 1, 1),
+]
+
+
+def _make_case(name, color, depth, ch, w, h):
+    rng = np.random.default_rng(abs(hash(name)) % (2 ** 31) if False else sum(map(ord, name)))
+    samples = rng.integers(0, 1 << depth, size=(h, w, ch), dtype=np.int64)
+    samples[:, : w // 2] = samples[:, :1]              # runs, so that the deflate stream has matches
+    palette = trns = None
+    if color == 3:
+        n = 1 << depth
+        palette = rng.integers(0, 256, size=(n, 3), dtype=np.uint8)
+        trns = bytes(rng.integers(0, 256, size=n // 2 + 1, dtype=np.uint8))
+    elif color == 0 and name in ("grey8", "grey16", "grey4"):
+        trns = struct.pack(">H", int(samples[0, 0, 0]))
+    elif color == 2 and name in ("rgb8", "rgb16"):
+        trns = struct.pack(">HHH", *[int(v) for v in samples[0, 0, :3]])
+    return samples, palette, trns
+
+
+@pytest.mark.parametrize("name,color,depth,ch,interlace,w,h", CASES)
+def test_png_reader(tmp_path, name, color, depth, ch, interlace, w, h):
+    samples, palette, trns = _make_case(name, color, depth, ch, w, h)
+    p = str(tmp_path / f"{name}.png")
+    write_png(p, samples, color, depth, palette=palette, trns=trns, interlace=interlace,
+              idat_split=97 if name in ("rgb8", "pal8") else 0, extra=((b"gAMA", struct.pack(">I", 45455)),))
+    want = expected_rgba8(samples, color, depth, palette, trns)
+    got = api.load_image(p)
+    assert got.shape == (h, w, 4)
+    assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0))
+    if oracle.have_stbi():
+        assert np.array_equal(oracle.ref_stbi_load(p), want)
+
+
+@pytest.mark.parametrize("level", [0, 1, 9])
+def test_png_reader_deflate_block_kinds(tmp_path, level):
+    """level 0 = stored blocks, 1 = mostly fixed/dynamic Huffman with short matches, 9 = dynamic with long matches."""
+    rng = np.random.default_rng(level)
+    samples = np.zeros((64, 300, 3), np.int64)
+    samples[:, :, 0] = np.arange(300)[None, :] % 7 * 30
+    samples[::3] = rng.integers(0, 256, size=samples[::3].shape)
+    p = str(tmp_path / "t.png")
+    write_png(p, samples, 2, 8, level=level, kinds=(4,))
+    assert np.array_equal(api.load_image(p)[..., :3], samples.astype(np.float32) / np.float32(255.0))
+
+
+def test_png_reader_refuses_damaged_files(tmp_path):
+    samples = np.random.default_rng(1).integers(0, 256, size=(8, 8, 3), dtype=np.int64)
+    p = str(tmp_path / "ok.png")
+    write_png(p, samples, 2, 8)
+    data = open(p, "rb").read()
+    for name, blob in [("short.png", data[:len(data) // 2]), ("nosig.png", b"\x89PNX" + data[4:]),
+                       ("noidat.png", data[:33] + _chunk(b"IEND", b""))]:
+        q = tmp_path / name
+        q.write_bytes(blob)
+        with pytest.raises(api.PtError):
+            api.load_image(str(q))
+
+
+def test_png_writer_round_trip(tmp_path):
+    rng = np.random.default_rng(2)
+    for (w, h) in [(1, 1), (5, 3), (300, 200), (1280, 18)]:       # 300x200x3+200 > 65535: several stored blocks
+        img = rng.integers(0, 256, size=(h, w, 3), dtype=np.uint8)
+        p = str(tmp_path / f"w{w}.png")
+        api.save_png(p, img)
+        data = open(p, "rb").read()
+        # independent decode: walk the chunks, check every CRC, inflate with zlib, expect filter byte 0 on every row
+        assert data[:8] == b"\x89PNG\r\n\x1a\n"
+        pos, idat, kinds = 8, b"", []
+        while pos < len(data):
+            n, kind = struct.unpack(">I4s", data[pos:pos + 8])
+            body = data[pos + 8:pos + 8 + n]
+            assert struct.unpack(">I", data[pos + 8 + n:pos + 12 + n])[0] == zlib.crc32(kind + body) & 0xffffffff
+            kinds.append(kind)
+            if kind == b"IHDR":
+                assert struct.unpack(">IIBBBBB", body) == (w, h, 8, 2, 0, 0, 0)
+            if kind == b"IDAT":
+                idat += body
+            pos += 12 + n
+        assert kinds[0] == b"IHDR" and kinds[-1] == b"IEND"
+        raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 3 * w + 1)
+        assert np.all(raw[:, 0] == 0) and np.array_equal(raw[:, 1:].reshape(h, w, 3), img)
+        assert np.array_equal(api.load_image(p)[..., :3], img.astype(np.float32) / np.float32(255.0))
+        if oracle.have_stbi():
+            assert np.array_equal(oracle.ref_stbi_load(p)[..., :3], img)
+
+
+def test_png_committed_fixture():
+    """tests/golden/png/tiles.png (palette, Adam7) with the reference's stb_image result recorded beside it."""
+    got = api.load_image(os.path.join(PNG, "tiles.png"))
+    want = np.load(os.path.join(PNG, "tiles_stbi.npy"))
+    assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0))
