@@ -71,6 +71,8 @@ SYMBOLS = [
     ("pt_environment_size", C.c_int32, [_P]),
     ("pt_download_environment", C.c_int, [_P, _P]),
     ("pt_load_environment", C.c_int, [_P, C.c_char_p]),
+    ("pt_checkpoint_save", C.c_int, [_P, C.c_char_p]),
+    ("pt_checkpoint_load", C.c_int, [_P, C.c_char_p]),
     ("pt_image_save_png", C.c_int, [C.c_char_p, C.c_int32, C.c_int32, _P]),
     ("pt_image_load_hdr", C.c_int, [C.c_char_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(_F)]),
     ("pt_set_bvh", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
@@ -420,6 +422,13 @@ class Renderer:
         self.bvh_stats = stats
         _check(self.lib.pt_seed_rng(ctx, seed))
         return self
+
+    # -- checkpoint / resume (no counterpart in the reference)
+    def SaveCheckpoint(self, path):
+        _check(self.lib.pt_checkpoint_save(self.ctx, path.encode()))
+
+    def LoadCheckpoint(self, path):
+        _check(self.lib.pt_checkpoint_load(self.ctx, path.encode()))
 
     # -- LoadEnvironmnet, Renderer.cpp:236-323
     def SetEnvironmentCubemap(self, faces):

@@ -227,6 +227,12 @@ int pt_synchronize(pt_context* ctx);
 int pt_download_accum(pt_context* ctx, float* rgba);
 void* pt_accum_device_ptr(pt_context* ctx);                        /* for NCCL reduce across ranks (width*height*4 floats) */
 int pt_set_accum_device_ptr(pt_context* ctx, void* dev_rgba);      /* render into caller-owned device memory */
+/* Checkpoint / resume of a long render (no counterpart in the reference): the per-pixel RNG table, the
+ * accumulation buffer and numSamples, with a checksum; written beside `path` and renamed into place. After a load into a
+ * context of the same size and scene, further frames are bit-identical to those of an uninterrupted run. One file per
+ * GPU in a multi-GPU render (each rank owns its RNG table and partial sum). */
+int pt_checkpoint_save(pt_context* ctx, const char* path);
+int pt_checkpoint_load(pt_context* ctx, const char* path);
 /* Renderer::Present (Present.frag:13-37): /numSamples, Uncharted-2, gamma 2.2 -> RGB float and/or 8-bit. */
 int pt_resolve(pt_context* ctx, uint32_t num_samples, float* rgb_f32_or_null, uint8_t* rgb_u8_or_null);
 /* Present without the stall of a swap: the resolve kernel is queued behind the frames rendered so far and its 8-bit image

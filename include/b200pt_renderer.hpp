@@ -90,6 +90,11 @@ public:
     void ResetSamples() { check(pt_reset_samples(ctx_)); }        // Renderer.cpp:687-691
     uint32_t GetNumSamples() { return pt_num_samples(ctx_); }     // Renderer.cpp:693-695
     void SaveScreenshot(const std::string& filename) { check(pt_save_screenshot(ctx_, filename.c_str())); }   // :697-705
+    // beyond the reference: a long render that survives a restart (RNG table + running sum + numSamples)
+    void SaveCheckpoint(const std::string& path) { check(pt_checkpoint_save(ctx_, path.c_str())); }
+    void LoadCheckpoint(const std::string& path) { check(pt_checkpoint_load(ctx_, path.c_str())); }
+    // LoadEnvironmnet (Renderer.cpp:236-323) after Initialize, e.g. to swap the sky of a loaded scene
+    void LoadEnvironment(const std::string& args) { check(pt_load_environment(ctx_, args.c_str())); }
     void CleanUp() { if (ctx_) { pt_destroy(ctx_); ctx_ = nullptr; } }                                       // :638-647
     // Renderer::RenderReference (the stale CPU renderer, Renderer.cpp:1075-1187) has no counterpart: out of scope.
     const pt_bvh_stats& BvhStats() const { return bvh_stats_; }

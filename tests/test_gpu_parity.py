@@ -153,3 +153,43 @@ def test_present_async_matches_present():
         r2.RenderFrame(cam, 1)
         assert np.array_equal(r2.Present(as_u8=True), bufs[i]), f"frame {i}"
     r.CleanUp(); r2.CleanUp()
+
+
+def test_checkpoint_resume_is_bit_identical(tmp_path):
+    """3 frames + save + 5 frames == 3 frames, restart in a fresh context, load, 5 frames."""
+    s = get_scene("cornell_small")
+    w, h = 64, 48
+    cam = make_camera(s.data, w, h)
+    ck = str(tmp_path / "render.ckpt")
+    r = _renderer(s, w, h, max_depth=5, seed=11)
+    r.RenderFrame(cam, 3)
+    r.SaveCheckpoint(ck)
+    r.RenderFrame(cam, 5)
+    want, want_rng = r.DownloadAccum(), r.GetRNG()
+    r.CleanUp()
+    assert not (tmp_path / "render.ckpt.part").exists()
+
+    r2 = _renderer(s, w, h, max_depth=5, seed=999)         # different seed: everything must come from the file
+    r2.LoadCheckpoint(ck)
+    assert r2.GetNumSamples() == 3
+    r2.RenderFrame(cam, 5)
+    assert r2.GetNumSamples() == 8
+    got, got_rng = r2.DownloadAccum(), r2.GetRNG()
+    assert np.array_equal(got_rng, want_rng)
+    assert np.array_equal(np.nan_to_num(got, nan=-1.0), np.nan_to_num(want, nan=-1.0))
+    # wrong size and damaged files are refused, the context stays usable
+    r3 = _renderer(s, 32, 32, max_depth=5, seed=1)
+    with pytest.raises(Exception):
+        r3.LoadCheckpoint(ck)
+    data = open(ck, "rb").read()
+    bad = tmp_path / "bad.ckpt"
+    bad.write_bytes(data[:-7])
+    with pytest.raises(Exception):
+        r2.LoadCheckpoint(str(bad))
+    flipped = bytearray(data); flipped[len(data) // 2] ^= 0x40
+    bad.write_bytes(bytes(flipped))
+    with pytest.raises(Exception):
+        r2.LoadCheckpoint(str(bad))
+    r2.RenderFrame(cam, 1)
+    assert r2.GetNumSamples() == 9
+    r2.CleanUp(); r3.CleanUp()

@@ -1,6 +1,6 @@
 // tools/headless_main.cpp -- the reference's main() (src/Program.cpp:55-152) without the window: scene.txt in, image out.
 //   g++ -std=c++17 tools/headless_main.cpp -Iinclude -Lgpupathtracer_b200 -lb200pt -Wl,-rpath,$PWD/gpupathtracer_b200 -o headless
-//   ./headless [scene.txt] [spp] [out.ppm]
+//   ./headless [scene.txt] [spp] [out.png]      (the reference saves PNG screenshots, Renderer.cpp:698; .ppm/.pfm also work)
 #include "b200pt_renderer.hpp"
 #include <cstdio>
 #include <cstdlib>
@@ -8,7 +8,7 @@
 int main(int argc, char** argv) {
     const char* scene_txt = argc > 1 ? argv[1] : "scene.txt";
     int spp = argc > 2 ? std::atoi(argv[2]) : 64;
-    const char* out = argc > 3 ? argv[3] : "out.ppm";
+    const char* out = argc > 3 ? argv[3] : "out.png";
     pt_scene_txt st;
     if (pt_scene_txt_read(scene_txt, &st) != PT_OK) { std::fprintf(stderr, "%s\n", pt_last_error()); return 1; }
     b200pt::Window window; window.Width = 1280; window.Height = 720;               // Program.cpp:22-23
