@@ -27,7 +27,7 @@ class PtError(RuntimeError):
 class pt_config(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_depth", C.c_int32),
                 ("microfacet_model", C.c_int32), ("device", C.c_int32), ("bvh_layout", C.c_int32),
-                ("n_slices", C.c_int32), ("reserved", C.c_int32 * 5)]
+                ("n_slices", C.c_int32), ("sun_light", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
 class pt_camera(C.Structure):
@@ -66,6 +66,7 @@ SYMBOLS = [
     ("pt_set_materials", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
     ("pt_set_lights", C.c_int, [_P, _P, C.c_int32, C.c_float]),
     ("pt_set_environment_color", C.c_int, [_P, _F]),
+    ("pt_set_sun", C.c_int, [_P, _F, C.c_float]),
     ("pt_set_environment_cubemap", C.c_int, [_P, _P, C.c_int32]),
     ("pt_set_environment_equirect", C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32]),
     ("pt_environment_size", C.c_int32, [_P]),
@@ -368,9 +369,9 @@ class Renderer:
 
     # -- Renderer::Initialize, Renderer.cpp:448-636
     def Initialize(self, width, height, scene, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=PT_MICROFACET_GGX,
-                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0, bvh_layout=PT_BVH_REFERENCE):
+                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0, bvh_layout=PT_BVH_REFERENCE, sun_light=False):
         cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
-                        device=device, bvh_layout=bvh_layout, n_slices=n_slices)
+                        device=device, bvh_layout=bvh_layout, n_slices=n_slices, sun_light=1 if sun_light else 0)
         ctx = C.c_void_p()
         _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
         self.ctx = ctx
@@ -429,6 +430,10 @@ class Renderer:
 
     def LoadCheckpoint(self, path):
         _check(self.lib.pt_checkpoint_load(self.ctx, path.encode()))
+
+    def SetSun(self, direction, radius):
+        """uniforms sunDir / sunRadius (Iterative.comp:89-90); only used with Initialize(.., sun_light=True)."""
+        _check(self.lib.pt_set_sun(self.ctx, _f3(direction), float(radius)))
 
     # -- LoadEnvironmnet, Renderer.cpp:236-323
     def SetEnvironmentCubemap(self, faces):

@@ -97,6 +97,7 @@ struct pt_context {
     float total_light_area = 0.0f;
     float env[3] = {1.0f, 1.0f, 1.0f};
     DevBuf<float4> d_env; int env_size = 0;      // cubemap faces, 0: constant colour
+    float sun_dir[3] = {0.0f, 1.0f, 0.0f}; float sun_radius = 0.0f;   // set in pt_create
 
     CameraRec cam{};
     bool have_cam = false, have_rng = false;
@@ -135,6 +136,7 @@ static SceneDev scene_dev(pt_context* c) {
     s.lights = c->d_lights.p; s.n_lights = c->n_lights; s.total_light_area = c->total_light_area;
     s.env[0] = c->env[0]; s.env[1] = c->env[1]; s.env[2] = c->env[2];
     s.env_faces = c->d_env.p; s.env_size = c->env_size;
+    s.sun_dir[0] = c->sun_dir[0]; s.sun_dir[1] = c->sun_dir[1]; s.sun_dir[2] = c->sun_dir[2]; s.sun_radius = c->sun_radius;
     return s;
 }
 
@@ -167,6 +169,12 @@ int pt_create(const pt_config* cfg, pt_context** out) {
     CK(cudaSetDevice(cfg->device));
     pt_context* c = new pt_context();
     c->cfg = *cfg;
+    {   // Renderer.cpp:23-26: sunDir = normalize(vec3(2, 40 + 29, 12)), sunRadius = tan(radians(5)), all in binary32
+        const float v[3] = {2.0f, 40.0f + 29.0f, 12.0f};
+        const float inv = 1.0f / sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        for (int k = 0; k < 3; k++) c->sun_dir[k] = v[k] * inv;
+        c->sun_radius = tanf(5.0f * 0.01745329251994329576923690768489f);
+    }
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&c->ev0));
     CK(cudaEventCreate(&c->ev1));
@@ -380,6 +388,14 @@ int pt_set_environment_color(pt_context* c, const float rgb[3]) {
     invalidate_graphs(c);
     c->env[0] = rgb[0]; c->env[1] = rgb[1]; c->env[2] = rgb[2];
     if (c->env_size) { CK(cudaSetDevice(c->cfg.device)); CK(cudaDeviceSynchronize()); c->d_env.release(); c->env_size = 0; }
+    return PT_OK;
+}
+
+int pt_set_sun(pt_context* c, const float direction[3], float radius) {
+    if (!c || !direction || !(radius > 0.0f)) return fail(PT_ERR_INVALID, "pt_set_sun: bad argument");
+    invalidate_graphs(c);
+    for (int k = 0; k < 3; k++) c->sun_dir[k] = direction[k];
+    c->sun_radius = radius;
     return PT_OK;
 }
 
@@ -718,7 +734,7 @@ static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, in
     p.cam = c->d_cam.p;
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.slice_first = first; p.slice_count = count < 0 ? c->cfg.width * c->cfg.height : count;
-    p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model;
+    p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model; p.sun = c->cfg.sun_light ? 1 : 0;
     p.rng_table = c->d_rng.p; p.accum = c->d_accum;
     const size_t o = (size_t)first;                              // the slice's sub-range of every per-path array
     for (int q = 0; q < 2; q++) {

@@ -124,7 +124,7 @@ static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims&
 }
 
 // ------------------------------------------------------------------ shade
-template <int MODEL>
+template <int MODEL, bool SUN>
 __global__ void __launch_bounds__(PT_SHADE_THREADS, 6)
 k_shade(FrameParams p, int bounce, int qi) {
     const int lane = threadIdx.x & 31;
@@ -191,10 +191,28 @@ k_shade(FrameParams p, int bounce, int qi) {
 
                 // GenerateLightSample, Iterative.comp:113-147
                 V3 lpos, lnrm; uint32_t lmat;
-                random_light_vertex(s, rng, lpos, lnrm, lmat);
-                float lightPdf = 1.0f / s.total_light_area;
-                float radius = distance(lpos, vpos);
-                tmax = radius - 0.005f;
+                float lightPdf, radius;
+                if (SUN) {
+                    // #ifdef SUN_LIGHT, Iterative.comp:116-126: a coin flip between the emitter table and the sun disk
+                    float lightPick = rng.next();
+                    if (lightPick > 0.5f) {
+                        random_light_vertex(s, rng, lpos, lnrm, lmat);
+                        lightPdf = 0.5f / s.total_light_area;
+                        radius = distance(lpos, vpos);
+                        tmax = radius - 0.005f;
+                    } else {
+                        random_sun_vertex(s, rng, vpos, lpos, lnrm, lmat);
+                        float sunArea = PT_PI * s.sun_radius * s.sun_radius;              // Iterative.comp:92
+                        lightPdf = 0.5f / sunArea;
+                        radius = distance(lpos, vpos);
+                        tmax = 1e20f;
+                    }
+                } else {
+                    random_light_vertex(s, rng, lpos, lnrm, lmat);
+                    lightPdf = 1.0f / s.total_light_area;
+                    radius = distance(lpos, vpos);
+                    tmax = radius - 0.005f;
+                }
                 ldir = normalize(lpos - vpos);
                 {
                     Interaction li = it;
@@ -294,6 +312,16 @@ __global__ void k_tally(FrameParams p) {
     atomicAdd(&p.totals[0], closest); atomicAdd(&p.totals[1], shadow); atomicAdd(&p.totals[2], (unsigned long long)p.slice_count);
 }
 
+static void launch_shade(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
+    if (p.sun) {
+        if (p.model == 1) k_shade<1, true><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
+        else k_shade<0, true><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
+    } else {
+        if (p.model == 1) k_shade<1, false><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
+        else k_shade<0, false><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
+    }
+}
+
 int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, cudaEvent_t* evs) {
     // evs (optional): one event recorded before every kernel and one after the last, for per-stage timing
     int launches = 0;
@@ -305,9 +333,7 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
         if (evs) cudaEventRecord(evs[launches], st);
         launch_extend(p, b, qi, dims, st); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
-        if (p.model == 1) k_shade<1><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
-        else k_shade<0><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
-        launches++;
+        launch_shade(p, b, qi, dims, st); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
         launch_shadow(p, b, qi ^ 1, dims, st); launches++;
         qi ^= 1;
@@ -328,9 +354,7 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
     if (wait_prev) cudaStreamWaitEvent(A, ss.ev_shadow, 0);
     int qi = 0;
     for (int b = 0; b < p.max_depth; b++) {
-        if (p.model == 1) k_shade<1><<<dims.shade_blocks, PT_SHADE_THREADS, 0, A>>>(p, b, qi);
-        else k_shade<0><<<dims.shade_blocks, PT_SHADE_THREADS, 0, A>>>(p, b, qi);
-        launches++;
+        launch_shade(p, b, qi, dims, A); launches++;
         cudaEventRecord(ss.ev_shade, A);
         cudaStreamWaitEvent(B, ss.ev_shade, 0);
         launch_shadow(p, b, qi ^ 1, dims, B); launches++;
@@ -458,7 +482,7 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);
     }
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0>, PT_SHADE_THREADS, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0, false>, PT_SHADE_THREADS, 0);
     int per = per_sm_ext < per_sm_shadow ? per_sm_ext : per_sm_shadow;
     if (per < 1) per = 1;
     if (per_sm_shade < 1) per_sm_shade = 1;

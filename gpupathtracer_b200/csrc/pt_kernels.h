@@ -20,6 +20,7 @@ struct FrameParams {
     int slice_first, slice_count;   // this launch sequence owns ray indices [slice_first, slice_first + slice_count)
     int max_depth;
     int model;
+    int sun;              // SUN_LIGHT (Iterative.comp:116-126), off in the reference as shipped
     uint4* rng_table;     // per pixel
     float4* accum;        // per pixel, running sum
     PathQueue queue[2];

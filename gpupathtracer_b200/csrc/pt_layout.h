@@ -81,6 +81,8 @@ struct SceneDev {
     int n_lights;
     float total_light_area;
     float env[3];                // constant environment ("GENERATE COLOR"), used when env_size == 0
+    float sun_dir[3];            // uniform sunDir / sunRadius (Iterative.comp:89-90, Renderer.cpp:23-26,626-627)
+    float sun_radius;
     const float4* env_faces;     // cubemap: 6 x env_size x env_size RGBA32F, faces +X -X +Y -Y +Z -Z, rows as uploaded
     int env_size;
 };

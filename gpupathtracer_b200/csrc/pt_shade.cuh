@@ -247,6 +247,26 @@ __device__ inline void random_light_vertex(const SceneDev& s, Rng& rng, V3& pos,
     mat = __float_as_uint(t4.z);
 }
 
+// RandomSunVertex, Iterative.comp:84-110: the sun is a disk of radius sunRadius one unit away along sunDir, sampled
+// uniformly by area in the frame ConstructTBN(-sunDir); its material is the sky's (matId 0), whose emission
+// (25 * (30, 26, 19), Scene.cpp:239) is what the NEE sample picks up.
+__device__ inline void random_sun_vertex(const SceneDev& s, Rng& rng, V3 vertex, V3& pos, V3& nrm, uint32_t& mat) {
+    V3 sd = v3(s.sun_dir[0], s.sun_dir[1], s.sun_dir[2]);
+    V3 n = -sd;
+    V3 normcrs = (fabsf(n.y) > 0.99f) ? v3(1.0f, 0.0f, 0.0f) : v3(0.0f, 1.0f, 0.0f);     // ConstructTBN, Material.glsl:71-76
+    V3 t = normalize(cross(normcrs, n));
+    V3 b = cross(t, n);
+    float rx = rng.next(), ry = rng.next();
+    float radius = s.sun_radius * sqrtf(rx);
+    float phi = 2.0f * PT_PI * ry;
+    float sn, cs; sincosf(phi, &sn, &cs);
+    V3 d = v3(radius * cs, radius * sn, 0.0f);
+    V3 off = v3(t.x * d.x + b.x * d.y + n.x * d.z, t.y * d.x + b.y * d.y + n.y * d.z, t.z * d.x + b.z * d.y + n.z * d.z);
+    pos = vertex + sd + off;
+    nrm = n;
+    mat = 0u;
+}
+
 // ---------------------------------------------------------------- ray generation
 __device__ __forceinline__ int compact1by1(int x) {          // Iterative.comp:154-161
     x &= 0x55555555;

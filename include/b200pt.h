@@ -55,7 +55,9 @@ typedef struct pt_config {
     int32_t n_slices;             /* a frame is rendered as this many pixel-disjoint slices on concurrent streams so that
                                      one slice's kernels fill the drain phase of another's; 0 = default (3). Results do
                                      not depend on it (every pixel keeps its own RNG sequence). */
-    int32_t reserved[5];
+    int32_t sun_light;            /* 1 = compile the reference's `#ifdef SUN_LIGHT` branch in (Iterative.comp:116-126): NEE flips a
+                                     coin between the emitter table and a sun disk. Off in the reference as shipped. */
+    int32_t reserved[4];
 } pt_config;
 
 /* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
@@ -113,6 +115,9 @@ int pt_set_environment_color(pt_context* ctx, const float rgb[3]);   /* LoadEnvi
 /* Environment cubemap sampled on a miss (Iterative.comp:251: texture(samplerCube, ray.direction)): six size x size
  * RGBA32F faces in the order +X -X +Y -Y +Z -Z, rows as they would be handed to glTexImage2D; looked up with the
  * OpenGL cube-map face table, GL_LINEAR, CLAMP_TO_EDGE per face (Renderer.cpp:318-322). */
+/* uniforms sunDir / sunRadius (Iterative.comp:89-90). Defaults are the reference's constants (Renderer.cpp:23-26):
+ * normalize(2, 69, 12) and tan(radians(5)). Only read when pt_config.sun_light is set. */
+int pt_set_sun(pt_context* ctx, const float direction[3], float radius);
 int pt_set_environment_cubemap(pt_context* ctx, const float* faces_rgba, int32_t size);
 /* The .hdr branch of LoadEnvironmnet (Renderer.cpp:262-312) as one kernel: the six 90-degree raster passes over
  * EquirectangularConverter.vert/.frag written out per face texel. rgba = width x height RGBA32F, row 0 = top of the

@@ -42,7 +42,7 @@ class OrCamera(C.Structure):
 
 class OrConfig(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("max_depth", C.c_int), ("microfacet_model", C.c_int),
-                ("n_threads", C.c_int)]
+                ("n_threads", C.c_int), ("sun_light", C.c_int), ("sun_dir", C.c_float * 3), ("sun_radius", C.c_float)]
 
 
 class OrCounters(C.Structure):
@@ -212,10 +212,13 @@ class Oracle:
         c.lens_radius = float(a[18])
         return c
 
-    def render(self, cam_array, width, height, rng, accum, n_frames=1, max_depth=66, model=0, n_threads=0):
-        """In place on rng (px,4) uint32 and accum (h,w,4) float32. Returns counters."""
+    def render(self, cam_array, width, height, rng, accum, n_frames=1, max_depth=66, model=0, n_threads=0, sun=None):
+        """In place on rng (px,4) uint32 and accum (h,w,4) float32. Returns counters. sun = (direction, radius) turns the
+        shader's SUN_LIGHT branch on."""
         cam = self.camera(cam_array)
         cfg = OrConfig(width, height, max_depth, model, n_threads)
+        if sun is not None:
+            cfg.sun_light, cfg.sun_dir, cfg.sun_radius = 1, (C.c_float * 3)(*sun[0]), float(sun[1])
         c = OrCounters()
         assert rng.dtype == np.uint32 and rng.flags.c_contiguous and accum.dtype == np.float32 and accum.flags.c_contiguous
         self.l.or_render(C.byref(self.s), C.byref(cam), C.byref(cfg), _p(rng), _p(accum), n_frames, C.byref(c))

@@ -456,12 +456,45 @@ LightVertex random_light_vertex(const OrScene& s, Rng& rng) {
     return lv;
 }
 
-// GenerateLightSample, Iterative.comp:113-147 (SUN_LIGHT off). `it` is passed by value as in the shader.
-Ray light_sample(const OrScene& s, int model, V3 vpos, V3 vnormal, const Material& m, Interaction it, Rng& rng,
+// RandomSunVertex, Iterative.comp:84-110
+LightVertex random_sun_vertex(const OrConfig& cfg, V3 vertexPosition, Rng& rng) {
+    V3 sunDir = v3(cfg.sun_dir[0], cfg.sun_dir[1], cfg.sun_dir[2]);
+    Interaction tbn{};
+    make_tbn(-sunDir, tbn);                       // mat3 sunTBN = ConstructTBN(-sunDir)
+    float rx = rng.next(), ry = rng.next();       // vec2 r = rand2()
+    float radius = cfg.sun_radius * sqrtf(rx);
+    float phi = 2.0f * kPi * ry;
+    V3 diskPosition = v3(radius * cosf(phi), radius * sinf(phi), 0.0f);
+    LightVertex lv;
+    lv.position = vertexPosition + sunDir + tbn_mul(tbn, diskPosition);
+    lv.normal = -sunDir;
+    lv.mat = 0;
+    return lv;
+}
+
+// GenerateLightSample, Iterative.comp:113-147. `it` is passed by value as in the shader.
+Ray light_sample(const OrScene& s, const OrConfig& cfg, V3 vpos, V3 vnormal, const Material& m, Interaction it, Rng& rng,
                  float& tmax, V3 throughput, V3& lightThroughput, uint32_t& lightMat) {
-    LightVertex lv = random_light_vertex(s, rng);
-    float lightPdf = 1.0f / s.total_light_area;
-    tmax = distance(lv.position, vpos) - 0.005f;
+    const int model = cfg.microfacet_model;
+    LightVertex lv;
+    float lightPdf;
+    if (cfg.sun_light) {                          // #ifdef SUN_LIGHT, :116-126
+        float lightPick = rng.next();
+        if (lightPick > 0.5f) {
+            lv = random_light_vertex(s, rng);
+            lightPdf = 0.5f / s.total_light_area;
+            tmax = distance(lv.position, vpos) - 0.005f;
+        } else {
+            lv = random_sun_vertex(cfg, vpos, rng);
+            float sunArea = kPi * cfg.sun_radius * cfg.sun_radius;     // :92
+            lightPdf = 0.5f / sunArea;
+            tmax = 1e20f;
+        }
+    } else {
+        lv = random_light_vertex(s, rng);
+        lightPdf = 1.0f / s.total_light_area;
+        tmax = distance(lv.position, vpos) - 0.005f;
+    }
     float radius = distance(lv.position, vpos);
     V3 lightDir = normalize(lv.position - vpos);
     set_incoming(it, lightDir);
@@ -569,7 +602,7 @@ void trace_path(const OrScene& s, const OrCamera& cam, const OrConfig& cfg, int 
 
         // NEE, Iterative.comp:272-280
         float tmax; V3 lightThroughput; uint32_t lightMat;
-        Ray lightRay = light_sample(s, model, vpos, vnormal, mat, it, rng, tmax, p.throughput, lightThroughput, lightMat);
+        Ray lightRay = light_sample(s, cfg, vpos, vnormal, mat, it, rng, tmax, p.throughput, lightThroughput, lightMat);
         Hit lh; lh.t = tmax; lh.u = lh.v = 0; lh.tri = -1;
         nShadow++;
         if (!any_hit(s, lightRay, lh, scnt)) {

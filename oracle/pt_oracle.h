@@ -71,6 +71,9 @@ typedef struct OrConfig {
     int max_depth;         /* max closest-hit rays per path; reference = 66 (`i > 64`, Iterative.comp:293) */
     int microfacet_model;  /* 0 = Trowbridge-Reitz (live, Microfacet.glsl:90-92), 1 = Beckmann (:35-55) */
     int n_threads;         /* host threads; <=0: hardware_concurrency */
+    int sun_light;         /* 1: the `#ifdef SUN_LIGHT` branch of GenerateLightSample (Iterative.comp:116-126) */
+    float sun_dir[3];      /* uniform sunDir (Iterative.comp:89; Renderer.cpp:23: normalize(2, 69, 12)) */
+    float sun_radius;      /* uniform sunRadius (Iterative.comp:90; Renderer.cpp:24-25: tan(radians(5))) */
 } OrConfig;
 
 typedef struct OrCounters {
