@@ -476,7 +476,9 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<WideTraverser<4>>, PT_TRACE_THREADS, 0);
     } else {
         out->top_pairs = 0;
+#ifdef PT_SMEM_TOP   // only when the staging code is compiled in (pt_trace.cuh)
         if (const char* e = getenv("PT_SMEM_TOP")) out->top_pairs = atoi(e);
+#endif
         if (out->top_pairs < 0) out->top_pairs = 0;
         if (out->top_pairs > 700) out->top_pairs = 700;                      // 44.8 KB: below the 48-KB dynamic limit without opt-in
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);

@@ -78,11 +78,18 @@ struct Traverser {
         result = false;
     }
     // Stage the top of the tree (pair records [0, top_pairs), breadth-first) in shared memory, once per CTA.
+    // Compile-time experiment (build with PT_NVCC_EXTRA=-DPT_SMEM_TOP, run with PT_SMEM_TOP=<pairs>): measured slower than
+    // L1 on both workloads, and even switched off at run time the extra compare/branch in inner_step cost 3.8 % on the
+    // atrium (3.02 -> 2.90 Grays/s), so it is not compiled in by default.
     static __device__ __forceinline__ void prologue(const SceneDev& s) {
+#ifdef PT_SMEM_TOP
         extern __shared__ float4 s_top[];
         const float4* src = reinterpret_cast<const float4*>(s.pairs);
         for (int i = threadIdx.x; i < 4 * s.top_pairs; i += blockDim.x) s_top[i] = __ldg(src + i);
         __syncthreads();
+#else
+        (void)s;
+#endif
     }
     __device__ __forceinline__ void idle() { current = 0; sp = 0; }
     __device__ __forceinline__ bool at_leaf() const { return current < 0; }
@@ -95,11 +102,14 @@ struct Traverser {
     template <bool ANY>
     __device__ __forceinline__ bool inner_step(const SceneDev& s, int* stack) {
         float4 a0, a1, b0, b1;
+#ifdef PT_SMEM_TOP
         if (current < s.top_pairs) {
             extern __shared__ float4 s_top[];
             const float4* q = s_top + 4 * current;
             a0 = q[0]; a1 = q[1]; b0 = q[2]; b1 = q[3];
-        } else {
+        } else
+#endif
+        {
             const float4* q = s.pairs[current].q;
             F8 ca = ldg256(q), cb = ldg256(q + 2);
             a0 = ca.lo; a1 = ca.hi; b0 = cb.lo; b1 = cb.hi;
