@@ -160,6 +160,10 @@ __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io
     const unsigned lt_mask = (1u << lane) - 1u;
     const int n = io.count();
     int* cursor = io.cursor();
+    // bits 16.. of leaf_thresh: inner steps a lane may take per vote round (the vote/refill bookkeeping is ~28
+    // instructions against ~60 for a pair test, so re-voting after every single step is expensive)
+    const int burst = leaf_thresh >> 16, leaf_burst = (leaf_thresh >> 8) & 0xff;
+    leaf_thresh &= 0xff;
     TR::prologue(s);
     TR tr;
     typename TR::StackEntry stack[TR::kStack];   // per-lane traversal stack (local memory, L1-resident)
@@ -194,9 +198,15 @@ __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io
         unsigned m_inner = m_active & ~m_leaf;
         bool done = false;
         if (m_inner != 0 && __popc(m_leaf) < leaf_thresh) {
-            if (active && !at_leaf) done = tr.template inner_step<ANY>(s, stack);
+            if (active && !at_leaf) {
+                done = tr.template inner_step<ANY>(s, stack);
+                for (int k = 1; k < burst && !done && !tr.at_leaf(); k++) done = tr.template inner_step<ANY>(s, stack);
+            }
         } else {
-            if (at_leaf) done = tr.template leaf_step<ANY>(s, stack);
+            if (at_leaf) {
+                done = tr.template leaf_step<ANY>(s, stack);
+                for (int k = 1; k < leaf_burst && !done && tr.at_leaf(); k++) done = tr.template leaf_step<ANY>(s, stack);
+            }
         }
         if (done) {
             io.store(ridx, tr.h, tr.result);
