@@ -115,6 +115,10 @@ struct pt_context {
     // staging for host-pointer batch entry points
     DevBuf<float4> d_stage_rays, d_stage_hits;
     DevBuf<unsigned char> d_stage_flags;
+    // processing order of big ray batches (launch_ray_order)
+    DevBuf<unsigned> d_ray_bins, d_ray_bin; DevBuf<int> d_ray_perm;
+    int ray_order = 0;                     // 0 auto, 1 always, -1 never (PT_RAY_ORDER)
+    size_t l2_bytes = 0;
     DevBuf<float> d_resolve_f32;
     DevBuf<unsigned char> d_resolve_u8;
     // per-stage timing (pt_set_stage_timing)
@@ -175,6 +179,8 @@ int pt_create(const pt_config* cfg, pt_context** out) {
         for (int k = 0; k < 3; k++) c->sun_dir[k] = v[k] * inv;
         c->sun_radius = tanf(5.0f * 0.01745329251994329576923690768489f);
     }
+    c->l2_bytes = (size_t)prop.l2CacheSize;
+    if (const char* e = getenv("PT_RAY_ORDER")) c->ray_order = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&c->ev0));
     CK(cudaEventCreate(&c->ev1));
@@ -237,6 +243,7 @@ void pt_destroy(pt_context* c) {
     for (int k = 0; k < 4; k++) c->d_shadow[k].release();
     c->d_hits.release(); c->d_counters.release(); c->d_totals.release(); c->d_cursor.release();
     c->d_stage_rays.release(); c->d_stage_hits.release(); c->d_stage_flags.release();
+    c->d_ray_bins.release(); c->d_ray_bin.release(); c->d_ray_perm.release();
     c->d_resolve_f32.release(); c->d_resolve_u8.release();
     for (cudaEvent_t e : c->stage_events) cudaEventDestroy(e);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1);
@@ -716,6 +723,26 @@ int pt_get_rng(pt_context* c, uint32_t* state4) {
     return PT_OK;
 }
 
+static const int64_t kHostChunk = 1 << 21;      // host batches are traced in chunks of this many rays (pipelined copies)
+static const int64_t kRayOrderMin = 1 << 16;    // smaller batches are not worth three extra launches
+// Decide whether a batch is traced in binned order and, if so, enqueue the binning; nullptr = natural order.
+static int order_rays(pt_context* c, const float4* d_rays, int64_t n, const int** perm) {
+    *perm = nullptr;
+    if (c->ray_order < 0 || n < (c->ray_order > 0 ? 2 : kRayOrderMin)) return PT_OK;
+    if (c->ray_order == 0) {
+        // auto: only when the traversal layout outgrows L2 (every node step a DRAM round trip); measured in DESIGN.md 4
+        const size_t tree = c->dims.wide ? c->d_wide.n + c->d_wide_tris.n * sizeof(LeafTri)
+                                         : c->d_pairs.n * sizeof(BvhPair) + c->d_leaf.n * sizeof(LeafTri);
+        if (tree <= c->l2_bytes) return PT_OK;
+    }
+    CK(c->d_ray_bins.alloc(1 << 18));
+    CK(c->d_ray_bin.alloc((size_t)n));
+    CK(c->d_ray_perm.alloc((size_t)n));
+    c->counters.kernel_launches += launch_ray_order(scene_dev(c), d_rays, n, c->d_ray_bins.p, c->d_ray_bin.p, c->d_ray_perm.p, c->stream);
+    *perm = c->d_ray_perm.p;
+    return PT_OK;
+}
+
 static int check_scene(pt_context* c, const char* who, bool need_shading) {
     if (!c->d_pairs.p || !c->d_leaf.p || !c->d_tris.p) return fail(PT_ERR_INVALID, "%s: triangles and BVH must be set first", who);
     if (need_shading) {
@@ -982,7 +1009,9 @@ int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* 
     int rc = check_scene(c, "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
-    launch_trace_closest(scene_dev(c), (const float4*)d_rays, n, (float4*)d_hits, c->d_cursor.p, c->dims, c->stream);
+    const int* perm = nullptr;
+    if ((rc = order_rays(c, (const float4*)d_rays, n, &perm)) != PT_OK) return rc;
+    launch_trace_closest(scene_dev(c), (const float4*)d_rays, n, (float4*)d_hits, c->d_cursor.p, c->dims, c->stream, perm);
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaGetLastError());
     c->counters.kernel_launches++;
@@ -995,7 +1024,9 @@ int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_fl
     int rc = check_scene(c, "pt_trace_any", false);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
-    launch_trace_any(scene_dev(c), (const float4*)d_rays, n, (unsigned char*)d_flags, c->d_cursor.p, c->dims, c->stream);
+    const int* perm = nullptr;
+    if ((rc = order_rays(c, (const float4*)d_rays, n, &perm)) != PT_OK) return rc;
+    launch_trace_any(scene_dev(c), (const float4*)d_rays, n, (unsigned char*)d_flags, c->d_cursor.p, c->dims, c->stream, perm);
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaGetLastError());
     c->counters.kernel_launches++;
@@ -1006,7 +1037,7 @@ int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_fl
 // Host batches: chunks of kHostChunk rays flow through a three-stage pipeline -- H2D on `in_stream`, the traversal
 // kernel on the render stream, D2H on `copy_stream` -- with double-buffered staging, so a 16 M-ray batch costs about
 // max(PCIe in, kernel, PCIe out) instead of their sum (pinned host memory makes the copies truly asynchronous).
-static const int64_t kHostChunk = 1 << 21;
+
 
 static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, size_t out_bytes, bool any) {
     CK(cudaSetDevice(c->cfg.device));
@@ -1033,16 +1064,18 @@ static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, si
         CK(cudaEventRecord(c->ev_h_in[k], c->in_stream));
         CK(cudaStreamWaitEvent(c->stream, c->ev_h_in[k], 0));
         CK(cudaStreamWaitEvent(c->stream, c->ev_h_out[k], 0));        // the copy that last read this result buffer
+        const int* perm = nullptr;
+        if ((rc = order_rays(c, d_rays, m, &perm)) != PT_OK) return rc;
         if (any) {
             unsigned char* d_out = c->d_stage_flags.p + (size_t)k * chunk;
-            launch_trace_any(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream);
+            launch_trace_any(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream, perm);
             CK(cudaEventRecord(c->ev_h_done[k], c->stream));
             CK(cudaStreamWaitEvent(c->copy_stream, c->ev_h_done[k], 0));
             CK(cudaMemcpyAsync((unsigned char*)out + first, d_out, (size_t)m, cudaMemcpyDeviceToHost, c->copy_stream));
             c->counters.shadow_rays += (uint64_t)m;
         } else {
             float4* d_out = c->d_stage_hits.p + (size_t)k * chunk;
-            launch_trace_closest(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream);
+            launch_trace_closest(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream, perm);
             CK(cudaEventRecord(c->ev_h_done[k], c->stream));
             CK(cudaStreamWaitEvent(c->copy_stream, c->ev_h_done[k], 0));
             CK(cudaMemcpyAsync((char*)out + out_bytes * first, d_out, out_bytes * (size_t)m, cudaMemcpyDeviceToHost, c->copy_stream));

@@ -20,21 +20,100 @@ namespace pt {
 #define PT_TRACE_THREADS 128   // 10 CTAs/SM at 48 registers; forcing 12 (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
 #define PT_STREAM_THREADS 256
 #define PT_SHADE_THREADS 128
+#define PT_RAY_ORDER_MAX_BITS 5
 
 // ------------------------------------------------------------------ fixed ray batches
 struct BatchIO {
     const float4* rays; float4* hits; unsigned char* flags; int n; int* cur;
+    const int* perm;      // optional processing order (launch_ray_order); results still land at the ray's own index
     __device__ __forceinline__ int count() const { return n; }
     __device__ __forceinline__ int* cursor() const { return cur; }
     __device__ __forceinline__ void load(int i, V3& o, V3& d, float& tmax) const {
+        if (perm) i = __ldg(perm + i);
         float4 ro = __ldg(rays + 2 * (size_t)i), rd = __ldg(rays + 2 * (size_t)i + 1);
         o = xyz(ro); d = xyz(rd); tmax = rd.w;
     }
     __device__ __forceinline__ void store(int i, const HitRec& h, bool result) const {
+        if (perm) i = __ldg(perm + i);
         if (flags) flags[i] = result ? 1 : 0;
         else hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
     }
 };
+
+// ---- processing order for big incoherent batches: rays binned by origin cell (Morton, `bits` per axis inside the root
+// box) and direction octant with a counting sort over global atomics -- two passes over the rays, no stability needed.
+// Neighbouring lanes then start in the same part of the tree and head the same way, which is what the caches (and on a
+// tree that outgrows L2, the DRAM row buffers) reward. A ray's own traversal and result do not depend on the order.
+__device__ __forceinline__ unsigned spread3(unsigned v) {      // 10 bits -> every third bit
+    v = (v | (v << 16)) & 0x030000ffu;
+    v = (v | (v << 8)) & 0x0300f00fu;
+    v = (v | (v << 4)) & 0x030c30c3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__global__ void k_ray_bin(SceneDev s, const float4* __restrict__ rays, int n, int bits, unsigned* counts, unsigned* ray_bin) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4* q = s.pairs[0].q;
+    float4 a0 = __ldg(q), a1 = __ldg(q + 1), b0 = __ldg(q + 2), b1 = __ldg(q + 3);
+    float lo[3] = {fminf(a0.x, b0.x), fminf(a0.y, b0.y), fminf(a0.z, b0.z)};
+    float hi[3] = {fmaxf(a1.x, b1.x), fmaxf(a1.y, b1.y), fmaxf(a1.z, b1.z)};
+    float4 ro = __ldg(rays + 2 * (size_t)i), rd = __ldg(rays + 2 * (size_t)i + 1);
+    const int cells = 1 << bits;
+    float o[3] = {ro.x, ro.y, ro.z};
+    unsigned c[3];
+    for (int k = 0; k < 3; k++) {
+        float ext = hi[k] - lo[k];
+        float f = ext > 0.0f ? (o[k] - lo[k]) / ext * (float)cells : 0.0f;
+        int v = f >= 0.0f ? (int)fminf(f, (float)(cells - 1)) : 0;            // NaN and outside origins clamp
+        c[k] = (unsigned)v;
+    }
+    unsigned morton = spread3(c[0]) | (spread3(c[1]) << 1) | (spread3(c[2]) << 2);
+    unsigned oct = (rd.x < 0.0f ? 1u : 0u) | (rd.y < 0.0f ? 2u : 0u) | (rd.z < 0.0f ? 4u : 0u);
+    unsigned bin = (morton << 3) | oct;
+    ray_bin[i] = bin;
+    atomicAdd(counts + bin, 1u);
+}
+// exclusive scan of n_bins counters in place, one block of 1024 threads, n_bins a multiple of 1024
+__global__ void __launch_bounds__(1024) k_ray_bin_scan(unsigned* counts, int n_bins) {
+    __shared__ unsigned warp_sums[32];
+    const int per = n_bins / 1024, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned* mine = counts + (size_t)threadIdx.x * per;
+    unsigned sum = 0;
+    for (int k = 0; k < per; k++) sum += mine[k];
+    unsigned x = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_sums[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned w = warp_sums[lane], z = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, z, o); if (lane >= o) z += y; }
+        warp_sums[lane] = z - w;
+    }
+    __syncthreads();
+    unsigned run = warp_sums[warp] + (x - sum);
+    for (int k = 0; k < per; k++) { unsigned v = mine[k]; mine[k] = run; run += v; }
+}
+__global__ void k_ray_bin_scatter(const unsigned* __restrict__ ray_bin, int n, unsigned* cursors, int* perm) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned pos = atomicAdd(cursors + ray_bin[i], 1u);
+    perm[pos] = i;
+}
+int launch_ray_order(const SceneDev& s, const float4* rays, long long n, unsigned* bins, unsigned* ray_bin, int* perm, cudaStream_t st) {
+    // about 64 rays per bin, 2..5 bits per axis (+3 octant bits): 512 .. 262144 bins
+    int bits = 2;
+    while (bits < PT_RAY_ORDER_MAX_BITS && (n >> (3 * (bits + 1) + 3)) >= 64) bits++;
+    const int n_bins = 1 << (3 * bits + 3);
+    cudaMemsetAsync(bins, 0, sizeof(unsigned) * (n_bins < 1024 ? 1024 : n_bins), st);
+    const int blocks = (int)((n + 255) / 256);
+    k_ray_bin<<<blocks, 256, 0, st>>>(s, rays, (int)n, bits, bins, ray_bin);
+    k_ray_bin_scan<<<1, 1024, 0, st>>>(bins, n_bins < 1024 ? 1024 : n_bins);
+    k_ray_bin_scatter<<<blocks, 256, 0, st>>>(ray_bin, (int)n, bins, perm);
+    return 3;
+}
 
 template <bool ANY, class TR>
 __global__ void __launch_bounds__(PT_TRACE_THREADS)
@@ -43,17 +122,17 @@ k_trace_batch(SceneDev s, BatchIO io, int leaf_thresh, int fetch_thresh) {
 }
 
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
-                          const LaunchDims& dims, cudaStream_t st) {
+                          const LaunchDims& dims, cudaStream_t st, const int* perm) {
     cudaMemsetAsync(cursor, 0, sizeof(int), st);
-    BatchIO io{rays, hits, nullptr, (int)n, cursor};
+    BatchIO io{rays, hits, nullptr, (int)n, cursor, perm};
     if (dims.wide == 8) k_trace_batch<false, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_trace_batch<false, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else k_trace_batch<false, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
-                      const LaunchDims& dims, cudaStream_t st) {
+                      const LaunchDims& dims, cudaStream_t st, const int* perm) {
     cudaMemsetAsync(cursor, 0, sizeof(int), st);
-    BatchIO io{rays, nullptr, flags, (int)n, cursor};
+    BatchIO io{rays, nullptr, flags, (int)n, cursor, perm};
     if (dims.wide == 8) k_trace_batch<true, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_trace_batch<true, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else k_trace_batch<true, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);

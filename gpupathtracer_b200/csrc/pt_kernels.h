@@ -34,9 +34,12 @@ struct LaunchDims { int sm_count; int extend_blocks; int stream_blocks; int shad
 
 // fixed ray batches (AoS rays: n x {o.xyz, -, d.xyz, tmax})
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
-                          const LaunchDims& dims, cudaStream_t st);
+                          const LaunchDims& dims, cudaStream_t st, const int* perm = nullptr);
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
-                      const LaunchDims& dims, cudaStream_t st);
+                      const LaunchDims& dims, cudaStream_t st, const int* perm = nullptr);
+// processing order for a batch: counting sort of the rays by origin cell + direction octant. bins: >= 262144 counters,
+// ray_bin / perm: n entries each. Returns the number of kernels launched.
+int launch_ray_order(const SceneDev& s, const float4* rays, long long n, unsigned* bins, unsigned* ray_bin, int* perm, cudaStream_t st);
 
 // one frame = raygen + max_depth x (extend, shade, shadow) + tally; returns number of kernels launched
 // kernel k of a frame: 0 = raygen, 1+3b = extend, 2+3b = shade, 3+3b = shadow (bounce b), last = tally
