@@ -151,3 +151,27 @@ def test_host_batches_larger_than_one_pipeline_chunk():
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
     assert np.array_equal(gflag, wflag)
     assert c["closest_rays"] == n and c["shadow_rays"] == n
+
+
+def test_ray_ordering_does_not_change_any_result(monkeypatch):
+    """Big batches may be traced in binned order (origin cell + direction octant, launch_ray_order): forced on (it is
+    automatic only for trees larger than L2) the hits and flags must be the bits of the natural order and of the oracle,
+    device pointers and chunked host batches alike, including origins outside the root box and a ragged size."""
+    from common import mixed_rays
+    s = get_scene("soup")
+    n = 300_001
+    rays = mixed_rays(s, n, seed=41)
+    rays[:1000, 0:3] *= 50.0                                     # far outside the scene
+    anyr = mixed_rays(s, n, seed=42, any_hit=True)
+    want, _ = oracle.Oracle(s).trace_closest(rays)
+    wflag, _ = oracle.Oracle(s).trace_any(anyr)
+    out = {}
+    for mode in ("-1", "1"):
+        monkeypatch.setenv("PT_RAY_ORDER", mode)
+        r = Renderer().Initialize(64, 64, s)
+        out[mode] = (r.TraceClosest(rays), r.TraceAny(anyr), r.Counters()["kernel_launches"])
+        r.CleanUp()
+    for mode in ("-1", "1"):
+        assert np.array_equal(out[mode][0].view(np.uint32), want.view(np.uint32))
+        assert np.array_equal(out[mode][1], wflag)
+    assert out["1"][2] == out["-1"][2] + 6                       # 3 binning kernels per ordered launch
