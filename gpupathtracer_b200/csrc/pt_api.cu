@@ -730,12 +730,13 @@ static int order_rays(pt_context* c, const float4* d_rays, int64_t n, const int*
     *perm = nullptr;
     if (c->ray_order < 0 || n < (c->ray_order > 0 ? 2 : kRayOrderMin)) return PT_OK;
     if (c->ray_order == 0) {
-        // auto: only when the traversal layout outgrows L2 (every node step a DRAM round trip); measured in DESIGN.md 4
-        const size_t tree = c->dims.wide ? c->d_wide.n + c->d_wide_tris.n * sizeof(LeafTri)
-                                         : c->d_pairs.n * sizeof(BvhPair) + c->d_leaf.n * sizeof(LeafTri);
-        if (tree <= c->l2_bytes) return PT_OK;
+        // auto: the binary layout once it outgrows L2 (every node step a DRAM round trip). Measured: +26 % on
+        // the 10 M-triangle batch; -4 % on an L2-resident tree (binning costs what the trace gains); the wide layouts
+        // are issue-bound, the halved DRAM traffic does not pay for the binning there (-4 %).
+        if (c->dims.wide) return PT_OK;
+        if (c->d_pairs.n * sizeof(BvhPair) + c->d_leaf.n * sizeof(LeafTri) <= c->l2_bytes) return PT_OK;
     }
-    CK(c->d_ray_bins.alloc(1 << 18));
+    CK(c->d_ray_bins.alloc((1 << 21) + 2048));                  // counters + scan tile totals (launch_ray_order)
     CK(c->d_ray_bin.alloc((size_t)n));
     CK(c->d_ray_perm.alloc((size_t)n));
     c->counters.kernel_launches += launch_ray_order(scene_dev(c), d_rays, n, c->d_ray_bins.p, c->d_ray_bin.p, c->d_ray_perm.p, c->stream);

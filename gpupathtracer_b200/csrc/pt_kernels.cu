@@ -20,7 +20,8 @@ namespace pt {
 #define PT_TRACE_THREADS 128   // 10 CTAs/SM at 48 registers; forcing 12 (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
 #define PT_STREAM_THREADS 256
 #define PT_SHADE_THREADS 128
-#define PT_RAY_ORDER_MAX_BITS 5
+#define PT_RAY_ORDER_MAX_BITS 6      // 64^3 cells x 8 octants = 2097152 bins = 2048 scan tiles
+#define PT_RAY_ORDER_PER_BIN 64
 
 // ------------------------------------------------------------------ fixed ray batches
 struct BatchIO {
@@ -74,14 +75,43 @@ __global__ void k_ray_bin(SceneDev s, const float4* __restrict__ rays, int n, in
     ray_bin[i] = bin;
     atomicAdd(counts + bin, 1u);
 }
-// exclusive scan of n_bins counters in place, one block of 1024 threads, n_bins a multiple of 1024
-__global__ void __launch_bounds__(1024) k_ray_bin_scan(unsigned* counts, int n_bins) {
+// exclusive scan of n_bins counters in place (n_bins a multiple of 1024, at most 1024 tiles): tile totals, then every
+// tile adds the totals of the tiles before it to its own scan -- two small coalesced launches
+__global__ void __launch_bounds__(1024) k_ray_bin_tile_sums(const unsigned* __restrict__ counts, unsigned* tile_sums) {
     __shared__ unsigned warp_sums[32];
-    const int per = n_bins / 1024, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned* mine = counts + (size_t)threadIdx.x * per;
-    unsigned sum = 0;
-    for (int k = 0; k < per; k++) sum += mine[k];
-    unsigned x = sum;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned x = counts[(size_t)blockIdx.x * 1024 + threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+    if (lane == 0) warp_sums[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned z = warp_sums[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) z += __shfl_down_sync(0xffffffffu, z, o);
+        if (lane == 0) tile_sums[blockIdx.x] = z;
+    }
+}
+__global__ void __launch_bounds__(1024) k_ray_bin_scan(unsigned* counts, const unsigned* __restrict__ tile_sums) {
+    __shared__ unsigned warp_sums[32];
+    __shared__ unsigned tile_base;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // totals of the tiles before this one
+    unsigned before = 0u;
+    for (int t = threadIdx.x; t < (int)blockIdx.x; t += 1024) before += tile_sums[t];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) before += __shfl_down_sync(0xffffffffu, before, o);
+    if (lane == 0) warp_sums[warp] = before;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned z = warp_sums[lane];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) z += __shfl_down_sync(0xffffffffu, z, o);
+        if (lane == 0) tile_base = z;
+    }
+    __syncthreads();
+    unsigned* mine = counts + (size_t)blockIdx.x * 1024 + threadIdx.x;
+    unsigned v = *mine, x = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
     if (lane == 31) warp_sums[warp] = x;
@@ -93,8 +123,7 @@ __global__ void __launch_bounds__(1024) k_ray_bin_scan(unsigned* counts, int n_b
         warp_sums[lane] = z - w;
     }
     __syncthreads();
-    unsigned run = warp_sums[warp] + (x - sum);
-    for (int k = 0; k < per; k++) { unsigned v = mine[k]; mine[k] = run; run += v; }
+    *mine = tile_base + warp_sums[warp] + (x - v);
 }
 __global__ void k_ray_bin_scatter(const unsigned* __restrict__ ray_bin, int n, unsigned* cursors, int* perm) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -103,16 +132,24 @@ __global__ void k_ray_bin_scatter(const unsigned* __restrict__ ray_bin, int n, u
     perm[pos] = i;
 }
 int launch_ray_order(const SceneDev& s, const float4* rays, long long n, unsigned* bins, unsigned* ray_bin, int* perm, cudaStream_t st) {
-    // about 64 rays per bin, 2..5 bits per axis (+3 octant bits): 512 .. 262144 bins
-    int bits = 2;
-    while (bits < PT_RAY_ORDER_MAX_BITS && (n >> (3 * (bits + 1) + 3)) >= 64) bits++;
-    const int n_bins = 1 << (3 * bits + 3);
-    cudaMemsetAsync(bins, 0, sizeof(unsigned) * (n_bins < 1024 ? 1024 : n_bins), st);
+    // about PT_RAY_ORDER_PER_BIN rays per bin, 2..PT_RAY_ORDER_MAX_BITS bits per axis (+3 octant bits)
+    int bits = 2, max_bits = PT_RAY_ORDER_MAX_BITS, per_bin = PT_RAY_ORDER_PER_BIN;
+    if (const char* e = getenv("PT_RAY_ORDER_BITS")) max_bits = atoi(e);
+    if (const char* e = getenv("PT_RAY_ORDER_PER_BIN")) per_bin = atoi(e);
+    if (max_bits > PT_RAY_ORDER_MAX_BITS) max_bits = PT_RAY_ORDER_MAX_BITS;
+    if (per_bin < 1) per_bin = 1;
+    while (bits < max_bits && (n >> (3 * (bits + 1) + 3)) >= per_bin) bits++;
+    int n_bins = 1 << (3 * bits + 3);
+    if (n_bins < 1024) n_bins = 1024;
+    const int tiles = n_bins / 1024;
+    unsigned* tile_sums = bins + n_bins;
+    cudaMemsetAsync(bins, 0, sizeof(unsigned) * n_bins, st);
     const int blocks = (int)((n + 255) / 256);
     k_ray_bin<<<blocks, 256, 0, st>>>(s, rays, (int)n, bits, bins, ray_bin);
-    k_ray_bin_scan<<<1, 1024, 0, st>>>(bins, n_bins < 1024 ? 1024 : n_bins);
+    k_ray_bin_tile_sums<<<tiles, 1024, 0, st>>>(bins, tile_sums);
+    k_ray_bin_scan<<<tiles, 1024, 0, st>>>(bins, tile_sums);
     k_ray_bin_scatter<<<blocks, 256, 0, st>>>(ray_bin, (int)n, bins, perm);
-    return 3;
+    return 4;
 }
 
 template <bool ANY, class TR>

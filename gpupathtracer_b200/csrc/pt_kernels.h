@@ -37,7 +37,7 @@ void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, fl
                           const LaunchDims& dims, cudaStream_t st, const int* perm = nullptr);
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
                       const LaunchDims& dims, cudaStream_t st, const int* perm = nullptr);
-// processing order for a batch: counting sort of the rays by origin cell + direction octant. bins: >= 262144 counters,
+// processing order for a batch: counting sort of the rays by origin cell + direction octant. bins: 2097152 counters + 2048 tile totals,
 // ray_bin / perm: n entries each. Returns the number of kernels launched.
 int launch_ray_order(const SceneDev& s, const float4* rays, long long n, unsigned* bins, unsigned* ray_bin, int* perm, cudaStream_t st);
 

@@ -174,4 +174,4 @@ def test_ray_ordering_does_not_change_any_result(monkeypatch):
     for mode in ("-1", "1"):
         assert np.array_equal(out[mode][0].view(np.uint32), want.view(np.uint32))
         assert np.array_equal(out[mode][1], wflag)
-    assert out["1"][2] == out["-1"][2] + 6                       # 3 binning kernels per ordered launch
+    assert out["1"][2] == out["-1"][2] + 8                       # 4 binning kernels per ordered launch
