@@ -484,7 +484,9 @@ def run_micro(args, name, wl):
             line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                 "frac": achieved / peak, "traffic": traffic_for(name, "k_trace_batch<false>"),
                                 "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
-                                "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": steps, "avg_launch_ms": ms_c / steps}
+                                "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": steps, "avg_launch_ms": ms_c / steps,
+                                "note": "avg_launch_ms spans the ray binning (4 small kernels, ~0.35 ms, reference layout only) and "
+                                        "k_trace_batch; the binning halves the DRAM traffic of the trace (profiles/traffic.json)"}
         print(json.dumps(line))
     r.CleanUp()
     d.close()
