@@ -482,7 +482,8 @@ def run_micro(args, name, wl):
             b_ray, pairs, tris = bytes_per_ray(cc, m, B_HIT_OUT)
             achieved = n * b_ray / (ms_c / steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                "frac": achieved / peak, "traffic": traffic_for(name, "k_trace_batch<false>"),
+                                "frac": achieved / peak,
+                                "traffic": traffic_for(name, "k_trace_batch<false>" + {"wide": " wide-8", "wide4": " wide-4"}.get(args.bvh, "")),
                                 "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
                                 "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": steps, "avg_launch_ms": ms_c / steps,
                                 "note": "avg_launch_ms spans the ray binning (4 small kernels, ~0.35 ms, reference layout only) and "
