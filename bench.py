@@ -332,6 +332,24 @@ def run_pathtrace(args, name, wl):
     value = rays / (ms_total * 1e-3) / 1e6
     samples_per_s = world * args.steps * W * H / (ms_total * 1e-3)
 
+    # ---- the same K frames with every NEE sample traced, as the reference and the CPU arm do (pt_config.trace_null_shadow):
+    #      identical image, the ray population of the reference; reported beside `value`, not instead of it
+    r_all = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
+                                  seed=0xB200 ^ (rank * 0x9E3779B9), bvh="given", bvh_layout=LAYOUTS[args.bvh], trace_null_shadow=True)
+    for _ in range(warmup):
+        r_all.RenderFrame(cam, 1)
+    r_all.Synchronize()
+    ca0 = r_all.Counters()
+    d.barrier(r)
+    r_all.RenderFrame(cam, args.steps); r_all.Synchronize()
+    ms_all = r_all.LastDeviceMs()
+    ca1 = r_all.Counters()
+    r_all.CleanUp()
+    ms_all, rays_all = d.max_sum([ms_all + ms_reduce, float(ca1["closest_rays"] - ca0["closest_rays"] + ca1["shadow_rays"] - ca0["shadow_rays"])])
+    all_nee = {"value": rays_all / (ms_all * 1e-3) / 1e6, "unit": "Mrays/s", "samples_per_s": world * args.steps * W * H / (ms_all * 1e-3),
+               "ms_per_step": ms_all / args.steps,
+               "note": "pt_config.trace_null_shadow = 1: NEE samples with exactly zero radiance are traced too, the reference's ray population"}
+
     # ---- end to end through the public API with host buffers: camera in (H2D), presented 8-bit frame out (D2H)
     d.barrier(r)
     c2 = r.Counters()
@@ -350,6 +368,11 @@ def run_pathtrace(args, name, wl):
         peak, which = measured_peaks()
         line = {
             "metric": metric_name(name, wl), "value": value, "unit": "Mrays/s", "samples_per_s": samples_per_s,
+            "rays_per_step": {"closest": closest / args.steps, "shadow_traced": shadow / args.steps,
+                              "shadow_not_needed": float(c1["null_shadow_rays"] - c0["null_shadow_rays"]) / args.steps,
+                              "note": "rank 0's share for shadow_not_needed; NEE samples whose radiance is exactly 0 (light below the "
+                                      "horizon) are settled without a ray -- the reference traces them and adds 0; value counts traced rays only"},
+            "all_nee_samples_traced": all_nee,
             "n_gpus": world, "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],

@@ -27,7 +27,7 @@ class PtError(RuntimeError):
 class pt_config(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_depth", C.c_int32),
                 ("microfacet_model", C.c_int32), ("device", C.c_int32), ("bvh_layout", C.c_int32),
-                ("n_slices", C.c_int32), ("sun_light", C.c_int32), ("reserved", C.c_int32 * 4)]
+                ("n_slices", C.c_int32), ("sun_light", C.c_int32), ("trace_null_shadow", C.c_int32), ("reserved", C.c_int32 * 3)]
 
 
 class pt_camera(C.Structure):
@@ -41,7 +41,7 @@ class pt_texture(C.Structure):
 
 class pt_counters(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64),
-                ("frames", C.c_uint64), ("kernel_launches", C.c_uint64)]
+                ("frames", C.c_uint64), ("kernel_launches", C.c_uint64), ("null_shadow_rays", C.c_uint64)]
 
 
 class pt_bvh_stats(C.Structure):
@@ -369,9 +369,11 @@ class Renderer:
 
     # -- Renderer::Initialize, Renderer.cpp:448-636
     def Initialize(self, width, height, scene, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=PT_MICROFACET_GGX,
-                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0, bvh_layout=PT_BVH_REFERENCE, sun_light=False):
+                   device=0, rng_state=None, seed=None, bvh="given", n_slices=0, bvh_layout=PT_BVH_REFERENCE, sun_light=False,
+                   trace_null_shadow=False):
         cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
-                        device=device, bvh_layout=bvh_layout, n_slices=n_slices, sun_light=1 if sun_light else 0)
+                        device=device, bvh_layout=bvh_layout, n_slices=n_slices, sun_light=1 if sun_light else 0,
+                        trace_null_shadow=1 if trace_null_shadow else 0)
         ctx = C.c_void_p()
         _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
         self.ctx = ctx

@@ -181,6 +181,7 @@ int pt_create(const pt_config* cfg, pt_context** out) {
     }
     c->l2_bytes = (size_t)prop.l2CacheSize;
     if (const char* e = getenv("PT_RAY_ORDER")) c->ray_order = atoi(e);
+    if (const char* e = getenv("PT_TRACE_NULL_SHADOW")) c->cfg.trace_null_shadow = atoi(e);
     CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CK(cudaEventCreate(&c->ev0));
     CK(cudaEventCreate(&c->ev1));
@@ -762,7 +763,7 @@ static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, in
     p.cam = c->d_cam.p;
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.slice_first = first; p.slice_count = count < 0 ? c->cfg.width * c->cfg.height : count;
-    p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model; p.sun = c->cfg.sun_light ? 1 : 0;
+    p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model; p.sun = c->cfg.sun_light ? 1 : 0; p.trace_null = c->cfg.trace_null_shadow ? 1 : 0;
     p.rng_table = c->d_rng.p; p.accum = c->d_accum;
     const size_t o = (size_t)first;                              // the slice's sub-range of every per-path array
     for (int q = 0; q < 2; q++) {
@@ -1127,7 +1128,7 @@ int pt_get_counters(pt_context* c, pt_counters* out) {
     CK(cudaMemcpyAsync(t, c->d_totals.p, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     *out = c->counters;
-    out->closest_rays += t[0]; out->shadow_rays += t[1]; out->paths = t[2];
+    out->closest_rays += t[0]; out->shadow_rays += t[1]; out->paths = t[2]; out->null_shadow_rays = t[3];
     return PT_OK;
 }
 

@@ -256,7 +256,7 @@ k_shade(FrameParams p, int bounce, int qi) {
 
     for (int base = warp_id * 32; base < n; base += warps_total * 32) {
         const int i = base + lane;
-        bool alive = false, has_shadow = false;
+        bool alive = false, has_shadow = false, null_shadow = false;
         // outputs
         V3 vpos = v3(0.0f), newdir = v3(0.0f), thr = v3(0.0f), contrib = v3(0.0f), L = v3(0.0f), ldir = v3(0.0f), lorg = v3(0.0f);
         float pdf0 = 0.0f, pdf1 = 0.0f, tmax = 0.0f;
@@ -340,7 +340,11 @@ k_shade(FrameParams p, int bounce, int qi) {
                     L = lightThroughput * xyz(le);              // Iterative.comp:279
                 }
                 lorg = vpos + 0.001f * vnormal;
-                has_shadow = true;
+                // The reference traces this ray unconditionally (Iterative.comp:276-280). When L is exactly zero (light below
+                // the surface's horizon: n.i = 0) the answer cannot change the sum -- contribution + 0 -- so the sample is
+                // settled here and never queued. NaN / Inf radiance is not zero and takes the normal route.
+                has_shadow = p.trace_null || !(L.x == 0.0f && L.y == 0.0f && L.z == 0.0f);
+                null_shadow = !has_shadow;
 
                 // BSDF sample, Iterative.comp:282-288
                 newdir = importance_sample<MODEL>(mat, it, rng, pdf0, pdf1);
@@ -357,10 +361,12 @@ k_shade(FrameParams p, int bounce, int qi) {
         // ---- compaction: one atomic per warp per queue
         unsigned m_alive = __ballot_sync(0xffffffffu, alive);
         unsigned m_shadow = __ballot_sync(0xffffffffu, has_shadow);
+        unsigned m_null = __ballot_sync(0xffffffffu, null_shadow);
         int base_alive = 0, base_shadow = 0;
         if (lane == 0) {
             if (m_alive) base_alive = atomicAdd(&c[1].n_paths, __popc(m_alive));
             if (m_shadow) base_shadow = atomicAdd(&c->n_shadow, __popc(m_shadow));
+            if (m_null) atomicAdd(&c->n_null, __popc(m_null));
         }
         base_alive = __shfl_sync(0xffffffffu, base_alive, 0);
         base_shadow = __shfl_sync(0xffffffffu, base_shadow, 0);
@@ -372,7 +378,11 @@ k_shade(FrameParams p, int bounce, int qi) {
             qout.q1[j] = f4(newdir, pdf1);
             qout.q2[j] = f4(thr, __int_as_float(pix));
             qout.q4[j] = make_uint4(rng.x, rng.y, rng.z, rng.w);
-            // q3 (contribution) is written by k_shadow once visibility is known
+            // q3 (contribution) is written by k_shadow once visibility is known -- or here when no ray is needed
+            if (null_shadow) qout.q3[j] = f4(contrib, 0.0f);
+        } else if (null_shadow) {
+            float4 acc = p.accum[pix];                               // imageStore, Iterative.comp:295
+            p.accum[pix] = make_float4(acc.x + contrib.x, acc.y + contrib.y, acc.z + contrib.z, 1.0f);
         }
         if (has_shadow) {
             int k = base_shadow + __popc(m_shadow & lt_mask);
@@ -422,10 +432,11 @@ static void launch_shadow(const FrameParams& p, int b, int qi_next, const Launch
 
 __global__ void k_tally(FrameParams p) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    unsigned long long closest = 0, shadow = 0;
-    for (int b = 0; b < p.max_depth; b++) { closest += p.counters[b].n_paths; shadow += p.counters[b].n_shadow; }
+    unsigned long long closest = 0, shadow = 0, nulls = 0;
+    for (int b = 0; b < p.max_depth; b++) { closest += p.counters[b].n_paths; shadow += p.counters[b].n_shadow; nulls += p.counters[b].n_null; }
     // slices of one frame tally concurrently from different streams
     atomicAdd(&p.totals[0], closest); atomicAdd(&p.totals[1], shadow); atomicAdd(&p.totals[2], (unsigned long long)p.slice_count);
+    atomicAdd(&p.totals[3], nulls);
 }
 
 static void launch_shade(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {

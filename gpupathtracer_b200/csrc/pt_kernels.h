@@ -11,6 +11,7 @@ struct BounceCounters {
     int n_shadow;     // size of the shadow queue produced by this bounce's shade
     int fetch_extend; // persistent-kernel work cursors
     int fetch_shadow;
+    int n_null;       // NEE samples of this bounce whose radiance is exactly zero: not queued for a shadow ray
 };
 
 struct FrameParams {
@@ -21,13 +22,14 @@ struct FrameParams {
     int max_depth;
     int model;
     int sun;              // SUN_LIGHT (Iterative.comp:116-126), off in the reference as shipped
+    int trace_null;       // 1: queue a shadow ray even when its radiance is exactly 0 (pt_config.trace_null_shadow)
     uint4* rng_table;     // per pixel
     float4* accum;        // per pixel, running sum
     PathQueue queue[2];
     ShadowQueue shadow;
     float4* hits;         // per queue slot (queue, shadow and hit pointers are already offset to the slice's sub-range)
     BounceCounters* counters;   // [max_depth + 2], one block per slice
-    unsigned long long* totals; // [0] closest rays, [1] shadow rays, [2] paths
+    unsigned long long* totals; // [0] closest rays, [1] shadow rays traced, [2] paths, [3] shadow rays not needed (radiance 0)
 };
 
 struct LaunchDims { int sm_count; int extend_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; int wide; int top_pairs; };

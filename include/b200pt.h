@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200PT_ABI_VERSION 1
+#define B200PT_ABI_VERSION 2
 
 typedef enum pt_status {
     PT_OK = 0,
@@ -57,7 +57,11 @@ typedef struct pt_config {
                                      not depend on it (every pixel keeps its own RNG sequence). */
     int32_t sun_light;            /* 1 = compile the reference's `#ifdef SUN_LIGHT` branch in (Iterative.comp:116-126): NEE flips a
                                      coin between the emitter table and a sun disk. Off in the reference as shipped. */
-    int32_t reserved[4];
+    int32_t trace_null_shadow;    /* 0 (default): an NEE sample whose radiance is exactly 0 whatever the visibility (light below
+                                     the surface's horizon) is settled without a shadow ray -- same image bits, ~1/3 fewer
+                                     shadow rays on the atrium. 1: trace it anyway, as the reference does, so that ray
+                                     counts are comparable one to one with the reference's. */
+    int32_t reserved[3];
 } pt_config;
 
 /* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
@@ -89,6 +93,9 @@ typedef struct pt_light {          /* LightTriangleInfo after the prefix sum, Sc
 typedef struct pt_counters {
     uint64_t closest_rays, shadow_rays, paths, frames;
     uint64_t kernel_launches;      /* kernels of this library launched since pt_create */
+    uint64_t null_shadow_rays;     /* NEE samples whose radiance is exactly 0 (light below the horizon): the reference traces
+                                      their shadow ray and adds 0, this library settles them without a ray; not part of
+                                      shadow_rays, which counts rays actually traced */
 } pt_counters;
 
 typedef struct pt_bvh_stats {

@@ -48,7 +48,7 @@ class OrConfig(C.Structure):
 class OrCounters(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("node_pairs", C.c_uint64),
                 ("leaf_visits", C.c_uint64), ("tri_tests", C.c_uint64), ("paths", C.c_uint64),
-                ("shadow_node_pairs", C.c_uint64), ("shadow_tri_tests", C.c_uint64)]
+                ("shadow_node_pairs", C.c_uint64), ("shadow_tri_tests", C.c_uint64), ("null_shadow_rays", C.c_uint64)]
 
     def as_dict(self):
         return {k: int(getattr(self, k)) for k, _ in self._fields_}

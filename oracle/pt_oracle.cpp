@@ -62,7 +62,7 @@ struct Rng {
 
 // ---------------------------------------------------------------- traversal
 struct Hit { float t, u, v; int tri; };
-struct Cnt { uint64_t pairs = 0, leaves = 0, tris = 0; std::vector<uint8_t>* ops = nullptr; };   // ops: optional per-step trace (0 = pair test, 1 = triangle test)
+struct Cnt { uint64_t pairs = 0, leaves = 0, tris = 0, nulls = 0; std::vector<uint8_t>* ops = nullptr; };   // ops: optional per-step trace (0 = pair test, 1 = triangle test)
 
 // IntersectNodeFast, BVH.glsl:379-391. iray = {o' = -o/d, 1/d}.
 inline float slab(const float* node, const Ray& iray, float tcur, bool& hit) {
@@ -214,7 +214,7 @@ void add_counters(OrCounters* c, const Cnt& k, uint64_t closest, uint64_t shadow
     if (!c) return;
     // callers serialise this
     c->node_pairs += k.pairs; c->leaf_visits += k.leaves; c->tri_tests += k.tris;
-    if (shadowShare) { c->shadow_node_pairs += shadowShare->pairs; c->shadow_tri_tests += shadowShare->tris; }
+    if (shadowShare) { c->shadow_node_pairs += shadowShare->pairs; c->shadow_tri_tests += shadowShare->tris; c->null_shadow_rays += shadowShare->nulls; }
     c->closest_rays += closest; c->shadow_rays += shadow; c->paths += paths;
 }
 
@@ -605,6 +605,13 @@ void trace_path(const OrScene& s, const OrCamera& cam, const OrConfig& cfg, int 
         Ray lightRay = light_sample(s, cfg, vpos, vnormal, mat, it, rng, tmax, p.throughput, lightThroughput, lightMat);
         Hit lh; lh.t = tmax; lh.u = lh.v = 0; lh.tri = -1;
         nShadow++;
+        {
+            // bookkeeping only (the reference always traces the ray): samples whose radiance is exactly zero whatever the
+            // visibility (light below the horizon: n.i = 0) -- the CUDA path does not trace those
+            const float* lm0 = s.materials + 12 * (size_t)(lightMat >> 1);
+            V3 L = lightThroughput * v3(lm0[4], lm0[5], lm0[6]);
+            if (L.x == 0.0f && L.y == 0.0f && L.z == 0.0f) scnt.nulls++;
+        }
         if (!any_hit(s, lightRay, lh, scnt)) {
             const float* lm = s.materials + 12 * (size_t)(lightMat >> 1);
             p.contribution = p.contribution + lightThroughput * v3(lm[4], lm[5], lm[6]);

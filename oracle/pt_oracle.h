@@ -81,6 +81,7 @@ typedef struct OrCounters {
     uint64_t node_pairs, leaf_visits, tri_tests;   /* summed over both ray kinds */
     uint64_t paths;
     uint64_t shadow_node_pairs, shadow_tri_tests;  /* the any-hit share of node_pairs / tri_tests */
+    uint64_t null_shadow_rays;                     /* shadow rays (counted in shadow_rays) whose radiance is exactly 0 */
 } OrCounters;
 
 /* ---- scalar pieces ---- */

@@ -93,7 +93,9 @@ def test_frames_match_oracle(name, depth, model):
     assert np.array_equal(np.isnan(got[..., 0]), np.isnan(want[..., 0])) or frac > 0.999
     # ray counters (device-side) agree with the oracle's to the same tolerance
     assert abs(cnt["closest_rays"] - c["closest_rays"]) <= 0.005 * c["closest_rays"]
-    assert abs(cnt["shadow_rays"] - c["shadow_rays"]) <= 0.005 * c["shadow_rays"]
+    # the oracle, like the reference, traces every NEE shadow ray; the CUDA path skips those whose radiance is exactly 0
+    assert abs(cnt["shadow_rays"] + cnt["null_shadow_rays"] - c["shadow_rays"]) <= 0.005 * c["shadow_rays"]
+    assert abs(cnt["null_shadow_rays"] - c["null_shadow_rays"]) <= 0.005 * c["shadow_rays"]
     assert rel_mse(got[..., :3], want[..., :3]) < 1e-3
 
 
@@ -193,3 +195,22 @@ def test_checkpoint_resume_is_bit_identical(tmp_path):
     r2.RenderFrame(cam, 1)
     assert r2.GetNumSamples() == 9
     r2.CleanUp(); r3.CleanUp()
+
+
+def test_null_radiance_shadow_samples_need_no_ray():
+    """An NEE sample whose radiance is exactly 0 (light below the horizon) cannot change the pixel: by default it is settled
+    without a shadow ray. With trace_null_shadow the reference's ray population is traced; image and RNG are the same bits."""
+    s = get_scene("atrium_small")
+    w, h = 64, 64
+    cam = make_camera(s.data, w, h)
+    rng = make_rng_table(w * h, 17)
+    res = []
+    for trace_all in (False, True):
+        r = _renderer(s, w, h, max_depth=5, rng_state=rng, trace_null_shadow=trace_all)
+        r.RenderFrame(cam, 4)
+        res.append((r.DownloadAccum(), r.GetRNG(), r.Counters()))
+        r.CleanUp()
+    (a0, g0, c0), (a1, g1, c1) = res
+    assert np.array_equal(np.nan_to_num(a0, nan=-1.0), np.nan_to_num(a1, nan=-1.0)) and np.array_equal(g0, g1)
+    assert c1["null_shadow_rays"] == 0 and c0["null_shadow_rays"] > 0.1 * c1["shadow_rays"]
+    assert c0["shadow_rays"] + c0["null_shadow_rays"] == c1["shadow_rays"] and c0["closest_rays"] == c1["closest_rays"]
