@@ -465,7 +465,11 @@ int pt_load_environment(pt_context* c, const char* args) {
         if (!load_hdr_rgba32f(a, w, h, px, err)) return fail(PT_ERR_IO, "pt_load_environment: %s", err.c_str());
         return pt_set_environment_equirect(c, px.data(), w, h, 1024);
     }
-    if (ext == "jpg") return fail(PT_ERR_UNSUPPORTED, "pt_load_environment: %s: no JPEG decoder in this build (convert to .hdr)", args);
+    if (ext == "jpg") {                                           // stbi_loadf on an 8-bit file: gamma-2.2 expansion, then the same passes
+        int w = 0, h = 0; std::vector<float> px; std::string err;
+        if (!load_ldr_as_hdr_rgba32f(a, w, h, px, err)) return fail(PT_ERR_IO, "pt_load_environment: %s", err.c_str());
+        return pt_set_environment_equirect(c, px.data(), w, h, 1024);
+    }
     // TextureCubemap::LoadTexture (Texture.cpp:245-276): six lines (those starting with '#' skipped), paths relative
     // to the list's folder, order +X -X +Y -Y +Z -Z, each decoded to RGBA bytes -> normalised floats
     std::string path = a;

@@ -63,7 +63,9 @@ struct SceneFile;
 bool load_obj_file(const std::string& path, SceneFile& out, std::string& err);
 bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<float>& rgba);
 bool decode_png_rgba8(const std::vector<unsigned char>& file, int& w, int& h, std::vector<unsigned char>& rgba);          // pt_image.cpp
+bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& w, int& h, std::vector<unsigned char>& rgba, std::string& err);   // pt_image.cpp
 bool write_png_rgb8(const char* path, int w, int h, const unsigned char* rgb_top_down);                                    // pt_image.cpp
+bool load_ldr_as_hdr_rgba32f(const std::string& path, int& w, int& h, std::vector<float>& rgba, std::string& err);        // pt_image.cpp
 bool load_hdr_rgba32f(const std::string& path, int& w, int& h, std::vector<float>& rgba, std::string& err);   // pt_image.cpp
 void set_last_error(const char* msg);       // message returned by pt_last_error() on this thread
 

@@ -1,4 +1,5 @@
-// pt_image.cpp -- Radiance .hdr (RGBE) reader for the environment path; PNG reader (map_Kd, cube faces) and writer (SaveScreenshot).
+// pt_image.cpp -- Radiance .hdr (RGBE) reader for the environment path; PNG and JPEG readers (map_Kd, cube faces, .jpg environment),
+// PNG writer (SaveScreenshot).
 //
 // The reference reads its equirectangular environment with stbi_loadf(path, &w, &h, &c, 4) (Renderer.cpp:262-266; stb_image
 // comes with SOIL2, extern/soil2-cmake/src/SOIL2/stb_image.h). This restates what that call yields for a Radiance file:
@@ -8,7 +9,7 @@
 //     a scanline that does not start that way switches the reader to flat 4-byte pixels -- and, like stb, restarts the
 //     flat read at pixel 1 of row 0 (only right when it happens on the first row; kept for identical output)
 //   * pixel = byte * 2^(e - 136), alpha 1, e == 0 -> black; rows in file order (no flip); reads past the end yield 0
-// oracle/ref_stbi.cpp compiles stb_image in place as the checker (tests/test_environment.py).
+// oracle/ref_stbi.c compiles stb_image in place as the checker (tests/test_environment.py).
 #include "pt_host.h"
 #include <algorithm>
 #include <cmath>
@@ -350,6 +351,386 @@ bool decode_png_rgba8(const std::vector<unsigned char>& b, int& w, int& h, std::
     return true;
 }
 
+// ------------------------------------------------------------------------------------------------ JPEG
+// Baseline / extended-sequential Huffman JPEG (SOF0, SOF1; 8 bit; 1, 3 or 4 components; any sampling factors; restart
+// intervals) decoded to RGBA8 exactly as stbi_load(.., 4) of the reference's stb_image v2.15 does, which pins four things
+// the JPEG standard leaves open:
+//   * the inverse DCT: the integer "islow" scheme with 12-bit constants computed as (int)(c * 4096 + 0.5) -- truncation,
+//     so negative constants round towards zero --, column pass kept at 2 extra bits (+512 >> 10, or dc << 2 when the
+//     column's AC terms are all zero), row pass + 65536 + (128 << 17) >> 17, clamped to 0..255
+//   * chroma upsampling: 2x horizontally / vertically / both with the (3 * near + far) triangle filter and stb's rounding
+//     (+2 >> 2 once, +8 >> 4 for the 2x2 case computed from the vertically filtered row), edge samples replicated; any
+//     other factor by sample replication; the far row of the last image row is the last row that carries image data
+//   * YCbCr -> RGB in 20-bit fixed point with constants ((int)(c * 4096.0f + 0.5f)) << 8 and the green Cb term masked to
+//     its upper 16 bits; components named 'R','G','B', or an Adobe segment with transform 0 in a file without JFIF
+//     header, are taken as RGB; four components as CMYK / YCCK per the Adobe transform, multiplied out with
+//     (x * k + 128 + ((x * k + 128) >> 8)) >> 8
+//   * the decode covers whole MCUs; the picture is the top-left width x height of the padded planes
+// Progressive files (SOF2) are refused (stb decodes them; here PT_ERR_IO says so).
+namespace {
+
+struct JpegHuff {
+    unsigned char size[257]; unsigned short code[256]; unsigned char value[256];
+    int maxcode[18], delta[17]; int n = 0;
+    bool build(const int* counts) {                               // ITU T.81 Annex C
+        int k = 0;
+        for (int i = 0; i < 16; i++) for (int j = 0; j < counts[i]; j++) { if (k >= 256) return false; size[k++] = (unsigned char)(i + 1); }
+        size[k] = 0; n = k;
+        int c = 0; k = 0;
+        for (int l = 1; l <= 16; l++) {
+            delta[l] = k - c;
+            if (size[k] == l) {
+                while (size[k] == l) code[k++] = (unsigned short)c++;
+                if (c - 1 >= (1 << l)) return false;
+            }
+            maxcode[l] = c << (16 - l);
+            c <<= 1;
+        }
+        maxcode[17] = 0x7fffffff;
+        return true;
+    }
+};
+
+struct JpegBits {
+    const unsigned char* p; size_t n, pos = 0;
+    unsigned buf = 0; int cnt = 0; int marker = 0xff; bool nomore = false;   // marker 0xff: none pending
+    int byte() { return pos < n ? p[pos++] : 0; }
+    bool eof() const { return pos >= n; }
+    void fill() {
+        do {
+            int b = nomore ? 0 : byte();
+            if (b == 0xff) {
+                int c = byte();
+                while (c == 0xff) c = byte();
+                if (c != 0) { marker = c; nomore = true; return; }
+            }
+            buf |= (unsigned)b << (24 - cnt);
+            cnt += 8;
+        } while (cnt <= 24);
+    }
+    int decode(const JpegHuff& h) {                               // Annex F.2.2.3, 16 bits looked at at once
+        if (cnt < 16) fill();
+        unsigned top = buf >> 16;
+        int l = 1;
+        while (l <= 16 && (int)top >= h.maxcode[l]) l++;
+        if (l > 16 || l > cnt) return -1;
+        int idx = (int)((buf >> (32 - l)) & ((1u << l) - 1u)) + h.delta[l];
+        if (idx < 0 || idx >= h.n) return -1;
+        buf <<= l; cnt -= l;
+        return h.value[idx];
+    }
+    int receive_extend(int s) {                                   // F.2.2.1 RECEIVE + EXTEND
+        if (cnt < s) fill();
+        int v = (int)(buf >> (32 - s));
+        buf <<= s; cnt -= s;
+        return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v;
+    }
+    void reset() { buf = 0; cnt = 0; nomore = false; marker = 0xff; }
+};
+
+const unsigned char kDezigzag[64 + 15] = {
+    0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63,
+    63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};
+
+inline int jfix(float c) { return (int)(c * 4096 + 0.5); }
+inline unsigned char jclamp(int x) { return (unsigned char)(x < 0 ? 0 : x > 255 ? 255 : x); }
+
+// one 8-point pass of the "islow" inverse DCT; even part in x[0..3], odd part in t[0..3]
+inline void idct_1d(int s0, int s1, int s2, int s3, int s4, int s5, int s6, int s7, int x[4], int t[4]) {
+    int p2 = s2, p3 = s6;
+    int p1 = (p2 + p3) * jfix(0.5411961f);
+    int t2 = p1 + p3 * jfix(-1.847759065f);
+    int t3 = p1 + p2 * jfix(0.765366865f);
+    p2 = s0; p3 = s4;
+    int t0 = (p2 + p3) * 4096, t1 = (p2 - p3) * 4096;
+    x[0] = t0 + t3; x[3] = t0 - t3; x[1] = t1 + t2; x[2] = t1 - t2;
+    t0 = s7; t1 = s5; t2 = s3; t3 = s1;
+    p3 = t0 + t2; int p4 = t1 + t3; p1 = t0 + t3; p2 = t1 + t2;
+    int p5 = (p3 + p4) * jfix(1.175875602f);
+    t0 = t0 * jfix(0.298631336f); t1 = t1 * jfix(2.053119869f); t2 = t2 * jfix(3.072711026f); t3 = t3 * jfix(1.501321110f);
+    p1 = p5 + p1 * jfix(-0.899976223f); p2 = p5 + p2 * jfix(-2.562915447f);
+    p3 = p3 * jfix(-1.961570560f); p4 = p4 * jfix(-0.390180644f);
+    t[3] = t3 + p1 + p4; t[2] = t2 + p2 + p3; t[1] = t1 + p2 + p4; t[0] = t0 + p1 + p3;
+}
+void idct_block(unsigned char* out, int stride, const short d[64]) {
+    int v[64];
+    for (int i = 0; i < 8; i++) {
+        if (d[i + 8] == 0 && d[i + 16] == 0 && d[i + 24] == 0 && d[i + 32] == 0 && d[i + 40] == 0 && d[i + 48] == 0 && d[i + 56] == 0) {
+            int dc = d[i] * 4;
+            for (int r = 0; r < 8; r++) v[i + 8 * r] = dc;
+        } else {
+            int x[4], t[4];
+            idct_1d(d[i], d[i + 8], d[i + 16], d[i + 24], d[i + 32], d[i + 40], d[i + 48], d[i + 56], x, t);
+            for (int k = 0; k < 4; k++) x[k] += 512;
+            v[i] = (x[0] + t[3]) >> 10; v[i + 56] = (x[0] - t[3]) >> 10;
+            v[i + 8] = (x[1] + t[2]) >> 10; v[i + 48] = (x[1] - t[2]) >> 10;
+            v[i + 16] = (x[2] + t[1]) >> 10; v[i + 40] = (x[2] - t[1]) >> 10;
+            v[i + 24] = (x[3] + t[0]) >> 10; v[i + 32] = (x[3] - t[0]) >> 10;
+        }
+    }
+    for (int r = 0; r < 8; r++) {
+        const int* w = v + 8 * r; unsigned char* o = out + (size_t)r * stride;
+        int x[4], t[4];
+        idct_1d(w[0], w[1], w[2], w[3], w[4], w[5], w[6], w[7], x, t);
+        for (int k = 0; k < 4; k++) x[k] += 65536 + (128 << 17);
+        o[0] = jclamp((x[0] + t[3]) >> 17); o[7] = jclamp((x[0] - t[3]) >> 17);
+        o[1] = jclamp((x[1] + t[2]) >> 17); o[6] = jclamp((x[1] - t[2]) >> 17);
+        o[2] = jclamp((x[2] + t[1]) >> 17); o[5] = jclamp((x[2] - t[1]) >> 17);
+        o[3] = jclamp((x[3] + t[0]) >> 17); o[4] = jclamp((x[3] - t[0]) >> 17);
+    }
+}
+
+struct JpegComp {
+    int id = 0, h = 1, v = 1, tq = 0, hd = 0, ha = 0, dc_pred = 0;
+    int x = 0, y = 0, w2 = 0, h2 = 0;                             // effective size, padded plane size
+    std::vector<unsigned char> data;
+};
+
+inline unsigned char blinn8(unsigned x, unsigned y) { unsigned t = x * y + 128; return (unsigned char)((t + (t >> 8)) >> 8); }
+
+}  // namespace
+
+bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& height, std::vector<unsigned char>& rgba, std::string& err) {
+    JpegBits br{file.data(), file.size()};
+    auto get16 = [&]() { int a = br.byte(); return (a << 8) | br.byte(); };
+    auto next_marker = [&]() -> int {                             // 0xff: no marker at this position
+        if (br.marker != 0xff) { int m = br.marker; br.marker = 0xff; return m; }
+        int x = br.byte();
+        if (x != 0xff) return 0xff;
+        while (x == 0xff) x = br.byte();
+        return x;
+    };
+    if (next_marker() != 0xd8) { err = "not a JPEG file"; return false; }
+    JpegHuff hdc[4], hac[4]; bool have_dc[4] = {}, have_ac[4] = {};
+    unsigned short dequant[4][64] = {};
+    JpegComp comp[4]; int ncomp = 0, order[4] = {}, scan_n = 0;
+    int restart = 0, adobe = -1, rgb_ids = 0; bool jfif = false, have_frame = false;
+    int hmax = 1, vmax = 1, mcux = 0, mcuy = 0;
+    auto table_marker = [&](int m) -> bool {
+        if (m == 0xdd) { if (get16() != 4) return false; restart = get16(); return true; }
+        if (m == 0xdb) {
+            int L = get16() - 2;
+            while (L > 0) {
+                int q = br.byte(), p = q >> 4, t = q & 15;
+                if ((p != 0 && p != 1) || t > 3) return false;
+                for (int i = 0; i < 64; i++) dequant[t][kDezigzag[i]] = (unsigned short)(p ? get16() : br.byte());
+                L -= p ? 129 : 65;
+            }
+            return L == 0;
+        }
+        if (m == 0xc4) {
+            int L = get16() - 2;
+            while (L > 0) {
+                int q = br.byte(), tc = q >> 4, th = q & 15, counts[16], n = 0;
+                if (tc > 1 || th > 3) return false;
+                for (int i = 0; i < 16; i++) { counts[i] = br.byte(); n += counts[i]; }
+                if (n > 256) return false;
+                JpegHuff& h = tc ? hac[th] : hdc[th];
+                if (!h.build(counts)) return false;
+                for (int i = 0; i < n; i++) h.value[i] = (unsigned char)br.byte();
+                (tc ? have_ac : have_dc)[th] = true;
+                L -= 17 + n;
+            }
+            return L == 0;
+        }
+        if ((m >= 0xe0 && m <= 0xef) || m == 0xfe) {
+            int L = get16();
+            if (L < 2) return false;
+            L -= 2;
+            if (m == 0xe0 && L >= 5) {
+                const char tag[5] = {'J', 'F', 'I', 'F', 0}; bool ok = true;
+                for (int i = 0; i < 5; i++) if (br.byte() != (unsigned char)tag[i]) ok = false;
+                L -= 5;
+                if (ok) jfif = true;
+            } else if (m == 0xee && L >= 12) {
+                const char tag[6] = {'A', 'd', 'o', 'b', 'e', 0}; bool ok = true;
+                for (int i = 0; i < 6; i++) if (br.byte() != (unsigned char)tag[i]) ok = false;
+                L -= 6;
+                if (ok) { br.byte(); get16(); get16(); adobe = br.byte(); L -= 6; }
+            }
+            br.pos = std::min(br.n, br.pos + (size_t)L);
+            return true;
+        }
+        return false;
+    };
+    // ---- tables and frame header
+    int m = next_marker();
+    while (!(m == 0xc0 || m == 0xc1 || m == 0xc2)) {
+        if (m == 0xff || !table_marker(m)) { err = "corrupt JPEG (marker before the frame header)"; return false; }
+        m = next_marker();
+        while (m == 0xff) { if (br.eof()) { err = "corrupt JPEG (no frame header)"; return false; } m = next_marker(); }
+    }
+    if (m == 0xc2) { err = "progressive JPEG is not supported"; return false; }
+    {
+        int Lf = get16(), prec = br.byte();
+        height = get16(); width = get16(); ncomp = br.byte();
+        if (Lf < 11 || prec != 8 || height <= 0 || width <= 0 || (ncomp != 1 && ncomp != 3 && ncomp != 4) || Lf != 8 + 3 * ncomp) { err = "unsupported JPEG frame header"; return false; }
+        for (int i = 0; i < ncomp; i++) {
+            comp[i].id = br.byte();
+            if (ncomp == 3 && comp[i].id == "RGB"[i]) rgb_ids++;
+            int q = br.byte();
+            comp[i].h = q >> 4; comp[i].v = q & 15; comp[i].tq = br.byte();
+            if (comp[i].h < 1 || comp[i].h > 4 || comp[i].v < 1 || comp[i].v > 4 || comp[i].tq > 3) { err = "corrupt JPEG (component)"; return false; }
+            hmax = std::max(hmax, comp[i].h); vmax = std::max(vmax, comp[i].v);
+        }
+        if ((double)width * height > 1.0e9) { err = "JPEG too large"; return false; }
+        mcux = (width + hmax * 8 - 1) / (hmax * 8); mcuy = (height + vmax * 8 - 1) / (vmax * 8);
+        for (int i = 0; i < ncomp; i++) {
+            comp[i].x = (width * comp[i].h + hmax - 1) / hmax; comp[i].y = (height * comp[i].v + vmax - 1) / vmax;
+            comp[i].w2 = mcux * comp[i].h * 8; comp[i].h2 = mcuy * comp[i].v * 8;
+            comp[i].data.assign((size_t)comp[i].w2 * comp[i].h2, 0);
+        }
+        have_frame = true;
+    }
+    // ---- scans
+    auto decode_block = [&](JpegComp& c, short data[64]) -> bool {
+        if (!have_dc[c.hd] || !have_ac[c.ha]) return false;
+        const unsigned short* dq = dequant[c.tq];
+        int t = br.decode(hdc[c.hd]);
+        if (t < 0 || t > 15) return false;
+        std::memset(data, 0, 64 * sizeof(short));
+        int diff = t ? br.receive_extend(t) : 0;
+        c.dc_pred += diff;
+        data[0] = (short)(c.dc_pred * dq[0]);
+        int k = 1;
+        do {
+            int rs = br.decode(hac[c.ha]);
+            if (rs < 0) return false;
+            int s = rs & 15, r = rs >> 4;
+            if (s == 0) { if (rs != 0xf0) break; k += 16; }
+            else { k += r; int zig = kDezigzag[k++]; data[zig] = (short)(br.receive_extend(s) * dq[zig]); }
+        } while (k < 64);
+        return true;
+    };
+    m = next_marker();
+    while (m != 0xd9) {
+        if (m == 0xda) {
+            int Ls = get16(); scan_n = br.byte();
+            if (scan_n < 1 || scan_n > 4 || scan_n > ncomp || Ls != 6 + 2 * scan_n) { err = "corrupt JPEG (scan header)"; return false; }
+            for (int i = 0; i < scan_n; i++) {
+                int id = br.byte(), q = br.byte(), which = 0;
+                while (which < ncomp && comp[which].id != id) which++;
+                if (which == ncomp || (q >> 4) > 3 || (q & 15) > 3) { err = "corrupt JPEG (scan component)"; return false; }
+                comp[which].hd = q >> 4; comp[which].ha = q & 15; order[i] = which;
+            }
+            int ss = br.byte(); br.byte(); int a = br.byte();
+            if (ss != 0 || a != 0) { err = "corrupt JPEG (spectral selection in a sequential scan)"; return false; }
+            br.reset();
+            for (int i = 0; i < 4; i++) comp[i].dc_pred = 0;
+            int todo = restart ? restart : 0x7fffffff;
+            short data[64];
+            bool stop = false;
+            auto after_mcu = [&]() {                              // restart interval bookkeeping; true: leave the scan
+                if (--todo > 0) return false;
+                if (br.cnt < 24) br.fill();
+                if (!(br.marker >= 0xd0 && br.marker <= 0xd7)) return true;
+                br.reset();
+                for (int i = 0; i < 4; i++) comp[i].dc_pred = 0;
+                todo = restart ? restart : 0x7fffffff;
+                return false;
+            };
+            if (scan_n == 1) {
+                JpegComp& c = comp[order[0]];
+                int bw = (c.x + 7) >> 3, bh = (c.y + 7) >> 3;
+                for (int j = 0; j < bh && !stop; j++)
+                    for (int i = 0; i < bw && !stop; i++) {
+                        if (!decode_block(c, data)) { err = "corrupt JPEG (entropy-coded data)"; return false; }
+                        idct_block(c.data.data() + (size_t)c.w2 * j * 8 + i * 8, c.w2, data);
+                        stop = after_mcu();
+                    }
+            } else {
+                for (int j = 0; j < mcuy && !stop; j++)
+                    for (int i = 0; i < mcux && !stop; i++) {
+                        for (int k = 0; k < scan_n; k++) {
+                            JpegComp& c = comp[order[k]];
+                            for (int y = 0; y < c.v; y++)
+                                for (int x = 0; x < c.h; x++) {
+                                    if (!decode_block(c, data)) { err = "corrupt JPEG (entropy-coded data)"; return false; }
+                                    idct_block(c.data.data() + (size_t)c.w2 * ((j * c.v + y) * 8) + (i * c.h + x) * 8, c.w2, data);
+                                }
+                        }
+                        stop = after_mcu();
+                    }
+            }
+            if (br.marker == 0xff) {                              // padding after the scan: look for the next 0xff xx
+                while (!br.eof()) { if (br.byte() == 255) { br.marker = br.byte(); break; } }
+            }
+        } else if (m == 0xdc) { get16(); get16(); }
+        else if (m == 0xff || !table_marker(m)) { err = "corrupt JPEG (marker)"; return false; }
+        m = next_marker();
+    }
+    if (!have_frame) return false;
+    // ---- upsample + colour conversion, row by row
+    const bool is_rgb = ncomp == 3 && (rgb_ids == 3 || (adobe == 0 && !jfif));
+    rgba.assign((size_t)width * height * 4, 255);
+    struct Up { int hs, vs, ystep, ypos, w_lores; const unsigned char *line0, *line1; std::vector<unsigned char> buf; };
+    Up up[4];
+    for (int k = 0; k < ncomp; k++) {
+        up[k].hs = hmax / comp[k].h; up[k].vs = vmax / comp[k].v;
+        up[k].ystep = up[k].vs >> 1; up[k].ypos = 0;
+        up[k].w_lores = (width + up[k].hs - 1) / up[k].hs;
+        up[k].line0 = up[k].line1 = comp[k].data.data();
+        up[k].buf.assign((size_t)up[k].w_lores * std::max(up[k].hs, 1) + 8, 0);
+    }
+    const int c_r = ((int)(1.40200f * 4096.0f + 0.5f)) << 8, c_g1 = ((int)(0.71414f * 4096.0f + 0.5f)) << 8;
+    const int c_g2 = ((int)(0.34414f * 4096.0f + 0.5f)) << 8, c_b = ((int)(1.77200f * 4096.0f + 0.5f)) << 8;
+    for (int j = 0; j < height; j++) {
+        const unsigned char* row[4] = {nullptr, nullptr, nullptr, nullptr};
+        for (int k = 0; k < ncomp; k++) {
+            Up& u = up[k];
+            const bool bottom = u.ystep >= (u.vs >> 1);
+            const unsigned char* near = bottom ? u.line1 : u.line0; const unsigned char* far = bottom ? u.line0 : u.line1;
+            unsigned char* o = u.buf.data();
+            const int w = u.w_lores;
+            if (u.hs == 1 && u.vs == 1) row[k] = near;
+            else if (u.hs == 1 && u.vs == 2) { for (int i = 0; i < w; i++) o[i] = (unsigned char)((3 * near[i] + far[i] + 2) >> 2); row[k] = o; }
+            else if (u.hs == 2 && u.vs == 1) {
+                if (w == 1) o[0] = o[1] = near[0];
+                else {
+                    o[0] = near[0]; o[1] = (unsigned char)((near[0] * 3 + near[1] + 2) >> 2);
+                    int i = 1;
+                    for (; i < w - 1; i++) { int n3 = 3 * near[i] + 2; o[2 * i] = (unsigned char)((n3 + near[i - 1]) >> 2); o[2 * i + 1] = (unsigned char)((n3 + near[i + 1]) >> 2); }
+                    o[2 * i] = (unsigned char)((near[w - 2] * 3 + near[w - 1] + 2) >> 2); o[2 * i + 1] = near[w - 1];
+                }
+                row[k] = o;
+            } else if (u.hs == 2 && u.vs == 2) {
+                if (w == 1) o[0] = o[1] = (unsigned char)((3 * near[0] + far[0] + 2) >> 2);
+                else {
+                    int t1 = 3 * near[0] + far[0];
+                    o[0] = (unsigned char)((t1 + 2) >> 2);
+                    for (int i = 1; i < w; i++) {
+                        int t0 = t1; t1 = 3 * near[i] + far[i];
+                        o[2 * i - 1] = (unsigned char)((3 * t0 + t1 + 8) >> 4); o[2 * i] = (unsigned char)((3 * t1 + t0 + 8) >> 4);
+                    }
+                    o[2 * w - 1] = (unsigned char)((t1 + 2) >> 2);
+                }
+                row[k] = o;
+            } else { for (int i = 0; i < w; i++) for (int q = 0; q < u.hs; q++) o[i * u.hs + q] = near[i]; row[k] = o; }
+            if (++u.ystep >= u.vs) {
+                u.ystep = 0; u.line0 = u.line1;
+                if (++u.ypos < comp[k].y) u.line1 += comp[k].w2;
+            }
+        }
+        unsigned char* out = &rgba[(size_t)j * width * 4];
+        auto ycc = [&](int i, unsigned char* o) {
+            int yf = (row[0][i] << 20) + (1 << 19), cr = row[2][i] - 128, cb = row[1][i] - 128;
+            int r = yf + cr * c_r, g = yf + cr * -c_g1 + (int)((unsigned)(cb * -c_g2) & 0xffff0000u), b = yf + cb * c_b;
+            o[0] = jclamp(r >> 20); o[1] = jclamp(g >> 20); o[2] = jclamp(b >> 20);
+        };
+        for (int i = 0; i < width; i++) {
+            unsigned char* o = out + 4 * i;
+            if (ncomp == 1) o[0] = o[1] = o[2] = row[0][i];
+            else if (ncomp == 3) { if (is_rgb) { o[0] = row[0][i]; o[1] = row[1][i]; o[2] = row[2][i]; } else ycc(i, o); }
+            else if (adobe == 0) { unsigned k = row[3][i]; o[0] = blinn8(row[0][i], k); o[1] = blinn8(row[1][i], k); o[2] = blinn8(row[2][i], k); }
+            else if (adobe == 2) { unsigned k = row[3][i]; ycc(i, o); o[0] = blinn8(255u - o[0], k); o[1] = blinn8(255u - o[1], k); o[2] = blinn8(255u - o[2], k); }
+            else ycc(i, o);
+            o[3] = 255;
+        }
+    }
+    return true;
+}
+
 bool write_png_rgb8(const char* path, int w, int h, const unsigned char* rgb_top_down) {
     static uint32_t crc_table[256]; static bool have_table = false;
     if (!have_table) {
@@ -395,12 +776,44 @@ bool write_png_rgb8(const char* path, int w, int h, const unsigned char* rgb_top
     return std::fclose(f) == 0;
 }
 
+// stbi_loadf(path, .., 4) for a file that is NOT Radiance (the ".jpg" environment branch, Renderer.cpp:262-266): the 8-bit
+// decode goes through stbi__ldr_to_hdr -- colour = (float)(pow(byte / 255.0f, 2.2f) * 1.0f) evaluated in double (SOIL2.c is
+// C: pow is the double one, its arguments the float quotient and the float constant 2.2f), alpha = byte / 255.0f.
+bool load_ldr_as_hdr_rgba32f(const std::string& path, int& w, int& h, std::vector<float>& rgba, std::string& err) {
+    std::vector<unsigned char> file;
+    {
+        FILE* f = std::fopen(path.c_str(), "rb");
+        if (!f) { err = "cannot open " + path; return false; }
+        unsigned char tmp[65536]; size_t n;
+        while ((n = std::fread(tmp, 1, sizeof(tmp), f)) > 0) file.insert(file.end(), tmp, tmp + n);
+        std::fclose(f);
+    }
+    std::vector<unsigned char> px;
+    bool ok = false;
+    if (file.size() > 3 && file[0] == 0xff && file[1] == 0xd8) ok = decode_jpeg_rgba8(file, w, h, px, err);
+    else if (file.size() > 8 && file[0] == 137 && file[1] == 'P') { ok = decode_png_rgba8(file, w, h, px); if (!ok) err = "cannot decode PNG"; }
+    else err = "neither JPEG nor PNG";
+    if (!ok) { err = path + ": " + err; return false; }
+    static float lut[256]; static bool have = false;
+    if (!have) { for (int i = 0; i < 256; i++) lut[i] = (float)(std::pow((double)(i / 255.0f), (double)2.2f) * (double)1.0f); have = true; }
+    rgba.resize(px.size());
+    for (size_t i = 0; i < px.size(); i += 4) {
+        rgba[i] = lut[px[i]]; rgba[i + 1] = lut[px[i + 1]]; rgba[i + 2] = lut[px[i + 2]];
+        rgba[i + 3] = px[i + 3] / 255.0f;
+    }
+    return true;
+}
+
 }  // namespace pt
 
 extern "C" int pt_image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba) {
     if (!path || !width || !height || !rgba) return PT_ERR_INVALID;
     int w = 0, h = 0; std::vector<float> px; std::string err;
-    if (!pt::load_hdr_rgba32f(path, w, h, px, err)) { pt::set_last_error(err.c_str()); return PT_ERR_IO; }
+    // stbi_loadf: Radiance files as they are, anything else through the 8-bit decoders and the gamma-2.2 expansion
+    bool radiance = false;
+    if (FILE* f = std::fopen(path, "rb")) { char sig[3] = {0, 0, 0}; size_t got = std::fread(sig, 1, 2, f); std::fclose(f); radiance = got == 2 && sig[0] == '#' && sig[1] == '?'; }
+    const bool ok = radiance ? pt::load_hdr_rgba32f(path, w, h, px, err) : pt::load_ldr_as_hdr_rgba32f(path, w, h, px, err);
+    if (!ok) { pt::set_last_error(err.c_str()); return PT_ERR_IO; }
     *rgba = (float*)std::malloc(px.size() * sizeof(float));
     if (!*rgba) return PT_ERR_LIMIT;
     std::memcpy(*rgba, px.data(), px.size() * sizeof(float));

@@ -450,6 +450,13 @@ bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<flo
     auto put = [&](size_t px, int r, int g, int bl, int a) {
         rgba[4 * px] = r / 255.0f; rgba[4 * px + 1] = g / 255.0f; rgba[4 * px + 2] = bl / 255.0f; rgba[4 * px + 3] = a / 255.0f;
     };
+    if (b[0] == 0xff && b[1] == 0xd8) {
+        std::vector<unsigned char> px; std::string err;
+        if (!decode_jpeg_rgba8(b, w, h, px, err)) return false;
+        rgba.resize(px.size());
+        for (size_t i = 0; i < px.size(); i++) rgba[i] = px[i] / 255.0f;
+        return true;
+    }
     if (b[0] == 137 && b[1] == 'P' && b[2] == 'N' && b[3] == 'G') {
         std::vector<unsigned char> px;
         if (!decode_png_rgba8(b, w, h, px)) return false;

@@ -134,7 +134,8 @@ int32_t pt_environment_size(pt_context* ctx);                        /* 0: const
 int pt_download_environment(pt_context* ctx, float* faces_rgba);     /* 6 x size x size x 4 floats */
 /* All of LoadEnvironmnet: "GENERATE COLOR x" | path ending in .hdr (Radiance RGBE, equirect -> 1024^2 cubemap) | text
  * file naming six face images (TextureCubemap::LoadTexture, Texture.cpp:245-276; faces as .ppm/.bmp/.tga).
- * ".jpg" (stbi_loadf + gamma 2.2 in the reference) returns PT_ERR_UNSUPPORTED: no JPEG decoder here. */
+ * ".jpg" goes through the JPEG decoder and stb's gamma-2.2 expansion (stbi_loadf on an 8-bit file); progressive JPEGs are
+ * refused. */
 int pt_load_environment(pt_context* ctx, const char* args);
 
 /* ---- BVH: BoundingVolumeHierarchy::BuildBinnedSpatial (BVH.cpp:2197-2293) ---- */
@@ -196,12 +197,12 @@ const char* pt_scene_file_texture_path(const pt_scene_file* sf, int32_t material
 int32_t pt_scene_file_num_shapes(const pt_scene_file* sf);
 const char* pt_scene_file_warnings(const pt_scene_file* sf);
 /* map_Kd image -> RGBA32F texels (byte / 255, rows in file order; Texture2D::LoadTexture, Texture.cpp:146-156, decodes
- * through SOIL2 -- here: .png (all colour types / depths / Adam7, as stb_image reads them), .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
+ * through SOIL2 -- here: .jpg (baseline / extended sequential, as stb_image reads them), .png (all colour types / depths / Adam7), .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
 int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgba);
 /* 8-bit RGB PNG, rows top-down (filter 0, stored deflate blocks): the format of Renderer::SaveScreenshot (Renderer.cpp:698). */
 int pt_image_save_png(const char* path, int32_t width, int32_t height, const uint8_t* rgb_top_down);
-/* Radiance .hdr -> RGBA32F as stbi_loadf(path, .., 4) returns it (Renderer.cpp:265): byte * 2^(e-136), alpha 1, rows in
- * file order. *rgba is malloc()ed, release with pt_free. */
+/* stbi_loadf(path, .., 4) (Renderer.cpp:265): a Radiance .hdr as byte * 2^(e-136), alpha 1; a JPEG / PNG through the 8-bit
+ * decode and pow(byte / 255, 2.2) (alpha byte / 255). Rows in file order. *rgba is malloc()ed, release with pt_free. */
 int pt_image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba);
 /* scene.txt: line 1 scene path, line 2 environment string, then camera position xyz and rotation (yaw pitch roll). */
 typedef struct pt_scene_txt {

@@ -224,3 +224,117 @@ def test_png_committed_fixture():
     got = api.load_image(os.path.join(PNG, "tiles.png"))
     want = np.load(os.path.join(PNG, "tiles_stbi.npy"))
     assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0))
+
+
+# ------------------------------------------------------------------------------------------------ JPEG
+JPG = os.path.join(GOLDEN, "jpg")
+
+
+def _test_image(w, h, seed):
+    """Smooth colour gradients + hard edges + noise: exercises DC prediction, long zero runs and busy blocks."""
+    rng = np.random.default_rng(seed)
+    y, x = np.mgrid[0:h, 0:w]
+    img = np.zeros((h, w, 3), np.float64)
+    img[..., 0] = 128 + 100 * np.sin(x / 7.0) * np.cos(y / 5.0)
+    img[..., 1] = (x * 255.0 / max(w - 1, 1))
+    img[..., 2] = (y * 255.0 / max(h - 1, 1))
+    img[(x // 6 + y // 4) % 5 == 0] = (250, 10, 30)
+    img += rng.normal(0, 12, size=img.shape)
+    return np.clip(img, 0, 255).astype(np.uint8)
+
+
+def _pil():
+    return pytest.importorskip("PIL.Image")
+
+
+JPEG_CASES = [  # (name, size, mode, PIL save options)
+    ("q75_420", (64, 48), "RGB", dict(quality=75, subsampling=2)),
+    ("q95_444", (33, 17), "RGB", dict(quality=95, subsampling=0)),
+    ("q30_422", (57, 23), "RGB", dict(quality=30, subsampling=1)),
+    ("q85_420_odd", (17, 33), "RGB", dict(quality=85, subsampling=2)),
+    ("tiny_420", (1, 1), "RGB", dict(quality=90, subsampling=2)),
+    ("narrow_420", (2, 40), "RGB", dict(quality=90, subsampling=2)),
+    ("optimised_tables", (80, 60), "RGB", dict(quality=60, subsampling=2, optimize=True)),
+    ("grey", (45, 31), "L", dict(quality=80)),
+    ("cmyk", (24, 24), "CMYK", dict(quality=90)),
+    ("restart_rows", (96, 64), "RGB", dict(quality=75, subsampling=2, restart_marker_rows=1)),
+    ("restart_blocks", (96, 64), "RGB", dict(quality=75, subsampling=0, restart_marker_blocks=3)),
+    ("q100_444", (40, 40), "RGB", dict(quality=100, subsampling=0)),
+]
+
+
+@pytest.mark.parametrize("name,size,mode,opts", JPEG_CASES)
+def test_jpeg_reader_matches_stb(tmp_path, name, size, mode, opts):
+    Image = _pil()
+    if not oracle.have_stbi():
+        pytest.skip("oracle/_ref not built: covered by test_jpeg_committed_fixtures")
+    w, h = size
+    rgb = _test_image(w, h, seed=len(name))
+    im = Image.fromarray(rgb).convert(mode)
+    p = str(tmp_path / f"{name}.jpg")
+    try:
+        im.save(p, "JPEG", **opts)
+    except TypeError:
+        pytest.skip("this Pillow does not know " + ", ".join(opts))
+    want = oracle.ref_stbi_load(p)
+    assert want is not None
+    got = api.load_image(p)
+    assert got.shape == (h, w, 4)
+    assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0))
+    if mode == "RGB" and opts.get("quality", 0) >= 95:
+        assert np.abs(want[..., :3].astype(int) - rgb.astype(int)).mean() < 6      # and it is the picture we encoded
+
+
+@pytest.mark.parametrize("factor", [411, 440, 422, 420, 444])
+def test_jpeg_reader_other_sampling_factors(tmp_path, factor):
+    cv2 = pytest.importorskip("cv2")
+    if not oracle.have_stbi() or not hasattr(cv2, "IMWRITE_JPEG_SAMPLING_FACTOR"):
+        pytest.skip("needs oracle/_ref and an OpenCV that can choose the sampling factor")
+    rgb = _test_image(70, 50, seed=factor)
+    p = str(tmp_path / f"s{factor}.jpg")
+    flag = getattr(cv2, f"IMWRITE_JPEG_SAMPLING_FACTOR_{factor}")
+    assert cv2.imwrite(p, rgb[..., ::-1], [cv2.IMWRITE_JPEG_QUALITY, 88, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, flag])
+    want = oracle.ref_stbi_load(p)
+    got = api.load_image(p)
+    assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0))
+
+
+def test_jpeg_reader_refuses_progressive_and_damaged(tmp_path):
+    Image = _pil()
+    rgb = _test_image(32, 32, seed=1)
+    p = str(tmp_path / "prog.jpg")
+    Image.fromarray(rgb).save(p, "JPEG", quality=80, progressive=True)
+    with pytest.raises(api.PtError):
+        api.load_image(p)
+    q = str(tmp_path / "base.jpg")
+    Image.fromarray(rgb).save(q, "JPEG", quality=80)
+    data = open(q, "rb").read()
+    cut = tmp_path / "cut.jpg"
+    cut.write_bytes(data[:len(data) // 3])
+    with pytest.raises(api.PtError):
+        api.load_image(str(cut))
+
+
+def test_jpeg_committed_fixtures():
+    """tests/golden/jpg/*.jpg with the reference's stb_image result recorded beside each (tools/make_jpg_golden.py)."""
+    names = sorted(f[:-4] for f in os.listdir(JPG) if f.endswith(".jpg"))
+    assert len(names) >= 3
+    for n in names:
+        got = api.load_image(os.path.join(JPG, n + ".jpg"))
+        want = np.load(os.path.join(JPG, n + "_stbi.npy"))
+        assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0)), n
+
+
+def test_ldr_files_through_loadf_get_stbs_gamma(tmp_path):
+    """The reference's ".jpg" environment is read with stbi_loadf (Renderer.cpp:262-266): 8-bit decode, then
+    pow(byte / 255, 2.2) per colour channel. pt_image_load_hdr gives the same floats, bit for bit."""
+    Image = _pil()
+    if not oracle.have_stbi():
+        pytest.skip("oracle/_ref not built")
+    rgb = _test_image(48, 24, seed=9)
+    p = str(tmp_path / "env.jpg")
+    Image.fromarray(rgb).save(p, "JPEG", quality=92, subsampling=0)
+    got = api.load_hdr(p)
+    want = oracle.ref_stbi_loadf(p)
+    assert got.shape == want.shape and np.array_equal(got, want)
+    assert got[..., :3].max() <= 1.0 and np.all(got[..., 3] == 1.0)
