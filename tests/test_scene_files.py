@@ -190,3 +190,42 @@ def test_load_scene_from_files_matches_array_upload():
     close = np.isclose(img_a[..., :3], want[..., :3], rtol=1e-4, atol=1e-6).all(axis=2)
     assert close.mean() > 0.995
     assert img_a[..., :3].max() > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("texture", ["jpg/420.jpg", "png/tiles.png"])
+def test_room_with_jpeg_and_png_textures(tmp_path, texture):
+    """The same room with its map_Kd pointing at a JPEG / PNG: pt_load_scene decodes it (pt_image.cpp) and the frames equal
+    those of the array upload fed by the Python-side decode of the same file, and the oracle's."""
+    import shutil
+    from gpupathtracer_b200 import Renderer, Scene, Camera, make_rng_table
+    src = os.path.join(HERE, "golden", "obj")
+    for f in ("room.obj",):
+        shutil.copy(os.path.join(src, f), tmp_path / f)
+    tex = os.path.basename(texture)
+    shutil.copy(os.path.join(HERE, "golden", texture), tmp_path / tex)
+    mtl = open(os.path.join(src, "room.mtl")).read().replace("checker.ppm", tex)
+    (tmp_path / "room.mtl").write_text(mtl)
+    obj = str(tmp_path / "room.obj")
+    data = api.scene_data_from_obj(obj)
+    assert len(data.textures) == 1 and data.textures[0].shape[0] > 4       # the real image, not the 4x4 checker
+    w = h = 64
+    cam = Camera(1.0, np.radians(60.0), 1.5, 0.0)
+    cam.SetPosition((0.0, 1.0, 0.9)); cam.SetRotation((0.0, 0.0, 0.0)); cam.GenerateImagePlane()
+    rng = make_rng_table(w * h, 5)
+    a = Renderer().InitializeFromFile(w, h, obj, "GENERATE COLOR WHITE", max_depth=5)
+    a.SetRNG(rng); a.RenderFrame(cam, 4)
+    img_a = a.DownloadAccum()
+    nodes, refs = a.GetBVH()
+    a.CleanUp()
+    s = Scene(data)
+    s.set_bvh(nodes, refs)
+    b = Renderer().Initialize(w, h, s, max_depth=5, rng_state=rng)
+    b.RenderFrame(cam, 4)
+    img_b = b.DownloadAccum()
+    b.CleanUp()
+    assert np.array_equal(img_a.view(np.uint32), img_b.view(np.uint32))
+    want = np.zeros((h, w, 4), np.float32)
+    oracle.Oracle(s).render(cam.as_array(), w, h, rng.copy(), want, n_frames=4, max_depth=5)
+    close = np.isclose(img_a[..., :3], want[..., :3], rtol=1e-4, atol=1e-6).all(axis=2)
+    assert close.mean() > 0.995
