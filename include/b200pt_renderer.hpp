@@ -66,7 +66,8 @@ public:
         width_ = window->Width; height_ = window->Height;
     }
     // The reference's own signature: Initialize(Window*, scenePath, env) (Renderer.cpp:448, called at Program.cpp:81).
-    // scenePath is an .obj (the only live loader, Scene.cpp:248-259), env e.g. "GENERATE COLOR WHITE".
+    // scenePath is an .obj (the only live loader, Scene.cpp:248-259); env is any LoadEnvironmnet string: "GENERATE COLOR WHITE",
+    // a .hdr / .jpg equirectangular image, or a text file naming six cube faces.
     void Initialize(const Window* window, const char* scenePath, const std::string& env, int max_depth = 66, uint64_t seed = 0,
                     int bvh_layout = PT_BVH_REFERENCE) {
         pt_config cfg{};
