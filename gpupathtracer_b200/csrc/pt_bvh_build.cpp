@@ -29,8 +29,11 @@
 namespace pt {
 namespace {
 
-constexpr float kCostTraversal = 1.23f, kCostIntersection = 5.33f;
-constexpr int kBins = 16;
+constexpr float kCostTraversal = 1.23f;
+constexpr int kMaxBins = 64;
+// tuning-run overrides (read per build): PT_BVH_CI = intersection cost of the SAH model, PT_BVH_BINS = bins per axis
+static float kCostIntersection = 5.33f;
+static int kBins = 16;
 constexpr int kMaxDepth = 56;          // the traversal stack holds 64 entries
 constexpr float kAlpha = 1e-5f;
 constexpr int kParallelThreshold = 8192;
@@ -113,10 +116,10 @@ struct Builder {
             for (const Ref& r : refs) { float c = centroid(r, ax); clo = std::min(clo, c); chi = std::max(chi, c); }
             if (!(chi > clo)) continue;
             float k1 = kBins / (chi - clo);
-            Box bb[kBins]; int cnt[kBins];
+            Box bb[kMaxBins]; int cnt[kMaxBins];
             for (int b = 0; b < kBins; b++) { bb[b].reset(); cnt[b] = 0; }
             for (const Ref& r : refs) { int b = bin_of(centroid(r, ax), clo, k1); bb[b].grow(r.box); cnt[b]++; }
-            Box rb[kBins]; Box acc; acc.reset();
+            Box rb[kMaxBins]; Box acc; acc.reset();
             for (int b = kBins - 1; b >= 1; b--) { acc.grow(bb[b]); rb[b] = acc; }
             Box lb; lb.reset(); int nl = 0;
             for (int b = 1; b < kBins; b++) {
@@ -167,7 +170,7 @@ struct Builder {
             float lo = nb.lo[ax], hi = nb.hi[ax];
             if (!(hi > lo)) continue;
             float k1 = kBins / (hi - lo), width = (hi - lo) / kBins;
-            Box bb[kBins]; int enter[kBins], leave[kBins];
+            Box bb[kMaxBins]; int enter[kMaxBins], leave[kMaxBins];
             for (int b = 0; b < kBins; b++) { bb[b].reset(); enter[b] = leave[b] = 0; }
             for (const Ref& r : refs) {
                 int b0 = bin_of(r.box.lo[ax], lo, k1), b1 = bin_of(r.box.hi[ax], lo, k1);
@@ -182,7 +185,7 @@ struct Builder {
                 }
                 if (cur.box.valid()) bb[b1].grow(cur.box);
             }
-            Box rb[kBins]; int rc[kBins]; Box acc; acc.reset(); int c = 0;
+            Box rb[kMaxBins]; int rc[kMaxBins]; Box acc; acc.reset(); int c = 0;
             for (int b = kBins - 1; b >= 1; b--) { acc.grow(bb[b]); c += leave[b]; rb[b] = acc; rc[b] = c; }
             Box lb; lb.reset(); int nl = 0;
             for (int b = 1; b < kBins; b++) {
@@ -328,6 +331,8 @@ struct Flat {
 
 bool build_sbvh(const float* tris_pre, int64_t n, int n_threads, HostBvh& out, std::string& msg) {
     if (n < 2) { msg = "need at least 2 triangles (the root must be an inner node, BVH.glsl:627)"; return false; }
+    if (const char* e = getenv("PT_BVH_CI")) kCostIntersection = (float)atof(e);
+    if (const char* e = getenv("PT_BVH_BINS")) kBins = std::min(std::max(atoi(e), 2), kMaxBins);
     Builder b;
     b.tris = tris_pre;
     b.n_threads = n_threads > 0 ? n_threads : (int)std::max(1u, std::thread::hardware_concurrency());

@@ -9,6 +9,10 @@
 // Extend and shadow are persistent kernels: one resident grid, warps pull 32-ray packets from a
 // device-side cursor. Shade is a streaming kernel that compacts survivors and shadow items with
 // warp ballots + one atomic per warp.
+#define PT_TRACE_THREADS 128   // 10 CTAs/SM at 48 registers; forcing 12 (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
+#ifndef PT_TRACE_MIN_BLOCKS
+#define PT_TRACE_MIN_BLOCKS 1   // experiment: 10 caps k_extend at 48 registers (it compiles to 51-53 = 9 CTAs/SM)
+#endif
 #include "pt_kernels.h"
 #include "pt_trace.cuh"
 #include "pt_trace_wide.cuh"
@@ -17,7 +21,6 @@
 
 namespace pt {
 
-#define PT_TRACE_THREADS 128   // 10 CTAs/SM at 48 registers; forcing 12 (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
 #define PT_STREAM_THREADS 256
 #define PT_SHADE_THREADS 128
 #define PT_RAY_ORDER_MAX_BITS 6      // 64^3 cells x 8 octants = 2097152 bins = 2048 scan tiles
@@ -37,7 +40,7 @@ struct BatchIO {
     __device__ __forceinline__ void store(int i, const HitRec& h, bool result) const {
         if (perm) i = __ldg(perm + i);
         if (flags) flags[i] = result ? 1 : 0;
-        else hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+        else st_stream(hits + i, make_float4(h.t, h.u, h.v, __int_as_float(h.tri)));
     }
 };
 
@@ -153,7 +156,7 @@ int launch_ray_order(const SceneDev& s, const float4* rays, long long n, unsigne
 }
 
 template <bool ANY, class TR>
-__global__ void __launch_bounds__(PT_TRACE_THREADS)
+__global__ void __launch_bounds__(PT_TRACE_THREADS, PT_TRACE_MIN_BLOCKS)
 k_trace_batch(SceneDev s, BatchIO io, int leaf_thresh, int fetch_thresh) {
     trace_persistent<ANY, TR>(s, io, leaf_thresh, fetch_thresh);
 }
@@ -219,16 +222,16 @@ struct ExtendIO {
     __device__ __forceinline__ int count() const { return c->n_paths; }
     __device__ __forceinline__ int* cursor() const { return &c->fetch_extend; }
     __device__ __forceinline__ void load(int i, V3& o, V3& d, float& tmax) const {
-        float4 ro = q.q0[i], rd = q.q1[i];
+        float4 ro = ld_stream(q.q0 + i), rd = ld_stream(q.q1 + i);
         o = xyz(ro); d = xyz(rd); tmax = 1e20f;                      // Iterative.comp:232
     }
     __device__ __forceinline__ void store(int i, const HitRec& h, bool) const {
-        hits[i] = make_float4(h.t, h.u, h.v, __int_as_float(h.tri));
+        st_stream(hits + i, make_float4(h.t, h.u, h.v, __int_as_float(h.tri)));
     }
 };
 
 template <class TR>
-__global__ void __launch_bounds__(PT_TRACE_THREADS)
+__global__ void __launch_bounds__(PT_TRACE_THREADS, PT_TRACE_MIN_BLOCKS)
 k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
     ExtendIO io{p.queue[qi], p.hits, p.counters + bounce};
     trace_persistent<false, TR>(p.scene, io, leaf_thresh, fetch_thresh);
@@ -400,16 +403,16 @@ struct ShadowIO {
     __device__ __forceinline__ int count() const { return c->n_shadow; }
     __device__ __forceinline__ int* cursor() const { return &c->fetch_shadow; }
     __device__ __forceinline__ void load(int i, V3& o, V3& d, float& tmax) const {
-        float4 s0 = sq.s0[i], s1 = sq.s1[i];
+        float4 s0 = ld_stream(sq.s0 + i), s1 = ld_stream(sq.s1 + i);
         o = xyz(s0); d = xyz(s1); tmax = s0.w;
     }
     __device__ __forceinline__ void store(int i, const HitRec&, bool occluded) const {
-        float4 s2 = sq.s2[i], s3 = sq.s3[i];
+        float4 s2 = ld_stream(sq.s2 + i), s3 = ld_stream(sq.s3 + i);
         int dest = __float_as_int(sq.s1[i].w);
         V3 contrib = xyz(s3);
         if (!occluded) contrib = contrib + xyz(s2);                  // Iterative.comp:278-280
         if (dest >= 0) {
-            qn.q3[dest] = f4(contrib, 0.0f);
+            st_stream(qn.q3 + dest, f4(contrib, 0.0f));
         } else {
             int pix = ~dest;                                         // imageStore, Iterative.comp:295
             float4 acc = accum[pix];
@@ -419,7 +422,7 @@ struct ShadowIO {
 };
 
 template <class TR>
-__global__ void __launch_bounds__(PT_TRACE_THREADS)
+__global__ void __launch_bounds__(PT_TRACE_THREADS, PT_TRACE_MIN_BLOCKS)
 k_shadow(FrameParams p, int bounce, int qi_next, int leaf_thresh, int fetch_thresh) {
     ShadowIO io{p.shadow, p.queue[qi_next], p.accum, p.counters + bounce};
     trace_persistent<true, TR>(p.scene, io, leaf_thresh, fetch_thresh);

@@ -53,12 +53,42 @@ __device__ __forceinline__ float4 ldg4(const float4* p) { return __ldg(p); }
 // per lane for a 32-B half record instead of two. The traversal kernels are bound by exactly that pipe
 // (l1tex__data_pipe_lsu_wavefronts ~ 89 % of peak with 128-bit loads, profiles/), so record loads use this.
 struct F8 { float4 lo, hi; };
+// PT_NODE_HINT (compile-time experiment): eviction priority of the BVH record loads. 0: none; 1: L1::evict_last;
+// 2: L1::evict_last + L2::evict_last; 3: L2::evict_last (sm_100 accepts L2 priorities on 256-bit loads only).
+#ifndef PT_NODE_HINT
+#define PT_NODE_HINT 0
+#endif
+#if PT_NODE_HINT == 1
+#define PT_LDG256 "ld.global.nc.L1::evict_last.v8.f32"
+#elif PT_NODE_HINT == 2
+#define PT_LDG256 "ld.global.nc.L1::evict_last.L2::evict_last.v8.f32"
+#elif PT_NODE_HINT == 3
+#define PT_LDG256 "ld.global.nc.L2::evict_last.v8.f32"
+#else
+#define PT_LDG256 "ld.global.nc.v8.f32"
+#endif
 __device__ __forceinline__ F8 ldg256(const void* p) {
     F8 r;
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+    asm(PT_LDG256 " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
         : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
         : "l"(p));
     return r;
 }
+
+// Ray-queue / hit-record traffic of the traversal kernels is touched once per launch: with PT_STREAM_NA it bypasses
+// L1 allocation (LDG.E.NA / STG.E.NA) so that it does not evict BVH records, which is what the L1 is for here.
+#ifdef PT_STREAM_NA
+__device__ __forceinline__ float4 ld_stream(const float4* p) {
+    float4 a;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(p));
+    return a;
+}
+__device__ __forceinline__ void st_stream(float4* p, float4 a) {
+    asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" :: "l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
+}
+#else
+__device__ __forceinline__ float4 ld_stream(const float4* p) { return *p; }
+__device__ __forceinline__ void st_stream(float4* p, float4 a) { *p = a; }
+#endif
 
 }  // namespace pt

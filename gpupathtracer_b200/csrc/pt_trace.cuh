@@ -21,6 +21,28 @@ namespace pt {
 
 struct HitRec { float t, u, v; int tri; };
 
+// Per-lane traversal stack. Default: a local-memory array (L1-resident; lanes at the same depth share a wavefront).
+// Compile-time experiment -DPT_SMEM_STACK=S: the S entries nearest the bottom live in shared memory, transposed
+// ([entry][thread]: conflict-free, one wavefront per push/pop whatever the lanes' depths), deeper ones stay local.
+#ifndef PT_SMEM_STACK
+#define PT_SMEM_STACK 8
+#endif
+#if PT_SMEM_STACK > 0
+__device__ __forceinline__ int* smem_stack() {
+    __shared__ int s_stack[PT_SMEM_STACK * PT_TRACE_THREADS];
+    return s_stack + threadIdx.x;
+}
+__device__ __forceinline__ void stack_push(int* stack, int sp, int v) {
+    if (sp < PT_SMEM_STACK) smem_stack()[sp * PT_TRACE_THREADS] = v; else stack[sp] = v;
+}
+__device__ __forceinline__ int stack_at(const int* stack, int sp) {
+    return sp < PT_SMEM_STACK ? smem_stack()[sp * PT_TRACE_THREADS] : stack[sp];
+}
+#else
+__device__ __forceinline__ void stack_push(int* stack, int sp, int v) { stack[sp] = v; }
+__device__ __forceinline__ int stack_at(const int* stack, int sp) { return stack[sp]; }
+#endif
+
 // slab test of one child (IntersectNodeFast); returns t_entry
 __device__ __forceinline__ float slab_test(float4 bmin, float4 bmax, V3 inv, V3 oinv, float tcur, bool& hit) {
     float ax = bmin.x * inv.x + oinv.x, ay = bmin.y * inv.y + oinv.y, az = bmin.z * inv.z + oinv.z;
@@ -96,7 +118,7 @@ struct Traverser {
     // returns true when the ray is finished
     __device__ __forceinline__ bool pop(const int* stack) {
         if (sp == 0) return true;
-        current = stack[--sp];
+        current = stack_at(stack, --sp);
         return false;
     }
     template <bool ANY>
@@ -125,7 +147,7 @@ struct Traverser {
             bool swap = d0 > d1;
             current = swap ? sub1 : sub0;
             const int far_child = swap ? sub0 : sub1;
-            stack[sp++] = far_child;
+            stack_push(stack, sp++, far_child);
 #ifdef PT_PREFETCH_FAR   // measured (build with PT_NVCC_EXTRA=-DPT_PREFETCH_FAR): atrium 3.03 -> 2.85 Grays/s, 10M-triangle batch 2.40 -> 1.91:
                          // the prefetch costs an L1 tag look-up on a pipe that is already the bottleneck, and half the pushed nodes are culled
             if (far_child >= 0) asm volatile("prefetch.global.L1 [%0];" :: "l"(s.pairs + far_child));
