@@ -236,10 +236,10 @@ k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
     ExtendIO io{p.queue[qi], p.hits, p.counters + bounce};
     trace_persistent<false, TR>(p.scene, io, leaf_thresh, fetch_thresh);
 }
-static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
-    if (dims.wide == 8) k_extend<WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
-    else if (dims.wide == 4) k_extend<WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
-    else k_extend<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims& dims, int blocks, cudaStream_t st) {
+    if (dims.wide == 8) k_extend<WideTraverser<8>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.wide == 4) k_extend<WideTraverser<4>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+    else k_extend<Traverser><<<blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 // ------------------------------------------------------------------ shade
@@ -427,10 +427,10 @@ k_shadow(FrameParams p, int bounce, int qi_next, int leaf_thresh, int fetch_thre
     ShadowIO io{p.shadow, p.queue[qi_next], p.accum, p.counters + bounce};
     trace_persistent<true, TR>(p.scene, io, leaf_thresh, fetch_thresh);
 }
-static void launch_shadow(const FrameParams& p, int b, int qi_next, const LaunchDims& dims, cudaStream_t st) {
-    if (dims.wide == 8) k_shadow<WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
-    else if (dims.wide == 4) k_shadow<WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
-    else k_shadow<Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+static void launch_shadow(const FrameParams& p, int b, int qi_next, const LaunchDims& dims, int blocks, cudaStream_t st) {
+    if (dims.wide == 8) k_shadow<WideTraverser<8>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.wide == 4) k_shadow<WideTraverser<4>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+    else k_shadow<Traverser><<<blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
 }
 
 __global__ void k_tally(FrameParams p) {
@@ -461,11 +461,11 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
     int qi = 0;
     for (int b = 0; b < p.max_depth; b++) {
         if (evs) cudaEventRecord(evs[launches], st);
-        launch_extend(p, b, qi, dims, st); launches++;
+        launch_extend(p, b, qi, dims, dims.extend_blocks, st); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
         launch_shade(p, b, qi, dims, st); launches++;
         if (evs) cudaEventRecord(evs[launches], st);
-        launch_shadow(p, b, qi ^ 1, dims, st); launches++;
+        launch_shadow(p, b, qi ^ 1, dims, dims.extend_blocks, st); launches++;
         qi ^= 1;
     }
     if (evs) cudaEventRecord(evs[launches], st);
@@ -479,7 +479,7 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
     cudaStream_t A = ss.a, B = ss.b;
     cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), A);
     k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, A>>>(p); launches++;
-    launch_extend(p, 0, 0, dims, A); launches++;
+    launch_extend(p, 0, 0, dims, dims.frame_blocks, A); launches++;
     // shade(0) rewrites the shadow queue and accum pixels the previous frame's last shadow kernel may still be using
     if (wait_prev) cudaStreamWaitEvent(A, ss.ev_shadow, 0);
     int qi = 0;
@@ -487,12 +487,12 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
         launch_shade(p, b, qi, dims, A); launches++;
         cudaEventRecord(ss.ev_shade, A);
         cudaStreamWaitEvent(B, ss.ev_shade, 0);
-        launch_shadow(p, b, qi ^ 1, dims, B); launches++;
+        launch_shadow(p, b, qi ^ 1, dims, dims.frame_blocks, B); launches++;
         if (b + 1 == p.max_depth) { k_tally<<<1, 32, 0, B>>>(p); launches++; }
         cudaEventRecord(ss.ev_shadow, B);
         qi ^= 1;
         if (b + 1 < p.max_depth) {
-            launch_extend(p, b + 1, qi, dims, A); launches++;
+            launch_extend(p, b + 1, qi, dims, dims.frame_blocks, A); launches++;
             cudaStreamWaitEvent(A, ss.ev_shadow, 0);         // shade(b+1) reuses the shadow queue and reads q3 written by shadow(b)
         }
     }
@@ -597,7 +597,7 @@ void launch_equirect_to_cube(const float4* src, int w, int h, float4* faces, int
 // + 2 leaf steps per round: 3.35; + leaf_thresh 8 -> 4: 3.38. Results are unaffected (a lane's own step sequence is
 // the same whatever the schedule).
 #ifndef PT_INNER_BURST
-#define PT_INNER_BURST 8
+#define PT_INNER_BURST 12
 #endif
 #ifndef PT_LEAF_BURST
 #define PT_LEAF_BURST 2
@@ -648,6 +648,15 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
     }
     if (const char* e = getenv("PT_FETCH_THRESH")) out->fetch_thresh = atoi(e);
     if (const char* e = getenv("PT_BLOCKS_PER_SM")) out->extend_blocks = prop.multiProcessorCount * atoi(e);
+    // Grid of k_extend / k_shadow inside the frame DAG (enqueue_frame_dag), where shadow(b), extend(b+1) and the other
+    // slices' kernels are in flight together: a persistent grid that fills the machine keeps the next kernel's CTAs out
+    // until its own drain phase, 4 CTAs/SM let two or three of them share every SM. Measured on the headline config
+    // (one box, 3 slices): 9 CTAs/SM 2.070 ms/frame, 6: 2.034, 5: 2.017, 4: 2.009, 3: 2.005, 2: 2.110 -- while the same
+    // kernel ALONE gets slower (extend 1.03 -> 1.30 ms at 4), so sequential launches (launch_frame, ray batches) keep the
+    // full grid.
+    out->frame_blocks = prop.multiProcessorCount * (per < 4 ? per : 4);
+    if (const char* e = getenv("PT_FRAME_BLOCKS_PER_SM")) out->frame_blocks = prop.multiProcessorCount * atoi(e);
+    if (const char* e = getenv("PT_SHADE_BLOCKS_PER_SM")) out->shade_blocks = prop.multiProcessorCount * atoi(e);
 }
 
 }  // namespace pt

@@ -32,7 +32,7 @@ struct FrameParams {
     unsigned long long* totals; // [0] closest rays, [1] shadow rays traced, [2] paths, [3] shadow rays not needed (radiance 0)
 };
 
-struct LaunchDims { int sm_count; int extend_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; int wide; int top_pairs; };
+struct LaunchDims { int sm_count; int extend_blocks; int frame_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; int wide; int top_pairs; };
 
 // fixed ray batches (AoS rays: n x {o.xyz, -, d.xyz, tmax})
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,

@@ -8,7 +8,7 @@ import sys, json
 for l in sys.stdin:
     l = l.strip()
     if l.startswith('{'):
-        d = json.loads(l); print('$1', '$wl', round(d['value'], 1), d['unit'], 'ms/step', round(d['ms_per_step'], 4), 'e2e', round(d['e2e']['value'], 1), d.get('stage_share'))
+        d = json.loads(l); print('$1', '$wl', round(d['value'], 1), d['unit'], 'ms/step', round(d['ms_per_step'], 4), 'e2e', round(d['e2e']['value'], 1), {k: round(v, 3) for k, v in (d.get('stage_ms_per_step') or {}).items()})
 "; }
 run base ""
 for v in "$@"; do run $(basename $v .so) $PWD/$v; done
