@@ -9,9 +9,11 @@
 // Extend and shadow are persistent kernels: one resident grid, warps pull 32-ray packets from a
 // device-side cursor. Shade is a streaming kernel that compacts survivors and shadow items with
 // warp ballots + one atomic per warp.
-#define PT_TRACE_THREADS 128   // 10 CTAs/SM at 48 registers; forcing 12 (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
+#define PT_TRACE_THREADS 128   // forcing 12 CTAs/SM (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
 #ifndef PT_TRACE_MIN_BLOCKS
-#define PT_TRACE_MIN_BLOCKS 1   // experiment: 10 caps k_extend at 48 registers (it compiles to 51-53 = 9 CTAs/SM)
+#define PT_TRACE_MIN_BLOCKS 9   // caps the traversal kernels at 56 registers (k_extend takes 64 when left alone = 8 CTAs/SM). Measured, one box,
+                                // 8 / 9 / 10 (48 registers, 16-32 B of spills): atrium 3.20 / 3.22 / 3.19 Grays/s, bathroom 2.87 / 2.93 / 2.85,
+                                // 10M-triangle batch 3.12 / 3.23 / 3.24, bunny primary rays 4.49 / 4.52 / 4.31
 #endif
 #include "pt_kernels.h"
 #include "pt_trace.cuh"
