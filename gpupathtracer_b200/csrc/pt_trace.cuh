@@ -43,6 +43,18 @@ __device__ __forceinline__ void stack_push(int* stack, int sp, int v) { stack[sp
 __device__ __forceinline__ int stack_at(const int* stack, int sp) { return stack[sp]; }
 #endif
 
+// Compile-time experiment -DPT_POP_CULL (closest hit only): the far child's entry distance is kept beside its link
+// and an INNER entry whose distance exceeds the current hit distance is dropped at pop time without fetching its pair
+// record. Exactly equivalent: child boxes lie inside the parent's box, the slab arithmetic is monotonic in the box
+// planes, so both children of such a node fail `t_entry <= min(t_exit, t)` and the reference pops again. Leaf entries are
+// never dropped (a triangle's Moeller-Trumbore t is not bounded by its box's t_entry in floating point).
+#ifdef PT_POP_CULL
+__device__ __forceinline__ float* smem_tstack() {
+    __shared__ float s_tstack[(PT_SMEM_STACK > 0 ? PT_SMEM_STACK : 1) * PT_TRACE_THREADS];
+    return s_tstack + threadIdx.x;
+}
+#endif
+
 // slab test of one child (IntersectNodeFast); returns t_entry
 __device__ __forceinline__ float slab_test(float4 bmin, float4 bmax, V3 inv, V3 oinv, float tcur, bool& hit) {
     float ax = bmin.x * inv.x + oinv.x, ay = bmin.y * inv.y + oinv.y, az = bmin.z * inv.z + oinv.z;
@@ -84,11 +96,19 @@ __device__ __forceinline__ bool tri_test(const LeafTri* __restrict__ rec, V3 o, 
 // `current` < 0: ~current = next record of the leaf triangle stream to test (leaf step).
 struct Traverser {
     typedef int StackEntry;
+#ifdef PT_POP_CULL
+    static const int kStack = 2 * PT_STACK_SIZE;
+#else
     static const int kStack = PT_STACK_SIZE;
+#endif
     V3 o, d, inv, oinv;
     HitRec h;
     int current, sp;
     bool result;          // "some triangle of the current leaf was accepted"
+#ifdef PT_POP_CULL   // distances live in the upper half of the lane's stack array
+    static __device__ __forceinline__ void tpush(int* stack, int at, float t) { if (at < PT_SMEM_STACK) smem_tstack()[at * PT_TRACE_THREADS] = t; else stack[PT_STACK_SIZE + at] = __float_as_int(t); }
+    static __device__ __forceinline__ float tat(const int* stack, int at) { return at < PT_SMEM_STACK ? smem_tstack()[at * PT_TRACE_THREADS] : __int_as_float(stack[PT_STACK_SIZE + at]); }
+#endif
 
     __device__ __forceinline__ void begin(V3 org, V3 dir, float tmax) {
         o = org; d = dir;
@@ -116,7 +136,18 @@ struct Traverser {
     __device__ __forceinline__ void idle() { current = 0; sp = 0; }
     __device__ __forceinline__ bool at_leaf() const { return current < 0; }
     // returns true when the ray is finished
+    template <bool ANY>
     __device__ __forceinline__ bool pop(const int* stack) {
+#ifdef PT_POP_CULL
+        if (!ANY) {
+            while (sp > 0) {
+                current = stack_at(stack, --sp);
+                if (current >= 0 && tat(stack, sp) > h.t) continue;
+                return false;
+            }
+            return true;
+        }
+#endif
         if (sp == 0) return true;
         current = stack_at(stack, --sp);
         return false;
@@ -147,6 +178,9 @@ struct Traverser {
             bool swap = d0 > d1;
             current = swap ? sub1 : sub0;
             const int far_child = swap ? sub0 : sub1;
+#ifdef PT_POP_CULL
+            if (!ANY) tpush(stack, sp, swap ? d0 : d1);
+#endif
             stack_push(stack, sp++, far_child);
 #ifdef PT_PREFETCH_FAR   // measured (build with PT_NVCC_EXTRA=-DPT_PREFETCH_FAR): atrium 3.03 -> 2.85 Grays/s, 10M-triangle batch 2.40 -> 1.91:
                          // the prefetch costs an L1 tag look-up on a pipe that is already the bottleneck, and half the pushed nodes are culled
@@ -156,7 +190,7 @@ struct Traverser {
             return false;
         }
         if (hit0 != hit1) { current = hit0 ? sub0 : sub1; return false; }
-        return pop(stack);
+        return pop<ANY>(stack);
     }
     // one triangle of the current leaf; the leaf is always tested to its end marker (IntersectLeaf)
     template <bool ANY>
@@ -167,7 +201,7 @@ struct Traverser {
         result = result || hit;
         if (!last && ri + 1 < s.n_leaf_tris) { current = ~(ri + 1); return false; }
         if (ANY && result) return true;                // IfIfAnyHit returns after the first leaf that hit
-        return pop(stack);
+        return pop<ANY>(stack);
     }
 };
 
