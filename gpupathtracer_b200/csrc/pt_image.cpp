@@ -352,7 +352,7 @@ bool decode_png_rgba8(const std::vector<unsigned char>& b, int& w, int& h, std::
 }
 
 // ------------------------------------------------------------------------------------------------ JPEG
-// Baseline / extended-sequential Huffman JPEG (SOF0, SOF1; 8 bit; 1, 3 or 4 components; any sampling factors; restart
+// Baseline / extended-sequential / progressive Huffman JPEG (SOF0, SOF1, SOF2; 8 bit; 1, 3 or 4 components; any sampling factors; restart
 // intervals) decoded to RGBA8 exactly as stbi_load(.., 4) of the reference's stb_image v2.15 does, which pins four things
 // the JPEG standard leaves open:
 //   * the inverse DCT: the integer "islow" scheme with 12-bit constants computed as (int)(c * 4096 + 0.5) -- truncation,
@@ -366,7 +366,8 @@ bool decode_png_rgba8(const std::vector<unsigned char>& b, int& w, int& h, std::
 //     header, are taken as RGB; four components as CMYK / YCCK per the Adobe transform, multiplied out with
 //     (x * k + 128 + ((x * k + 128) >> 8)) >> 8
 //   * the decode covers whole MCUs; the picture is the top-left width x height of the padded planes
-// Progressive files (SOF2) are refused (stb decodes them; here PT_ERR_IO says so).
+// Progressive files (SOF2) go through the same back end: spectral selection and successive approximation scans (DC
+// first / refinement, AC first / refinement with EOB runs) accumulate un-dequantised coefficients, transformed at EOI.
 namespace {
 
 struct JpegHuff {
@@ -424,6 +425,18 @@ struct JpegBits {
         int v = (int)(buf >> (32 - s));
         buf <<= s; cnt -= s;
         return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v;
+    }
+    int get_bits(int n) {                                         // n unsigned bits (progressive EOB runs)
+        if (cnt < n) fill();
+        int v = (int)(buf >> (32 - n));
+        buf <<= n; cnt -= n;
+        return v;
+    }
+    bool get_bit() {
+        if (cnt < 1) fill();
+        bool v = (buf & 0x80000000u) != 0;
+        buf <<= 1; cnt--;
+        return v;
     }
     void reset() { buf = 0; cnt = 0; nomore = false; marker = 0xff; }
 };
@@ -485,6 +498,7 @@ struct JpegComp {
     int id = 0, h = 1, v = 1, tq = 0, hd = 0, ha = 0, dc_pred = 0;
     int x = 0, y = 0, w2 = 0, h2 = 0;                             // effective size, padded plane size
     std::vector<unsigned char> data;
+    std::vector<short> coeff;                                     // progressive files: 64 coefficients per block of the padded plane
 };
 
 inline unsigned char blinn8(unsigned x, unsigned y) { unsigned t = x * y + 128; return (unsigned char)((t + (t >> 8)) >> 8); }
@@ -561,7 +575,7 @@ bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& 
         m = next_marker();
         while (m == 0xff) { if (br.eof()) { err = "corrupt JPEG (no frame header)"; return false; } m = next_marker(); }
     }
-    if (m == 0xc2) { err = "progressive JPEG is not supported"; return false; }
+    const bool progressive = m == 0xc2;
     {
         int Lf = get16(), prec = br.byte();
         height = get16(); width = get16(); ncomp = br.byte();
@@ -580,6 +594,7 @@ bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& 
             comp[i].x = (width * comp[i].h + hmax - 1) / hmax; comp[i].y = (height * comp[i].v + vmax - 1) / vmax;
             comp[i].w2 = mcux * comp[i].h * 8; comp[i].h2 = mcuy * comp[i].v * 8;
             comp[i].data.assign((size_t)comp[i].w2 * comp[i].h2, 0);
+            if (progressive) comp[i].coeff.assign((size_t)comp[i].w2 * comp[i].h2, 0);
         }
         have_frame = true;
     }
@@ -603,6 +618,73 @@ bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& 
         } while (k < 64);
         return true;
     };
+    // Progressive scans (SOF2): coefficients accumulate over the scans in comp[].coeff, un-dequantised, and are
+    // dequantised + transformed once at the end -- the arithmetic (shifts in 16-bit shorts, refinement of the sign-carrying
+    // magnitude, EOB runs) as stb_image v2.15 does it.
+    int spec_start = 0, spec_end = 63, succ_high = 0, succ_low = 0, eob_run = 0;
+    auto prog_dc = [&](JpegComp& c, short* data) -> bool {
+        if (spec_end != 0) return false;                          // "can't merge dc and ac"
+        if (br.cnt < 16) br.fill();
+        if (succ_high == 0) {
+            if (!have_dc[c.hd]) return false;
+            std::memset(data, 0, 64 * sizeof(short));
+            int t = br.decode(hdc[c.hd]);
+            if (t < 0 || t > 15) return false;
+            int diff = t ? br.receive_extend(t) : 0;
+            c.dc_pred += diff;
+            data[0] = (short)(c.dc_pred * (1 << succ_low));
+        } else if (br.get_bit()) data[0] = (short)(data[0] + (short)(1 << succ_low));
+        return true;
+    };
+    auto prog_ac = [&](JpegComp& c, short* data) -> bool {
+        if (spec_start == 0 || !have_ac[c.ha]) return false;
+        const JpegHuff& h = hac[c.ha];
+        if (succ_high == 0) {
+            if (eob_run) { eob_run--; return true; }
+            int k = spec_start;
+            do {
+                int rs = br.decode(h);
+                if (rs < 0) return false;
+                int s2 = rs & 15, r = rs >> 4;
+                if (s2 == 0) {
+                    if (r < 15) { eob_run = 1 << r; if (r) eob_run += br.get_bits(r); eob_run--; break; }
+                    k += 16;
+                } else {
+                    k += r;
+                    int zig = kDezigzag[k++];
+                    data[zig] = (short)(br.receive_extend(s2) * (1 << succ_low));
+                }
+            } while (k <= spec_end);
+        } else {
+            const short bit = (short)(1 << succ_low);
+            auto refine = [&](short* q) {                         // one correction bit for an already non-zero coefficient
+                if (br.get_bit() && (*q & bit) == 0) *q = (short)(*q > 0 ? *q + bit : *q - bit);
+            };
+            if (eob_run) {
+                eob_run--;
+                for (int k = spec_start; k <= spec_end; k++) { short* q = &data[kDezigzag[k]]; if (*q != 0) refine(q); }
+            } else {
+                int k = spec_start;
+                do {
+                    int rs = br.decode(h);
+                    if (rs < 0) return false;
+                    int s2 = rs & 15, r = rs >> 4;
+                    if (s2 == 0) {
+                        if (r < 15) { eob_run = (1 << r) - 1; if (r) eob_run += br.get_bits(r); r = 64; }   // r = 64: to the end of the band
+                    } else {
+                        if (s2 != 1) return false;
+                        s2 = br.get_bit() ? bit : -bit;
+                    }
+                    while (k <= spec_end) {
+                        short* q = &data[kDezigzag[k++]];
+                        if (*q != 0) refine(q);
+                        else { if (r == 0) { *q = (short)s2; break; } r--; }
+                    }
+                } while (k <= spec_end);
+            }
+        }
+        return true;
+    };
     m = next_marker();
     while (m != 0xd9) {
         if (m == 0xda) {
@@ -614,8 +696,12 @@ bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& 
                 if (which == ncomp || (q >> 4) > 3 || (q & 15) > 3) { err = "corrupt JPEG (scan component)"; return false; }
                 comp[which].hd = q >> 4; comp[which].ha = q & 15; order[i] = which;
             }
-            int ss = br.byte(); br.byte(); int a = br.byte();
-            if (ss != 0 || a != 0) { err = "corrupt JPEG (spectral selection in a sequential scan)"; return false; }
+            spec_start = br.byte(); spec_end = br.byte(); int a = br.byte();
+            succ_high = a >> 4; succ_low = a & 15;
+            if (progressive) {
+                if (spec_start > 63 || spec_end > 63 || spec_start > spec_end || succ_high > 13 || succ_low > 13) { err = "corrupt JPEG (progressive scan header)"; return false; }
+            } else if (spec_start != 0 || a != 0) { err = "corrupt JPEG (spectral selection in a sequential scan)"; return false; }
+            eob_run = 0;
             br.reset();
             for (int i = 0; i < 4; i++) comp[i].dc_pred = 0;
             int todo = restart ? restart : 0x7fffffff;
@@ -627,10 +713,34 @@ bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& 
                 if (!(br.marker >= 0xd0 && br.marker <= 0xd7)) return true;
                 br.reset();
                 for (int i = 0; i < 4; i++) comp[i].dc_pred = 0;
+                eob_run = 0;
                 todo = restart ? restart : 0x7fffffff;
                 return false;
             };
-            if (scan_n == 1) {
+            if (progressive && scan_n == 1) {
+                JpegComp& c = comp[order[0]];
+                int bw = (c.x + 7) >> 3, bh = (c.y + 7) >> 3, cw = c.w2 >> 3;
+                for (int j = 0; j < bh && !stop; j++)
+                    for (int i = 0; i < bw && !stop; i++) {
+                        short* blk = c.coeff.data() + 64 * ((size_t)i + (size_t)j * cw);
+                        if (!(spec_start == 0 ? prog_dc(c, blk) : prog_ac(c, blk))) { err = "corrupt JPEG (progressive scan data)"; return false; }
+                        stop = after_mcu();
+                    }
+            } else if (progressive) {                             // interleaved progressive scans carry DC bits only
+                for (int j = 0; j < mcuy && !stop; j++)
+                    for (int i = 0; i < mcux && !stop; i++) {
+                        for (int k = 0; k < scan_n; k++) {
+                            JpegComp& c = comp[order[k]];
+                            const int cw = c.w2 >> 3;
+                            for (int y = 0; y < c.v; y++)
+                                for (int x = 0; x < c.h; x++) {
+                                    short* blk = c.coeff.data() + 64 * ((size_t)(i * c.h + x) + (size_t)(j * c.v + y) * cw);
+                                    if (!prog_dc(c, blk)) { err = "corrupt JPEG (progressive scan data)"; return false; }
+                                }
+                        }
+                        stop = after_mcu();
+                    }
+            } else if (scan_n == 1) {
                 JpegComp& c = comp[order[0]];
                 int bw = (c.x + 7) >> 3, bh = (c.y + 7) >> 3;
                 for (int j = 0; j < bh && !stop; j++)
@@ -661,6 +771,19 @@ bool decode_jpeg_rgba8(const std::vector<unsigned char>& file, int& width, int& 
         m = next_marker();
     }
     if (!have_frame) return false;
+    if (progressive) {                                            // stbi__jpeg_finish: dequantise + inverse DCT of the blocks that carry image data
+        for (int n = 0; n < ncomp; n++) {
+            JpegComp& c = comp[n];
+            const unsigned short* dq = dequant[c.tq];
+            int bw = (c.x + 7) >> 3, bh = (c.y + 7) >> 3, cw = c.w2 >> 3;
+            for (int j = 0; j < bh; j++)
+                for (int i = 0; i < bw; i++) {
+                    short* blk = c.coeff.data() + 64 * ((size_t)i + (size_t)j * cw);
+                    for (int k = 0; k < 64; k++) blk[k] = (short)(blk[k] * dq[k]);
+                    idct_block(c.data.data() + (size_t)c.w2 * j * 8 + i * 8, c.w2, blk);
+                }
+        }
+    }
     // ---- upsample + colour conversion, row by row
     const bool is_rgb = ncomp == 3 && (rgb_ids == 3 || (adobe == 0 && !jfif));
     rgba.assign((size_t)width * height * 4, 255);

@@ -134,8 +134,8 @@ int32_t pt_environment_size(pt_context* ctx);                        /* 0: const
 int pt_download_environment(pt_context* ctx, float* faces_rgba);     /* 6 x size x size x 4 floats */
 /* All of LoadEnvironmnet: "GENERATE COLOR x" | path ending in .hdr (Radiance RGBE, equirect -> 1024^2 cubemap) | text
  * file naming six face images (TextureCubemap::LoadTexture, Texture.cpp:245-276; faces as .ppm/.bmp/.tga).
- * ".jpg" goes through the JPEG decoder and stb's gamma-2.2 expansion (stbi_loadf on an 8-bit file); progressive JPEGs are
- * refused. */
+ * ".jpg" goes through the JPEG decoder and stb's gamma-2.2 expansion (stbi_loadf on an 8-bit file), progressive files
+ * included. */
 int pt_load_environment(pt_context* ctx, const char* args);
 
 /* ---- BVH: BoundingVolumeHierarchy::BuildBinnedSpatial (BVH.cpp:2197-2293) ---- */
@@ -197,7 +197,7 @@ const char* pt_scene_file_texture_path(const pt_scene_file* sf, int32_t material
 int32_t pt_scene_file_num_shapes(const pt_scene_file* sf);
 const char* pt_scene_file_warnings(const pt_scene_file* sf);
 /* map_Kd image -> RGBA32F texels (byte / 255, rows in file order; Texture2D::LoadTexture, Texture.cpp:146-156, decodes
- * through SOIL2 -- here: .jpg (baseline / extended sequential, as stb_image reads them), .png (all colour types / depths / Adam7), .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
+ * through SOIL2 -- here: .jpg (baseline / extended sequential / progressive, as stb_image reads them), .png (all colour types / depths / Adam7), .ppm, 24/32-bit .bmp, true-colour .tga). *rgba is malloc()ed, release with pt_free. */
 int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgba);
 /* 8-bit RGB PNG, rows top-down (filter 0, stored deflate blocks): the format of Renderer::SaveScreenshot (Renderer.cpp:698). */
 int pt_image_save_png(const char* path, int32_t width, int32_t height, const uint8_t* rgb_top_down);

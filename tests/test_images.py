@@ -260,6 +260,18 @@ JPEG_CASES = [  # (name, size, mode, PIL save options)
     ("restart_rows", (96, 64), "RGB", dict(quality=75, subsampling=2, restart_marker_rows=1)),
     ("restart_blocks", (96, 64), "RGB", dict(quality=75, subsampling=0, restart_marker_blocks=3)),
     ("q100_444", (40, 40), "RGB", dict(quality=100, subsampling=0)),
+    # progressive (SOF2): libjpeg's default script = interleaved DC, per-component AC bands, successive approximation
+    ("prog_420", (64, 48), "RGB", dict(quality=75, subsampling=2, progressive=True)),
+    ("prog_444_q95", (33, 17), "RGB", dict(quality=95, subsampling=0, progressive=True)),
+    ("prog_422_q30", (57, 23), "RGB", dict(quality=30, subsampling=1, progressive=True)),
+    ("prog_420_odd", (17, 33), "RGB", dict(quality=85, subsampling=2, progressive=True)),
+    ("prog_tiny", (1, 1), "RGB", dict(quality=90, subsampling=2, progressive=True)),
+    ("prog_grey", (45, 31), "L", dict(quality=80, progressive=True)),
+    ("prog_cmyk", (24, 24), "CMYK", dict(quality=90, progressive=True)),
+    ("prog_restart", (96, 64), "RGB", dict(quality=75, subsampling=2, progressive=True, restart_marker_rows=1)),
+    ("prog_restart_blocks", (96, 64), "RGB", dict(quality=60, subsampling=0, progressive=True, restart_marker_blocks=3)),
+    ("prog_q100", (40, 40), "RGB", dict(quality=100, subsampling=0, progressive=True, optimize=True)),
+    ("prog_big", (200, 150), "RGB", dict(quality=50, subsampling=2, progressive=True)),
 ]
 
 
@@ -299,13 +311,9 @@ def test_jpeg_reader_other_sampling_factors(tmp_path, factor):
     assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0))
 
 
-def test_jpeg_reader_refuses_progressive_and_damaged(tmp_path):
+def test_jpeg_reader_refuses_damaged(tmp_path):
     Image = _pil()
     rgb = _test_image(32, 32, seed=1)
-    p = str(tmp_path / "prog.jpg")
-    Image.fromarray(rgb).save(p, "JPEG", quality=80, progressive=True)
-    with pytest.raises(api.PtError):
-        api.load_image(p)
     q = str(tmp_path / "base.jpg")
     Image.fromarray(rgb).save(q, "JPEG", quality=80)
     data = open(q, "rb").read()
@@ -313,6 +321,16 @@ def test_jpeg_reader_refuses_progressive_and_damaged(tmp_path):
     cut.write_bytes(data[:len(data) // 3])
     with pytest.raises(api.PtError):
         api.load_image(str(cut))
+    # a progressive file cut inside its scans: stb (and this reader) decode what is there; no crash, same picture
+    p = str(tmp_path / "prog.jpg")
+    Image.fromarray(rgb).save(p, "JPEG", quality=80, progressive=True)
+    data = open(p, "rb").read()
+    cut2 = tmp_path / "cut_prog.jpg"
+    cut2.write_bytes(data[:len(data) * 2 // 3] + b"\xff\xd9")
+    if oracle.have_stbi():
+        want = oracle.ref_stbi_load(str(cut2))
+        if want is not None:
+            assert np.array_equal(api.load_image(str(cut2)), want.astype(np.float32) / np.float32(255.0))
 
 
 def test_jpeg_committed_fixtures():

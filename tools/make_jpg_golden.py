@@ -1,4 +1,4 @@
-"""Writes tests/golden/jpg/{420,444_grey,422_restart,411}.jpg (Pillow / OpenCV encoders) and, beside each, what stbi_load(.., 4)
+"""Writes tests/golden/jpg/{420,grey,422_restart,411,progressive_420,progressive_444_restart}.jpg (Pillow / OpenCV encoders) and, beside each, what stbi_load(.., 4)
 of the stb_image vendored in the reference's SOIL2 returns for it. Needs oracle/_ref; run from the repo root."""
 import os
 import sys
@@ -18,6 +18,9 @@ assert oracle.have_stbi(), "build oracle/_ref first (make -C oracle ref)"
 Image.fromarray(_test_image(40, 24, 1)).save(os.path.join(out, "420.jpg"), "JPEG", quality=75, subsampling=2)
 Image.fromarray(_test_image(21, 13, 2)).convert("L").save(os.path.join(out, "grey.jpg"), "JPEG", quality=85)
 Image.fromarray(_test_image(33, 20, 3)).save(os.path.join(out, "422_restart.jpg"), "JPEG", quality=60, subsampling=1, restart_marker_rows=1)
+Image.fromarray(_test_image(45, 28, 5)).save(os.path.join(out, "progressive_420.jpg"), "JPEG", quality=70, subsampling=2, progressive=True)
+Image.fromarray(_test_image(30, 22, 6)).save(os.path.join(out, "progressive_444_restart.jpg"), "JPEG", quality=90, subsampling=0, progressive=True,
+                                             restart_marker_blocks=5)
 cv2.imwrite(os.path.join(out, "411.jpg"), _test_image(37, 19, 4)[..., ::-1],
             [cv2.IMWRITE_JPEG_QUALITY, 88, cv2.IMWRITE_JPEG_SAMPLING_FACTOR, cv2.IMWRITE_JPEG_SAMPLING_FACTOR_411])
 for f in sorted(os.listdir(out)):
