@@ -284,7 +284,7 @@ def run_pathtrace(args, name, wl):
     scene = build_scene(wl)
     t0 = time.perf_counter()
     r = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
-                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh="device" if args.builder == "device" else "build",
+                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh={"device": "device", "ploc": "ploc"}.get(args.builder, "build"),
                               bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     cam = make_camera(scene, W, H)
@@ -377,7 +377,7 @@ def run_pathtrace(args, name, wl):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
                        "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
-                       "bvh": f"{'device LBVH' if args.builder == 'device' else 'own SBVH'} builder, {args.bvh} layout",
+                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                        "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
                        "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
@@ -426,7 +426,7 @@ def run_micro(args, name, wl):
     n = wl["n_rays"]
     scene, closest, anyr = micro_scene_and_rays(n, 0xB200 + 7 * rank)
     t0 = time.perf_counter()
-    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh="device" if args.builder == "device" else "build",
+    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh={"device": "device", "ploc": "ploc"}.get(args.builder, "build"),
                               bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     d_closest = torch.from_numpy(closest).cuda()
@@ -478,7 +478,7 @@ def run_micro(args, name, wl):
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "rays_per_step": 2 * n,
-                       "bvh": f"{'device LBVH' if args.builder == 'device' else 'own SBVH'} builder, {args.bvh} layout",
+                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                        "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "bvh_nodes": int(r.bvh_stats.n_nodes), "bvh_refs": int(r.bvh_stats.n_refs),
                        "l2": "ray batches (2 x 512 MB) and tree + leaf stream (~1.2 GB) exceed the 126 MB L2",
@@ -531,27 +531,33 @@ def run_primary(args, name, wl):
     cam = make_camera(scene, W, H)
     r.lib.pt_set_camera(r.ctx, cam.plane)
     n = W * H
-    # the device builder (Morton LBVH): build time and what its tree costs to traverse
+    # the device builders (Morton LBVH, PLOC): build time and what their trees cost to traverse
     dev = {}
     if args.bvh == "reference":
-        s2 = Scene(scene.data)
-        r2 = Renderer().Initialize(W, H, s2, max_depth=1, device=local, seed=1, bvh="device")
-        dev_builds = [float(r2.bvh_stats.build_ms)]
         import ctypes as C
         from gpupathtracer_b200.api import pt_bvh_stats
-        for _ in range(4):
-            st = pt_bvh_stats(); r2.lib.pt_build_bvh_device(r2.ctx, C.byref(st)); dev_builds.append(float(st.build_ms)); tot = float(st.total_ms)
-        dev = {"device_lbvh_kernels_best_of_5": min(dev_builds), "device_lbvh_total_call_ms": tot,
-               "device_lbvh_sah_cost": float(r2.bvh_stats.sah_cost), "device_lbvh_depth": int(r2.bvh_stats.max_depth)}
-        r2.lib.pt_set_camera(r2.ctx, cam.plane)
-        pr2 = r2.RaygenProbe(0, n)
-        rays2 = np.zeros((n, 8), np.float32); rays2[:, 0:3] = pr2[:, 2:5]; rays2[:, 4:7] = pr2[:, 5:8]; rays2[:, 7] = 1e20
-        d2 = torch.from_numpy(rays2).cuda(); h2 = torch.empty((n, 4), dtype=torch.float32, device="cuda"); torch.cuda.synchronize()
-        ms2 = []
-        for _ in range(8):
-            r2.TraceClosestDevice(d2.data_ptr(), n, h2.data_ptr()); ms2.append(r2.LastDeviceMs())
-        dev["device_lbvh_primary_mrays_s"] = n / min(ms2) / 1e3
-        r2.CleanUp()
+        for key, which in (("device_lbvh", "device"), ("device_ploc", "ploc")):
+            s2 = Scene(scene.data)
+            r2 = Renderer().Initialize(W, H, s2, max_depth=1, device=local, seed=1, bvh=which)
+            dev_builds = [float(r2.bvh_stats.build_ms)]
+            for _ in range(4):
+                st = pt_bvh_stats()
+                if which == "ploc":
+                    r2.lib.pt_build_bvh_device_ploc(r2.ctx, 16, C.byref(st))
+                else:
+                    r2.lib.pt_build_bvh_device(r2.ctx, C.byref(st))
+                dev_builds.append(float(st.build_ms)); tot = float(st.total_ms)
+            dev.update({key + "_kernels_best_of_5": min(dev_builds), key + "_total_call_ms": tot,
+                        key + "_sah_cost": float(r2.bvh_stats.sah_cost), key + "_depth": int(r2.bvh_stats.max_depth)})
+            r2.lib.pt_set_camera(r2.ctx, cam.plane)
+            pr2 = r2.RaygenProbe(0, n)
+            rays2 = np.zeros((n, 8), np.float32); rays2[:, 0:3] = pr2[:, 2:5]; rays2[:, 4:7] = pr2[:, 5:8]; rays2[:, 7] = 1e20
+            d2 = torch.from_numpy(rays2).cuda(); h2 = torch.empty((n, 4), dtype=torch.float32, device="cuda"); torch.cuda.synchronize()
+            ms2 = []
+            for _ in range(8):
+                r2.TraceClosestDevice(d2.data_ptr(), n, h2.data_ptr()); ms2.append(r2.LastDeviceMs())
+            dev[key + "_primary_mrays_s"] = n / min(ms2) / 1e3
+            r2.CleanUp()
     pr = r.RaygenProbe(0, n)
     rays = np.zeros((n, 8), np.float32)
     rays[:, 0:3] = pr[:, 2:5]; rays[:, 4:7] = pr[:, 5:8]; rays[:, 7] = 1e20
@@ -629,8 +635,9 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--builder", default="host", choices=["host", "device"],
-                    help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels")
+    ap.add_argument("--builder", default="host", choices=["host", "device", "ploc"],
+                    help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels; ploc: the same with a "
+                         "PLOC hierarchy (pt_build_bvh_device_ploc)")
     ap.add_argument("--bvh", default="reference", choices=["reference", "wide", "wide4"],
                     help="device BVH layout: the reference's binary fp32 tree (bit-exact) or the compressed 8-/4-wide collapse of it")
     args = ap.parse_args()

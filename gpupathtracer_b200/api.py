@@ -79,6 +79,7 @@ SYMBOLS = [
     ("pt_set_bvh", C.c_int, [_P, _P, C.c_int32, _P, C.c_int32]),
     ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_build_bvh_device", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
+    ("pt_build_bvh_device_ploc", C.c_int, [_P, C.c_int32, C.POINTER(pt_bvh_stats)]),
     ("pt_bvh_build_host", C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(_F), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32), C.POINTER(pt_bvh_stats)]),
     ("pt_free", None, [_P]),
     ("pt_bvh_collapse_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, C.c_int32, C.POINTER(C.POINTER(C.c_uint8)),
@@ -390,9 +391,12 @@ class Renderer:
         _check(self.lib.pt_set_environment_color(ctx, _f3(scene.env_color)))
         if getattr(scene, "env_cubemap", None) is not None:
             self.SetEnvironmentCubemap(scene.env_cubemap)
-        if bvh == "device":
+        if bvh in ("device", "ploc"):
             stats = pt_bvh_stats()
-            _check(self.lib.pt_build_bvh_device(ctx, C.byref(stats)))
+            if bvh == "ploc":
+                _check(self.lib.pt_build_bvh_device_ploc(ctx, int(os.environ.get("PT_PLOC_RADIUS", "16")), C.byref(stats)))
+            else:
+                _check(self.lib.pt_build_bvh_device(ctx, C.byref(stats)))
             self.bvh_stats = stats
             nodes, refs = self.GetBVH()            # reads the serialised tree back from the device
             scene.set_bvh(nodes, refs)

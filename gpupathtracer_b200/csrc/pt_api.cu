@@ -560,7 +560,7 @@ int pt_set_bvh(pt_context* c, const float* nodes, int32_t n_nodes, const int32_t
     int64_t nt = c->h_tris.empty() ? -1 : (int64_t)(c->h_tris.size() / 20);
     int depth = validate_bvh(nodes, n_nodes, refs, n_refs, nt, msg, &n_leaves);
     if (depth < 0) return fail(PT_ERR_INVALID, "pt_set_bvh: %s", msg.c_str());
-    if (depth >= 64) return fail(PT_ERR_LIMIT, "pt_set_bvh: tree depth %d exceeds the traversal stack (64)", depth);
+    if (depth >= PT_MAX_TREE_DEPTH) return fail(PT_ERR_LIMIT, "pt_set_bvh: tree depth %d exceeds the traversal stack (%d)", depth, PT_MAX_TREE_DEPTH);
     c->h_bvh.nodes.assign(nodes, nodes + 8 * (size_t)n_nodes);
     c->h_bvh.refs.assign(refs, refs + n_refs);
     c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = n_leaves;
@@ -593,7 +593,13 @@ int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
 }
 
 // The device builder (pt_bvh_gpu.cu): Morton LBVH, one triangle per leaf, reference serialised form
-int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) {
+static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radius);
+int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) { return build_bvh_on_device(c, stats, 0); }
+int pt_build_bvh_device_ploc(pt_context* c, int32_t radius, pt_bvh_stats* stats) {
+    if (radius < 1 || radius > 256) return fail(PT_ERR_INVALID, "pt_build_bvh_device_ploc: radius 1 .. 256");
+    return build_bvh_on_device(c, stats, radius);
+}
+static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radius) {
     if (!c) return fail(PT_ERR_INVALID, "pt_build_bvh_device: null context");
     if (c->h_tris.empty() || !c->d_tris.p) return fail(PT_ERR_INVALID, "pt_build_bvh_device: call pt_set_triangles first");
     const int64_t n = (int64_t)(c->h_tris.size() / 20);
@@ -609,12 +615,23 @@ int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) {
     CK(c->d_leaf.alloc((size_t)n));
     float kernel_ms = 0.0f; int depth = 0;
     int launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
-                                     c->stream, &kernel_ms);
+                                     c->stream, &kernel_ms, ploc_radius);
     if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
     c->counters.kernel_launches += launches;
-    if (depth >= 64) {
+    if (depth >= PT_MAX_TREE_DEPTH && ploc_radius > 0) {
+        // agglomerative clustering does not bound the depth (chains of small clusters joining a big one); the Morton
+        // hierarchy does (30 key bits + index tie-break), so it takes over. Not an error: the note is left in pt_last_error().
+        fail(PT_OK, "pt_build_bvh_device_ploc: PLOC tree depth %d exceeds the traversal stack (%d); Morton hierarchy used instead", depth, PT_MAX_TREE_DEPTH);
+        float ms2 = 0.0f;
+        launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
+                                     c->stream, &ms2, 0);
+        if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
+        c->counters.kernel_launches += launches;
+        kernel_ms += ms2;
+    }
+    if (depth >= PT_MAX_TREE_DEPTH) {
         c->d_pairs.release(); c->d_leaf.release();
-        return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (64); use pt_build_bvh", depth);
+        return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (%d); use pt_build_bvh", depth, PT_MAX_TREE_DEPTH);
     }
     c->n_leaf = (int)n;
     c->top_pairs = 0;                                             // Karras order: the top levels are not contiguous

@@ -3,6 +3,14 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// Deepest tree the binary traversal kernels accept (entries of the per-lane stack). The reference's shader has 27
+// (BVH.glsl:489) and is undefined beyond; uploads of deeper trees are refused with PT_ERR_LIMIT. 96 rather than 64 since
+// the PLOC builder came out 64-66 deep on the 10 M-triangle nested-shell mesh; entries beyond the few in shared memory
+// are local memory that costs nothing until touched.
+#ifndef PT_MAX_TREE_DEPTH
+#define PT_MAX_TREE_DEPTH 96
+#endif
+
 namespace pt {
 
 // ---- BVH, PT_BVH_REFERENCE layout -------------------------------------------------------------

@@ -17,7 +17,7 @@
 
 namespace pt {
 
-#define PT_STACK_SIZE 64   // reference: 27 (BVH.glsl:489); upload rejects deeper trees with PT_ERR_LIMIT
+#define PT_STACK_SIZE PT_MAX_TREE_DEPTH   // reference: 27 (BVH.glsl:489); upload rejects deeper trees with PT_ERR_LIMIT
 
 struct HitRec { float t, u, v; int tri; };
 

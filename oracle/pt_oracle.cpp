@@ -117,7 +117,7 @@ inline void leaf(const OrScene& s, int leafv, const Ray& ray, Hit& h, bool& resu
     }
 }
 
-const int kStack = 64;   // reference: 27 (BVH.glsl:489); deeper trees are UB there, defined here
+const int kStack = 96;   // reference: 27 (BVH.glsl:489); deeper trees are UB there, defined here (libb200pt accepts depth < 96)
 
 // IfIfClosestHit, BVH.glsl:634-767 (SPECULATIVE_TRAVERSAL off).
 bool closest_hit(const OrScene& s, const Ray& ray, Hit& h, Cnt& c) {

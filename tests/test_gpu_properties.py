@@ -96,14 +96,16 @@ def test_full_size_batch_closest_vs_any_consistency(atrium_full):
     r2.CleanUp()
 
 
+@pytest.mark.parametrize("builder", ["device", "ploc"])
 @pytest.mark.parametrize("name", ["cornell", "soup", "bunny"])
-def test_device_built_bvh(name):
-    """pt_build_bvh_device (Morton LBVH built by CUDA kernels): the tree comes back in the reference's serialised form,
+def test_device_built_bvh(name, builder):
+    """pt_build_bvh_device (Morton LBVH built by CUDA kernels) and pt_build_bvh_device_ploc (the same pipeline with the
+    hierarchy from parallel locally-ordered clustering): the tree comes back in the reference's serialised form,
     references every triangle exactly once, its boxes enclose their subtrees, the CUDA walk of it is bit-exact against
     the ORACLE walking the same tree, and it finds the same surfaces as the reference builder's tree."""
     s_ref = get_scene(name)
     s = Scene(s_ref.data)
-    r = Renderer().Initialize(64, 64, s, bvh="device")
+    r = Renderer().Initialize(64, 64, s, bvh=builder)
     st = r.bvh_stats
     nodes, refs = s.nodes, s.refs
     n = s.tris.shape[0]
