@@ -435,12 +435,226 @@ bool load_obj_file(const std::string& path, SceneFile& out, std::string& err) {
 }
 
 // ---- small image readers for map_Kd (the reference decodes through SOIL2; no decoder library exists here):
-// binary/ASCII PPM, uncompressed or RLE true-colour TGA, 24/32-bit BMP. Texels become RGBA32F = byte / 255 (GL_RGBA8
-// unorm, Texture.cpp:146-156), rows in file order.
+// binary/ASCII PPM here; TGA and BMP below, JPEG and PNG in pt_image.cpp -- each held byte-identical to the stb_image the
+// reference's SOIL2 carries. Texels become RGBA32F = byte / 255 (GL_RGBA8 unorm, Texture.cpp:146-156), top row first.
 static bool read_file(const std::string& path, std::vector<unsigned char>& buf) {
     std::ifstream f(path, std::ios::binary);
     if (!f) return false;
     buf.assign(std::istreambuf_iterator<char>(f), std::istreambuf_iterator<char>());
+    return true;
+}
+
+// Byte cursor with stb_image's end-of-data behaviour: reads past the end give 0, a negative skip goes to the end.
+struct LdrReader {
+    const std::vector<unsigned char>& b; size_t pos = 0;
+    int get8() { return pos < b.size() ? b[pos++] : 0; }
+    int get16le() { int z = get8(); return z + (get8() << 8); }
+    uint32_t get32le() { uint32_t z = (uint32_t)get16le(); return z + ((uint32_t)get16le() << 16); }
+    void skip(long n) { if (n < 0) pos = b.size(); else pos = std::min(b.size(), pos + (size_t)n); }
+};
+
+// .bmp as stbi_load(.., 4) of the reference's stb_image v2.15 returns it: header sizes 12 / 40 / 56 / 108 / 124; 4- and
+// 8-bit palettes, 16 / 24 / 32 bits with default or BI_BITFIELDS masks (channels widened by bit replication); no RLE, no
+// 1-bit; a 32-bit file of a 40/56-byte header whose alpha is zero everywhere comes back opaque; rows bottom-up unless the
+// height is negative. Quirk kept: with a 40-byte header + BI_BITFIELDS the three masks are read and THEN
+// `offset - 14 - header` bytes are skipped, so the pixels start 12 bytes late when `offset` accounts for the masks.
+static bool decode_bmp_rgba8(const std::vector<unsigned char>& file, int& w, int& h, std::vector<unsigned char>& out) {
+    LdrReader s{file};
+    if (s.get8() != 'B' || s.get8() != 'M') return false;
+    s.get32le(); s.get16le(); s.get16le();
+    const int offset = (int)s.get32le(), hsz = (int)s.get32le();
+    uint32_t mr = 0, mg = 0, mb = 0, ma = 0, all_a = 255;
+    if (hsz != 12 && hsz != 40 && hsz != 56 && hsz != 108 && hsz != 124) return false;
+    int iw, ih;
+    if (hsz == 12) { iw = s.get16le(); ih = s.get16le(); } else { iw = (int)s.get32le(); ih = (int)s.get32le(); }
+    if (s.get16le() != 1) return false;
+    const int bpp = s.get16le();
+    if (bpp == 1) return false;
+    if (hsz != 12) {
+        const int compress = (int)s.get32le();
+        if (compress == 1 || compress == 2) return false;
+        for (int i = 0; i < 5; i++) s.get32le();
+        if (hsz == 40 || hsz == 56) {
+            if (hsz == 56) for (int i = 0; i < 4; i++) s.get32le();
+            if (bpp == 16 || bpp == 32) {
+                if (compress == 0) {
+                    if (bpp == 32) { mr = 0xffu << 16; mg = 0xffu << 8; mb = 0xffu; ma = 0xffu << 24; all_a = 0; }
+                    else { mr = 31u << 10; mg = 31u << 5; mb = 31u; }
+                } else if (compress == 3) {
+                    mr = s.get32le(); mg = s.get32le(); mb = s.get32le();
+                    if (mr == mg && mg == mb) return false;
+                } else return false;
+            }
+        } else {
+            mr = s.get32le(); mg = s.get32le(); mb = s.get32le(); ma = s.get32le();
+            s.get32le();
+            for (int i = 0; i < 12; i++) s.get32le();
+            if (hsz == 124) for (int i = 0; i < 4; i++) s.get32le();
+        }
+    }
+    const bool flip = ih > 0;
+    ih = ih < 0 ? -ih : ih;
+    if (iw <= 0 || ih <= 0 || (double)iw * ih > 1.0e9) return false;
+    w = iw; h = ih;
+    int psize = 0;
+    if (hsz == 12) { if (bpp < 24) psize = (offset - 14 - 24) / 3; }
+    else if (bpp < 16) psize = (offset - 14 - hsz) >> 2;
+    out.assign((size_t)w * h * 4, 255);
+    size_t z = 0;
+    if (bpp < 16) {
+        if (psize == 0 || psize > 256) return false;
+        unsigned char pal[256][3];
+        for (int i = 0; i < psize; i++) { pal[i][2] = (unsigned char)s.get8(); pal[i][1] = (unsigned char)s.get8(); pal[i][0] = (unsigned char)s.get8(); if (hsz != 12) s.get8(); }
+        for (int i = psize; i < 256; i++) pal[i][0] = pal[i][1] = pal[i][2] = 0;     // stb reads its uninitialised stack here; files that index past the palette are damaged
+        s.skip((long)offset - 14 - hsz - (long)psize * (hsz == 12 ? 3 : 4));
+        int width;
+        if (bpp == 4) width = (w + 1) >> 1; else if (bpp == 8) width = w; else return false;
+        const int pad = (-width) & 3;
+        for (int j = 0; j < h; j++) {
+            for (int i = 0; i < w; i += 2) {
+                int v = s.get8(), v2 = 0;
+                if (bpp == 4) { v2 = v & 15; v >>= 4; }
+                out[z] = pal[v][0]; out[z + 1] = pal[v][1]; out[z + 2] = pal[v][2]; z += 4;
+                if (i + 1 == w) break;
+                v = bpp == 8 ? s.get8() : v2;
+                out[z] = pal[v][0]; out[z + 1] = pal[v][1]; out[z + 2] = pal[v][2]; z += 4;
+            }
+            s.skip(pad);
+        }
+    } else {
+        auto high_bit = [](uint32_t v) { int n = -1; while (v) { n++; v >>= 1; } return n; };
+        auto bitcount = [](uint32_t v) { int n = 0; while (v) { n += (int)(v & 1u); v >>= 1; } return n; };
+        auto shiftsigned = [](int v, int shift, int bits) {
+            if (shift < 0) v <<= -shift; else v >>= shift;
+            int result = v;
+            for (int q = bits; q < 8; q += bits) result += v >> q;
+            return result;
+        };
+        s.skip((long)offset - 14 - hsz);
+        int width = bpp == 24 ? 3 * w : bpp == 16 ? 2 * w : 0;
+        const int pad = (-width) & 3;
+        int easy = 0;
+        if (bpp == 24) easy = 1;
+        else if (bpp == 32 && mb == 0xffu && mg == 0xff00u && mr == 0x00ff0000u && ma == 0xff000000u) easy = 2;
+        int rshift = 0, gshift = 0, bshift = 0, ashift = 0, rcount = 0, gcount = 0, bcount = 0, acount = 0;
+        if (!easy) {
+            if (!mr || !mg || !mb) return false;
+            rshift = high_bit(mr) - 7; rcount = bitcount(mr); gshift = high_bit(mg) - 7; gcount = bitcount(mg);
+            bshift = high_bit(mb) - 7; bcount = bitcount(mb); ashift = high_bit(ma) - 7; acount = bitcount(ma);
+            if (rcount == 0 || gcount == 0 || bcount == 0) return false;
+        }
+        for (int j = 0; j < h; j++) {
+            for (int i = 0; i < w; i++, z += 4) {
+                if (easy) {
+                    out[z + 2] = (unsigned char)s.get8(); out[z + 1] = (unsigned char)s.get8(); out[z] = (unsigned char)s.get8();
+                    unsigned a = easy == 2 ? (unsigned)s.get8() : 255u;
+                    all_a |= a; out[z + 3] = (unsigned char)a;
+                } else {
+                    uint32_t v = bpp == 16 ? (uint32_t)s.get16le() : s.get32le();
+                    out[z] = (unsigned char)(shiftsigned((int)(v & mr), rshift, rcount) & 255);
+                    out[z + 1] = (unsigned char)(shiftsigned((int)(v & mg), gshift, gcount) & 255);
+                    out[z + 2] = (unsigned char)(shiftsigned((int)(v & mb), bshift, bcount) & 255);
+                    int a = ma ? shiftsigned((int)(v & ma), ashift, acount) : 255;
+                    all_a |= (uint32_t)a; out[z + 3] = (unsigned char)(a & 255);
+                }
+            }
+            s.skip(pad);
+        }
+    }
+    if (all_a == 0) for (size_t i = 3; i < out.size(); i += 4) out[i] = 255;
+    if (flip)
+        for (int j = 0; j < h / 2; j++)
+            std::swap_ranges(out.begin() + (size_t)j * w * 4, out.begin() + (size_t)(j + 1) * w * 4, out.begin() + (size_t)(h - 1 - j) * w * 4);
+    return true;
+}
+
+// .tga as stbi_load(.., 4) of stb_image v2.15 returns it: image types 1 / 2 / 3 and their RLE forms 9 / 10 / 11; 8-bit grey,
+// 16-bit grey + alpha, 15/16-bit RGB (5 bits each, (c * 255) / 31, no alpha), 24/32-bit BGR(A); colour maps with 8- or
+// 16-bit indices and entries of any of those formats (stb skips `first entry index` BYTES before the map and maps an index
+// past the end to entry 0); origin bit 5 = top-down, the horizontal flip bit is ignored; TGA has no magic number, so the
+// header must pass stb's plausibility test.
+static bool decode_tga_rgba8(const std::vector<unsigned char>& file, int& w, int& h, std::vector<unsigned char>& out) {
+    if (file.size() < 18) return false;
+    LdrReader s{file};
+    const int id_len = s.get8(), indexed = s.get8();
+    int type = s.get8();
+    const int pal_start = s.get16le(), pal_len = s.get16le(), pal_bits = s.get8();
+    s.get16le(); s.get16le();
+    const int tw = s.get16le(), th = s.get16le(), bpp = s.get8(), desc = s.get8();
+    // stbi__tga_test
+    if (indexed > 1) return false;
+    if (indexed == 1) {
+        if (type != 1 && type != 9) return false;
+        if (pal_bits != 8 && pal_bits != 15 && pal_bits != 16 && pal_bits != 24 && pal_bits != 32) return false;
+        if (bpp != 8 && bpp != 16) return false;
+    } else {
+        if (type != 2 && type != 3 && type != 10 && type != 11) return false;
+        if (bpp != 8 && bpp != 15 && bpp != 16 && bpp != 24 && bpp != 32) return false;
+    }
+    if (tw < 1 || th < 1) return false;
+    bool rle = false;
+    if (type >= 8) { type -= 8; rle = true; }
+    const bool inverted = ((desc >> 5) & 1) == 0;                        // bottom-up file: rows are flipped after decoding
+    bool rgb16 = false;
+    auto comp_of = [&](int bits, bool grey) -> int {
+        switch (bits) {
+            case 8: return 1;
+            case 16: if (grey) return 2;                                   // fall through
+            case 15: rgb16 = true; return 3;
+            case 24: case 32: return bits / 8;
+            default: return 0;
+        }
+    };
+    const int comp = indexed ? comp_of(pal_bits, false) : comp_of(bpp, type == 3);
+    if (!comp) return false;
+    w = tw; h = th;
+    const size_t n = (size_t)w * h;
+    std::vector<unsigned char> data(n * comp), palette;
+    auto read_rgb16 = [&](unsigned char* o) {
+        unsigned px = (unsigned)s.get16le();
+        o[0] = (unsigned char)((((px >> 10) & 31) * 255) / 31); o[1] = (unsigned char)((((px >> 5) & 31) * 255) / 31); o[2] = (unsigned char)(((px & 31) * 255) / 31);
+    };
+    s.skip(id_len);
+    if (indexed) {
+        s.skip(pal_start);
+        palette.assign((size_t)pal_len * comp, 0);
+        if (rgb16) for (int i = 0; i < pal_len; i++) read_rgb16(palette.data() + (size_t)i * comp);
+        else {
+            if (s.pos + palette.size() > file.size()) return false;       // "bad palette"
+            std::memcpy(palette.data(), file.data() + s.pos, palette.size()); s.pos += palette.size();
+        }
+    }
+    unsigned char raw[4] = {0, 0, 0, 0};
+    int rle_count = 0; bool repeating = false, read_next = true;
+    for (size_t i = 0; i < n; i++) {
+        if (rle) {
+            if (rle_count == 0) { int cmd = s.get8(); rle_count = 1 + (cmd & 127); repeating = (cmd >> 7) != 0; read_next = true; }
+            else if (!repeating) read_next = true;
+        } else read_next = true;
+        if (read_next) {
+            if (indexed) {
+                int idx = bpp == 8 ? s.get8() : s.get16le();
+                if (idx >= pal_len) idx = 0;
+                for (int j = 0; j < comp; j++) raw[j] = palette.empty() ? 0 : palette[(size_t)idx * comp + j];
+            } else if (rgb16) read_rgb16(raw);
+            else for (int j = 0; j < comp; j++) raw[j] = (unsigned char)s.get8();
+            read_next = false;
+        }
+        for (int j = 0; j < comp; j++) data[i * comp + j] = raw[j];
+        rle_count--;
+    }
+    out.assign(n * 4, 255);
+    for (int y = 0; y < h; y++) {
+        const int src = inverted ? h - 1 - y : y;
+        for (int x = 0; x < w; x++) {
+            const unsigned char* q = data.data() + ((size_t)src * w + x) * comp;
+            unsigned char* o = out.data() + ((size_t)y * w + x) * 4;
+            if (comp == 1) { o[0] = o[1] = o[2] = q[0]; }
+            else if (comp == 2) { o[0] = o[1] = o[2] = q[0]; o[3] = q[1]; }
+            else if (rgb16) { o[0] = q[0]; o[1] = q[1]; o[2] = q[2]; }
+            else { o[0] = q[2]; o[1] = q[1]; o[2] = q[0]; if (comp == 4) o[3] = q[3]; }
+        }
+    }
     return true;
 }
 
@@ -494,48 +708,12 @@ bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<flo
         }
         return true;
     }
-    if (b[0] == 'B' && b[1] == 'M' && b.size() > 54) {
-        auto u32 = [&](size_t o) { return (uint32_t)b[o] | ((uint32_t)b[o + 1] << 8) | ((uint32_t)b[o + 2] << 16) | ((uint32_t)b[o + 3] << 24); };
-        uint32_t off = u32(10); int32_t bw = (int32_t)u32(18), bh = (int32_t)u32(22); int bpp = b[28] | (b[29] << 8);
-        if (u32(30) != 0 || (bpp != 24 && bpp != 32) || bw <= 0 || bh == 0) return false;
-        w = bw; h = bh < 0 ? -bh : bh;
-        size_t stride = ((size_t)w * (bpp / 8) + 3) & ~(size_t)3;
-        if (b.size() < off + stride * h) return false;
-        rgba.assign((size_t)w * h * 4, 1.0f);
-        for (int y = 0; y < h; y++) {
-            int src = bh < 0 ? y : h - 1 - y;                           // BMP rows are bottom-up unless height < 0
-            for (int x = 0; x < w; x++) {
-                const unsigned char* q = b.data() + off + stride * src + (size_t)x * (bpp / 8);
-                put((size_t)y * w + x, q[2], q[1], q[0], bpp == 32 ? q[3] : 255);
-            }
-        }
-        return true;
-    }
-    // TGA: no magic; accept true-colour types 2 (raw) and 10 (RLE)
-    int idlen = b[0], cmap = b[1], type = b[2], bpp = b[16];
-    w = b[12] | (b[13] << 8); h = b[14] | (b[15] << 8);
-    if (cmap != 0 || (type != 2 && type != 10) || (bpp != 24 && bpp != 32) || w <= 0 || h <= 0) return false;
-    size_t pos = 18 + idlen, n = (size_t)w * h, bytes = bpp / 8;
-    bool top_down = (b[17] & 0x20) != 0;
-    rgba.assign(n * 4, 1.0f);
-    std::vector<unsigned char> px(n * 4, 255);
-    size_t i = 0;
-    while (i < n && pos < b.size()) {
-        int count = 1; bool rle = false;
-        if (type == 10) { unsigned char hd = b[pos++]; count = (hd & 127) + 1; rle = hd & 128; }
-        for (int k = 0; k < count && i < n; k++, i++) {
-            if (pos + bytes > b.size()) return false;
-            px[4 * i] = b[pos + 2]; px[4 * i + 1] = b[pos + 1]; px[4 * i + 2] = b[pos]; if (bytes == 4) px[4 * i + 3] = b[pos + 3];
-            if (!rle || k == count - 1) pos += bytes;
-        }
-    }
-    for (int y = 0; y < h; y++) {
-        int src = top_down ? y : h - 1 - y;
-        for (int x = 0; x < w; x++) {
-            const unsigned char* q = px.data() + 4 * ((size_t)src * w + x);
-            put((size_t)y * w + x, q[0], q[1], q[2], q[3]);
-        }
-    }
+    std::vector<unsigned char> px;
+    if (b[0] == 'B' && b[1] == 'M') {
+        if (!decode_bmp_rgba8(b, w, h, px)) return false;
+    } else if (!decode_tga_rgba8(b, w, h, px)) return false;
+    rgba.resize(px.size());
+    for (size_t i = 0; i < px.size(); i++) rgba[i] = px[i] / 255.0f;
     return true;
 }
 
@@ -576,7 +754,7 @@ int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgb
     if (!path || !width || !height || !rgba) return PT_ERR_INVALID;
     int w = 0, h = 0; std::vector<float> px;
     if (!pt::load_image_rgba32f(path, w, h, px)) {
-        pt::set_last_error((std::string("cannot decode '") + path + "' (supported: .ppm, .bmp 24/32 bit, .tga true colour)").c_str());
+        pt::set_last_error((std::string("cannot decode '") + path + "' (supported: .jpg, .png, .bmp, .tga, .ppm as stb_image reads them)").c_str());
         return PT_ERR_IO;
     }
     *width = w; *height = h;

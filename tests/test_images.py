@@ -343,6 +343,52 @@ def test_jpeg_committed_fixtures():
         assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0)), n
 
 
+def test_tga_and_bmp_readers_match_stb(tmp_path):
+    """.tga (types 1/2/3/9/10/11: grey, grey + alpha, 15/16/24/32-bit colour, colour maps, RLE, both origins) and .bmp (4/8-bit
+    palettes, 16/24/32 bits, BI_BITFIELDS, V4 headers, OS/2 headers, top-down, the all-zero-alpha rule) written by Pillow or
+    packed by hand in tests/ldr_cases.py decode to the bytes stbi_load(.., 4) of the reference's stb_image gives -- Crytek's
+    Sponza ships its textures as .tga."""
+    import ldr_cases
+    if not oracle.have_stbi():
+        pytest.skip("oracle/_ref not built: covered by test_tga_bmp_committed_fixtures")
+    rgb = _test_image(37, 23, seed=3)
+    files = {}
+    try:
+        for name, (img, opts) in ldr_cases.pillow_cases(rgb).items():
+            p = str(tmp_path / name); img.save(p, **opts); files[name] = p
+    except ImportError:
+        pass
+    for name, data in ldr_cases.handmade_cases(rgb).items():
+        p = tmp_path / name; p.write_bytes(data); files[name] = str(p)
+    assert len(files) >= 11
+    for name, p in files.items():
+        want = oracle.ref_stbi_load(p)
+        assert want is not None, name
+        got = api.load_image(p)
+        assert got.shape == (23, 37, 4), name
+        assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0)), name
+    # what stb refuses is refused: 1-bit and RLE-compressed .bmp, a colour-mapped .tga of a true-colour type
+    from PIL import Image
+    bad = {"mono.bmp": None, "typed_wrong.tga": None}
+    Image.fromarray(rgb).convert("1").save(str(tmp_path / "mono.bmp"))
+    (tmp_path / "typed_wrong.tga").write_bytes(bytes([0, 1, 2, 0, 0, 4, 0, 24, 0, 0, 0, 0, 2, 0, 2, 0, 24, 0]) + bytes(24))
+    for name in bad:
+        assert oracle.ref_stbi_load(str(tmp_path / name)) is None, name
+        with pytest.raises(api.PtError):
+            api.load_image(str(tmp_path / name))
+
+
+def test_tga_bmp_committed_fixtures():
+    """tests/golden/ldr/*.{tga,bmp} with stb_image's result recorded beside each (tools/make_ldr_golden.py)."""
+    d = os.path.join(GOLDEN, "ldr")
+    names = sorted(f for f in os.listdir(d) if f.endswith((".tga", ".bmp")))
+    assert len(names) >= 6
+    for n in names:
+        got = api.load_image(os.path.join(d, n))
+        want = np.load(os.path.join(d, n + "_stbi.npy"))
+        assert np.array_equal(got, want.astype(np.float32) / np.float32(255.0)), n
+
+
 def test_ldr_files_through_loadf_get_stbs_gamma(tmp_path):
     """The reference's ".jpg" environment is read with stbi_loadf (Renderer.cpp:262-266): 8-bit decode, then
     pow(byte / 255, 2.2) per colour channel. pt_image_load_hdr gives the same floats, bit for bit."""
