@@ -678,24 +678,31 @@ bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<flo
         for (size_t i = 0; i < px.size(); i++) rgba[i] = px[i] / 255.0f;
         return true;
     }
-    if (b[0] == 'P' && (b[1] == '6' || b[1] == '3')) {
+    if (b[0] == 'P' && (b[1] == '6' || b[1] == '5' || b[1] == '3')) {
+        // binary .ppm / .pgm as stb_image reads them: bytes are taken as they are (no rescaling by the maximum value, which must
+        // be <= 255), grey replicated to RGB. ASCII "P3" is an extension of this reader (stb refuses it); its values are scaled.
         size_t pos = 2; int vals[3], got = 0;
         while (got < 3 && pos < b.size()) {
-            while (pos < b.size() && (b[pos] == ' ' || b[pos] == '\n' || b[pos] == '\r' || b[pos] == '\t')) pos++;
-            if (pos < b.size() && b[pos] == '#') { while (pos < b.size() && b[pos] != '\n') pos++; continue; }
+            while (pos < b.size() && (b[pos] == ' ' || b[pos] == '\n' || b[pos] == '\r' || b[pos] == '\t' || b[pos] == '\v' || b[pos] == '\f')) pos++;
+            if (pos < b.size() && b[pos] == '#') { while (pos < b.size() && b[pos] != '\n' && b[pos] != '\r') pos++; continue; }
             int v = 0; bool any = false;
             while (pos < b.size() && b[pos] >= '0' && b[pos] <= '9') { v = v * 10 + (b[pos] - '0'); pos++; any = true; }
             if (!any) return false;
             vals[got++] = v;
         }
         w = vals[0]; h = vals[1];
-        if (got < 3 || w <= 0 || h <= 0 || vals[2] <= 0 || vals[2] > 255) return false;
+        if (got < 3 || w <= 0 || h <= 0 || vals[2] > 255 || (double)w * h > 1.0e9) return false;
         rgba.assign((size_t)w * h * 4, 1.0f);
-        if (b[1] == '6') {
-            pos++;
-            if (b.size() < pos + (size_t)w * h * 3) return false;
-            for (size_t i = 0; i < (size_t)w * h; i++) put(i, b[pos + 3 * i] * 255 / vals[2], b[pos + 3 * i + 1] * 255 / vals[2], b[pos + 3 * i + 2] * 255 / vals[2], 255);
+        if (b[1] != '3') {
+            const size_t nc = b[1] == '6' ? 3 : 1;
+            pos++;                                                       // the one whitespace byte after the maximum value
+            if (b.size() < pos + (size_t)w * h * nc) return false;
+            for (size_t i = 0; i < (size_t)w * h; i++) {
+                const unsigned char* q = b.data() + pos + nc * i;
+                if (nc == 3) put(i, q[0], q[1], q[2], 255); else put(i, q[0], q[0], q[0], 255);
+            }
         } else {
+            if (vals[2] <= 0) return false;
             for (size_t i = 0; i < (size_t)w * h; i++) {
                 int c[3];
                 for (int k = 0; k < 3; k++) {

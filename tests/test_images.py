@@ -360,7 +360,11 @@ def test_tga_and_bmp_readers_match_stb(tmp_path):
         pass
     for name, data in ldr_cases.handmade_cases(rgb).items():
         p = tmp_path / name; p.write_bytes(data); files[name] = str(p)
-    assert len(files) >= 11
+    # binary .ppm / .pgm: stb copies the bytes (no rescaling by the maximum value), grey goes to all three channels
+    files["plain.ppm"] = str(tmp_path / "plain.ppm"); (tmp_path / "plain.ppm").write_bytes(b"P6\n# comment\n37 23\n255\n" + rgb.tobytes())
+    files["max100.ppm"] = str(tmp_path / "max100.ppm"); (tmp_path / "max100.ppm").write_bytes(b"P6 37 23 100\n" + (rgb // 3).tobytes())
+    files["grey.pgm"] = str(tmp_path / "grey.pgm"); (tmp_path / "grey.pgm").write_bytes(b"P5\n37\t23\n255\n" + rgb[..., 1].tobytes())
+    assert len(files) >= 14
     for name, p in files.items():
         want = oracle.ref_stbi_load(p)
         assert want is not None, name
