@@ -527,7 +527,8 @@ def run_primary(args, name, wl):
     for _ in range(3):
         _, _, st = build_bvh_host(scene.tris)
         builds.append(st["build_ms"])
-    r = Renderer().Initialize(W, H, scene, max_depth=1, device=local, seed=0xB200 + rank, bvh="build", bvh_layout=LAYOUTS[args.bvh])
+    r = Renderer().Initialize(W, H, scene, max_depth=1, device=local, seed=0xB200 + rank,
+                              bvh={"device": "device", "ploc": "ploc"}.get(args.builder, "build"), bvh_layout=LAYOUTS[args.bvh])
     cam = make_camera(scene, W, H)
     r.lib.pt_set_camera(r.ctx, cam.plane)
     n = W * H
@@ -536,11 +537,12 @@ def run_primary(args, name, wl):
     if args.bvh == "reference":
         import ctypes as C
         from gpupathtracer_b200.api import pt_bvh_stats
-        for key, which in (("device_lbvh", "device"), ("device_ploc", "ploc")):
+        for key, which in (("host_sbvh", "build"), ("device_lbvh", "device"), ("device_ploc", "ploc")):
             s2 = Scene(scene.data)
             r2 = Renderer().Initialize(W, H, s2, max_depth=1, device=local, seed=1, bvh=which)
             dev_builds = [float(r2.bvh_stats.build_ms)]
-            for _ in range(4):
+            tot = float(r2.bvh_stats.total_ms)
+            for _ in range(4 if which != "build" else 0):
                 st = pt_bvh_stats()
                 if which == "ploc":
                     r2.lib.pt_build_bvh_device_ploc(r2.ctx, 16, C.byref(st))
@@ -556,7 +558,13 @@ def run_primary(args, name, wl):
             ms2 = []
             for _ in range(8):
                 r2.TraceClosestDevice(d2.data_ptr(), n, h2.data_ptr()); ms2.append(r2.LastDeviceMs())
-            dev[key + "_primary_mrays_s"] = n / min(ms2) / 1e3
+            dev[key + "_primary_mrays_s_warm_l2"] = n / min(ms2) / 1e3     # best of 8 back-to-back launches: the tree stays in L2
+            fl = torch.empty(256 << 20, dtype=torch.uint8, device="cuda"); ms3 = []
+            for _ in range(8):
+                fl.zero_(); torch.cuda.synchronize()
+                r2.TraceClosestDevice(d2.data_ptr(), n, h2.data_ptr()); ms3.append(r2.LastDeviceMs())
+            dev[key + "_primary_mrays_s_flushed_l2"] = n * len(ms3) / sum(ms3) / 1e3    # as the timed region does
+            del fl
             r2.CleanUp()
     pr = r.RaygenProbe(0, n)
     rays = np.zeros((n, 8), np.float32)
@@ -593,7 +601,10 @@ def run_primary(args, name, wl):
             "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "width": W, "height": H,
-                       "bvh": "own SBVH builder (host, all cores), reference layout", "l2": "256 MB flush between timed launches"},
+                       "bvh": {"device": "device LBVH builder", "ploc": "device PLOC builder (pt_build_bvh_device_ploc, radius 16)"}.get(
+                           args.builder, "own SBVH builder (host, all cores)") + f", {args.bvh} layout",
+                       "bvh_build_kernels_ms": float(r.bvh_stats.build_ms) if args.builder in ("device", "ploc") else None,
+                       "l2": "256 MB flush between timed launches"},
             "bvh_build_ms": {**dev, "ours_host_all_cores_best_of_3": min(builds), "nodes": int(r.bvh_stats.n_nodes), "refs": int(r.bvh_stats.n_refs),
                              "sah_cost": float(r.bvh_stats.sah_cost)},
             "hit_fraction": float((hits[:, 3].view(np.int32) >= 0).mean()),
