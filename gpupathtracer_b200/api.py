@@ -124,6 +124,7 @@ SYMBOLS = [
     ("pt_trace_closest_device", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_trace_any_device", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_raygen_probe", C.c_int, [_P, C.c_int64, C.c_int64, _P]),
+    ("pt_trace_primary_async", C.c_int, [_P, _P]),
     ("pt_get_counters", C.c_int, [_P, C.POINTER(pt_counters)]),
     ("pt_last_device_ms", C.c_float, [_P]),
     ("pt_set_stage_timing", C.c_int, [_P, C.c_int]),
@@ -539,6 +540,17 @@ class Renderer:
 
     def TraceAnyHost(self, h_rays, n, h_flags):
         _check(self.lib.pt_trace_any(self.ctx, C.c_void_p(h_rays), n, C.c_void_p(h_flags)))
+
+    def TracePrimaryAsync(self, host_ptr):
+        """pt_trace_primary_async into (preferably pinned) host memory of width * height * 16 bytes; complete after Synchronize()."""
+        _check(self.lib.pt_trace_primary_async(self.ctx, C.c_void_p(host_ptr)))
+
+    def TracePrimary(self):
+        """One primary ray per pixel as RenderFrame's first bounce traces it -> (height * width, 4) hit records in pixel order."""
+        out = np.zeros((self.width * self.height, 4), dtype=np.float32)
+        _check(self.lib.pt_trace_primary_async(self.ctx, _ptr(out)))
+        _check(self.lib.pt_synchronize(self.ctx))
+        return out
 
     def RaygenProbe(self, first, n):
         out = np.zeros((n, 12), dtype=np.float32)

@@ -66,6 +66,9 @@ struct pt_context {
     cudaStream_t in_stream = nullptr;
     cudaEvent_t ev_h_in[2] = {nullptr, nullptr}, ev_h_done[2] = {nullptr, nullptr}, ev_h_out[2] = {nullptr, nullptr};
     DevBuf<unsigned char> d_present[2];
+    DevBuf<float4> d_primary[2];
+    cudaEvent_t ev_primary = nullptr, ev_primary_copied[2] = {nullptr, nullptr};
+    int primary_turn = 0;
     cudaEvent_t ev_resolved = nullptr, ev_copied[2] = {nullptr, nullptr};
     int present_turn = 0;
     LaunchDims dims{};
@@ -212,6 +215,8 @@ int pt_create(const pt_config* cfg, pt_context** out) {
         CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&c->ev_resolved, cudaEventDisableTiming));
         for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&c->ev_primary, cudaEventDisableTiming));
+        for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&c->ev_primary_copied[k], cudaEventDisableTiming));
     }
     CK(c->d_rng.alloc(npx));
     CK(c->d_accum_own.alloc(npx));
@@ -264,6 +269,8 @@ void pt_destroy(pt_context* c) {
         if (c->ev_h_out[k]) cudaEventDestroy(c->ev_h_out[k]);
     }
     if (c->ev_resolved) cudaEventDestroy(c->ev_resolved);
+    if (c->ev_primary) cudaEventDestroy(c->ev_primary);
+    for (int k = 0; k < 2; k++) { if (c->ev_primary_copied[k]) cudaEventDestroy(c->ev_primary_copied[k]); c->d_primary[k].release(); }
     for (int k = 0; k < 2; k++) { if (c->ev_copied[k]) cudaEventDestroy(c->ev_copied[k]); c->d_present[k].release(); }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     cudaStreamDestroy(c->stream);
@@ -997,6 +1004,31 @@ int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) 
     CK(cudaStreamWaitEvent(c->copy_stream, c->ev_resolved, 0));
     CK(cudaMemcpyAsync(host_rgb_u8, c->d_present[k].p, npx * 3, cudaMemcpyDeviceToHost, c->copy_stream));
     CK(cudaEventRecord(c->ev_copied[k], c->copy_stream));
+    return PT_OK;
+}
+
+// One primary ray per pixel exactly as the first bounce of RenderFrame traces it (InitRay Iterative.comp:174-210 with the
+// pixel's RNG state, IfIfClosestHit), hit records in pixel order; the copy runs on the copy stream, double-buffered
+int pt_trace_primary_async(pt_context* c, float* host_hits) {
+    if (!c || !host_hits) return fail(PT_ERR_INVALID, "pt_trace_primary_async: bad argument");
+    CK(cudaSetDevice(c->cfg.device));
+    int rc = check_scene(c, "pt_trace_primary_async", false);
+    if (rc != PT_OK) return rc;
+    if (!c->have_cam || !c->have_rng) return fail(PT_ERR_INVALID, "pt_trace_primary_async: camera and RNG table must be set");
+    const size_t npx = (size_t)c->cfg.width * c->cfg.height;
+    const int k = c->primary_turn; c->primary_turn ^= 1;
+    CK(c->d_primary[k].alloc(npx));
+    CK(cudaEventRecord(c->ev0, c->stream));
+    CK(cudaStreamWaitEvent(c->stream, c->ev_primary_copied[k], 0));
+    FrameParams p = frame_params(c);
+    c->counters.kernel_launches += launch_primary(p, c->dims, c->d_primary[k].p, c->stream);
+    c->counters.closest_rays += (uint64_t)npx;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev1, c->stream));
+    CK(cudaEventRecord(c->ev_primary, c->stream));
+    CK(cudaStreamWaitEvent(c->copy_stream, c->ev_primary, 0));
+    CK(cudaMemcpyAsync(host_hits, c->d_primary[k].p, npx * sizeof(float4), cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaEventRecord(c->ev_primary_copied[k], c->copy_stream));
     return PT_OK;
 }
 

@@ -501,6 +501,21 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
     return launches;
 }
 
+// ---- primary rays only (pt_trace_primary_async): the first two kernels of a frame -- InitRay for every pixel, closest hit --
+// and the hit records put in pixel order (the queue is in 8x8 Morton tile order, Iterative.comp:163-172)
+__global__ void k_primary_gather(FrameParams p, float4* by_pixel) {
+    const int n = p.slice_count;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        by_pixel[__float_as_int(p.queue[0].q2[i].w)] = p.hits[i];
+}
+int launch_primary(const FrameParams& p, const LaunchDims& dims, float4* by_pixel, cudaStream_t st) {
+    cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), st);
+    k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p);
+    launch_extend(p, 0, 0, dims, dims.extend_blocks, st);
+    k_primary_gather<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, by_pixel);
+    return 3;
+}
+
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st) {
     int blocks = (int)((n + 255) / 256);
     if (blocks > 0) k_raygen_probe<<<blocks, 256, 0, st>>>(p, first, n, out3);

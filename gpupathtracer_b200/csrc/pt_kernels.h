@@ -58,6 +58,7 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
 int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
                       cudaStream_t st, float* kernel_ms, int ploc_radius = 0);
 
+int launch_primary(const FrameParams& p, const LaunchDims& dims, float4* by_pixel, cudaStream_t st);
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);
 void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st);
 void query_launch_dims(int device, int wide, LaunchDims* out);

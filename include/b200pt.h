@@ -271,6 +271,14 @@ int pt_trace_any(pt_context* ctx, const float* rays, int64_t n, uint8_t* flags);
 int pt_trace_closest_device(pt_context* ctx, const void* d_rays, int64_t n, void* d_hits);
 int pt_trace_any_device(pt_context* ctx, const void* d_rays, int64_t n, void* d_flags);
 
+/* One primary ray per pixel exactly as RenderFrame's first bounce traces it -- InitRay (Iterative.comp:174-210: pixel jitter +
+ * thin-lens sample from the pixel's RNG state, which is NOT advanced) and IfIfClosestHit -- with the hit records
+ * {t, u, v, triangle id (int bits, -1 = miss)} delivered in PIXEL order (y * width + x) to host memory. Asynchronous like
+ * pt_present_async: the 16-byte-per-pixel copy runs on the copy stream from one of two device buffers, so back-to-back
+ * calls overlap tracing and transfer; the data is complete after pt_synchronize. Camera and RNG table must be set.
+ * BASELINE.json configs[0] ("1 spp primary closest-hit") without shipping 32 bytes per ray to the device first. */
+int pt_trace_primary_async(pt_context* ctx, float* host_hits);
+
 /* ---- per-stage probes (parity of raygen on its own; rng table is advanced like the shader does) ---- */
 /* out: n x 12 floats {pixel.x, pixel.y (int bits), o.xyz, d.xyz, 0,0,0,0} for ray indices [first, first+n). */
 int pt_raygen_probe(pt_context* ctx, int64_t first, int64_t n, float* out);

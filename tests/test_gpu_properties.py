@@ -134,6 +134,28 @@ def test_device_built_bvh(name, builder):
     assert np.array_equal(got[same, :3].view(np.uint32), other[same, :3].view(np.uint32))
 
 
+def test_trace_primary_is_the_first_bounce_in_pixel_order():
+    """pt_trace_primary_async = InitRay for every pixel + closest hit, hit records by pixel: equal, bit for bit, to tracing the
+    rays pt_raygen_probe reports for the same RNG table (the probe advances the table, the primary trace does not), and
+    leaves the table where it was (calling it twice gives the same hits)."""
+    s = get_scene("cornell")
+    w, h = 96, 64
+    cam = make_camera(s.data, w, h, aperture=0.3)                                # lens radius > 0: the lens sample is part of the ray
+    r = Renderer().Initialize(w, h, s, max_depth=5, rng_state=make_rng_table(w * h, 11))
+    r.lib.pt_set_camera(r.ctx, cam.plane)
+    first = r.TracePrimary()
+    again = r.TracePrimary()
+    assert np.array_equal(first.view(np.uint32), again.view(np.uint32))
+    probe = r.RaygenProbe(0, w * h)
+    px, py = probe[:, 0].copy().view(np.int32), probe[:, 1].copy().view(np.int32)
+    rays = np.zeros((w * h, 8), np.float32)
+    rays[:, 0:3] = probe[:, 2:5]; rays[:, 4:7] = probe[:, 5:8]; rays[:, 7] = 1e20
+    want = r.TraceClosest(rays)
+    r.CleanUp()
+    assert np.array_equal(first[py * w + px].view(np.uint32), want.view(np.uint32))
+    assert (first[:, 3].view(np.int32) >= 0).mean() > 0.5                        # it is looking at the box
+
+
 def test_host_batches_larger_than_one_pipeline_chunk():
     """pt_trace_closest / pt_trace_any stream host batches through the device in 2 M-ray chunks (H2D, kernel, D2H
     overlapped, double-buffered staging): 2.5 chunks with a ragged tail must give the oracle's bits."""
