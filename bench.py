@@ -408,6 +408,7 @@ def run_pathtrace(args, name, wl):
             achieved = closest_stage * b_ray / ext_s / 1e9 if ext_s > 0 else None
             line["roofline"] = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                 "frac": achieved / peak if achieved else None, "traffic": traffic_for(name, "k_extend"),
+                                "ncu": traffic_for(name, "k_extend ncu"),
                                 "algorithmic_bytes_per_launch": closest_stage * b_ray / launches, "peak_source": which,
                                 "bytes_per_ray": b_ray, "pairs_per_ray": pairs_c, "tris_per_ray": tris_c,
                                 "launches": launches, "avg_launch_ms": stage["extend"] / launches,
@@ -507,6 +508,7 @@ def run_micro(args, name, wl):
             line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                 "frac": achieved / peak,
                                 "traffic": traffic_for(name, "k_trace_batch<false>" + {"wide": " wide-8", "wide4": " wide-4"}.get(args.bvh, "")),
+                                "ncu": traffic_for(name, "k_trace_batch<false> ncu") if args.bvh == "reference" else None,
                                 "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
                                 "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": steps, "avg_launch_ms": ms_c / steps,
                                 "note": "avg_launch_ms spans the ray binning (4 small kernels, ~0.35 ms, reference layout only) and "
@@ -649,6 +651,7 @@ def run_primary(args, name, wl):
             achieved = n * b_ray / (ms_total / args.steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                 "frac": achieved / peak, "traffic": traffic_for(name, "k_trace_batch<false>"),
+                                "ncu": traffic_for(name, "k_trace_batch<false> ncu"),
                                 "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
                                 "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": args.steps, "avg_launch_ms": ms_total / args.steps,
                                 "note": "coherent primary rays on a 10 MB tree: L1/L2-resident, issue-slot bound (DESIGN.md 4)"}
