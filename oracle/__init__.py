@@ -108,6 +108,48 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
+GLSL_SO = os.path.join(_HERE, "_ref", "libref_glsl.so")
+_glsl = None
+
+
+def have_glsl():
+    return os.path.exists(GLSL_SO)
+
+
+class RefGlsl:
+    """The reference's own traversal SHADER SOURCE (IfIfClosestHit / IfIfAnyHit and what they call, common/BVH.glsl +
+    common/Geometry.glsl) compiled as C++ in place by oracle/Makefile (oracle/_ref/libref_glsl.so, harness oracle/ref_glsl.cpp).
+    One binding at a time: the samplers are globals, as uniforms are."""
+
+    def __init__(self, nodes, refs, tris_pre):
+        global _glsl
+        if _glsl is None:
+            _glsl = C.CDLL(GLSL_SO)
+            _glsl.ref_glsl_bind.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+            _glsl.ref_glsl_trace_closest.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+            _glsl.ref_glsl_trace_any.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+        self.nodes = np.ascontiguousarray(nodes, dtype=np.float32)
+        self.refs = np.ascontiguousarray(refs, dtype=np.int32)
+        self.tris = np.ascontiguousarray(tris_pre, dtype=np.float32)
+
+    def _bind(self):
+        _glsl.ref_glsl_bind(_p(self.nodes), _p(self.refs), _p(self.tris), self.tris.shape[0])
+
+    def trace_closest(self, rays, n_threads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        hits = np.zeros((rays.shape[0], 4), dtype=np.float32)
+        self._bind()
+        _glsl.ref_glsl_trace_closest(_p(rays), rays.shape[0], _p(hits), n_threads)
+        return hits
+
+    def trace_any(self, rays, n_threads=0):
+        rays = np.ascontiguousarray(rays, dtype=np.float32)
+        flags = np.zeros(rays.shape[0], dtype=np.uint8)
+        self._bind()
+        _glsl.ref_glsl_trace_any(_p(rays), rays.shape[0], _p(flags), n_threads)
+        return flags
+
+
 def ref_build_sbvh(tris_abs):
     """BoundingVolumeHierarchy::BuildBinnedSpatial (BVH.cpp:2197-2293) on absolute-position triangles.
     Returns (nodes (n,8) float32 in NewLayout, refs int32). stdout of the reference is silenced."""

@@ -15,6 +15,13 @@
  *   - image plane           vs math/Camera.cpp:6-22   (bit-exact)
  *   - Uncharted-2 tonemap   vs Renderer.cpp:980-994   (bit-exact)
  *   - the BVH it traverses  IS the reference builder's output (BVH.cpp:2197-2293)
+ *   - closest_hit / any_hit (IfIfClosestHit, IfIfAnyHit, IntersectNodeFast, IntersectLeaf, IntersectTriangleMT)
+ *                           vs the reference's own SHADER SOURCE for them, extracted from common/BVH.glsl +
+ *                           common/Geometry.glsl and compiled as C++ with glm (oracle/ref_glsl.cpp ->
+ *                           oracle/_ref/libref_glsl.so): same triangle index, (t,u,v) bits and flags, live and on
+ *                           the committed vectors tests/golden/trace_glsl_*.npz
+ * The traversal half is therefore pinned to the reference's code; the shading half (Iterative.comp's main loop,
+ * materials, BSDF, light sampling) remains "parity unpinned".
  *
  * Float mode (stated, because GLSL does not pin one): IEEE-754 binary32, every operation
  * separately rounded (built with -ffp-contract=off -fno-fast-math), division and sqrt

@@ -1,0 +1,99 @@
+// oracle/ref_glsl.cpp -- TEST INFRASTRUCTURE ONLY (never linked into the product).
+//
+// Harness around the reference's OWN shader source for the traversal path, compiled as C++ where it lies under
+// /root/reference: oracle/Makefile extracts, at build time and into the git-ignored oracle/_ref/, these line ranges
+//   src/shaders/common/Util.glsl      4-5      fbu / fbs
+//   src/shaders/common/Geometry.glsl  8-11     Ray;  145-161 PackedCompactTriangle + ReadPackedCompactTriangle;
+//                                     193-226  HitInfo + IntersectTriangleMT;  313 #define IntersectTriangle
+//   src/shaders/common/BVH.glsl       300-302  BVHNode;  356-364 GetNode;  379-391 IntersectNodeFast;  420-437 IntersectLeaf;
+//                                     622-627  the ifif macros;  634-767 IfIfClosestHit;  769-854 IfIfAnyHit
+// and applies four syntactic rewrites (parameter qualifiers, swizzle spelling, ^^); see the Makefile. Nothing of the
+// reference is copied into the repository. This file supplies only what the GL runtime supplies to a shader: the buffer
+// textures (samplerBuffer + texelFetch over plain float arrays), glm as the vector library (the reference's own, extern/glm)
+// and entry points that loop over a ray batch. It exists to PIN oracle/pt_oracle.cpp's hand restatement of the same
+// functions: tests/test_oracle_pins.py requires both to agree bit for bit.
+//
+// Two things the shader leaves open and this harness fixes, both outside the arithmetic:
+//   * BVH_STACK_SIZE is 27 in the shader (BVH.glsl:489) and deeper trees overrun its array; here 96, like the product;
+//   * the shader never stores the triangle INDEX of a hit (it copies the 80-byte triangle into HitInfo.intersected). The
+//     harness feeds it a vertex buffer whose padding word (float 19 of each triangle, "uint padding", Geometry.glsl:142) holds
+//     the triangle's index, so the accepted triangle names itself. No traversal arithmetic reads that word.
+#define GLM_FORCE_SWIZZLE
+#include <glm/glm.hpp>
+#include <atomic>
+#include <cstdint>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+namespace refglsl {
+using namespace glm;
+
+// what `uniform samplerBuffer` + texelFetch are to the shader: RGBA32F texels (nodes, triangles) or R32F (reference list)
+struct samplerBuffer { const float* p = nullptr; int comps = 4; };
+inline vec4 texelFetch(const samplerBuffer& s, int i) {
+    if (s.comps == 4) return vec4(s.p[4 * (size_t)i], s.p[4 * (size_t)i + 1], s.p[4 * (size_t)i + 2], s.p[4 * (size_t)i + 3]);
+    return vec4(s.p[i], 0.0f, 0.0f, 1.0f);                       // GL fills missing components with (0, 0, 1)
+}
+static samplerBuffer vertexTex, nodesTex, referenceTex;           // Geometry.glsl:6, BVH.glsl:353-354
+
+#define BVH_STACK_SIZE 96
+#include "ref_glsl_traversal.inc"
+
+}  // namespace refglsl
+
+namespace {
+template <class F>
+void parallel_for(int64_t n, int n_threads, F f) {
+    int nt = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
+    if (nt < 1 || n < 4096) nt = 1;
+    std::atomic<int64_t> next(0);
+    auto work = [&]() { for (;;) { int64_t b = next.fetch_add(2048); if (b >= n) break; f(b, std::min(n, b + 2048)); } };
+    if (nt == 1) { work(); return; }
+    std::vector<std::thread> th;
+    for (int i = 0; i < nt; i++) th.emplace_back(work);
+    for (auto& t : th) t.join();
+}
+std::vector<float> g_stamped;                                      // triangles with their index in the padding word
+}  // namespace
+
+extern "C" {
+
+// nodes: n_nodes x 8 floats (NodeSerialized, NewLayout), refs: int32 reference list, tris: n_tris x 20 floats (pre-subtracted
+// edges, as uploaded by Scene.cpp:334-347). Not re-entrant (the samplers are globals, as uniforms are).
+void ref_glsl_bind(const float* nodes, const int32_t* refs, const float* tris, int64_t n_tris) {
+    g_stamped.assign(tris, tris + 20 * (size_t)n_tris);
+    for (int64_t i = 0; i < n_tris; i++) { int32_t id = (int32_t)i; std::memcpy(&g_stamped[20 * (size_t)i + 19], &id, 4); }
+    refglsl::nodesTex.p = nodes; refglsl::nodesTex.comps = 4;
+    refglsl::referenceTex.p = reinterpret_cast<const float*>(refs); refglsl::referenceTex.comps = 1;
+    refglsl::vertexTex.p = g_stamped.data(); refglsl::vertexTex.comps = 4;
+}
+
+// rays: n x 8 floats {o.xyz, -, d.xyz, tmax}; hits: n x 4 floats {t, u, v, triangle index as int bits (-1 = miss)}.
+// The caller of IfIfClosestHit in the shader starts with intersection.di.x = the ray's maximum distance (Iterative.comp:232).
+void ref_glsl_trace_closest(const float* rays, int64_t n, float* hits, int n_threads) {
+    parallel_for(n, n_threads, [&](int64_t b, int64_t e) {
+        for (int64_t i = b; i < e; i++) {
+            const float* r = rays + 8 * i;
+            refglsl::Ray ray; ray.origin = glm::vec3(r[0], r[1], r[2]); ray.direction = glm::vec3(r[4], r[5], r[6]);
+            refglsl::HitInfo h; h.di = glm::vec4(r[7], 0.0f, 0.0f, 0.0f);
+            bool any = refglsl::IfIfClosestHit(ray, h);
+            int32_t id = -1;
+            if (any) std::memcpy(&id, &h.intersected.data[4].w, 4);
+            hits[4 * i] = h.di.x; hits[4 * i + 1] = h.di.y; hits[4 * i + 2] = h.di.z; std::memcpy(&hits[4 * i + 3], &id, 4);
+        }
+    });
+}
+
+void ref_glsl_trace_any(const float* rays, int64_t n, uint8_t* flags, int n_threads) {
+    parallel_for(n, n_threads, [&](int64_t b, int64_t e) {
+        for (int64_t i = b; i < e; i++) {
+            const float* r = rays + 8 * i;
+            refglsl::Ray ray; ray.origin = glm::vec3(r[0], r[1], r[2]); ray.direction = glm::vec3(r[4], r[5], r[6]);
+            refglsl::HitInfo h; h.di = glm::vec4(r[7], 0.0f, 0.0f, 0.0f);
+            flags[i] = refglsl::IfIfAnyHit(ray, h) ? 1 : 0;
+        }
+    });
+}
+
+}  // extern "C"

@@ -87,6 +87,10 @@ def scene_fixtures():
         rays_any = mixed_rays(s, 4096, seed=23, any_hit=True)
         flags, _ = o.trace_any(rays_any)
         np.savez_compressed(os.path.join(HERE, f"trace_{name}.npz"), rays=rays, hits=hits, rays_any=rays_any, flags=flags)
+        # the same batches through the reference's own traversal SHADER SOURCE compiled as C++ (oracle/ref_glsl.cpp):
+        # these are the reference's answers, recorded so that the pin holds where /root/reference is absent
+        g = oracle.RefGlsl(nodes, refs, s.tris)
+        np.savez_compressed(os.path.join(HERE, f"trace_glsl_{name}.npz"), hits=g.trace_closest(rays, 1), flags=g.trace_any(rays_any, 1))
         w = h = 32
         cam = make_camera(s.data, w, h).as_array()
         rng = make_rng_table(w * h, 77); rng0 = rng.copy()

@@ -39,6 +39,26 @@ def test_any_hit_bit_exact(name, n):
     assert 0.05 < want.mean() < 0.95
 
 
+@pytest.mark.skipif(not oracle.have_glsl(), reason="oracle/_ref/libref_glsl.so not built (it travels with the snapshot when it was)")
+@pytest.mark.parametrize("name,n", [("cornell", 200000), ("soup", 200000), ("bunny", 300000), ("atrium_small", 200000)])
+def test_cuda_traversal_equals_reference_shader_source(name, n):
+    """The CUDA kernels against the reference's OWN traversal shader source compiled as C++ (oracle/ref_glsl.cpp: IfIfClosestHit /
+    IfIfAnyHit and their callees extracted from common/BVH.glsl + common/Geometry.glsl), no restatement in between: same
+    triangle index, same (t, u, v) bits, same occlusion flag for every ray."""
+    s = get_scene(name)
+    g = oracle.RefGlsl(s.nodes, s.refs, s.tris)
+    rays = mixed_rays(s, n, seed=41)
+    anyr = mixed_rays(s, n, seed=42, any_hit=True)
+    want = g.trace_closest(rays)
+    wflag = g.trace_any(anyr)
+    r = _renderer(s)
+    got = r.TraceClosest(rays)
+    gflag = r.TraceAny(anyr)
+    r.CleanUp()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(gflag, wflag)
+
+
 def test_empty_and_ragged_batches():
     s = get_scene("cornell_small")
     r = _renderer(s)

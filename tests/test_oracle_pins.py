@@ -109,6 +109,48 @@ def test_oracle_regression_on_golden_tree(name):
     assert [c["closest_rays"], c["shadow_rays"]] == list(f["counters"])
 
 
+@pytest.mark.parametrize("name", ["cornell_small", "soup_small"])
+def test_oracle_traversal_equals_reference_shader_golden(name):
+    """tests/golden/trace_glsl_*.npz hold what the reference's OWN shader source -- IfIfClosestHit / IfIfAnyHit with GetNode,
+    IntersectNodeFast, IntersectLeaf, IntersectTriangleMT, extracted from common/BVH.glsl + common/Geometry.glsl and compiled
+    as C++ by oracle/Makefile -- answered for the committed ray batches on the reference builder's committed tree. The hand
+    restatement in oracle/pt_oracle.cpp must give the same bits: (t, u, v), the triangle index and every any-hit flag."""
+    s = Scene(SCENES[name]())
+    z = np.load(os.path.join(GOLDEN, f"tree_{name}.npz"))
+    s.set_bvh(z["nodes"], z["refs"])
+    t = np.load(os.path.join(GOLDEN, f"trace_{name}.npz"))
+    g = np.load(os.path.join(GOLDEN, f"trace_glsl_{name}.npz"))
+    o = oracle.Oracle(s)
+    hits, _ = o.trace_closest(t["rays"])
+    assert np.array_equal(hits.view(np.uint32), g["hits"].view(np.uint32))
+    flags, _ = o.trace_any(t["rays_any"])
+    assert np.array_equal(flags, g["flags"])
+    assert (g["hits"][:, 3].view(np.int32) >= 0).mean() > 0.3 and 0.05 < g["flags"].mean() < 0.95       # the batches exercise both outcomes
+
+
+needs_glsl = pytest.mark.skipif(not oracle.have_glsl(), reason="oracle/_ref/libref_glsl.so not built (no /root/reference)")
+
+
+@needs_glsl
+@pytest.mark.parametrize("name", ["cornell", "soup", "bunny", "atrium_small"])
+def test_oracle_traversal_equals_live_reference_shader(name):
+    """The same comparison live and larger: 100 000 closest-hit + 100 000 any-hit rays per scene (random, camera-like and
+    surface-to-surface rays, finite and infinite tmax) through the reference's shader source compiled as C++ and through the
+    oracle, on the tree the reference's own builder makes for the scene."""
+    from common import get_scene, mixed_rays
+    s = get_scene(name)
+    g = oracle.RefGlsl(s.nodes, s.refs, s.tris)
+    o = oracle.Oracle(s)
+    rays = mixed_rays(s, 100000, seed=5)
+    want = g.trace_closest(rays)
+    got, _ = o.trace_closest(rays)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    anyr = mixed_rays(s, 100000, seed=6, any_hit=True)
+    wflag = g.trace_any(anyr)
+    gflag, _ = o.trace_any(anyr)
+    assert np.array_equal(gflag, wflag)
+
+
 # ----------------------------------------------------------------------------------- live reference (this container)
 needs_ref = pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/libref_shim.so not built (no /root/reference)")
 
