@@ -116,6 +116,54 @@ def have_glsl():
     return os.path.exists(GLSL_SO)
 
 
+def shade_probe_inputs(n, seed):
+    """Random cases for or_shade_probe / ref_glsl_shade_probe: n x 16 floats {albedo.rgb, props.g (sqrt-roughness), props.b
+    (metallic), normal, outgoing, light direction} + n x 4 RNG words. Views above and (10 %) below the surface, light directions
+    over the whole sphere, rough to near-mirror, dielectric to metal."""
+    g = np.random.default_rng(seed)
+    def unit(m):
+        v = g.normal(size=(m, 3)); return (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+    a = np.zeros((n, 16), np.float32)
+    a[:, 0:3] = g.uniform(0.02, 1.0, size=(n, 3))
+    a[:, 3] = g.uniform(0.02, 1.0, size=n) ** 1.5
+    a[:, 4] = np.where(g.uniform(size=n) < 0.3, 1.0, np.where(g.uniform(size=n) < 0.5, 0.0, g.uniform(size=n)))
+    nrm = unit(n); nrm[: n // 8] = (0.0, 1.0, 0.0)                       # the ConstructTBN branch for |n.y| > 0.99
+    o = unit(n); flip = (np.sum(o * nrm, axis=1) < 0) & (g.uniform(size=n) < 0.9); o[flip] *= -1
+    a[:, 5:8], a[:, 8:11], a[:, 11:14] = nrm, o, unit(n)
+    rng = g.integers(129, 2 ** 32, size=(n, 4), dtype=np.uint64).astype(np.uint32)
+    return a, rng
+
+
+def shade_probe(inputs, rng, model=0):
+    """or_shade_probe: the oracle's shading arithmetic on explicit inputs -> (n x 20 floats, RNG words after the sample)."""
+    l = lib()
+    l.or_shade_probe.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+    a = np.ascontiguousarray(inputs, dtype=np.float32); r = np.ascontiguousarray(rng, dtype=np.uint32).copy()
+    out = np.zeros((a.shape[0], 20), np.float32)
+    l.or_shade_probe(_p(a), _p(r), a.shape[0], model, _p(out))
+    return out, r
+
+
+def ref_glsl_shade_probe(inputs, rng, model=0):
+    """The same probe through the reference's own shader functions compiled as C++ (oracle/ref_glsl.cpp); model 1 = the copy
+    whose three model macros (Microfacet.glsl:88-90) point at the file's Beckmann functions."""
+    g = C.CDLL(GLSL_SO)
+    fn = g.ref_glsl_shade_probe_beckmann if model == 1 else g.ref_glsl_shade_probe
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    a = np.ascontiguousarray(inputs, dtype=np.float32); r = np.ascontiguousarray(rng, dtype=np.uint32).copy()
+    out = np.zeros((a.shape[0], 20), np.float32)
+    fn(_p(a), _p(r), a.shape[0], _p(out))
+    return out, r
+
+
+def ref_glsl_hybrid_taus(state4, n):
+    g = C.CDLL(GLSL_SO)
+    g.ref_glsl_hybrid_taus.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    st = np.ascontiguousarray(state4, dtype=np.uint32).copy(); out = np.zeros(n, np.float32)
+    g.ref_glsl_hybrid_taus(_p(st), n, _p(out))
+    return out, st
+
+
 class RefGlsl:
     """The reference's own traversal SHADER SOURCE (IfIfClosestHit / IfIfAnyHit and what they call, common/BVH.glsl +
     common/Geometry.glsl) compiled as C++ in place by oracle/Makefile (oracle/_ref/libref_glsl.so, harness oracle/ref_glsl.cpp).

@@ -641,6 +641,38 @@ void trace_path(const OrScene& s, const OrCamera& cam, const OrConfig& cfg, int 
 // ================================================================= C entry points
 extern "C" {
 
+// Probe of the shading arithmetic on explicit inputs, in the order Iterative.comp:236-288 uses it (material from the two
+// texture reads, interaction, NEE evaluation towards `light_dir`, BSDF sample, throughput factor). in: 16 floats per case
+// {data0.rgb, data1.g, data1.b, normal.xyz, outgoing.xyz, light_dir.xyz, -, -} + 4 RNG words; out: 20 floats
+// {bsdf_light.rgb, pdf_light, ndi_light, sample_dir.xyz, pdfSample, pdfMIS, bsdf_sample.rgb, ndi_sample, mis, factor.rgb, pmf, -}
+// and the RNG words after the sample. model: 0 GGX (the shader's macros as shipped), 1 Beckmann.
+void or_shade_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) {
+    for (int64_t k = 0; k < n; k++) {
+        const float* a = in + 16 * k; float* o = out + 20 * k; uint32_t* rs = rng_io + 4 * k;
+        Material m{};
+        m.albedo = v3(a[0], a[1], a[2]);
+        m.roughness = gmax(a[3] * a[3], 1e-4f);
+        m.roughness2 = m.roughness * m.roughness;
+        m.metallic = a[4];
+        m.reflectance = mix(v3(0.04f), m.albedo, m.metallic);
+        V3 nrm = v3(a[5], a[6], a[7]), og = v3(a[8], a[9], a[10]), ld = v3(a[11], a[12], a[13]);
+        Interaction it = make_interaction(nrm, og);
+        Interaction li = it;
+        set_incoming(li, ld);
+        V3 fl = bsdf(model, m, li);
+        o[0] = fl.x; o[1] = fl.y; o[2] = fl.z; o[3] = pdf_direction(model, m, li); o[4] = li.ndi;
+        Rng rng; rng.x = rs[0]; rng.y = rs[1]; rng.z = rs[2]; rng.w = rs[3];
+        float p0, p1;
+        V3 d = importance_sample(model, m, it, rng, p0, p1);
+        V3 fs = bsdf(model, m, it);
+        float w = mis_weight(p0, p1);
+        V3 factor = fs * it.ndi * w / p0;                                // Iterative.comp:284
+        o[5] = d.x; o[6] = d.y; o[7] = d.z; o[8] = p0; o[9] = p1; o[10] = fs.x; o[11] = fs.y; o[12] = fs.z; o[13] = it.ndi; o[14] = w;
+        o[15] = factor.x; o[16] = factor.y; o[17] = factor.z; o[18] = diffuse_pmf(m, it); o[19] = 0.0f;
+        rs[0] = rng.x; rs[1] = rng.y; rs[2] = rng.z; rs[3] = rng.w;
+    }
+}
+
 void or_hybrid_taus(uint32_t state[4], int n, float* out) {
     Rng r{state[0], state[1], state[2], state[3]};
     for (int i = 0; i < n; i++) out[i] = r.next();

@@ -20,8 +20,13 @@
  *                           common/Geometry.glsl and compiled as C++ with glm (oracle/ref_glsl.cpp ->
  *                           oracle/_ref/libref_glsl.so): same triangle index, (t,u,v) bits and flags, live and on
  *                           the committed vectors tests/golden/trace_glsl_*.npz
- * The traversal half is therefore pinned to the reference's code; the shading half (Iterative.comp's main loop,
- * materials, BSDF, light sampling) remains "parity unpinned".
+ *   - the shading arithmetic (material assignments, SurfaceInteraction, all of Microfacet.glsl, ComputeBSDF, MISWeight,
+ *                           GenerateImportanceSample, HybridTaus) vs the same kind of compile of common/{Material,Microfacet,
+ *                           BSDF,MIS,Random}.glsl, through or_shade_probe / ref_glsl_shade_probe: same bits, GGX and
+ *                           Beckmann, live and on tests/golden/shade_glsl.npz (one NaN-in-max() exception)
+ * Traversal and shading arithmetic are therefore pinned to the reference's code; Iterative.comp's main loop (call order,
+ * emission + MIS on hit, light sampling, Russian roulette, InitRay), texture filtering and the environment lookup remain
+ * "parity unpinned".
  *
  * Float mode (stated, because GLSL does not pin one): IEEE-754 binary32, every operation
  * separately rounded (built with -ffp-contract=off -fno-fast-math), division and sqrt
@@ -93,6 +98,9 @@ typedef struct OrCounters {
 
 /* ---- scalar pieces ---- */
 void or_hybrid_taus(uint32_t state[4], int n, float* out);            /* Random.glsl:47-70 */
+/* shading arithmetic on explicit inputs (material, interaction, NEE evaluation, BSDF sample) in Iterative.comp:236-288's order;
+ * in: n x 16 floats, rng_io: n x 4 words (advanced), out: n x 20 floats -- layout in pt_oracle.cpp */
+void or_shade_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out);
 void or_image_plane(float aspect, float fov, float focus, float aperture, const float pos[3],
                     const float rot[3], OrCamera* cam);                /* Camera.cpp:4-22 */
 int or_slab_test(const float bmin[3], const float bmax[3], const float iorg[3], const float idir[3],

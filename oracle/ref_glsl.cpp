@@ -7,6 +7,8 @@
 //                                     193-226  HitInfo + IntersectTriangleMT;  313 #define IntersectTriangle
 //   src/shaders/common/BVH.glsl       300-302  BVHNode;  356-364 GetNode;  379-391 IntersectNodeFast;  420-437 IntersectLeaf;
 //                                     622-627  the ifif macros;  634-767 IfIfClosestHit;  769-854 IfIfAnyHit
+//   and, for the shading arithmetic, Constants.glsl 4; Util.glsl 6-11; Random.glsl 42-45, 47-75, 77-79, 155; MIS.glsl 6-8;
+//   Material.glsl 23-37, 46-51, 57-130; Microfacet.glsl 9-193; BSDF.glsl 8-21
 // and applies four syntactic rewrites (parameter qualifiers, swizzle spelling, ^^); see the Makefile. Nothing of the
 // reference is copied into the repository. This file supplies only what the GL runtime supplies to a shader: the buffer
 // textures (samplerBuffer + texelFetch over plain float arrays), glm as the vector library (the reference's own, extern/glm)
@@ -40,7 +42,34 @@ static samplerBuffer vertexTex, nodesTex, referenceTex;           // Geometry.gl
 #define BVH_STACK_SIZE 96
 #include "ref_glsl_traversal.inc"
 
+// ---- the shading arithmetic, same recipe (oracle/Makefile: ref_glsl_shading.inc): M_PI, nndot / avdot / AverageLuminance, the
+// HybridTaus generator with its `state` global, MISWeight, MaterialInstance / SurfaceInteraction and their constructors, all
+// of Microfacet.glsl (distributions, visibility, Fresnel, pmf, pdfs, GenerateImportanceSample) and ComputeBSDF
+#undef M_PI
+#include "ref_glsl_shading.inc"
+
+// ConstructMaterialInstance (Material.glsl:39-54) reads two bindless textures; the harness supplies the two texels and runs the
+// shader's own six assignments after them (Material.glsl:46-51, extracted like the rest)
+inline MaterialInstance material_from_texels(vec4 data0, vec4 data1) {
+    MaterialInstance material;
+    material.emission = vec3(0.0f); material.materialType = 1u; material.ior = 0.0f;
+#include "ref_glsl_material_body.inc"
+    return material;
+}
+
 }  // namespace refglsl
+
+// the same shading source with Microfacet.glsl's three model macros pointed at its Beckmann functions
+namespace refglsl_beckmann {
+using namespace glm;
+#include "ref_glsl_shading_beckmann.inc"
+inline MaterialInstance material_from_texels(vec4 data0, vec4 data1) {
+    MaterialInstance material;
+    material.emission = vec3(0.0f); material.materialType = 1u; material.ior = 0.0f;
+#include "ref_glsl_material_body.inc"
+    return material;
+}
+}  // namespace refglsl_beckmann
 
 namespace {
 template <class F>
@@ -94,6 +123,43 @@ void ref_glsl_trace_any(const float* rays, int64_t n, uint8_t* flags, int n_thre
             flags[i] = refglsl::IfIfAnyHit(ray, h) ? 1 : 0;
         }
     });
+}
+
+// The shading probe of oracle/pt_oracle.cpp (or_shade_probe, same input / output layout) through the reference's shader
+// functions, called in Iterative.comp:236-288's order: material, interaction, NEE evaluation towards the light direction,
+// GenerateImportanceSample, ComputeBSDF, MISWeight, the throughput factor of :284. Single-threaded: `state` is a global.
+#define PT_SHADE_PROBE(NAME, NS) \
+void NAME(const float* in, uint32_t* rng_io, int64_t n, float* out) { \
+    using namespace NS; \
+    for (int64_t k = 0; k < n; k++) { \
+        const float* a = in + 16 * k; float* o = out + 20 * k; uint32_t* rs = rng_io + 4 * k; \
+        MaterialInstance material = material_from_texels(vec4(a[0], a[1], a[2], 1.0f), vec4(0.0f, a[3], a[4], 1.0f)); \
+        vec3 nrm(a[5], a[6], a[7]), og(a[8], a[9], a[10]), ld(a[11], a[12], a[13]); \
+        SurfaceInteraction interaction = ConstructSurfaceInteraction(nrm, og); \
+        SurfaceInteraction li = interaction; \
+        SetIncomingDirection(li, ld); \
+        vec3 fl = ComputeBSDF(material, li); \
+        o[0] = fl.x; o[1] = fl.y; o[2] = fl.z; o[3] = ProbabilityDensityDirection(material, li); o[4] = li.ndi; \
+        state = uvec4(rs[0], rs[1], rs[2], rs[3]); \
+        float bxdfPdf0, bxdfPdf1; \
+        vec3 d = GenerateImportanceSample(material, interaction, bxdfPdf0, bxdfPdf1); \
+        vec3 fs = ComputeBSDF(material, interaction); \
+        float w = MISWeight(bxdfPdf0, bxdfPdf1); \
+        vec3 factor = ComputeBSDF(material, interaction) * interaction.ndi * MISWeight(bxdfPdf0, bxdfPdf1) / bxdfPdf0; \
+        o[5] = d.x; o[6] = d.y; o[7] = d.z; o[8] = bxdfPdf0; o[9] = bxdfPdf1; o[10] = fs.x; o[11] = fs.y; o[12] = fs.z; o[13] = interaction.ndi; o[14] = w; \
+        o[15] = factor.x; o[16] = factor.y; o[17] = factor.z; o[18] = CalcDiffusePmf(material, interaction); o[19] = 0.0f; \
+        rs[0] = state.x; rs[1] = state.y; rs[2] = state.z; rs[3] = state.w; \
+    } \
+}
+PT_SHADE_PROBE(ref_glsl_shade_probe, refglsl)                     /* GGX, the macros as shipped; throughput factor: Iterative.comp:284 */
+PT_SHADE_PROBE(ref_glsl_shade_probe_beckmann, refglsl_beckmann)
+
+// n draws of the shader's HybridTaus from one state (Random.glsl:47-70)
+void ref_glsl_hybrid_taus(uint32_t st[4], int n, float* out) {
+    using namespace refglsl;
+    state = uvec4(st[0], st[1], st[2], st[3]);
+    for (int i = 0; i < n; i++) out[i] = HybridTaus();
+    st[0] = state.x; st[1] = state.y; st[2] = state.z; st[3] = state.w;
 }
 
 }  // extern "C"

@@ -100,7 +100,19 @@ def scene_fixtures():
                             counters=np.array([c["closest_rays"], c["shadow_rays"]], np.int64))
 
 
+def shading_fixture():
+    """The shading probe through the reference's own shader functions compiled as C++ (oracle/ref_glsl.cpp), both microfacet
+    models, 4096 random cases: the reference's answers for tests/test_oracle_pins.py where /root/reference is absent."""
+    a, rng = oracle.shade_probe_inputs(4096, 2024)
+    g0, r0 = oracle.ref_glsl_shade_probe(a, rng, 0)
+    g1, r1 = oracle.ref_glsl_shade_probe(a, rng, 1)
+    taus, st = oracle.ref_glsl_hybrid_taus(np.array([1234567, 7654321, 999999, 424242], np.uint32), 4096)
+    np.savez_compressed(os.path.join(HERE, "shade_glsl.npz"), inputs=a, rng=rng, ggx=g0, ggx_rng=r0, beckmann=g1, beckmann_rng=r1,
+                        taus=taus, taus_state=st)
+
+
 if __name__ == "__main__":
+    shading_fixture()
     ref_pins()
     scene_fixtures()
     print(sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))
