@@ -156,6 +156,48 @@ def ref_glsl_shade_probe(inputs, rng, model=0):
     return out, r
 
 
+def light_probe_inputs(scene, n, seed):
+    """Random cases for the light-sampling probes: surface points inside the scene's bounds with random normals, views mostly
+    above the surface, the materials of shade_probe_inputs, random throughput; n x 20 floats + n x 4 RNG words."""
+    a16, rng = shade_probe_inputs(n, seed)
+    g = np.random.default_rng(seed + 1000)
+    lo, hi = scene.bounds()
+    a = np.zeros((n, 20), np.float32)
+    a[:, 0:3] = g.uniform(lo, hi, size=(n, 3))
+    a[:, 3:6], a[:, 6:9] = a16[:, 5:8], a16[:, 8:11]
+    a[:, 9:12], a[:, 12], a[:, 13] = a16[:, 0:3], a16[:, 3], a16[:, 4]
+    a[:, 14:17] = g.uniform(0.0, 2.0, size=(n, 3))
+    return a, rng
+
+
+def ref_glsl_light_probe(scene, inputs, rng, model=0):
+    """GenerateLightSample + RandomLightVertex of Iterative.comp compiled as C++ (oracle/ref_glsl.cpp), on the scene's light
+    table and triangles."""
+    g = C.CDLL(GLSL_SO)
+    g.ref_glsl_bind.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+    g.ref_glsl_bind_lights.argtypes = [C.c_void_p, C.c_int, C.c_float]
+    g.ref_glsl_light_probe.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+    nodes = np.ascontiguousarray(scene.nodes, np.float32); refs = np.ascontiguousarray(scene.refs, np.int32)
+    tris = np.ascontiguousarray(scene.tris, np.float32); lights = np.ascontiguousarray(scene.lights, np.float32)
+    g.ref_glsl_bind(_p(nodes), _p(refs), _p(tris), tris.shape[0])
+    g.ref_glsl_bind_lights(_p(lights), lights.shape[0], float(scene.total_light_area))
+    a = np.ascontiguousarray(inputs, dtype=np.float32); r = np.ascontiguousarray(rng, dtype=np.uint32).copy()
+    out = np.zeros((a.shape[0], 12), np.float32)
+    g.ref_glsl_light_probe(_p(a), _p(r), a.shape[0], model, _p(out))
+    return out, r
+
+
+def ref_glsl_raygen(cam_array, width, height, total_light_area, rng_table, first, n):
+    """InitRay + RayIndexToMorton of Iterative.comp compiled as C++: n x 12 floats {pixel (int bits), origin, direction,
+    throughput.x, bxdfPdf0, bxdfPdf1, neePdf}; the pixels' RNG words in rng_table are advanced in place."""
+    g = C.CDLL(GLSL_SO)
+    g.ref_glsl_raygen_probe.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_int64, C.c_int64, C.c_void_p]
+    cam = np.ascontiguousarray(cam_array, dtype=np.float32)
+    out = np.zeros((n, 12), np.float32)
+    g.ref_glsl_raygen_probe(_p(cam), width, height, float(total_light_area), _p(rng_table), first, n, _p(out))
+    return out
+
+
 def ref_glsl_hybrid_taus(state4, n):
     g = C.CDLL(GLSL_SO)
     g.ref_glsl_hybrid_taus.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -313,6 +355,15 @@ class Oracle:
         assert rng.dtype == np.uint32 and rng.flags.c_contiguous and accum.dtype == np.float32 and accum.flags.c_contiguous
         self.l.or_render(C.byref(self.s), C.byref(cam), C.byref(cfg), _p(rng), _p(accum), n_frames, C.byref(c))
         return c.as_dict()
+
+    def light_probe(self, inputs, rng, model=0):
+        """or_light_probe: GenerateLightSample on explicit inputs (n x 20 floats) -> (n x 12 floats, RNG words after)."""
+        self.l.or_light_probe.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        a = np.ascontiguousarray(inputs, dtype=np.float32); r = np.ascontiguousarray(rng, dtype=np.uint32).copy()
+        cfg = OrConfig(64, 64, 66, model, 1)
+        out = np.zeros((a.shape[0], 12), np.float32)
+        self.l.or_light_probe(C.byref(self.s), C.byref(cfg), _p(a), _p(r), a.shape[0], _p(out))
+        return out, r
 
     def raygen(self, cam_array, width, height, rng, first, n):
         cam = self.camera(cam_array)

@@ -673,6 +673,30 @@ void or_shade_probe(const float* in, uint32_t* rng_io, int64_t n, int model, flo
     }
 }
 
+// GenerateLightSample (Iterative.comp:113-147) on explicit inputs, as main() calls it (:276). in: n x 20 floats {vertex
+// position, vertex normal, outgoing, data0.rgb, data1.g, data1.b, throughput.rgb, ...}; out: n x 12 floats {ray origin, ray
+// direction, tmax, lightThroughput.rgb, light material id (bits), lightPdf}; rng_io advanced. sun_light is taken from cfg.
+void or_light_probe(const OrScene* s, const OrConfig* cfg, const float* in, uint32_t* rng_io, int64_t n, float* out) {
+    for (int64_t k = 0; k < n; k++) {
+        const float* a = in + 20 * k; float* o = out + 12 * k; uint32_t* rs = rng_io + 4 * k;
+        V3 vpos = v3(a[0], a[1], a[2]), vn = v3(a[3], a[4], a[5]), og = v3(a[6], a[7], a[8]);
+        Material m{};
+        m.albedo = v3(a[9], a[10], a[11]);
+        m.roughness = gmax(a[12] * a[12], 1e-4f);
+        m.roughness2 = m.roughness * m.roughness;
+        m.metallic = a[13];
+        m.reflectance = mix(v3(0.04f), m.albedo, m.metallic);
+        Interaction it = make_interaction(vn, og);
+        Rng rng; rng.x = rs[0]; rng.y = rs[1]; rng.z = rs[2]; rng.w = rs[3];
+        float tmax; V3 lt; uint32_t lmat;
+        Ray r = light_sample(*s, *cfg, vpos, vn, m, it, rng, tmax, v3(a[14], a[15], a[16]), lt, lmat);
+        o[0] = r.origin.x; o[1] = r.origin.y; o[2] = r.origin.z; o[3] = r.direction.x; o[4] = r.direction.y; o[5] = r.direction.z;
+        o[6] = tmax; o[7] = lt.x; o[8] = lt.y; o[9] = lt.z; std::memcpy(&o[10], &lmat, 4);
+        o[11] = cfg->sun_light ? 0.0f : 1.0f / s->total_light_area;
+        rs[0] = rng.x; rs[1] = rng.y; rs[2] = rng.z; rs[3] = rng.w;
+    }
+}
+
 void or_hybrid_taus(uint32_t state[4], int n, float* out) {
     Rng r{state[0], state[1], state[2], state[3]};
     for (int i = 0; i < n; i++) out[i] = r.next();

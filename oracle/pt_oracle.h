@@ -24,9 +24,12 @@
  *                           GenerateImportanceSample, HybridTaus) vs the same kind of compile of common/{Material,Microfacet,
  *                           BSDF,MIS,Random}.glsl, through or_shade_probe / ref_glsl_shade_probe: same bits, GGX and
  *                           Beckmann, live and on tests/golden/shade_glsl.npz (one NaN-in-max() exception)
- * Traversal and shading arithmetic are therefore pinned to the reference's code; Iterative.comp's main loop (call order,
- * emission + MIS on hit, light sampling, Russian roulette, InitRay), texture filtering and the environment lookup remain
- * "parity unpinned".
+ *   - init_ray / light_sample (InitRay + RayIndexToMorton, GenerateLightSample + RandomLightVertex) vs Iterative.comp's own
+ *                           source for them compiled the same way (or_raygen, or_light_probe vs ref_glsl_raygen_probe,
+ *                           ref_glsl_light_probe): same bits, vectors in tests/golden/path_glsl_cornell_small.npz
+ * Traversal, shading arithmetic, ray generation and light sampling are therefore pinned to the reference's code; the glue of
+ * Iterative.comp's main() (call order, emission + MIS on hit, Russian roulette, path recycling), GetInterpolatedVertex,
+ * texture filtering and the environment lookup remain "parity unpinned".
  *
  * Float mode (stated, because GLSL does not pin one): IEEE-754 binary32, every operation
  * separately rounded (built with -ffp-contract=off -fno-fast-math), division and sqrt
@@ -101,6 +104,8 @@ void or_hybrid_taus(uint32_t state[4], int n, float* out);            /* Random.
 /* shading arithmetic on explicit inputs (material, interaction, NEE evaluation, BSDF sample) in Iterative.comp:236-288's order;
  * in: n x 16 floats, rng_io: n x 4 words (advanced), out: n x 20 floats -- layout in pt_oracle.cpp */
 void or_shade_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out);
+/* GenerateLightSample (Iterative.comp:113-147) on explicit inputs: n x 20 floats in, n x 12 out -- layout in pt_oracle.cpp */
+void or_light_probe(const OrScene* s, const OrConfig* cfg, const float* in, uint32_t* rng_io, int64_t n, float* out);
 void or_image_plane(float aspect, float fov, float focus, float aperture, const float pos[3],
                     const float rot[3], OrCamera* cam);                /* Camera.cpp:4-22 */
 int or_slab_test(const float bmin[3], const float bmax[3], const float iorg[3], const float idir[3],

@@ -32,43 +32,35 @@ namespace refglsl {
 using namespace glm;
 
 // what `uniform samplerBuffer` + texelFetch are to the shader: RGBA32F texels (nodes, triangles) or R32F (reference list)
-struct samplerBuffer { const float* p = nullptr; int comps = 4; };
+struct samplerBuffer { const float* p = nullptr; int comps = 4; int count = 0; };
 inline vec4 texelFetch(const samplerBuffer& s, int i) {
     if (s.comps == 4) return vec4(s.p[4 * (size_t)i], s.p[4 * (size_t)i + 1], s.p[4 * (size_t)i + 2], s.p[4 * (size_t)i + 3]);
+    if (s.comps == 2) return vec4(s.p[2 * (size_t)i], s.p[2 * (size_t)i + 1], 0.0f, 1.0f);     // RG32F: the light table
     return vec4(s.p[i], 0.0f, 0.0f, 1.0f);                       // GL fills missing components with (0, 0, 1)
 }
+inline int textureSize(const samplerBuffer& s) { return s.count; }
 static samplerBuffer vertexTex, nodesTex, referenceTex;           // Geometry.glsl:6, BVH.glsl:353-354
 
 #define BVH_STACK_SIZE 96
 #include "ref_glsl_traversal.inc"
 
-// ---- the shading arithmetic, same recipe (oracle/Makefile: ref_glsl_shading.inc): M_PI, nndot / avdot / AverageLuminance, the
-// HybridTaus generator with its `state` global, MISWeight, MaterialInstance / SurfaceInteraction and their constructors, all
-// of Microfacet.glsl (distributions, visibility, Fresnel, pmf, pdfs, GenerateImportanceSample) and ComputeBSDF
-#undef M_PI
-#include "ref_glsl_shading.inc"
-
-// ConstructMaterialInstance (Material.glsl:39-54) reads two bindless textures; the harness supplies the two texels and runs the
-// shader's own six assignments after them (Material.glsl:46-51, extracted like the rest)
-inline MaterialInstance material_from_texels(vec4 data0, vec4 data1) {
-    MaterialInstance material;
-    material.emission = vec3(0.0f); material.materialType = 1u; material.ior = 0.0f;
-#include "ref_glsl_material_body.inc"
-    return material;
-}
-
 }  // namespace refglsl
 
-// the same shading source with Microfacet.glsl's three model macros pointed at its Beckmann functions
+// ---- shading arithmetic + ray generation + light sampling, once per microfacet model (oracle/ref_glsl_ns.h): the extracted
+// source as shipped (GGX) and the copy with Microfacet.glsl's three model macros pointed at its Beckmann functions
+namespace refglsl_ggx {
+using namespace glm;
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
+}  // namespace refglsl_ggx
 namespace refglsl_beckmann {
 using namespace glm;
-#include "ref_glsl_shading_beckmann.inc"
-inline MaterialInstance material_from_texels(vec4 data0, vec4 data1) {
-    MaterialInstance material;
-    material.emission = vec3(0.0f); material.materialType = 1u; material.ior = 0.0f;
-#include "ref_glsl_material_body.inc"
-    return material;
-}
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading_beckmann.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
 }  // namespace refglsl_beckmann
 
 namespace {
@@ -125,38 +117,22 @@ void ref_glsl_trace_any(const float* rays, int64_t n, uint8_t* flags, int n_thre
     });
 }
 
-// The shading probe of oracle/pt_oracle.cpp (or_shade_probe, same input / output layout) through the reference's shader
-// functions, called in Iterative.comp:236-288's order: material, interaction, NEE evaluation towards the light direction,
-// GenerateImportanceSample, ComputeBSDF, MISWeight, the throughput factor of :284. Single-threaded: `state` is a global.
-#define PT_SHADE_PROBE(NAME, NS) \
-void NAME(const float* in, uint32_t* rng_io, int64_t n, float* out) { \
-    using namespace NS; \
-    for (int64_t k = 0; k < n; k++) { \
-        const float* a = in + 16 * k; float* o = out + 20 * k; uint32_t* rs = rng_io + 4 * k; \
-        MaterialInstance material = material_from_texels(vec4(a[0], a[1], a[2], 1.0f), vec4(0.0f, a[3], a[4], 1.0f)); \
-        vec3 nrm(a[5], a[6], a[7]), og(a[8], a[9], a[10]), ld(a[11], a[12], a[13]); \
-        SurfaceInteraction interaction = ConstructSurfaceInteraction(nrm, og); \
-        SurfaceInteraction li = interaction; \
-        SetIncomingDirection(li, ld); \
-        vec3 fl = ComputeBSDF(material, li); \
-        o[0] = fl.x; o[1] = fl.y; o[2] = fl.z; o[3] = ProbabilityDensityDirection(material, li); o[4] = li.ndi; \
-        state = uvec4(rs[0], rs[1], rs[2], rs[3]); \
-        float bxdfPdf0, bxdfPdf1; \
-        vec3 d = GenerateImportanceSample(material, interaction, bxdfPdf0, bxdfPdf1); \
-        vec3 fs = ComputeBSDF(material, interaction); \
-        float w = MISWeight(bxdfPdf0, bxdfPdf1); \
-        vec3 factor = ComputeBSDF(material, interaction) * interaction.ndi * MISWeight(bxdfPdf0, bxdfPdf1) / bxdfPdf0; \
-        o[5] = d.x; o[6] = d.y; o[7] = d.z; o[8] = bxdfPdf0; o[9] = bxdfPdf1; o[10] = fs.x; o[11] = fs.y; o[12] = fs.z; o[13] = interaction.ndi; o[14] = w; \
-        o[15] = factor.x; o[16] = factor.y; o[17] = factor.z; o[18] = CalcDiffusePmf(material, interaction); o[19] = 0.0f; \
-        rs[0] = state.x; rs[1] = state.y; rs[2] = state.z; rs[3] = state.w; \
-    } \
+// The probes of oracle/ref_glsl_ns.h; model 0 = GGX (the macros as shipped), 1 = Beckmann. Single-threaded: `state` is a global.
+void ref_glsl_shade_probe(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_ggx::shade_probe(in, rng_io, n, out); }
+void ref_glsl_shade_probe_beckmann(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_beckmann::shade_probe(in, rng_io, n, out); }
+void ref_glsl_bind_lights(const float* lights2, int n_lights, float total_light_area) {
+    refglsl_ggx::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann::bind_lights(lights2, n_lights, total_light_area);
 }
-PT_SHADE_PROBE(ref_glsl_shade_probe, refglsl)                     /* GGX, the macros as shipped; throughput factor: Iterative.comp:284 */
-PT_SHADE_PROBE(ref_glsl_shade_probe_beckmann, refglsl_beckmann)
+void ref_glsl_light_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) {
+    if (model == 1) refglsl_beckmann::light_probe(in, rng_io, n, out); else refglsl_ggx::light_probe(in, rng_io, n, out);
+}
+void ref_glsl_raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {
+    refglsl_ggx::raygen_probe(cam19, w, h, total_light_area, table, first, n, out);
+}
 
 // n draws of the shader's HybridTaus from one state (Random.glsl:47-70)
 void ref_glsl_hybrid_taus(uint32_t st[4], int n, float* out) {
-    using namespace refglsl;
+    using namespace refglsl_ggx;
     state = uvec4(st[0], st[1], st[2], st[3]);
     for (int i = 0; i < n; i++) out[i] = HybridTaus();
     st[0] = state.x; st[1] = state.y; st[2] = state.z; st[3] = state.w;

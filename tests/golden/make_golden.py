@@ -111,8 +111,26 @@ def shading_fixture():
                         taus=taus, taus_state=st)
 
 
+def path_fixture():
+    """Ray generation (InitRay + RayIndexToMorton) and light sampling (GenerateLightSample + RandomLightVertex) of Iterative.comp
+    compiled as C++ (oracle/ref_glsl.cpp) on the committed cornell_small tree / scene: the reference's answers."""
+    s = Scene(SCENES["cornell_small"]())
+    z = np.load(os.path.join(HERE, "tree_cornell_small.npz"))
+    s.set_bvh(z["nodes"], z["refs"])
+    a, rng = oracle.light_probe_inputs(s, 4096, 99)
+    l0, r0 = oracle.ref_glsl_light_probe(s, a, rng, 0)
+    l1, r1 = oracle.ref_glsl_light_probe(s, a, rng, 1)
+    w, h = 64, 40
+    cam = make_camera(s.data, w, h, aperture=0.3).as_array()
+    table = make_rng_table(w * h, 5); table0 = table.copy()
+    rays = oracle.ref_glsl_raygen(cam, w, h, s.total_light_area, table, 0, w * h)
+    np.savez_compressed(os.path.join(HERE, "path_glsl_cornell_small.npz"), inputs=a, rng=rng, ggx=l0, ggx_rng=r0, beckmann=l1,
+                        beckmann_rng=r1, cam=cam, size=np.array([w, h]), table0=table0, table1=table, rays=rays)
+
+
 if __name__ == "__main__":
     shading_fixture()
+    path_fixture()
     ref_pins()
     scene_fixtures()
     print(sorted(f for f in os.listdir(HERE) if f.endswith(".npz")))

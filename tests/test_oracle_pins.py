@@ -168,6 +168,42 @@ def test_oracle_shading_equals_reference_shader_golden(model):
     assert np.array_equal(out.view(np.uint32), z["taus"].view(np.uint32)) and np.array_equal(st, z["taus_state"])
 
 
+def _check_light_against(got, got_rng, want, want_rng, model):
+    """Bit equality of ray, tmax, lightThroughput, light material and lightPdf. The Beckmann exception of
+    _check_shading_against shows here as lightThroughput = 0 * NaN = NaN in the glm compile against exactly 0 in the stated
+    float mode (the BSDF is 0 there), nowhere else."""
+    assert np.array_equal(got_rng, want_rng)
+    same = _same_bits_or_both_nan(got, want)
+    if model == 0:
+        assert same.all()
+        return
+    assert same[:, [0, 1, 2, 3, 4, 5, 6, 10, 11]].all()
+    odd = ~same[:, 7:10].all(axis=1)
+    assert np.isnan(want[odd, 7:10]).all() and (got[odd, 7:10] == 0).all() and odd.mean() < 0.35
+
+
+def test_oracle_raygen_and_light_sampling_equal_reference_shader_golden():
+    """tests/golden/path_glsl_cornell_small.npz: what Iterative.comp's own InitRay + RayIndexToMorton (pixel order, jitter,
+    thin-lens sample, ray, the RNG words left behind) and GenerateLightSample + RandomLightVertex (CDF search, point on the
+    emitter, shadow ray, tmax, MIS-weighted light throughput, light material), compiled as C++ by oracle/Makefile, return on the
+    committed cornell_small scene. The oracle's restatements give the same bits."""
+    s = Scene(SCENES["cornell_small"]())
+    t = np.load(os.path.join(GOLDEN, "tree_cornell_small.npz"))
+    s.set_bvh(t["nodes"], t["refs"])
+    z = np.load(os.path.join(GOLDEN, "path_glsl_cornell_small.npz"))
+    o = oracle.Oracle(s)
+    for model, key in ((0, "ggx"), (1, "beckmann")):
+        got, rng = o.light_probe(z["inputs"], z["rng"], model)
+        _check_light_against(got, rng, z[key], z[key + "_rng"], model)
+    assert np.isfinite(z["ggx"][:, 7:10]).all() and (z["ggx"][:, 7:10] > 0).any(axis=1).mean() > 0.1
+    w, h = (int(v) for v in z["size"])
+    table = z["table0"].copy()
+    rays = o.raygen(z["cam"], w, h, table, 0, w * h)
+    assert np.array_equal(rays[:, :8].view(np.uint32), z["rays"][:, :8].view(np.uint32))
+    assert np.array_equal(table, z["table1"])
+    assert np.all(z["rays"][:, 8:11] == 1.0) and np.all(z["rays"][:, 11] == np.float32(0.5) / np.float32(s.total_light_area))
+
+
 needs_glsl = pytest.mark.skipif(not oracle.have_glsl(), reason="oracle/_ref/libref_glsl.so not built (no /root/reference)")
 
 
@@ -199,6 +235,27 @@ def test_oracle_shading_equals_live_reference_shader(model):
     want, wrng = oracle.ref_glsl_shade_probe(a, rng, model)
     got, grng = oracle.shade_probe(a, rng, model)
     _check_shading_against(got, grng, want, wrng, model)
+
+
+@needs_glsl
+@pytest.mark.parametrize("name", ["cornell", "atrium_small"])
+def test_oracle_raygen_and_light_sampling_equal_live_reference_shader(name):
+    """Live: 100 000 light-sampling cases per model and a full 64 x 40 frame of InitRay per scene."""
+    from common import get_scene, make_camera
+    from gpupathtracer_b200 import make_rng_table
+    s = get_scene(name)
+    o = oracle.Oracle(s)
+    a, rng = oracle.light_probe_inputs(s, 100000, 7)
+    for model in (0, 1):
+        want, wrng = oracle.ref_glsl_light_probe(s, a, rng, model)
+        got, grng = o.light_probe(a, rng, model)
+        _check_light_against(got, grng, want, wrng, model)
+    w, h = 64, 40
+    cam = make_camera(s.data, w, h, aperture=0.3).as_array()
+    t1 = make_rng_table(w * h, 5); t2 = t1.copy()
+    got = o.raygen(cam, w, h, t1, 0, w * h)
+    want = oracle.ref_glsl_raygen(cam, w, h, s.total_light_area, t2, 0, w * h)
+    assert np.array_equal(got[:, :8].view(np.uint32), want[:, :8].view(np.uint32)) and np.array_equal(t1, t2)
 
 
 # ----------------------------------------------------------------------------------- live reference (this container)
