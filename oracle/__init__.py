@@ -356,6 +356,31 @@ class Oracle:
         self.l.or_render(C.byref(self.s), C.byref(cam), C.byref(cfg), _p(rng), _p(accum), n_frames, C.byref(c))
         return c.as_dict()
 
+    def ref_glsl_render(self, cam_array, width, height, rng, accum, model=0, sun=None):
+        """One dispatch of the reference's own main() (Iterative.comp:214-307, compiled as C++ by oracle/Makefile) over a whole
+        frame of this scene, in place on rng and accum like render(). Its texture units and cube map are this library's
+        or_sample_texture / or_sample_environment (GL's fixed-function filtering has one statement), everything else on the
+        path is the reference's source. Path length is the shader's own (i > 64), i.e. max_depth 66. sun = (direction, radius)
+        runs the shader's SUN_LIGHT build."""
+        g = C.CDLL(GLSL_SO)
+        g.ref_glsl_bind.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+        g.ref_glsl_bind_lights.argtypes = [C.c_void_p, C.c_int, C.c_float]
+        g.ref_glsl_bind_materials.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        g.ref_glsl_render_frame.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_int]
+        g.ref_glsl_render_frame_sun.argtypes = g.ref_glsl_render_frame.argtypes + [C.c_void_p, C.c_float]
+        g.ref_glsl_bind(_p(self.nodes), _p(self.refs), _p(self.tris), self.tris.shape[0])
+        g.ref_glsl_bind_lights(_p(self.lights), self.lights.shape[0], float(self.s.total_light_area))
+        g.ref_glsl_bind_materials(_p(self.materials), self.materials.shape[0], C.addressof(self.s),
+                                  C.cast(self.l.or_sample_texture, C.c_void_p), C.cast(self.l.or_sample_environment, C.c_void_p))
+        cam = np.ascontiguousarray(cam_array, dtype=np.float32)
+        assert rng.dtype == np.uint32 and rng.flags.c_contiguous and accum.dtype == np.float32 and accum.flags.c_contiguous
+        tla = float(self.s.total_light_area)
+        if sun is not None:
+            d = np.ascontiguousarray(sun[0], dtype=np.float32)
+            g.ref_glsl_render_frame_sun(_p(cam), width, height, tla, _p(rng), _p(accum), model, _p(d), float(sun[1]))
+        else:
+            g.ref_glsl_render_frame(_p(cam), width, height, tla, _p(rng), _p(accum), model)
+
     def light_probe(self, inputs, rng, model=0):
         """or_light_probe: GenerateLightSample on explicit inputs (n x 20 floats) -> (n x 12 floats, RNG words after)."""
         self.l.or_light_probe.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]

@@ -697,6 +697,13 @@ void or_light_probe(const OrScene* s, const OrConfig* cfg, const float* in, uint
     }
 }
 
+// GL_LINEAR + GL_REPEAT lookup of scene texture `index` (what `texture(sampler2D, uv)` is to the shader); used by the compiled
+// shader source in oracle/ref_glsl.cpp as its texture unit, so that GL's fixed-function filtering is stated once
+void or_sample_texture(const OrScene* s, int index, float u, float v, float* rgba) {
+    if (index < 0 || index >= s->n_textures) { rgba[0] = rgba[1] = rgba[2] = 0.0f; rgba[3] = 1.0f; return; }
+    sample_texture(s->textures[index], u, v, rgba);
+}
+
 void or_hybrid_taus(uint32_t state[4], int n, float* out) {
     Rng r{state[0], state[1], state[2], state[3]};
     for (int i = 0; i < n; i++) out[i] = r.next();

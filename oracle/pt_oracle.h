@@ -103,6 +103,7 @@ typedef struct OrCounters {
 void or_hybrid_taus(uint32_t state[4], int n, float* out);            /* Random.glsl:47-70 */
 /* shading arithmetic on explicit inputs (material, interaction, NEE evaluation, BSDF sample) in Iterative.comp:236-288's order;
  * in: n x 16 floats, rng_io: n x 4 words (advanced), out: n x 20 floats -- layout in pt_oracle.cpp */
+void or_sample_texture(const OrScene* s, int index, float u, float v, float* rgba);   /* texture(sampler2D, uv): LINEAR + REPEAT */
 void or_shade_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out);
 /* GenerateLightSample (Iterative.comp:113-147) on explicit inputs: n x 20 floats in, n x 12 out -- layout in pt_oracle.cpp */
 void or_light_probe(const OrScene* s, const OrConfig* cfg, const float* in, uint32_t* rng_io, int64_t n, float* out);

@@ -24,6 +24,7 @@
 #include <glm/glm.hpp>
 #include <atomic>
 #include <cstdint>
+#include <cmath>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -44,6 +45,37 @@ static samplerBuffer vertexTex, nodesTex, referenceTex;           // Geometry.gl
 #define BVH_STACK_SIZE 96
 #include "ref_glsl_traversal.inc"
 
+// ---- the rest of the GL runtime main() sees: bindless texture handles, the material SSBO, the accumulation image.
+// A handle is an index into g_units; a unit is a scene texture (filtered by the oracle library's statement of GL_LINEAR /
+// GL_REPEAT through a function pointer, so that fixed-function behaviour is stated once) or a constant colour, which is what
+// the reference's 1 x 1 RGBA32F colour textures return for any coordinate (Texture.cpp:146-161). The environment cube map goes
+// through the oracle library's lookup the same way (constant colour or six faces).
+struct TexUnit { int scene_texture; vec4 constant; };
+static std::vector<TexUnit> g_units;
+typedef void (*tex2d_fn)(const void* scene, int index, float u, float v, float* rgba);        // or_sample_texture
+typedef void (*cube_fn)(const void* scene, const float* dirs, int64_t n, float* rgb);          // or_sample_environment
+static tex2d_fn g_tex2d = nullptr;
+static cube_fn g_cube = nullptr;
+static const void* g_gl_scene = nullptr;
+struct sampler2D { uvec2 h; explicit sampler2D(uvec2 x) : h(x) {} };
+struct samplerCube { uvec2 h; explicit samplerCube(uvec2 x) : h(x) {} };
+inline vec4 texture(const sampler2D& s, vec2 uv) {
+    const TexUnit& t = g_units[s.h.x];
+    if (t.scene_texture < 0) return t.constant;
+    if (!std::isfinite(uv.x) || !std::isfinite(uv.y)) return t.constant;   // main() looks material 0 up with a missed ray's unset hit record
+    float o[4]; g_tex2d(g_gl_scene, t.scene_texture, uv.x, uv.y, o);
+    return vec4(o[0], o[1], o[2], o[3]);
+}
+inline vec4 texture(const samplerCube&, vec3 d) {
+    float in[3] = {d.x, d.y, d.z}, o[3]; g_cube(g_gl_scene, in, 1, o);
+    return vec4(o[0], o[1], o[2], 1.0f);
+}
+static std::vector<vec4> g_material_ssbo;                          // `materialInstance[]`, Material.glsl:10-12 / Scene.cpp:296-299
+struct image2D { float* p = nullptr; int w = 0; };
+inline vec4 imageLoad(const image2D& im, ivec2 px) { const float* q = im.p + 4 * ((size_t)px.y * im.w + px.x); return vec4(q[0], q[1], q[2], q[3]); }
+inline void imageStore(const image2D& im, ivec2 px, vec4 v) { float* q = im.p + 4 * ((size_t)px.y * im.w + px.x); q[0] = v.x; q[1] = v.y; q[2] = v.z; q[3] = v.w; }
+static uvec3 gl_LocalInvocationID(0u);
+
 }  // namespace refglsl
 
 // ---- shading arithmetic + ray generation + light sampling, once per microfacet model (oracle/ref_glsl_ns.h): the extracted
@@ -62,6 +94,23 @@ using namespace refglsl;
 #include "ref_glsl_ns.h"
 #undef REFGLSL_SHADING
 }  // namespace refglsl_beckmann
+// ... and both again as the SUN_LIGHT build (GenerateLightSample's coin flip between the emitters and the sun disk)
+#define REFGLSL_SUN
+namespace refglsl_ggx_sun {
+using namespace glm;
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
+}  // namespace refglsl_ggx_sun
+namespace refglsl_beckmann_sun {
+using namespace glm;
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading_beckmann.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
+}  // namespace refglsl_beckmann_sun
+#undef REFGLSL_SUN
 
 namespace {
 template <class F>
@@ -122,10 +171,44 @@ void ref_glsl_shade_probe(const float* in, uint32_t* rng_io, int64_t n, float* o
 void ref_glsl_shade_probe_beckmann(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_beckmann::shade_probe(in, rng_io, n, out); }
 void ref_glsl_bind_lights(const float* lights2, int n_lights, float total_light_area) {
     refglsl_ggx::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann::bind_lights(lights2, n_lights, total_light_area);
+    refglsl_ggx_sun::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann_sun::bind_lights(lights2, n_lights, total_light_area);
 }
 void ref_glsl_light_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) {
     if (model == 1) refglsl_beckmann::light_probe(in, rng_io, n, out); else refglsl_ggx::light_probe(in, rng_io, n, out);
 }
+// materials: n x 12 floats as OrScene has them {colour.rgb, albedo texture index (int bits, -1 = none), emission.rgb, -,
+// props.rgb, props texture index}; laid out for the shader as Scene.cpp:296-299 does: [albedo handle, props handle][emission, flag]
+void ref_glsl_bind_materials(const float* materials12, int n, const void* gl_scene, refglsl::tex2d_fn tex2d, refglsl::cube_fn cube) {
+    using namespace refglsl;
+    g_units.clear(); g_material_ssbo.clear();
+    g_tex2d = tex2d; g_cube = cube; g_gl_scene = gl_scene;
+    for (int k = 0; k < n; k++) {
+        const float* m = materials12 + 12 * (size_t)k;
+        int at, pt; std::memcpy(&at, m + 3, 4); std::memcpy(&pt, m + 11, 4);
+        g_units.push_back(TexUnit{at, glm::vec4(m[0], m[1], m[2], 1.0f)});
+        g_units.push_back(TexUnit{pt, glm::vec4(m[8], m[9], m[10], 1.0f)});
+        glm::uvec4 handles(2u * k, 0u, 2u * k + 1u, 0u);
+        g_material_ssbo.push_back(glm::uintBitsToFloat(handles));
+        g_material_ssbo.push_back(glm::vec4(m[4], m[5], m[6], m[7]));
+    }
+    refglsl_ggx::materialInstance = g_material_ssbo.data(); refglsl_beckmann::materialInstance = g_material_ssbo.data();
+    refglsl_ggx_sun::materialInstance = g_material_ssbo.data(); refglsl_beckmann_sun::materialInstance = g_material_ssbo.data();
+}
+
+// One dispatch of the reference's main() (Iterative.comp:214-307) over a whole frame: every pixel's path, accumulated into
+// `accum` (h x w x 4 floats, `imageStore`), RNG words written back by freeRNG. One invocation loops over all rays, which the
+// persistent shader allows (any number of invocations share the ray counter). Scene: ref_glsl_bind + _bind_lights + _bind_materials.
+void ref_glsl_render_frame(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* accum, int model) {
+    if (model == 1) refglsl_beckmann::render_frame(cam19, w, h, total_light_area, table, accum);
+    else refglsl_ggx::render_frame(cam19, w, h, total_light_area, table, accum);
+}
+// The same with the shader compiled as the SUN_LIGHT build (sunDir, sunRadius: Iterative.comp:89-90)
+void ref_glsl_render_frame_sun(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* accum, int model,
+                               const float* sun_dir3, float sun_radius) {
+    if (model == 1) { refglsl_beckmann_sun::set_sun(sun_dir3, sun_radius); refglsl_beckmann_sun::render_frame(cam19, w, h, total_light_area, table, accum); }
+    else { refglsl_ggx_sun::set_sun(sun_dir3, sun_radius); refglsl_ggx_sun::render_frame(cam19, w, h, total_light_area, table, accum); }
+}
+
 void ref_glsl_raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {
     refglsl_ggx::raygen_probe(cam19, w, h, total_light_area, table, first, n, out);
 }

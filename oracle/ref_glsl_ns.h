@@ -19,12 +19,27 @@ inline MaterialInstance material_from_texels(vec4 data0, vec4 data1) {
 static uint globalNextRay;                                          // the ray counter SSBO, Iterative.comp:150-152
 inline uint atomicAdd(uint& x, uint v) { uint o = x; x += v; return o; }
 #define globalRayCount int(width * height)                          // Iterative.comp:149
-static const uint32_t* rngTable;                                    // `states[]`, Random.glsl (one uvec4 per pixel)
+static uint32_t* rngTable;                                          // `states[]`, Random.glsl (one uvec4 per pixel)
 inline void initRNG(uint ridx) {                                    // Random.glsl:232-237 without the LD-sequence state the path never reads
+    stateIdx = ridx;
     state = uvec4(rngTable[4 * (size_t)ridx], rngTable[4 * (size_t)ridx + 1], rngTable[4 * (size_t)ridx + 2], rngTable[4 * (size_t)ridx + 3]);
 }
+#ifdef REFGLSL_SUN
+#define SUN_LIGHT                                                   // Renderer.cpp compiles the shader with this when the sun is on
+#endif
 #include "ref_glsl_path.inc"
+#undef SUN_LIGHT
 #undef uniform
+
+// ---- main() itself (Iterative.comp:214-307) with GetInterpolatedVertex and ConstructMaterialInstance
+inline void freeRNG() {                                             // Random.glsl:239-242, again without the LD-sequence word
+    rngTable[4 * (size_t)stateIdx] = state.x; rngTable[4 * (size_t)stateIdx + 1] = state.y;
+    rngTable[4 * (size_t)stateIdx + 2] = state.z; rngTable[4 * (size_t)stateIdx + 3] = state.w;
+}
+static const vec4* materialInstance;                                // the `samplers` SSBO, Material.glsl:10-12
+static image2D accum;                                               // Iterative.comp:29
+static uvec2 threadIdx;                                             // Iterative.comp:4
+#include "ref_glsl_main.inc"
 
 // in / out layouts: oracle/pt_oracle.cpp or_shade_probe
 static void shade_probe(const float* in, uint32_t* rng_io, int64_t n, float* out) {
@@ -72,10 +87,21 @@ static void light_probe(const float* in, uint32_t* rng_io, int64_t n, float* out
 
 // InitRay (Iterative.comp:174-210) for ray indices [first, first + n); out: n x 12 floats as or_raygen {pixel.x, pixel.y (int
 // bits), origin, direction, throughput.x, bxdfPdf0, bxdfPdf1, neePdf}; the pixel's RNG words in `table` are advanced (freeRNG's part)
-static void raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {
+static void set_camera(const float* cam19, int w, int h, float total_light_area, uint32_t* table) {
     lower_left = vec3(cam19[0], cam19[1], cam19[2]); horizontal = vec3(cam19[3], cam19[4], cam19[5]); vertical = vec3(cam19[6], cam19[7], cam19[8]);
     position = vec3(cam19[9], cam19[10], cam19[11]); u = vec3(cam19[12], cam19[13], cam19[14]); v = vec3(cam19[15], cam19[16], cam19[17]);
     lens_radius = cam19[18]; width = w; height = h; totalLightArea = total_light_area; rngTable = table;
+}
+static void set_sun(const float* dir3, float radius) { sunDir = vec3(dir3[0], dir3[1], dir3[2]); sunRadius = radius; }
+// one dispatch of main(): a single invocation drains the ray counter
+static void render_frame(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* image) {
+    set_camera(cam19, w, h, total_light_area, table);
+    accum.p = image; accum.w = w;
+    globalNextRay = 0u;
+    shader_main();
+}
+static void raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {
+    set_camera(cam19, w, h, total_light_area, table);
     for (int64_t k = 0; k < n; k++) {
         globalNextRay = (uint)(first + k);
         ivec2 pixel; Ray ray; vec3 throughput, contribution, lastPosition; float bxdfPdf0, bxdfPdf1, neePdf;

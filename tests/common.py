@@ -76,3 +76,22 @@ def rel_mse(a, b, eps=1e-2):
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
     ok = np.isfinite(a) & np.isfinite(b)
     return float(np.mean(((a - b) ** 2 / (b ** 2 + eps))[ok]))
+
+
+def with_textures_and_sky(scene, seed=5):
+    """A copy of `scene` whose materials (all but the sky material 0) look their albedo and roughness/metallic up in small
+    random textures (odd sizes, a 1 x 1 one, some left constant) and whose environment is a random 8 x 8 cube map: every
+    texture unit main() can touch is exercised."""
+    import copy
+    s = copy.copy(scene)
+    g = np.random.default_rng(seed)
+    s.textures = [g.uniform(0.05, 0.95, size=(hh, ww, 4)).astype(np.float32) for hh, ww in ((8, 8), (5, 7), (16, 4), (1, 1))]
+    m = np.array(scene.materials, dtype=np.float32, copy=True)
+    mi = m.view(np.int32)
+    for k in range(1, m.shape[0]):
+        mi[k, 3] = k % 5 - 1
+        mi[k, 11] = (k * 3) % 5 - 1
+    s.materials = m
+    s.env_cubemap = g.uniform(0.0, 3.0, size=(6, 8, 8, 4)).astype(np.float32)
+    s.env_cubemap[..., 3] = 1.0
+    return s

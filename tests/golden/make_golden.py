@@ -128,8 +128,34 @@ def path_fixture():
                         beckmann_rng=r1, cam=cam, size=np.array([w, h]), table0=table0, table1=table, rays=rays)
 
 
+def frame_fixture():
+    """One frame of the reference's main() (Iterative.comp:214-307 compiled as C++) on the committed cornell_small tree, textured
+    and under a cube-map sky (tests/common.py with_textures_and_sky), both microfacet models, and the SUN_LIGHT build."""
+    from common import with_textures_and_sky
+    s0 = Scene(SCENES["cornell_small"]())
+    z = np.load(os.path.join(HERE, "tree_cornell_small.npz"))
+    s0.set_bvh(z["nodes"], z["refs"])
+    s = with_textures_and_sky(s0)
+    o = oracle.Oracle(s)
+    w, h = 40, 24
+    cam = make_camera(s.data, w, h, aperture=0.2).as_array()
+    table0 = make_rng_table(w * h, 17)
+    out = {}
+    for model, key in ((0, "ggx"), (1, "beckmann")):
+        table = table0.copy(); accum = np.zeros((h, w, 4), np.float32)
+        o.ref_glsl_render(cam, w, h, table, accum, model)
+        out[key], out[key + "_rng"] = accum, table
+    d = np.array([2.0, 9.0, 12.0], np.float32)
+    out["sun_dir"], out["sun_radius"] = d / np.float32(np.sqrt((d * d).sum(dtype=np.float32))), np.float32(0.05)
+    table = table0.copy(); accum = np.zeros((h, w, 4), np.float32)
+    o.ref_glsl_render(cam, w, h, table, accum, 0, sun=(out["sun_dir"], 0.05))
+    out["ggx_sun"], out["ggx_sun_rng"] = accum, table
+    np.savez_compressed(os.path.join(HERE, "frame_glsl_cornell_small.npz"), cam=cam, size=np.array([w, h]), table0=table0, **out)
+
+
 if __name__ == "__main__":
     shading_fixture()
+    frame_fixture()
     path_fixture()
     ref_pins()
     scene_fixtures()

@@ -258,6 +258,88 @@ def test_oracle_raygen_and_light_sampling_equal_live_reference_shader(name):
     assert np.array_equal(got[:, :8].view(np.uint32), want[:, :8].view(np.uint32)) and np.array_equal(t1, t2)
 
 
+def _check_frame_against(got, got_rng, want, want_rng, model):
+    """Whole frames: accumulation image and RNG table bit for bit. Beckmann keeps the exception of _check_shading_against: a
+    pixel whose path met max(NaN, x) is NaN in the glm compile and finite in the stated float mode; the RNG words agree even
+    there (the draws do not depend on it)."""
+    assert np.array_equal(got_rng, want_rng)
+    same = _same_bits_or_both_nan(got, want).all(axis=2)
+    if model == 0:
+        assert same.all() and np.isfinite(want).all()
+        return
+    assert np.isnan(want[~same]).any(axis=1).all() and (~same).mean() < 0.1
+
+
+def test_oracle_frame_equals_reference_main_golden():
+    """tests/golden/frame_glsl_cornell_small.npz: one frame of the reference's own main() (Iterative.comp:214-307 with
+    GetInterpolatedVertex and ConstructMaterialInstance, compiled as C++ by oracle/Makefile) on the committed cornell_small tree
+    with textures on every unit and a cube-map sky: accumulation image and the RNG table it leaves. or_render gives the same
+    bits, which pins the glue between the pieces pinned above: MIS bookkeeping across bounces, termination, the sky term,
+    accumulation, RNG write-back. The third frame is the shader's SUN_LIGHT build."""
+    from common import with_textures_and_sky
+    s0 = Scene(SCENES["cornell_small"]())
+    t = np.load(os.path.join(GOLDEN, "tree_cornell_small.npz"))
+    s0.set_bvh(t["nodes"], t["refs"])
+    s = with_textures_and_sky(s0)
+    z = np.load(os.path.join(GOLDEN, "frame_glsl_cornell_small.npz"))
+    w, h = (int(v) for v in z["size"])
+    o = oracle.Oracle(s)
+    for model, key in ((0, "ggx"), (1, "beckmann")):
+        table = z["table0"].copy(); accum = np.zeros((h, w, 4), np.float32)
+        o.render(z["cam"], w, h, table, accum, n_frames=1, max_depth=66, model=model)
+        _check_frame_against(accum, table, z[key], z[key + "_rng"], model)
+    assert (z["ggx"][..., :3] > 0).any(axis=2).mean() > 0.9
+    table = z["table0"].copy(); accum = np.zeros((h, w, 4), np.float32)
+    o.render(z["cam"], w, h, table, accum, n_frames=1, max_depth=66, model=0, sun=(z["sun_dir"], float(z["sun_radius"])))
+    _check_frame_against(accum, table, z["ggx_sun"], z["ggx_sun_rng"], 0)
+    assert not np.array_equal(z["ggx_sun"], z["ggx"])
+
+
+@needs_glsl
+@pytest.mark.parametrize("name", ["cornell", "soup_small", "atrium_small"])
+def test_oracle_frame_equals_live_reference_main(name):
+    """Live: the plain scene and its textured / cube-map variant, both microfacet models, two frames accumulated (the second
+    starts from the first's image and RNG table)."""
+    from common import get_scene, make_camera, with_textures_and_sky
+    from gpupathtracer_b200 import make_rng_table
+    base = get_scene(name)
+    w, h = 48, 32
+    for s in (base, with_textures_and_sky(base)):
+        o = oracle.Oracle(s)
+        cam = make_camera(s.data, w, h, aperture=0.2).as_array()
+        for model in (0, 1):
+            t1 = make_rng_table(w * h, 11); t2 = t1.copy()
+            a1 = np.zeros((h, w, 4), np.float32); a2 = a1.copy()
+            for _ in range(2):
+                o.render(cam, w, h, t1, a1, n_frames=1, max_depth=66, model=model)
+                o.ref_glsl_render(cam, w, h, t2, a2, model)
+            _check_frame_against(a1, t1, a2, t2, model)
+
+
+@needs_glsl
+@pytest.mark.parametrize("name", ["cornell", "soup_small", "atrium_small"])
+def test_oracle_sun_light_frame_equals_live_reference_main(name):
+    """The shader's SUN_LIGHT build (Iterative.comp:89-110,116-126: coin flip between the emitters and a sun disk one unit away,
+    unoccluded sun rays credit the sky material's emission) against or_render's sun branch: whole frames, bit for bit."""
+    from common import get_scene, make_camera
+    from gpupathtracer_b200 import make_rng_table
+    s = get_scene(name)
+    o = oracle.Oracle(s)
+    w, h = 48, 32
+    cam = make_camera(s.data, w, h, aperture=0.2).as_array()
+    d = np.array([2.0, 9.0, 12.0], np.float32)
+    sun = (d / np.float32(np.sqrt((d * d).sum(dtype=np.float32))), 0.05)
+    for model in (0, 1):
+        t1 = make_rng_table(w * h, 11); t2 = t1.copy()
+        a1 = np.zeros((h, w, 4), np.float32); a2 = a1.copy()
+        o.render(cam, w, h, t1, a1, n_frames=1, max_depth=66, model=model, sun=sun)
+        o.ref_glsl_render(cam, w, h, t2, a2, model, sun=sun)
+        _check_frame_against(a1, t1, a2, t2, model)
+        plain = np.zeros((h, w, 4), np.float32)
+        o.render(cam, w, h, make_rng_table(w * h, 11), plain, n_frames=1, max_depth=66, model=model)
+        assert not np.array_equal(plain, a1)                                   # the branch really is another program
+
+
 # ----------------------------------------------------------------------------------- live reference (this container)
 needs_ref = pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/libref_shim.so not built (no /root/reference)")
 
