@@ -7,7 +7,7 @@
  *
  * PARITY STATUS: the reference ships no tests, golden vectors or known-answer fixtures
  * (SURVEY.md section 4), and its GLSL cannot execute on this box (no GL stack), so the
- * shader restatement is "parity unpinned" by the reference's own tests. What IS pinned,
+ * pins below come from compiling the reference's own sources in place, not from its tests. What IS pinned,
  * against the reference's own C++ compiled in place (oracle/_ref/libref_shim.so, see
  * oracle/Makefile and tests/test_oracle_vs_ref.py):
  *   - HybridTaus            vs Renderer.cpp:764-782   (bit-exact)
@@ -27,9 +27,13 @@
  *   - init_ray / light_sample (InitRay + RayIndexToMorton, GenerateLightSample + RandomLightVertex) vs Iterative.comp's own
  *                           source for them compiled the same way (or_raygen, or_light_probe vs ref_glsl_raygen_probe,
  *                           ref_glsl_light_probe): same bits, vectors in tests/golden/path_glsl_cornell_small.npz
- * Traversal, shading arithmetic, ray generation and light sampling are therefore pinned to the reference's code; the glue of
- * Iterative.comp's main() (call order, emission + MIS on hit, Russian roulette, path recycling), GetInterpolatedVertex,
- * texture filtering and the environment lookup remain "parity unpinned".
+ *   - or_render (whole frames: main() of Iterative.comp:214-307, GetInterpolatedVertex, ConstructMaterialInstance, and the
+ *                           SUN_LIGHT build) vs that source compiled the same way with the harness as its GL runtime
+ *                           (ref_glsl_render_frame[_sun]): same bits in the accumulation image and the RNG table, plain and
+ *                           textured / cube-map scenes, vectors in tests/golden/frame_glsl_cornell_small.npz
+ * The whole shader path is therefore pinned to the reference's code. What remains "parity unpinned" is GL's fixed-function
+ * part only: GL_LINEAR / GL_REPEAT filtering behind texture() and the cube-map face selection (or_sample_texture,
+ * or_sample_environment, which the compiled shader source calls as its texture units).
  *
  * Float mode (stated, because GLSL does not pin one): IEEE-754 binary32, every operation
  * separately rounded (built with -ffp-contract=off -fno-fast-math), division and sqrt
