@@ -119,6 +119,36 @@ def test_frames_match_oracle(name, depth, model):
     assert rel_mse(got[..., :3], want[..., :3]) < 1e-3
 
 
+@pytest.mark.skipif(not oracle.have_glsl(), reason="oracle/_ref/libref_glsl.so not built (it travels with the snapshot when it was)")
+@pytest.mark.parametrize("name,textured", [("cornell", False), ("cornell", True), ("atrium_small", True)])
+def test_cuda_frames_equal_reference_main(name, textured):
+    """RenderFrame against the reference's OWN main() (Iterative.comp:214-307 compiled as C++, oracle/ref_glsl.cpp), no
+    restatement in between, at the shader's own path length: the same tolerance as test_frames_match_oracle (a 1-2 ulp libm
+    difference in sin / cos / log / exp can flip a decision in a few pixels; everywhere else image and RNG words agree)."""
+    from common import with_textures_and_sky
+    s = get_scene(name)
+    if textured:
+        s = with_textures_and_sky(s)
+    w, h, frames = 64, 64, 2
+    cam = make_camera(s.data, w, h, aperture=0.1)
+    rng = make_rng_table(w * h, 23)
+    r = _renderer(s, w, h, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=0, rng_state=rng)
+    r.RenderFrame(cam, frames)
+    got = r.DownloadAccum()
+    rng_got = r.GetRNG()
+    r.CleanUp()
+    rng_ref = rng.copy()
+    want = np.zeros((h, w, 4), np.float32)
+    o = oracle.Oracle(s)
+    for _ in range(frames):
+        o.ref_glsl_render(cam.as_array(), w, h, rng_ref, want, 0)
+    assert np.isfinite(want).all()
+    close = np.isclose(got[..., :3], want[..., :3], rtol=1e-4, atol=1e-6).all(axis=2)
+    assert close.mean() > 0.995, f"only {close.mean():.5f} of pixels agree to 1e-4"
+    assert float((rng_got == rng_ref).all(axis=1).mean()) > 0.995
+    assert rel_mse(got[..., :3], want[..., :3]) < 1e-3
+
+
 def test_reset_and_accumulate():
     s = get_scene("cornell_small")
     w, h = 32, 32
