@@ -381,6 +381,26 @@ class Oracle:
         else:
             g.ref_glsl_render_frame(_p(cam), width, height, tla, _p(rng), _p(accum), model)
 
+    def ref_glsl_render_mp(self, cam_array, width, height, rng, accum, n_frames=1, max_depth=66, model=0, n_procs=0):
+        """n_frames dispatches of the reference's main() by n_procs forked processes that share the ray counter the way the
+        GPU's invocations share the SSBO word (oracle/ref_glsl.cpp ref_glsl_render_frames_mp): the reference's own code on
+        all host cores. Same bits as ref_glsl_render, whichever process traces a pixel."""
+        g = C.CDLL(GLSL_SO)
+        g.ref_glsl_bind.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64]
+        g.ref_glsl_bind_lights.argtypes = [C.c_void_p, C.c_int, C.c_float]
+        g.ref_glsl_bind_materials.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        g.ref_glsl_render_frames_mp.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+        g.ref_glsl_bind(_p(self.nodes), _p(self.refs), _p(self.tris), self.tris.shape[0])
+        g.ref_glsl_bind_lights(_p(self.lights), self.lights.shape[0], float(self.s.total_light_area))
+        g.ref_glsl_bind_materials(_p(self.materials), self.materials.shape[0], C.addressof(self.s),
+                                  C.cast(self.l.or_sample_texture, C.c_void_p), C.cast(self.l.or_sample_environment, C.c_void_p))
+        cam = np.ascontiguousarray(cam_array, dtype=np.float32)
+        assert rng.dtype == np.uint32 and rng.flags.c_contiguous and accum.dtype == np.float32 and accum.flags.c_contiguous
+        rc = g.ref_glsl_render_frames_mp(_p(cam), width, height, float(self.s.total_light_area), _p(rng), _p(accum), model,
+                                         max_depth, n_frames, n_procs or (os.cpu_count() or 1))
+        if rc != 0:
+            raise RuntimeError("ref_glsl_render_frames_mp: a worker process failed")
+
     def light_probe(self, inputs, rng, model=0):
         """or_light_probe: GenerateLightSample on explicit inputs (n x 20 floats) -> (n x 12 floats, RNG words after)."""
         self.l.or_light_probe.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]

@@ -25,6 +25,11 @@
 #include <atomic>
 #include <cstdint>
 #include <cmath>
+#include <sched.h>
+#include <signal.h>
+#include <sys/mman.h>
+#include <sys/wait.h>
+#include <unistd.h>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -202,6 +207,61 @@ void ref_glsl_render_frame(const float* cam19, int w, int h, float total_light_a
     if (model == 1) refglsl_beckmann::render_frame(cam19, w, h, total_light_area, table, accum);
     else refglsl_ggx::render_frame(cam19, w, h, total_light_area, table, accum);
 }
+// n_frames dispatches of main() by n_procs processes sharing the ray counter, as the GPU's invocations share the SSBO word:
+// image, RNG table, one counter and one arrival word per frame live in a MAP_SHARED mapping, the children are forked once,
+// each drains frame f's counter and waits for the others before frame f + 1 (a pixel's next frame reads what any process wrote).
+// max_depth as pt_config has it (66 = the shader as shipped). Returns 0, or -1 when a child did not exit cleanly.
+int ref_glsl_render_frames_mp(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* accum, int model,
+                              int max_depth, int n_frames, int n_procs) {
+    const size_t px = (size_t)w * h, words = 2 * (size_t)n_frames;
+    const size_t bytes = ((words * 4 + 63) / 64) * 64 + px * 16 * 2;
+    void* m = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    if (m == MAP_FAILED) return -1;
+    uint32_t* ctr = (uint32_t*)m;
+    uint32_t* arrive = ctr + n_frames;
+    uint32_t* stable = (uint32_t*)((char*)m + ((words * 4 + 63) / 64) * 64);
+    float* simage = (float*)(stable + px * 4);
+    std::memset(ctr, 0, words * 4);
+    std::memcpy(stable, table, px * 16); std::memcpy(simage, accum, px * 16);
+    refglsl_ggx::maxPathIndex = refglsl_beckmann::maxPathIndex = max_depth - 2;
+    if (n_procs < 1) n_procs = 1;
+    std::vector<pid_t> kids;
+    for (int k = 0; k < n_procs; k++) {
+        pid_t pid = fork();
+        if (pid == 0) {
+            for (int f = 0; f < n_frames; f++) {
+                if (model == 1) refglsl_beckmann::render_frame_shared(cam19, w, h, total_light_area, stable, simage, ctr + f);
+                else refglsl_ggx::render_frame_shared(cam19, w, h, total_light_area, stable, simage, ctr + f);
+                __atomic_fetch_add(arrive + f, 1u, __ATOMIC_ACQ_REL);
+                while (__atomic_load_n(arrive + f, __ATOMIC_ACQUIRE) < (uint32_t)n_procs) sched_yield();
+            }
+            _exit(0);
+        }
+        if (pid < 0) break;
+        kids.push_back(pid);
+    }
+    // a child that could not be started or died leaves the others waiting at the frame barrier: stop them all and report it
+    int rc = (int)kids.size() == n_procs ? 0 : -1;
+    size_t left = kids.size();
+    std::vector<bool> done(kids.size(), false);
+    while (left) {
+        if (rc != 0) for (size_t k = 0; k < kids.size(); k++) if (!done[k]) kill(kids[k], SIGKILL);
+        for (size_t k = 0; k < kids.size(); k++) {
+            if (done[k]) continue;
+            int st = 0;
+            pid_t r = waitpid(kids[k], &st, rc != 0 ? 0 : WNOHANG);
+            if (r == 0) continue;
+            done[k] = true; left--;
+            if (r < 0 || !WIFEXITED(st) || WEXITSTATUS(st) != 0) rc = -1;
+        }
+        if (left && rc == 0) usleep(500);
+    }
+    refglsl_ggx::maxPathIndex = refglsl_beckmann::maxPathIndex = 64;
+    if (rc == 0) { std::memcpy(table, stable, px * 16); std::memcpy(accum, simage, px * 16); }
+    munmap(m, bytes);
+    return rc;
+}
+
 // The same with the shader compiled as the SUN_LIGHT build (sunDir, sunRadius: Iterative.comp:89-90)
 void ref_glsl_render_frame_sun(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* accum, int model,
                                const float* sun_dir3, float sun_radius) {

@@ -16,8 +16,11 @@ inline MaterialInstance material_from_texels(vec4 data0, vec4 data1) {
 
 // ---- Iterative.comp's ray generation and light sampling
 #define uniform
-static uint globalNextRay;                                          // the ray counter SSBO, Iterative.comp:150-152
-inline uint atomicAdd(uint& x, uint v) { uint o = x; x += v; return o; }
+static uint g_ray_counter_local;                                    // the ray counter SSBO, Iterative.comp:150-152: this word, or one
+static uint* g_ray_counter = &g_ray_counter_local;                  // in memory shared by several processes (ref_glsl_render_frames_mp)
+#define globalNextRay (*g_ray_counter)
+inline uint atomicAdd(uint& x, uint v) { return __atomic_fetch_add(&x, v, __ATOMIC_RELAXED); }
+static int maxPathIndex = 64;                                       // the literal of `i > 64` (Iterative.comp:295), see oracle/Makefile
 #define globalRayCount int(width * height)                          // Iterative.comp:149
 static uint32_t* rngTable;                                          // `states[]`, Random.glsl (one uvec4 per pixel)
 inline void initRNG(uint ridx) {                                    // Random.glsl:232-237 without the LD-sequence state the path never reads
@@ -99,6 +102,15 @@ static void render_frame(const float* cam19, int w, int h, float total_light_are
     accum.p = image; accum.w = w;
     globalNextRay = 0u;
     shader_main();
+}
+// the same dispatch with the ray counter in shared memory: every process that calls this with the same counter is one more
+// invocation of the persistent shader draining it (pixels are disjoint, so image and RNG table can be shared as they are)
+static void render_frame_shared(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* image, uint* counter) {
+    set_camera(cam19, w, h, total_light_area, table);
+    accum.p = image; accum.w = w;
+    g_ray_counter = counter;
+    shader_main();
+    g_ray_counter = &g_ray_counter_local;
 }
 static void raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {
     set_camera(cam19, w, h, total_light_area, table);

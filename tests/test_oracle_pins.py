@@ -340,6 +340,29 @@ def test_oracle_sun_light_frame_equals_live_reference_main(name):
         assert not np.array_equal(plain, a1)                                   # the branch really is another program
 
 
+@needs_glsl
+@pytest.mark.parametrize("depth", [66, 5])
+def test_reference_main_on_all_cores_is_the_same_frame(depth):
+    """ref_glsl_render_frames_mp (what bench.py's reference arm times): several processes draining one shared ray counter, three
+    accumulated frames, give the bits of the single invocation and of or_render -- also at BASELINE's depth-5 configuration,
+    where the literal of the shader's `i > 64` is the only thing replaced."""
+    from common import get_scene, make_camera
+    from gpupathtracer_b200 import make_rng_table
+    s = get_scene("atrium_small")
+    o = oracle.Oracle(s)
+    w, h = 64, 48
+    cam = make_camera(s.data, w, h, aperture=0.2).as_array()
+    t1 = make_rng_table(w * h, 3); t2 = t1.copy(); t3 = t1.copy()
+    a1 = np.zeros((h, w, 4), np.float32); a2 = a1.copy(); a3 = a1.copy()
+    o.render(cam, w, h, t1, a1, n_frames=3, max_depth=depth, model=0)
+    o.ref_glsl_render_mp(cam, w, h, t2, a2, n_frames=3, max_depth=depth, model=0, n_procs=4)
+    _check_frame_against(a1, t1, a2, t2, 0)
+    if depth == 66:
+        for _ in range(3):
+            o.ref_glsl_render(cam, w, h, t3, a3, 0)
+        _check_frame_against(a3, t3, a2, t2, 0)
+
+
 # ----------------------------------------------------------------------------------- live reference (this container)
 needs_ref = pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref/libref_shim.so not built (no /root/reference)")
 
