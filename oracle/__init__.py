@@ -198,6 +198,34 @@ def ref_glsl_raygen(cam_array, width, height, total_light_area, rng_table, first
     return out
 
 
+def ref_glsl_present(accum, num_samples, exposure=1.68):
+    """Present.frag compiled as C++ (oracle/ref_glsl.cpp) on an (h, w, 4) accumulation image -> (h, w, 3) float32, the colour the
+    fragment shader writes; exposure is the uniform the reference sets to kExposure (Renderer.cpp:18)."""
+    g = C.CDLL(GLSL_SO)
+    g.ref_glsl_present.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]
+    a = np.ascontiguousarray(accum, dtype=np.float32)
+    out = np.zeros(a.shape[:2] + (3,), np.float32)
+    g.ref_glsl_present(_p(a), a.shape[1], a.shape[0], int(num_samples), float(exposure), _p(out))
+    return out
+
+
+def equirect_uv(sample_coords):
+    """or_equirect_uv: the oracle's statement of EquirectangularConverter.frag's coordinate arithmetic, (n, 3) -> (n, 2)."""
+    p = np.ascontiguousarray(sample_coords, dtype=np.float32); out = np.zeros((p.shape[0], 2), np.float32)
+    lib().or_equirect_uv.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    lib().or_equirect_uv(_p(p), p.shape[0], _p(out))
+    return out
+
+
+def ref_glsl_equirect_uv(sample_coords):
+    """SampleSphericalMap(normalize(sampleCoords)) of EquirectangularConverter.frag compiled as C++."""
+    g = C.CDLL(GLSL_SO)
+    g.ref_glsl_equirect_uv.argtypes = [C.c_void_p, C.c_int64, C.c_void_p]
+    p = np.ascontiguousarray(sample_coords, dtype=np.float32); out = np.zeros((p.shape[0], 2), np.float32)
+    g.ref_glsl_equirect_uv(_p(p), p.shape[0], _p(out))
+    return out
+
+
 def ref_glsl_hybrid_taus(state4, n):
     g = C.CDLL(GLSL_SO)
     g.ref_glsl_hybrid_taus.argtypes = [C.c_void_p, C.c_int, C.c_void_p]

@@ -794,6 +794,15 @@ void or_equirect_to_cube(const float* rgba, int width, int height, int size, flo
     });
 }
 
+// the fragment shader's part of the above on explicit sampleCoords (= -position): n x 3 -> n x 2 texture coordinates
+void or_equirect_uv(const float* sample_coords, int64_t n, float* uv) {
+    for (int64_t i = 0; i < n; i++) {
+        V3 d = normalize(ld3(sample_coords + 3 * i));
+        if (d.z == 0.0f) d.z = 0.0f;
+        uv[2 * i] = atan2f(d.z, d.x) * 0.1591f + 0.5f; uv[2 * i + 1] = asinf(d.y) * 0.3183f + 0.5f;
+    }
+}
+
 static OrCounters g_dummy;
 
 void or_trace_closest(const OrScene* s, const float* rays, int64_t n, float* hits, OrCounters* c, int n_threads) {

@@ -31,6 +31,9 @@
  *                           SUN_LIGHT build) vs that source compiled the same way with the harness as its GL runtime
  *                           (ref_glsl_render_frame[_sun]): same bits in the accumulation image and the RNG table, plain and
  *                           textured / cube-map scenes, vectors in tests/golden/frame_glsl_cornell_small.npz
+ *   - or_tonemap            vs Present.frag compiled the same way (ref_glsl_present), tests/golden/present_glsl.npz
+ *   - the coordinate arithmetic of or_equirect_to_cube vs EquirectangularConverter.frag's SampleSphericalMap (ref_glsl_equirect_uv),
+ *                           tests/golden/equirect_glsl.npz
  * The whole shader path is therefore pinned to the reference's code. What remains "parity unpinned" is GL's fixed-function
  * part only: GL_LINEAR / GL_REPEAT filtering behind texture() and the cube-map face selection (or_sample_texture,
  * or_sample_environment, which the compiled shader source calls as its texture units).
@@ -107,6 +110,7 @@ typedef struct OrCounters {
 void or_hybrid_taus(uint32_t state[4], int n, float* out);            /* Random.glsl:47-70 */
 /* shading arithmetic on explicit inputs (material, interaction, NEE evaluation, BSDF sample) in Iterative.comp:236-288's order;
  * in: n x 16 floats, rng_io: n x 4 words (advanced), out: n x 20 floats -- layout in pt_oracle.cpp */
+void or_equirect_uv(const float* sample_coords, int64_t n, float* uv);   /* EquirectangularConverter.frag:9-19 without the fetch */
 void or_sample_texture(const OrScene* s, int index, float u, float v, float* rgba);   /* texture(sampler2D, uv): LINEAR + REPEAT */
 void or_shade_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out);
 /* GenerateLightSample (Iterative.comp:113-147) on explicit inputs: n x 20 floats in, n x 12 out -- layout in pt_oracle.cpp */

@@ -117,6 +117,25 @@ using namespace refglsl;
 }  // namespace refglsl_beckmann_sun
 #undef REFGLSL_SUN
 
+// The present pass (Present.frag): division by the sample count, exposure, Uncharted-2 curve, gamma. The harness is the
+// texture unit behind `directAccum`, the fragment coordinate and the output variable.
+namespace refglsl_present {
+using namespace glm;
+struct AccumTex { const float* p = nullptr; int w = 0; };
+static AccumTex directAccum;                                        // Present.frag:7
+inline vec4 texelFetch(const AccumTex& t, ivec2 px, int) { const float* q = t.p + 4 * ((size_t)px.y * t.w + px.x); return vec4(q[0], q[1], q[2], q[3]); }
+static vec4 gl_FragCoord;
+static vec3 color;                                                  // Present.frag:5
+#define uniform
+#include "ref_glsl_present.inc"
+#undef uniform
+}  // namespace refglsl_present
+
+namespace refglsl_equirect {
+using namespace glm;
+#include "ref_glsl_equirect.inc"
+}  // namespace refglsl_equirect
+
 namespace {
 template <class F>
 void parallel_for(int64_t n, int n_threads, F f) {
@@ -267,6 +286,29 @@ void ref_glsl_render_frame_sun(const float* cam19, int w, int h, float total_lig
                                const float* sun_dir3, float sun_radius) {
     if (model == 1) { refglsl_beckmann_sun::set_sun(sun_dir3, sun_radius); refglsl_beckmann_sun::render_frame(cam19, w, h, total_light_area, table, accum); }
     else { refglsl_ggx_sun::set_sun(sun_dir3, sun_radius); refglsl_ggx_sun::render_frame(cam19, w, h, total_light_area, table, accum); }
+}
+
+// Present.frag over a whole accumulation image (h x w x 4 float sums) -> h x w x 3 floats, the colour the fragment shader writes
+// before the framebuffer quantises it
+void ref_glsl_present(const float* accum, int w, int h, int num_samples, float exposure_uniform, float* rgb) {
+    using namespace refglsl_present;
+    directAccum.p = accum; directAccum.w = w; numSamples = num_samples; exposure = exposure_uniform;
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            gl_FragCoord = glm::vec4(x + 0.5f, y + 0.5f, 0.0f, 1.0f);
+            present_main();
+            float* o = rgb + 3 * ((size_t)y * w + x);
+            o[0] = color.x; o[1] = color.y; o[2] = color.z;
+        }
+}
+
+// EquirectangularConverter.frag's main() without the fetch: where in hdrTex the fragment with these sampleCoords looks
+void ref_glsl_equirect_uv(const float* sample_coords, int64_t n, float* uv) {
+    for (int64_t i = 0; i < n; i++) {
+        glm::vec3 c(sample_coords[3 * i], sample_coords[3 * i + 1], sample_coords[3 * i + 2]);
+        glm::vec2 r = refglsl_equirect::SampleSphericalMap(glm::normalize(c));
+        uv[2 * i] = r.x; uv[2 * i + 1] = r.y;
+    }
 }
 
 void ref_glsl_raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {

@@ -153,8 +153,38 @@ def frame_fixture():
     np.savez_compressed(os.path.join(HERE, "frame_glsl_cornell_small.npz"), cam=cam, size=np.array([w, h]), table0=table0, **out)
 
 
+def present_inputs():
+    g = np.random.default_rng(3)
+    a = np.ones((16, 32, 4), np.float32)
+    a[..., :3] = (g.uniform(0, 1, size=(16, 32, 3)) ** 4 * 400).astype(np.float32)
+    a[0, 0, :3] = 0
+    a[0, 1, :3] = (1e6, 1e-8, 3.0)
+    return a
+
+
+def equirect_inputs(n, seed):
+    p = np.random.default_rng(seed).normal(size=(n, 3)).astype(np.float32)
+    p[:6] = [[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1]]
+    p[6] = [-1, 0.3, 0.0]
+    return p
+
+
+def equirect_fixture():
+    p = equirect_inputs(4096, 1)
+    np.savez_compressed(os.path.join(HERE, "equirect_glsl.npz"), coords=p, uv=oracle.ref_glsl_equirect_uv(p))
+
+
+def present_fixture():
+    """Present.frag compiled as C++ on an HDR accumulation image at three sample counts."""
+    a = present_inputs()
+    np.savez_compressed(os.path.join(HERE, "present_glsl.npz"), accum=a, counts=np.array([1, 7, 64]),
+                        rgb=np.stack([oracle.ref_glsl_present(a, n) for n in (1, 7, 64)]))
+
+
 if __name__ == "__main__":
     shading_fixture()
+    present_fixture()
+    equirect_fixture()
     frame_fixture()
     path_fixture()
     ref_pins()

@@ -204,6 +204,27 @@ def test_oracle_raygen_and_light_sampling_equal_reference_shader_golden():
     assert np.all(z["rays"][:, 8:11] == 1.0) and np.all(z["rays"][:, 11] == np.float32(0.5) / np.float32(s.total_light_area))
 
 
+def test_oracle_present_equals_reference_shader_golden():
+    """tests/golden/present_glsl.npz: what Present.frag (division by the sample count, exposure, Uncharted-2 curve, gamma), compiled
+    as C++ by oracle/Makefile, writes for an HDR accumulation image; or_tonemap gives the same bits."""
+    z = np.load(os.path.join(GOLDEN, "present_glsl.npz"))
+    for n, want in zip(z["counts"], z["rgb"]):
+        got = oracle.tonemap(z["accum"][..., :3], int(n)).reshape(want.shape)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert z["rgb"].max() > 1.0 and z["rgb"].min() < 0.01
+
+
+def test_oracle_equirect_coordinates_equal_reference_shader_golden():
+    """tests/golden/equirect_glsl.npz: SampleSphericalMap(normalize(sampleCoords)) of EquirectangularConverter.frag compiled as C++
+    on random directions and the six axes; the oracle's statement inside or_equirect_to_cube gives the same bits. (Its one
+    deliberate difference is atan(-0, x < 0), which GLSL leaves open: the oracle and the CUDA kernel read -0 as +0.)"""
+    z = np.load(os.path.join(GOLDEN, "equirect_glsl.npz"))
+    got = oracle.equirect_uv(z["coords"])
+    assert np.array_equal(got.view(np.uint32), z["uv"].view(np.uint32))
+    minus_zero = z["coords"][6:7].copy(); minus_zero[0, 2] = -0.0
+    assert np.array_equal(oracle.equirect_uv(minus_zero), got[6:7])
+
+
 needs_glsl = pytest.mark.skipif(not oracle.have_glsl(), reason="oracle/_ref/libref_glsl.so not built (no /root/reference)")
 
 
@@ -361,6 +382,25 @@ def test_reference_main_on_all_cores_is_the_same_frame(depth):
         for _ in range(3):
             o.ref_glsl_render(cam, w, h, t3, a3, 0)
         _check_frame_against(a3, t3, a2, t2, 0)
+
+
+@needs_glsl
+def test_oracle_equirect_coordinates_equal_live_reference_shader():
+    p = np.random.default_rng(5).normal(size=(500000, 3)).astype(np.float32)
+    p[::7, 1] = 0.0
+    p = p[~((p[:, 2] == 0) & np.signbit(p[:, 2]))]
+    assert np.array_equal(oracle.equirect_uv(p).view(np.uint32), oracle.ref_glsl_equirect_uv(p).view(np.uint32))
+
+
+@needs_glsl
+def test_oracle_present_equals_live_reference_shader():
+    g = np.random.default_rng(11)
+    a = np.ones((64, 64, 4), np.float32)
+    a[..., :3] = (g.uniform(0, 1, size=(64, 64, 3)) ** 6 * 5000).astype(np.float32)
+    for n in (1, 3, 1000):
+        want = oracle.ref_glsl_present(a, n)
+        got = oracle.tonemap(a[..., :3], n).reshape(want.shape)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
 
 
 # ----------------------------------------------------------------------------------- live reference (this container)
