@@ -143,10 +143,13 @@ def cpu_reference_run(scene, steps, warmup, w, h, wl, threads=0):
             t0 = time.perf_counter()
             o.ref_glsl_render_mp(cam, w, h, rng2, acc2, n_frames=steps, max_depth=wl["depth"], model=wl["model"], n_procs=procs)
             dt2 = time.perf_counter() - t0
-            same = bool(np.array_equal(rng2, rng)) and bool(np.array_equal(acc2.view(np.uint32), acc.view(np.uint32)))
+            eq = (acc2.view(np.uint32) == acc.view(np.uint32)).all(axis=2)
+            nan_px = np.isnan(acc2).any(axis=2)                       # Beckmann only: NaN through GLSL max(), DESIGN.md section 2
+            same = bool(np.array_equal(rng2, rng)) and bool((eq | nan_px).all())
             info = {"kind": "reference", "what": "the reference's own main() (Iterative.comp:214-307 and callees compiled as C++, "
                     "oracle/_ref/libref_glsl.so; reference GLSL via a GL stack: unavailable on this box), one process per host "
-                    "core sharing the ray counter", "port_value": rays / dt / 1e6, "same_bits_as_port": same}
+                    "core sharing the ray counter", "port_value": rays / dt / 1e6, "same_bits_as_port": same,
+                    "nan_pixels_in_glm_compile": int(nan_px.sum())}
             dt = dt2
         except Exception as e:                                       # never lose the bench line to the baseline leg
             info["reference_leg_error"] = repr(e)
