@@ -9,7 +9,10 @@
 // Extend and shadow are persistent kernels: one resident grid, warps pull 32-ray packets from a
 // device-side cursor. Shade is a streaming kernel that compacts survivors and shadow items with
 // warp ballots + one atomic per warp.
-#define PT_TRACE_THREADS 128   // forcing 12 CTAs/SM (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
+#ifndef PT_TRACE_THREADS
+#define PT_TRACE_THREADS 128   // measured, one box, same warps per SM (profiles/r07_ab_cta_size.log): 64 threads x 18 CTAs 3.26, 128 x 9 3.27,
+#endif                         // 256 x 4 (64 registers) 3.18 Grays/s on the atrium
+// forcing 12 CTAs/SM (40 registers, spills) was measured: atrium +0.4 %, 10M-triangle microbench -37 %
 #ifndef PT_TRACE_MIN_BLOCKS
 #define PT_TRACE_MIN_BLOCKS 9   // caps the traversal kernels at 56 registers (k_extend takes 64 when left alone = 8 CTAs/SM). Measured, one box,
                                 // 8 / 9 / 10 (48 registers, 16-32 B of spills): atrium 3.20 / 3.22 / 3.19 Grays/s, bathroom 2.87 / 2.93 / 2.85,
