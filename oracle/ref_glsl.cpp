@@ -9,10 +9,17 @@
 //                                     622-627  the ifif macros;  634-767 IfIfClosestHit;  769-854 IfIfAnyHit
 //   and, for the shading arithmetic, Constants.glsl 4; Util.glsl 6-11; Random.glsl 42-45, 47-75, 77-79, 155; MIS.glsl 6-8;
 //   Material.glsl 23-37, 46-51, 57-130; Microfacet.glsl 9-193; BSDF.glsl 8-21
-// and applies four syntactic rewrites (parameter qualifiers, swizzle spelling, ^^); see the Makefile. Nothing of the
-// reference is copied into the repository. This file supplies only what the GL runtime supplies to a shader: the buffer
+//   for the path itself, src/shaders/Iterative.comp 20-22, 24-25, 32, 34-82 (RandomLightVertex), 89-110 (the sun disk),
+//   113-147 (GenerateLightSample), 154-172 (RayIndexToMorton), 174-210 (InitRay), 214-307 (main) with Geometry.glsl 92-98,
+//   130-143, 163-182, 315-337 (GetInterpolatedVertex) and Material.glsl 39-54 (ConstructMaterialInstance)
+//   and the two shaders either side of it: Present.frag 8-9, 11, 13-27, 29-37; EquirectangularConverter.frag 9-16
+// and applies syntactic rewrites only (parameter qualifiers, swizzle spelling, ^^, float literal suffixes, two implicit
+// conversions; one literal, the path-length bound of `i > 64`, becomes a variable); see the Makefile. Nothing of the
+// reference is copied into the repository: the extracts are make intermediates, deleted once this file is compiled. This file supplies only what the GL runtime supplies to a shader: the buffer
 // textures (samplerBuffer + texelFetch over plain float arrays), glm as the vector library (the reference's own, extern/glm)
-// and entry points that loop over a ray batch. It exists to PIN oracle/pt_oracle.cpp's hand restatement of the same
+// and entry points that loop over a ray batch; for main() also the material SSBO, bindless handles, the accumulation image,
+// the RNG table and the shared ray counter (ref_glsl_render_frames_mp: one process per core, what bench.py's reference arm
+// times). GL's fixed-function texture filtering is NOT here: the texture units call back into the oracle library. It exists to PIN oracle/pt_oracle.cpp's hand restatement of the same
 // functions: tests/test_oracle_pins.py requires both to agree bit for bit.
 //
 // Two things the shader leaves open and this harness fixes, both outside the arithmetic:
