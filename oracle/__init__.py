@@ -146,9 +146,11 @@ def shade_probe(inputs, rng, model=0):
 
 def ref_glsl_shade_probe(inputs, rng, model=0):
     """The same probe through the reference's own shader functions compiled as C++ (oracle/ref_glsl.cpp); model 1 = the copy
-    whose three model macros (Microfacet.glsl:88-90) point at the file's Beckmann functions."""
+    whose three model macros (Microfacet.glsl:88-90) point at the file's Beckmann functions; model 2 = that copy with scalar
+    min / max meaning IEEE minNum / maxNum (what NVIDIA's FMNMX executes) instead of glm's ternaries. ref_glsl_light_probe and
+    Oracle.ref_glsl_render take the same codes."""
     g = C.CDLL(GLSL_SO)
-    fn = g.ref_glsl_shade_probe_beckmann if model == 1 else g.ref_glsl_shade_probe
+    fn = {0: g.ref_glsl_shade_probe, 1: g.ref_glsl_shade_probe_beckmann, 2: g.ref_glsl_shade_probe_beckmann_maxnum}[model]
     fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     a = np.ascontiguousarray(inputs, dtype=np.float32); r = np.ascontiguousarray(rng, dtype=np.uint32).copy()
     out = np.zeros((a.shape[0], 20), np.float32)

@@ -123,6 +123,16 @@ using namespace refglsl;
 #undef REFGLSL_SHADING
 }  // namespace refglsl_beckmann_sun
 #undef REFGLSL_SUN
+// ... and the Beckmann copy once more with scalar min / max = IEEE minNum / maxNum (see ref_glsl_ns.h): model code 2
+#define REFGLSL_MAXNUM
+namespace refglsl_beckmann_maxnum {
+using namespace glm;
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading_beckmann.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
+}  // namespace refglsl_beckmann_maxnum
+#undef REFGLSL_MAXNUM
 
 // The present pass (Present.frag): division by the sample count, exposure, Uncharted-2 curve, gamma. The harness is the
 // texture unit behind `directAccum`, the fragment coordinate and the output variable.
@@ -200,12 +210,15 @@ void ref_glsl_trace_any(const float* rays, int64_t n, uint8_t* flags, int n_thre
 // The probes of oracle/ref_glsl_ns.h; model 0 = GGX (the macros as shipped), 1 = Beckmann. Single-threaded: `state` is a global.
 void ref_glsl_shade_probe(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_ggx::shade_probe(in, rng_io, n, out); }
 void ref_glsl_shade_probe_beckmann(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_beckmann::shade_probe(in, rng_io, n, out); }
+void ref_glsl_shade_probe_beckmann_maxnum(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_beckmann_maxnum::shade_probe(in, rng_io, n, out); }
 void ref_glsl_bind_lights(const float* lights2, int n_lights, float total_light_area) {
     refglsl_ggx::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann::bind_lights(lights2, n_lights, total_light_area);
     refglsl_ggx_sun::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann_sun::bind_lights(lights2, n_lights, total_light_area);
+    refglsl_beckmann_maxnum::bind_lights(lights2, n_lights, total_light_area);
 }
 void ref_glsl_light_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) {
-    if (model == 1) refglsl_beckmann::light_probe(in, rng_io, n, out); else refglsl_ggx::light_probe(in, rng_io, n, out);
+    if (model == 2) refglsl_beckmann_maxnum::light_probe(in, rng_io, n, out);
+    else if (model == 1) refglsl_beckmann::light_probe(in, rng_io, n, out); else refglsl_ggx::light_probe(in, rng_io, n, out);
 }
 // materials: n x 12 floats as OrScene has them {colour.rgb, albedo texture index (int bits, -1 = none), emission.rgb, -,
 // props.rgb, props texture index}; laid out for the shader as Scene.cpp:296-299 does: [albedo handle, props handle][emission, flag]
@@ -224,13 +237,15 @@ void ref_glsl_bind_materials(const float* materials12, int n, const void* gl_sce
     }
     refglsl_ggx::materialInstance = g_material_ssbo.data(); refglsl_beckmann::materialInstance = g_material_ssbo.data();
     refglsl_ggx_sun::materialInstance = g_material_ssbo.data(); refglsl_beckmann_sun::materialInstance = g_material_ssbo.data();
+    refglsl_beckmann_maxnum::materialInstance = g_material_ssbo.data();
 }
 
 // One dispatch of the reference's main() (Iterative.comp:214-307) over a whole frame: every pixel's path, accumulated into
 // `accum` (h x w x 4 floats, `imageStore`), RNG words written back by freeRNG. One invocation loops over all rays, which the
 // persistent shader allows (any number of invocations share the ray counter). Scene: ref_glsl_bind + _bind_lights + _bind_materials.
 void ref_glsl_render_frame(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* accum, int model) {
-    if (model == 1) refglsl_beckmann::render_frame(cam19, w, h, total_light_area, table, accum);
+    if (model == 2) refglsl_beckmann_maxnum::render_frame(cam19, w, h, total_light_area, table, accum);
+    else if (model == 1) refglsl_beckmann::render_frame(cam19, w, h, total_light_area, table, accum);
     else refglsl_ggx::render_frame(cam19, w, h, total_light_area, table, accum);
 }
 // n_frames dispatches of main() by n_procs processes sharing the ray counter, as the GPU's invocations share the SSBO word:

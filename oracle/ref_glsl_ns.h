@@ -3,6 +3,13 @@
 // Everything between the #include lines is what the GL runtime supplies to the shader (uniforms, SSBOs, atomics) or a
 // probe that calls the shader's functions in the shader's order; the arithmetic is all in the .inc files.
 #undef M_PI
+#ifdef REFGLSL_MAXNUM
+// GLSL leaves max(NaN, x) undefined; glm spells max as a ternary (NaN propagates), NVIDIA's FMNMX, which is what the shader runs
+// on, is IEEE maxNum (the other operand). This build gives scalar min / max the latter meaning and nothing else: the
+// float mode oracle/pt_oracle.h states. (Every min / max of the shading path is scalar.)
+inline float max(float a, float b) { return fmaxf(a, b); }
+inline float min(float a, float b) { return fminf(a, b); }
+#endif
 #include REFGLSL_SHADING
 
 // ConstructMaterialInstance (Material.glsl:39-54) reads two bindless textures; the harness supplies the two texels and runs the

@@ -141,7 +141,7 @@ def frame_fixture():
     cam = make_camera(s.data, w, h, aperture=0.2).as_array()
     table0 = make_rng_table(w * h, 17)
     out = {}
-    for model, key in ((0, "ggx"), (1, "beckmann")):
+    for model, key in ((0, "ggx"), (1, "beckmann"), (2, "beckmann_maxnum")):
         table = table0.copy(); accum = np.zeros((h, w, 4), np.float32)
         o.ref_glsl_render(cam, w, h, table, accum, model)
         out[key], out[key + "_rng"] = accum, table

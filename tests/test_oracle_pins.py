@@ -310,6 +310,9 @@ def test_oracle_frame_equals_reference_main_golden():
         o.render(z["cam"], w, h, table, accum, n_frames=1, max_depth=66, model=model)
         _check_frame_against(accum, table, z[key], z[key + "_rng"], model)
     assert (z["ggx"][..., :3] > 0).any(axis=2).mean() > 0.9
+    table = z["table0"].copy(); accum = np.zeros((h, w, 4), np.float32)                  # Beckmann with max() = IEEE maxNum: exact
+    o.render(z["cam"], w, h, table, accum, n_frames=1, max_depth=66, model=1)
+    _check_frame_against(accum, table, z["beckmann_maxnum"], z["beckmann_maxnum_rng"], 0)
     table = z["table0"].copy(); accum = np.zeros((h, w, 4), np.float32)
     o.render(z["cam"], w, h, table, accum, n_frames=1, max_depth=66, model=0, sun=(z["sun_dir"], float(z["sun_radius"])))
     _check_frame_against(accum, table, z["ggx_sun"], z["ggx_sun_rng"], 0)
@@ -335,6 +338,29 @@ def test_oracle_frame_equals_live_reference_main(name):
                 o.render(cam, w, h, t1, a1, n_frames=1, max_depth=66, model=model)
                 o.ref_glsl_render(cam, w, h, t2, a2, model)
             _check_frame_against(a1, t1, a2, t2, model)
+        # Beckmann with GLSL max() meaning IEEE maxNum, as the hardware the shader runs on executes it: no exception left
+        t1 = make_rng_table(w * h, 11); t2 = t1.copy()
+        a1 = np.zeros((h, w, 4), np.float32); a2 = a1.copy()
+        o.render(cam, w, h, t1, a1, n_frames=1, max_depth=66, model=1)
+        o.ref_glsl_render(cam, w, h, t2, a2, 2)
+        _check_frame_against(a1, t1, a2, t2, 0)
+
+
+@needs_glsl
+def test_beckmann_exception_is_only_the_nan_rule_of_max():
+    """The reference's Beckmann source built with scalar min / max = IEEE minNum / maxNum (oracle/ref_glsl_ns.h REFGLSL_MAXNUM;
+    the stated float mode, what NVIDIA's FMNMX executes for GLSL max) instead of glm's NaN-propagating ternaries: the shading
+    probe (200 000 cases) and the light-sampling probe agree with the oracle bit for bit, with no exception."""
+    from common import get_scene
+    a, rng = oracle.shade_probe_inputs(200000, 3)
+    got, grng = oracle.shade_probe(a, rng, 1)
+    want, wrng = oracle.ref_glsl_shade_probe(a, rng, 2)
+    assert _same_bits_or_both_nan(got, want).all() and np.array_equal(grng, wrng)
+    s = get_scene("atrium_small")
+    la, lrng = oracle.light_probe_inputs(s, 100000, 7)
+    got, grng = oracle.Oracle(s).light_probe(la, lrng, 1)
+    want, wrng = oracle.ref_glsl_light_probe(s, la, lrng, 2)
+    assert _same_bits_or_both_nan(got, want).all() and np.array_equal(grng, wrng)
 
 
 @needs_glsl
