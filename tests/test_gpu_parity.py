@@ -167,6 +167,28 @@ def test_reset_and_accumulate():
     r.CleanUp()
 
 
+def test_present_matches_present_frag():
+    """k_resolve against Present.frag (compiled as C++ when oracle/_ref travels, else the oracle's restatement, which is held to
+    it bit for bit): the float image to a few ulp (CUDA's powf against glibc's), the 8-bit image to one step at rounding
+    boundaries. Everything before the pow is IEEE arithmetic without FMA on both sides."""
+    s = get_scene("cornell")
+    w, h = 64, 48
+    cam = make_camera(s.data, w, h)
+    r = _renderer(s, w, h, max_depth=5, seed=5)
+    r.RenderFrame(cam, 3)
+    a = r.DownloadAccum()
+    n = r.GetNumSamples()
+    got = r.Present()
+    got8 = r.Present(as_u8=True)
+    r.CleanUp()
+    assert n == 3 and np.isfinite(a).all() and (a[..., :3] > 0).any()
+    want = oracle.ref_glsl_present(a, n) if oracle.have_glsl() else oracle.tonemap(a[..., :3], n).reshape(h, w, 3)
+    np.testing.assert_allclose(got, want, rtol=1e-5, atol=1e-7)
+    want8 = np.floor(np.clip(want, 0.0, 1.0) * np.float32(255.0) + np.float32(0.5)).astype(np.int32)
+    d = np.abs(got8.astype(np.int32) - want8)
+    assert d.max() <= 1 and (d == 0).mean() > 0.999
+
+
 def test_slices_do_not_change_the_image():
     """pt_config.n_slices only changes scheduling (pixel-disjoint slices on concurrent streams): the accumulation
     buffer and the RNG table must be BIT-identical for 1, 3 and 4 slices, and ragged slice sizes must work."""
