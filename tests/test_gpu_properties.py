@@ -199,3 +199,21 @@ def test_ray_ordering_does_not_change_any_result(monkeypatch):
         assert np.array_equal(out[mode][0].view(np.uint32), want.view(np.uint32))
         assert np.array_equal(out[mode][1], wflag)
     assert out["1"][2] == out["-1"][2] + 8                       # 4 binning kernels per ordered launch
+
+
+def test_device_seeded_rng_table_meets_hybrid_taus_requirements():
+    """pt_seed_rng (k_seed_rng) stands in for Renderer.cpp:545-553 (uniform_int_distribution(129, UINT32_MAX) per word): every
+    word >= 129 (the Tausworthe lanes need > 128), states distinct per pixel, the same table for the same seed and another
+    one for another seed, words spread over the whole range."""
+    from common import get_scene
+    s = get_scene("cornell_small")
+    tabs = []
+    for seed in (5, 5, 6):
+        r = Renderer().Initialize(96, 64, s, max_depth=5, seed=seed)
+        tabs.append(r.GetRNG())
+        r.CleanUp()
+    t = tabs[0]
+    assert t.shape == (96 * 64, 4) and t.dtype == np.uint32 and (t >= 129).all()
+    assert np.array_equal(tabs[0], tabs[1]) and not np.array_equal(tabs[0], tabs[2])
+    assert len({tuple(row) for row in t}) == t.shape[0]
+    assert abs(float(t.mean()) / 2**32 - 0.5) < 0.01 and (t >> 31).mean() > 0.45
