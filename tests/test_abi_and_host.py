@@ -152,3 +152,14 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["sample"]
     assert d["e2e"] == {"value": d["value"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["steps"] == 1 and d["warmup"] == 0 and d["n_gpus"] == 1 and d["vs_baseline"] is None
+
+
+def test_no_reference_text_is_left_in_the_tree():
+    """oracle/Makefile extracts line ranges of the reference at build time; they are make intermediates and must be gone once
+    the checker libraries are linked: oracle/_ref holds built libraries only."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    d = os.path.join(root, "oracle", "_ref")
+    if not os.path.isdir(d):
+        pytest.skip("oracle/_ref not built")
+    left = [f for f in os.listdir(d) if not f.endswith(".so")]
+    assert left == [], left
