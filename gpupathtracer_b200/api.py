@@ -15,6 +15,7 @@ LIB_PATH = os.environ.get("PT_LIB_PATH") or os.path.join(_HERE, "libb200pt.so") 
 PT_OK = 0
 PT_MICROFACET_GGX, PT_MICROFACET_BECKMANN = 0, 1
 PT_BVH_REFERENCE, PT_BVH_WIDE, PT_BVH_WIDE4 = 0, 1, 2
+PT_PARITY_LIBM = 1
 REFERENCE_MAX_DEPTH = 66      # `i > 64`, Iterative.comp:293
 
 
@@ -27,7 +28,7 @@ class PtError(RuntimeError):
 class pt_config(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("max_depth", C.c_int32),
                 ("microfacet_model", C.c_int32), ("device", C.c_int32), ("bvh_layout", C.c_int32),
-                ("n_slices", C.c_int32), ("sun_light", C.c_int32), ("trace_null_shadow", C.c_int32), ("reserved", C.c_int32 * 3)]
+                ("n_slices", C.c_int32), ("sun_light", C.c_int32), ("trace_null_shadow", C.c_int32), ("parity_flags", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class pt_camera(C.Structure):
@@ -125,6 +126,7 @@ SYMBOLS = [
     ("pt_trace_any_device", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_raygen_probe", C.c_int, [_P, C.c_int64, C.c_int64, _P]),
     ("pt_trace_primary_async", C.c_int, [_P, _P]),
+    ("pt_parity_libm_probe", C.c_int, [_P, C.c_int32, _P, _P, C.c_int64, _P]),
     ("pt_get_counters", C.c_int, [_P, C.POINTER(pt_counters)]),
     ("pt_last_device_ms", C.c_float, [_P]),
     ("pt_set_stage_timing", C.c_int, [_P, C.c_int]),
@@ -372,10 +374,10 @@ class Renderer:
     # -- Renderer::Initialize, Renderer.cpp:448-636
     def Initialize(self, width, height, scene, max_depth=REFERENCE_MAX_DEPTH, microfacet_model=PT_MICROFACET_GGX,
                    device=0, rng_state=None, seed=None, bvh="given", n_slices=0, bvh_layout=PT_BVH_REFERENCE, sun_light=False,
-                   trace_null_shadow=False):
+                   trace_null_shadow=False, parity_libm=False):
         cfg = pt_config(width=width, height=height, max_depth=max_depth, microfacet_model=microfacet_model,
                         device=device, bvh_layout=bvh_layout, n_slices=n_slices, sun_light=1 if sun_light else 0,
-                        trace_null_shadow=1 if trace_null_shadow else 0)
+                        trace_null_shadow=1 if trace_null_shadow else 0, parity_flags=PT_PARITY_LIBM if parity_libm else 0)
         ctx = C.c_void_p()
         _check(self.lib.pt_create(C.byref(cfg), C.byref(ctx)))
         self.ctx = ctx
@@ -555,6 +557,15 @@ class Renderer:
     def RaygenProbe(self, first, n):
         out = np.zeros((n, 12), dtype=np.float32)
         _check(self.lib.pt_raygen_probe(self.ctx, first, n, _ptr(out)))
+        return out
+
+    def ParityLibmProbe(self, fn, x, y=None):
+        """pt_parity_libm.h on the device: fn in ('sin', 'cos', 'log', 'exp', 'pow')."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        yy = np.ascontiguousarray(y, dtype=np.float32) if y is not None else None
+        out = np.zeros_like(x)
+        _check(self.lib.pt_parity_libm_probe(self.ctx, ["sin", "cos", "log", "exp", "pow"].index(fn), _ptr(x),
+                                             _ptr(yy) if yy is not None else None, x.size, _ptr(out)))
         return out
 
     def Counters(self):

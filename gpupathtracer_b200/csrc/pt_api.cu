@@ -11,6 +11,8 @@
 #include <vector>
 #include <chrono>
 #include <cstdlib>
+#include <climits>
+#include <exception>
 
 using namespace pt;
 
@@ -80,6 +82,7 @@ struct pt_context {
     std::vector<float> h_tris;
     HostBvh h_bvh;
     std::vector<pt_material> h_mats;
+    std::vector<pt_light> h_lights;
 
     DevBuf<float4> d_tris;
     DevBuf<BvhPair> d_pairs;
@@ -347,9 +350,29 @@ static int upload_leaf_stream(pt_context* c) {
     return PT_OK;
 }
 
+// The tables index each other on the device without bounds checks (make_material: matId >> 1; random_light_vertex: the light
+// entry's triangle), so inconsistent uploads are refused here, whichever table arrives last.
+static int check_mat_ids(const float* tris, int64_t n, size_t n_mats, const char* who) {
+    if (!n_mats) return PT_OK;
+    for (int64_t i = 0; i < n; i++) {
+        uint32_t id; memcpy(&id, tris + 20 * i + 18, 4);
+        if ((size_t)(id >> 1) >= n_mats) return fail(PT_ERR_INVALID, "%s: triangle %lld has matId %u, but there are %zu materials (matId = 2 * k, Scene.cpp:153-158)", who, (long long)i, id, n_mats);
+    }
+    return PT_OK;
+}
+static int check_light_tris(const pt_light* lights, int32_t n, int64_t n_tris, const char* who) {
+    if (n_tris <= 0) return PT_OK;
+    for (int32_t i = 0; i < n; i++)
+        if ((int64_t)lights[i].tri_index >= n_tris) return fail(PT_ERR_INVALID, "%s: light %d names triangle %u of %lld", who, i, lights[i].tri_index, (long long)n_tris);
+    return PT_OK;
+}
+
 int pt_set_triangles(pt_context* c, const float* tris, int64_t n) {
     if (!c || !tris || n <= 0) return fail(PT_ERR_INVALID, "pt_set_triangles: bad argument");
     if (n >= (1ll << 30)) return fail(PT_ERR_LIMIT, "pt_set_triangles: too many triangles");
+    int rc = check_mat_ids(tris, n, c->h_mats.size(), "pt_set_triangles");
+    if (rc == PT_OK) rc = check_light_tris(c->h_lights.data(), (int32_t)c->h_lights.size(), n, "pt_set_triangles");
+    if (rc != PT_OK) return rc;
     CK(cudaSetDevice(c->cfg.device));
     invalidate_graphs(c);
     c->h_tris.assign(tris, tris + 20 * n);
@@ -361,39 +384,58 @@ int pt_set_triangles(pt_context* c, const float* tris, int64_t n) {
 
 int pt_set_materials(pt_context* c, const pt_material* mats, int32_t n_mats, const pt_texture* tex, int32_t n_tex) {
     if (!c || !mats || n_mats <= 0 || n_tex < 0 || (n_tex > 0 && !tex)) return fail(PT_ERR_INVALID, "pt_set_materials: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
     static_assert(sizeof(pt_material) == sizeof(MaterialRec), "material record layout");
-    invalidate_graphs(c);
-    c->h_mats.assign(mats, mats + n_mats);
-    CK(c->d_mats.alloc(n_mats));
-    CK(cudaMemcpyAsync(c->d_mats.p, mats, sizeof(pt_material) * n_mats, cudaMemcpyHostToDevice, c->stream));
-    for (float4* t : c->d_texels) cudaFree(t);
-    c->d_texels.clear();
-    std::vector<TextureRec> recs(n_tex);
-    for (int i = 0; i < n_tex; i++) {
+    // everything is validated and the new texture set is built beside the old one; the context changes only on success
+    for (int i = 0; i < n_tex; i++)
         if (tex[i].width <= 0 || tex[i].height <= 0 || !tex[i].rgba) return fail(PT_ERR_INVALID, "pt_set_materials: texture %d invalid", i);
+    int rc = check_mat_ids(c->h_tris.data(), (int64_t)(c->h_tris.size() / 20), (size_t)n_mats, "pt_set_materials");
+    if (rc != PT_OK) return rc;
+    CK(cudaSetDevice(c->cfg.device));
+    std::vector<float4*> texels;
+    std::vector<TextureRec> recs(n_tex);
+    DevBuf<MaterialRec> mats_new; DevBuf<TextureRec> texrec_new;
+    cudaError_t e = mats_new.alloc(n_mats);
+    if (e == cudaSuccess) e = texrec_new.alloc(n_tex > 0 ? n_tex : 1);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(mats_new.p, mats, sizeof(pt_material) * n_mats, cudaMemcpyHostToDevice, c->stream);
+    for (int i = 0; i < n_tex && e == cudaSuccess; i++) {
         size_t cnt = (size_t)tex[i].width * tex[i].height;
         float4* d = nullptr;
-        CK(cudaMalloc((void**)&d, cnt * sizeof(float4)));
-        c->d_texels.push_back(d);
-        CK(cudaMemcpyAsync(d, tex[i].rgba, cnt * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+        e = cudaMalloc((void**)&d, cnt * sizeof(float4));
+        if (e != cudaSuccess) break;
+        texels.push_back(d);
+        e = cudaMemcpyAsync(d, tex[i].rgba, cnt * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
         recs[i].width = tex[i].width; recs[i].height = tex[i].height; recs[i].texels = d;
     }
-    CK(c->d_texrec.alloc(n_tex > 0 ? n_tex : 1));
-    if (n_tex > 0) CK(cudaMemcpyAsync(c->d_texrec.p, recs.data(), sizeof(TextureRec) * n_tex, cudaMemcpyHostToDevice, c->stream));
+    if (e == cudaSuccess && n_tex > 0) e = cudaMemcpyAsync(texrec_new.p, recs.data(), sizeof(TextureRec) * n_tex, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) {
+        cudaStreamSynchronize(c->stream);
+        for (float4* t : texels) cudaFree(t);
+        mats_new.release(); texrec_new.release();
+        return fail(PT_ERR_CUDA, "pt_set_materials: %s (the previous materials stay in place)", cudaGetErrorString(e));
+    }
+    invalidate_graphs(c);
+    CK(cudaDeviceSynchronize());                                 // nothing in flight reads the old set
+    for (float4* t : c->d_texels) cudaFree(t);
+    c->d_mats.release(); c->d_texrec.release();
+    c->d_texels.swap(texels);
+    c->d_mats = mats_new; c->d_texrec = texrec_new;              // ownership moves (DevBuf is a plain pointer + count)
+    c->h_mats.assign(mats, mats + n_mats);
     c->n_textures = n_tex;
-    CK(cudaStreamSynchronize(c->stream));
     return PT_OK;
 }
 
 int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_light_area) {
     if (!c || !lights || n <= 0) return fail(PT_ERR_INVALID, "pt_set_lights: a scene needs at least one emissive triangle (Iterative.comp:42-61)");
+    int rc = check_light_tris(lights, n, (int64_t)(c->h_tris.size() / 20), "pt_set_lights");
+    if (rc != PT_OK) return rc;
     CK(cudaSetDevice(c->cfg.device));
     static_assert(sizeof(pt_light) == sizeof(float2), "light record layout");
     invalidate_graphs(c);
     CK(c->d_lights.alloc(n));
     CK(cudaMemcpyAsync(c->d_lights.p, lights, sizeof(pt_light) * n, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    c->h_lights.assign(lights, lights + n);
     c->n_lights = n; c->total_light_area = total_light_area;
     return PT_OK;
 }
@@ -458,7 +500,13 @@ int pt_download_environment(pt_context* c, float* faces) {
 }
 
 // LoadEnvironmnet (Renderer.cpp:236-323): "GENERATE COLOR x" | *.hdr (equirect -> 1024^2 cubemap) | text file naming six faces
+static int load_environment_impl(pt_context* c, const char* args);
 int pt_load_environment(pt_context* c, const char* args) {
+    // image headers drive allocations: std::bad_alloc / length_error from a damaged file must not cross the C ABI
+    try { return load_environment_impl(c, args); }
+    catch (const std::exception& e) { return fail(PT_ERR_LIMIT, "pt_load_environment: %s", e.what()); }
+}
+static int load_environment_impl(pt_context* c, const char* args) {
     if (!c || !args) return fail(PT_ERR_INVALID, "pt_load_environment: bad argument");
     std::string a = args;
     std::string ext = a.substr(a.find_last_of('.') + 1);       // npos + 1 == 0: the whole string, as in the reference
@@ -660,7 +708,12 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
 }
 
 // Renderer::Initialize's scene half (Renderer.cpp:519-523 -> Scene::LoadScene, Scene.cpp:233-357) from files
+static int load_scene_impl(pt_context* c, const char* scene_path, const char* environment, pt_bvh_stats* stats);
 int pt_load_scene(pt_context* c, const char* scene_path, const char* environment, pt_bvh_stats* stats) {
+    try { return load_scene_impl(c, scene_path, environment, stats); }
+    catch (const std::exception& e) { return fail(PT_ERR_LIMIT, "pt_load_scene: %s", e.what()); }
+}
+static int load_scene_impl(pt_context* c, const char* scene_path, const char* environment, pt_bvh_stats* stats) {
     if (!c || !scene_path) return fail(PT_ERR_INVALID, "pt_load_scene: bad argument");
     std::string path(scene_path);
     size_t dot = path.find_last_of('.');
@@ -752,6 +805,9 @@ int pt_get_rng(pt_context* c, uint32_t* state4) {
     return PT_OK;
 }
 
+// The persistent kernels hand out ray indices from an int cursor that every resident warp bumps by up to 32 once more after
+// the batch is exhausted (148 SMs x 9 CTAs x 4 warps x 32 = 170 k on a B200): batches stop well short of INT_MAX.
+static const int64_t kMaxBatchRays = 1ll << 30;
 static const int64_t kHostChunk = 1 << 21;      // host batches are traced in chunks of this many rays (pipelined copies)
 static const int64_t kRayOrderMin = 1 << 16;    // smaller batches are not worth three extra launches
 // Decide whether a batch is traced in binned order and, if so, enqueue the binning; nullptr = natural order.
@@ -792,6 +848,7 @@ static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, in
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.slice_first = first; p.slice_count = count < 0 ? c->cfg.width * c->cfg.height : count;
     p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model; p.sun = c->cfg.sun_light ? 1 : 0; p.trace_null = c->cfg.trace_null_shadow ? 1 : 0;
+    p.plibm = (c->cfg.parity_flags & PT_PARITY_LIBM) ? 1 : 0;
     p.rng_table = c->d_rng.p; p.accum = c->d_accum;
     const size_t o = (size_t)first;                              // the slice's sub-range of every per-path array
     for (int q = 0; q < 2; q++) {
@@ -981,7 +1038,7 @@ int pt_resolve(pt_context* c, uint32_t num_samples, float* rgb_f32, uint8_t* rgb
     float* d_f = nullptr; unsigned char* d_u = nullptr;
     if (rgb_f32) { CK(c->d_resolve_f32.alloc(npx * 3)); d_f = c->d_resolve_f32.p; }
     if (rgb_u8) { CK(c->d_resolve_u8.alloc(npx * 3)); d_u = c->d_resolve_u8.p; }
-    launch_resolve(c->d_accum, (long long)npx, num_samples, d_f, d_u, c->stream);
+    launch_resolve(c->d_accum, (long long)npx, num_samples, d_f, d_u, c->stream, (c->cfg.parity_flags & PT_PARITY_LIBM) != 0);
     c->counters.kernel_launches++;
     CK(cudaGetLastError());
     if (rgb_f32) CK(cudaMemcpyAsync(rgb_f32, d_f, npx * 12, cudaMemcpyDeviceToHost, c->stream));
@@ -997,7 +1054,7 @@ int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) 
     const int k = c->present_turn; c->present_turn ^= 1;
     CK(c->d_present[k].alloc(npx * 3));
     CK(cudaStreamWaitEvent(c->stream, c->ev_copied[k], 0));          // the copy that last used this buffer (no-op the first time)
-    launch_resolve(c->d_accum, (long long)npx, num_samples, nullptr, c->d_present[k].p, c->stream);
+    launch_resolve(c->d_accum, (long long)npx, num_samples, nullptr, c->d_present[k].p, c->stream, (c->cfg.parity_flags & PT_PARITY_LIBM) != 0);
     c->counters.kernel_launches++;
     CK(cudaGetLastError());
     CK(cudaEventRecord(c->ev_resolved, c->stream));
@@ -1059,7 +1116,7 @@ int pt_save_screenshot(pt_context* c, const char* path) {
 }
 
 int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* d_hits) {
-    if (!c || !d_rays || !d_hits || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_closest_device: bad argument");
+    if (!c || !d_rays || !d_hits || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_closest_device: bad argument");
     CK(cudaSetDevice(c->cfg.device));
     int rc = check_scene(c, "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
@@ -1074,7 +1131,7 @@ int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* 
     return PT_OK;
 }
 int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_flags) {
-    if (!c || !d_rays || !d_flags || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_any_device: bad argument");
+    if (!c || !d_rays || !d_flags || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_any_device: bad argument");
     CK(cudaSetDevice(c->cfg.device));
     int rc = check_scene(c, "pt_trace_any", false);
     if (rc != PT_OK) return rc;
@@ -1147,12 +1204,12 @@ static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, si
 }
 
 int pt_trace_closest(pt_context* c, const float* rays, int64_t n, float* hits) {
-    if (!c || !rays || !hits || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_closest: bad argument");
+    if (!c || !rays || !hits || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_closest: bad argument");
     if (n == 0) return PT_OK;
     return trace_host(c, rays, n, hits, 16, false);
 }
 int pt_trace_any(pt_context* c, const float* rays, int64_t n, uint8_t* flags) {
-    if (!c || !rays || !flags || n < 0 || n > 0x7fffff00ll) return fail(PT_ERR_INVALID, "pt_trace_any: bad argument");
+    if (!c || !rays || !flags || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_any: bad argument");
     if (n == 0) return PT_OK;
     return trace_host(c, rays, n, flags, 1, true);
 }
@@ -1171,6 +1228,24 @@ int pt_raygen_probe(pt_context* c, int64_t first, int64_t n, float* out) {
     CK(cudaMemcpyAsync(out, d, 48 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     cudaFree(d);
+    return PT_OK;
+}
+
+int pt_parity_libm_probe(pt_context* c, int32_t fn, const float* x, const float* y, int64_t n, float* out) {
+    if (!c || !x || !out || n < 0 || fn < 0 || fn > 4 || (fn == 4 && !y)) return fail(PT_ERR_INVALID, "pt_parity_libm_probe: bad argument");
+    if (n == 0) return PT_OK;
+    CK(cudaSetDevice(c->cfg.device));
+    DevBuf<float> dx, dy, dout;
+    CK(dx.alloc((size_t)n)); CK(dy.alloc((size_t)n)); CK(dout.alloc((size_t)n));
+    CK(cudaMemcpyAsync(dx.p, x, 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    if (y) CK(cudaMemcpyAsync(dy.p, y, 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    launch_plibm_probe(fn, dx.p, dy.p, n, dout.p, c->stream);
+    c->counters.kernel_launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dout.p, 4 * (size_t)n, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    dx.release(); dy.release(); dout.release();
+    if (e != cudaSuccess) return fail(PT_ERR_CUDA, "pt_parity_libm_probe: %s", cudaGetErrorString(e));
     return PT_OK;
 }
 

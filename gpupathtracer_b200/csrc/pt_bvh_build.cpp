@@ -34,7 +34,7 @@ constexpr int kMaxBins = 64;
 // tuning-run overrides (read per build): PT_BVH_CI = intersection cost of the SAH model, PT_BVH_BINS = bins per axis
 static float kCostIntersection = 5.33f;
 static int kBins = 16;
-constexpr int kMaxDepth = 56;          // the traversal stack holds 64 entries
+constexpr int kMaxDepth = 56;          // the traversal stack holds PT_MAX_TREE_DEPTH (96) entries
 constexpr float kAlpha = 1e-5f;
 constexpr int kParallelThreshold = 8192;
 
@@ -320,7 +320,11 @@ struct Flat {
     int32_t emit_leaf(const Node* nd) {
         int32_t off = (int32_t)refs.size();
         for (int idx : nd->leaf) refs.push_back(idx);
-        refs.back() = -refs.back();                    // end-of-leaf marker, BVH.cpp:2117
+        // The end-of-leaf marker is the sign of the last entry (BVH.cpp:2117) and triangle 0 cannot carry it (-0 == 0): the
+        // reference's traversal then runs on into the next leaf. Same results, wasted triangle tests -- so triangle 0 is kept
+        // out of the last slot whenever the leaf has another entry (a one-entry leaf of triangle 0 keeps the quirk).
+        if (refs.back() == 0 && nd->leaf.size() > 1) std::swap(refs[refs.size() - 1], refs[refs.size() - 2]);
+        refs.back() = -refs.back();
         n_leaves++;
         cost += kCostIntersection * nd->box.area() * (double)nd->leaf.size();
         return -off;

@@ -369,13 +369,15 @@ __global__ void k_emit(const int* __restrict__ vals, int n, const int2* __restri
     if (i >= n) return;
     refs[i] = -vals[i];
     if (leaf) {
-        // what upload_leaf_stream does on the host: intersection record of the leaf's triangle; the end-of-leaf marker is
-        // the sign of the reference-list entry, which triangle 0 cannot carry (-0 == 0, BVH.cpp:2117)
+        // what upload_leaf_stream does on the host: intersection record of the leaf's triangle. The stream marks the end of a
+        // leaf with ~index, which triangle 0 can carry too -- unlike the reference list's -0 == 0 (BVH.cpp:2117), whose
+        // run-on into the next leaf costs triangle tests and changes no result. (A tree read back and re-installed through
+        // pt_set_bvh gets the copied-marker behaviour of the reference again.)
         const int tri = vals[i];
         const float4* t = tris + 5 * (size_t)tri;
         float4 t0 = t[0], t1 = t[1], t2 = t[2];
         leaf[i].r[0] = t0; leaf[i].r[1] = t1;
-        leaf[i].r[2] = make_float4(t2.x, __int_as_float(tri > 0 ? ~tri : tri), 0.0f, 0.0f);
+        leaf[i].r[2] = make_float4(t2.x, __int_as_float(~tri), 0.0f, 0.0f);
         leaf[i].r[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
     if (i >= n - 1) return;

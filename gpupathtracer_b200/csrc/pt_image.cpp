@@ -167,7 +167,8 @@ struct Huffman {
     }
 };
 
-bool inflate_zlib(const unsigned char* data, size_t n, std::vector<unsigned char>& out) {
+// max_out: the decoder stops with an error once more than this has been produced (a PNG knows its raw size: no zip bombs)
+bool inflate_zlib(const unsigned char* data, size_t n, std::vector<unsigned char>& out, size_t max_out = (size_t)-1) {
     if (n < 2 || (data[0] & 15) != 8 || ((data[0] << 8) | data[1]) % 31 != 0 || (data[1] & 32)) return false;
     BitReader br{data + 2, n - 2};
     static const uint16_t lbase[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
@@ -183,6 +184,7 @@ bool inflate_zlib(const unsigned char* data, size_t n, std::vector<unsigned char
             unsigned len = br.p[br.pos] | (br.p[br.pos + 1] << 8), nlen = br.p[br.pos + 2] | (br.p[br.pos + 3] << 8);
             br.pos += 4;
             if ((len ^ 0xffffu) != nlen || br.pos + len > br.n) return false;
+            if (out.size() + len > max_out) return false;
             out.insert(out.end(), br.p + br.pos, br.p + br.pos + len);
             br.pos += len;
         } else if (type == 1 || type == 2) {
@@ -225,7 +227,7 @@ bool inflate_zlib(const unsigned char* data, size_t n, std::vector<unsigned char
             for (;;) {
                 int sym = lit.decode(br);
                 if (sym < 0) return false;
-                if (sym < 256) out.push_back((unsigned char)sym);
+                if (sym < 256) { if (out.size() >= max_out) return false; out.push_back((unsigned char)sym); }
                 else if (sym == 256) break;
                 else {
                     sym -= 257;
@@ -234,7 +236,7 @@ bool inflate_zlib(const unsigned char* data, size_t n, std::vector<unsigned char
                     int ds = dist.decode(br);
                     if (ds < 0 || ds >= 30) return false;
                     size_t d = dbase[ds] + (size_t)br.bits(dext[ds]);
-                    if (br.bad || d > out.size()) return false;
+                    if (br.bad || d > out.size() || out.size() + (size_t)len > max_out) return false;
                     size_t from = out.size() - d;
                     for (int k = 0; k < len; k++) out.push_back(out[from + k]);
                 }
@@ -287,7 +289,7 @@ bool decode_png_rgba8(const std::vector<unsigned char>& b, int& w, int& h, std::
         if (is("IHDR")) {
             if (len != 13) return false;
             w = (int)be32(d); h = (int)be32(d + 4); depth = d[8]; color = d[9]; interlace = d[12];
-            if (w <= 0 || h <= 0 || w > (1 << 24) || h > (1 << 24) || d[10] || d[11] || interlace > 1) return false;
+            if (w <= 0 || h <= 0 || w > (1 << 24) || h > (1 << 24) || (double)w * h > 1.0e9 || d[10] || d[11] || interlace > 1) return false;
             if (depth != 1 && depth != 2 && depth != 4 && depth != 8 && depth != 16) return false;
             if (color != 0 && color != 2 && color != 3 && color != 4 && color != 6) return false;
             if (color == 3 && depth == 16) return false;
@@ -306,8 +308,10 @@ bool decode_png_rgba8(const std::vector<unsigned char>& b, int& w, int& h, std::
     const int channels = color == 0 ? 1 : color == 2 ? 3 : color == 3 ? 1 : color == 4 ? 2 : 4;
     const int bits_pp = channels * depth, bpp = std::max(1, bits_pp / 8);
     std::vector<unsigned char> raw;
-    raw.reserve(((size_t)w * bits_pp / 8 + 2) * h);
-    if (!inflate_zlib(idat.data(), idat.size(), raw)) return false;
+    // filter byte + packed row for every row; the seven Adam7 passes together add at most 7 more bytes per row and 8 short rows
+    const size_t raw_max = ((size_t)w * bits_pp / 8 + 9) * ((size_t)h + 8);
+    raw.reserve(std::min(raw_max, idat.size() * 64 + 4096));
+    if (!inflate_zlib(idat.data(), idat.size(), raw, raw_max)) return false;
     rgba.assign((size_t)w * h * 4, 255);
     const unsigned maxv = depth == 16 ? 65535u : (1u << depth) - 1u;
     auto emit = [&](int x, int y, const unsigned* s) {           // s: channel samples at the file's bit depth
@@ -929,7 +933,12 @@ bool load_ldr_as_hdr_rgba32f(const std::string& path, int& w, int& h, std::vecto
 
 }  // namespace pt
 
+static int image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba);
 extern "C" int pt_image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba) {
+    try { return image_load_hdr(path, width, height, rgba); }
+    catch (const std::exception& e) { pt::set_last_error((std::string("pt_image_load_hdr: ") + e.what()).c_str()); return PT_ERR_LIMIT; }
+}
+static int image_load_hdr(const char* path, int32_t* width, int32_t* height, float** rgba) {
     if (!path || !width || !height || !rgba) return PT_ERR_INVALID;
     int w = 0, h = 0; std::vector<float> px; std::string err;
     // stbi_loadf: Radiance files as they are, anything else through the 8-bit decoders and the gamma-2.2 expansion

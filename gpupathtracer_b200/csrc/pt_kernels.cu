@@ -184,6 +184,7 @@ void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsign
 }
 
 // ------------------------------------------------------------------ ray generation
+template <bool PL>
 __global__ void __launch_bounds__(PT_STREAM_THREADS)
 k_raygen(FrameParams p) {
     const int n = p.slice_count;
@@ -196,7 +197,7 @@ k_raygen(FrameParams p) {
         uint4 st = p.rng_table[pix];                         // initRNG, Random.glsl:232-237
         Rng rng; rng.x = st.x; rng.y = st.y; rng.z = st.z; rng.w = st.w;
         V3 o, d;
-        init_ray(*p.cam, p.width, p.height, px, py, rng, o, d);
+        init_ray<PL>(*p.cam, p.width, p.height, px, py, rng, o, d);
         q.q0[i] = f4(o, 1.0f);
         q.q1[i] = f4(d, 1.0f);
         q.q2[i] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(pix));
@@ -205,6 +206,7 @@ k_raygen(FrameParams p) {
     }
 }
 
+template <bool PL>
 __global__ void k_raygen_probe(FrameParams p, long long first, long long n, float4* out3) {
     long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (k >= n) return;
@@ -214,7 +216,7 @@ __global__ void k_raygen_probe(FrameParams p, long long first, long long n, floa
     uint4 st = p.rng_table[pix];
     Rng rng; rng.x = st.x; rng.y = st.y; rng.z = st.z; rng.w = st.w;
     V3 o, d;
-    init_ray(*p.cam, p.width, p.height, px, py, rng, o, d);
+    init_ray<PL>(*p.cam, p.width, p.height, px, py, rng, o, d);
     p.rng_table[pix] = make_uint4(rng.x, rng.y, rng.z, rng.w);
     out3[3 * k + 0] = make_float4(__int_as_float(px), __int_as_float(py), o.x, o.y);
     out3[3 * k + 1] = make_float4(o.z, d.x, d.y, d.z);
@@ -325,7 +327,7 @@ k_shade(FrameParams p, int bounce, int qi) {
                         radius = distance(lpos, vpos);
                         tmax = radius - 0.005f;
                     } else {
-                        random_sun_vertex(s, rng, vpos, lpos, lnrm, lmat);
+                        random_sun_vertex<PT_MODEL_PLIBM(MODEL)>(s, rng, vpos, lpos, lnrm, lmat);
                         float sunArea = PT_PI * s.sun_radius * s.sun_radius;              // Iterative.comp:92
                         lightPdf = 0.5f / sunArea;
                         radius = distance(lpos, vpos);
@@ -447,14 +449,21 @@ __global__ void k_tally(FrameParams p) {
     atomicAdd(&p.totals[3], nulls);
 }
 
-static void launch_shade(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
-    if (p.sun) {
-        if (p.model == 1) k_shade<1, true><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
-        else k_shade<0, true><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
-    } else {
-        if (p.model == 1) k_shade<1, false><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
-        else k_shade<0, false><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi);
+template <bool SUN>
+static void launch_shade_model(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
+    switch ((p.model & 1) | (p.plibm ? 2 : 0)) {     // bit 0: Beckmann, bit 1: PT_PARITY_LIBM (pt_shade.cuh)
+    case 0: k_shade<0, SUN><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi); break;
+    case 1: k_shade<1, SUN><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi); break;
+    case 2: k_shade<2, SUN><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi); break;
+    default: k_shade<3, SUN><<<dims.shade_blocks, PT_SHADE_THREADS, 0, st>>>(p, b, qi); break;
     }
+}
+static void launch_shade(const FrameParams& p, int b, int qi, const LaunchDims& dims, cudaStream_t st) {
+    if (p.sun) launch_shade_model<true>(p, b, qi, dims, st); else launch_shade_model<false>(p, b, qi, dims, st);
+}
+static void launch_raygen(const FrameParams& p, const LaunchDims& dims, cudaStream_t st) {
+    if (p.plibm) k_raygen<true><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p);
+    else k_raygen<false><<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p);
 }
 
 int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, cudaEvent_t* evs) {
@@ -462,7 +471,7 @@ int launch_frame(const FrameParams& p, const LaunchDims& dims, cudaStream_t st, 
     int launches = 0;
     cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), st);
     if (evs) cudaEventRecord(evs[launches], st);
-    k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p); launches++;
+    launch_raygen(p, dims, st); launches++;
     int qi = 0;
     for (int b = 0; b < p.max_depth; b++) {
         if (evs) cudaEventRecord(evs[launches], st);
@@ -483,7 +492,7 @@ int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceS
     int launches = 0;
     cudaStream_t A = ss.a, B = ss.b;
     cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), A);
-    k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, A>>>(p); launches++;
+    launch_raygen(p, dims, A); launches++;
     launch_extend(p, 0, 0, dims, dims.frame_blocks, A); launches++;
     // shade(0) rewrites the shadow queue and accum pixels the previous frame's last shadow kernel may still be using
     if (wait_prev) cudaStreamWaitEvent(A, ss.ev_shadow, 0);
@@ -513,7 +522,7 @@ __global__ void k_primary_gather(FrameParams p, float4* by_pixel) {
 }
 int launch_primary(const FrameParams& p, const LaunchDims& dims, float4* by_pixel, cudaStream_t st) {
     cudaMemsetAsync(p.counters, 0, sizeof(BounceCounters) * (p.max_depth + 2), st);
-    k_raygen<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p);
+    launch_raygen(p, dims, st);
     launch_extend(p, 0, 0, dims, dims.extend_blocks, st);
     k_primary_gather<<<dims.stream_blocks, PT_STREAM_THREADS, 0, st>>>(p, by_pixel);
     return 3;
@@ -521,7 +530,10 @@ int launch_primary(const FrameParams& p, const LaunchDims& dims, float4* by_pixe
 
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st) {
     int blocks = (int)((n + 255) / 256);
-    if (blocks > 0) k_raygen_probe<<<blocks, 256, 0, st>>>(p, first, n, out3);
+    if (blocks > 0) {
+        if (p.plibm) k_raygen_probe<true><<<blocks, 256, 0, st>>>(p, first, n, out3);
+        else k_raygen_probe<false><<<blocks, 256, 0, st>>>(p, first, n, out3);
+    }
 }
 
 // ------------------------------------------------------------------ RNG table seeding
@@ -547,6 +559,7 @@ void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStr
 }
 
 // ------------------------------------------------------------------ resolve (Present.frag:13-37)
+template <bool PL>
 __global__ void k_resolve(const float4* __restrict__ accum, long long n, unsigned num_samples, float* rgb_f32,
                           unsigned char* rgb_u8) {
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -561,15 +574,37 @@ __global__ void k_resolve(const float4* __restrict__ accum, long long n, unsigne
         color *= 2.0f;
         color = ((color * (A * color + C * B) + D * E) / (color * (A * color + B) + D * F)) - E / F;
         color /= white;
-        color = powf(color, 1.0f / 2.2f);
+        color = pow_sel<PL>(color, 1.0f / 2.2f);
         if (rgb_f32) rgb_f32[3 * i + c] = color;
         if (rgb_u8) rgb_u8[3 * i + c] = (unsigned char)(gmin(gmax(color, 0.0f), 1.0f) * 255.0f + 0.5f);
     }
 }
 void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
-                    cudaStream_t st) {
+                    cudaStream_t st, bool plibm) {
     int blocks = (int)((n + 255) / 256);
-    if (blocks > 0) k_resolve<<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
+    if (blocks <= 0) return;
+    if (plibm) k_resolve<true><<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
+    else k_resolve<false><<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
+}
+
+// ------------------------------------------------------------------ pt_parity_libm.h on the device, argument by argument
+// fn: 0 sin, 1 cos, 2 log, 3 exp, 4 pow(x, y). The CPU checkers run the same header; tests require equal bits.
+__global__ void k_plibm_probe(int fn, const float* __restrict__ x, const float* __restrict__ y, long long n, float* out) {
+    long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float a = x[i], r;
+    switch (fn) {
+    case 0: r = ptpl::sinf_(a); break;
+    case 1: r = ptpl::cosf_(a); break;
+    case 2: r = ptpl::logf_(a); break;
+    case 3: r = ptpl::expf_(a); break;
+    default: r = ptpl::powf_(a, y[i]); break;
+    }
+    out[i] = r;
+}
+void launch_plibm_probe(int fn, const float* x, const float* y, long long n, float* out, cudaStream_t st) {
+    int blocks = (int)((n + 255) / 256);
+    if (blocks > 0) k_plibm_probe<<<blocks, 256, 0, st>>>(fn, x, y, n, out);
 }
 
 // ------------------------------------------------------------------ equirectangular -> cubemap

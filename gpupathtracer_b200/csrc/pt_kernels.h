@@ -22,6 +22,7 @@ struct FrameParams {
     int max_depth;
     int model;
     int sun;              // SUN_LIGHT (Iterative.comp:116-126), off in the reference as shipped
+    int plibm;            // PT_PARITY_LIBM: transcendentals through pt_parity_libm.h (bit-identical to the CPU checkers)
     int trace_null;       // 1: queue a shadow ray even when its radiance is exactly 0 (pt_config.trace_null_shadow)
     uint4* rng_table;     // per pixel
     float4* accum;        // per pixel, running sum
@@ -63,7 +64,8 @@ void launch_raygen_probe(const FrameParams& p, long long first, long long n, flo
 void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStream_t st);
 void query_launch_dims(int device, int wide, LaunchDims* out);
 void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
-                    cudaStream_t st);
+                    cudaStream_t st, bool plibm = false);
+void launch_plibm_probe(int fn, const float* x, const float* y, long long n, float* out, cudaStream_t st);
 void launch_equirect_to_cube(const float4* src, int w, int h, float4* faces, int n, cudaStream_t st);
 
 }  // namespace pt

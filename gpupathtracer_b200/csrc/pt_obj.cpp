@@ -502,7 +502,7 @@ static bool decode_bmp_rgba8(const std::vector<unsigned char>& file, int& w, int
     out.assign((size_t)w * h * 4, 255);
     size_t z = 0;
     if (bpp < 16) {
-        if (psize == 0 || psize > 256) return false;
+        if (psize <= 0 || psize > 256) return false;     // a pixel offset smaller than the headers makes psize negative: damaged file
         unsigned char pal[256][3];
         for (int i = 0; i < psize; i++) { pal[i][2] = (unsigned char)s.get8(); pal[i][1] = (unsigned char)s.get8(); pal[i][0] = (unsigned char)s.get8(); if (hsz != 12) s.get8(); }
         for (int i = psize; i < 256; i++) pal[i][0] = pal[i][1] = pal[i][2] = 0;     // stb reads its uninitialised stack here; files that index past the palette are damaged
@@ -591,7 +591,7 @@ static bool decode_tga_rgba8(const std::vector<unsigned char>& file, int& w, int
         if (type != 2 && type != 3 && type != 10 && type != 11) return false;
         if (bpp != 8 && bpp != 15 && bpp != 16 && bpp != 24 && bpp != 32) return false;
     }
-    if (tw < 1 || th < 1) return false;
+    if (tw < 1 || th < 1 || (double)tw * th > 1.0e9) return false;
     bool rle = false;
     if (type >= 8) { type -= 8; rle = true; }
     const bool inverted = ((desc >> 5) & 1) == 0;                        // bottom-up file: rows are flipped after decoding
@@ -686,7 +686,7 @@ bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<flo
             while (pos < b.size() && (b[pos] == ' ' || b[pos] == '\n' || b[pos] == '\r' || b[pos] == '\t' || b[pos] == '\v' || b[pos] == '\f')) pos++;
             if (pos < b.size() && b[pos] == '#') { while (pos < b.size() && b[pos] != '\n' && b[pos] != '\r') pos++; continue; }
             int v = 0; bool any = false;
-            while (pos < b.size() && b[pos] >= '0' && b[pos] <= '9') { v = v * 10 + (b[pos] - '0'); pos++; any = true; }
+            while (pos < b.size() && b[pos] >= '0' && b[pos] <= '9') { if (v > 100000000) return false; v = v * 10 + (b[pos] - '0'); pos++; any = true; }
             if (!any) return false;
             vals[got++] = v;
         }
@@ -707,7 +707,7 @@ bool load_image_rgba32f(const std::string& path, int& w, int& h, std::vector<flo
                 int c[3];
                 for (int k = 0; k < 3; k++) {
                     while (pos < b.size() && (b[pos] < '0' || b[pos] > '9')) pos++;
-                    int v = 0; while (pos < b.size() && b[pos] >= '0' && b[pos] <= '9') { v = v * 10 + (b[pos] - '0'); pos++; }
+                    int v = 0; while (pos < b.size() && b[pos] >= '0' && b[pos] <= '9') { if (v < 100000) v = v * 10 + (b[pos] - '0'); pos++; }
                     c[k] = v * 255 / vals[2];
                 }
                 put(i, c[0], c[1], c[2], 255);
@@ -736,7 +736,10 @@ int pt_scene_file_load_obj(const char* obj_path, pt_scene_file** out) {
     *out = nullptr;
     pt_scene_file* sf = new pt_scene_file();
     std::string err;
-    if (!pt::load_obj_file(obj_path, sf->s, err)) {
+    bool ok = false;
+    try { ok = pt::load_obj_file(obj_path, sf->s, err); }
+    catch (const std::exception& e) { err = std::string("pt_scene_file_load_obj: ") + e.what(); }
+    if (!ok) {
         pt::set_last_error(err.c_str());
         delete sf;
         return PT_ERR_IO;
@@ -760,7 +763,13 @@ const char* pt_scene_file_warnings(const pt_scene_file* sf) { return sf ? sf->s.
 int pt_image_load(const char* path, int32_t* width, int32_t* height, float** rgba) {
     if (!path || !width || !height || !rgba) return PT_ERR_INVALID;
     int w = 0, h = 0; std::vector<float> px;
-    if (!pt::load_image_rgba32f(path, w, h, px)) {
+    bool ok = false;
+    try { ok = pt::load_image_rgba32f(path, w, h, px); }
+    catch (const std::exception& e) {      // a header that asks for more memory than there is: std::bad_alloc / length_error must not cross the C ABI
+        pt::set_last_error((std::string("cannot decode '") + path + "': " + e.what()).c_str());
+        return PT_ERR_LIMIT;
+    }
+    if (!ok) {
         pt::set_last_error((std::string("cannot decode '") + path + "' (supported: .jpg, .png, .bmp, .tga, .ppm as stb_image reads them)").c_str());
         return PT_ERR_IO;
     }

@@ -6,8 +6,20 @@
 #pragma once
 #include "pt_math.cuh"
 #include "pt_layout.h"
+#include "pt_parity_libm.h"
 
 namespace pt {
+
+// The template parameter MODEL of the shading functions carries two switches: bit 0 = microfacet model (0 Trowbridge-Reitz,
+// 1 Beckmann), bit 1 = PT_PARITY_LIBM (transcendentals through pt_parity_libm.h instead of CUDA's libm).
+#define PT_MODEL_BECKMANN(M) (((M) & 1) != 0)
+#define PT_MODEL_PLIBM(M) (((M) & 2) != 0)
+template <bool PL> __device__ __forceinline__ void sincos_sel(float x, float* s, float* c) {
+    if (PL) ptpl::sincosf_(x, s, c); else sincosf(x, s, c);
+}
+template <bool PL> __device__ __forceinline__ float log_sel(float x) { return PL ? ptpl::logf_(x) : logf(x); }
+template <bool PL> __device__ __forceinline__ float exp_sel(float x) { return PL ? ptpl::expf_(x) : expf(x); }
+template <bool PL> __device__ __forceinline__ float pow_sel(float x, float y) { return PL ? ptpl::powf_(x, y) : powf(x, y); }
 
 // ---------------------------------------------------------------- HybridTaus (Random.glsl:47-70)
 struct Rng {
@@ -141,10 +153,10 @@ __device__ __forceinline__ V3 fresnel(V3 f0, float ndo) {                  // :9
 }
 template <int MODEL>
 __device__ __forceinline__ float D_micro(const Material& m, const Interaction& it) {
-    if (MODEL == 1) {                                                      // Beckmann :35-39
-        float sub = 2.0f * logf(sqrtf(PT_PI) * m.roughness * it.ndm);
+    if (PT_MODEL_BECKMANN(MODEL)) {                                        // Beckmann :35-39
+        float sub = 2.0f * log_sel<PT_MODEL_PLIBM(MODEL)>(sqrtf(PT_PI) * m.roughness * it.ndm);
         float add = (it.ndm2 - 1.0f) / (it.ndm2 * m.roughness2);
-        return expf(add - sub);
+        return exp_sel<PT_MODEL_PLIBM(MODEL)>(add - sub);
     } else {                                                               // Trowbridge-Reitz :13-16
         float divsor = (m.roughness2 - 1.0f) * it.ndm2 + 1.0f;
         return m.roughness2 / gmax(PT_PI * divsor * divsor, 1e-20f);
@@ -194,7 +206,7 @@ __device__ inline V3 importance_sample(const Material& m, Interaction& it, Rng& 
     float rx = rng.next(), ry = rng.next();
     float phi = 2.0f * PT_PI * ry;
     float sphi, cphi;
-    sincosf(phi, &sphi, &cphi);
+    sincos_sel<PT_MODEL_PLIBM(MODEL)>(phi, &sphi, &cphi);
     if (diffuse) {
         float radius = sqrtf(rx);
         float z = sqrtf(1.0f - rx);
@@ -203,8 +215,8 @@ __device__ inline V3 importance_sample(const Material& m, Interaction& it, Rng& 
         pdfMIS = sp * pdf_micro<MODEL>(m, it);
     } else {
         float z2, radius;
-        if (MODEL == 1) {
-            float g = -m.roughness2 * logf(1.0f - rx);
+        if (PT_MODEL_BECKMANN(MODEL)) {
+            float g = -m.roughness2 * log_sel<PT_MODEL_PLIBM(MODEL)>(1.0f - rx);
             z2 = 1.0f / (1.0f + g);
             radius = sqrtf(1.0f - z2);
         } else {
@@ -250,6 +262,7 @@ __device__ inline void random_light_vertex(const SceneDev& s, Rng& rng, V3& pos,
 // RandomSunVertex, Iterative.comp:84-110: the sun is a disk of radius sunRadius one unit away along sunDir, sampled
 // uniformly by area in the frame ConstructTBN(-sunDir); its material is the sky's (matId 0), whose emission
 // (25 * (30, 26, 19), Scene.cpp:239) is what the NEE sample picks up.
+template <bool PL>
 __device__ inline void random_sun_vertex(const SceneDev& s, Rng& rng, V3 vertex, V3& pos, V3& nrm, uint32_t& mat) {
     V3 sd = v3(s.sun_dir[0], s.sun_dir[1], s.sun_dir[2]);
     V3 n = -sd;
@@ -259,7 +272,7 @@ __device__ inline void random_sun_vertex(const SceneDev& s, Rng& rng, V3 vertex,
     float rx = rng.next(), ry = rng.next();
     float radius = s.sun_radius * sqrtf(rx);
     float phi = 2.0f * PT_PI * ry;
-    float sn, cs; sincosf(phi, &sn, &cs);
+    float sn, cs; sincos_sel<PL>(phi, &sn, &cs);
     V3 d = v3(radius * cs, radius * sn, 0.0f);
     V3 off = v3(t.x * d.x + b.x * d.y + n.x * d.z, t.y * d.x + b.y * d.y + n.y * d.z, t.z * d.x + b.z * d.y + n.z * d.z);
     pos = vertex + sd + off;
@@ -287,6 +300,7 @@ __device__ __forceinline__ void ray_index_to_morton(int idx, int width, int& px,
 __device__ __forceinline__ V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
 
 // InitRay, Iterative.comp:174-210
+template <bool PL>
 __device__ inline void init_ray(const CameraRec& cam, int width, int height, int px, int py, Rng& rng, V3& o, V3& d) {
     float jx = rng.next(), jy = rng.next();
     float s = ((float)px + jx) / (float)width;
@@ -294,7 +308,7 @@ __device__ inline void init_ray(const CameraRec& cam, int width, int height, int
     float rx = rng.next(), ry = rng.next();
     float phi = 2.0f * PT_PI * ry;
     float sphi, cphi;
-    sincosf(phi, &sphi, &cphi);
+    sincos_sel<PL>(phi, &sphi, &cphi);
     float rdx = cam.lens_radius * rx * cphi;     // `lens_radius * r * vec2(cos, sin)`: r, not sqrt(r.x)
     float rdy = cam.lens_radius * ry * sphi;
     V3 offset = ld3(cam.u) * rdx + ld3(cam.v) * rdy;

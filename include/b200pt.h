@@ -61,8 +61,17 @@ typedef struct pt_config {
                                      the surface's horizon) is settled without a shadow ray -- same image bits, ~1/3 fewer
                                      shadow rays on the atrium. 1: trace it anyway, as the reference does, so that ray
                                      counts are comparable one to one with the reference's. */
-    int32_t reserved[3];
+    int32_t parity_flags;         /* PT_PARITY_*: switches that pin what GLSL leaves open so that results can be compared for
+                                     EQUALITY with the reference's shader source compiled on a CPU (tests, parity runs); 0 = fast defaults */
+    int32_t reserved[2];
 } pt_config;
+
+/* pt_config.parity_flags. PT_PARITY_LIBM: sin / cos / log / exp / pow of the shading path (InitRay Iterative.comp:191-192, the
+ * importance samplers Microfacet.glsl:25,49,153, Beckmann :36-44, Present.frag:36) are evaluated by csrc/pt_parity_libm.h -- binary64
+ * series built from IEEE + - * / only, one rounding to binary32 -- instead of CUDA's sincosf / logf / expf / powf, which differ from
+ * glibc's by 1-2 ulp on some arguments. With it, frames are BIT-identical to the reference's main() compiled as C++ with the same
+ * header (accumulation image and RNG table); without it < 0.1 % of pixels differ after a few frames. ~15 % slower shade stage. */
+enum { PT_PARITY_LIBM = 1 };
 
 /* The 7 camera uniforms of Shader::LoadCamera (Shader.cpp:74-84). */
 typedef struct pt_camera {
@@ -282,6 +291,10 @@ int pt_trace_primary_async(pt_context* ctx, float* host_hits);
 /* ---- per-stage probes (parity of raygen on its own; rng table is advanced like the shader does) ---- */
 /* out: n x 12 floats {pixel.x, pixel.y (int bits), o.xyz, d.xyz, 0,0,0,0} for ray indices [first, first+n). */
 int pt_raygen_probe(pt_context* ctx, int64_t first, int64_t n, float* out);
+/* csrc/pt_parity_libm.h evaluated on the device: out[i] = fn(x[i] [, y[i]]) with fn 0 sin, 1 cos, 2 log, 3 exp, 4 pow (host arrays).
+ * The CPU checkers compile the same header; tests require equal bits, which is what makes PT_PARITY_LIBM frames comparable
+ * for equality with the reference's shader source (GLSL's sin / cos / log / exp / pow: Iterative.comp:191-192, Microfacet.glsl:25-49). */
+int pt_parity_libm_probe(pt_context* ctx, int32_t fn, const float* x, const float* y_or_null, int64_t n, float* out);
 
 int pt_get_counters(pt_context* ctx, pt_counters* out);
 /* CUDA-event milliseconds of the last pt_render_frames / pt_trace_*_device call (device time only). */

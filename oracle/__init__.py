@@ -84,6 +84,26 @@ def have_ref():
     return os.path.exists(REF_SO)
 
 
+# ---- parity libm (gpupathtracer_b200/csrc/pt_parity_libm.h compiled into every checker)
+PLIBM_FNS = ["sin", "cos", "log", "exp", "pow"]
+
+
+def set_parity_libm(on):
+    """GLSL's sin / cos / log / exp / pow inside libpt_oracle.so: glibc (False) or pt_parity_libm.h (True)."""
+    lib().or_set_parity_libm(1 if on else 0)
+
+
+def parity_libm_probe(fn, x, y=None):
+    """pt_parity_libm.h as the host compiler evaluates it, element by element."""
+    l = lib()
+    l.or_parity_libm_probe.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    yy = np.ascontiguousarray(y if y is not None else np.zeros_like(x), dtype=np.float32)
+    out = np.zeros_like(x)
+    l.or_parity_libm_probe(PLIBM_FNS.index(fn), _p(x), _p(yy), x.size, _p(out))
+    return out
+
+
 def ref():
     """The reference's own code; None when oracle/_ref has not been built (e.g. no /root/reference)."""
     global _ref
@@ -150,10 +170,14 @@ def ref_glsl_shade_probe(inputs, rng, model=0):
     min / max meaning IEEE minNum / maxNum (what NVIDIA's FMNMX executes) instead of glm's ternaries. ref_glsl_light_probe and
     Oracle.ref_glsl_render take the same codes."""
     g = C.CDLL(GLSL_SO)
-    fn = {0: g.ref_glsl_shade_probe, 1: g.ref_glsl_shade_probe_beckmann, 2: g.ref_glsl_shade_probe_beckmann_maxnum}[model]
-    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     a = np.ascontiguousarray(inputs, dtype=np.float32); r = np.ascontiguousarray(rng, dtype=np.uint32).copy()
     out = np.zeros((a.shape[0], 20), np.float32)
+    if model in (4, 6):                                        # 0 | 4, 2 | 4: the builds with pt_parity_libm.h's transcendentals
+        g.ref_glsl_shade_probe_model.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_int, C.c_void_p]
+        g.ref_glsl_shade_probe_model(_p(a), _p(r), a.shape[0], model, _p(out))
+        return out, r
+    fn = {0: g.ref_glsl_shade_probe, 1: g.ref_glsl_shade_probe_beckmann, 2: g.ref_glsl_shade_probe_beckmann_maxnum}[model]
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
     fn(_p(a), _p(r), a.shape[0], _p(out))
     return out, r
 
@@ -200,14 +224,16 @@ def ref_glsl_raygen(cam_array, width, height, total_light_area, rng_table, first
     return out
 
 
-def ref_glsl_present(accum, num_samples, exposure=1.68):
+def ref_glsl_present(accum, num_samples, exposure=1.68, parity_libm=False):
     """Present.frag compiled as C++ (oracle/ref_glsl.cpp) on an (h, w, 4) accumulation image -> (h, w, 3) float32, the colour the
-    fragment shader writes; exposure is the uniform the reference sets to kExposure (Renderer.cpp:18)."""
+    fragment shader writes; exposure is the uniform the reference sets to kExposure (Renderer.cpp:18). parity_libm: the build
+    whose pow() is pt_parity_libm.h's."""
     g = C.CDLL(GLSL_SO)
-    g.ref_glsl_present.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]
+    fn = g.ref_glsl_present_pl if parity_libm else g.ref_glsl_present
+    fn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p]
     a = np.ascontiguousarray(accum, dtype=np.float32)
     out = np.zeros(a.shape[:2] + (3,), np.float32)
-    g.ref_glsl_present(_p(a), a.shape[1], a.shape[0], int(num_samples), float(exposure), _p(out))
+    fn(_p(a), a.shape[1], a.shape[0], int(num_samples), float(exposure), _p(out))
     return out
 
 
@@ -374,9 +400,17 @@ class Oracle:
         c.lens_radius = float(a[18])
         return c
 
-    def render(self, cam_array, width, height, rng, accum, n_frames=1, max_depth=66, model=0, n_threads=0, sun=None):
+    def render(self, cam_array, width, height, rng, accum, n_frames=1, max_depth=66, model=0, n_threads=0, sun=None,
+               parity_libm=False):
         """In place on rng (px,4) uint32 and accum (h,w,4) float32. Returns counters. sun = (direction, radius) turns the
-        shader's SUN_LIGHT branch on."""
+        shader's SUN_LIGHT branch on. parity_libm: sin / cos / log / exp from pt_parity_libm.h for this call."""
+        set_parity_libm(parity_libm)
+        try:
+            return self._render(cam_array, width, height, rng, accum, n_frames, max_depth, model, n_threads, sun)
+        finally:
+            set_parity_libm(False)
+
+    def _render(self, cam_array, width, height, rng, accum, n_frames, max_depth, model, n_threads, sun):
         cam = self.camera(cam_array)
         cfg = OrConfig(width, height, max_depth, model, n_threads)
         if sun is not None:

@@ -2,6 +2,7 @@
 // and the stated float mode. Every function cites the reference file:line it restates
 // (paths relative to /root/reference/src).
 #include "pt_oracle.h"
+#include "pt_parity_libm.h"     // gpupathtracer_b200/csrc: the ONE definition of sin / cos / log / exp / pow shared by every compile in parity mode
 #include <cmath>
 #include <cstring>
 #include <cstdlib>
@@ -11,6 +12,15 @@
 #include <algorithm>
 
 namespace {
+
+// GLSL's sin / cos / log / exp / pow: glibc's float functions by default; pt_parity_libm.h after or_set_parity_libm(1)
+// (set once before a run; the worker threads only read it).
+int g_parity_libm = 0;
+inline float o_sin(float x) { return g_parity_libm ? ptpl::sinf_(x) : sinf(x); }
+inline float o_cos(float x) { return g_parity_libm ? ptpl::cosf_(x) : cosf(x); }
+inline float o_log(float x) { return g_parity_libm ? ptpl::logf_(x) : logf(x); }
+inline float o_exp(float x) { return g_parity_libm ? ptpl::expf_(x) : expf(x); }
+inline float o_pow(float x, float y) { return g_parity_libm ? ptpl::powf_(x, y) : powf(x, y); }
 
 // ---------------------------------------------------------------- GLSL-like vector math
 struct V3 { float x, y, z; };
@@ -347,9 +357,9 @@ inline float D_tr(const Material& m, const Interaction& it) {
     return m.roughness2 / gmax(kPi * divsor * divsor, 1e-20f);
 }
 inline float D_beckmann(const Material& m, const Interaction& it) {
-    float sub = 2.0f * logf(sqrtf(kPi) * m.roughness * it.ndm);
+    float sub = 2.0f * o_log(sqrtf(kPi) * m.roughness * it.ndm);
     float add = (it.ndm2 - 1.0f) / (it.ndm2 * m.roughness2);
-    return expf(add - sub);
+    return o_exp(add - sub);
 }
 inline float D_micro(int model, const Material& m, const Interaction& it) {
     return model == 1 ? D_beckmann(m, it) : D_tr(m, it);
@@ -401,14 +411,14 @@ V3 importance_sample(int model, const Material& m, Interaction& it, Rng& rng, fl
         float radius = sqrtf(rx);
         float phi = 2.0f * kPi * ry;
         float z = sqrtf(1.0f - rx);
-        set_incoming(it, tbn_mul(it, v3(radius * sinf(phi), radius * cosf(phi), z)));
+        set_incoming(it, tbn_mul(it, v3(radius * o_sin(phi), radius * o_cos(phi), z)));
         pdfSample = dp * (it.ndi / kPi);
         pdfMIS = sp * pdf_micro(model, m, it);
     } else {
         float rx = rng.next(), ry = rng.next();
         float z2;
         if (model == 1) {
-            float g = -m.roughness2 * logf(1.0f - rx);
+            float g = -m.roughness2 * o_log(1.0f - rx);
             z2 = 1.0f / (1.0f + g);
         } else {
             z2 = gmax((1.0f - rx) / (rx * (m.roughness2 - 1.0f) + 1.0f), 0.0f);
@@ -416,7 +426,7 @@ V3 importance_sample(int model, const Material& m, Interaction& it, Rng& rng, fl
         float z = sqrtf(z2);
         float phi = 2.0f * kPi * ry;
         float radius = (model == 1) ? sqrtf(1.0f - z2) : sqrtf(gmax(1.0f - z2, 0.0f));
-        set_microfacet(it, tbn_mul(it, v3(radius * sinf(phi), radius * cosf(phi), z)));
+        set_microfacet(it, tbn_mul(it, v3(radius * o_sin(phi), radius * o_cos(phi), z)));
         float pdfDiffuse = dp * (it.ndi / kPi);
         pdfSample = sp * pdf_micro(model, m, it);
         pdfMIS = pdfDiffuse;
@@ -464,7 +474,7 @@ LightVertex random_sun_vertex(const OrConfig& cfg, V3 vertexPosition, Rng& rng) 
     float rx = rng.next(), ry = rng.next();       // vec2 r = rand2()
     float radius = cfg.sun_radius * sqrtf(rx);
     float phi = 2.0f * kPi * ry;
-    V3 diskPosition = v3(radius * cosf(phi), radius * sinf(phi), 0.0f);
+    V3 diskPosition = v3(radius * o_cos(phi), radius * o_sin(phi), 0.0f);
     LightVertex lv;
     lv.position = vertexPosition + sunDir + tbn_mul(tbn, diskPosition);
     lv.normal = -sunDir;
@@ -543,8 +553,8 @@ void init_ray(const OrCamera& cam, const OrConfig& cfg, float totalLightArea, in
     float t = ((float)p.py + jy) / (float)cfg.height;
     float rx = rng.next(), ry = rng.next();
     float phi = 2.0f * kPi * ry;
-    float rdx = cam.lens_radius * rx * cosf(phi);     // `lens_radius * r * vec2(cos, sin)`: r, not sqrt(r.x)
-    float rdy = cam.lens_radius * ry * sinf(phi);
+    float rdx = cam.lens_radius * rx * o_cos(phi);     // `lens_radius * r * vec2(cos, sin)`: r, not sqrt(r.x)
+    float rdy = cam.lens_radius * ry * o_sin(phi);
     V3 offset = ld3(cam.u) * rdx + ld3(cam.v) * rdy;
     p.ray.origin = ld3(cam.position) + offset;
     p.ray.direction = normalize(ld3(cam.lower_left) + s * ld3(cam.horizontal) + t * ld3(cam.vertical) - offset);
@@ -704,6 +714,15 @@ void or_sample_texture(const OrScene* s, int index, float u, float v, float* rgb
     sample_texture(s->textures[index], u, v, rgba);
 }
 
+void or_set_parity_libm(int on) { g_parity_libm = on ? 1 : 0; }
+int or_get_parity_libm(void) { return g_parity_libm; }
+// pt_parity_libm.h as this compiler evaluates it: out[i] = fn(x[i] [, y[i]]), fn 0 sin, 1 cos, 2 log, 3 exp, 4 pow
+void or_parity_libm_probe(int fn, const float* x, const float* y, int64_t n, float* out) {
+    for (int64_t i = 0; i < n; i++) {
+        float a = x[i];
+        out[i] = fn == 0 ? ptpl::sinf_(a) : fn == 1 ? ptpl::cosf_(a) : fn == 2 ? ptpl::logf_(a) : fn == 3 ? ptpl::expf_(a) : ptpl::powf_(a, y[i]);
+    }
+}
 void or_hybrid_taus(uint32_t state[4], int n, float* out) {
     Rng r{state[0], state[1], state[2], state[3]};
     for (int i = 0; i < n; i++) out[i] = r.next();
@@ -752,7 +771,7 @@ void or_tonemap(const float rgb_sum[3], int num_samples, float out_rgb[3]) {
         color *= 2.0f;
         color = ((color * (A * color + C * B) + D * E) / (color * (A * color + B) + D * F)) - E / F;
         color /= white;
-        out_rgb[c] = powf(color, 1.0f / 2.2f);
+        out_rgb[c] = o_pow(color, 1.0f / 2.2f);
     }
 }
 

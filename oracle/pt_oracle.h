@@ -108,6 +108,12 @@ typedef struct OrCounters {
 
 /* ---- scalar pieces ---- */
 void or_hybrid_taus(uint32_t state[4], int n, float* out);            /* Random.glsl:47-70 */
+/* GLSL pins no algorithm for sin / cos / log / exp / pow. Default: glibc's float functions. After or_set_parity_libm(1): the
+ * binary64 series of gpupathtracer_b200/csrc/pt_parity_libm.h, the same header the CUDA kernels (pt_config.parity_flags &
+ * PT_PARITY_LIBM) and the reference's shader source compiled as C++ (model code | 4) use, so whole frames compare for equality. */
+void or_set_parity_libm(int on);
+int or_get_parity_libm(void);
+void or_parity_libm_probe(int fn, const float* x, const float* y, int64_t n, float* out);   /* fn 0 sin 1 cos 2 log 3 exp 4 pow */
 /* shading arithmetic on explicit inputs (material, interaction, NEE evaluation, BSDF sample) in Iterative.comp:236-288's order;
  * in: n x 16 floats, rng_io: n x 4 words (advanced), out: n x 20 floats -- layout in pt_oracle.cpp */
 void or_equirect_uv(const float* sample_coords, int64_t n, float* uv);   /* EquirectangularConverter.frag:9-19 without the fetch */

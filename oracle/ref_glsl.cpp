@@ -29,6 +29,7 @@
 //     the triangle's index, so the accepted triangle names itself. No traversal arithmetic reads that word.
 #define GLM_FORCE_SWIZZLE
 #include <glm/glm.hpp>
+#include "pt_parity_libm.h"     // gpupathtracer_b200/csrc: used only by the *_pl namespaces below (model codes 4 and 6)
 #include <atomic>
 #include <cstdint>
 #include <cmath>
@@ -134,6 +135,27 @@ using namespace refglsl;
 }  // namespace refglsl_beckmann_maxnum
 #undef REFGLSL_MAXNUM
 
+// ... and GGX / Beckmann-maxNum once more with the scalar transcendentals of pt_parity_libm.h (see ref_glsl_ns.h): model codes 4
+// and 6 (= 0 | 4, 2 | 4), the builds whose frames the CUDA path must reproduce BIT for bit under PT_PARITY_LIBM
+#define REFGLSL_PLIBM
+namespace refglsl_ggx_pl {
+using namespace glm;
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
+}  // namespace refglsl_ggx_pl
+#define REFGLSL_MAXNUM
+namespace refglsl_beckmann_maxnum_pl {
+using namespace glm;
+using namespace refglsl;
+#define REFGLSL_SHADING "ref_glsl_shading_beckmann.inc"
+#include "ref_glsl_ns.h"
+#undef REFGLSL_SHADING
+}  // namespace refglsl_beckmann_maxnum_pl
+#undef REFGLSL_MAXNUM
+#undef REFGLSL_PLIBM
+
 // The present pass (Present.frag): division by the sample count, exposure, Uncharted-2 curve, gamma. The harness is the
 // texture unit behind `directAccum`, the fragment coordinate and the output variable.
 namespace refglsl_present {
@@ -147,6 +169,19 @@ static vec3 color;                                                  // Present.f
 #include "ref_glsl_present.inc"
 #undef uniform
 }  // namespace refglsl_present
+
+namespace refglsl_present_pl {                                     // the same with pow() from pt_parity_libm.h, component by component
+using namespace glm;
+struct AccumTex { const float* p = nullptr; int w = 0; };
+static AccumTex directAccum;
+inline vec4 texelFetch(const AccumTex& t, ivec2 px, int) { const float* q = t.p + 4 * ((size_t)px.y * t.w + px.x); return vec4(q[0], q[1], q[2], q[3]); }
+static vec4 gl_FragCoord;
+static vec3 color;
+inline vec3 pow(vec3 x, vec3 y) { return vec3(ptpl::powf_(x.x, y.x), ptpl::powf_(x.y, y.y), ptpl::powf_(x.z, y.z)); }
+#define uniform
+#include "ref_glsl_present.inc"
+#undef uniform
+}  // namespace refglsl_present_pl
 
 namespace refglsl_equirect {
 using namespace glm;
@@ -166,6 +201,28 @@ void parallel_for(int64_t n, int n_threads, F f) {
     for (auto& t : th) t.join();
 }
 std::vector<float> g_stamped;                                      // triangles with their index in the padding word
+
+// One compile of the shader path per model code: 0 GGX as shipped, 1 Beckmann (Microfacet.glsl's macros), 2 Beckmann with scalar
+// min / max = IEEE minNum / maxNum, 4 / 6 = 0 / 2 with the transcendentals of pt_parity_libm.h.
+struct ModelBuild {
+    void (*shade_probe)(const float*, uint32_t*, int64_t, float*);
+    void (*light_probe)(const float*, uint32_t*, int64_t, float*);
+    void (*bind_lights)(const float*, int, float);
+    void (*render_frame)(const float*, int, int, float, uint32_t*, float*);
+    void (*render_frame_shared)(const float*, int, int, float, uint32_t*, float*, glm::uint*);
+    void (*raygen_probe)(const float*, int, int, float, uint32_t*, int64_t, int64_t, float*);
+    const glm::vec4** material_instance;
+    int* max_path_index;
+};
+#define REFGLSL_BUILD(ns) ModelBuild{ns::shade_probe, ns::light_probe, ns::bind_lights, ns::render_frame, ns::render_frame_shared, \
+                                     ns::raygen_probe, &ns::materialInstance, &ns::maxPathIndex}
+ModelBuild g_builds[] = {REFGLSL_BUILD(refglsl_ggx), REFGLSL_BUILD(refglsl_beckmann), REFGLSL_BUILD(refglsl_beckmann_maxnum),
+                         REFGLSL_BUILD(refglsl_ggx_pl), REFGLSL_BUILD(refglsl_beckmann_maxnum_pl),
+                         REFGLSL_BUILD(refglsl_ggx_sun), REFGLSL_BUILD(refglsl_beckmann_sun)};
+const int kBuilds = (int)(sizeof(g_builds) / sizeof(g_builds[0]));
+ModelBuild& build_of(int model) {
+    switch (model) { case 1: return g_builds[1]; case 2: return g_builds[2]; case 4: return g_builds[3]; case 6: return g_builds[4]; default: return g_builds[0]; }
+}
 }  // namespace
 
 extern "C" {
@@ -211,15 +268,11 @@ void ref_glsl_trace_any(const float* rays, int64_t n, uint8_t* flags, int n_thre
 void ref_glsl_shade_probe(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_ggx::shade_probe(in, rng_io, n, out); }
 void ref_glsl_shade_probe_beckmann(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_beckmann::shade_probe(in, rng_io, n, out); }
 void ref_glsl_shade_probe_beckmann_maxnum(const float* in, uint32_t* rng_io, int64_t n, float* out) { refglsl_beckmann_maxnum::shade_probe(in, rng_io, n, out); }
+void ref_glsl_shade_probe_model(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) { build_of(model).shade_probe(in, rng_io, n, out); }
 void ref_glsl_bind_lights(const float* lights2, int n_lights, float total_light_area) {
-    refglsl_ggx::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann::bind_lights(lights2, n_lights, total_light_area);
-    refglsl_ggx_sun::bind_lights(lights2, n_lights, total_light_area); refglsl_beckmann_sun::bind_lights(lights2, n_lights, total_light_area);
-    refglsl_beckmann_maxnum::bind_lights(lights2, n_lights, total_light_area);
+    for (int k = 0; k < kBuilds; k++) g_builds[k].bind_lights(lights2, n_lights, total_light_area);
 }
-void ref_glsl_light_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) {
-    if (model == 2) refglsl_beckmann_maxnum::light_probe(in, rng_io, n, out);
-    else if (model == 1) refglsl_beckmann::light_probe(in, rng_io, n, out); else refglsl_ggx::light_probe(in, rng_io, n, out);
-}
+void ref_glsl_light_probe(const float* in, uint32_t* rng_io, int64_t n, int model, float* out) { build_of(model).light_probe(in, rng_io, n, out); }
 // materials: n x 12 floats as OrScene has them {colour.rgb, albedo texture index (int bits, -1 = none), emission.rgb, -,
 // props.rgb, props texture index}; laid out for the shader as Scene.cpp:296-299 does: [albedo handle, props handle][emission, flag]
 void ref_glsl_bind_materials(const float* materials12, int n, const void* gl_scene, refglsl::tex2d_fn tex2d, refglsl::cube_fn cube) {
@@ -235,18 +288,14 @@ void ref_glsl_bind_materials(const float* materials12, int n, const void* gl_sce
         g_material_ssbo.push_back(glm::uintBitsToFloat(handles));
         g_material_ssbo.push_back(glm::vec4(m[4], m[5], m[6], m[7]));
     }
-    refglsl_ggx::materialInstance = g_material_ssbo.data(); refglsl_beckmann::materialInstance = g_material_ssbo.data();
-    refglsl_ggx_sun::materialInstance = g_material_ssbo.data(); refglsl_beckmann_sun::materialInstance = g_material_ssbo.data();
-    refglsl_beckmann_maxnum::materialInstance = g_material_ssbo.data();
+    for (int k = 0; k < kBuilds; k++) *g_builds[k].material_instance = g_material_ssbo.data();
 }
 
 // One dispatch of the reference's main() (Iterative.comp:214-307) over a whole frame: every pixel's path, accumulated into
 // `accum` (h x w x 4 floats, `imageStore`), RNG words written back by freeRNG. One invocation loops over all rays, which the
 // persistent shader allows (any number of invocations share the ray counter). Scene: ref_glsl_bind + _bind_lights + _bind_materials.
 void ref_glsl_render_frame(const float* cam19, int w, int h, float total_light_area, uint32_t* table, float* accum, int model) {
-    if (model == 2) refglsl_beckmann_maxnum::render_frame(cam19, w, h, total_light_area, table, accum);
-    else if (model == 1) refglsl_beckmann::render_frame(cam19, w, h, total_light_area, table, accum);
-    else refglsl_ggx::render_frame(cam19, w, h, total_light_area, table, accum);
+    build_of(model).render_frame(cam19, w, h, total_light_area, table, accum);
 }
 // n_frames dispatches of main() by n_procs processes sharing the ray counter, as the GPU's invocations share the SSBO word:
 // image, RNG table, one counter and one arrival word per frame live in a MAP_SHARED mapping, the children are forked once,
@@ -264,15 +313,15 @@ int ref_glsl_render_frames_mp(const float* cam19, int w, int h, float total_ligh
     float* simage = (float*)(stable + px * 4);
     std::memset(ctr, 0, words * 4);
     std::memcpy(stable, table, px * 16); std::memcpy(simage, accum, px * 16);
-    refglsl_ggx::maxPathIndex = refglsl_beckmann::maxPathIndex = max_depth - 2;
+    ModelBuild& mb = build_of(model);
+    *mb.max_path_index = max_depth - 2;
     if (n_procs < 1) n_procs = 1;
     std::vector<pid_t> kids;
     for (int k = 0; k < n_procs; k++) {
         pid_t pid = fork();
         if (pid == 0) {
             for (int f = 0; f < n_frames; f++) {
-                if (model == 1) refglsl_beckmann::render_frame_shared(cam19, w, h, total_light_area, stable, simage, ctr + f);
-                else refglsl_ggx::render_frame_shared(cam19, w, h, total_light_area, stable, simage, ctr + f);
+                mb.render_frame_shared(cam19, w, h, total_light_area, stable, simage, ctr + f);
                 __atomic_fetch_add(arrive + f, 1u, __ATOMIC_ACQ_REL);
                 while (__atomic_load_n(arrive + f, __ATOMIC_ACQUIRE) < (uint32_t)n_procs) sched_yield();
             }
@@ -297,7 +346,7 @@ int ref_glsl_render_frames_mp(const float* cam19, int w, int h, float total_ligh
         }
         if (left && rc == 0) usleep(500);
     }
-    refglsl_ggx::maxPathIndex = refglsl_beckmann::maxPathIndex = 64;
+    *mb.max_path_index = 64;
     if (rc == 0) { std::memcpy(table, stable, px * 16); std::memcpy(accum, simage, px * 16); }
     munmap(m, bytes);
     return rc;
@@ -324,6 +373,18 @@ void ref_glsl_present(const float* accum, int w, int h, int num_samples, float e
         }
 }
 
+void ref_glsl_present_pl(const float* accum, int w, int h, int num_samples, float exposure_uniform, float* rgb) {
+    using namespace refglsl_present_pl;
+    directAccum.p = accum; directAccum.w = w; numSamples = num_samples; exposure = exposure_uniform;
+    for (int y = 0; y < h; y++)
+        for (int x = 0; x < w; x++) {
+            gl_FragCoord = glm::vec4(x + 0.5f, y + 0.5f, 0.0f, 1.0f);
+            present_main();
+            float* o = rgb + 3 * ((size_t)y * w + x);
+            o[0] = color.x; o[1] = color.y; o[2] = color.z;
+        }
+}
+
 // EquirectangularConverter.frag's main() without the fetch: where in hdrTex the fragment with these sampleCoords looks
 void ref_glsl_equirect_uv(const float* sample_coords, int64_t n, float* uv) {
     for (int64_t i = 0; i < n; i++) {
@@ -335,6 +396,9 @@ void ref_glsl_equirect_uv(const float* sample_coords, int64_t n, float* uv) {
 
 void ref_glsl_raygen_probe(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, float* out) {
     refglsl_ggx::raygen_probe(cam19, w, h, total_light_area, table, first, n, out);
+}
+void ref_glsl_raygen_probe_model(const float* cam19, int w, int h, float total_light_area, uint32_t* table, int64_t first, int64_t n, int model, float* out) {
+    build_of(model).raygen_probe(cam19, w, h, total_light_area, table, first, n, out);
 }
 
 // n draws of the shader's HybridTaus from one state (Random.glsl:47-70)

@@ -10,6 +10,16 @@
 inline float max(float a, float b) { return fmaxf(a, b); }
 inline float min(float a, float b) { return fminf(a, b); }
 #endif
+#ifdef REFGLSL_PLIBM
+// GLSL pins no algorithm for its transcendental functions; this build gives the scalar sin / cos / log / exp / pow the shading path
+// calls (Iterative.comp:101,192; Microfacet.glsl:25,36-49,153) the one definition of pt_parity_libm.h instead of glm's (= glibc's),
+// and nothing else: the same header the CUDA kernels use under PT_PARITY_LIBM, so whole frames can be compared for equality.
+inline float sin(float x) { return ptpl::sinf_(x); }
+inline float cos(float x) { return ptpl::cosf_(x); }
+inline float log(float x) { return ptpl::logf_(x); }
+inline float exp(float x) { return ptpl::expf_(x); }
+inline float pow(float x, float y) { return ptpl::powf_(x, y); }
+#endif
 #include REFGLSL_SHADING
 
 // ConstructMaterialInstance (Material.glsl:39-54) reads two bindless textures; the harness supplies the two texels and runs the

@@ -217,3 +217,37 @@ def test_device_seeded_rng_table_meets_hybrid_taus_requirements():
     assert np.array_equal(tabs[0], tabs[1]) and not np.array_equal(tabs[0], tabs[2])
     assert len({tuple(row) for row in t}) == t.shape[0]
     assert abs(float(t.mean()) / 2**32 - 0.5) < 0.01 and (t >> 31).mean() > 0.45
+
+
+def test_inconsistent_tables_are_refused_and_leave_the_context_usable():
+    """The device indexes materials by matId >> 1 and triangles by the light entries without bounds checks, so uploads that
+    disagree are refused on the host; a failed pt_set_materials leaves the previous set in place."""
+    import ctypes as C
+    from gpupathtracer_b200.api import PtError, _ptr, pt_texture
+    s = get_scene("cornell_small")
+    w, h = 32, 32
+    cam = make_camera(s.data, w, h)
+    r = Renderer().Initialize(w, h, s, max_depth=5, seed=3)
+    r.RenderFrame(cam, 1)
+    before = r.DownloadAccum()
+    lib, ctx = r.lib, r.ctx
+    # fewer materials than the triangles name
+    assert lib.pt_set_materials(ctx, _ptr(s.materials), 1, None, 0) == -1 and b"matId" in lib.pt_last_error()
+    # a texture without texels
+    bad = (pt_texture * 1)(); bad[0].width, bad[0].height = 4, 4
+    assert lib.pt_set_materials(ctx, _ptr(s.materials), s.materials.shape[0], C.cast(bad, C.c_void_p), 1) == -1
+    # a light entry beyond the triangle array
+    lights = s.lights.copy(); lights.view(np.uint32)[0, 1] = s.tris.shape[0]
+    assert lib.pt_set_lights(ctx, _ptr(lights), lights.shape[0], C.c_float(s.total_light_area)) == -1
+    # triangles that name a material beyond the table
+    tris = s.tris.copy(); tris.view(np.uint32)[5, 18] = 2 * s.materials.shape[0]
+    assert lib.pt_set_triangles(ctx, _ptr(tris), tris.shape[0]) == -1
+    # ray batches stop short of the int cursor's range
+    assert lib.pt_trace_closest_device(ctx, C.c_void_p(16), (1 << 30) + 1, C.c_void_p(16)) == -1
+    # nothing above changed the context: the same frame renders again
+    r2 = Renderer().Initialize(w, h, s, max_depth=5, seed=3)
+    r2.RenderFrame(cam, 2)
+    r.RenderFrame(cam, 1)
+    assert np.array_equal(np.nan_to_num(r.DownloadAccum(), nan=-1.0), np.nan_to_num(r2.DownloadAccum(), nan=-1.0))
+    assert not np.array_equal(before, r.DownloadAccum())
+    r.CleanUp(); r2.CleanUp()

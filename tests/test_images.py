@@ -406,3 +406,39 @@ def test_ldr_files_through_loadf_get_stbs_gamma(tmp_path):
     want = oracle.ref_stbi_loadf(p)
     assert got.shape == want.shape and np.array_equal(got, want)
     assert got[..., :3].max() <= 1.0 and np.all(got[..., 3] == 1.0)
+
+
+def test_damaged_headers_are_refused_not_trusted(tmp_path):
+    """Image headers drive allocations and table sizes; a damaged one must come back as an error code, never as a write outside
+    a buffer or an exception through the C ABI (ADVICE r1: BMP palette size from a pixel offset smaller than the headers;
+    PNG / TGA / PPM dimensions; deflate output larger than the image)."""
+    import struct
+    import zlib
+    from ldr_cases import _bmp
+    rgb = _test_image(8, 8, 3)
+    idx = (rgb[..., 0] >> 4).astype(np.uint8)
+    pal = b"".join(bytes([i, i // 2, 255 - i, 0]) for i in range(256))
+    good = _bmp(8, 8, 8, [idx[y].tobytes() for y in range(8)], palette=pal)
+    files = {}
+    for name, off in (("bmp_offset_0.bmp", 0), ("bmp_offset_small.bmp", 30), ("bmp_offset_huge.bmp", 0x80000010), ("bmp_offset_neg.bmp", 0xfffffff0)):
+        files[name] = good[:10] + struct.pack("<I", off) + good[14:]
+    os2 = _bmp(8, 8, 8, [idx[y].tobytes() for y in range(8)], hsz=12, palette=pal[:3 * 68])
+    files["os2_offset_0.bmp"] = os2[:10] + struct.pack("<I", 0) + os2[14:]
+    files["tga_huge.tga"] = struct.pack("<BBBHHBHHHHBB", 0, 0, 2, 0, 0, 0, 0, 0, 65535, 65535, 32, 0) + bytes(64)
+    files["ppm_huge.ppm"] = b"P6\n99999999999999999999 2\n255\n" + bytes(64)
+    files["ppm_big.ppm"] = b"P6\n60000 60000\n255\n" + bytes(64)
+
+    def chunk(kind, data):
+        return struct.pack(">I", len(data)) + kind + data + struct.pack(">I", zlib.crc32(kind + data) & 0xffffffff)
+    sig = bytes([137, 80, 78, 71, 13, 10, 26, 10])
+    files["png_huge.png"] = sig + chunk(b"IHDR", struct.pack(">IIBBBBB", 1 << 23, 1 << 23, 8, 6, 0, 0, 0)) + chunk(b"IDAT", zlib.compress(bytes(64))) + chunk(b"IEND", b"")
+    # a 4 x 4 image whose IDAT inflates to 8 MB
+    files["png_bomb.png"] = sig + chunk(b"IHDR", struct.pack(">IIBBBBB", 4, 4, 8, 2, 0, 0, 0)) + chunk(b"IDAT", zlib.compress(bytes(8 << 20), 9)) + chunk(b"IEND", b"")
+    for name, data in files.items():
+        p = tmp_path / name
+        p.write_bytes(data)
+        with pytest.raises(api.PtError):
+            api.load_image(str(p))
+    # the undamaged file still decodes
+    (tmp_path / "good.bmp").write_bytes(good)
+    assert api.load_image(str(tmp_path / "good.bmp")).shape == (8, 8, 4)
