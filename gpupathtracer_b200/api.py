@@ -132,6 +132,38 @@ SYMBOLS = [
     ("pt_set_stage_timing", C.c_int, [_P, C.c_int]),
     ("pt_get_stage_ms", C.c_int, [_P, _F]),
     ("pt_stream", _P, [_P]),
+    ("pt_comm_unique_id", C.c_int, [_P]),
+    ("pt_comm_init", C.c_int, [_P, _P, C.c_int32, C.c_int32]),
+    ("pt_comm_rank", C.c_int32, [_P]),
+    ("pt_comm_world", C.c_int32, [_P]),
+    ("pt_comm_nccl_version", C.c_int, []),
+    ("pt_rank_seed", C.c_uint64, [C.c_uint64, C.c_int32]),
+    ("pt_split_samples", None, [C.c_uint32, C.c_int32, C.c_int32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    ("pt_comm_seed_rng", C.c_int, [_P, C.c_uint64]),
+    ("pt_comm_broadcast_bvh", C.c_int, [_P, C.c_int32]),
+    ("pt_render_batch", C.c_int, [_P, C.c_int32]),
+    ("pt_comm_reset", C.c_int, [_P]),
+    ("pt_comm_num_samples", C.c_uint32, [_P]),
+    ("pt_comm_synchronize", C.c_int, [_P]),
+    ("pt_comm_download_total", C.c_int, [_P, _P]),
+    ("pt_comm_download_batch", C.c_int, [_P, _P]),
+    ("pt_comm_total_device_ptr", _P, [_P]),
+    ("pt_comm_last_reduce_ms", C.c_float, [_P]),
+    ("pt_comm_present_async", C.c_int, [_P, _P]),
+    ("pt_create_multi", C.c_int, [C.POINTER(pt_config), _P, C.c_int32, C.POINTER(_P)]),
+    ("pt_group_destroy", None, [_P]),
+    ("pt_group_size", C.c_int32, [_P]),
+    ("pt_group_context", _P, [_P, C.c_int32]),
+    ("pt_group_share_scene", C.c_int, [_P]),
+    ("pt_group_set_camera", C.c_int, [_P, C.POINTER(pt_camera)]),
+    ("pt_group_seed_rng", C.c_int, [_P, C.c_uint64]),
+    ("pt_group_render_batch", C.c_int, [_P, C.c_int32]),
+    ("pt_group_reset_samples", C.c_int, [_P]),
+    ("pt_group_num_samples", C.c_uint32, [_P]),
+    ("pt_group_synchronize", C.c_int, [_P]),
+    ("pt_group_download_total", C.c_int, [_P, _P]),
+    ("pt_group_present_async", C.c_int, [_P, _P]),
+    ("pt_group_save_screenshot", C.c_int, [_P, C.c_char_p]),
 ]
 
 _lib = None
@@ -404,6 +436,8 @@ class Renderer:
             nodes, refs = self.GetBVH()            # reads the serialised tree back from the device
             scene.set_bvh(nodes, refs)
             stats.sah_cost = self.lib.pt_bvh_sah_cost(_ptr(scene.nodes), scene.nodes.shape[0], _ptr(scene.refs), scene.refs.shape[0])
+        elif bvh == "none":
+            self.bvh_stats = pt_bvh_stats()         # the tree arrives later (CommBroadcastBVH / pt_set_bvh)
         elif bvh == "build" or scene.nodes is None:
             stats = pt_bvh_stats()
             _check(self.lib.pt_build_bvh(ctx, C.byref(stats)))
@@ -592,6 +626,54 @@ class Renderer:
         """Present() whose D2H copy overlaps the next frame (pt_present_async); complete after Synchronize()."""
         _check(self.lib.pt_present_async(self.ctx, num_samples or self.GetNumSamples(), C.c_void_p(host_ptr_u8)))
 
+    # -- several GPUs, one process per GPU (pt_comm_*): samples split across ranks, one NCCL reduce per batch
+    @staticmethod
+    def CommUniqueId():
+        buf = (C.c_uint8 * 128)()
+        _check(load_library().pt_comm_unique_id(buf))
+        return bytes(buf)
+
+    def CommInit(self, unique_id, rank, world):
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        _check(self.lib.pt_comm_init(self.ctx, buf, rank, world))
+        self.rank, self.world = rank, world
+
+    def CommBroadcastBVH(self, root=0):
+        _check(self.lib.pt_comm_broadcast_bvh(self.ctx, root))
+
+    def CommSeedRNG(self, seed):
+        _check(self.lib.pt_comm_seed_rng(self.ctx, seed))
+
+    def RenderBatch(self, camera, n_frames):
+        """n_frames on this rank + the batch's reduce to rank 0 (collective: every rank calls it)."""
+        _check(self.lib.pt_set_camera(self.ctx, C.byref(camera.plane)))
+        _check(self.lib.pt_render_batch(self.ctx, n_frames))
+
+    def CommReset(self):
+        _check(self.lib.pt_comm_reset(self.ctx))
+
+    def CommNumSamples(self):
+        return int(self.lib.pt_comm_num_samples(self.ctx))
+
+    def CommSynchronize(self):
+        _check(self.lib.pt_comm_synchronize(self.ctx))
+
+    def CommDownloadTotal(self):
+        out = np.zeros((self.height, self.width, 4), dtype=np.float32)
+        _check(self.lib.pt_comm_download_total(self.ctx, _ptr(out)))
+        return out
+
+    def CommDownloadBatch(self):
+        out = np.zeros((self.height, self.width, 4), dtype=np.float32)
+        _check(self.lib.pt_comm_download_batch(self.ctx, _ptr(out)))
+        return out
+
+    def CommPresentAsync(self, host_ptr_u8):
+        _check(self.lib.pt_comm_present_async(self.ctx, C.c_void_p(host_ptr_u8)))
+
+    def CommLastReduceMs(self):
+        return float(self.lib.pt_comm_last_reduce_ms(self.ctx))
+
     def AccumDevicePtr(self):
         return int(self.lib.pt_accum_device_ptr(self.ctx))
 
@@ -599,6 +681,99 @@ class Renderer:
         if self.ctx is not None:
             self.lib.pt_destroy(self.ctx)
             self.ctx = None
+
+    def __del__(self):
+        try:
+            self.CleanUp()
+        except Exception:
+            pass
+
+
+class _Borrowed(Renderer):
+    """A Renderer view of a context owned by a MultiRenderer's group (never destroys it)."""
+
+    def __init__(self, ctx, width, height):
+        super().__init__()
+        self.ctx, self.width, self.height = ctx, width, height
+
+    def CleanUp(self):
+        self.ctx = None
+
+
+class MultiRenderer:
+    """One process, one host thread, n GPUs (pt_create_multi): the Renderer interface with the samples of every frame split
+    across the GPUs. RenderFrame(camera, n) renders n frames on EVERY GPU (n x n_gpus samples per pixel) and reduces them to
+    GPU 0, whose running total Present / DownloadAccum / GetNumSamples report."""
+
+    def __init__(self):
+        self.lib = load_library()
+        self.group = None
+
+    def Initialize(self, width, height, scene, n_gpus, device_ids=None, seed=1, bvh="given", **kw):
+        cfg = pt_config(width=width, height=height, max_depth=kw.get("max_depth", REFERENCE_MAX_DEPTH),
+                        microfacet_model=kw.get("microfacet_model", PT_MICROFACET_GGX), device=0,
+                        bvh_layout=kw.get("bvh_layout", PT_BVH_REFERENCE), n_slices=kw.get("n_slices", 0),
+                        sun_light=1 if kw.get("sun_light") else 0, trace_null_shadow=1 if kw.get("trace_null_shadow") else 0,
+                        parity_flags=PT_PARITY_LIBM if kw.get("parity_libm") else 0)
+        ids = (C.c_int32 * n_gpus)(*(device_ids or range(n_gpus)))
+        g = C.c_void_p()
+        _check(self.lib.pt_create_multi(C.byref(cfg), ids, n_gpus, C.byref(g)))
+        self.group, self.width, self.height, self.n_gpus = g, width, height, n_gpus
+        self.scene = scene
+        ctx0 = C.c_void_p(self.lib.pt_group_context(g, 0))
+        r0 = self.rank(0)
+        _check(self.lib.pt_set_triangles(ctx0, _ptr(scene.tris), scene.tris.shape[0]))
+        texs = (pt_texture * max(1, len(scene.textures)))()
+        for i, t in enumerate(scene.textures):
+            texs[i].width, texs[i].height = t.shape[1], t.shape[0]
+            texs[i].rgba = t.ctypes.data_as(C.POINTER(C.c_float))
+        _check(self.lib.pt_set_materials(ctx0, _ptr(scene.materials), scene.materials.shape[0], C.cast(texs, C.c_void_p), len(scene.textures)))
+        _check(self.lib.pt_set_lights(ctx0, _ptr(scene.lights), scene.lights.shape[0], scene.total_light_area))
+        _check(self.lib.pt_set_environment_color(ctx0, _f3(scene.env_color)))
+        if getattr(scene, "env_cubemap", None) is not None:
+            r0.SetEnvironmentCubemap(scene.env_cubemap)
+        stats = pt_bvh_stats()
+        if bvh == "build" or scene.nodes is None:
+            _check(self.lib.pt_build_bvh(ctx0, C.byref(stats)))
+            scene.set_bvh(*r0.GetBVH())
+        else:
+            _check(self.lib.pt_set_bvh(ctx0, _ptr(scene.nodes), scene.nodes.shape[0], _ptr(scene.refs), scene.refs.shape[0]))
+        self.bvh_stats = stats
+        _check(self.lib.pt_group_share_scene(g))          # the other GPUs get copies; the tree is never rebuilt
+        _check(self.lib.pt_group_seed_rng(g, seed))
+        return self
+
+    def rank(self, i):
+        return _Borrowed(C.c_void_p(self.lib.pt_group_context(self.group, i)), self.width, self.height)
+
+    def RenderFrame(self, camera, n_frames=1):
+        _check(self.lib.pt_group_set_camera(self.group, C.byref(camera.plane)))
+        _check(self.lib.pt_group_render_batch(self.group, n_frames))
+
+    def ResetSamples(self):
+        _check(self.lib.pt_group_reset_samples(self.group))
+
+    def GetNumSamples(self):
+        return int(self.lib.pt_group_num_samples(self.group))
+
+    def Synchronize(self):
+        _check(self.lib.pt_group_synchronize(self.group))
+
+    def DownloadAccum(self):
+        out = np.zeros((self.height, self.width, 4), dtype=np.float32)
+        _check(self.lib.pt_group_download_total(self.group, _ptr(out)))
+        return out
+
+    def PresentAsync(self, host_ptr_u8):
+        _check(self.lib.pt_group_present_async(self.group, C.c_void_p(host_ptr_u8)))
+
+    def SaveScreenshot(self, filename):
+        _check(self.lib.pt_group_save_screenshot(self.group, filename.encode()))
+
+    def CleanUp(self):
+        if self.group is not None:
+            self.lib.pt_group_destroy(self.group)
+            self.group = None
 
     def __del__(self):
         try:

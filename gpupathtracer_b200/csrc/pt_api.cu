@@ -1,8 +1,6 @@
 // pt_api.cu -- implementation of the C ABI declared in include/b200pt.h.
 // Owns the context (device buffers, stream, events) and the host->device re-layout of the scene.
-#include "../../include/b200pt.h"
-#include "pt_kernels.h"
-#include "pt_host.h"
+#include "pt_context.h"
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstring>
@@ -19,126 +17,19 @@ using namespace pt;
 static thread_local std::string g_err;
 namespace pt { void set_last_error(const char* msg) { g_err = msg ? msg : ""; } }
 
-static int fail(int code, const char* fmt, ...) {
+int pt_fail(int code, const char* fmt, ...) {
     char buf[1024];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof(buf), fmt, ap); va_end(ap);
     g_err = buf;
     return code;
 }
-#define CK(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t e__ = (call);                                                                  \
-        if (e__ != cudaSuccess)                                                                    \
-            return fail(PT_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
-    } while (0)
 
-template <class T>
-struct DevBuf {
-    T* p = nullptr; size_t n = 0;
-    cudaError_t alloc(size_t count) {
-        if (count <= n && p) return cudaSuccess;
-        release();
-        cudaError_t e = cudaMalloc((void**)&p, (count ? count : 1) * sizeof(T));
-        if (e == cudaSuccess) n = count;
-        return e;
-    }
-    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
-};
-
-struct pt_context {
-    pt_config cfg;
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    // A frame is cut into n_slices ranges of ray indices (pixel-disjoint, so RNG table and accum need no
-    // synchronisation); every slice runs its own raygen -> (extend, shade, shadow)* sequence on its own stream,
-    // so the drain phase of one slice's persistent kernel is filled by another slice's kernels.
-    // Inside a slice, shadow(b) and extend(b+1) run concurrently on two streams (enqueue_frame_dag). The whole
-    // fork/join structure of `g` consecutive frames is captured once into a CUDA graph and replayed.
-    int n_slices = 1, slice_size = 0;
-    std::vector<SliceStreams> slice_streams;
-    std::vector<cudaEvent_t> slice_done;      // 2 per slice (streams a and b)
-    cudaEvent_t ev_fork = nullptr;
-    bool use_graph = true;
-    struct FrameGraph { cudaGraphExec_t exec = nullptr; int launches = 0; };
-    FrameGraph graph;                          // one frame, all slices
-    DevBuf<CameraRec> d_cam;
-    // pt_present_async: double-buffered resolve target + copy stream
-    cudaStream_t copy_stream = nullptr;
-    // host-batch pipeline (trace_host)
-    cudaStream_t in_stream = nullptr;
-    cudaEvent_t ev_h_in[2] = {nullptr, nullptr}, ev_h_done[2] = {nullptr, nullptr}, ev_h_out[2] = {nullptr, nullptr};
-    DevBuf<unsigned char> d_present[2];
-    DevBuf<float4> d_primary[2];
-    cudaEvent_t ev_primary = nullptr, ev_primary_copied[2] = {nullptr, nullptr};
-    int primary_turn = 0;
-    cudaEvent_t ev_resolved = nullptr, ev_copied[2] = {nullptr, nullptr};
-    int present_turn = 0;
-    LaunchDims dims{};
-    float last_ms = 0.0f;
-    pt_counters counters{};
-    uint32_t num_samples = 0;
-
-    // host mirrors (what the reference keeps in triangleVec / nodesVec / referenceVec, Scene.h:23, BVH.h:97-98)
-    std::vector<float> h_tris;
-    HostBvh h_bvh;
-    std::vector<pt_material> h_mats;
-    std::vector<pt_light> h_lights;
-
-    DevBuf<float4> d_tris;
-    DevBuf<BvhPair> d_pairs;
-    DevBuf<LeafTri> d_leaf;
-    DevBuf<unsigned char> d_wide;          // PT_BVH_WIDE / PT_BVH_WIDE4 node bytes
-    DevBuf<LeafTri> d_wide_tris;
-    WideBvh h_wide;
-    // device builder: serialised tree kept on the device, host mirror fetched on demand
-    DevBuf<float4> d_ser_nodes; DevBuf<int> d_ser_refs;
-    bool host_bvh_stale = false; int64_t ser_nodes = 0, ser_refs = 0;
-    float wide_ms = 0.0f;
-    DevBuf<MaterialRec> d_mats;
-    DevBuf<TextureRec> d_texrec;
-    std::vector<float4*> d_texels;
-    DevBuf<float2> d_lights;
-    int n_lights = 0, n_textures = 0, n_leaf = 0;
-    int top_pairs = 0;                     // pair records [0, top_pairs) are the breadth-first top of the tree
-    float total_light_area = 0.0f;
-    float env[3] = {1.0f, 1.0f, 1.0f};
-    DevBuf<float4> d_env; int env_size = 0;      // cubemap faces, 0: constant colour
-    float sun_dir[3] = {0.0f, 1.0f, 0.0f}; float sun_radius = 0.0f;   // set in pt_create
-
-    CameraRec cam{};
-    bool have_cam = false, have_rng = false;
-
-    DevBuf<uint4> d_rng;
-    DevBuf<float4> d_accum_own;
-    float4* d_accum = nullptr;
-    DevBuf<float4> d_q[2][4];
-    DevBuf<uint4> d_qrng[2];
-    DevBuf<float4> d_shadow[4];
-    DevBuf<float4> d_hits;
-    DevBuf<BounceCounters> d_counters;
-    DevBuf<unsigned long long> d_totals;
-    DevBuf<int> d_cursor;
-    // staging for host-pointer batch entry points
-    DevBuf<float4> d_stage_rays, d_stage_hits;
-    DevBuf<unsigned char> d_stage_flags;
-    // processing order of big ray batches (launch_ray_order)
-    DevBuf<unsigned> d_ray_bins, d_ray_bin; DevBuf<int> d_ray_perm;
-    int ray_order = 0;                     // 0 auto, 1 always, -1 never (PT_RAY_ORDER)
-    size_t l2_bytes = 0;
-    DevBuf<float> d_resolve_f32;
-    DevBuf<unsigned char> d_resolve_u8;
-    // per-stage timing (pt_set_stage_timing)
-    bool stage_timing = false;
-    std::vector<cudaEvent_t> stage_events;
-    int stage_frames = 0, stage_events_per_frame = 0;
-};
-
-static void invalidate_graphs(pt_context* c) {
+void pt_invalidate_graphs(pt_context* c) {
     if (c->graph.exec) cudaGraphExecDestroy(c->graph.exec);
     c->graph.exec = nullptr; c->graph.launches = 0;
 }
 
-static SceneDev scene_dev(pt_context* c) {
+SceneDev pt_scene_dev(pt_context* c) {
     SceneDev s{};
     s.pairs = c->d_pairs.p; s.leaf_tris = c->d_leaf.p; s.n_leaf_tris = c->n_leaf; s.top_pairs = c->top_pairs;
     s.wide_nodes = c->d_wide.p; s.wide_tris = c->d_wide_tris.p;
@@ -242,6 +133,7 @@ int pt_create(const pt_config* cfg, pt_context** out) {
 
 void pt_destroy(pt_context* c) {
     if (!c) return;
+    pt_comm_release(c);
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
     c->d_wide.release(); c->d_wide_tris.release(); c->d_ser_nodes.release(); c->d_ser_refs.release();
@@ -281,7 +173,7 @@ void pt_destroy(pt_context* c) {
 }
 
 // host mirror of a device-built tree (nodesVec / referenceVec of the reference), fetched when first needed
-static int ensure_host_bvh(pt_context* c) {
+int pt_ensure_host_bvh(pt_context* c) {
     if (!c->host_bvh_stale) return PT_OK;
     HostBvh b;
     b.nodes.resize(8 * (size_t)c->ser_nodes); b.refs.resize((size_t)c->ser_refs);
@@ -324,7 +216,7 @@ static int upload_wide(pt_context* c) {
 
 // (re)build the leaf triangle stream from host triangles + reference list
 static int upload_leaf_stream(pt_context* c) {
-    { int rc = ensure_host_bvh(c); if (rc != PT_OK) return rc; }
+    { int rc = pt_ensure_host_bvh(c); if (rc != PT_OK) return rc; }
     if (c->h_tris.empty() || c->h_bvh.refs.empty()) return PT_OK;
     const size_t nr = c->h_bvh.refs.size();
     const int64_t nt = (int64_t)(c->h_tris.size() / 20);
@@ -374,7 +266,7 @@ int pt_set_triangles(pt_context* c, const float* tris, int64_t n) {
     if (rc == PT_OK) rc = check_light_tris(c->h_lights.data(), (int32_t)c->h_lights.size(), n, "pt_set_triangles");
     if (rc != PT_OK) return rc;
     CK(cudaSetDevice(c->cfg.device));
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     c->h_tris.assign(tris, tris + 20 * n);
     CK(c->d_tris.alloc(5 * (size_t)n));
     CK(cudaMemcpyAsync(c->d_tris.p, tris, 80 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
@@ -414,13 +306,18 @@ int pt_set_materials(pt_context* c, const pt_material* mats, int32_t n_mats, con
         mats_new.release(); texrec_new.release();
         return fail(PT_ERR_CUDA, "pt_set_materials: %s (the previous materials stay in place)", cudaGetErrorString(e));
     }
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     CK(cudaDeviceSynchronize());                                 // nothing in flight reads the old set
     for (float4* t : c->d_texels) cudaFree(t);
     c->d_mats.release(); c->d_texrec.release();
     c->d_texels.swap(texels);
     c->d_mats = mats_new; c->d_texrec = texrec_new;              // ownership moves (DevBuf is a plain pointer + count)
     c->h_mats.assign(mats, mats + n_mats);
+    c->h_texels.clear(); c->h_texdims.clear();
+    for (int i = 0; i < n_tex; i++) {
+        c->h_texels.emplace_back(tex[i].rgba, tex[i].rgba + 4 * (size_t)tex[i].width * tex[i].height);
+        c->h_texdims.emplace_back(tex[i].width, tex[i].height);
+    }
     c->n_textures = n_tex;
     return PT_OK;
 }
@@ -431,7 +328,7 @@ int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_
     if (rc != PT_OK) return rc;
     CK(cudaSetDevice(c->cfg.device));
     static_assert(sizeof(pt_light) == sizeof(float2), "light record layout");
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     CK(c->d_lights.alloc(n));
     CK(cudaMemcpyAsync(c->d_lights.p, lights, sizeof(pt_light) * n, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -442,7 +339,7 @@ int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_
 
 int pt_set_environment_color(pt_context* c, const float rgb[3]) {
     if (!c || !rgb) return fail(PT_ERR_INVALID, "pt_set_environment_color: bad argument");
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     c->env[0] = rgb[0]; c->env[1] = rgb[1]; c->env[2] = rgb[2];
     if (c->env_size) { CK(cudaSetDevice(c->cfg.device)); CK(cudaDeviceSynchronize()); c->d_env.release(); c->env_size = 0; }
     return PT_OK;
@@ -450,7 +347,7 @@ int pt_set_environment_color(pt_context* c, const float rgb[3]) {
 
 int pt_set_sun(pt_context* c, const float direction[3], float radius) {
     if (!c || !direction || !(radius > 0.0f)) return fail(PT_ERR_INVALID, "pt_set_sun: bad argument");
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     for (int k = 0; k < 3; k++) c->sun_dir[k] = direction[k];
     c->sun_radius = radius;
     return PT_OK;
@@ -460,7 +357,7 @@ int pt_set_environment_cubemap(pt_context* c, const float* faces, int32_t size) 
     if (!c || !faces || size < 1 || size > 16384) return fail(PT_ERR_INVALID, "pt_set_environment_cubemap: bad argument");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaDeviceSynchronize());
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     CK(c->d_env.alloc(6 * (size_t)size * size));
     CK(cudaMemcpy(c->d_env.p, faces, 6 * (size_t)size * size * sizeof(float4), cudaMemcpyHostToDevice));
     c->env_size = size;
@@ -472,7 +369,7 @@ int pt_set_environment_equirect(pt_context* c, const float* rgba, int32_t width,
         return fail(PT_ERR_INVALID, "pt_set_environment_equirect: bad argument");
     CK(cudaSetDevice(c->cfg.device));
     CK(cudaDeviceSynchronize());
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     DevBuf<float4> src;
     CK(src.alloc((size_t)width * height));
     cudaError_t e = cudaMemcpy(src.p, rgba, (size_t)width * height * sizeof(float4), cudaMemcpyHostToDevice);
@@ -552,7 +449,7 @@ static int load_environment_impl(pt_context* c, const char* args) {
 }
 
 static int install_bvh(pt_context* c) {
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     c->host_bvh_stale = false;                                    // the host tree is the authority again
     const float* nodes = c->h_bvh.nodes.data();
     const int n_nodes = (int)(c->h_bvh.nodes.size() / 8);
@@ -661,7 +558,7 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
     if (n < 2 || n > (1 << 29)) return fail(PT_ERR_LIMIT, "pt_build_bvh_device: 2 .. 2^29 triangles");
     CK(cudaSetDevice(c->cfg.device));
     auto t0 = std::chrono::steady_clock::now();
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     // the serialised tree stays on the device (read back only when somebody asks for it: pt_get_bvh, wide collapse);
     // the traversal layout (pair records + leaf stream) is written by the build kernels themselves
     CK(c->d_ser_nodes.alloc(2 * (size_t)(2 * n - 1)));
@@ -694,7 +591,7 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
     c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = (int)n;
     c->host_bvh_stale = true; c->ser_nodes = 2 * n - 1; c->ser_refs = n;
     if (c->cfg.bvh_layout != PT_BVH_REFERENCE) {                 // the wide collapse runs on the host
-        int rc = ensure_host_bvh(c);
+        int rc = pt_ensure_host_bvh(c);
         if (rc != PT_OK) return rc;
         if ((rc = upload_wide(c)) != PT_OK) return rc;
     }
@@ -758,7 +655,7 @@ static int load_scene_impl(pt_context* c, const char* scene_path, const char* en
 
 int pt_get_bvh(pt_context* c, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs) {
     if (!c || !n_nodes || !n_refs) return fail(PT_ERR_INVALID, "pt_get_bvh: bad argument");
-    { CK(cudaSetDevice(c->cfg.device)); int rc = ensure_host_bvh(c); if (rc != PT_OK) return rc; }
+    { CK(cudaSetDevice(c->cfg.device)); int rc = pt_ensure_host_bvh(c); if (rc != PT_OK) return rc; }
     *n_nodes = (int32_t)(c->h_bvh.nodes.size() / 8);
     *n_refs = (int32_t)c->h_bvh.refs.size();
     if (nodes) memcpy(nodes, c->h_bvh.nodes.data(), c->h_bvh.nodes.size() * 4);
@@ -824,12 +721,12 @@ static int order_rays(pt_context* c, const float4* d_rays, int64_t n, const int*
     CK(c->d_ray_bins.alloc((1 << 21) + 2048));                  // counters + scan tile totals (launch_ray_order)
     CK(c->d_ray_bin.alloc((size_t)n));
     CK(c->d_ray_perm.alloc((size_t)n));
-    c->counters.kernel_launches += launch_ray_order(scene_dev(c), d_rays, n, c->d_ray_bins.p, c->d_ray_bin.p, c->d_ray_perm.p, c->stream);
+    c->counters.kernel_launches += launch_ray_order(pt_scene_dev(c), d_rays, n, c->d_ray_bins.p, c->d_ray_bin.p, c->d_ray_perm.p, c->stream);
     *perm = c->d_ray_perm.p;
     return PT_OK;
 }
 
-static int check_scene(pt_context* c, const char* who, bool need_shading) {
+int pt_check_scene(pt_context* c, const char* who, bool need_shading) {
     if (!c->d_pairs.p || !c->d_leaf.p || !c->d_tris.p) return fail(PT_ERR_INVALID, "%s: triangles and BVH must be set first", who);
     if (need_shading) {
         if (!c->d_mats.p) return fail(PT_ERR_INVALID, "%s: materials not set", who);
@@ -843,7 +740,7 @@ static int check_scene(pt_context* c, const char* who, bool need_shading) {
 // parameters of the launch sequence that owns ray indices [first, first + count); counter block `block`
 static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, int block = 0) {
     FrameParams p{};
-    p.scene = scene_dev(c);
+    p.scene = pt_scene_dev(c);
     p.cam = c->d_cam.p;
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.slice_first = first; p.slice_count = count < 0 ? c->cfg.width * c->cfg.height : count;
@@ -866,7 +763,7 @@ static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, in
 
 // `g` consecutive frames of every slice between a fork from and a join into the main stream. Slices advance through
 // their frames independently; stream-capturable (every cross-stream edge is an event).
-static int enqueue_frames(pt_context* c, int g) {
+int pt_enqueue_frames(pt_context* c, int g) {
     const int npx = c->cfg.width * c->cfg.height;
     int launches = 0;
     cudaEventRecord(c->ev_fork, c->stream);
@@ -891,7 +788,7 @@ static int ensure_graph(pt_context* c) {
     if (c->graph.exec) return PT_OK;
     cudaGraph_t graph = nullptr;
     CK(cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
-    int launches = enqueue_frames(c, 1);
+    int launches = pt_enqueue_frames(c, 1);
     cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
     if (e != cudaSuccess || !graph) { cudaGetLastError(); return fail(PT_ERR_CUDA, "frame graph capture failed: %s", cudaGetErrorString(e)); }
     e = cudaGraphInstantiate(&c->graph.exec, graph, 0);
@@ -904,7 +801,7 @@ static int ensure_graph(pt_context* c) {
 int pt_render_frames(pt_context* c, int32_t n_frames) {
     if (!c || n_frames < 0) return fail(PT_ERR_INVALID, "pt_render_frames: bad argument");
     CK(cudaSetDevice(c->cfg.device));
-    int rc = check_scene(c, "pt_render_frames", true);
+    int rc = pt_check_scene(c, "pt_render_frames", true);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
     const int epf = 3 * c->cfg.max_depth + 3;
@@ -927,7 +824,7 @@ int pt_render_frames(pt_context* c, int32_t n_frames) {
         c->counters.kernel_launches += c->graph.launches;
     } else {
         // batches: slices run through all their frames without a join in between (measured faster than replaying graphs)
-        c->counters.kernel_launches += enqueue_frames(c, n_frames);
+        c->counters.kernel_launches += pt_enqueue_frames(c, n_frames);
     }
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaGetLastError());
@@ -964,7 +861,7 @@ int pt_download_accum(pt_context* c, float* rgba) {
 void* pt_accum_device_ptr(pt_context* c) { return c ? (void*)c->d_accum : nullptr; }
 int pt_set_accum_device_ptr(pt_context* c, void* dev_rgba) {
     if (!c) return fail(PT_ERR_INVALID, "pt_set_accum_device_ptr: null context");
-    invalidate_graphs(c);
+    pt_invalidate_graphs(c);
     c->d_accum = dev_rgba ? (float4*)dev_rgba : c->d_accum_own.p;
     return PT_OK;
 }
@@ -1069,7 +966,7 @@ int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) 
 int pt_trace_primary_async(pt_context* c, float* host_hits) {
     if (!c || !host_hits) return fail(PT_ERR_INVALID, "pt_trace_primary_async: bad argument");
     CK(cudaSetDevice(c->cfg.device));
-    int rc = check_scene(c, "pt_trace_primary_async", false);
+    int rc = pt_check_scene(c, "pt_trace_primary_async", false);
     if (rc != PT_OK) return rc;
     if (!c->have_cam || !c->have_rng) return fail(PT_ERR_INVALID, "pt_trace_primary_async: camera and RNG table must be set");
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
@@ -1118,12 +1015,12 @@ int pt_save_screenshot(pt_context* c, const char* path) {
 int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* d_hits) {
     if (!c || !d_rays || !d_hits || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_closest_device: bad argument");
     CK(cudaSetDevice(c->cfg.device));
-    int rc = check_scene(c, "pt_trace_closest", false);
+    int rc = pt_check_scene(c, "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
     const int* perm = nullptr;
     if ((rc = order_rays(c, (const float4*)d_rays, n, &perm)) != PT_OK) return rc;
-    launch_trace_closest(scene_dev(c), (const float4*)d_rays, n, (float4*)d_hits, c->d_cursor.p, c->dims, c->stream, perm);
+    launch_trace_closest(pt_scene_dev(c), (const float4*)d_rays, n, (float4*)d_hits, c->d_cursor.p, c->dims, c->stream, perm);
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaGetLastError());
     c->counters.kernel_launches++;
@@ -1133,12 +1030,12 @@ int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* 
 int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_flags) {
     if (!c || !d_rays || !d_flags || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_any_device: bad argument");
     CK(cudaSetDevice(c->cfg.device));
-    int rc = check_scene(c, "pt_trace_any", false);
+    int rc = pt_check_scene(c, "pt_trace_any", false);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
     const int* perm = nullptr;
     if ((rc = order_rays(c, (const float4*)d_rays, n, &perm)) != PT_OK) return rc;
-    launch_trace_any(scene_dev(c), (const float4*)d_rays, n, (unsigned char*)d_flags, c->d_cursor.p, c->dims, c->stream, perm);
+    launch_trace_any(pt_scene_dev(c), (const float4*)d_rays, n, (unsigned char*)d_flags, c->d_cursor.p, c->dims, c->stream, perm);
     CK(cudaEventRecord(c->ev1, c->stream));
     CK(cudaGetLastError());
     c->counters.kernel_launches++;
@@ -1153,7 +1050,7 @@ int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_fl
 
 static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, size_t out_bytes, bool any) {
     CK(cudaSetDevice(c->cfg.device));
-    int rc = check_scene(c, any ? "pt_trace_any" : "pt_trace_closest", false);
+    int rc = pt_check_scene(c, any ? "pt_trace_any" : "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
     const int64_t chunk = n < kHostChunk ? n : kHostChunk;
     CK(c->d_stage_rays.alloc(2 * 2 * (size_t)chunk));                 // 2 buffers x 2 float4 per ray
@@ -1180,14 +1077,14 @@ static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, si
         if ((rc = order_rays(c, d_rays, m, &perm)) != PT_OK) return rc;
         if (any) {
             unsigned char* d_out = c->d_stage_flags.p + (size_t)k * chunk;
-            launch_trace_any(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream, perm);
+            launch_trace_any(pt_scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream, perm);
             CK(cudaEventRecord(c->ev_h_done[k], c->stream));
             CK(cudaStreamWaitEvent(c->copy_stream, c->ev_h_done[k], 0));
             CK(cudaMemcpyAsync((unsigned char*)out + first, d_out, (size_t)m, cudaMemcpyDeviceToHost, c->copy_stream));
             c->counters.shadow_rays += (uint64_t)m;
         } else {
             float4* d_out = c->d_stage_hits.p + (size_t)k * chunk;
-            launch_trace_closest(scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream, perm);
+            launch_trace_closest(pt_scene_dev(c), d_rays, m, d_out, c->d_cursor.p, c->dims, c->stream, perm);
             CK(cudaEventRecord(c->ev_h_done[k], c->stream));
             CK(cudaStreamWaitEvent(c->copy_stream, c->ev_h_done[k], 0));
             CK(cudaMemcpyAsync((char*)out + out_bytes * first, d_out, out_bytes * (size_t)m, cudaMemcpyDeviceToHost, c->copy_stream));

@@ -1,32 +1,45 @@
-"""Multi-GPU sample split: every rank renders its share of the samples of EVERY pixel with its own
-RNG table; the accumulation buffers (running sums) are added with ONE reduce per batch. Backend-agnostic
-(`nccl` on GPUs over NVLink, `gloo` in the CPU tests); there is no data-path collective besides that reduce."""
-import torch
-import torch.distributed as dist
+"""One process per GPU (torchrun): the glue between torch.distributed's rendezvous and the library's own NCCL communicator.
+
+The sample split itself -- per-rank RNG seeds, double-buffered batch accumulators, the ncclReduce per batch on its own
+stream, the BVH broadcast -- lives in the library (csrc/pt_comm.cu, include/b200pt.h "several GPUs"). torch.distributed is
+only the launcher-side channel that carries the 128-byte NCCL id from rank 0 to the others; MPI or a file would do as well.
+"""
+import os
+
+from .api import Renderer, load_library
 
 
-def split_samples(total_spp, world_size):
-    """spp per rank: as even as possible, remainder to the low ranks; sums to total_spp."""
-    base, rem = divmod(int(total_spp), int(world_size))
-    return [base + (1 if r < rem else 0) for r in range(world_size)]
+def env_rank_world():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
 
 
 def rank_seed(seed, rank):
-    """Decorrelated per-rank RNG-table seed (seed ^ golden-ratio hash of the rank)."""
-    return (int(seed) ^ ((int(rank) * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF)) & 0xFFFFFFFFFFFFFFFF
+    """pt_rank_seed: the seed rank `rank` gives pt_seed_rng (rank 0 keeps `seed`, so a 1-GPU run is unchanged)."""
+    return int(load_library().pt_rank_seed(seed, rank))
 
 
-def reduce_accum(accum, dst=0, group=None):
-    """Sum the per-rank accumulation buffers into rank `dst` (in place there). accum: (H, W, 4) float32 running sums;
-    alpha (forced to 1 by every store, Iterative.comp:263) is restored to 1 on the destination."""
-    if not dist.is_initialized() or dist.get_world_size(group) == 1:
-        return accum
-    dist.reduce(accum, dst=dst, op=dist.ReduceOp.SUM, group=group)
-    if dist.get_rank(group) == dst:
-        accum[..., 3] = 1.0
-    return accum
+def split_samples(total_spp, world, rank):
+    """pt_split_samples: (first, count) of the samples per pixel that belong to `rank` when `total_spp` is fixed."""
+    import ctypes as C
+    f, n = C.c_uint32(), C.c_uint32()
+    load_library().pt_split_samples(total_spp, world, rank, C.byref(f), C.byref(n))
+    return int(f.value), int(n.value)
 
 
-def mean_image(accum_sum, total_spp):
-    """Present.frag:30 normalisation of the reduced sum."""
-    return accum_sum[..., :3] / float(total_spp)
+def exchange_unique_id(dist, rank, make_id=None):
+    """Rank 0 creates the id (pt_comm_unique_id), everybody receives it through torch.distributed (any backend)."""
+    box = [(make_id or Renderer.CommUniqueId)() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
+
+
+def init_comm(renderer, dist=None):
+    """Attach the library's communicator to `renderer` (this process's context). `dist`: an initialised torch.distributed
+    module; None reads RANK / WORLD_SIZE and does nothing for a single process."""
+    rank, world, _ = env_rank_world()
+    if world == 1:
+        return rank, world
+    if dist is None:
+        import torch.distributed as dist
+    renderer.CommInit(exchange_unique_id(dist, rank), rank, world)
+    return rank, world

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define B200PT_ABI_VERSION 2
+#define B200PT_ABI_VERSION 3
 
 typedef enum pt_status {
     PT_OK = 0,
@@ -305,6 +305,58 @@ int pt_set_stage_timing(pt_context* ctx, int on);
 int pt_get_stage_ms(pt_context* ctx, float out[5]);
 /* cudaStream_t the library launches on (for callers that record their own events). */
 void* pt_stream(pt_context* ctx);
+
+/* ---- several GPUs: samples split across ranks, one NCCL reduce per batch ----
+ * RenderFrame (Renderer.cpp:651-662) adds one sample to every pixel; with N GPUs every rank adds its own samples of every
+ * pixel to a private sum (scene + BVH replicated, RNG tables decorrelated by rank) and a batch of frames ends with ONE
+ * ncclReduce(sum) of the RGBA32F sums to rank 0, which keeps the running total. Two batch accumulators alternate and the
+ * reduce runs on its own stream, so the reduce of batch k overlaps the rendering of batch k + 1. fp32 addition order differs
+ * from a 1-GPU run: N-GPU images are compared by relMSE, not bitwise. NCCL is bound at run time (dlopen of libnccl.so.2,
+ * the copy already in the process if there is one; PT_NCCL_LIB overrides); contexts without a communicator never load it.
+ *
+ * One process per GPU (torchrun, MPI): rank 0 calls pt_comm_unique_id, the caller's launcher moves the 128 bytes to the
+ * other ranks, every rank calls pt_comm_init on its own context. */
+#define PT_COMM_ID_BYTES 128
+int pt_comm_unique_id(uint8_t id[PT_COMM_ID_BYTES]);
+int pt_comm_init(pt_context* ctx, const uint8_t id[PT_COMM_ID_BYTES], int32_t rank, int32_t world);
+int32_t pt_comm_rank(pt_context* ctx);
+int32_t pt_comm_world(pt_context* ctx);
+int pt_comm_nccl_version(void);                                   /* e.g. 22809; 0 when NCCL cannot be loaded */
+uint64_t pt_rank_seed(uint64_t seed, int32_t rank);               /* the seed rank `rank` passes to pt_seed_rng (host arithmetic) */
+void pt_split_samples(uint32_t total_spp, int32_t world, int32_t rank, uint32_t* first, uint32_t* count);  /* rank's share of a fixed total */
+int pt_comm_seed_rng(pt_context* ctx, uint64_t seed);             /* pt_seed_rng(ctx, pt_rank_seed(seed, rank)) */
+/* The tree is built once: the root rank's BVH (any builder) reaches the others as device-to-device broadcasts of the traversal
+ * layout and the serialised form; pt_set_triangles must have been called on every rank. Binary layout only. */
+int pt_comm_broadcast_bvh(pt_context* ctx, int32_t root);
+/* n_frames on this rank (and on every other rank: a collective call), then the batch's reduce to rank 0, asynchronous. */
+int pt_render_batch(pt_context* ctx, int32_t n_frames);
+int pt_comm_reset(pt_context* ctx);                               /* ResetSamples for the running total */
+uint32_t pt_comm_num_samples(pt_context* ctx);                    /* samples per pixel in the total: world x frames so far */
+int pt_comm_synchronize(pt_context* ctx);
+int pt_comm_download_total(pt_context* ctx, float* rgba);         /* rank 0: the running total (sum); other ranks: no-op */
+int pt_comm_download_batch(pt_context* ctx, float* rgba);         /* this rank's own sum of the last batch (what it sent) */
+void* pt_comm_total_device_ptr(pt_context* ctx);                  /* rank 0, else NULL */
+float pt_comm_last_reduce_ms(pt_context* ctx);                    /* CUDA-event time of the last ncclReduce on its stream */
+int pt_comm_present_async(pt_context* ctx, uint8_t* host_rgb_u8); /* rank 0: Present of total / samples, as pt_present_async */
+
+/* One process, one host thread, n GPUs (ncclCommInitAll): the form b200pt::Renderer::Initialize(.., n_gpus) uses.
+ * device_ids NULL = 0 .. n-1. n = 1 is a plain context without NCCL. Load or upload the scene into pt_group_context(g, 0),
+ * then pt_group_share_scene copies tables, textures, environment and the BVH as built to the other GPUs. */
+typedef struct pt_group pt_group;
+int pt_create_multi(const pt_config* cfg, const int32_t* device_ids, int32_t n, pt_group** out);
+void pt_group_destroy(pt_group* g);
+int32_t pt_group_size(pt_group* g);
+pt_context* pt_group_context(pt_group* g, int32_t i);
+int pt_group_share_scene(pt_group* g);
+int pt_group_set_camera(pt_group* g, const pt_camera* cam);
+int pt_group_seed_rng(pt_group* g, uint64_t seed);
+int pt_group_render_batch(pt_group* g, int32_t n_frames_per_gpu);
+int pt_group_reset_samples(pt_group* g);
+uint32_t pt_group_num_samples(pt_group* g);
+int pt_group_synchronize(pt_group* g);
+int pt_group_download_total(pt_group* g, float* rgba);
+int pt_group_present_async(pt_group* g, uint8_t* host_rgb_u8);
+int pt_group_save_screenshot(pt_group* g, const char* path);      /* Renderer::SaveScreenshot of the combined image */
 
 #ifdef __cplusplus
 }

@@ -42,11 +42,12 @@ public:
     ~Renderer() { CleanUp(); }
 
     // Renderer::Initialize(Window*, scenePath, env) (Renderer.cpp:448-636): scene assembly, BVH build, uploads, RNG tables.
-    void Initialize(const Window* window, const SceneArrays& scene, int max_depth = 66, uint64_t seed = 0) {
-        pt_config cfg{};
-        cfg.width = (int32_t)window->Width; cfg.height = (int32_t)window->Height;
-        cfg.max_depth = max_depth; cfg.microfacet_model = PT_MICROFACET_GGX; cfg.device = 0; cfg.bvh_layout = PT_BVH_REFERENCE;
-        check(pt_create(&cfg, &ctx_));
+    // n_gpus > 1: the samples of every RenderFrame are split across that many GPUs (one host thread, NCCL reduce to GPU 0);
+    // the scene is loaded and the tree built ONCE, on GPU 0, and copied to the others.
+    void Initialize(const Window* window, const SceneArrays& scene, int max_depth = 66, uint64_t seed = 0, int n_gpus = 1,
+                    int microfacet_model = PT_MICROFACET_GGX) {
+        create(window, max_depth, microfacet_model, PT_BVH_REFERENCE, n_gpus);
+        pt_context* ctx = pt_group_context(group_, 0);
         const int64_t n = (int64_t)scene.mat_ids.size();
         std::vector<float> tris((size_t)n * 20);
         check(pt_assemble_triangles(scene.verts.data(), scene.mat_ids.data(), n, tris.data()));           // Scene.cpp:263-292
@@ -56,54 +57,64 @@ public:
         std::vector<pt_light> lights((size_t)nl);
         pt_build_light_table(tris.data(), n, scene.materials.data(), (int32_t)scene.materials.size(), lights.data(), nl, &total);
         pt_presubtract_edges(tris.data(), n);                                                                // Scene.cpp:334-337
-        check(pt_set_triangles(ctx_, tris.data(), n));
-        check(pt_set_materials(ctx_, scene.materials.data(), (int32_t)scene.materials.size(), scene.textures.data(),
+        check(pt_set_triangles(ctx, tris.data(), n));
+        check(pt_set_materials(ctx, scene.materials.data(), (int32_t)scene.materials.size(), scene.textures.data(),
                                (int32_t)scene.textures.size()));
-        check(pt_set_lights(ctx_, lights.data(), nl, total));
-        check(pt_set_environment_color(ctx_, scene.env_color));
-        check(pt_build_bvh(ctx_, &bvh_stats_));                                                              // Scene.cpp:294
-        check(pt_seed_rng(ctx_, seed));                                                                      // Renderer.cpp:545-553
-        width_ = window->Width; height_ = window->Height;
+        check(pt_set_lights(ctx, lights.data(), nl, total));
+        check(pt_set_environment_color(ctx, scene.env_color));
+        check(pt_build_bvh(ctx, &bvh_stats_));                                                               // Scene.cpp:294
+        finish(seed);
     }
     // The reference's own signature: Initialize(Window*, scenePath, env) (Renderer.cpp:448, called at Program.cpp:81).
     // scenePath is an .obj (the only live loader, Scene.cpp:248-259); env is any LoadEnvironmnet string: "GENERATE COLOR WHITE",
     // a .hdr / .jpg equirectangular image, or a text file naming six cube faces.
     void Initialize(const Window* window, const char* scenePath, const std::string& env, int max_depth = 66, uint64_t seed = 0,
-                    int bvh_layout = PT_BVH_REFERENCE) {
-        pt_config cfg{};
-        cfg.width = (int32_t)window->Width; cfg.height = (int32_t)window->Height;
-        cfg.max_depth = max_depth; cfg.microfacet_model = PT_MICROFACET_GGX; cfg.device = 0; cfg.bvh_layout = bvh_layout;
-        check(pt_create(&cfg, &ctx_));
-        check(pt_load_scene(ctx_, scenePath, env.c_str(), &bvh_stats_));                                    // Scene::LoadScene
-        check(pt_seed_rng(ctx_, seed));
-        width_ = window->Width; height_ = window->Height;
+                    int bvh_layout = PT_BVH_REFERENCE, int n_gpus = 1, int microfacet_model = PT_MICROFACET_GGX) {
+        create(window, max_depth, microfacet_model, bvh_layout, n_gpus);
+        check(pt_load_scene(pt_group_context(group_, 0), scenePath, env.c_str(), &bvh_stats_));             // Scene::LoadScene
+        finish(seed);
     }
-    void RenderFrame(const Camera& camera) {                      // Renderer.cpp:651-662
-        check(pt_set_camera(ctx_, &camera.Plane()));
-        check(pt_render_frames(ctx_, 1));
+    void RenderFrame(const Camera& camera) {                      // Renderer.cpp:651-662: +1 sample per pixel on every GPU
+        check(pt_group_set_camera(group_, &camera.Plane()));
+        check(pt_group_render_batch(group_, 1));
     }
     // Renderer::Present (Renderer.cpp:681-685): headless resolve into a host buffer (width*height*3 bytes, row 0 = bottom).
-    void Present(uint8_t* rgb8) { check(pt_resolve(ctx_, pt_num_samples(ctx_), nullptr, rgb8)); }
+    void Present(uint8_t* rgb8) { PresentAsync(rgb8); Synchronize(); }
     // The same without stalling the render stream: the copy to (pinned) host memory overlaps the next RenderFrame;
     // the image is complete after Synchronize(). At most two presents in flight.
-    void PresentAsync(uint8_t* rgb8) { check(pt_present_async(ctx_, pt_num_samples(ctx_), rgb8)); }
-    void Synchronize() { check(pt_synchronize(ctx_)); }
-    void ResetSamples() { check(pt_reset_samples(ctx_)); }        // Renderer.cpp:687-691
-    uint32_t GetNumSamples() { return pt_num_samples(ctx_); }     // Renderer.cpp:693-695
-    void SaveScreenshot(const std::string& filename) { check(pt_save_screenshot(ctx_, filename.c_str())); }   // :697-705
-    // beyond the reference: a long render that survives a restart (RNG table + running sum + numSamples)
-    void SaveCheckpoint(const std::string& path) { check(pt_checkpoint_save(ctx_, path.c_str())); }
-    void LoadCheckpoint(const std::string& path) { check(pt_checkpoint_load(ctx_, path.c_str())); }
+    void PresentAsync(uint8_t* rgb8) { check(pt_group_present_async(group_, rgb8)); }
+    void Synchronize() { check(pt_group_synchronize(group_)); }
+    void ResetSamples() { check(pt_group_reset_samples(group_)); }   // Renderer.cpp:687-691
+    uint32_t GetNumSamples() { return pt_group_num_samples(group_); }   // Renderer.cpp:693-695 (all GPUs together)
+    void SaveScreenshot(const std::string& filename) { check(pt_group_save_screenshot(group_, filename.c_str())); }   // :697-705
+    // beyond the reference: a long render that survives a restart (RNG table + running sum + numSamples); single GPU
+    void SaveCheckpoint(const std::string& path) { check(pt_checkpoint_save(Context(), path.c_str())); }
+    void LoadCheckpoint(const std::string& path) { check(pt_checkpoint_load(Context(), path.c_str())); }
     // LoadEnvironmnet (Renderer.cpp:236-323) after Initialize, e.g. to swap the sky of a loaded scene
-    void LoadEnvironment(const std::string& args) { check(pt_load_environment(ctx_, args.c_str())); }
-    void CleanUp() { if (ctx_) { pt_destroy(ctx_); ctx_ = nullptr; } }                                       // :638-647
+    void LoadEnvironment(const std::string& args) {
+        check(pt_load_environment(Context(), args.c_str()));
+        if (pt_group_size(group_) > 1) check(pt_group_share_scene(group_));
+    }
+    void CleanUp() { if (group_) { pt_group_destroy(group_); group_ = nullptr; } }                           // :638-647
     // Renderer::RenderReference (the stale CPU renderer, Renderer.cpp:1075-1187) has no counterpart: out of scope.
     const pt_bvh_stats& BvhStats() const { return bvh_stats_; }
-    pt_context* Context() { return ctx_; }
+    pt_context* Context() { return group_ ? pt_group_context(group_, 0) : nullptr; }
+    int NumGpus() { return group_ ? pt_group_size(group_) : 0; }
 
 private:
     static void check(int rc) { if (rc != PT_OK) throw std::runtime_error(pt_last_error()); }
-    pt_context* ctx_ = nullptr;
+    void create(const Window* window, int max_depth, int microfacet_model, int bvh_layout, int n_gpus) {
+        pt_config cfg{};
+        cfg.width = (int32_t)window->Width; cfg.height = (int32_t)window->Height;
+        cfg.max_depth = max_depth; cfg.microfacet_model = microfacet_model; cfg.bvh_layout = bvh_layout;
+        check(pt_create_multi(&cfg, nullptr, n_gpus, &group_));        // devices 0 .. n_gpus-1
+        width_ = window->Width; height_ = window->Height;
+    }
+    void finish(uint64_t seed) {
+        if (pt_group_size(group_) > 1) check(pt_group_share_scene(group_));
+        check(pt_group_seed_rng(group_, seed));                                                              // Renderer.cpp:545-553
+    }
+    pt_group* group_ = nullptr;
     pt_bvh_stats bvh_stats_{};
     uint32_t width_ = 0, height_ = 0;
 };

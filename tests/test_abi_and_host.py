@@ -30,7 +30,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), f"{n} declared in include/b200pt.h but not exported by {LIB_PATH}"
     bound = {n for n, _, _ in SYMBOLS}
     assert set(names) == bound, f"python binding and header disagree: {set(names) ^ bound}"
-    assert lib.pt_abi_version() == 2
+    assert lib.pt_abi_version() == 3
 
 
 def test_no_cpu_fallback_create_fails_loudly_without_a_gpu():
