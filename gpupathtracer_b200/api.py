@@ -124,6 +124,8 @@ SYMBOLS = [
     ("pt_trace_any", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_trace_closest_device", C.c_int, [_P, _P, C.c_int64, _P]),
     ("pt_trace_any_device", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_trace_closest_device_noalloc", C.c_int, [_P, _P, C.c_int64, _P]),
+    ("pt_noalloc_max_rays", C.c_int64, []),
     ("pt_raygen_probe", C.c_int, [_P, C.c_int64, C.c_int64, _P]),
     ("pt_trace_primary_async", C.c_int, [_P, _P]),
     ("pt_parity_libm_probe", C.c_int, [_P, C.c_int32, _P, _P, C.c_int64, _P]),
@@ -566,6 +568,10 @@ class Renderer:
     def TraceClosestDevice(self, d_rays, n, d_hits):
         """Device-resident batch (raw device pointers); asynchronous on the library's stream."""
         _check(self.lib.pt_trace_closest_device(self.ctx, C.c_void_p(d_rays), n, C.c_void_p(d_hits)))
+
+    def TraceClosestDeviceNoAlloc(self, d_rays, n, d_hits):
+        """pt_trace_closest_device_noalloc: the binned trace with its scratch in a fixed __device__ array (no allocation)."""
+        _check(self.lib.pt_trace_closest_device_noalloc(self.ctx, C.c_void_p(d_rays), n, C.c_void_p(d_hits)))
 
     def TraceAnyDevice(self, d_rays, n, d_flags):
         _check(self.lib.pt_trace_any_device(self.ctx, C.c_void_p(d_rays), n, C.c_void_p(d_flags)))

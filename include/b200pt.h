@@ -280,6 +280,18 @@ int pt_trace_any(pt_context* ctx, const float* rays, int64_t n, uint8_t* flags);
 int pt_trace_closest_device(pt_context* ctx, const void* d_rays, int64_t n, void* d_hits);
 int pt_trace_any_device(pt_context* ctx, const void* d_rays, int64_t n, void* d_flags);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it). Same contract and same results as
+ * pt_trace_closest_device (rays always traced in binned order), but the call allocates nothing: the scratch of the binned trace
+ * (work cursor, bin counters, per-ray bin ids, permutation) lives in a file-scope __device__ array of fixed size inside the
+ * library (csrc/pt_noalloc.cu), so the call issues only memsets and kernel launches on the context's stream (asynchronous, like
+ * pt_trace_closest_device). Limits and caveats: at most PT_NOALLOC_MAX_RAYS rays per call (PT_ERR_LIMIT beyond); binary BVH layout
+ * only; the array costs ~9.4 MB on every GPU that loads the library, until exit; it is shared by all calls and contexts on a GPU
+ * and keeps the last call's contents (each call clears what must start at zero), so calls that overlap on one GPU race -- serialise them. */
+#define PT_NOALLOC_MAX_RAYS (1 << 20)
+int pt_trace_closest_device_noalloc(pt_context* ctx, const void* d_rays, int64_t n, void* d_hits);
+int64_t pt_noalloc_max_rays(void);
+
 /* One primary ray per pixel exactly as RenderFrame's first bounce traces it -- InitRay (Iterative.comp:174-210: pixel jitter +
  * thin-lens sample from the pixel's RNG state, which is NOT advanced) and IfIfClosestHit -- with the hit records
  * {t, u, v, triangle id (int bits, -1 = miss)} delivered in PIXEL order (y * width + x) to host memory. Asynchronous like
