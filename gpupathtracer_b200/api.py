@@ -42,7 +42,9 @@ class pt_texture(C.Structure):
 
 class pt_counters(C.Structure):
     _fields_ = [("closest_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("paths", C.c_uint64),
-                ("frames", C.c_uint64), ("kernel_launches", C.c_uint64), ("null_shadow_rays", C.c_uint64)]
+                ("frames", C.c_uint64), ("kernel_launches", C.c_uint64), ("null_shadow_rays", C.c_uint64),
+                ("closest_pair_tests", C.c_uint64), ("closest_tri_tests", C.c_uint64), ("shadow_pair_tests", C.c_uint64),
+                ("shadow_tri_tests", C.c_uint64), ("counted_closest_rays", C.c_uint64), ("counted_shadow_rays", C.c_uint64)]
 
 
 class pt_bvh_stats(C.Structure):
@@ -130,6 +132,7 @@ SYMBOLS = [
     ("pt_trace_primary_async", C.c_int, [_P, _P]),
     ("pt_parity_libm_probe", C.c_int, [_P, C.c_int32, _P, _P, C.c_int64, _P]),
     ("pt_get_counters", C.c_int, [_P, C.POINTER(pt_counters)]),
+    ("pt_set_visit_counting", C.c_int, [_P, C.c_int]),
     ("pt_last_device_ms", C.c_float, [_P]),
     ("pt_set_stage_timing", C.c_int, [_P, C.c_int]),
     ("pt_get_stage_ms", C.c_int, [_P, _F]),
@@ -151,6 +154,7 @@ SYMBOLS = [
     ("pt_comm_download_batch", C.c_int, [_P, _P]),
     ("pt_comm_total_device_ptr", _P, [_P]),
     ("pt_comm_last_reduce_ms", C.c_float, [_P]),
+    ("pt_comm_last_batch_ms", C.c_float, [_P]),
     ("pt_comm_present_async", C.c_int, [_P, _P]),
     ("pt_create_multi", C.c_int, [C.POINTER(pt_config), _P, C.c_int32, C.POINTER(_P)]),
     ("pt_group_destroy", None, [_P]),
@@ -613,6 +617,10 @@ class Renderer:
         _check(self.lib.pt_get_counters(self.ctx, C.byref(c)))
         return {k: int(getattr(c, k)) for k, _ in pt_counters._fields_}
 
+    def SetVisitCounting(self, on=True):
+        """Instrumented traversal kernels: Counters() then carries pair / triangle tests of the rays traced meanwhile."""
+        _check(self.lib.pt_set_visit_counting(self.ctx, 1 if on else 0))
+
     def LastDeviceMs(self):
         return float(self.lib.pt_last_device_ms(self.ctx))
 
@@ -676,6 +684,9 @@ class Renderer:
 
     def CommPresentAsync(self, host_ptr_u8):
         _check(self.lib.pt_comm_present_async(self.ctx, C.c_void_p(host_ptr_u8)))
+
+    def CommLastBatchMs(self):
+        return float(self.lib.pt_comm_last_batch_ms(self.ctx))
 
     def CommLastReduceMs(self):
         return float(self.lib.pt_comm_last_reduce_ms(self.ctx))

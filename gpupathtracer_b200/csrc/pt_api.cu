@@ -24,6 +24,10 @@ int pt_fail(int code, const char* fmt, ...) {
     return code;
 }
 
+// every entry point that touches device state the slices may still be working on: select the device, then make `stream`
+// wait for the slices (a device-side wait; nothing to do unless chained frames are pending)
+#define PT_ENTER(c) do { CK(cudaSetDevice((c)->cfg.device)); int rcj__ = pt_join_slices(c); if (rcj__ != PT_OK) return rcj__; } while (0)
+
 void pt_invalidate_graphs(pt_context* c) {
     if (c->graph.exec) cudaGraphExecDestroy(c->graph.exec);
     c->graph.exec = nullptr; c->graph.launches = 0;
@@ -37,6 +41,7 @@ SceneDev pt_scene_dev(pt_context* c) {
     s.lights = c->d_lights.p; s.n_lights = c->n_lights; s.total_light_area = c->total_light_area;
     s.env[0] = c->env[0]; s.env[1] = c->env[1]; s.env[2] = c->env[2];
     s.env_faces = c->d_env.p; s.env_size = c->env_size;
+    s.visits = c->count_visits ? c->d_visits.p : nullptr;
     s.sun_dir[0] = c->sun_dir[0]; s.sun_dir[1] = c->sun_dir[1]; s.sun_dir[2] = c->sun_dir[2]; s.sun_radius = c->sun_radius;
     return s;
 }
@@ -105,7 +110,10 @@ int pt_create(const pt_config* cfg, pt_context** out) {
         }
         CK(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
         if (const char* e = getenv("PT_NO_GRAPH")) c->use_graph = atoi(e) == 0;
-        CK(c->d_cam.alloc(1));
+        if (const char* e = getenv("PT_LAZY_JOIN")) c->lazy_join = atoi(e) != 0;
+        c->slice_presented.resize(c->n_slices);
+        for (int s = 0; s < c->n_slices; s++) CK(cudaEventCreateWithFlags(&c->slice_presented[s], cudaEventDisableTiming));
+        CK(c->d_cam.alloc(PT_CAM_RING));
         CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         CK(cudaEventCreateWithFlags(&c->ev_resolved, cudaEventDisableTiming));
         for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&c->ev_copied[k], cudaEventDisableTiming));
@@ -142,7 +150,7 @@ void pt_destroy(pt_context* c) {
     c->d_lights.release(); c->d_env.release(); c->d_rng.release(); c->d_accum_own.release();
     for (int q = 0; q < 2; q++) { for (int k = 0; k < 4; k++) c->d_q[q][k].release(); c->d_qrng[q].release(); }
     for (int k = 0; k < 4; k++) c->d_shadow[k].release();
-    c->d_hits.release(); c->d_counters.release(); c->d_totals.release(); c->d_cursor.release();
+    c->d_hits.release(); c->d_counters.release(); c->d_totals.release(); c->d_cursor.release(); c->d_visits.release();
     c->d_stage_rays.release(); c->d_stage_hits.release(); c->d_stage_flags.release();
     c->d_ray_bins.release(); c->d_ray_bin.release(); c->d_ray_perm.release();
     c->d_resolve_f32.release(); c->d_resolve_u8.release();
@@ -154,6 +162,7 @@ void pt_destroy(pt_context* c) {
         cudaEventDestroy(ss.ev_shade); cudaEventDestroy(ss.ev_shadow);
     }
     for (cudaEvent_t e : c->slice_done) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->slice_presented) cudaEventDestroy(e);
     if (c->graph.exec) cudaGraphExecDestroy(c->graph.exec);
     c->d_cam.release();
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
@@ -265,7 +274,7 @@ int pt_set_triangles(pt_context* c, const float* tris, int64_t n) {
     int rc = check_mat_ids(tris, n, c->h_mats.size(), "pt_set_triangles");
     if (rc == PT_OK) rc = check_light_tris(c->h_lights.data(), (int32_t)c->h_lights.size(), n, "pt_set_triangles");
     if (rc != PT_OK) return rc;
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     pt_invalidate_graphs(c);
     c->h_tris.assign(tris, tris + 20 * n);
     CK(c->d_tris.alloc(5 * (size_t)n));
@@ -282,7 +291,7 @@ int pt_set_materials(pt_context* c, const pt_material* mats, int32_t n_mats, con
         if (tex[i].width <= 0 || tex[i].height <= 0 || !tex[i].rgba) return fail(PT_ERR_INVALID, "pt_set_materials: texture %d invalid", i);
     int rc = check_mat_ids(c->h_tris.data(), (int64_t)(c->h_tris.size() / 20), (size_t)n_mats, "pt_set_materials");
     if (rc != PT_OK) return rc;
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     std::vector<float4*> texels;
     std::vector<TextureRec> recs(n_tex);
     DevBuf<MaterialRec> mats_new; DevBuf<TextureRec> texrec_new;
@@ -326,7 +335,7 @@ int pt_set_lights(pt_context* c, const pt_light* lights, int32_t n, float total_
     if (!c || !lights || n <= 0) return fail(PT_ERR_INVALID, "pt_set_lights: a scene needs at least one emissive triangle (Iterative.comp:42-61)");
     int rc = check_light_tris(lights, n, (int64_t)(c->h_tris.size() / 20), "pt_set_lights");
     if (rc != PT_OK) return rc;
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     static_assert(sizeof(pt_light) == sizeof(float2), "light record layout");
     pt_invalidate_graphs(c);
     CK(c->d_lights.alloc(n));
@@ -341,7 +350,7 @@ int pt_set_environment_color(pt_context* c, const float rgb[3]) {
     if (!c || !rgb) return fail(PT_ERR_INVALID, "pt_set_environment_color: bad argument");
     pt_invalidate_graphs(c);
     c->env[0] = rgb[0]; c->env[1] = rgb[1]; c->env[2] = rgb[2];
-    if (c->env_size) { CK(cudaSetDevice(c->cfg.device)); CK(cudaDeviceSynchronize()); c->d_env.release(); c->env_size = 0; }
+    if (c->env_size) { PT_ENTER(c); CK(cudaDeviceSynchronize()); c->d_env.release(); c->env_size = 0; }
     return PT_OK;
 }
 
@@ -355,7 +364,7 @@ int pt_set_sun(pt_context* c, const float direction[3], float radius) {
 
 int pt_set_environment_cubemap(pt_context* c, const float* faces, int32_t size) {
     if (!c || !faces || size < 1 || size > 16384) return fail(PT_ERR_INVALID, "pt_set_environment_cubemap: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaDeviceSynchronize());
     pt_invalidate_graphs(c);
     CK(c->d_env.alloc(6 * (size_t)size * size));
@@ -367,7 +376,7 @@ int pt_set_environment_cubemap(pt_context* c, const float* faces, int32_t size) 
 int pt_set_environment_equirect(pt_context* c, const float* rgba, int32_t width, int32_t height, int32_t cube_size) {
     if (!c || !rgba || width < 1 || height < 1 || cube_size < 1 || cube_size > 16384)
         return fail(PT_ERR_INVALID, "pt_set_environment_equirect: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaDeviceSynchronize());
     pt_invalidate_graphs(c);
     DevBuf<float4> src;
@@ -390,7 +399,7 @@ int32_t pt_environment_size(pt_context* c) { return c ? c->env_size : 0; }
 int pt_download_environment(pt_context* c, float* faces) {
     if (!c || !faces) return fail(PT_ERR_INVALID, "pt_download_environment: bad argument");
     if (!c->env_size) return fail(PT_ERR_INVALID, "pt_download_environment: the environment is a constant colour");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaDeviceSynchronize());
     CK(cudaMemcpy(faces, c->d_env.p, 6 * (size_t)c->env_size * c->env_size * sizeof(float4), cudaMemcpyDeviceToHost));
     return PT_OK;
@@ -507,7 +516,7 @@ static int install_bvh(pt_context* c) {
 
 int pt_set_bvh(pt_context* c, const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs) {
     if (!c || !nodes || !refs || n_nodes < 3 || n_refs < 1) return fail(PT_ERR_INVALID, "pt_set_bvh: bad argument (the root must be an inner node, BVH.glsl:627)");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     std::string msg; int n_leaves = 0;
     int64_t nt = c->h_tris.empty() ? -1 : (int64_t)(c->h_tris.size() / 20);
     int depth = validate_bvh(nodes, n_nodes, refs, n_refs, nt, msg, &n_leaves);
@@ -522,7 +531,7 @@ int pt_set_bvh(pt_context* c, const float* nodes, int32_t n_nodes, const int32_t
 int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
     if (!c) return fail(PT_ERR_INVALID, "pt_build_bvh: null context");
     if (c->h_tris.empty()) return fail(PT_ERR_INVALID, "pt_build_bvh: call pt_set_triangles first");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     std::string msg;
     HostBvh b;
     cudaEvent_t dummy; (void)dummy;
@@ -556,7 +565,7 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
     if (c->h_tris.empty() || !c->d_tris.p) return fail(PT_ERR_INVALID, "pt_build_bvh_device: call pt_set_triangles first");
     const int64_t n = (int64_t)(c->h_tris.size() / 20);
     if (n < 2 || n > (1 << 29)) return fail(PT_ERR_LIMIT, "pt_build_bvh_device: 2 .. 2^29 triangles");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     auto t0 = std::chrono::steady_clock::now();
     pt_invalidate_graphs(c);
     // the serialised tree stays on the device (read back only when somebody asks for it: pt_get_bvh, wide collapse);
@@ -655,7 +664,7 @@ static int load_scene_impl(pt_context* c, const char* scene_path, const char* en
 
 int pt_get_bvh(pt_context* c, float* nodes, int32_t* n_nodes, int32_t* refs, int32_t* n_refs) {
     if (!c || !n_nodes || !n_refs) return fail(PT_ERR_INVALID, "pt_get_bvh: bad argument");
-    { CK(cudaSetDevice(c->cfg.device)); int rc = pt_ensure_host_bvh(c); if (rc != PT_OK) return rc; }
+    { PT_ENTER(c); int rc = pt_ensure_host_bvh(c); if (rc != PT_OK) return rc; }
     *n_nodes = (int32_t)(c->h_bvh.nodes.size() / 8);
     *n_refs = (int32_t)c->h_bvh.refs.size();
     if (nodes) memcpy(nodes, c->h_bvh.nodes.data(), c->h_bvh.nodes.size() * 4);
@@ -668,15 +677,20 @@ int pt_set_camera(pt_context* c, const pt_camera* cam) {
     static_assert(sizeof(pt_camera) == sizeof(CameraRec), "camera record layout");
     memcpy(&c->cam, cam, sizeof(CameraRec));
     CK(cudaSetDevice(c->cfg.device));
-    // 76 bytes of uniforms (Shader::LoadCamera); stream-ordered, so frames already queued keep their camera
-    CK(cudaMemcpyAsync(c->d_cam.p, &c->cam, sizeof(CameraRec), cudaMemcpyHostToDevice, c->stream));
+    // 76 bytes of uniforms (Shader::LoadCamera). Frames already queued keep their camera: stream order when every frame is
+    // joined into `stream`; with chained frames (lazy join) the records live in a ring and a slot is reused only after a join.
+    if (c->lazy_join) {
+        c->cam_slot = (c->cam_slot + 1) % PT_CAM_RING;
+        if (c->cam_slot == 0) { int rc = pt_join_slices(c); if (rc != PT_OK) return rc; }
+    }
+    CK(cudaMemcpyAsync(c->d_cam.p + c->cam_slot, &c->cam, sizeof(CameraRec), cudaMemcpyHostToDevice, c->stream));
     c->have_cam = true;
     return PT_OK;
 }
 
 int pt_set_rng(pt_context* c, const uint32_t* state4) {
     if (!c || !state4) return fail(PT_ERR_INVALID, "pt_set_rng: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     size_t npx = (size_t)c->cfg.width * c->cfg.height;
     CK(cudaMemcpyAsync(c->d_rng.p, state4, npx * 16, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -685,7 +699,7 @@ int pt_set_rng(pt_context* c, const uint32_t* state4) {
 }
 int pt_seed_rng(pt_context* c, uint64_t seed) {
     if (!c) return fail(PT_ERR_INVALID, "pt_seed_rng: null context");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     launch_seed_rng(c->d_rng.p, (long long)c->cfg.width * c->cfg.height, seed, c->stream);
     c->counters.kernel_launches++;
     CK(cudaGetLastError());
@@ -695,7 +709,7 @@ int pt_seed_rng(pt_context* c, uint64_t seed) {
 }
 int pt_get_rng(pt_context* c, uint32_t* state4) {
     if (!c || !state4) return fail(PT_ERR_INVALID, "pt_get_rng: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     size_t npx = (size_t)c->cfg.width * c->cfg.height;
     CK(cudaMemcpyAsync(state4, c->d_rng.p, npx * 16, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -741,7 +755,7 @@ int pt_check_scene(pt_context* c, const char* who, bool need_shading) {
 static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, int block = 0) {
     FrameParams p{};
     p.scene = pt_scene_dev(c);
-    p.cam = c->d_cam.p;
+    p.cam = c->d_cam.p + c->cam_slot;
     p.width = c->cfg.width; p.height = c->cfg.height;
     p.slice_first = first; p.slice_count = count < 0 ? c->cfg.width * c->cfg.height : count;
     p.max_depth = c->cfg.max_depth; p.model = c->cfg.microfacet_model; p.sun = c->cfg.sun_light ? 1 : 0; p.trace_null = c->cfg.trace_null_shadow ? 1 : 0;
@@ -763,26 +777,42 @@ static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, in
 
 // `g` consecutive frames of every slice between a fork from and a join into the main stream. Slices advance through
 // their frames independently; stream-capturable (every cross-stream edge is an event).
-int pt_enqueue_frames(pt_context* c, int g) {
+static int join_impl(pt_context* c, bool mark_time);
+static int enqueue_frames_impl(pt_context* c, int g, bool join) {
     const int npx = c->cfg.width * c->cfg.height;
     int launches = 0;
+    const bool chained = c->pending_join;          // the previous frame of every slice is still on its streams, not joined
     cudaEventRecord(c->ev_fork, c->stream);
     for (int s = 0; s < c->n_slices; s++) cudaStreamWaitEvent(c->slice_streams[s].a, c->ev_fork, 0);
-    for (int f = 0; f < g; f++)
+    for (int f = 0; f < g; f++, c->frame_seq++)
         for (int s = 0; s < c->n_slices; s++) {
             int first = s * c->slice_size;
             int count = npx - first < c->slice_size ? npx - first : c->slice_size;
-            FrameParams p = frame_params(c, first, count, 2 * s + (f & 1));
-            launches += enqueue_frame_dag(p, c->dims, c->slice_streams[s], f > 0);
+            FrameParams p = frame_params(c, first, count, 2 * s + (c->frame_seq & 1));
+            launches += enqueue_frame_dag(p, c->dims, c->slice_streams[s], f > 0 || chained);
         }
     for (int s = 0; s < c->n_slices; s++) {
         cudaEventRecord(c->slice_done[2 * s], c->slice_streams[s].a);
         cudaEventRecord(c->slice_done[2 * s + 1], c->slice_streams[s].b);
-        cudaStreamWaitEvent(c->stream, c->slice_done[2 * s], 0);
-        cudaStreamWaitEvent(c->stream, c->slice_done[2 * s + 1], 0);
     }
+    c->pending_join = true;
+    if (join) join_impl(c, false);
     return launches;
 }
+int pt_enqueue_frames(pt_context* c, int g) { return enqueue_frames_impl(c, g, true); }
+
+static int join_impl(pt_context* c, bool mark_time) {
+    if (!c->pending_join) return PT_OK;
+    for (int s = 0; s < c->n_slices; s++) {
+        CK(cudaStreamWaitEvent(c->stream, c->slice_done[2 * s], 0));
+        CK(cudaStreamWaitEvent(c->stream, c->slice_done[2 * s + 1], 0));
+        if (c->slices_presenting) CK(cudaStreamWaitEvent(c->stream, c->slice_presented[s], 0));
+    }
+    c->pending_join = false; c->slices_presenting = false;
+    if (mark_time) CK(cudaEventRecord(c->ev1, c->stream));      // device time of chained frames runs up to their join
+    return PT_OK;
+}
+int pt_join_slices(pt_context* c) { return join_impl(c, true); }
 
 static int ensure_graph(pt_context* c) {
     if (c->graph.exec) return PT_OK;
@@ -803,21 +833,31 @@ int pt_render_frames(pt_context* c, int32_t n_frames) {
     CK(cudaSetDevice(c->cfg.device));
     int rc = pt_check_scene(c, "pt_render_frames", true);
     if (rc != PT_OK) return rc;
-    CK(cudaEventRecord(c->ev0, c->stream));
     const int epf = 3 * c->cfg.max_depth + 3;
+    if (c->lazy_join && n_frames == 1 && !c->stage_timing) {
+        // The interactive case (one RenderFrame per Present): the frame is chained behind the previous one slice by slice and
+        // nothing is joined -- the next entry point that needs the result joins (pt_join_slices). Device time (ev0 .. ev1)
+        // spans the whole chain.
+        if (!c->pending_join) CK(cudaEventRecord(c->ev0, c->stream));
+        c->counters.kernel_launches += enqueue_frames_impl(c, 1, false);
+        CK(cudaGetLastError());
+        c->num_samples += 1;
+        c->counters.frames += 1;
+        return PT_OK;
+    }
+    if ((rc = pt_join_slices(c)) != PT_OK) return rc;
+    CK(cudaEventRecord(c->ev0, c->stream));
     if (c->stage_timing) {
         // one launch sequence for the whole frame on the main stream (per-stage events need kernels that do not overlap)
         FrameParams p = frame_params(c);
-        if (c->stage_timing) {
-            while ((int)c->stage_events.size() < epf * n_frames) {
-                cudaEvent_t e; CK(cudaEventCreate(&e)); c->stage_events.push_back(e);
-            }
-            c->stage_frames = n_frames; c->stage_events_per_frame = epf;
+        while ((int)c->stage_events.size() < epf * n_frames) {
+            cudaEvent_t e; CK(cudaEventCreate(&e)); c->stage_events.push_back(e);
         }
+        c->stage_frames = n_frames; c->stage_events_per_frame = epf;
         for (int f = 0; f < n_frames; f++)
-            c->counters.kernel_launches += launch_frame(p, c->dims, c->stream, c->stage_timing ? c->stage_events.data() + (size_t)f * epf : nullptr);
+            c->counters.kernel_launches += launch_frame(p, c->dims, c->stream, c->stage_events.data() + (size_t)f * epf);
     } else if (c->use_graph && n_frames == 1) {
-        // the interactive case (one RenderFrame per Present): replay the captured fork/join DAG of one frame
+        // PT_LAZY_JOIN=0: replay the captured fork/join DAG of one frame
         int rc2 = ensure_graph(c);
         if (rc2 != PT_OK) return rc2;
         CK(cudaGraphLaunch(c->graph.exec, c->stream));
@@ -835,7 +875,7 @@ int pt_render_frames(pt_context* c, int32_t n_frames) {
 
 int pt_synchronize(pt_context* c) {
     if (!c) return fail(PT_ERR_INVALID, "pt_synchronize: null context");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaStreamSynchronize(c->copy_stream));
     return PT_OK;
@@ -843,7 +883,7 @@ int pt_synchronize(pt_context* c) {
 
 int pt_reset_samples(pt_context* c) {
     if (!c) return fail(PT_ERR_INVALID, "pt_reset_samples: null context");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     // glClearTexSubImage(accum, {0,0,0,1}) + numSamples = 0, Renderer.cpp:687-691
     CK(cudaMemsetAsync(c->d_accum, 0, (size_t)c->cfg.width * c->cfg.height * sizeof(float4), c->stream));
     c->num_samples = 0;
@@ -853,7 +893,7 @@ uint32_t pt_num_samples(pt_context* c) { return c ? c->num_samples : 0; }
 
 int pt_download_accum(pt_context* c, float* rgba) {
     if (!c || !rgba) return fail(PT_ERR_INVALID, "pt_download_accum: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaMemcpyAsync(rgba, c->d_accum, (size_t)c->cfg.width * c->cfg.height * 16, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     return PT_OK;
@@ -883,7 +923,7 @@ static uint64_t fnv1a(const void* data, size_t n, uint64_t h = 14695981039346656
 int pt_checkpoint_save(pt_context* c, const char* path) {
     if (!c || !path) return fail(PT_ERR_INVALID, "pt_checkpoint_save: bad argument");
     if (!c->have_rng) return fail(PT_ERR_INVALID, "pt_checkpoint_save: no RNG table yet (pt_set_rng / pt_seed_rng)");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
     std::vector<unsigned char> payload(npx * 32);
     CK(cudaMemcpyAsync(payload.data(), c->d_rng.p, npx * 16, cudaMemcpyDeviceToHost, c->stream));
@@ -918,7 +958,7 @@ int pt_checkpoint_load(pt_context* c, const char* path) {
     if (ok) { payload.resize(npx * 32); ok = h.payload_bytes == payload.size() && fread(payload.data(), 1, payload.size(), f) == payload.size(); }
     fclose(f);
     if (!ok || fnv1a(payload.data(), payload.size()) != h.payload_fnv1a) return fail(PT_ERR_IO, "pt_checkpoint_load: %s is not a complete checkpoint", path);
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaStreamSynchronize(c->stream));
     CK(c->d_rng.alloc(npx));
     CK(cudaMemcpy(c->d_rng.p, payload.data(), npx * 16, cudaMemcpyHostToDevice));
@@ -930,7 +970,7 @@ int pt_checkpoint_load(pt_context* c, const char* path) {
 
 int pt_resolve(pt_context* c, uint32_t num_samples, float* rgb_f32, uint8_t* rgb_u8) {
     if (!c || num_samples == 0) return fail(PT_ERR_INVALID, "pt_resolve: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     size_t npx = (size_t)c->cfg.width * c->cfg.height;
     float* d_f = nullptr; unsigned char* d_u = nullptr;
     if (rgb_f32) { CK(c->d_resolve_f32.alloc(npx * 3)); d_f = c->d_resolve_f32.p; }
@@ -949,13 +989,33 @@ int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) 
     CK(cudaSetDevice(c->cfg.device));
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
     const int k = c->present_turn; c->present_turn ^= 1;
+    const bool plibm = (c->cfg.parity_flags & PT_PARITY_LIBM) != 0;
     CK(c->d_present[k].alloc(npx * 3));
-    CK(cudaStreamWaitEvent(c->stream, c->ev_copied[k], 0));          // the copy that last used this buffer (no-op the first time)
-    launch_resolve(c->d_accum, (long long)npx, num_samples, nullptr, c->d_present[k].p, c->stream, (c->cfg.parity_flags & PT_PARITY_LIBM) != 0);
-    c->counters.kernel_launches++;
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(c->ev_resolved, c->stream));
-    CK(cudaStreamWaitEvent(c->copy_stream, c->ev_resolved, 0));
+    if (c->pending_join) {
+        // Chained frames (pt_render_frames(1) without a join): every slice resolves ITS OWN pixels on its own stream right
+        // behind its last kernels, so slice s's next frame waits for slice s only; just the copy waits for all slices.
+        // (Present.frag runs per fragment: which stream shades a pixel changes nothing.)
+        for (int s = 0; s < c->n_slices; s++) {
+            const SliceStreams& ss = c->slice_streams[s];
+            const int first = s * c->slice_size;
+            const int count = (int)npx - first < c->slice_size ? (int)npx - first : c->slice_size;
+            CK(cudaStreamWaitEvent(ss.a, c->slice_done[2 * s + 1], 0));         // the slice's last shadow kernel (stream b)
+            CK(cudaStreamWaitEvent(ss.a, c->ev_copied[k], 0));                  // the copy that last read this buffer
+            launch_resolve_slice(c->d_accum, first, count, c->cfg.width, num_samples, c->d_present[k].p, ss.a, plibm);
+            c->counters.kernel_launches++;
+            CK(cudaEventRecord(c->slice_presented[s], ss.a));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->slice_presented[s], 0));
+        }
+        c->slices_presenting = true;
+        CK(cudaGetLastError());
+    } else {
+        CK(cudaStreamWaitEvent(c->stream, c->ev_copied[k], 0));          // the copy that last used this buffer (no-op the first time)
+        launch_resolve(c->d_accum, (long long)npx, num_samples, nullptr, c->d_present[k].p, c->stream, plibm);
+        c->counters.kernel_launches++;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev_resolved, c->stream));
+        CK(cudaStreamWaitEvent(c->copy_stream, c->ev_resolved, 0));
+    }
     CK(cudaMemcpyAsync(host_rgb_u8, c->d_present[k].p, npx * 3, cudaMemcpyDeviceToHost, c->copy_stream));
     CK(cudaEventRecord(c->ev_copied[k], c->copy_stream));
     return PT_OK;
@@ -965,7 +1025,7 @@ int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) 
 // pixel's RNG state, IfIfClosestHit), hit records in pixel order; the copy runs on the copy stream, double-buffered
 int pt_trace_primary_async(pt_context* c, float* host_hits) {
     if (!c || !host_hits) return fail(PT_ERR_INVALID, "pt_trace_primary_async: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     int rc = pt_check_scene(c, "pt_trace_primary_async", false);
     if (rc != PT_OK) return rc;
     if (!c->have_cam || !c->have_rng) return fail(PT_ERR_INVALID, "pt_trace_primary_async: camera and RNG table must be set");
@@ -1014,7 +1074,7 @@ int pt_save_screenshot(pt_context* c, const char* path) {
 
 int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* d_hits) {
     if (!c || !d_rays || !d_hits || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_closest_device: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     int rc = pt_check_scene(c, "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
@@ -1029,7 +1089,7 @@ int pt_trace_closest_device(pt_context* c, const void* d_rays, int64_t n, void* 
 }
 int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_flags) {
     if (!c || !d_rays || !d_flags || n < 0 || n > kMaxBatchRays) return fail(PT_ERR_INVALID, "pt_trace_any_device: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     int rc = pt_check_scene(c, "pt_trace_any", false);
     if (rc != PT_OK) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
@@ -1049,7 +1109,7 @@ int pt_trace_any_device(pt_context* c, const void* d_rays, int64_t n, void* d_fl
 
 
 static int trace_host(pt_context* c, const float* rays, int64_t n, void* out, size_t out_bytes, bool any) {
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     int rc = pt_check_scene(c, any ? "pt_trace_any" : "pt_trace_closest", false);
     if (rc != PT_OK) return rc;
     const int64_t chunk = n < kHostChunk ? n : kHostChunk;
@@ -1115,7 +1175,7 @@ int pt_raygen_probe(pt_context* c, int64_t first, int64_t n, float* out) {
     if (!c || !out || first < 0 || n < 0 || first + n > (int64_t)c->cfg.width * c->cfg.height) return fail(PT_ERR_INVALID, "pt_raygen_probe: bad range");
     if (!c->have_cam || !c->have_rng) return fail(PT_ERR_INVALID, "pt_raygen_probe: camera and RNG table must be set");
     if (n == 0) return PT_OK;
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     float4* d = nullptr;
     CK(cudaMalloc((void**)&d, 48 * (size_t)n));
     FrameParams p = frame_params(c);
@@ -1131,7 +1191,7 @@ int pt_raygen_probe(pt_context* c, int64_t first, int64_t n, float* out) {
 int pt_parity_libm_probe(pt_context* c, int32_t fn, const float* x, const float* y, int64_t n, float* out) {
     if (!c || !x || !out || n < 0 || fn < 0 || fn > 4 || (fn == 4 && !y)) return fail(PT_ERR_INVALID, "pt_parity_libm_probe: bad argument");
     if (n == 0) return PT_OK;
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     DevBuf<float> dx, dy, dout;
     CK(dx.alloc((size_t)n)); CK(dy.alloc((size_t)n)); CK(dout.alloc((size_t)n));
     CK(cudaMemcpyAsync(dx.p, x, 4 * (size_t)n, cudaMemcpyHostToDevice, c->stream));
@@ -1148,18 +1208,41 @@ int pt_parity_libm_probe(pt_context* c, int32_t fn, const float* x, const float*
 
 int pt_get_counters(pt_context* c, pt_counters* out) {
     if (!c || !out) return fail(PT_ERR_INVALID, "pt_get_counters: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     unsigned long long t[4];
     CK(cudaMemcpyAsync(t, c->d_totals.p, sizeof(t), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     *out = c->counters;
     out->closest_rays += t[0]; out->shadow_rays += t[1]; out->paths = t[2]; out->null_shadow_rays = t[3];
+    if (c->d_visits.p) {
+        unsigned long long v[4];
+        CK(cudaMemcpy(v, c->d_visits.p, sizeof(v), cudaMemcpyDeviceToHost));
+        out->closest_pair_tests = v[0]; out->closest_tri_tests = v[1]; out->shadow_pair_tests = v[2]; out->shadow_tri_tests = v[3];
+        out->counted_closest_rays = c->counted_rays[0] + (c->count_visits ? out->closest_rays - c->counted_base[0] : 0);
+        out->counted_shadow_rays = c->counted_rays[1] + (c->count_visits ? out->shadow_rays - c->counted_base[1] : 0);
+    }
+    return PT_OK;
+}
+
+int pt_set_visit_counting(pt_context* c, int on) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_set_visit_counting: null context");
+    if (c->dims.wide && on) return fail(PT_ERR_UNSUPPORTED, "pt_set_visit_counting: binary layout only");
+    pt_counters now;
+    int rc = pt_get_counters(c, &now);                                  // joins and synchronises
+    if (rc != PT_OK) return rc;
+    if (on && !c->d_visits.p) { CK(c->d_visits.alloc(4)); CK(cudaMemset(c->d_visits.p, 0, 4 * sizeof(unsigned long long))); }
+    if (on && !c->count_visits) { c->counted_base[0] = now.closest_rays; c->counted_base[1] = now.shadow_rays; }
+    if (!on && c->count_visits) { c->counted_rays[0] += now.closest_rays - c->counted_base[0]; c->counted_rays[1] += now.shadow_rays - c->counted_base[1]; }
+    c->count_visits = on != 0;
+    c->dims.count_visits = on ? 1 : 0;
+    pt_invalidate_graphs(c);
     return PT_OK;
 }
 
 float pt_last_device_ms(pt_context* c) {
     if (!c) return -1.0f;
     cudaSetDevice(c->cfg.device);
+    if (pt_join_slices(c) != PT_OK) return -1.0f;
     if (cudaEventSynchronize(c->ev1) != cudaSuccess) return -1.0f;
     float ms = -1.0f;
     if (cudaEventElapsedTime(&ms, c->ev0, c->ev1) != cudaSuccess) return -1.0f;
@@ -1173,7 +1256,7 @@ int pt_set_stage_timing(pt_context* c, int on) {
 }
 int pt_get_stage_ms(pt_context* c, float out[5]) {
     if (!c || !out) return fail(PT_ERR_INVALID, "pt_get_stage_ms: bad argument");
-    CK(cudaSetDevice(c->cfg.device));
+    PT_ENTER(c);
     CK(cudaStreamSynchronize(c->stream));
     for (int i = 0; i < 5; i++) out[i] = 0.0f;
     const int epf = c->stage_events_per_frame;

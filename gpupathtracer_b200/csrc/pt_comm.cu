@@ -83,6 +83,7 @@ struct pt_comm_state {
     DevBuf<float4> reduced, total;                 // rank 0: sum over ranks of one batch; running total
     cudaEvent_t ev_rendered[2] = {nullptr, nullptr}, ev_reduced[2] = {nullptr, nullptr};
     cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;  // timing of the last reduce
+    cudaEvent_t ev_done = nullptr;                 // end of the last batch on the communication stream (reduce + rank 0's add)
     int turn = 0, last_turn = -1;
     uint32_t total_samples = 0;                    // samples per pixel in `total`: world x frames of every batch
     uint64_t batches = 0;
@@ -110,6 +111,7 @@ static int comm_attach(pt_context* c, ncclComm_t comm, int rank, int world) {
     }
     CK(cudaEventCreate(&s->ev_r0));
     CK(cudaEventCreate(&s->ev_r1));
+    CK(cudaEventCreate(&s->ev_done));
     pt_invalidate_graphs(c);                       // batches switch accumulators: frames are enqueued eagerly from here on
     c->d_accum = c->d_accum_own.p;
     CK(cudaStreamSynchronize(c->stream));
@@ -126,6 +128,7 @@ void pt_comm_release(pt_context* c) {
     for (int k = 0; k < 2; k++) { if (s->ev_rendered[k]) cudaEventDestroy(s->ev_rendered[k]); if (s->ev_reduced[k]) cudaEventDestroy(s->ev_reduced[k]); }
     if (s->ev_r0) cudaEventDestroy(s->ev_r0);
     if (s->ev_r1) cudaEventDestroy(s->ev_r1);
+    if (s->ev_done) cudaEventDestroy(s->ev_done);
     if (s->stream) cudaStreamDestroy(s->stream);
     delete s;
     c->comm = nullptr;
@@ -137,6 +140,7 @@ static int batch_render(pt_context* c, int n_frames) {
     pt_comm_state* s = c->comm;
     CK(cudaSetDevice(c->cfg.device));
     int rc = pt_check_scene(c, "pt_render_batch", true);
+    if (rc == PT_OK) rc = pt_join_slices(c);
     if (rc != PT_OK) return rc;
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
     const int k = s->turn;
@@ -178,6 +182,7 @@ static int batch_finish(pt_context* c, int n_frames) {
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(s->ev_reduced[k], s->stream));
+    CK(cudaEventRecord(s->ev_done, s->stream));
     s->last_turn = k;
     s->turn ^= 1;
     s->total_samples += (uint32_t)n_frames * (uint32_t)s->world;
@@ -299,6 +304,16 @@ float pt_comm_last_reduce_ms(pt_context* c) {
     if (cudaEventSynchronize(c->comm->ev_r1) != cudaSuccess) return -1.0f;
     float ms = -1.0f;
     if (cudaEventElapsedTime(&ms, c->comm->ev_r0, c->comm->ev_r1) != cudaSuccess) return -1.0f;
+    return ms;
+}
+
+// device time of the last pt_render_batch on this rank: from its first kernel to the end of its reduce (+ rank 0's add)
+float pt_comm_last_batch_ms(pt_context* c) {
+    if (!c || !c->comm || c->comm->batches == 0) return -1.0f;
+    cudaSetDevice(c->cfg.device);
+    if (cudaEventSynchronize(c->comm->ev_done) != cudaSuccess) return -1.0f;
+    float ms = -1.0f;
+    if (cudaEventElapsedTime(&ms, c->ev0, c->comm->ev_done) != cudaSuccess) return -1.0f;
     return ms;
 }
 

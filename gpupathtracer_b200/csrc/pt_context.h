@@ -46,6 +46,13 @@ struct pt_context {
     std::vector<cudaEvent_t> slice_done;      // 2 per slice (streams a and b)
     cudaEvent_t ev_fork = nullptr;
     bool use_graph = true;
+    // Interactive loop (RenderFrame(1) + Present per frame): frames are enqueued eagerly and the slices are NOT joined into
+    // `stream` after each one; slice s's next frame follows slice s's own present, so the GPU never drains between frames.
+    // Every other entry point joins first (pt_join_slices). PT_LAZY_JOIN=0 restores the per-frame graph replay + join.
+    bool lazy_join = true, pending_join = false, slices_presenting = false;
+    unsigned frame_seq = 0;                    // counter-block parity of eagerly chained single frames
+    std::vector<cudaEvent_t> slice_presented;  // per slice: its part of the last pt_present_async
+    int cam_slot = 0;                          // ring of camera records: frames in flight keep the camera they were enqueued with
     struct FrameGraph { cudaGraphExec_t exec = nullptr; int launches = 0; };
     FrameGraph graph;                          // one frame, all slices
     DevBuf<CameraRec> d_cam;
@@ -106,6 +113,9 @@ struct pt_context {
     DevBuf<BounceCounters> d_counters;
     DevBuf<unsigned long long> d_totals;
     DevBuf<int> d_cursor;
+    DevBuf<unsigned long long> d_visits;   // pt_set_visit_counting: 4 visit counters written by the instrumented traversal kernels
+    bool count_visits = false;
+    uint64_t counted_rays[2] = {0, 0}, counted_base[2] = {0, 0};     // closest / shadow rays traced while counting was on
     // staging for host-pointer batch entry points
     DevBuf<float4> d_stage_rays, d_stage_hits;
     DevBuf<unsigned char> d_stage_flags;
@@ -128,6 +138,8 @@ struct pt_context {
 void pt_invalidate_graphs(pt_context* c);
 pt::SceneDev pt_scene_dev(pt_context* c);
 extern "C" int pt_check_scene(pt_context* c, const char* who, bool need_shading);
+extern "C" int pt_join_slices(pt_context* c);   // c->stream waits for everything the slices have been given (device-side wait)
+#define PT_CAM_RING 64
 extern "C" int pt_enqueue_frames(pt_context* c, int n_frames);            // n frames of every slice between a fork from and a join into c->stream
 extern "C" int pt_ensure_host_bvh(pt_context* c);
 void pt_comm_release(pt_context* c);                          // pt_comm.cu; called by pt_destroy

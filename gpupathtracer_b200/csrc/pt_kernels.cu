@@ -172,6 +172,7 @@ void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, fl
     BatchIO io{rays, hits, nullptr, (int)n, cursor, perm};
     if (dims.wide == 8) k_trace_batch<false, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_trace_batch<false, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.count_visits) k_trace_batch<false, CountingTraverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else k_trace_batch<false, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsigned char* flags, int* cursor,
@@ -180,6 +181,7 @@ void launch_trace_any(const SceneDev& s, const float4* rays, long long n, unsign
     BatchIO io{rays, nullptr, flags, (int)n, cursor, perm};
     if (dims.wide == 8) k_trace_batch<true, WideTraverser<8>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_trace_batch<true, WideTraverser<4>><<<dims.extend_blocks, PT_TRACE_THREADS, 0, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.count_visits) k_trace_batch<true, CountingTraverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
     else k_trace_batch<true, Traverser><<<dims.extend_blocks, PT_TRACE_THREADS, 64 * s.top_pairs, st>>>(s, io, dims.leaf_thresh, dims.fetch_thresh);
 }
 
@@ -246,6 +248,7 @@ k_extend(FrameParams p, int bounce, int qi, int leaf_thresh, int fetch_thresh) {
 static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims& dims, int blocks, cudaStream_t st) {
     if (dims.wide == 8) k_extend<WideTraverser<8>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_extend<WideTraverser<4>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.count_visits) k_extend<CountingTraverser><<<blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
     else k_extend<Traverser><<<blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi, dims.leaf_thresh, dims.fetch_thresh);
 }
 
@@ -437,6 +440,7 @@ k_shadow(FrameParams p, int bounce, int qi_next, int leaf_thresh, int fetch_thre
 static void launch_shadow(const FrameParams& p, int b, int qi_next, const LaunchDims& dims, int blocks, cudaStream_t st) {
     if (dims.wide == 8) k_shadow<WideTraverser<8>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
     else if (dims.wide == 4) k_shadow<WideTraverser<4>><<<blocks, PT_TRACE_THREADS, 0, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
+    else if (dims.count_visits) k_shadow<CountingTraverser><<<blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
     else k_shadow<Traverser><<<blocks, PT_TRACE_THREADS, 64 * p.scene.top_pairs, st>>>(p, b, qi_next, dims.leaf_thresh, dims.fetch_thresh);
 }
 
@@ -561,9 +565,14 @@ void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStr
 // ------------------------------------------------------------------ resolve (Present.frag:13-37)
 template <bool PL>
 __global__ void k_resolve(const float4* __restrict__ accum, long long n, unsigned num_samples, float* rgb_f32,
-                          unsigned char* rgb_u8) {
+                          unsigned char* rgb_u8, int first, int width) {
     long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (width > 0) {                   // slice form: i counts ray indices from `first`; the pixel is their Morton-tile position
+        int px, py;
+        ray_index_to_morton(first + (int)i, width, px, py);
+        i = (long long)py * width + px;
+    }
     const float A = 0.15f, B = 0.50f, C = 0.10f, D = 0.20f, E = 0.02f, F = 0.30f, W = 11.2f;
     const float white = ((W * (A * W + C * B) + D * E) / (W * (A * W + B) + D * F)) - E / F;
     float4 a = accum[i];
@@ -583,8 +592,15 @@ void launch_resolve(const float4* accum, long long n, unsigned num_samples, floa
                     cudaStream_t st, bool plibm) {
     int blocks = (int)((n + 255) / 256);
     if (blocks <= 0) return;
-    if (plibm) k_resolve<true><<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
-    else k_resolve<false><<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8);
+    if (plibm) k_resolve<true><<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8, 0, 0);
+    else k_resolve<false><<<blocks, 256, 0, st>>>(accum, n, num_samples, rgb_f32, rgb_u8, 0, 0);
+}
+void launch_resolve_slice(const float4* accum, int first, int count, int width, unsigned num_samples, unsigned char* rgb_u8,
+                          cudaStream_t st, bool plibm) {
+    int blocks = (count + 255) / 256;
+    if (blocks <= 0) return;
+    if (plibm) k_resolve<true><<<blocks, 256, 0, st>>>(accum, count, num_samples, nullptr, rgb_u8, first, width);
+    else k_resolve<false><<<blocks, 256, 0, st>>>(accum, count, num_samples, nullptr, rgb_u8, first, width);
 }
 
 // ------------------------------------------------------------------ pt_parity_libm.h on the device, argument by argument
@@ -663,6 +679,7 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
     cudaGetDeviceProperties(&prop, device);
     int per_sm_ext = 1, per_sm_shadow = 1, per_sm_shade = 1;
     out->wide = wide;
+    out->count_visits = 0;
     out->top_pairs = 0;
     if (wide == 8) {
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<WideTraverser<8>>, PT_TRACE_THREADS, 0);

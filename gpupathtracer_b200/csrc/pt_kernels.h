@@ -33,7 +33,7 @@ struct FrameParams {
     unsigned long long* totals; // [0] closest rays, [1] shadow rays traced, [2] paths, [3] shadow rays not needed (radiance 0)
 };
 
-struct LaunchDims { int sm_count; int extend_blocks; int frame_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; int wide; int top_pairs; };
+struct LaunchDims { int count_visits; int sm_count; int extend_blocks; int frame_blocks; int stream_blocks; int shade_blocks; int leaf_thresh; int fetch_thresh; int wide; int top_pairs; };
 
 // fixed ray batches (AoS rays: n x {o.xyz, -, d.xyz, tmax})
 void launch_trace_closest(const SceneDev& s, const float4* rays, long long n, float4* hits, int* cursor,
@@ -65,6 +65,9 @@ void launch_seed_rng(uint4* table, long long n, unsigned long long seed, cudaStr
 void query_launch_dims(int device, int wide, LaunchDims* out);
 void launch_resolve(const float4* accum, long long n, unsigned num_samples, float* rgb_f32, unsigned char* rgb_u8,
                     cudaStream_t st, bool plibm = false);
+// the same for the pixels of ray indices [first, first + count) (8x8 Morton tiles, Iterative.comp:163-172): one slice's part of a present
+void launch_resolve_slice(const float4* accum, int first, int count, int width, unsigned num_samples, unsigned char* rgb_u8,
+                          cudaStream_t st, bool plibm = false);
 void launch_plibm_probe(int fn, const float* x, const float* y, long long n, float* out, cudaStream_t st);
 void launch_equirect_to_cube(const float4* src, int w, int h, float4* faces, int n, cudaStream_t st);
 

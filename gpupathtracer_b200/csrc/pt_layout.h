@@ -91,6 +91,7 @@ struct SceneDev {
     float env[3];                // constant environment ("GENERATE COLOR"), used when env_size == 0
     float sun_dir[3];            // uniform sunDir / sunRadius (Iterative.comp:89-90, Renderer.cpp:23-26,626-627)
     float sun_radius;
+    unsigned long long* visits;  // optional (pt_set_visit_counting): {closest pair tests, closest triangle tests, shadow pair tests, shadow triangle tests}
     const float4* env_faces;     // cubemap: 6 x env_size x env_size RGBA32F, faces +X -X +Y -Y +Z -Z, rows as uploaded
     int env_size;
 };

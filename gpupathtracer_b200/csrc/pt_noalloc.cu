@@ -61,6 +61,7 @@ int pt_trace_closest_device_noalloc(pt_context* c, const void* d_rays, int64_t n
     if (c->dims.wide) return fail(PT_ERR_UNSUPPORTED, "pt_trace_closest_device_noalloc: binary BVH layout only");
     CK(cudaSetDevice(c->cfg.device));
     int rc = pt_check_scene(c, "pt_trace_closest_device_noalloc", false);
+    if (rc == PT_OK) rc = pt_join_slices(c);          // chained frames still on the slice streams (a device-side wait, no allocation)
     if (rc != PT_OK) return rc;
     unsigned* scratch = nullptr;
     if ((rc = scratch_for_device(c->cfg.device, &scratch)) != PT_OK) return rc;

@@ -134,6 +134,7 @@ struct Traverser {
 #endif
     }
     __device__ __forceinline__ void idle() { current = 0; sp = 0; }
+    __device__ __forceinline__ void epilogue(unsigned long long*) {}          // see CountingTraverser
     __device__ __forceinline__ bool at_leaf() const { return current < 0; }
     // returns true when the ray is finished
     template <bool ANY>
@@ -205,6 +206,23 @@ struct Traverser {
     }
 };
 
+// The same walk with visit counters (pt_set_visit_counting): pair tests and triangle tests of every ray this lane traced,
+// summed per warp and added to SceneDev::visits at the end of the kernel -- the N_inner / N_tri of SURVEY 8d's algorithmic
+// bytes, measured on the rays the kernel actually traced. An instrumented variant: the timed kernels are `Traverser`.
+struct CountingTraverser : Traverser {
+    unsigned long long n_pairs = 0, n_tris = 0;
+    template <bool ANY>
+    __device__ __forceinline__ bool inner_step(const SceneDev& s, int* stack) { n_pairs++; return Traverser::inner_step<ANY>(s, stack); }
+    template <bool ANY>
+    __device__ __forceinline__ bool leaf_step(const SceneDev& s, const int* stack) { n_tris++; return Traverser::leaf_step<ANY>(s, stack); }
+    __device__ __forceinline__ void epilogue(unsigned long long* out) {
+        unsigned long long a = n_pairs, b = n_tris;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a += __shfl_down_sync(0xffffffffu, a, o); b += __shfl_down_sync(0xffffffffu, b, o); }
+        if ((threadIdx.x & 31) == 0 && out) { atomicAdd(out, a); atomicAdd(out + 1, b); }
+    }
+};
+
 // The warp-scheduled persistent traversal loop. IO supplies:
 //   int  count() const;  int* cursor() const;
 //   void load(int i, V3& o, V3& d, float& tmax) const;
@@ -269,6 +287,7 @@ __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io
             active = false;
         }
     }
+    tr.epilogue(s.visits ? s.visits + (ANY ? 2 : 0) : nullptr);
 }
 
 }  // namespace pt

@@ -53,6 +53,7 @@ template <int N>
 struct WideTraverser {
     typedef uint2 StackEntry;
     static const int kStack = 32;
+    __device__ __forceinline__ void epilogue(unsigned long long*) {}
     V3 o, d, inv;
     HitRec h;
     uint2 G, T;

@@ -105,6 +105,10 @@ typedef struct pt_counters {
     uint64_t null_shadow_rays;     /* NEE samples whose radiance is exactly 0 (light below the horizon): the reference traces
                                       their shadow ray and adds 0, this library settles them without a ray; not part of
                                       shadow_rays, which counts rays actually traced */
+    /* visit counts of the rays traced while pt_set_visit_counting was on (0 otherwise): sibling-pair tests (IntersectNodeFast x 2,
+       BVH.glsl:692-705) and triangle tests (IntersectTriangleMT) of closest-hit and of shadow rays -- SURVEY 8d's N_inner / N_tri */
+    uint64_t closest_pair_tests, closest_tri_tests, shadow_pair_tests, shadow_tri_tests;
+    uint64_t counted_closest_rays, counted_shadow_rays;   /* the rays those visits belong to */
 } pt_counters;
 
 typedef struct pt_bvh_stats {
@@ -309,6 +313,9 @@ int pt_raygen_probe(pt_context* ctx, int64_t first, int64_t n, float* out);
 int pt_parity_libm_probe(pt_context* ctx, int32_t fn, const float* x, const float* y_or_null, int64_t n, float* out);
 
 int pt_get_counters(pt_context* ctx, pt_counters* out);
+/* Instrumented traversal: while on, pt_render_frames / pt_trace_* run a variant of the binary-layout traversal kernels that also
+ * counts node-pair and triangle tests per ray kind (same rays, same results; a few percent slower, so timed runs leave it off). */
+int pt_set_visit_counting(pt_context* ctx, int on);
 /* CUDA-event milliseconds of the last pt_render_frames / pt_trace_*_device call (device time only). */
 float pt_last_device_ms(pt_context* ctx);
 /* Per-stage device time of the last pt_render_frames call, from CUDA events recorded on the library's stream
@@ -348,6 +355,7 @@ int pt_comm_synchronize(pt_context* ctx);
 int pt_comm_download_total(pt_context* ctx, float* rgba);         /* rank 0: the running total (sum); other ranks: no-op */
 int pt_comm_download_batch(pt_context* ctx, float* rgba);         /* this rank's own sum of the last batch (what it sent) */
 void* pt_comm_total_device_ptr(pt_context* ctx);                  /* rank 0, else NULL */
+float pt_comm_last_batch_ms(pt_context* ctx);                     /* last pt_render_batch on this rank: first kernel .. end of its reduce */
 float pt_comm_last_reduce_ms(pt_context* ctx);                    /* CUDA-event time of the last ncclReduce on its stream */
 int pt_comm_present_async(pt_context* ctx, uint8_t* host_rgb_u8); /* rank 0: Present of total / samples, as pt_present_async */
 

@@ -251,3 +251,66 @@ def test_inconsistent_tables_are_refused_and_leave_the_context_usable():
     assert np.array_equal(np.nan_to_num(r.DownloadAccum(), nan=-1.0), np.nan_to_num(r2.DownloadAccum(), nan=-1.0))
     assert not np.array_equal(before, r.DownloadAccum())
     r.CleanUp(); r2.CleanUp()
+
+
+def test_chained_frames_and_per_slice_present_change_nothing():
+    """The interactive loop (RenderFrame(1) + PresentAsync per frame) chains frames slice by slice without joining them and lets
+    every slice resolve its own pixels; a camera change between frames must reach exactly the frames rendered after it. Same
+    accumulation bits, RNG table and presented bytes as the joined path (PT_LAZY_JOIN=0 semantics: one batch call / blocking
+    Present), for 1, 3 and 4 slices including a ragged last slice, and across a camera-ring wrap (> 64 frames)."""
+    s = get_scene("cornell")
+    w, h, frames = 72, 40, 70
+    cams = [make_camera(s.data, w, h, aperture=a) for a in (0.0, 0.4)]
+    rng = make_rng_table(w * h, 33)
+    # reference run: every frame joined (blocking Present after each)
+    r0 = Renderer().Initialize(w, h, s, max_depth=5, rng_state=rng, n_slices=1)
+    want8 = []
+    for i in range(frames):
+        r0.RenderFrame(cams[(i // 5) & 1], 1)
+        want8.append(r0.Present(as_u8=True))
+    want, want_rng = r0.DownloadAccum(), r0.GetRNG()
+    r0.CleanUp()
+    for n_slices in (1, 3, 4):
+        r = Renderer().Initialize(w, h, s, max_depth=5, rng_state=rng, n_slices=n_slices)
+        bufs = [np.zeros((h, w, 3), np.uint8) for _ in range(frames)]
+        for i in range(frames):
+            r.RenderFrame(cams[(i // 5) & 1], 1)
+            r.PresentAsync(bufs[i].ctypes.data)
+            if i % 2 == 1:
+                r.Synchronize()                    # at most two presents in flight (double-buffered target)
+        r.Synchronize()
+        assert np.array_equal(np.nan_to_num(r.DownloadAccum(), nan=-1.0), np.nan_to_num(want, nan=-1.0)), n_slices
+        assert np.array_equal(r.GetRNG(), want_rng)
+        for i in range(frames):
+            assert np.array_equal(bufs[i], want8[i]), (n_slices, i)
+        assert r.Counters()["paths"] == frames * w * h
+        r.CleanUp()
+
+
+def test_device_visit_counters_equal_the_oracles():
+    """pt_set_visit_counting: pair tests and triangle tests per ray, counted by the instrumented traversal kernels on the rays they
+    trace, equal the instrumented oracle's on the same batch -- closest-hit rays exactly (same walk, ray by ray). Any-hit rays are
+    walked near child first by the kernel and in the reference's fixed order by the oracle (same flags, pt_trace.cuh): an occluded
+    ray stops at a different leaf, so those counts agree only roughly (15 %)."""
+    from common import mixed_rays
+    s = get_scene("atrium_small")
+    rays, anyr = mixed_rays(s, 100000, seed=5), mixed_rays(s, 100000, seed=6, any_hit=True)
+    o = oracle.Oracle(s)
+    want_hits, cc = o.trace_closest(rays)
+    _, ca = o.trace_any(anyr)
+    r = Renderer().Initialize(64, 64, s)
+    plain = r.TraceClosest(rays)
+    r.SetVisitCounting(True)
+    got = r.TraceClosest(rays)
+    r.TraceAny(anyr)
+    r.SetVisitCounting(False)
+    c = r.Counters()
+    r.TraceClosest(rays)                                   # not counted any more
+    c2 = r.Counters()
+    r.CleanUp()
+    assert np.array_equal(got.view(np.uint32), plain.view(np.uint32)) and np.array_equal(got.view(np.uint32), want_hits.view(np.uint32))
+    assert c["counted_closest_rays"] == rays.shape[0] and c["counted_shadow_rays"] == anyr.shape[0]
+    assert c["closest_pair_tests"] == cc["node_pairs"] and c["closest_tri_tests"] == cc["tri_tests"]
+    assert abs(c["shadow_pair_tests"] - ca["node_pairs"]) <= 0.15 * ca["node_pairs"]
+    assert abs(c["shadow_tri_tests"] - ca["tri_tests"]) <= 0.15 * ca["tri_tests"]
+    assert c2["closest_pair_tests"] == c["closest_pair_tests"] and c2["counted_closest_rays"] == c["counted_closest_rays"]

@@ -91,7 +91,7 @@ def test_one_process_per_gpu(tmp_path):
     assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-4000:]
     z = [np.load(tmp_path / f"rank{r}.npz") for r in range(2)]
     assert np.array_equal(z[0]["hits"].view(np.uint32), z[1]["hits"].view(np.uint32))       # the broadcast tree traces like the built one
-    assert np.array_equal(z[0]["nodes"], z[1]["nodes"]) and np.array_equal(z[0]["refs"], z[1]["refs"])
+    assert np.array_equal(z[0]["nodes"].view(np.uint32), z[1]["nodes"].view(np.uint32)) and np.array_equal(z[0]["refs"], z[1]["refs"])   # link words are ints: compare bits
     assert not np.array_equal(z[0]["rng"], z[1]["rng"])
     want = np.zeros_like(z[0]["total"][..., :3])
     for b in range(3):
