@@ -276,7 +276,9 @@ def run_reference(args):
 
 
 class Dist:
-    """torch.distributed plumbing shared by the workloads (one process per GPU, NCCL)."""
+    """torch.distributed plumbing shared by the workloads (one process per GPU, NCCL): rendezvous, barriers, max / sum of
+    the per-rank timings. The data path's own exchange -- the reduce of the accumulation buffers -- runs inside the library
+    (csrc/pt_comm.cu) over its own NCCL communicator, whose id travels through this process group."""
 
     def __init__(self):
         import torch
@@ -291,7 +293,7 @@ class Dist:
 
     def barrier(self, r=None):
         if r is not None:
-            r.Synchronize()
+            r.CommSynchronize() if self.world > 1 else r.Synchronize()
         self.torch.cuda.synchronize()
         if self.world > 1:
             self.dist.barrier()
@@ -311,155 +313,346 @@ class Dist:
 
 
 LAYOUTS = {"reference": 0, "wide": 1, "wide4": 2}
+BUILDERS = {"device": "device", "ploc": "ploc"}
 
 
-def run_pathtrace(args, name, wl):
-    d = Dist()
-    torch, dist, world, rank, local = d.torch, d.dist, d.world, d.rank, d.local
+def make_renderer(d, scene, W, H, wl, args, **kw):
+    """One context per rank. N > 1: the tree is built ONCE, on rank 0, and reaches the other ranks through the library's
+    broadcast (pt_comm_broadcast_bvh); RNG tables are seeded per rank by the library (pt_comm_seed_rng)."""
     from gpupathtracer_b200 import Renderer
-    W, H, depth = wl["width"], wl["height"], wl["depth"]
-    scene = build_scene(wl)
-    t0 = time.perf_counter()
-    r = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
-                              seed=0xB200 ^ (rank * 0x9E3779B9), bvh={"device": "device", "ploc": "ploc"}.get(args.builder, "build"),
-                              bvh_layout=LAYOUTS[args.bvh])
-    init_s = time.perf_counter() - t0
-    cam = make_camera(scene, W, H)
-    # accumulation buffer owned by torch so NCCL can reduce it in place
-    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-    r.lib.pt_set_accum_device_ptr(r.ctx, accum.data_ptr())
-    pinned = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
-    warmup = max(args.warmup, 3)
+    from gpupathtracer_b200.distributed import init_comm
+    how = BUILDERS.get(args.builder, "build")
+    if d.world > 1 and d.rank != 0 and LAYOUTS[args.bvh] == 0:
+        how = "none"
+    r = Renderer().Initialize(W, H, scene, max_depth=wl["depth"], microfacet_model=wl["model"], device=d.local, bvh=how,
+                              bvh_layout=LAYOUTS[args.bvh], **kw)
+    if d.world > 1:
+        init_comm(r, d.dist)
+        if LAYOUTS[args.bvh] == 0:
+            r.CommBroadcastBVH(0)
+            if d.rank != 0:
+                scene.set_bvh(*r.GetBVH())
+        r.CommSeedRNG(0xB200)
+    else:
+        r.lib.pt_seed_rng(r.ctx, 0xB200)
+    return r
 
-    # ---- warm-up
-    for _ in range(warmup):
-        r.RenderFrame(cam, 1)
-    if world > 1:
-        r.Synchronize(); dist.reduce(accum, dst=0); torch.cuda.synchronize()
-    d.barrier(r)
 
-    # ---- timed region: K frames, device time from CUDA events on the library's stream (+ the reduce for N > 1)
-    r.ResetSamples(); r.Synchronize()
-    c0 = r.Counters()
-    sampler = ClockSampler(local); sampler.start()
-    d.barrier(r)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    r.RenderFrame(cam, args.steps)                 # K frames back to back; all inputs already resident in HBM
-    r.Synchronize()
-    ms_render = r.LastDeviceMs()
-    ms_reduce = 0.0
-    if world > 1:
-        ev0.record(); dist.reduce(accum, dst=0); ev1.record(); torch.cuda.synchronize()
-        ms_reduce = ev0.elapsed_time(ev1)
-    d.barrier(r)
-    clocks = sampler.result()
-    c1 = r.Counters()
-    # per-kernel durations: a second pass with the frame as ONE launch sequence (no overlapping slices), CUDA events
-    # between kernels on the library's stream
-    stage_frames = min(args.steps, 16)
-    r.SetStageTiming(True)
-    r.RenderFrame(cam, stage_frames); r.Synchronize()
-    stage = r.StageMs()
-    r.SetStageTiming(False)
-    cs = r.Counters()
-    closest_stage = float(cs["closest_rays"] - c1["closest_rays"])
-    ms_total, closest, shadow = d.max_sum([ms_render + ms_reduce, float(c1["closest_rays"] - c0["closest_rays"]),
-                                           float(c1["shadow_rays"] - c0["shadow_rays"])])
-    rays = closest + shadow
-    value = rays / (ms_total * 1e-3) / 1e6
-    samples_per_s = world * args.steps * W * H / (ms_total * 1e-3)
+def rel_mse(a, b, eps=1e-2):
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    ok = np.isfinite(a) & np.isfinite(b)
+    return float(np.mean(((a - b) ** 2 / (b ** 2 + eps))[ok]))
 
-    # ---- the same K frames with every NEE sample traced, as the reference and the CPU arm do (pt_config.trace_null_shadow):
-    #      identical image, the ray population of the reference; reported beside `value`, not instead of it
-    r_all = Renderer().Initialize(W, H, scene, max_depth=depth, microfacet_model=wl["model"], device=local,
-                                  seed=0xB200 ^ (rank * 0x9E3779B9), bvh="given", bvh_layout=LAYOUTS[args.bvh], trace_null_shadow=True)
+
+def parity_sample(scene, wl, frames=2):
+    """The CUDA path against the reference's own main() on a bounded sample of THIS workload (the 480 x 272 crop the CPU arm
+    renders, same camera / scene / tree / depth / RNG table): bit-for-bit under the parity libm (both sides evaluate sin / cos /
+    log / exp through csrc/pt_parity_libm.h), and how many pixels the default fast-libm build differs on."""
+    import oracle
+    from gpupathtracer_b200 import Renderer, make_rng_table
+    if not oracle.have_glsl():
+        return {"skipped": "oracle/_ref/libref_glsl.so not built"}
+    w, h = CPU_SAMPLE
+    cam = make_camera(scene, w, h, aspect=wl["width"] / wl["height"])
+    rng0 = make_rng_table(w * h, 4321)
+    o = oracle.Oracle(scene)
+    out = {"pixels": w * h, "frames": frames, "against": "the reference's main() (Iterative.comp:214-307 compiled as C++, all host cores)"}
+    for plibm, code in ((True, 6 if wl["model"] else 4), (False, 2 if wl["model"] else 0)):
+        r = Renderer().Initialize(w, h, scene, max_depth=wl["depth"], microfacet_model=wl["model"], rng_state=rng0, bvh="given", parity_libm=plibm)
+        r.RenderFrame(cam, frames)
+        got, rng_got = r.DownloadAccum(), r.GetRNG()
+        r.CleanUp()
+        rng_ref, want = rng0.copy(), np.zeros((h, w, 4), np.float32)
+        o.ref_glsl_render_mp(cam.as_array(), w, h, rng_ref, want, n_frames=frames, max_depth=wl["depth"], model=code)
+        same = (got.view(np.uint32) == want.view(np.uint32)) | (np.isnan(got) & np.isnan(want))
+        bad = int((~same.all(axis=2)).sum())
+        if plibm:
+            out.update({"accum_bit_exact": bad == 0, "rng_bit_exact": bool(np.array_equal(rng_got, rng_ref)), "mismatching_pixels": bad})
+        else:
+            close = np.isclose(got[..., :3], want[..., :3], rtol=1e-4, atol=1e-6).all(axis=2) | (np.isnan(got[..., :3]) & np.isnan(want[..., :3])).all(axis=2)
+            out["default_libm"] = {"pixels_differing_in_some_bit": bad / float(w * h), "pixels_differing_by_more_than_1e-4": float((~close).mean())}
+    return out
+
+
+def timed_batches(d, r, cam, steps, min_seconds=1.0, max_reps=64):
+    """Repeat the K-frame batch until the timed region is at least `min_seconds` long; every repetition is bracketed by a
+    barrier + synchronize and timed on the device (CUDA events on the library's streams, max over ranks; for N > 1 the
+    batch includes its reduce to rank 0). Returns the per-repetition records and the clock record."""
+    reps, total_ms = [], 0.0
+    sampler = ClockSampler(d.local); sampler.start()
+    t_wall = time.perf_counter()
+    while len(reps) < 3 or (total_ms < min_seconds * 1e3 and len(reps) < max_reps):
+        d.barrier(r)
+        c0 = r.Counters()
+        if d.world > 1:
+            r.RenderBatch(cam, steps); r.CommSynchronize()
+            ms = r.CommLastBatchMs()
+        else:
+            r.RenderFrame(cam, steps); r.Synchronize()
+            ms = r.LastDeviceMs()
+        d.barrier(r)
+        c1 = r.Counters()
+        ms, closest, shadow, nulls = d.max_sum([ms, float(c1["closest_rays"] - c0["closest_rays"]), float(c1["shadow_rays"] - c0["shadow_rays"]),
+                                                float(c1["null_shadow_rays"] - c0["null_shadow_rays"])])
+        reps.append((ms, closest, shadow, nulls, int(c1["kernel_launches"] - c0["kernel_launches"])))
+        total_ms += ms
+    return reps, sampler.result(), time.perf_counter() - t_wall
+
+
+def all_nee_pass(d, scene, W, H, wl, args, cam, steps, warmup):
+    """The same K frames with every NEE sample traced, as the reference and the CPU arm do (pt_config.trace_null_shadow):
+    identical image, the ray population of the reference; reported beside `value`, not instead of it."""
+    from gpupathtracer_b200 import Renderer
+    r_all = Renderer().Initialize(W, H, scene, max_depth=wl["depth"], microfacet_model=wl["model"], device=d.local, seed=0xB200,
+                                  bvh="given", bvh_layout=LAYOUTS[args.bvh], trace_null_shadow=True)
     for _ in range(warmup):
         r_all.RenderFrame(cam, 1)
     r_all.Synchronize()
-    ca0 = r_all.Counters()
-    d.barrier(r)
-    r_all.RenderFrame(cam, args.steps); r_all.Synchronize()
-    ms_all = r_all.LastDeviceMs()
-    ca1 = r_all.Counters()
+    best = None
+    for _ in range(3):
+        ca0 = r_all.Counters()
+        r_all.RenderFrame(cam, steps); r_all.Synchronize()
+        ms = r_all.LastDeviceMs()
+        ca1 = r_all.Counters()
+        rays = float(ca1["closest_rays"] - ca0["closest_rays"] + ca1["shadow_rays"] - ca0["shadow_rays"])
+        if best is None or ms < best[0]:
+            best = (ms, rays)
     r_all.CleanUp()
-    ms_all, rays_all = d.max_sum([ms_all + ms_reduce, float(ca1["closest_rays"] - ca0["closest_rays"] + ca1["shadow_rays"] - ca0["shadow_rays"])])
-    all_nee = {"value": rays_all / (ms_all * 1e-3) / 1e6, "unit": "Mrays/s", "samples_per_s": world * args.steps * W * H / (ms_all * 1e-3),
-               "ms_per_step": ms_all / args.steps,
-               "note": "pt_config.trace_null_shadow = 1: NEE samples with exactly zero radiance are traced too, the reference's ray population"}
+    ms, rays = best
+    return {"value": rays / (ms * 1e-3) / 1e6, "unit": "Mrays/s", "samples_per_s": steps * W * H / (ms * 1e-3), "ms_per_step": ms / steps,
+            "note": "pt_config.trace_null_shadow = 1: NEE samples with exactly zero radiance are traced too, the reference's ray population"}
 
-    # ---- end to end through the public API with host buffers: camera in (H2D), presented 8-bit frame out (D2H)
+
+def run_pathtrace(args, name, wl, d, sub=False):
+    """One path-tracing workload -> the JSON line as a dict. sub: a short run for the `configs` block of the default command
+    (no all-NEE pass, no CPU baseline)."""
+    torch, world, rank, local = d.torch, d.world, d.rank, d.local
+    W, H, depth = wl["width"], wl["height"], wl["depth"]
+    scene = build_scene(wl)
+    t0 = time.perf_counter()
+    r = make_renderer(d, scene, W, H, wl, args)
+    init_s = time.perf_counter() - t0
+    cam = make_camera(scene, W, H)
+    pinned = [torch.empty((H, W, 3), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    warmup = max(args.warmup, 3)
+    steps = args.steps
+
+    def render(n):
+        r.RenderBatch(cam, n) if world > 1 else r.RenderFrame(cam, n)
+
+    for _ in range(warmup):
+        render(1)
+    d.barrier(r)
+    r.CommReset() if world > 1 else r.ResetSamples()
+    # ---- timed region: repetitions of K frames back to back, device time; scene / BVH / RNG tables resident in HBM
+    reps, clocks, region_s = timed_batches(d, r, cam, steps, min_seconds=0.4 if sub else 1.0)
+    ms_all_reps = sorted(x[0] for x in reps)
+    ms_total, closest, shadow, nulls, launches = sorted(reps, key=lambda x: x[0])[len(reps) // 2]
+    rays = closest + shadow
+    value = rays / (ms_total * 1e-3) / 1e6
+    samples_per_s = world * steps * W * H / (ms_total * 1e-3)
+    ms_reduce = r.CommLastReduceMs() if world > 1 else 0.0
+
+    # ---- end to end through the public API with host buffers: camera in (H2D), the presented 8-bit frame out (D2H).
+    #      N > 1: every step is a one-frame batch on every rank + its reduce, and rank 0 presents the COMBINED image.
     d.barrier(r)
     c2 = r.Counters()
+    e2e_steps = steps if not sub else min(steps, 16)
     t0 = time.perf_counter()
-    for i in range(args.steps):
+    for i in range(e2e_steps):
         cam.GenerateImagePlane()                   # host: Camera::GenerateImagePlane; H2D: the 76 B of camera uniforms
-        r.RenderFrame(cam, 1)
-        r.PresentAsync(pinned[i & 1].data_ptr())   # Present(): /numSamples + tonemap, D2H into pinned host memory (double-buffered)
+        if world > 1:
+            r.RenderBatch(cam, 1)
+            r.CommPresentAsync(pinned[i & 1].data_ptr())
+        else:
+            r.RenderFrame(cam, 1)
+            r.PresentAsync(pinned[i & 1].data_ptr())   # Present(): /numSamples + tonemap, D2H into pinned host memory (double-buffered)
     d.barrier(r)                                   # all K presented frames are in host memory here
     e2e_s = time.perf_counter() - t0
     c3 = r.Counters()
     e2e_s, e2e_rays = d.max_sum([e2e_s, float(c3["closest_rays"] - c2["closest_rays"] + c3["shadow_rays"] - c2["shadow_rays"])])
     e2e_value = e2e_rays / e2e_s / 1e6
 
+    # ---- per-kernel durations: a separate pass with the frame as ONE launch sequence (no overlapping slices), CUDA events
+    #      between kernels; then two frames through the instrumented kernels for the visit counts
+    stage_frames = min(steps, 8)
+    c4 = r.Counters()
+    r.SetStageTiming(True)
+    r.RenderFrame(cam, stage_frames); r.Synchronize()
+    stage = r.StageMs()
+    r.SetStageTiming(False)
+    c5 = r.Counters()
+    closest_stage = float(c5["closest_rays"] - c4["closest_rays"])
+    shadow_stage = float(c5["shadow_rays"] - c4["shadow_rays"])
+    visits = None
+    if args.bvh == "reference":
+        r.SetVisitCounting(True)
+        r.RenderFrame(cam, 2); r.Synchronize()
+        r.SetVisitCounting(False)
+        v = r.Counters()
+        visits = {"closest_pairs_per_ray": v["closest_pair_tests"] / max(v["counted_closest_rays"], 1),
+                  "closest_tris_per_ray": v["closest_tri_tests"] / max(v["counted_closest_rays"], 1),
+                  "shadow_pairs_per_ray": v["shadow_pair_tests"] / max(v["counted_shadow_rays"], 1),
+                  "shadow_tris_per_ray": v["shadow_tri_tests"] / max(v["counted_shadow_rays"], 1),
+                  "source": "device counters of the instrumented traversal kernels (pt_set_visit_counting) over 2 frames of this workload"}
+    line = None
     if rank == 0:
-        peak, which = measured_peaks()
-        line = {
-            "metric": metric_name(name, wl), "value": value, "unit": "Mrays/s", "samples_per_s": samples_per_s,
-            "rays_per_step": {"closest": closest / args.steps, "shadow_traced": shadow / args.steps,
-                              "shadow_not_needed": float(c1["null_shadow_rays"] - c0["null_shadow_rays"]) / args.steps,
-                              "note": "rank 0's share for shadow_not_needed; NEE samples whose radiance is exactly 0 (light below the "
-                                      "horizon) are settled without a ray -- the reference traces them and adds 0; value counts traced rays only"},
-            "all_nee_samples_traced": all_nee,
-            "n_gpus": world, "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
-                       "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
-                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
-                       "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
-                       "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
-                       "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
-                       "parallelism": f"samples split over {world} GPU(s), 1 NCCL reduce of the accumulation buffer per {args.steps}-frame batch",
-                       "init_s": init_s},
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": W * H * 3,
-                    "ms_per_step": e2e_s / args.steps * 1e3},
-            "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]),
-            "clocks": clocks,
-            "stage_ms_per_step": {k: v / stage_frames for k, v in stage.items()},
-            "stage_note": f"per-kernel times from a separate {stage_frames}-frame pass without slice overlap; their sum exceeds "
-                          "ms_per_step because the timed region overlaps slices",
-            "ms_reduce": ms_reduce,
-        }
-        # ---- CPU baseline (bounded sample) + visit counts for the algorithmic-bytes figure
+        line = pathtrace_line(args, name, wl, d, scene, r, cam, dict(
+            value=value, samples_per_s=samples_per_s, closest=closest, shadow=shadow, nulls=nulls, launches=launches, steps=steps,
+            warmup=warmup, ms_total=ms_total, ms_all_reps=ms_all_reps, reps=len(reps), region_s=region_s, clocks=clocks, ms_reduce=ms_reduce,
+            e2e_value=e2e_value, e2e_s=e2e_s, e2e_steps=e2e_steps, stage=stage, stage_frames=stage_frames, closest_stage=closest_stage,
+            shadow_stage=shadow_stage, visits=visits, init_s=init_s))
+        if world == 1 and not sub:
+            line["all_nee_samples_traced"] = all_nee_pass(d, scene, W, H, wl, args, cam, steps, warmup)
         if world == 1 and not args.no_cpu_baseline:
+            line["parity_on_sample"] = parity_sample(scene, wl)
+        if world == 1 and not args.no_cpu_baseline and not sub:
             w, h = CPU_SAMPLE
             mrays, sps, ms, tot, info = cpu_reference_run(scene, 4, 1, w, h, wl)
             line["cpu_baseline"] = {"value": mrays, "unit": "Mrays/s", "cores": os.cpu_count() or 1, "kind": info["kind"],
                                     "sample": f"{w}x{h} px of the same camera/scene/tree, 4 frames; {info['what']}",
                                     "samples_per_s": sps, **{k: v for k, v in info.items() if k not in ("kind", "what")}}
-            n_c = tot["closest_rays"]
-            pairs_c = (tot["node_pairs"] - tot["shadow_node_pairs"]) / n_c
-            tris_c = (tot["tri_tests"] - tot["shadow_tri_tests"]) / n_c
-            b_ray = B_RAY_IN + B_HIT_OUT + pairs_c * B_PAIR + tris_c * B_TRI
-            ext_s = stage["extend"] * 1e-3
-            launches = stage_frames * depth
-            achieved = closest_stage * b_ray / ext_s / 1e9 if ext_s > 0 else None
-            line["roofline"] = {"bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                                "frac": achieved / peak if achieved else None, "traffic": traffic_for(name, "k_extend"),
-                                "ncu": traffic_for(name, "k_extend ncu"),
-                                "algorithmic_bytes_per_launch": closest_stage * b_ray / launches, "peak_source": which,
-                                "bytes_per_ray": b_ray, "pairs_per_ray": pairs_c, "tris_per_ray": tris_c,
-                                "launches": launches, "avg_launch_ms": stage["extend"] / launches,
-                                "note": "scene (~50 MB) is L2-resident: algorithmic bytes are served by L1/L2, the binding limit is the "
-                                        "L1 data pipe (DESIGN.md 4); the HBM-bound case is --workload micro"}
-        print(json.dumps(line))
     r.CleanUp()
-    d.close()
+    return line
 
 
-def run_micro(args, name, wl):
-    """configs[3]: fixed ray batches against a scene far larger than L2 -- the HBM-bound case."""
-    d = Dist()
+def pathtrace_line(args, name, wl, d, scene, r, cam, m):
+    """The JSON line of a path-tracing workload from the measurements `m` of run_pathtrace."""
+    world = d.world
+    W, H, depth, steps = wl["width"], wl["height"], wl["depth"], m["steps"]
+    peak, which = measured_peaks()
+    line = {
+        "metric": metric_name(name, wl), "value": m["value"], "unit": "Mrays/s", "samples_per_s": m["samples_per_s"],
+        "rays_per_step": {"closest": m["closest"] / steps, "shadow_traced": m["shadow"] / steps, "shadow_not_needed": m["nulls"] / steps,
+                          "note": "NEE samples whose radiance is exactly 0 (light below the horizon) are settled without a ray -- the "
+                                  "reference traces them and adds 0; value counts traced rays only"},
+        "n_gpus": world, "steps": steps, "warmup": m["warmup"], "ms_per_step": m["ms_total"] / steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "timed_region": {"repetitions": m["reps"], "steps_each": steps, "seconds": sum(m["ms_all_reps"]) * 1e-3, "wall_s": m["region_s"],
+                         "ms_per_step_min": m["ms_all_reps"][0] / steps, "ms_per_step_median": m["ms_total"] / steps,
+                         "ms_per_step_max": m["ms_all_reps"][-1] / steps,
+                         "note": "value / ms_per_step are the MEDIAN repetition of K back-to-back frames"},
+        "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
+                   "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
+                   "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
+                   "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
+                   "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
+                   "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
+                   "parallelism": (f"samples split over {world} GPUs inside the library (pt_comm_init): BVH built on rank 0 and broadcast, "
+                                   f"per-rank RNG seeds, 1 ncclReduce of the accumulation buffer per {steps}-frame batch on its own stream"
+                                   if world > 1 else "1 GPU"),
+                   "init_s": m["init_s"]},
+        "e2e": {"value": m["e2e_value"], "unit": "Mrays/s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": W * H * 3,
+                "ms_per_step": m["e2e_s"] / m["e2e_steps"] * 1e3, "steps": m["e2e_steps"],
+                "what": ("RenderFrame + Present per step: camera in, every rank renders a frame, ncclReduce to rank 0, the COMBINED "
+                         "frame resolved and copied to rank 0's pinned host memory" if world > 1 else
+                         "RenderFrame + PresentAsync per step through the C ABI: camera in, tonemapped 8-bit frame out to pinned host "
+                         "memory; slices chain frame to frame (no per-frame drain), each slice resolves its own pixels")},
+        "gpu_launches": m["launches"], "clocks": m["clocks"], "ms_reduce": m["ms_reduce"],
+    }
+    stage, stage_frames, visits = m["stage"], m["stage_frames"], m["visits"]
+    line["stage_ms_per_step"] = {k: v / stage_frames for k, v in stage.items()}
+    line["stage_note"] = (f"per-kernel times from a separate {stage_frames}-frame pass without slice overlap; their sum exceeds "
+                          "ms_per_step because the timed region overlaps slices")
+    ext_s, n_launch = stage["extend"] * 1e-3, stage_frames * depth
+    if visits and ext_s > 0:
+        pairs_c, tris_c = visits["closest_pairs_per_ray"], visits["closest_tris_per_ray"]
+        b_ray = B_RAY_IN + B_HIT_OUT + pairs_c * B_PAIR + tris_c * B_TRI
+        achieved = m["closest_stage"] * b_ray / ext_s / 1e9
+        compulsory = m["closest_stage"] * (B_RAY_IN + B_HIT_OUT) / ext_s / 1e9
+        tr = traffic_for(name, "k_extend")
+        dram_per_launch = tr.get("dram_bytes_per_launch") if isinstance(tr, dict) else tr
+        line["roofline"] = {
+            "bound": "hbm", "kernel": "k_extend", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": dram_per_launch, "compulsory_frac": compulsory / peak,
+            "dram_frac": (dram_per_launch / (stage["extend"] / n_launch * 1e-3) / 1e9 / peak) if dram_per_launch else None,
+            "binding_limit": "L1 data pipe / SIMD efficiency, not HBM: the ~50 MB scene is L2-resident, so `frac` (algorithmic bytes over the "
+                             "HBM peak, as the contract defines it) can exceed 1; compulsory_frac counts ray-in + hit-out only, dram_frac the "
+                             "DRAM bytes ncu measured (profiles/traffic.json)",
+            "ncu": traffic_for(name, "k_extend ncu"),
+            "algorithmic_bytes_per_launch": m["closest_stage"] * b_ray / n_launch, "peak_source": which,
+            "bytes_per_ray": b_ray, "pairs_per_ray": pairs_c, "tris_per_ray": tris_c, "visit_counts": visits,
+            "launches": n_launch, "avg_launch_ms": stage["extend"] / n_launch,
+            "shadow": {"avg_launch_ms": stage["shadow"] / n_launch, "rays_per_launch": m["shadow_stage"] / n_launch,
+                       "bytes_per_ray": B_RAY_IN + B_FLAG_OUT + visits["shadow_pairs_per_ray"] * B_PAIR + visits["shadow_tris_per_ray"] * B_TRI}}
+    return line
+
+
+def run_fixed_spp(args, name, wl, d):
+    """BASELINE.json configs[4] as written: a FIXED total of samples per pixel (--spp, 4096) split over the GPUs -- spp / N frames
+    per GPU in 64-frame batches, one ncclReduce per batch overlapped with the next batch -- and the time until the combined,
+    tonemapped image is in rank 0's host memory. The reduced image is then checked against two further, independent batches."""
     torch, world, rank, local = d.torch, d.world, d.rank, d.local
+    W, H, depth = wl["width"], wl["height"], wl["depth"]
+    per_gpu = (args.spp + world - 1) // world
+    total, batch = per_gpu * world, 64
+    scene = build_scene(wl)
+    r = make_renderer(d, scene, W, H, wl, args)
+    cam = make_camera(scene, W, H)
+    pinned = torch.empty((H, W, 3), dtype=torch.uint8).pin_memory()
+
+    def render(n):
+        r.RenderBatch(cam, n) if world > 1 else r.RenderFrame(cam, n)
+
+    def total_image():
+        if world > 1:
+            r.CommSynchronize()
+            return r.CommDownloadTotal()[..., :3] if rank == 0 else None
+        r.Synchronize()
+        return r.DownloadAccum()[..., :3]
+
+    for _ in range(max(args.warmup, 3)):
+        render(1)
+    d.barrier(r)
+    r.CommReset() if world > 1 else r.ResetSamples()
+    d.barrier(r)
+    c0 = r.Counters()
+    sampler = ClockSampler(local); sampler.start()
+    t0 = time.perf_counter()
+    done, n_batches = 0, 0
+    while done < per_gpu:
+        n = min(batch, per_gpu - done)
+        render(n)
+        done += n; n_batches += 1
+    r.CommPresentAsync(pinned.data_ptr()) if world > 1 else r.PresentAsync(pinned.data_ptr())
+    d.barrier(r)                                   # the combined 8-bit image is in rank 0's host memory
+    wall = time.perf_counter() - t0
+    clocks = sampler.result()
+    c1 = r.Counters()
+    wall, rays = d.max_sum([wall, float(c1["closest_rays"] - c0["closest_rays"] + c1["shadow_rays"] - c0["shadow_rays"])])
+    final = total_image()
+    spp_final = r.CommNumSamples() if world > 1 else r.GetNumSamples()
+    render(batch); t1 = total_image()              # image check (untimed): two more batches, each an independent estimate
+    render(batch); t2 = total_image()
+    line = None
+    if rank == 0:
+        nb = batch * world
+        a_img, b_img, f_img = (t1 - final) / nb, (t2 - t1) / nb, final / spp_final
+        floor = rel_mse(a_img, b_img)
+        err = 0.5 * (rel_mse(a_img, f_img) + rel_mse(b_img, f_img))
+        line = {"metric": f"time to image, {name} {W}x{H} depth {depth}, {total} spp split over the GPUs, reduce per {batch}-frame batch",
+                "value": wall, "unit": "s", "higher_is_better": False, "n_gpus": world, "steps": n_batches, "warmup": max(args.warmup, 3),
+                "ms_per_step": wall / n_batches * 1e3, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "samples_per_s": total * W * H / wall, "mrays_per_s": rays / wall / 1e6,
+                "config": {"workload": wl["desc"], "width": W, "height": H, "total_spp": total, "frames_per_gpu": per_gpu, "batches": n_batches,
+                           "triangles": scene.tris.shape[0], "parallelism": f"{world} GPU(s), samples split inside the library, one ncclReduce per "
+                           "batch on its own stream overlapped with the next batch (double-buffered accumulators)"},
+                "e2e": {"value": wall, "unit": "s", "h2d_bytes_per_step": 76, "d2h_bytes_per_step": W * H * 3 / n_batches,
+                        "what": "wall clock from the first batch to the combined tonemapped image in rank 0's pinned host memory"},
+                "image_check": {"spp": int(spp_final), "relmse_final_vs_independent_batches": err, "relmse_between_independent_batches": floor,
+                                "ok": bool(err < floor and np.isfinite(f_img).mean() > 0.999),
+                                "note": f"two further {nb}-spp batches (untimed) are each an independent estimate of the image; the final image "
+                                        "must be closer to both than they are to each other"},
+                "reduce_ms_last": r.CommLastReduceMs() if world > 1 else 0.0,
+                "gpu_launches": int(c1["kernel_launches"] - c0["kernel_launches"]), "clocks": clocks}
+    r.CleanUp()
+    return line
+
+
+def run_micro(args, name, wl, d, sub=False):
+    """configs[3]: fixed ray batches against a scene far larger than L2 -- the HBM-bound case."""
+    torch, world, rank, local = d.torch, d.world, d.rank, d.local
+    line = None
     from gpupathtracer_b200 import Renderer
     n = wl["n_rays"]
     scene, closest, anyr = micro_scene_and_rays(n, 0xB200 + 7 * rank)
@@ -541,6 +734,13 @@ def run_micro(args, name, wl):
             line["parity_on_sample"] = {"closest_bit_exact": bool(np.array_equal(want.view(np.uint32), hits[:m].view(np.uint32))),
                                         "any_bit_exact": bool(np.array_equal(wflag, d_flags[:m].cpu().numpy()))}
             b_ray, pairs, tris = bytes_per_ray(cc, m, B_HIT_OUT)
+            if args.bvh == "reference":                      # visit counts of ALL rays of the batch, from the instrumented kernel
+                r.SetVisitCounting(True)
+                r.TraceClosestDevice(d_closest.data_ptr(), n, d_hits.data_ptr()); r.Synchronize()
+                r.SetVisitCounting(False)
+                v = r.Counters()
+                pairs, tris = v["closest_pair_tests"] / v["counted_closest_rays"], v["closest_tri_tests"] / v["counted_closest_rays"]
+                b_ray = B_RAY_IN + B_HIT_OUT + pairs * B_PAIR + tris * B_TRI
             achieved = n * b_ray / (ms_c / steps * 1e-3) / 1e9
             line["roofline"] = {"bound": "hbm", "kernel": "k_trace_batch<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
                                 "frac": achieved / peak,
@@ -550,15 +750,14 @@ def run_micro(args, name, wl):
                                 "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": steps, "avg_launch_ms": ms_c / steps,
                                 "note": "avg_launch_ms spans the ray binning (4 small kernels, ~0.35 ms, reference layout only) and "
                                         "k_trace_batch; the binning halves the DRAM traffic of the trace (profiles/traffic.json)"}
-        print(json.dumps(line))
     r.CleanUp()
-    d.close()
+    return line
 
 
-def run_primary(args, name, wl):
+def run_primary(args, name, wl, d, sub=False):
     """configs[0]: BVH build + 1 spp primary closest-hit at 1280x720."""
-    d = Dist()
     torch, world, rank, local = d.torch, d.world, d.rank, d.local
+    line = None
     from gpupathtracer_b200 import Renderer, Scene, scenes, build_bvh_host
     W, H = wl["width"], wl["height"]
     scene = Scene(scenes.bunny_like(seed=1))
@@ -692,9 +891,8 @@ def run_primary(args, name, wl):
                                 "algorithmic_bytes_per_launch": n * b_ray, "peak_source": which, "bytes_per_ray": b_ray,
                                 "pairs_per_ray": pairs, "tris_per_ray": tris, "launches": args.steps, "avg_launch_ms": ms_total / args.steps,
                                 "note": "coherent primary rays on a 10 MB tree: L1/L2-resident, issue-slot bound (DESIGN.md 4)"}
-        print(json.dumps(line))
     r.CleanUp()
-    d.close()
+    return line
 
 
 def main():
@@ -705,6 +903,9 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--workload", default="atrium", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="default command only: skip the short runs of the other BASELINE.json configs")
+    ap.add_argument("--spp", type=int, default=0, help="path-tracing workloads: render a FIXED total of samples per pixel split over the GPUs "
+                    "(64-frame batches per GPU, one reduce per batch) and report time-to-image (BASELINE.json configs[4] as written: --workload 4k --spp 4096)")
     ap.add_argument("--builder", default="host", choices=["host", "device", "ploc"],
                     help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels; ploc: the same with a "
                          "PLOC hierarchy (pt_build_bvh_device_ploc)")
@@ -712,13 +913,35 @@ def main():
                     help="device BVH layout: the reference's binary fp32 tree (bit-exact) or the compressed 8-/4-wide collapse of it")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    default_command = args.workload == "atrium" and args.builder == "host" and args.bvh == "reference" and not args.spp
     if args.steps is None:
         args.steps = {"pt": 64, "rays": 8, "primary": 32}[wl["kind"]] if args.impl != "reference" else 3
         if args.workload == "4k":
             args.steps = 16
     if args.impl == "reference":
         return run_reference(args)
-    {"pt": run_pathtrace, "rays": run_micro, "primary": run_primary}[wl["kind"]](args, args.workload, wl)
+    d = Dist()
+    runners = {"pt": run_pathtrace, "rays": run_micro, "primary": run_primary}
+    if args.spp:
+        line = run_fixed_spp(args, args.workload, wl, d)
+    else:
+        line = runners[wl["kind"]](args, args.workload, wl, d)
+    if default_command and d.world == 1 and not args.no_configs and line is not None:
+        # the other BASELINE.json configs, short runs (value, e2e, parity_on_sample, roofline), so that one command observes all five
+        import copy
+        line["configs"] = {}
+        for name, steps in (("bunny", 8), ("bathroom", 8), ("4k", 4), ("micro", 2)):
+            a2 = copy.copy(args); a2.steps = steps; a2.warmup = 3
+            t0 = time.perf_counter()
+            try:
+                sub = runners[WORKLOADS[name]["kind"]](a2, name, WORKLOADS[name], d, sub=True)
+                sub["wall_s"] = time.perf_counter() - t0
+                line["configs"][name] = sub
+            except Exception as e:                 # never lose the headline line to a side run
+                line["configs"][name] = {"error": repr(e)}
+    if line is not None:
+        print(json.dumps(line))
+    d.close()
 
 
 if __name__ == "__main__":

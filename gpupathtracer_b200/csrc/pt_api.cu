@@ -130,6 +130,7 @@ int pt_create(const pt_config* cfg, pt_context** out) {
     }
     for (int k = 0; k < 4; k++) CK(c->d_shadow[k].alloc(npx));
     CK(c->d_hits.alloc(npx));
+    for (int k = 0; k < 2; k++) CK(c->d_present[k].alloc(npx * 3));    // present targets up front: a cudaMalloc inside the frame loop drains the device
     CK(c->d_counters.alloc((size_t)2 * c->n_slices * (cfg->max_depth + 2)));   // 2 blocks per slice: frame parity
     CK(c->d_totals.alloc(4));
     CK(cudaMemsetAsync(c->d_totals.p, 0, 4 * sizeof(unsigned long long), c->stream));
@@ -992,18 +993,21 @@ int pt_present_async(pt_context* c, uint32_t num_samples, uint8_t* host_rgb_u8) 
     const bool plibm = (c->cfg.parity_flags & PT_PARITY_LIBM) != 0;
     CK(c->d_present[k].alloc(npx * 3));
     if (c->pending_join) {
-        // Chained frames (pt_render_frames(1) without a join): every slice resolves ITS OWN pixels on its own stream right
-        // behind its last kernels, so slice s's next frame waits for slice s only; just the copy waits for all slices.
+        // Chained frames (pt_render_frames(1) without a join): every slice resolves ITS OWN pixels on its own streams right
+        // behind its last kernel, so slice s's next frame waits for slice s only; just the copy waits for all slices.
         // (Present.frag runs per fragment: which stream shades a pixel changes nothing.)
         for (int s = 0; s < c->n_slices; s++) {
             const SliceStreams& ss = c->slice_streams[s];
             const int first = s * c->slice_size;
             const int count = (int)npx - first < c->slice_size ? (int)npx - first : c->slice_size;
-            CK(cudaStreamWaitEvent(ss.a, c->slice_done[2 * s + 1], 0));         // the slice's last shadow kernel (stream b)
-            CK(cudaStreamWaitEvent(ss.a, c->ev_copied[k], 0));                  // the copy that last read this buffer
-            launch_resolve_slice(c->d_accum, first, count, c->cfg.width, num_samples, c->d_present[k].p, ss.a, plibm);
+            // On stream b, right behind the slice's last shadow kernel (the last writer of its pixels). Stream a stays free
+            // for the next frame's raygen + extend(0); its shade(0) -- the next writer of these pixels -- waits for
+            // ev_shadow, which is therefore recorded again behind the resolve.
+            CK(cudaStreamWaitEvent(ss.b, c->ev_copied[k], 0));                  // the copy that last read this buffer
+            launch_resolve_slice(c->d_accum, first, count, c->cfg.width, num_samples, c->d_present[k].p, ss.b, plibm);
             c->counters.kernel_launches++;
-            CK(cudaEventRecord(c->slice_presented[s], ss.a));
+            CK(cudaEventRecord(c->slice_presented[s], ss.b));
+            CK(cudaEventRecord(ss.ev_shadow, ss.b));
             CK(cudaStreamWaitEvent(c->copy_stream, c->slice_presented[s], 0));
         }
         c->slices_presenting = true;
