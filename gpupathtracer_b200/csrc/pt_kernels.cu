@@ -18,6 +18,10 @@
                                 // 8 / 9 / 10 (48 registers, 16-32 B of spills): atrium 3.20 / 3.22 / 3.19 Grays/s, bathroom 2.87 / 2.93 / 2.85,
                                 // 10M-triangle batch 3.12 / 3.23 / 3.24, bunny primary rays 4.49 / 4.52 / 4.31
 #endif
+#ifndef PT_DEFAULT_CARVEOUT
+#define PT_DEFAULT_CARVEOUT -1
+#define PT_DEFAULT_CARVEOUT_SHADE -1
+#endif
 #include "pt_kernels.h"
 #include "pt_trace.cuh"
 #include "pt_trace_wide.cuh"
@@ -696,6 +700,25 @@ void query_launch_dims(int device, int wide, LaunchDims* out) {
         if (out->top_pairs > 700) out->top_pairs = 700;                      // 44.8 KB: below the 48-KB dynamic limit without opt-in
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ext, k_extend<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shadow, k_shadow<Traverser>, PT_TRACE_THREADS, 64 * out->top_pairs);
+    }
+    // Shared-memory carve-out of the frame kernels (percent of the SM's 228 KB; -1 = the driver's choice). The driver gives
+    // the traversal kernels 100 KB although 9 CTAs x (4 KB stack + 1 KB) need 45 KB, and k_shade 32 KB: unequal preferences
+    // and less L1 than possible for kernels that live on their L1 hit rate.
+    {
+        int carve = PT_DEFAULT_CARVEOUT, carve_shade = PT_DEFAULT_CARVEOUT_SHADE;
+        if (const char* e = getenv("PT_CARVEOUT")) carve = atoi(e);
+        if (const char* e = getenv("PT_CARVEOUT_SHADE")) carve_shade = atoi(e);
+        if (carve >= 0) {
+            cudaFuncSetAttribute(k_extend<Traverser>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_shadow<Traverser>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_trace_batch<false, Traverser>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+            cudaFuncSetAttribute(k_trace_batch<true, Traverser>, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
+        }
+        if (carve_shade >= 0) {
+            cudaFuncSetAttribute(k_shade<0, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve_shade);
+            cudaFuncSetAttribute(k_shade<1, false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve_shade);
+            cudaFuncSetAttribute(k_raygen<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve_shade);
+        }
     }
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_shade, k_shade<0, false>, PT_SHADE_THREADS, 0);
     int per = per_sm_ext < per_sm_shadow ? per_sm_ext : per_sm_shadow;

@@ -79,12 +79,28 @@ __device__ __forceinline__ bool tri_test(const LeafTri* __restrict__ rec, V3 o, 
     id = last ? ~id : id;
     V3 p = cross(d, v02);
     float det = dot(v01, p);
-    float idet = 1.0f / det;
     V3 tv = o - p0;
+#ifdef PT_TRI_EARLY_REJECT
+    // Experiment: u, v and t are numerator * (1 / det), so each has the sign of numerator x det (or is 0 / NaN / inf when one of
+    // them is); a numerator that is zero or of the other sign than det cannot pass `u > 0`, `v > 0`, `t > 0`. Rejecting on the
+    // signs skips the IEEE division (a ~20-instruction subroutine) when every lane of the leaf round rejects; everything that
+    // is not rejected here goes through the unchanged arithmetic below, so accepted hits keep their bits.
+    const float un = dot(tv, p);
+    if (un == 0.0f || ((un < 0.0f) != (det < 0.0f))) return false;
+    V3 q = cross(tv, v01);
+    const float vn = dot(d, q), tn = dot(v02, q);
+    if (vn == 0.0f || ((vn < 0.0f) != (det < 0.0f)) || tn == 0.0f || ((tn < 0.0f) != (det < 0.0f))) return false;
+    float idet = 1.0f / det;
+    float u = un * idet;
+    float v = vn * idet;
+    float t = tn * idet;
+#else
+    float idet = 1.0f / det;
     float u = dot(tv, p) * idet;
     V3 q = cross(tv, v01);
     float v = dot(d, q) * idet;
     float t = dot(v02, q) * idet;
+#endif
     if (u > 0.0f && u < 1.0f && v > 0.0f && u + v < 1.0f && t < h.t && t > 0.0f) {
         h.t = t; h.u = u; h.v = v; h.tri = id;
         return true;
@@ -176,7 +192,11 @@ struct Traverser {
             // Near child first. For ANY this differs from IfIfAnyHit's fixed order (BVH.glsl:806-812) but cannot
             // change the flag: until the first accepted triangle h.t stays at tmax, so which leaves are reachable
             // does not depend on the visiting order, and the answer is "some reachable leaf holds a hit".
+#ifdef PT_ANY_FIXED_ORDER      // experiment: any-hit rays keep the reference's child order (larger child first, BVH.glsl:806-812)
+            bool swap = ANY ? false : d0 > d1;
+#else
             bool swap = d0 > d1;
+#endif
             current = swap ? sub1 : sub0;
             const int far_child = swap ? sub0 : sub1;
 #ifdef PT_POP_CULL
