@@ -313,7 +313,7 @@ class Dist:
 
 
 LAYOUTS = {"reference": 0, "wide": 1, "wide4": 2}
-BUILDERS = {"device": "device", "ploc": "ploc"}
+BUILDERS = {"device": "device", "ploc": "ploc", "split": "split", "split_lbvh": "split_lbvh"}
 
 
 def make_renderer(d, scene, W, H, wl, args, **kw):
@@ -534,7 +534,7 @@ def pathtrace_line(args, name, wl, d, scene, r, cam, m):
                          "note": "value / ms_per_step are the MEDIAN repetition of K back-to-back frames"},
         "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
                    "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
-                   "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
+                   "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                    "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                    "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
                    "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
@@ -657,7 +657,7 @@ def run_micro(args, name, wl, d, sub=False):
     n = wl["n_rays"]
     scene, closest, anyr = micro_scene_and_rays(n, 0xB200 + 7 * rank)
     t0 = time.perf_counter()
-    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh={"device": "device", "ploc": "ploc"}.get(args.builder, "build"),
+    r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh=BUILDERS.get(args.builder, "build"),
                               bvh_layout=LAYOUTS[args.bvh])
     init_s = time.perf_counter() - t0
     d_closest = torch.from_numpy(closest).cuda()
@@ -709,7 +709,7 @@ def run_micro(args, name, wl, d, sub=False):
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "rays_per_step": 2 * n,
-                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
+                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                        "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "bvh_nodes": int(r.bvh_stats.n_nodes), "bvh_refs": int(r.bvh_stats.n_refs),
                        "l2": "ray batches (2 x 512 MB) and tree + leaf stream (~1.2 GB) exceed the 126 MB L2",
@@ -766,7 +766,7 @@ def run_primary(args, name, wl, d, sub=False):
         _, _, st = build_bvh_host(scene.tris)
         builds.append(st["build_ms"])
     r = Renderer().Initialize(W, H, scene, max_depth=1, device=local, seed=0xB200 + rank,
-                              bvh={"device": "device", "ploc": "ploc"}.get(args.builder, "build"), bvh_layout=LAYOUTS[args.bvh])
+                              bvh=BUILDERS.get(args.builder, "build"), bvh_layout=LAYOUTS[args.bvh])
     cam = make_camera(scene, W, H)
     r.lib.pt_set_camera(r.ctx, cam.plane)
     n = W * H
@@ -906,7 +906,7 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="default command only: skip the short runs of the other BASELINE.json configs")
     ap.add_argument("--spp", type=int, default=0, help="path-tracing workloads: render a FIXED total of samples per pixel split over the GPUs "
                     "(64-frame batches per GPU, one reduce per batch) and report time-to-image (BASELINE.json configs[4] as written: --workload 4k --spp 4096)")
-    ap.add_argument("--builder", default="host", choices=["host", "device", "ploc"],
+    ap.add_argument("--builder", default="host", choices=["host", "device", "ploc", "split", "split_lbvh"],
                     help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels; ploc: the same with a "
                          "PLOC hierarchy (pt_build_bvh_device_ploc)")
     ap.add_argument("--bvh", default="reference", choices=["reference", "wide", "wide4"],

@@ -83,6 +83,8 @@ SYMBOLS = [
     ("pt_build_bvh", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_build_bvh_device", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_build_bvh_device_ploc", C.c_int, [_P, C.c_int32, C.POINTER(pt_bvh_stats)]),
+    ("pt_build_bvh_device_split", C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(pt_bvh_stats)]),
+    ("pt_build_bvh_device_sah", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
     ("pt_bvh_build_host", C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(_F), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32), C.POINTER(pt_bvh_stats)]),
     ("pt_free", None, [_P]),
     ("pt_bvh_collapse_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, C.c_int32, C.POINTER(C.POINTER(C.c_uint8)),
@@ -432,9 +434,14 @@ class Renderer:
         _check(self.lib.pt_set_environment_color(ctx, _f3(scene.env_color)))
         if getattr(scene, "env_cubemap", None) is not None:
             self.SetEnvironmentCubemap(scene.env_cubemap)
-        if bvh in ("device", "ploc"):
+        if bvh in ("device", "ploc", "split", "split_lbvh", "sah"):
             stats = pt_bvh_stats()
-            if bvh == "ploc":
+            if bvh in ("split", "split_lbvh"):      # device build with spatial splits: PLOC (or the Morton hierarchy) over pre-split references
+                _check(self.lib.pt_build_bvh_device_split(ctx, int(os.environ.get("PT_PLOC_RADIUS", "16")) if bvh == "split" else 0,
+                                                          int(os.environ.get("PT_SPLIT_GRID", "64")), C.byref(stats)))
+            elif bvh == "sah":                       # top-down binned SAH on the device
+                _check(self.lib.pt_build_bvh_device_sah(ctx, C.byref(stats)))
+            elif bvh == "ploc":
                 _check(self.lib.pt_build_bvh_device_ploc(ctx, int(os.environ.get("PT_PLOC_RADIUS", "16")), C.byref(stats)))
             else:
                 _check(self.lib.pt_build_bvh_device(ctx, C.byref(stats)))

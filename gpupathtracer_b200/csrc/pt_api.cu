@@ -555,13 +555,19 @@ int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
 }
 
 // The device builder (pt_bvh_gpu.cu): Morton LBVH, one triangle per leaf, reference serialised form
-static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radius);
-int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) { return build_bvh_on_device(c, stats, 0); }
+static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radius, int split_grid);
+int pt_build_bvh_device(pt_context* c, pt_bvh_stats* stats) { return build_bvh_on_device(c, stats, 0, 0); }
 int pt_build_bvh_device_ploc(pt_context* c, int32_t radius, pt_bvh_stats* stats) {
     if (radius < 1 || radius > 256) return fail(PT_ERR_INVALID, "pt_build_bvh_device_ploc: radius 1 .. 256");
-    return build_bvh_on_device(c, stats, radius);
+    return build_bvh_on_device(c, stats, radius, 0);
 }
-static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radius) {
+int pt_build_bvh_device_split(pt_context* c, int32_t ploc_radius, int32_t split_grid, pt_bvh_stats* stats) {
+    if (ploc_radius < 0 || ploc_radius > 256) return fail(PT_ERR_INVALID, "pt_build_bvh_device_split: ploc_radius 0 (Morton hierarchy) .. 256");
+    if (split_grid < 2 || split_grid > 1024) return fail(PT_ERR_INVALID, "pt_build_bvh_device_split: split_grid 2 .. 1024");
+    return build_bvh_on_device(c, stats, ploc_radius, split_grid);
+}
+int pt_build_bvh_device_sah(pt_context* c, pt_bvh_stats* stats) { return build_bvh_on_device(c, stats, -1, 0); }
+static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radius, int split_grid) {
     if (!c) return fail(PT_ERR_INVALID, "pt_build_bvh_device: null context");
     if (c->h_tris.empty() || !c->d_tris.p) return fail(PT_ERR_INVALID, "pt_build_bvh_device: call pt_set_triangles first");
     const int64_t n = (int64_t)(c->h_tris.size() / 20);
@@ -569,24 +575,37 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
     PT_ENTER(c);
     auto t0 = std::chrono::steady_clock::now();
     pt_invalidate_graphs(c);
+    // spatial splits first (pt_build_bvh_device_split): the leaves of the build are then m >= n references
+    RefSet refset; float split_ms = 0.0f;
+    if (split_grid > 0) {
+        int l = presplit_device(c->d_tris.p, (int)n, split_grid, &refset, c->stream, &split_ms);
+        if (l < 0) return fail(l == -(int)cudaErrorInvalidValue ? PT_ERR_LIMIT : PT_ERR_CUDA, "pt_build_bvh_device_split: %s",
+                               l == -(int)cudaErrorInvalidValue ? "the split grid would more than double the scene; use a coarser split_grid"
+                                                                 : cudaGetErrorString((cudaError_t)(-l)));
+        c->counters.kernel_launches += l;
+    }
+    const int64_t m = split_grid > 0 ? refset.m : n;
+    struct RefGuard { RefSet* r; ~RefGuard() { free_refset(r); } } guard{&refset};
     // the serialised tree stays on the device (read back only when somebody asks for it: pt_get_bvh, wide collapse);
     // the traversal layout (pair records + leaf stream) is written by the build kernels themselves
-    CK(c->d_ser_nodes.alloc(2 * (size_t)(2 * n - 1)));
-    CK(c->d_ser_refs.alloc((size_t)n));
-    CK(c->d_pairs.alloc((size_t)(n - 1)));
-    CK(c->d_leaf.alloc((size_t)n));
+    CK(c->d_ser_nodes.alloc(2 * (size_t)(2 * m - 1)));
+    CK(c->d_ser_refs.alloc((size_t)m));
+    CK(c->d_pairs.alloc((size_t)(m - 1)));
+    CK(c->d_leaf.alloc((size_t)m));
     float kernel_ms = 0.0f; int depth = 0;
+    const RefSet* rs = split_grid > 0 ? &refset : nullptr;
     int launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
-                                     c->stream, &kernel_ms, ploc_radius);
+                                     c->stream, &kernel_ms, ploc_radius, rs);
     if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
     c->counters.kernel_launches += launches;
-    if (depth >= PT_MAX_TREE_DEPTH && ploc_radius > 0) {
+    kernel_ms += split_ms;
+    if (depth >= PT_MAX_TREE_DEPTH && ploc_radius != 0) {
         // agglomerative clustering does not bound the depth (chains of small clusters joining a big one); the Morton
         // hierarchy does (30 key bits + index tie-break), so it takes over. Not an error: the note is left in pt_last_error().
-        fail(PT_OK, "pt_build_bvh_device_ploc: PLOC tree depth %d exceeds the traversal stack (%d); Morton hierarchy used instead", depth, PT_MAX_TREE_DEPTH);
+        fail(PT_OK, "pt_build_bvh_device_%s tree depth %d exceeds the traversal stack (%d); Morton hierarchy used instead", ploc_radius > 0 ? "ploc: PLOC" : "sah: SAH", depth, PT_MAX_TREE_DEPTH);
         float ms2 = 0.0f;
         launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
-                                     c->stream, &ms2, 0);
+                                     c->stream, &ms2, 0, rs);
         if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
         c->counters.kernel_launches += launches;
         kernel_ms += ms2;
@@ -595,18 +614,18 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
         c->d_pairs.release(); c->d_leaf.release();
         return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (%d); use pt_build_bvh", depth, PT_MAX_TREE_DEPTH);
     }
-    c->n_leaf = (int)n;
+    c->n_leaf = (int)m;
     c->top_pairs = 0;                                             // Karras order: the top levels are not contiguous
     c->h_bvh = HostBvh();
-    c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = (int)n;
-    c->host_bvh_stale = true; c->ser_nodes = 2 * n - 1; c->ser_refs = n;
+    c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = (int)m;
+    c->host_bvh_stale = true; c->ser_nodes = 2 * m - 1; c->ser_refs = m;
     if (c->cfg.bvh_layout != PT_BVH_REFERENCE) {                 // the wide collapse runs on the host
         int rc = pt_ensure_host_bvh(c);
         if (rc != PT_OK) return rc;
         if ((rc = upload_wide(c)) != PT_OK) return rc;
     }
     if (stats) {
-        stats->n_nodes = (int)(2 * n - 1); stats->n_refs = (int)n; stats->n_leaves = (int)n; stats->max_depth = depth;
+        stats->n_nodes = (int)(2 * m - 1); stats->n_refs = (int)m; stats->n_leaves = (int)m; stats->max_depth = depth;
         stats->sah_cost = c->host_bvh_stale ? 0.0f : c->h_bvh.sah_cost;     // known once the tree has been read back
         stats->build_ms = kernel_ms;        // CUDA-event time of the build kernels (the tree is usable at that point)
         stats->total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();

@@ -36,6 +36,7 @@ static float kCostIntersection = 5.33f;
 static int kBins = 16;
 constexpr int kMaxDepth = 56;          // the traversal stack holds PT_MAX_TREE_DEPTH (96) entries
 constexpr float kAlpha = 1e-5f;
+static bool g_no_spatial = false;     // PT_BVH_NO_SPATIAL=1 (experiments): object splits only, to tell what the spatial splits are worth
 constexpr int kParallelThreshold = 8192;
 
 struct Box {
@@ -258,10 +259,10 @@ struct Builder {
         if (n > kBins) object_split_binned(refs, best);
         else object_split_sweep(refs, best);
         // spatial split only where the object split leaves overlapping children (BVH.cpp:2015-2021)
-        bool try_spatial = true;
+        bool try_spatial = !g_no_spatial;
         if (best.axis >= 0) {
             Box ov = best.lbox; ov.clip(best.rbox);
-            try_spatial = ov.valid() && ov.area() > kAlpha * root_area;
+            try_spatial = !g_no_spatial && ov.valid() && ov.area() > kAlpha * root_area;
         }
         if (try_spatial) {
             Split sp = best;
@@ -336,6 +337,7 @@ struct Flat {
 bool build_sbvh(const float* tris_pre, int64_t n, int n_threads, HostBvh& out, std::string& msg) {
     if (n < 2) { msg = "need at least 2 triangles (the root must be an inner node, BVH.glsl:627)"; return false; }
     if (const char* e = getenv("PT_BVH_CI")) kCostIntersection = (float)atof(e);
+    if (const char* e = getenv("PT_BVH_NO_SPATIAL")) g_no_spatial = atoi(e) != 0;
     if (const char* e = getenv("PT_BVH_BINS")) kBins = std::min(std::max(atoi(e), 2), kMaxBins);
     Builder b;
     b.tris = tris_pre;

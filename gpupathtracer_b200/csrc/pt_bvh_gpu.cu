@@ -38,13 +38,24 @@ __device__ __forceinline__ void tri_box(const float4* t, float lo[3], float hi[3
     }
 }
 
-__global__ void k_scene_bounds(const float4* __restrict__ tris, int n, unsigned* bounds /* 3 min, 3 max (ordered uints) */) {
+// What the n leaves of a build are: the triangles themselves (ref_* null: leaf i = triangle i, its box = the triangle's), or a
+// set of REFERENCES from the pre-split pass below (leaf i = triangle ref_tri[i] restricted to the box [ref_lo[i], ref_hi[i]]).
+struct LeafSrc { const float4* tris; const int* ref_tri; const float4* ref_lo; const float4* ref_hi; };
+__device__ __forceinline__ void leaf_box(const LeafSrc& s, int id, float lo[3], float hi[3]) {
+    if (s.ref_lo) {
+        float4 a = s.ref_lo[id], b = s.ref_hi[id];
+        lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; hi[0] = b.x; hi[1] = b.y; hi[2] = b.z;
+    } else tri_box(s.tris + 5 * (size_t)id, lo, hi);
+}
+__device__ __forceinline__ int leaf_tri(const LeafSrc& s, int id) { return s.ref_tri ? s.ref_tri[id] : id; }
+
+__global__ void k_scene_bounds(LeafSrc src, int n, unsigned* bounds /* 3 min, 3 max (ordered uints) */) {
     __shared__ unsigned s[6];
     if (threadIdx.x < 3) s[threadIdx.x] = 0xffffffffu; else if (threadIdx.x < 6) s[threadIdx.x] = 0u;
     __syncthreads();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         float lo[3], hi[3];
-        tri_box(tris + 5 * (size_t)i, lo, hi);
+        leaf_box(src, i, lo, hi);
 #pragma unroll
         for (int k = 0; k < 3; k++) {
             // centroid bounds are what the Morton grid needs; triangle boxes are fitted later
@@ -65,11 +76,11 @@ __device__ __forceinline__ unsigned expand10(unsigned v) {      // 10 bits -> ev
     return v;
 }
 
-__global__ void k_morton(const float4* __restrict__ tris, int n, const unsigned* __restrict__ bounds, unsigned* keys, int* vals) {
+__global__ void k_morton(LeafSrc src, int n, const unsigned* __restrict__ bounds, unsigned* keys, int* vals) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float lo[3], hi[3];
-    tri_box(tris + 5 * (size_t)i, lo, hi);
+    leaf_box(src, i, lo, hi);
     unsigned q[3];
 #pragma unroll
     for (int k = 0; k < 3; k++) {
@@ -206,13 +217,13 @@ __global__ void k_hierarchy(const unsigned* __restrict__ keys, int n, int2* chil
 }
 
 // bottom-up boxes: the second thread to arrive at an inner node fits it and climbs on
-__global__ void k_fit(const float4* __restrict__ tris, const int* __restrict__ vals, int n, const int2* __restrict__ children,
+__global__ void k_fit(LeafSrc src, const int* __restrict__ vals, int n, const int2* __restrict__ children,
                       const int* __restrict__ parent_inner, const int* __restrict__ parent_leaf, float4* leaf_lo, float4* leaf_hi,
                       float4* inner_lo, float4* inner_hi, unsigned* flags) {
     int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l >= n) return;
     float lo[3], hi[3];
-    tri_box(tris + 5 * (size_t)vals[l], lo, hi);
+    leaf_box(src, vals[l], lo, hi);
     leaf_lo[l] = make_float4(lo[0], lo[1], lo[2], 0.0f);
     leaf_hi[l] = make_float4(hi[0], hi[1], hi[2], 0.0f);
     int cur = parent_leaf[l];
@@ -238,12 +249,12 @@ __global__ void k_fit(const float4* __restrict__ tris, const int* __restrict__ v
 // the cluster array is compacted in order, repeat until one cluster is left. Bottom-up agglomeration with a surface-area
 // criterion gives trees close to a SAH sweep (the Karras hierarchy above splits by Morton bits only), at the price of
 // ~4 small kernels per round and one 4-byte read-back of the cluster count. Output goes through the same k_emit.
-__global__ void k_ploc_leaves(const float4* __restrict__ tris, const int* __restrict__ vals, int n, float4* leaf_lo, float4* leaf_hi,
+__global__ void k_ploc_leaves(LeafSrc src, const int* __restrict__ vals, int n, float4* leaf_lo, float4* leaf_hi,
                               int* cid, float4* clo, float4* chi) {
     int l = blockIdx.x * blockDim.x + threadIdx.x;
     if (l >= n) return;
     float lo[3], hi[3];
-    tri_box(tris + 5 * (size_t)vals[l], lo, hi);
+    leaf_box(src, vals[l], lo, hi);
     float4 a = make_float4(lo[0], lo[1], lo[2], 0.0f), b = make_float4(hi[0], hi[1], hi[2], 0.0f);
     leaf_lo[l] = a; leaf_hi[l] = b;
     cid[l] = ~l; clo[l] = a; chi[l] = b;
@@ -364,16 +375,17 @@ __device__ __forceinline__ float box_area(float4 lo, float4 hi) {
 __global__ void k_emit(const int* __restrict__ vals, int n, const int2* __restrict__ children, const float4* __restrict__ leaf_lo,
                        const float4* __restrict__ leaf_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi,
                        float4* nodes /* 2 float4 per node */, int* refs, const float4* __restrict__ tris, BvhPair* pairs, LeafTri* leaf,
-                       const int* __restrict__ remap /* optional: inner node id -> position */) {
+                       const int* __restrict__ remap /* optional: inner node id -> position */, const int* __restrict__ ref_tri) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    refs[i] = -vals[i];
+    const int tri_of_leaf = ref_tri ? ref_tri[vals[i]] : vals[i];
+    refs[i] = -tri_of_leaf;
     if (leaf) {
         // what upload_leaf_stream does on the host: intersection record of the leaf's triangle. The stream marks the end of a
         // leaf with ~index, which triangle 0 can carry too -- unlike the reference list's -0 == 0 (BVH.cpp:2117), whose
         // run-on into the next leaf costs triangle tests and changes no result. (A tree read back and re-installed through
         // pt_set_bvh gets the copied-marker behaviour of the reference again.)
-        const int tri = vals[i];
+        const int tri = tri_of_leaf;
         const float4* t = tris + 5 * (size_t)tri;
         float4 t0 = t[0], t1 = t[1], t2 = t[2];
         leaf[i].r[0] = t0; leaf[i].r[1] = t1;
@@ -421,17 +433,536 @@ __global__ void k_depth(const int* __restrict__ parent_inner, const int* __restr
     if ((threadIdx.x & 31) == 0) atomicMax(max_depth, d);
 }
 
+// ---------------------------------------------------------------- top-down binned SAH on the device (pt_build_bvh_device_sah)
+// The reference's builder is a top-down SAH search (FindBestObjectSplit, BVH.cpp:1619-1763: 8 bins per axis, sweep below 8
+// references); its spatial splits are worth 2 % of SAH cost on the atrium and nothing on the bunny scene, the
+// top-down search itself is worth the 8-10 % that separate it from Morton / PLOC trees. Here the same search runs on the device,
+// breadth first: every level bins the primitives of all nodes larger than SAH_SMALL at once (SAH_BINS bins per axis over the
+// node's box, counts + boxes accumulated with atomics: block-private in shared memory for the node a block starts in, global for
+// the rest), one thread per node picks the cheapest of the 3 x (SAH_BINS - 1) planes and creates the children, and the primitives
+// are partitioned into the other index buffer; subtrees of <= SAH_SMALL primitives are finished by ONE thread each with an exact
+// sweep. One primitive per leaf, as the other device builders; inner ids are handed out by an atomic counter (root = 0) and made
+// depth-first by k_ploc_relabel, so the emitted tree does not depend on the order atomics happened to land in.
+#define SAH_BINS 16
+#define SAH_SMALL 16
+struct SahNode { int begin, end; };                            // position range of an inner node in the index buffer
+struct SahSplit { int axis, plane, nl; int left, right; };     // axis < 0: median by position; children: inner id, or ~leaf position
+
+__device__ __forceinline__ int sah_bin(float c, float lo, float hi) {
+    const float e = hi - lo;
+    if (!(e > 0.0f)) return 0;
+    int b = (int)((c - lo) / e * (float)SAH_BINS);
+    return b < 0 ? 0 : (b >= SAH_BINS ? SAH_BINS - 1 : b);
+}
+__device__ __forceinline__ float half_area(const float lo[3], const float hi[3]) {
+    const float x = hi[0] - lo[0], y = hi[1] - lo[1], z = hi[2] - lo[2];
+    return x * (y + z) + y * z;
+}
+
+__global__ void k_sah_init(LeafSrc src, int n, float4* prim_lo, float4* prim_hi, int* idx, int* node_of, unsigned* root_bounds) {
+    __shared__ unsigned s[6];
+    if (threadIdx.x < 3) s[threadIdx.x] = 0xffffffffu; else if (threadIdx.x < 6) s[threadIdx.x] = 0u;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float lo[3], hi[3];
+        leaf_box(src, i, lo, hi);
+        prim_lo[i] = make_float4(lo[0], lo[1], lo[2], 0.0f); prim_hi[i] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+        idx[i] = i; node_of[i] = 0;
+#pragma unroll
+        for (int k = 0; k < 3; k++) { atomicMin(&s[k], f2ord(lo[k])); atomicMax(&s[3 + k], f2ord(hi[k])); }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) atomicMin(&root_bounds[threadIdx.x], s[threadIdx.x]);
+    else if (threadIdx.x < 6) atomicMax(&root_bounds[threadIdx.x], s[threadIdx.x]);
+}
+__global__ void k_sah_root(const unsigned* __restrict__ root_bounds, int n, SahNode* nodes, float4* inner_lo, float4* inner_hi, int* parent_inner,
+                           int* subtree, int* slot_of, int* lists /* [0] large count, [1] small count */, int* large, int* small) {
+    nodes[0].begin = 0; nodes[0].end = n;
+    inner_lo[0] = make_float4(ord2f(root_bounds[0]), ord2f(root_bounds[1]), ord2f(root_bounds[2]), 0.0f);
+    inner_hi[0] = make_float4(ord2f(root_bounds[3]), ord2f(root_bounds[4]), ord2f(root_bounds[5]), 0.0f);
+    parent_inner[0] = -1; subtree[0] = n - 1;
+    if (n > SAH_SMALL) { large[0] = 0; slot_of[0] = 0; lists[0] = 1; lists[1] = 0; }
+    else { small[0] = 0; slot_of[0] = -1; lists[0] = 0; lists[1] = 1; }
+}
+
+// bins of every large node of this level: cnt[slot][axis][bin], box[slot][axis][bin][6] (ordered uints)
+__global__ void __launch_bounds__(BVH_THREADS)
+k_sah_bin(const int* __restrict__ idx, const int* __restrict__ node_of, int n, const int* __restrict__ slot_of, const float4* __restrict__ prim_lo,
+          const float4* __restrict__ prim_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi, unsigned* cnt, unsigned* box) {
+    __shared__ unsigned s_cnt[3 * SAH_BINS];
+    __shared__ unsigned s_box[3 * SAH_BINS * 6];
+    __shared__ int s_node;
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (threadIdx.x == 0) { int p0 = blockIdx.x * blockDim.x; s_node = p0 < n ? node_of[p0] : -1; }
+    for (int k = threadIdx.x; k < 3 * SAH_BINS; k += blockDim.x) s_cnt[k] = 0u;
+    for (int k = threadIdx.x; k < 3 * SAH_BINS * 6; k += blockDim.x) s_box[k] = (k % 6) < 3 ? 0xffffffffu : 0u;
+    __syncthreads();
+    const int first = s_node;
+    const int first_slot = first >= 0 ? slot_of[first] : -1;
+    if (pos < n) {
+        const int nd = node_of[pos];
+        const int slot = nd >= 0 ? slot_of[nd] : -1;
+        if (slot >= 0) {
+            const int prim = idx[pos];
+            const float4 plo = prim_lo[prim], phi = prim_hi[prim], nlo = inner_lo[nd], nhi = inner_hi[nd];
+            const float l[3] = {plo.x, plo.y, plo.z}, h[3] = {phi.x, phi.y, phi.z};
+            const float nl[3] = {nlo.x, nlo.y, nlo.z}, nh[3] = {nhi.x, nhi.y, nhi.z};
+            const bool priv = nd == first;
+#pragma unroll
+            for (int ax = 0; ax < 3; ax++) {
+                const int b = sah_bin(0.5f * (l[ax] + h[ax]), nl[ax], nh[ax]);
+                unsigned* c = priv ? &s_cnt[ax * SAH_BINS + b] : &cnt[((size_t)slot * 3 + ax) * SAH_BINS + b];
+                unsigned* x = priv ? &s_box[(ax * SAH_BINS + b) * 6] : &box[(((size_t)slot * 3 + ax) * SAH_BINS + b) * 6];
+                atomicAdd(c, 1u);
+#pragma unroll
+                for (int k = 0; k < 3; k++) { atomicMin(&x[k], f2ord(l[k])); atomicMax(&x[3 + k], f2ord(h[k])); }
+            }
+        }
+    }
+    __syncthreads();
+    if (first_slot >= 0) {
+        for (int k = threadIdx.x; k < 3 * SAH_BINS; k += blockDim.x) {
+            const unsigned c = s_cnt[k];
+            if (!c) continue;
+            atomicAdd(&cnt[(size_t)first_slot * 3 * SAH_BINS + k], c);
+            unsigned* x = &box[((size_t)first_slot * 3 * SAH_BINS + k) * 6];
+#pragma unroll
+            for (int q = 0; q < 3; q++) { atomicMin(&x[q], s_box[k * 6 + q]); atomicMax(&x[3 + q], s_box[k * 6 + 3 + q]); }
+        }
+    }
+}
+
+__global__ void k_sah_box_init(unsigned* box, size_t count) {
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < count) box[i] = (i % 6) < 3 ? 0xffffffffu : 0u;
+}
+
+// children of node `nd` after a split that puts nl primitives on the left: ids, ranges, boxes, parents; appended to the next lists
+__device__ void sah_make_children(int nd, int begin, int end, int nl, const float llo[3], const float lhi[3], const float rlo[3], const float rhi[3],
+                                  SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf,
+                                  int* subtree, int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, int& left, int& right) {
+    const int cnts[2] = {nl, end - begin - nl}, begins[2] = {begin, begin + nl};
+    int link[2];
+    for (int k = 0; k < 2; k++) {
+        if (cnts[k] == 1) { link[k] = ~begins[k]; parent_leaf[begins[k]] = nd; continue; }
+        const int id = atomicAdd(alloc, 1);
+        link[k] = id;
+        nodes[id].begin = begins[k]; nodes[id].end = begins[k] + cnts[k];
+        const float* lo = k ? rlo : llo; const float* hi = k ? rhi : lhi;
+        inner_lo[id] = make_float4(lo[0], lo[1], lo[2], 0.0f); inner_hi[id] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+        parent_inner[id] = nd; subtree[id] = cnts[k] - 1;
+        if (cnts[k] > SAH_SMALL) { const int s = atomicAdd(&next_lists[0], 1); next_large[s] = id; slot_of[id] = s; }
+        else { const int s = atomicAdd(&next_lists[1], 1); next_small[s] = id; slot_of[id] = -1; }
+    }
+    children[nd] = make_int2(link[0], link[1]);
+    left = link[0]; right = link[1];
+}
+
+__global__ void k_sah_split(const int* __restrict__ large, int n_large, const unsigned* __restrict__ cnt, const unsigned* __restrict__ box,
+                            SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf, int* subtree,
+                            int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, SahSplit* splits, unsigned* part_cnt /* 2 per slot */) {
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_large) return;
+    const int nd = large[slot];
+    const int begin = nodes[nd].begin, end = nodes[nd].end, count = end - begin;
+    float best = 3.4e38f; int baxis = -1, bplane = 0, bnl = 0;
+    float bl[6], br[6];
+    for (int ax = 0; ax < 3; ax++) {
+        const unsigned* c = cnt + ((size_t)slot * 3 + ax) * SAH_BINS;
+        const unsigned* x = box + ((size_t)slot * 3 + ax) * SAH_BINS * 6;
+        // suffix boxes: right side of plane k = bins k .. SAH_BINS-1
+        float rlo[SAH_BINS][3], rhi[SAH_BINS][3]; int rc[SAH_BINS];
+        float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}; int acc = 0;
+        for (int b = SAH_BINS - 1; b >= 1; b--) {
+            if (c[b]) for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], ord2f(x[b * 6 + k])); hi[k] = fmaxf(hi[k], ord2f(x[b * 6 + 3 + k])); }
+            acc += (int)c[b];
+            for (int k = 0; k < 3; k++) { rlo[b][k] = lo[k]; rhi[b][k] = hi[k]; }
+            rc[b] = acc;
+        }
+        float llo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, lhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}; int lc = 0;
+        for (int k = 1; k < SAH_BINS; k++) {                       // plane k: bins < k left
+            const int b = k - 1;
+            if (c[b]) for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], ord2f(x[b * 6 + q])); lhi[q] = fmaxf(lhi[q], ord2f(x[b * 6 + 3 + q])); }
+            lc += (int)c[b];
+            if (lc == 0 || rc[k] == 0) continue;
+            const float cost = half_area(llo, lhi) * (float)lc + half_area(rlo[k], rhi[k]) * (float)rc[k];
+            if (cost < best) {
+                best = cost; baxis = ax; bplane = k; bnl = lc;
+                for (int q = 0; q < 3; q++) { bl[q] = llo[q]; bl[3 + q] = lhi[q]; br[q] = rlo[k][q]; br[3 + q] = rhi[k][q]; }
+            }
+        }
+    }
+    if (baxis < 0) {
+        // every centroid in one bin on all three axes: halve by position; children keep the parent's box (conservative)
+        bnl = count / 2;
+        const float4 a = inner_lo[nd], b = inner_hi[nd];
+        bl[0] = br[0] = a.x; bl[1] = br[1] = a.y; bl[2] = br[2] = a.z; bl[3] = br[3] = b.x; bl[4] = br[4] = b.y; bl[5] = br[5] = b.z;
+    }
+    SahSplit sp; sp.axis = baxis; sp.plane = bplane; sp.nl = bnl;
+    sah_make_children(nd, begin, end, bnl, bl, bl + 3, br, br + 3, nodes, inner_lo, inner_hi, children, parent_inner, parent_leaf, subtree, slot_of,
+                      next_lists, next_large, next_small, alloc, sp.left, sp.right);
+    splits[slot] = sp;
+    part_cnt[2 * slot] = 0u; part_cnt[2 * slot + 1] = 0u;
+}
+
+// primitives of large nodes move to their side in the other buffer; everything else is copied through
+__global__ void __launch_bounds__(BVH_THREADS)
+k_sah_partition(const int* __restrict__ idx, const int* __restrict__ node_of, int n, const int* __restrict__ slot_of_level /* slots as of THIS level */,
+                const SahNode* __restrict__ nodes_level /* ranges as of this level (begin/end of the node being split) */, const SahSplit* __restrict__ splits,
+                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi,
+                unsigned* part_cnt, int* idx_out, int* node_out) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= n) return;
+    const int nd = node_of[pos];
+    const int slot = nd >= 0 ? slot_of_level[nd] : -1;
+    const int prim = idx[pos];
+    if (slot < 0) { if (nd < 0) { idx_out[pos] = prim; node_out[pos] = nd; } return; }   // small nodes are rewritten by k_sah_small
+    const SahSplit sp = splits[slot];
+    const int begin = nodes_level[nd].begin;
+    bool left;
+    if (sp.axis < 0) left = pos - begin < sp.nl;
+    else {
+        const float4 plo = prim_lo[prim], phi = prim_hi[prim], nlo = inner_lo[nd], nhi = inner_hi[nd];
+        const float c = sp.axis == 0 ? 0.5f * (plo.x + phi.x) : sp.axis == 1 ? 0.5f * (plo.y + phi.y) : 0.5f * (plo.z + phi.z);
+        const float lo = sp.axis == 0 ? nlo.x : sp.axis == 1 ? nlo.y : nlo.z, hi = sp.axis == 0 ? nhi.x : sp.axis == 1 ? nhi.y : nhi.z;
+        left = sah_bin(c, lo, hi) < sp.plane;
+    }
+    // one atomic per (node, side) group of the warp
+    const unsigned key = ((unsigned)slot << 1) | (left ? 0u : 1u);
+    const unsigned peers = __match_any_sync(__activemask(), key);
+    const int leader = __ffs(peers) - 1, lane = threadIdx.x & 31;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(&part_cnt[key], (unsigned)__popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    const int at = begin + (left ? 0 : sp.nl) + (int)base + __popc(peers & ((1u << lane) - 1u));
+    idx_out[at] = prim;
+    const int child = left ? sp.left : sp.right;
+    node_out[at] = child >= 0 ? child : -1;
+}
+
+// one thread finishes the whole subtree of a node with <= SAH_SMALL primitives: exact SAH over every centroid plane of every axis
+__global__ void k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ idx, const SahNode* __restrict__ nodes_in,
+                            const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, float4* inner_lo, float4* inner_hi, int2* children,
+                            int* parent_inner, int* parent_leaf, int* subtree, int* alloc, int* idx_out, int* node_out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_small) return;
+    const int root = small[t];
+    const int rb = nodes_in[root].begin, cnt0 = nodes_in[root].end - rb;
+    int ids[SAH_SMALL]; float lo[SAH_SMALL][3], hi[SAH_SMALL][3], ce[SAH_SMALL][3];
+    for (int k = 0; k < cnt0; k++) {
+        ids[k] = idx[rb + k];
+        const float4 a = prim_lo[ids[k]], b = prim_hi[ids[k]];
+        lo[k][0] = a.x; lo[k][1] = a.y; lo[k][2] = a.z; hi[k][0] = b.x; hi[k][1] = b.y; hi[k][2] = b.z;
+        for (int q = 0; q < 3; q++) ce[k][q] = 0.5f * (lo[k][q] + hi[k][q]);
+    }
+    int next_id = cnt0 > 2 ? atomicAdd(alloc, cnt0 - 2) : 0;     // the subtree has cnt0 - 1 inner nodes; `root` is one of them
+    // explicit stack of (node id, first, count) over the local arrays
+    int st_node[SAH_SMALL], st_first[SAH_SMALL], st_cnt[SAH_SMALL], sp = 0;
+    st_node[0] = root; st_first[0] = 0; st_cnt[0] = cnt0; sp = 1;
+    while (sp > 0) {
+        sp--;
+        const int nd = st_node[sp], f = st_first[sp], c = st_cnt[sp];
+        float best = 3.4e38f; int baxis = -1, bj = 0;
+        for (int ax = 0; ax < 3; ax++)
+            for (int j = f; j < f + c; j++) {
+                // plane at primitive j's centroid: left = centroids below it (ties by slot), j itself goes right
+                float llo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, lhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}, rlo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, rhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+                int nl = 0;
+                for (int i = f; i < f + c; i++) {
+                    const bool left = ce[i][ax] < ce[j][ax] || (ce[i][ax] == ce[j][ax] && i < j);
+                    if (left) { nl++; for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], lo[i][q]); lhi[q] = fmaxf(lhi[q], hi[i][q]); } }
+                    else for (int q = 0; q < 3; q++) { rlo[q] = fminf(rlo[q], lo[i][q]); rhi[q] = fmaxf(rhi[q], hi[i][q]); }
+                }
+                if (nl == 0) continue;
+                const float cost = half_area(llo, lhi) * (float)nl + half_area(rlo, rhi) * (float)(c - nl);
+                if (cost < best) { best = cost; baxis = ax; bj = j; }
+            }
+        // stable partition of [f, f + c) about the chosen plane (there always is one: the smallest centroid of an axis has nl = 0,
+        // every other primitive has nl >= 1, and c >= 2)
+        int tid[SAH_SMALL]; float tlo[SAH_SMALL][3], thi[SAH_SMALL][3], tce[SAH_SMALL][3]; int nl = 0, nr = 0;
+        if (baxis < 0) { baxis = 0; bj = f + c / 2; }            // unreachable for c >= 2 unless NaN boxes: halve
+        const float pivot = ce[bj][baxis];
+        bool side[SAH_SMALL];
+        for (int i = f; i < f + c; i++) { side[i - f] = best < 3.4e38f ? (ce[i][baxis] < pivot || (ce[i][baxis] == pivot && i < bj)) : (i - f < c / 2); nl += side[i - f] ? 1 : 0; }
+        int wl = 0, wr = nl;
+        for (int i = f; i < f + c; i++) {
+            const int w = side[i - f] ? wl++ : wr++;
+            tid[w] = ids[i];
+            for (int q = 0; q < 3; q++) { tlo[w][q] = lo[i][q]; thi[w][q] = hi[i][q]; tce[w][q] = ce[i][q]; }
+        }
+        nr = c - nl;
+        for (int w = 0; w < c; w++) { ids[f + w] = tid[w]; for (int q = 0; q < 3; q++) { lo[f + w][q] = tlo[w][q]; hi[f + w][q] = thi[w][q]; ce[f + w][q] = tce[w][q]; } }
+        int link[2];
+        const int firsts[2] = {f, f + nl}, cnts[2] = {nl, nr};
+        for (int k = 0; k < 2; k++) {
+            if (cnts[k] == 1) { link[k] = ~(rb + firsts[k]); parent_leaf[rb + firsts[k]] = nd; continue; }
+            const int id = next_id++;
+            link[k] = id;
+            float blo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, bhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+            for (int i = firsts[k]; i < firsts[k] + cnts[k]; i++) for (int q = 0; q < 3; q++) { blo[q] = fminf(blo[q], lo[i][q]); bhi[q] = fmaxf(bhi[q], hi[i][q]); }
+            inner_lo[id] = make_float4(blo[0], blo[1], blo[2], 0.0f); inner_hi[id] = make_float4(bhi[0], bhi[1], bhi[2], 0.0f);
+            parent_inner[id] = nd; subtree[id] = cnts[k] - 1;
+            st_node[sp] = id; st_first[sp] = firsts[k]; st_cnt[sp] = cnts[k]; sp++;
+        }
+        children[nd] = make_int2(link[0], link[1]);
+    }
+    for (int k = 0; k < cnt0; k++) { idx_out[rb + k] = ids[k]; node_out[rb + k] = -1; }
+}
+__global__ void k_sah_leaves(const int* __restrict__ idx, int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, int* vals,
+                             float4* leaf_lo, float4* leaf_hi) {
+    int l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n) return;
+    const int prim = idx[l];
+    vals[l] = prim; leaf_lo[l] = prim_lo[prim]; leaf_hi[l] = prim_hi[prim];
+}
+
+// ---------------------------------------------------------------- triangle pre-splitting (spatial splits for the device builders)
+// FindBestSpatialSplit (BVH.cpp:1793-1984) lets the reference cut a triangle that straddles a good split plane; Morton /
+// PLOC builders cluster whole triangles, so a wall quad that spans the room drags a room-sized box into every subtree it
+// lands in. Here long triangles are cut BEFORE the sort (Karras & Aila 2013, simplified): a triangle whose box is longer than
+// 1.5 cells of a grid^3 grid over the scene box along some axis is cut into ceil(extent / cell) slabs along that axis (at
+// most PRESPLIT_MAX_PIECES boxes per triangle), the triangle is clipped to every piece and empty pieces are dropped. Pieces
+// are work items of their own (one thread per piece, owner found by binary search in the scanned piece counts), so the two
+// ground triangles of a scene that need 4096 pieces each cost what 8192 small triangles cost.
+#define PRESPLIT_MAX_PIECES 4096
+#define SCAN_TILE 2048           // elements per block of the 3-kernel scan (256 threads x 8)
+
+__global__ void k_tri_scene_box(const float4* __restrict__ tris, int n, unsigned* bounds) {
+    __shared__ unsigned s[6];
+    if (threadIdx.x < 3) s[threadIdx.x] = 0xffffffffu; else if (threadIdx.x < 6) s[threadIdx.x] = 0u;
+    __syncthreads();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        float lo[3], hi[3];
+        tri_box(tris + 5 * (size_t)i, lo, hi);
+#pragma unroll
+        for (int k = 0; k < 3; k++) { atomicMin(&s[k], f2ord(lo[k])); atomicMax(&s[3 + k], f2ord(hi[k])); }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) atomicMin(&bounds[threadIdx.x], s[threadIdx.x]);
+    else if (threadIdx.x < 6) atomicMax(&bounds[threadIdx.x], s[threadIdx.x]);
+}
+
+// pieces per axis of triangle i, packed 12 bits each (<= 4096 in total)
+__device__ __forceinline__ unsigned presplit_plan(const float lo[3], const float hi[3], float cell) {
+    int nk[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        float e = hi[k] - lo[k];
+        nk[k] = e > 1.5f * cell ? (int)fminf(ceilf(e / cell), 4095.0f) : 1;
+    }
+    while ((long long)nk[0] * nk[1] * nk[2] > PRESPLIT_MAX_PIECES) {          // coarsen the axis with the most pieces
+        int k = nk[0] >= nk[1] ? (nk[0] >= nk[2] ? 0 : 2) : (nk[1] >= nk[2] ? 1 : 2);
+        nk[k] = (nk[k] + 1) / 2;
+    }
+    return (unsigned)nk[0] | ((unsigned)nk[1] << 12) | ((unsigned)nk[2] << 24);
+}
+__global__ void k_presplit_count(const float4* __restrict__ tris, int n, const unsigned* __restrict__ bounds, int grid, unsigned* pieces /* n + 1 */) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n) return;
+    if (i == n) { pieces[n] = 0u; return; }
+    float ext = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; k++) ext = fmaxf(ext, ord2f(bounds[3 + k]) - ord2f(bounds[k]));
+    float lo[3], hi[3];
+    tri_box(tris + 5 * (size_t)i, lo, hi);
+    unsigned plan = presplit_plan(lo, hi, ext / (float)grid);
+    pieces[i] = (plan & 4095u) * ((plan >> 12) & 4095u) * (plan >> 24);
+}
+
+// ---- exclusive scan of `count` unsigned values in place: tile sums, scan of the tile sums (one block), tile-local scan + base
+__global__ void __launch_bounds__(BVH_THREADS) k_scan_tile_sums(const unsigned* __restrict__ data, int count, int* sums) {
+    __shared__ unsigned w[BVH_THREADS / 32];
+    const int base = blockIdx.x * SCAN_TILE + threadIdx.x * 8;
+    unsigned t = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) if (base + k < count) t += data[base + k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    if ((threadIdx.x & 31) == 0) w[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) { unsigned z = 0; for (int k = 0; k < BVH_THREADS / 32; k++) z += w[k]; sums[blockIdx.x] = (int)z; }
+}
+__global__ void __launch_bounds__(BVH_THREADS) k_scan_apply(unsigned* data, int count, const int* __restrict__ tile_base) {
+    __shared__ unsigned w[BVH_THREADS / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int base = blockIdx.x * SCAN_TILE + threadIdx.x * 8;
+    unsigned v[8], t = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { v[k] = base + k < count ? data[base + k] : 0u; t += v[k]; }
+    unsigned x = t;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) w[warp] = x;
+    __syncthreads();
+    unsigned run = (unsigned)tile_base[blockIdx.x] + (x - t);
+    for (int k = 0; k < warp; k++) run += w[k];
+#pragma unroll
+    for (int k = 0; k < 8; k++) { if (base + k < count) data[base + k] = run; run += v[k]; }
+}
+
+// clip polygon `in` (n vertices) against the half space x[axis] >= value (keep_greater) or <= value
+__device__ int clip_halfspace(const float (*in)[3], int n, int axis, float value, bool keep_greater, float (*out)[3]) {
+    int m = 0;
+    for (int i = 0; i < n; i++) {
+        const float* a = in[i]; const float* b = in[(i + 1) % n];
+        const bool ia = keep_greater ? a[axis] >= value : a[axis] <= value;
+        const bool ib = keep_greater ? b[axis] >= value : b[axis] <= value;
+        if (ia) { out[m][0] = a[0]; out[m][1] = a[1]; out[m][2] = a[2]; m++; }
+        if (ia != ib) {
+            const float t = (value - a[axis]) / (b[axis] - a[axis]);
+            out[m][0] = a[0] + t * (b[0] - a[0]); out[m][1] = a[1] + t * (b[1] - a[1]); out[m][2] = a[2] + t * (b[2] - a[2]);
+            out[m][axis] = value;
+            m++;
+        }
+    }
+    return m;
+}
+
+// one thread per piece: owner triangle by binary search in the scanned piece counts, the piece's box, the clipped triangle's box
+__global__ void k_presplit_pieces(const float4* __restrict__ tris, int n, const unsigned* __restrict__ bounds, int grid,
+                                  const unsigned* __restrict__ offsets /* n + 1, scanned */, unsigned total, int* p_tri, float4* p_lo,
+                                  float4* p_hi, unsigned* p_valid /* total + 1 */) {
+    unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p > total) return;
+    if (p == total) { p_valid[total] = 0u; return; }
+    int a = 0, b = n;                                          // last i with offsets[i] <= p
+    while (b - a > 1) { int mid = (a + b) >> 1; if (offsets[mid] <= p) a = mid; else b = mid; }
+    const int i = a;
+    const unsigned j = p - offsets[i];
+    float ext = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; k++) ext = fmaxf(ext, ord2f(bounds[3 + k]) - ord2f(bounds[k]));
+    float lo[3], hi[3];
+    const float4* t = tris + 5 * (size_t)i;
+    tri_box(t, lo, hi);
+    const unsigned plan = presplit_plan(lo, hi, ext / (float)grid);
+    const unsigned nk[3] = {plan & 4095u, (plan >> 12) & 4095u, plan >> 24};
+    p_tri[p] = i;
+    if (nk[0] * nk[1] * nk[2] == 1u) {
+        p_lo[p] = make_float4(lo[0], lo[1], lo[2], 0.0f); p_hi[p] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+        p_valid[p] = 1u;
+        return;
+    }
+    const unsigned ix[3] = {j % nk[0], (j / nk[0]) % nk[1], j / (nk[0] * nk[1])};
+    float clo[3], chi[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {                              // piece ix of nk equal slabs of the triangle's own box; end planes exact
+        const float e = hi[k] - lo[k];
+        clo[k] = ix[k] == 0 ? lo[k] : lo[k] + e * ((float)ix[k] / (float)nk[k]);
+        chi[k] = ix[k] + 1 == nk[k] ? hi[k] : lo[k] + e * ((float)(ix[k] + 1) / (float)nk[k]);
+    }
+    float4 r0 = t[0], r1 = t[1], r2 = t[2];
+    float A[10][3], B[10][3];
+    A[0][0] = r0.x; A[0][1] = r0.y; A[0][2] = r0.z;
+    A[1][0] = r0.x + r0.w; A[1][1] = r0.y + r1.x; A[1][2] = r0.z + r1.y;
+    A[2][0] = r0.x + r1.z; A[2][1] = r0.y + r1.w; A[2][2] = r0.z + r2.x;
+    int m = 3;
+    for (int k = 0; k < 3 && m > 0; k++) {
+        if (nk[k] == 1u) continue;                             // the triangle lies inside its own box along this axis
+        m = clip_halfspace(A, m, k, clo[k], true, B);
+        m = m > 0 ? clip_halfspace(B, m, k, chi[k], false, A) : 0;
+    }
+    if (m < 3) { p_valid[p] = 0u; p_lo[p] = make_float4(0, 0, 0, 0); p_hi[p] = make_float4(0, 0, 0, 0); return; }
+    float blo[3] = {A[0][0], A[0][1], A[0][2]}, bhi[3] = {A[0][0], A[0][1], A[0][2]};
+    for (int q = 1; q < m; q++)
+#pragma unroll
+        for (int k = 0; k < 3; k++) { blo[k] = fminf(blo[k], A[q][k]); bhi[k] = fmaxf(bhi[k], A[q][k]); }
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        // interpolated vertices carry rounding error in the two coordinates that were not cut: widen by a few ulps of the
+        // coordinates involved, then never beyond the piece or the triangle's own box
+        const float pad = 4.0f * 1.1920929e-7f * fmaxf(fabsf(lo[k]), fabsf(hi[k]));
+        blo[k] = fmaxf(fmaxf(blo[k] - pad, clo[k]), lo[k]);
+        bhi[k] = fminf(fminf(bhi[k] + pad, chi[k]), hi[k]);
+    }
+    p_lo[p] = make_float4(blo[0], blo[1], blo[2], 0.0f); p_hi[p] = make_float4(bhi[0], bhi[1], bhi[2], 0.0f);
+    p_valid[p] = 1u;
+}
+__global__ void k_presplit_compact(const int* __restrict__ p_tri, const float4* __restrict__ p_lo, const float4* __restrict__ p_hi,
+                                   const unsigned* __restrict__ offsets /* scanned validity, total + 1 */, unsigned total, int* r_tri,
+                                   float4* r_lo, float4* r_hi) {
+    unsigned p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= total) return;
+    const unsigned at = offsets[p];
+    if (offsets[p + 1] == at) return;                          // dropped piece
+    r_tri[at] = p_tri[p]; r_lo[at] = p_lo[p]; r_hi[at] = p_hi[p];
+}
+
 // ---------------------------------------------------------------- driver
 #define BCK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { err = e__; goto done; } } while (0)
+
+void free_refset(RefSet* r) {
+    if (!r) return;
+    cudaFree(r->tri); cudaFree(r->lo); cudaFree(r->hi);
+    r->tri = nullptr; r->lo = r->hi = nullptr; r->m = 0;
+}
+
+// See pt_kernels.h. Two 4-byte read-backs (piece count, reference count) size the arrays.
+int presplit_device(const float4* d_tris, int n, int grid, RefSet* out, cudaStream_t st, float* kernel_ms) {
+    cudaError_t err = cudaSuccess;
+    int launches = 0;
+    unsigned *bounds = nullptr, *pieces = nullptr, *valid = nullptr;
+    int *tile_sums = nullptr, *d_total = nullptr, *p_tri = nullptr;
+    float4 *p_lo = nullptr, *p_hi = nullptr;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    const unsigned init_bounds[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    int total = 0, m = 0;
+    *out = RefSet();
+    auto scan = [&](unsigned* data, int count) {
+        const int nb = (count + SCAN_TILE - 1) / SCAN_TILE;
+        k_scan_tile_sums<<<nb, BVH_THREADS, 0, st>>>(data, count, tile_sums);
+        k_ploc_scan<<<1, 1024, 0, st>>>(tile_sums, nb, d_total);
+        k_scan_apply<<<nb, BVH_THREADS, 0, st>>>(data, count, tile_sums);
+        launches += 3;
+    };
+    BCK(cudaEventCreate(&e0)); BCK(cudaEventCreate(&e1));
+    BCK(cudaMalloc((void**)&bounds, sizeof(init_bounds)));
+    BCK(cudaMalloc((void**)&pieces, ((size_t)n + 1) * 4));
+    BCK(cudaMalloc((void**)&d_total, 4));
+    BCK(cudaMemcpyAsync(bounds, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice, st));
+    BCK(cudaEventRecord(e0, st));
+    k_tri_scene_box<<<min((n + BVH_THREADS - 1) / BVH_THREADS, 148 * 8), BVH_THREADS, 0, st>>>(d_tris, n, bounds); launches++;
+    k_presplit_count<<<(n + 1 + BVH_THREADS - 1) / BVH_THREADS, BVH_THREADS, 0, st>>>(d_tris, n, bounds, grid, pieces); launches++;
+    BCK(cudaMalloc((void**)&tile_sums, ((size_t)(n + 1) * 2 / SCAN_TILE + 64) * 4));      // pieces <= ~2 n in practice; checked below
+    scan(pieces, n + 1);
+    BCK(cudaMemcpyAsync(&total, d_total, 4, cudaMemcpyDeviceToHost, st));
+    BCK(cudaStreamSynchronize(st));
+    if (total < n || (long long)total > 2ll * n + (1 << 20)) { err = cudaErrorInvalidValue; goto done; }   // more than doubling the scene: refuse
+    BCK(cudaMalloc((void**)&p_tri, (size_t)total * 4)); BCK(cudaMalloc((void**)&p_lo, (size_t)total * 16)); BCK(cudaMalloc((void**)&p_hi, (size_t)total * 16));
+    BCK(cudaMalloc((void**)&valid, ((size_t)total + 1) * 4));
+    cudaFree(tile_sums); tile_sums = nullptr;
+    BCK(cudaMalloc((void**)&tile_sums, ((size_t)(total + 1) / SCAN_TILE + 64) * 4));
+    k_presplit_pieces<<<(total + 1 + BVH_THREADS - 1) / BVH_THREADS, BVH_THREADS, 0, st>>>(d_tris, n, bounds, grid, pieces, (unsigned)total, p_tri, p_lo, p_hi, valid); launches++;
+    scan(valid, total + 1);
+    BCK(cudaMemcpyAsync(&m, d_total, 4, cudaMemcpyDeviceToHost, st));
+    BCK(cudaStreamSynchronize(st));
+    if (m < 1 || m > total) { err = cudaErrorUnknown; goto done; }
+    BCK(cudaMalloc((void**)&out->tri, (size_t)m * 4)); BCK(cudaMalloc((void**)&out->lo, (size_t)m * 16)); BCK(cudaMalloc((void**)&out->hi, (size_t)m * 16));
+    k_presplit_compact<<<(total + BVH_THREADS - 1) / BVH_THREADS, BVH_THREADS, 0, st>>>(p_tri, p_lo, p_hi, valid, (unsigned)total, out->tri, out->lo, out->hi); launches++;
+    out->m = m;
+    BCK(cudaEventRecord(e1, st));
+    BCK(cudaGetLastError());
+    BCK(cudaStreamSynchronize(st));
+    if (kernel_ms) BCK(cudaEventElapsedTime(kernel_ms, e0, e1));
+done:
+    cudaFree(bounds); cudaFree(pieces); cudaFree(valid); cudaFree(tile_sums); cudaFree(d_total); cudaFree(p_tri); cudaFree(p_lo); cudaFree(p_hi);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    if (err != cudaSuccess) free_refset(out);
+    return err == cudaSuccess ? launches : -(int)err;
+}
 
 // d_tris: n x 5 float4 (device). d_nodes: 2 * (2n - 1) float4, d_refs: n ints (device, caller-owned). d_pairs (n - 1) /
 // d_leaf (n): optional, the traversal layout of pt_layout.h written directly. *depth: depth of the tree.
 // Returns the number of kernels launched (> 0) or -(cudaError) on failure; *kernel_ms = device time of the build.
 // ploc_radius > 0: the hierarchy is built by PLOC with that search radius instead of Karras' Morton-bit splits.
 int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
-                      cudaStream_t st, float* kernel_ms, int ploc_radius) {
+                      cudaStream_t st, float* kernel_ms, int ploc_radius, const RefSet* refset) {
     cudaError_t err = cudaSuccess;
     int launches = 0;
+    // with a reference set the leaves are its m references (n becomes m below); d_nodes / d_refs / d_pairs / d_leaf are sized by m
+    LeafSrc src{d_tris, refset ? refset->tri : nullptr, refset ? refset->lo : nullptr, refset ? refset->hi : nullptr};
+    if (refset) n = refset->m;
     const int n_blocks = (n + SORT_TILE - 1) / SORT_TILE;
     const int grid_n = (n + BVH_THREADS - 1) / BVH_THREADS;
     unsigned *bounds = nullptr, *keys[2] = {nullptr, nullptr}, *hist = nullptr, *flags = nullptr;
@@ -440,6 +971,11 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
     float4 *leaf_lo = nullptr, *leaf_hi = nullptr, *inner_lo = nullptr, *inner_hi = nullptr;
     int *cid[2] = {nullptr, nullptr}, *nn = nullptr, *valid = nullptr, *block_counts = nullptr, *d_m = nullptr, *subtree = nullptr, *remap = nullptr;
     float4 *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
+    float4 *sah_prim_lo = nullptr, *sah_prim_hi = nullptr;
+    int *sah_idx[2] = {nullptr, nullptr}, *sah_node_of[2] = {nullptr, nullptr}, *sah_slot_of = nullptr, *sah_large[2] = {nullptr, nullptr}, *sah_small[2] = {nullptr, nullptr};
+    int *sah_lists = nullptr, *sah_alloc = nullptr;
+    unsigned *sah_cnt = nullptr, *sah_box = nullptr, *sah_part = nullptr;
+    SahNode* sah_nodes = nullptr; SahSplit* sah_splits = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     const unsigned init_bounds[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     BCK(cudaEventCreate(&e0)); BCK(cudaEventCreate(&e1));
@@ -466,8 +1002,54 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
         BCK(cudaMemsetAsync(d_m, 0, 8, st));                     // [0] = cluster count of the round, [1] = inner nodes created
     }
     BCK(cudaEventRecord(e0, st));
-    k_scene_bounds<<<min(grid_n, 148 * 8), BVH_THREADS, 0, st>>>(d_tris, n, bounds); launches++;
-    k_morton<<<grid_n, BVH_THREADS, 0, st>>>(d_tris, n, bounds, keys[0], vals[0]); launches++;
+    if (ploc_radius < 0) {
+        // ---- top-down binned SAH (kernels above). Level loop on the host: one 8-byte read-back per level sizes the launches.
+        const int max_slots = n / (SAH_SMALL + 1) + 2;
+        BCK(cudaMalloc((void**)&sah_prim_lo, (size_t)n * 16)); BCK(cudaMalloc((void**)&sah_prim_hi, (size_t)n * 16));
+        for (int k = 0; k < 2; k++) { BCK(cudaMalloc((void**)&sah_idx[k], (size_t)n * 4)); BCK(cudaMalloc((void**)&sah_node_of[k], (size_t)n * 4)); }
+        BCK(cudaMalloc((void**)&sah_nodes, (size_t)n * sizeof(SahNode))); BCK(cudaMalloc((void**)&sah_slot_of, (size_t)n * 4));
+        BCK(cudaMalloc((void**)&subtree, (size_t)n * 4)); BCK(cudaMalloc((void**)&remap, (size_t)n * 4));
+        for (int k = 0; k < 2; k++) { BCK(cudaMalloc((void**)&sah_large[k], (size_t)max_slots * 4)); BCK(cudaMalloc((void**)&sah_small[k], (size_t)(n / 2 + 2) * 4)); }
+        BCK(cudaMalloc((void**)&sah_lists, 4 * 4)); BCK(cudaMalloc((void**)&sah_alloc, 4));
+        BCK(cudaMalloc((void**)&sah_cnt, (size_t)max_slots * 3 * SAH_BINS * 4)); BCK(cudaMalloc((void**)&sah_box, (size_t)max_slots * 3 * SAH_BINS * 6 * 4));
+        BCK(cudaMalloc((void**)&sah_splits, (size_t)max_slots * sizeof(SahSplit))); BCK(cudaMalloc((void**)&sah_part, (size_t)max_slots * 2 * 4));
+        const int one = 1;
+        BCK(cudaMemcpyAsync(sah_alloc, &one, 4, cudaMemcpyHostToDevice, st));             // inner id 0 is the root
+        k_sah_init<<<min(grid_n, 148 * 8), BVH_THREADS, 0, st>>>(src, n, sah_prim_lo, sah_prim_hi, sah_idx[0], sah_node_of[0], bounds); launches++;
+        k_sah_root<<<1, 1, 0, st>>>(bounds, n, sah_nodes, inner_lo, inner_hi, parent_inner, subtree, sah_slot_of, sah_lists, sah_large[0], sah_small[0]); launches++;
+        int cur = 0, lvl = 0;
+        for (;; lvl++) {
+            int counts[2] = {0, 0};
+            BCK(cudaMemcpyAsync(counts, sah_lists + 2 * (lvl & 1), 8, cudaMemcpyDeviceToHost, st));
+            BCK(cudaStreamSynchronize(st));
+            if (counts[0] == 0 && counts[1] == 0) break;
+            if (counts[0] > max_slots || counts[1] > n / 2 + 2 || lvl > 4 * PT_MAX_TREE_DEPTH) { err = cudaErrorUnknown; goto done; }
+            int* next_lists = sah_lists + 2 * ((lvl + 1) & 1);
+            BCK(cudaMemsetAsync(next_lists, 0, 8, st));
+            const int lv = lvl & 1, nx = lv ^ 1;
+            if (counts[0] > 0) {
+                const size_t bins = (size_t)counts[0] * 3 * SAH_BINS;
+                BCK(cudaMemsetAsync(sah_cnt, 0, bins * 4, st));
+                k_sah_box_init<<<(unsigned)((bins * 6 + BVH_THREADS - 1) / BVH_THREADS), BVH_THREADS, 0, st>>>(sah_box, bins * 6); launches++;
+                k_sah_bin<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_prim_lo, sah_prim_hi, inner_lo, inner_hi, sah_cnt, sah_box); launches++;
+                k_sah_split<<<(counts[0] + 127) / 128, 128, 0, st>>>(sah_large[lv], counts[0], sah_cnt, sah_box, sah_nodes, inner_lo, inner_hi, children, parent_inner,
+                                                                      parent_leaf, subtree, sah_slot_of, next_lists, sah_large[nx], sah_small[nx], sah_alloc, sah_splits, sah_part); launches++;
+            }
+            // copy-through + partition of the large nodes, then the small subtrees (disjoint positions of the other buffer)
+            k_sah_partition<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_nodes, sah_splits, sah_prim_lo, sah_prim_hi, inner_lo,
+                                                            inner_hi, sah_part, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
+            if (counts[1] > 0) {
+                k_sah_small<<<(counts[1] + 63) / 64, 64, 0, st>>>(sah_small[lv], counts[1], sah_idx[cur], sah_nodes, sah_prim_lo, sah_prim_hi, inner_lo, inner_hi, children,
+                                                                  parent_inner, parent_leaf, subtree, sah_alloc, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
+            }
+            cur ^= 1;
+        }
+        k_sah_leaves<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], n, sah_prim_lo, sah_prim_hi, vals[0], leaf_lo, leaf_hi); launches++;
+        k_ploc_relabel<<<grid_n, BVH_THREADS, 0, st>>>(children, parent_inner, subtree, n - 1, remap); launches++;
+        goto emit;
+    }
+    k_scene_bounds<<<min(grid_n, 148 * 8), BVH_THREADS, 0, st>>>(src, n, bounds); launches++;
+    k_morton<<<grid_n, BVH_THREADS, 0, st>>>(src, n, bounds, keys[0], vals[0]); launches++;
     for (int pass = 0; pass < 4; pass++) {
         const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
         k_sort_hist<<<n_blocks, BVH_THREADS, 0, st>>>(keys[src], n, shift, hist, n_blocks); launches++;
@@ -476,7 +1058,7 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
     }
     // 4 passes: the sorted arrays are back in buffer 0
     if (ploc_radius > 0) {
-        k_ploc_leaves<<<grid_n, BVH_THREADS, 0, st>>>(d_tris, vals[0], n, leaf_lo, leaf_hi, cid[0], clo[0], chi[0]); launches++;
+        k_ploc_leaves<<<grid_n, BVH_THREADS, 0, st>>>(src, vals[0], n, leaf_lo, leaf_hi, cid[0], clo[0], chi[0]); launches++;
         int m = n, cur = 0;
         while (m > 1) {
             const int nb = (m + BVH_THREADS - 1) / BVH_THREADS;
@@ -495,9 +1077,10 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
         k_ploc_relabel<<<grid_n, BVH_THREADS, 0, st>>>(children, parent_inner, subtree, n - 1, remap); launches++;
     } else {
         k_hierarchy<<<grid_n, BVH_THREADS, 0, st>>>(keys[0], n, children, parent_inner, parent_leaf); launches++;
-        k_fit<<<grid_n, BVH_THREADS, 0, st>>>(d_tris, vals[0], n, children, parent_inner, parent_leaf, leaf_lo, leaf_hi, inner_lo, inner_hi, flags); launches++;
+        k_fit<<<grid_n, BVH_THREADS, 0, st>>>(src, vals[0], n, children, parent_inner, parent_leaf, leaf_lo, leaf_hi, inner_lo, inner_hi, flags); launches++;
     }
-    k_emit<<<grid_n, BVH_THREADS, 0, st>>>(vals[0], n, children, leaf_lo, leaf_hi, inner_lo, inner_hi, d_nodes, d_refs, d_tris, d_pairs, d_leaf, ploc_radius > 0 ? remap : nullptr); launches++;
+emit:
+    k_emit<<<grid_n, BVH_THREADS, 0, st>>>(vals[0], n, children, leaf_lo, leaf_hi, inner_lo, inner_hi, d_nodes, d_refs, d_tris, d_pairs, d_leaf, ploc_radius != 0 ? remap : nullptr, src.ref_tri); launches++;
     k_depth<<<grid_n, BVH_THREADS, 0, st>>>(parent_inner, parent_leaf, n, d_depth); launches++;
     BCK(cudaEventRecord(e1, st));
     if (depth) BCK(cudaMemcpyAsync(depth, d_depth, 4, cudaMemcpyDeviceToHost, st));
@@ -510,6 +1093,9 @@ done:
     cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(inner_lo); cudaFree(inner_hi);
     for (int k = 0; k < 2; k++) { cudaFree(cid[k]); cudaFree(clo[k]); cudaFree(chi[k]); }
     cudaFree(nn); cudaFree(valid); cudaFree(block_counts); cudaFree(d_m); cudaFree(subtree); cudaFree(remap);
+    cudaFree(sah_prim_lo); cudaFree(sah_prim_hi); cudaFree(sah_slot_of); cudaFree(sah_lists); cudaFree(sah_alloc); cudaFree(sah_cnt); cudaFree(sah_box);
+    cudaFree(sah_part); cudaFree(sah_nodes); cudaFree(sah_splits);
+    for (int k = 0; k < 2; k++) { cudaFree(sah_idx[k]); cudaFree(sah_node_of[k]); cudaFree(sah_large[k]); cudaFree(sah_small[k]); }
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
     return err == cudaSuccess ? launches : -(int)err;

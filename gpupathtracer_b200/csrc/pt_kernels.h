@@ -56,8 +56,15 @@ struct SliceStreams { cudaStream_t a, b; cudaEvent_t ev_shade, ev_shadow; };
 int enqueue_frame_dag(const FrameParams& p, const LaunchDims& dims, const SliceStreams& ss, bool wait_prev);
 
 // pt_bvh_gpu.cu: LBVH on the device, output in the reference's serialised form
+// A reference = a triangle restricted to a box (the unit of spatial splits). presplit_device cuts every triangle whose box is
+// long against the scene (more than 1.5 cells of a `grid`^3 grid over the scene box) into pieces along a regular subdivision of
+// its OWN box, clips the triangle to each piece (Sutherland-Hodgman) and keeps the non-empty ones; all other triangles become
+// one reference each. Arrays are device memory owned by the caller afterwards (free_refset).
+struct RefSet { int m = 0; int* tri = nullptr; float4* lo = nullptr; float4* hi = nullptr; };
+int presplit_device(const float4* d_tris, int n, int grid, RefSet* out, cudaStream_t st, float* kernel_ms);   // launches, or -(cudaError)
+void free_refset(RefSet* r);
 int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
-                      cudaStream_t st, float* kernel_ms, int ploc_radius = 0);
+                      cudaStream_t st, float* kernel_ms, int ploc_radius = 0, const RefSet* refset = nullptr);
 
 int launch_primary(const FrameParams& p, const LaunchDims& dims, float4* by_pixel, cudaStream_t st);
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);

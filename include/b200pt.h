@@ -171,6 +171,19 @@ int pt_build_bvh_device(pt_context* ctx, pt_bvh_stats* stats);
  * not bound the depth: when the tree comes out deeper than the traversal stack (96 entries) the Morton hierarchy is
  * used instead, PT_OK is returned and pt_last_error() carries a note (10 M-triangle nested shells came out 64-66 deep). */
 int pt_build_bvh_device_ploc(pt_context* ctx, int32_t radius, pt_bvh_stats* stats);
+/* The device builders with SPATIAL SPLITS (FindBestSpatialSplit, BVH.cpp:1793-1984, by other means): before the Morton sort every
+ * triangle whose box is longer than 1.5 cells of a split_grid^3 grid over the scene box is cut into slabs of its own box (<= 4096
+ * pieces per triangle), clipped to each piece, empty pieces dropped; the hierarchy (ploc_radius 0 = Morton bits, else PLOC) is built
+ * over the resulting references, so the tree has one leaf per reference and a triangle can sit in several leaves, as in the
+ * reference's SBVH. Same serialised form. split_grid 2 .. 1024 (64 is a good start; PT_ERR_LIMIT if it would more than double the scene). */
+int pt_build_bvh_device_split(pt_context* ctx, int32_t ploc_radius, int32_t split_grid, pt_bvh_stats* stats);
+/* TOP-DOWN BINNED SAH on the device: the search the reference's builder runs (FindBestObjectSplit, BVH.cpp:1619-1763: bins per
+ * axis, the cheapest of the planes between them by surface area x count; sweep for small nodes) without its spatial splits,
+ * breadth first: per level one binning pass over the primitives of every node above 16 primitives (16 bins per axis), one thread
+ * per node choosing the plane, one partition pass; subtrees of <= 16 primitives are finished by one thread each with an exact
+ * sweep over every centroid plane. One triangle per leaf, same serialised form, same fallback to the Morton hierarchy (PT_OK + a
+ * note in pt_last_error()) should the tree come out deeper than the traversal stack. */
+int pt_build_bvh_device_sah(pt_context* ctx, pt_bvh_stats* stats);
 /* The same builder without a context or a device (pure host work): arrays are malloc()ed, release with pt_free. */
 int pt_bvh_build_host(const float* tris, int64_t n, int32_t n_threads, float** nodes, int32_t* n_nodes,
                       int32_t** refs, int32_t* n_refs, pt_bvh_stats* stats);

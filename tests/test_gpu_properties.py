@@ -96,11 +96,11 @@ def test_full_size_batch_closest_vs_any_consistency(atrium_full):
     r2.CleanUp()
 
 
-@pytest.mark.parametrize("builder", ["device", "ploc"])
+@pytest.mark.parametrize("builder", ["device", "ploc", "sah"])
 @pytest.mark.parametrize("name", ["cornell", "soup", "bunny"])
 def test_device_built_bvh(name, builder):
-    """pt_build_bvh_device (Morton LBVH built by CUDA kernels) and pt_build_bvh_device_ploc (the same pipeline with the
-    hierarchy from parallel locally-ordered clustering): the tree comes back in the reference's serialised form,
+    """pt_build_bvh_device (Morton LBVH built by CUDA kernels), pt_build_bvh_device_ploc (the same pipeline with the
+    hierarchy from parallel locally-ordered clustering) and pt_build_bvh_device_sah (top-down binned SAH): the tree comes back in the reference's serialised form,
     references every triangle exactly once, its boxes enclose their subtrees, the CUDA walk of it is bit-exact against
     the ORACLE walking the same tree, and it finds the same surfaces as the reference builder's tree."""
     s_ref = get_scene(name)
@@ -314,3 +314,48 @@ def test_device_visit_counters_equal_the_oracles():
     assert abs(c["shadow_pair_tests"] - ca["node_pairs"]) <= 0.15 * ca["node_pairs"]
     assert abs(c["shadow_tri_tests"] - ca["tri_tests"]) <= 0.15 * ca["tri_tests"]
     assert c2["closest_pair_tests"] == c["closest_pair_tests"] and c2["counted_closest_rays"] == c["counted_closest_rays"]
+
+
+@pytest.mark.parametrize("builder", ["split", "split_lbvh"])
+@pytest.mark.parametrize("name", ["cornell", "atrium_small", "bunny"])
+def test_device_built_bvh_with_spatial_splits(name, builder, monkeypatch):
+    """pt_build_bvh_device_split: long triangles are cut into clipped references before the sort (the device builders' spatial
+    splits). The tree keeps the reference's serialised form with one leaf per reference, every triangle is referenced at least
+    once, every reference box lies inside its triangle's box, parents contain children, the CUDA walk is bit-exact against the
+    oracle walking the same tree, and it finds the same surfaces as the reference builder's tree (closest AND any hit)."""
+    from common import mixed_rays
+    monkeypatch.setenv("PT_SPLIT_GRID", "24")                    # coarse scenes: make sure plenty of triangles are cut
+    s_ref = get_scene(name)
+    s = Scene(s_ref.data)
+    r = Renderer().Initialize(64, 64, s, bvh=builder)
+    st = r.bvh_stats
+    nodes, refs = s.nodes, s.refs
+    n, m = s.tris.shape[0], refs.shape[0]
+    assert m > n and nodes.shape[0] == 2 * m - 1 and st.n_leaves == m and st.n_refs == m
+    assert (refs <= 0).all() and np.array_equal(np.unique(np.abs(refs)), np.arange(n))      # one reference per leaf; nobody lost
+    d0 = nodes[:, 3].copy().view(np.int32)
+    inner = np.nonzero(d0 > 0)[0]
+    for c in (0, 1):
+        ch = d0[inner] + c
+        assert (nodes[ch, 0:3] >= nodes[inner, 0:3]).all() and (nodes[ch, 4:7] <= nodes[inner, 4:7]).all()
+    leaves = np.nonzero(d0 <= 0)[0]
+    leaves = leaves[leaves > 0]
+    tri = np.abs(refs[-d0[leaves]])
+    t = s.tris[tri]                                              # the device's own triangle box: p0, p0 + e1, p0 + e2 in binary32
+    p = np.stack([t[:, 0:3], t[:, 0:3] + t[:, 3:6], t[:, 0:3] + t[:, 6:9]], axis=1)
+    assert (nodes[leaves, 0:3] >= p.min(axis=1)).all() and (nodes[leaves, 4:7] <= p.max(axis=1)).all()
+    ext = nodes[leaves, 4:7] - nodes[leaves, 0:3]
+    assert (ext >= 0).all()
+    rays, anyr = mixed_rays(s, 200000), mixed_rays(s, 200000, seed=13, any_hit=True)
+    got, gflag = r.TraceClosest(rays), r.TraceAny(anyr)
+    r.CleanUp()
+    o = oracle.Oracle(s)
+    want, _ = o.trace_closest(rays)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(gflag, o.trace_any(anyr)[0])
+    o_ref = oracle.Oracle(s_ref)
+    other, _ = o_ref.trace_closest(rays)
+    same = got[:, 3].view(np.int32) == other[:, 3].view(np.int32)
+    assert same.mean() > 1 - 1e-4
+    assert np.array_equal(got[same, :3].view(np.uint32), other[same, :3].view(np.uint32))
+    assert (gflag == o_ref.trace_any(anyr)[0]).mean() > 1 - 1e-4
