@@ -438,7 +438,7 @@ __global__ void k_depth(const int* __restrict__ parent_inner, const int* __restr
 // references); its spatial splits are worth 2 % of SAH cost on the atrium and nothing on the bunny scene, the
 // top-down search itself is worth the 8-10 % that separate it from Morton / PLOC trees. Here the same search runs on the device,
 // breadth first: every level bins the primitives of all nodes larger than SAH_SMALL at once (SAH_BINS bins per axis over the
-// node's box, counts + boxes accumulated with atomics: block-private in shared memory for the node a block starts in, global for
+// node's CENTROID box, counts + boxes accumulated with atomics: block-private in shared memory for the node a block starts in, global for
 // the rest), one thread per node picks the cheapest of the 3 x (SAH_BINS - 1) planes and creates the children, and the primitives
 // are partitioned into the other index buffer; subtrees of <= SAH_SMALL primitives are finished by ONE thread each with an exact
 // sweep. One primitive per leaf, as the other device builders; inner ids are handed out by an atomic counter (root = 0) and made
@@ -459,9 +459,9 @@ __device__ __forceinline__ float half_area(const float lo[3], const float hi[3])
     return x * (y + z) + y * z;
 }
 
-__global__ void k_sah_init(LeafSrc src, int n, float4* prim_lo, float4* prim_hi, int* idx, int* node_of, unsigned* root_bounds) {
-    __shared__ unsigned s[6];
-    if (threadIdx.x < 3) s[threadIdx.x] = 0xffffffffu; else if (threadIdx.x < 6) s[threadIdx.x] = 0u;
+__global__ void k_sah_init(LeafSrc src, int n, float4* prim_lo, float4* prim_hi, int* idx, int* node_of, unsigned* root_bounds, unsigned* cb /* root's centroid box */) {
+    __shared__ unsigned s[12];
+    if (threadIdx.x < 12) s[threadIdx.x] = (threadIdx.x % 6) < 3 ? 0xffffffffu : 0u;
     __syncthreads();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         float lo[3], hi[3];
@@ -469,11 +469,17 @@ __global__ void k_sah_init(LeafSrc src, int n, float4* prim_lo, float4* prim_hi,
         prim_lo[i] = make_float4(lo[0], lo[1], lo[2], 0.0f); prim_hi[i] = make_float4(hi[0], hi[1], hi[2], 0.0f);
         idx[i] = i; node_of[i] = 0;
 #pragma unroll
-        for (int k = 0; k < 3; k++) { atomicMin(&s[k], f2ord(lo[k])); atomicMax(&s[3 + k], f2ord(hi[k])); }
+        for (int k = 0; k < 3; k++) {
+            atomicMin(&s[k], f2ord(lo[k])); atomicMax(&s[3 + k], f2ord(hi[k]));
+            const unsigned c = f2ord(0.5f * (lo[k] + hi[k]));
+            atomicMin(&s[6 + k], c); atomicMax(&s[9 + k], c);
+        }
     }
     __syncthreads();
     if (threadIdx.x < 3) atomicMin(&root_bounds[threadIdx.x], s[threadIdx.x]);
     else if (threadIdx.x < 6) atomicMax(&root_bounds[threadIdx.x], s[threadIdx.x]);
+    else if (threadIdx.x < 9) atomicMin(&cb[threadIdx.x - 6], s[threadIdx.x]);
+    else if (threadIdx.x < 12) atomicMax(&cb[threadIdx.x - 6], s[threadIdx.x]);
 }
 __global__ void k_sah_root(const unsigned* __restrict__ root_bounds, int n, SahNode* nodes, float4* inner_lo, float4* inner_hi, int* parent_inner,
                            int* subtree, int* slot_of, int* lists /* [0] large count, [1] small count */, int* large, int* small) {
@@ -488,7 +494,7 @@ __global__ void k_sah_root(const unsigned* __restrict__ root_bounds, int n, SahN
 // bins of every large node of this level: cnt[slot][axis][bin], box[slot][axis][bin][6] (ordered uints)
 __global__ void __launch_bounds__(BVH_THREADS)
 k_sah_bin(const int* __restrict__ idx, const int* __restrict__ node_of, int n, const int* __restrict__ slot_of, const float4* __restrict__ prim_lo,
-          const float4* __restrict__ prim_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi, unsigned* cnt, unsigned* box) {
+          const float4* __restrict__ prim_hi, const unsigned* __restrict__ cb, unsigned* cnt, unsigned* box) {
     __shared__ unsigned s_cnt[3 * SAH_BINS];
     __shared__ unsigned s_box[3 * SAH_BINS * 6];
     __shared__ int s_node;
@@ -504,9 +510,10 @@ k_sah_bin(const int* __restrict__ idx, const int* __restrict__ node_of, int n, c
         const int slot = nd >= 0 ? slot_of[nd] : -1;
         if (slot >= 0) {
             const int prim = idx[pos];
-            const float4 plo = prim_lo[prim], phi = prim_hi[prim], nlo = inner_lo[nd], nhi = inner_hi[nd];
+            const float4 plo = prim_lo[prim], phi = prim_hi[prim];
             const float l[3] = {plo.x, plo.y, plo.z}, h[3] = {phi.x, phi.y, phi.z};
-            const float nl[3] = {nlo.x, nlo.y, nlo.z}, nh[3] = {nhi.x, nhi.y, nhi.z};
+            const unsigned* nb = cb + (size_t)nd * 6;
+            const float nl[3] = {ord2f(nb[0]), ord2f(nb[1]), ord2f(nb[2])}, nh[3] = {ord2f(nb[3]), ord2f(nb[4]), ord2f(nb[5])};
             const bool priv = nd == first;
 #pragma unroll
             for (int ax = 0; ax < 3; ax++) {
@@ -540,7 +547,7 @@ __global__ void k_sah_box_init(unsigned* box, size_t count) {
 // children of node `nd` after a split that puts nl primitives on the left: ids, ranges, boxes, parents; appended to the next lists
 __device__ void sah_make_children(int nd, int begin, int end, int nl, const float llo[3], const float lhi[3], const float rlo[3], const float rhi[3],
                                   SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf,
-                                  int* subtree, int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, int& left, int& right) {
+                                  int* subtree, int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, unsigned* cb, int& left, int& right) {
     const int cnts[2] = {nl, end - begin - nl}, begins[2] = {begin, begin + nl};
     int link[2];
     for (int k = 0; k < 2; k++) {
@@ -551,6 +558,7 @@ __device__ void sah_make_children(int nd, int begin, int end, int nl, const floa
         const float* lo = k ? rlo : llo; const float* hi = k ? rhi : lhi;
         inner_lo[id] = make_float4(lo[0], lo[1], lo[2], 0.0f); inner_hi[id] = make_float4(hi[0], hi[1], hi[2], 0.0f);
         parent_inner[id] = nd; subtree[id] = cnts[k] - 1;
+        for (int q = 0; q < 6; q++) cb[(size_t)id * 6 + q] = q < 3 ? 0xffffffffu : 0u;      // filled by k_sah_partition
         if (cnts[k] > SAH_SMALL) { const int s = atomicAdd(&next_lists[0], 1); next_large[s] = id; slot_of[id] = s; }
         else { const int s = atomicAdd(&next_lists[1], 1); next_small[s] = id; slot_of[id] = -1; }
     }
@@ -558,49 +566,63 @@ __device__ void sah_make_children(int nd, int begin, int end, int nl, const floa
     left = link[0]; right = link[1];
 }
 
-__global__ void k_sah_split(const int* __restrict__ large, int n_large, const unsigned* __restrict__ cnt, const unsigned* __restrict__ box,
-                            SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf, int* subtree,
-                            int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, SahSplit* splits, unsigned* part_cnt /* 2 per slot */) {
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    if (slot >= n_large) return;
+// one WARP per large node: the 3 x (SAH_BINS - 1) planes are spread over the lanes, each summing its two sides from the node's bins
+// (staged in shared memory); the cheapest wins, the lowest (axis, plane) among equals
+#define SAH_SPLIT_WARPS 4
+#define SAH_PLANES (3 * (SAH_BINS - 1))
+__device__ __forceinline__ void sah_side(const unsigned* c, const unsigned* x, int b0, int b1, float lo[3], float hi[3], int& count) {
+    lo[0] = lo[1] = lo[2] = 3.4e38f; hi[0] = hi[1] = hi[2] = -3.4e38f; count = 0;
+    for (int b = b0; b < b1; b++) {
+        if (!c[b]) continue;
+        count += (int)c[b];
+        for (int q = 0; q < 3; q++) { lo[q] = fminf(lo[q], ord2f(x[b * 6 + q])); hi[q] = fmaxf(hi[q], ord2f(x[b * 6 + 3 + q])); }
+    }
+}
+__global__ void __launch_bounds__(32 * SAH_SPLIT_WARPS)
+k_sah_split(const int* __restrict__ large, int n_large, const unsigned* __restrict__ cnt, const unsigned* __restrict__ box,
+            SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf, int* subtree,
+            int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, SahSplit* splits, unsigned* part_cnt /* 2 per slot */, unsigned* cb) {
+    __shared__ unsigned s_cnt[SAH_SPLIT_WARPS][3 * SAH_BINS], s_box[SAH_SPLIT_WARPS][3 * SAH_BINS * 6];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int slot = blockIdx.x * SAH_SPLIT_WARPS + w;
+    if (slot >= n_large) return;                                  // whole warps leave
+    const unsigned full = 0xffffffffu;
+    for (int k = lane; k < 3 * SAH_BINS; k += 32) s_cnt[w][k] = cnt[(size_t)slot * 3 * SAH_BINS + k];
+    for (int k = lane; k < 3 * SAH_BINS * 6; k += 32) s_box[w][k] = box[(size_t)slot * 3 * SAH_BINS * 6 + k];
+    __syncwarp();
+    float best = 3.4e38f; int bc = 0x7fffffff;
+    for (int cand = lane; cand < SAH_PLANES; cand += 32) {
+        const int ax = cand / (SAH_BINS - 1), k = cand % (SAH_BINS - 1) + 1;     // plane k: bins < k on the left
+        float llo[3], lhi[3], rlo[3], rhi[3]; int lc, rc;
+        sah_side(s_cnt[w] + ax * SAH_BINS, s_box[w] + ax * SAH_BINS * 6, 0, k, llo, lhi, lc);
+        sah_side(s_cnt[w] + ax * SAH_BINS, s_box[w] + ax * SAH_BINS * 6, k, SAH_BINS, rlo, rhi, rc);
+        if (lc == 0 || rc == 0) continue;
+        const float cost = half_area(llo, lhi) * (float)lc + half_area(rlo, rhi) * (float)rc;
+        if (cost < best) { best = cost; bc = cand; }
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        const float ob = __shfl_xor_sync(full, best, off); const int oc = __shfl_xor_sync(full, bc, off);
+        if (ob < best || (ob == best && oc < bc)) { best = ob; bc = oc; }
+    }
+    if (lane != 0) return;
     const int nd = large[slot];
     const int begin = nodes[nd].begin, end = nodes[nd].end, count = end - begin;
-    float best = 3.4e38f; int baxis = -1, bplane = 0, bnl = 0;
     float bl[6], br[6];
-    for (int ax = 0; ax < 3; ax++) {
-        const unsigned* c = cnt + ((size_t)slot * 3 + ax) * SAH_BINS;
-        const unsigned* x = box + ((size_t)slot * 3 + ax) * SAH_BINS * 6;
-        // suffix boxes: right side of plane k = bins k .. SAH_BINS-1
-        float rlo[SAH_BINS][3], rhi[SAH_BINS][3]; int rc[SAH_BINS];
-        float lo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, hi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}; int acc = 0;
-        for (int b = SAH_BINS - 1; b >= 1; b--) {
-            if (c[b]) for (int k = 0; k < 3; k++) { lo[k] = fminf(lo[k], ord2f(x[b * 6 + k])); hi[k] = fmaxf(hi[k], ord2f(x[b * 6 + 3 + k])); }
-            acc += (int)c[b];
-            for (int k = 0; k < 3; k++) { rlo[b][k] = lo[k]; rhi[b][k] = hi[k]; }
-            rc[b] = acc;
-        }
-        float llo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, lhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}; int lc = 0;
-        for (int k = 1; k < SAH_BINS; k++) {                       // plane k: bins < k left
-            const int b = k - 1;
-            if (c[b]) for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], ord2f(x[b * 6 + q])); lhi[q] = fmaxf(lhi[q], ord2f(x[b * 6 + 3 + q])); }
-            lc += (int)c[b];
-            if (lc == 0 || rc[k] == 0) continue;
-            const float cost = half_area(llo, lhi) * (float)lc + half_area(rlo[k], rhi[k]) * (float)rc[k];
-            if (cost < best) {
-                best = cost; baxis = ax; bplane = k; bnl = lc;
-                for (int q = 0; q < 3; q++) { bl[q] = llo[q]; bl[3 + q] = lhi[q]; br[q] = rlo[k][q]; br[3 + q] = rhi[k][q]; }
-            }
-        }
-    }
-    if (baxis < 0) {
+    SahSplit sp;
+    if (best < 3.4e38f) {
+        sp.axis = bc / (SAH_BINS - 1); sp.plane = bc % (SAH_BINS - 1) + 1;
+        int rc;
+        sah_side(s_cnt[w] + sp.axis * SAH_BINS, s_box[w] + sp.axis * SAH_BINS * 6, 0, sp.plane, bl, bl + 3, sp.nl);
+        sah_side(s_cnt[w] + sp.axis * SAH_BINS, s_box[w] + sp.axis * SAH_BINS * 6, sp.plane, SAH_BINS, br, br + 3, rc);
+    } else {
         // every centroid in one bin on all three axes: halve by position; children keep the parent's box (conservative)
-        bnl = count / 2;
+        sp.axis = -1; sp.plane = 0; sp.nl = count / 2;
         const float4 a = inner_lo[nd], b = inner_hi[nd];
         bl[0] = br[0] = a.x; bl[1] = br[1] = a.y; bl[2] = br[2] = a.z; bl[3] = br[3] = b.x; bl[4] = br[4] = b.y; bl[5] = br[5] = b.z;
     }
-    SahSplit sp; sp.axis = baxis; sp.plane = bplane; sp.nl = bnl;
-    sah_make_children(nd, begin, end, bnl, bl, bl + 3, br, br + 3, nodes, inner_lo, inner_hi, children, parent_inner, parent_leaf, subtree, slot_of,
-                      next_lists, next_large, next_small, alloc, sp.left, sp.right);
+    sah_make_children(nd, begin, end, sp.nl, bl, bl + 3, br, br + 3, nodes, inner_lo, inner_hi, children, parent_inner, parent_leaf, subtree, slot_of,
+                      next_lists, next_large, next_small, alloc, cb, sp.left, sp.right);
     splits[slot] = sp;
     part_cnt[2 * slot] = 0u; part_cnt[2 * slot + 1] = 0u;
 }
@@ -609,8 +631,7 @@ __global__ void k_sah_split(const int* __restrict__ large, int n_large, const un
 __global__ void __launch_bounds__(BVH_THREADS)
 k_sah_partition(const int* __restrict__ idx, const int* __restrict__ node_of, int n, const int* __restrict__ slot_of_level /* slots as of THIS level */,
                 const SahNode* __restrict__ nodes_level /* ranges as of this level (begin/end of the node being split) */, const SahSplit* __restrict__ splits,
-                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi,
-                unsigned* part_cnt, int* idx_out, int* node_out) {
+                const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, unsigned* cb, unsigned* part_cnt, int* idx_out, int* node_out) {
     const int pos = blockIdx.x * blockDim.x + threadIdx.x;
     if (pos >= n) return;
     const int nd = node_of[pos];
@@ -620,12 +641,12 @@ k_sah_partition(const int* __restrict__ idx, const int* __restrict__ node_of, in
     const SahSplit sp = splits[slot];
     const int begin = nodes_level[nd].begin;
     bool left;
+    const float4 plo = prim_lo[prim], phi = prim_hi[prim];
+    const float cen[3] = {0.5f * (plo.x + phi.x), 0.5f * (plo.y + phi.y), 0.5f * (plo.z + phi.z)};
     if (sp.axis < 0) left = pos - begin < sp.nl;
     else {
-        const float4 plo = prim_lo[prim], phi = prim_hi[prim], nlo = inner_lo[nd], nhi = inner_hi[nd];
-        const float c = sp.axis == 0 ? 0.5f * (plo.x + phi.x) : sp.axis == 1 ? 0.5f * (plo.y + phi.y) : 0.5f * (plo.z + phi.z);
-        const float lo = sp.axis == 0 ? nlo.x : sp.axis == 1 ? nlo.y : nlo.z, hi = sp.axis == 0 ? nhi.x : sp.axis == 1 ? nhi.y : nhi.z;
-        left = sah_bin(c, lo, hi) < sp.plane;
+        const float c = sp.axis == 0 ? cen[0] : sp.axis == 1 ? cen[1] : cen[2];
+        left = sah_bin(c, ord2f(cb[(size_t)nd * 6 + sp.axis]), ord2f(cb[(size_t)nd * 6 + 3 + sp.axis])) < sp.plane;
     }
     // one atomic per (node, side) group of the warp
     const unsigned key = ((unsigned)slot << 1) | (left ? 0u : 1u);
@@ -638,75 +659,112 @@ k_sah_partition(const int* __restrict__ idx, const int* __restrict__ node_of, in
     idx_out[at] = prim;
     const int child = left ? sp.left : sp.right;
     node_out[at] = child >= 0 ? child : -1;
+    // the child's centroid box (what the next level bins over): reduced over the warp's group first
+    const int child_count = left ? sp.nl : nodes_level[nd].end - begin - sp.nl;
+    if (child_count > SAH_SMALL) {                                // small subtrees are swept exactly, no bins
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            const unsigned o = f2ord(cen[q]);
+            const unsigned mn = __reduce_min_sync(peers, o), mx = __reduce_max_sync(peers, o);
+            if (lane == leader) { atomicMin(&cb[(size_t)child * 6 + q], mn); atomicMax(&cb[(size_t)child * 6 + 3 + q], mx); }
+        }
+    }
 }
 
-// one thread finishes the whole subtree of a node with <= SAH_SMALL primitives: exact SAH over every centroid plane of every axis
-__global__ void k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ idx, const SahNode* __restrict__ nodes_in,
-                            const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, float4* inner_lo, float4* inner_hi, int2* children,
-                            int* parent_inner, int* parent_leaf, int* subtree, int* alloc, int* idx_out, int* node_out) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_small) return;
+// one WARP finishes the whole subtree of a node with <= SAH_SMALL primitives: exact SAH over every centroid plane of every axis
+// (3c candidates, up to two per lane, each an O(c) pass over the node's primitives in shared memory), stable partition by ballot
+#define SAH_SMALL_WARPS 4
+__global__ void __launch_bounds__(32 * SAH_SMALL_WARPS)
+k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ idx, const SahNode* __restrict__ nodes_in,
+            const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, float4* inner_lo, float4* inner_hi, int2* children,
+            int* parent_inner, int* parent_leaf, int* subtree, int* alloc, int* idx_out, int* node_out) {
+    __shared__ float s_lo[SAH_SMALL_WARPS][SAH_SMALL][3], s_hi[SAH_SMALL_WARPS][SAH_SMALL][3];
+    __shared__ int s_id[SAH_SMALL_WARPS][SAH_SMALL], s_stack[SAH_SMALL_WARPS][SAH_SMALL][3];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int t = blockIdx.x * SAH_SMALL_WARPS + w;
+    if (t >= n_small) return;                                     // whole warps leave
+    const unsigned full = 0xffffffffu, lt = (1u << lane) - 1u;
     const int root = small[t];
     const int rb = nodes_in[root].begin, cnt0 = nodes_in[root].end - rb;
-    int ids[SAH_SMALL]; float lo[SAH_SMALL][3], hi[SAH_SMALL][3], ce[SAH_SMALL][3];
-    for (int k = 0; k < cnt0; k++) {
-        ids[k] = idx[rb + k];
-        const float4 a = prim_lo[ids[k]], b = prim_hi[ids[k]];
-        lo[k][0] = a.x; lo[k][1] = a.y; lo[k][2] = a.z; hi[k][0] = b.x; hi[k][1] = b.y; hi[k][2] = b.z;
-        for (int q = 0; q < 3; q++) ce[k][q] = 0.5f * (lo[k][q] + hi[k][q]);
+    float (*lo)[3] = s_lo[w]; float (*hi)[3] = s_hi[w]; int* ids = s_id[w];
+    if (lane < cnt0) {
+        const int prim = idx[rb + lane];
+        const float4 a = prim_lo[prim], b = prim_hi[prim];
+        ids[lane] = prim; lo[lane][0] = a.x; lo[lane][1] = a.y; lo[lane][2] = a.z; hi[lane][0] = b.x; hi[lane][1] = b.y; hi[lane][2] = b.z;
     }
-    int next_id = cnt0 > 2 ? atomicAdd(alloc, cnt0 - 2) : 0;     // the subtree has cnt0 - 1 inner nodes; `root` is one of them
-    // explicit stack of (node id, first, count) over the local arrays
-    int st_node[SAH_SMALL], st_first[SAH_SMALL], st_cnt[SAH_SMALL], sp = 0;
-    st_node[0] = root; st_first[0] = 0; st_cnt[0] = cnt0; sp = 1;
+    int next_id = 0;                                              // the subtree has cnt0 - 1 inner nodes; `root` is one of them
+    if (cnt0 > 2) { if (lane == 0) next_id = atomicAdd(alloc, cnt0 - 2); next_id = __shfl_sync(full, next_id, 0); }
+    if (lane == 0) { s_stack[w][0][0] = root; s_stack[w][0][1] = 0; s_stack[w][0][2] = cnt0; }
+    int sp = 1;
+    __syncwarp();
     while (sp > 0) {
         sp--;
-        const int nd = st_node[sp], f = st_first[sp], c = st_cnt[sp];
-        float best = 3.4e38f; int baxis = -1, bj = 0;
-        for (int ax = 0; ax < 3; ax++)
-            for (int j = f; j < f + c; j++) {
-                // plane at primitive j's centroid: left = centroids below it (ties by slot), j itself goes right
-                float llo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, lhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}, rlo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, rhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
-                int nl = 0;
-                for (int i = f; i < f + c; i++) {
-                    const bool left = ce[i][ax] < ce[j][ax] || (ce[i][ax] == ce[j][ax] && i < j);
-                    if (left) { nl++; for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], lo[i][q]); lhi[q] = fmaxf(lhi[q], hi[i][q]); } }
-                    else for (int q = 0; q < 3; q++) { rlo[q] = fminf(rlo[q], lo[i][q]); rhi[q] = fmaxf(rhi[q], hi[i][q]); }
-                }
-                if (nl == 0) continue;
-                const float cost = half_area(llo, lhi) * (float)nl + half_area(rlo, rhi) * (float)(c - nl);
-                if (cost < best) { best = cost; baxis = ax; bj = j; }
+        const int nd = s_stack[w][sp][0], f = s_stack[w][sp][1], c = s_stack[w][sp][2];
+        __syncwarp();
+        float best = 3.4e38f; int bc = 0x7fffffff;
+        for (int cand = lane; cand < 3 * c; cand += 32) {
+            // plane at primitive j's centroid: left = centroids below it (ties by slot), j itself goes right
+            const int ax = cand / c, j = f + cand % c;
+            const float cj = 0.5f * (lo[j][ax] + hi[j][ax]);
+            float llo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, lhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}, rlo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, rhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+            int nl = 0;
+            for (int i = f; i < f + c; i++) {
+                const float ci = 0.5f * (lo[i][ax] + hi[i][ax]);
+                const bool left = ci < cj || (ci == cj && i < j);
+                if (left) { nl++; for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], lo[i][q]); lhi[q] = fmaxf(lhi[q], hi[i][q]); } }
+                else for (int q = 0; q < 3; q++) { rlo[q] = fminf(rlo[q], lo[i][q]); rhi[q] = fmaxf(rhi[q], hi[i][q]); }
             }
-        // stable partition of [f, f + c) about the chosen plane (there always is one: the smallest centroid of an axis has nl = 0,
-        // every other primitive has nl >= 1, and c >= 2)
-        int tid[SAH_SMALL]; float tlo[SAH_SMALL][3], thi[SAH_SMALL][3], tce[SAH_SMALL][3]; int nl = 0, nr = 0;
-        if (baxis < 0) { baxis = 0; bj = f + c / 2; }            // unreachable for c >= 2 unless NaN boxes: halve
-        const float pivot = ce[bj][baxis];
-        bool side[SAH_SMALL];
-        for (int i = f; i < f + c; i++) { side[i - f] = best < 3.4e38f ? (ce[i][baxis] < pivot || (ce[i][baxis] == pivot && i < bj)) : (i - f < c / 2); nl += side[i - f] ? 1 : 0; }
-        int wl = 0, wr = nl;
-        for (int i = f; i < f + c; i++) {
-            const int w = side[i - f] ? wl++ : wr++;
-            tid[w] = ids[i];
-            for (int q = 0; q < 3; q++) { tlo[w][q] = lo[i][q]; thi[w][q] = hi[i][q]; tce[w][q] = ce[i][q]; }
+            if (nl == 0) continue;
+            const float cost = half_area(llo, lhi) * (float)nl + half_area(rlo, rhi) * (float)(c - nl);
+            if (cost < best) { best = cost; bc = cand; }
         }
-        nr = c - nl;
-        for (int w = 0; w < c; w++) { ids[f + w] = tid[w]; for (int q = 0; q < 3; q++) { lo[f + w][q] = tlo[w][q]; hi[f + w][q] = thi[w][q]; ce[f + w][q] = tce[w][q]; } }
-        int link[2];
-        const int firsts[2] = {f, f + nl}, cnts[2] = {nl, nr};
-        for (int k = 0; k < 2; k++) {
-            if (cnts[k] == 1) { link[k] = ~(rb + firsts[k]); parent_leaf[rb + firsts[k]] = nd; continue; }
-            const int id = next_id++;
-            link[k] = id;
-            float blo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, bhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
-            for (int i = firsts[k]; i < firsts[k] + cnts[k]; i++) for (int q = 0; q < 3; q++) { blo[q] = fminf(blo[q], lo[i][q]); bhi[q] = fmaxf(bhi[q], hi[i][q]); }
-            inner_lo[id] = make_float4(blo[0], blo[1], blo[2], 0.0f); inner_hi[id] = make_float4(bhi[0], bhi[1], bhi[2], 0.0f);
-            parent_inner[id] = nd; subtree[id] = cnts[k] - 1;
-            st_node[sp] = id; st_first[sp] = firsts[k]; st_cnt[sp] = cnts[k]; sp++;
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {                  // cheapest plane, the lowest candidate among equals
+            const float ob = __shfl_xor_sync(full, best, off); const int oc = __shfl_xor_sync(full, bc, off);
+            if (ob < best || (ob == best && oc < bc)) { best = ob; bc = oc; }
         }
-        children[nd] = make_int2(link[0], link[1]);
+        // there always is a plane for c >= 2 (every centroid but an axis' smallest has somebody on its left) unless boxes hold NaN: halve then
+        const bool have = best < 3.4e38f;
+        const int ax = have ? bc / c : 0, bj = have ? f + bc % c : f;
+        const float pivot = 0.5f * (lo[bj][ax] + hi[bj][ax]);
+        const bool mine = lane < c;
+        const int i = f + (mine ? lane : 0);
+        const float ci = 0.5f * (lo[i][ax] + hi[i][ax]);
+        const bool left = mine && (have ? (ci < pivot || (ci == pivot && i < bj)) : lane < c / 2);
+        const unsigned bl = __ballot_sync(full, left), br = __ballot_sync(full, mine && !left);
+        const int nl = __popc(bl);
+        const int at = f + (left ? __popc(bl & lt) : nl + __popc(br & lt));
+        const int my_id = ids[i]; float ml[3], mh[3];
+        for (int q = 0; q < 3; q++) { ml[q] = lo[i][q]; mh[q] = hi[i][q]; }
+        float cl[3], chh[3], cr[3], crh[3];
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            const unsigned ol = f2ord(ml[q]), oh = f2ord(mh[q]);
+            cl[q] = ord2f(__reduce_min_sync(full, left ? ol : 0xffffffffu)); chh[q] = ord2f(__reduce_max_sync(full, left ? oh : 0u));
+            cr[q] = ord2f(__reduce_min_sync(full, mine && !left ? ol : 0xffffffffu)); crh[q] = ord2f(__reduce_max_sync(full, mine && !left ? oh : 0u));
+        }
+        __syncwarp();
+        if (mine) { ids[at] = my_id; for (int q = 0; q < 3; q++) { lo[at][q] = ml[q]; hi[at][q] = mh[q]; } }
+        const int cnts[2] = {nl, c - nl}, firsts[2] = {f, f + nl};
+        int child_id[2];
+        for (int k = 0; k < 2; k++) child_id[k] = cnts[k] > 1 ? next_id++ : -1;
+        if (lane == 0) {
+            int link[2], push = sp;
+            for (int k = 0; k < 2; k++) {
+                if (cnts[k] == 1) { link[k] = ~(rb + firsts[k]); parent_leaf[rb + firsts[k]] = nd; continue; }
+                const int id = child_id[k];
+                link[k] = id;
+                inner_lo[id] = k ? make_float4(cr[0], cr[1], cr[2], 0.0f) : make_float4(cl[0], cl[1], cl[2], 0.0f);
+                inner_hi[id] = k ? make_float4(crh[0], crh[1], crh[2], 0.0f) : make_float4(chh[0], chh[1], chh[2], 0.0f);
+                parent_inner[id] = nd; subtree[id] = cnts[k] - 1;
+                s_stack[w][push][0] = id; s_stack[w][push][1] = firsts[k]; s_stack[w][push][2] = cnts[k]; push++;
+            }
+            children[nd] = make_int2(link[0], link[1]);
+        }
+        sp += (cnts[0] > 1 ? 1 : 0) + (cnts[1] > 1 ? 1 : 0);
+        __syncwarp();
     }
-    for (int k = 0; k < cnt0; k++) { idx_out[rb + k] = ids[k]; node_out[rb + k] = -1; }
+    if (lane < cnt0) { idx_out[rb + lane] = ids[lane]; node_out[rb + lane] = -1; }
 }
 __global__ void k_sah_leaves(const int* __restrict__ idx, int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, int* vals,
                              float4* leaf_lo, float4* leaf_hi) {
@@ -974,7 +1032,7 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
     float4 *sah_prim_lo = nullptr, *sah_prim_hi = nullptr;
     int *sah_idx[2] = {nullptr, nullptr}, *sah_node_of[2] = {nullptr, nullptr}, *sah_slot_of = nullptr, *sah_large[2] = {nullptr, nullptr}, *sah_small[2] = {nullptr, nullptr};
     int *sah_lists = nullptr, *sah_alloc = nullptr;
-    unsigned *sah_cnt = nullptr, *sah_box = nullptr, *sah_part = nullptr;
+    unsigned *sah_cnt = nullptr, *sah_box = nullptr, *sah_part = nullptr, *sah_cb = nullptr;
     SahNode* sah_nodes = nullptr; SahSplit* sah_splits = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     const unsigned init_bounds[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
@@ -1001,7 +1059,6 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
         BCK(cudaMalloc((void**)&d_m, 8));
         BCK(cudaMemsetAsync(d_m, 0, 8, st));                     // [0] = cluster count of the round, [1] = inner nodes created
     }
-    BCK(cudaEventRecord(e0, st));
     if (ploc_radius < 0) {
         // ---- top-down binned SAH (kernels above). Level loop on the host: one 8-byte read-back per level sizes the launches.
         const int max_slots = n / (SAH_SMALL + 1) + 2;
@@ -1011,11 +1068,17 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
         BCK(cudaMalloc((void**)&subtree, (size_t)n * 4)); BCK(cudaMalloc((void**)&remap, (size_t)n * 4));
         for (int k = 0; k < 2; k++) { BCK(cudaMalloc((void**)&sah_large[k], (size_t)max_slots * 4)); BCK(cudaMalloc((void**)&sah_small[k], (size_t)(n / 2 + 2) * 4)); }
         BCK(cudaMalloc((void**)&sah_lists, 4 * 4)); BCK(cudaMalloc((void**)&sah_alloc, 4));
+        BCK(cudaMalloc((void**)&sah_cb, (size_t)n * 6 * 4));
+        BCK(cudaMemcpyAsync(sah_cb, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice, st));
         BCK(cudaMalloc((void**)&sah_cnt, (size_t)max_slots * 3 * SAH_BINS * 4)); BCK(cudaMalloc((void**)&sah_box, (size_t)max_slots * 3 * SAH_BINS * 6 * 4));
         BCK(cudaMalloc((void**)&sah_splits, (size_t)max_slots * sizeof(SahSplit))); BCK(cudaMalloc((void**)&sah_part, (size_t)max_slots * 2 * 4));
         const int one = 1;
         BCK(cudaMemcpyAsync(sah_alloc, &one, 4, cudaMemcpyHostToDevice, st));             // inner id 0 is the root
-        k_sah_init<<<min(grid_n, 148 * 8), BVH_THREADS, 0, st>>>(src, n, sah_prim_lo, sah_prim_hi, sah_idx[0], sah_node_of[0], bounds); launches++;
+    }
+    BCK(cudaEventRecord(e0, st));
+    if (ploc_radius < 0) {
+        const int max_slots = n / (SAH_SMALL + 1) + 2;
+        k_sah_init<<<min(grid_n, 148 * 8), BVH_THREADS, 0, st>>>(src, n, sah_prim_lo, sah_prim_hi, sah_idx[0], sah_node_of[0], bounds, sah_cb); launches++;
         k_sah_root<<<1, 1, 0, st>>>(bounds, n, sah_nodes, inner_lo, inner_hi, parent_inner, subtree, sah_slot_of, sah_lists, sah_large[0], sah_small[0]); launches++;
         int cur = 0, lvl = 0;
         for (;; lvl++) {
@@ -1031,15 +1094,15 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
                 const size_t bins = (size_t)counts[0] * 3 * SAH_BINS;
                 BCK(cudaMemsetAsync(sah_cnt, 0, bins * 4, st));
                 k_sah_box_init<<<(unsigned)((bins * 6 + BVH_THREADS - 1) / BVH_THREADS), BVH_THREADS, 0, st>>>(sah_box, bins * 6); launches++;
-                k_sah_bin<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_prim_lo, sah_prim_hi, inner_lo, inner_hi, sah_cnt, sah_box); launches++;
-                k_sah_split<<<(counts[0] + 127) / 128, 128, 0, st>>>(sah_large[lv], counts[0], sah_cnt, sah_box, sah_nodes, inner_lo, inner_hi, children, parent_inner,
-                                                                      parent_leaf, subtree, sah_slot_of, next_lists, sah_large[nx], sah_small[nx], sah_alloc, sah_splits, sah_part); launches++;
+                k_sah_bin<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_prim_lo, sah_prim_hi, sah_cb, sah_cnt, sah_box); launches++;
+                k_sah_split<<<(counts[0] + SAH_SPLIT_WARPS - 1) / SAH_SPLIT_WARPS, 32 * SAH_SPLIT_WARPS, 0, st>>>(sah_large[lv], counts[0], sah_cnt, sah_box, sah_nodes, inner_lo, inner_hi, children, parent_inner,
+                                                                      parent_leaf, subtree, sah_slot_of, next_lists, sah_large[nx], sah_small[nx], sah_alloc, sah_splits, sah_part, sah_cb); launches++;
             }
             // copy-through + partition of the large nodes, then the small subtrees (disjoint positions of the other buffer)
-            k_sah_partition<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_nodes, sah_splits, sah_prim_lo, sah_prim_hi, inner_lo,
-                                                            inner_hi, sah_part, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
+            k_sah_partition<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_nodes, sah_splits, sah_prim_lo, sah_prim_hi, sah_cb,
+                                                            sah_part, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
             if (counts[1] > 0) {
-                k_sah_small<<<(counts[1] + 63) / 64, 64, 0, st>>>(sah_small[lv], counts[1], sah_idx[cur], sah_nodes, sah_prim_lo, sah_prim_hi, inner_lo, inner_hi, children,
+                k_sah_small<<<(counts[1] + SAH_SMALL_WARPS - 1) / SAH_SMALL_WARPS, 32 * SAH_SMALL_WARPS, 0, st>>>(sah_small[lv], counts[1], sah_idx[cur], sah_nodes, sah_prim_lo, sah_prim_hi, inner_lo, inner_hi, children,
                                                                   parent_inner, parent_leaf, subtree, sah_alloc, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
             }
             cur ^= 1;
@@ -1094,7 +1157,7 @@ done:
     for (int k = 0; k < 2; k++) { cudaFree(cid[k]); cudaFree(clo[k]); cudaFree(chi[k]); }
     cudaFree(nn); cudaFree(valid); cudaFree(block_counts); cudaFree(d_m); cudaFree(subtree); cudaFree(remap);
     cudaFree(sah_prim_lo); cudaFree(sah_prim_hi); cudaFree(sah_slot_of); cudaFree(sah_lists); cudaFree(sah_alloc); cudaFree(sah_cnt); cudaFree(sah_box);
-    cudaFree(sah_part); cudaFree(sah_nodes); cudaFree(sah_splits);
+    cudaFree(sah_part); cudaFree(sah_nodes); cudaFree(sah_splits); cudaFree(sah_cb);
     for (int k = 0; k < 2; k++) { cudaFree(sah_idx[k]); cudaFree(sah_node_of[k]); cudaFree(sah_large[k]); cudaFree(sah_small[k]); }
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
