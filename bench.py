@@ -313,7 +313,7 @@ class Dist:
 
 
 LAYOUTS = {"reference": 0, "wide": 1, "wide4": 2}
-BUILDERS = {"device": "device", "ploc": "ploc", "split": "split", "split_lbvh": "split_lbvh"}
+BUILDERS = {"device": "device", "ploc": "ploc", "sah": "sah", "split": "split", "split_lbvh": "split_lbvh"}
 
 
 def make_renderer(d, scene, W, H, wl, args, **kw):
@@ -534,7 +534,7 @@ def pathtrace_line(args, name, wl, d, scene, r, cam, m):
                          "note": "value / ms_per_step are the MEDIAN repetition of K back-to-back frames"},
         "config": {"workload": wl["desc"], "width": W, "height": H, "max_depth": depth, "triangles": scene.tris.shape[0],
                    "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
-                   "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
+                   "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'sah': 'device top-down SAH', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                    "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                    "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
                    "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
@@ -709,7 +709,7 @@ def run_micro(args, name, wl, d, sub=False):
             "ms_per_step": ms_total / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "rays_per_step": 2 * n,
-                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
+                       "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'sah': 'device top-down SAH', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                        "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
                        "bvh_nodes": int(r.bvh_stats.n_nodes), "bvh_refs": int(r.bvh_stats.n_refs),
                        "l2": "ray batches (2 x 512 MB) and tree + leaf stream (~1.2 GB) exceed the 126 MB L2",
@@ -770,12 +770,12 @@ def run_primary(args, name, wl, d, sub=False):
     cam = make_camera(scene, W, H)
     r.lib.pt_set_camera(r.ctx, cam.plane)
     n = W * H
-    # the device builders (Morton LBVH, PLOC): build time and what their trees cost to traverse
+    # the device builders (Morton LBVH, PLOC, top-down binned SAH): build time and what their trees cost to traverse
     dev = {}
     if args.bvh == "reference":
         import ctypes as C
         from gpupathtracer_b200.api import pt_bvh_stats
-        for key, which in (("host_sbvh", "build"), ("device_lbvh", "device"), ("device_ploc", "ploc")):
+        for key, which in (("host_sbvh", "build"), ("device_lbvh", "device"), ("device_ploc", "ploc"), ("device_sah", "sah")):
             s2 = Scene(scene.data)
             r2 = Renderer().Initialize(W, H, s2, max_depth=1, device=local, seed=1, bvh=which)
             dev_builds = [float(r2.bvh_stats.build_ms)]
@@ -784,6 +784,8 @@ def run_primary(args, name, wl, d, sub=False):
                 st = pt_bvh_stats()
                 if which == "ploc":
                     r2.lib.pt_build_bvh_device_ploc(r2.ctx, 16, C.byref(st))
+                elif which == "sah":
+                    r2.lib.pt_build_bvh_device_sah(r2.ctx, C.byref(st))
                 else:
                     r2.lib.pt_build_bvh_device(r2.ctx, C.byref(st))
                 dev_builds.append(float(st.build_ms)); tot = float(st.total_ms)
@@ -853,9 +855,10 @@ def run_primary(args, name, wl, d, sub=False):
             "steps": args.steps, "warmup": warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": wl["desc"], "triangles": scene.tris.shape[0], "width": W, "height": H,
-                       "bvh": {"device": "device LBVH builder", "ploc": "device PLOC builder (pt_build_bvh_device_ploc, radius 16)"}.get(
+                       "bvh": {"device": "device LBVH builder", "ploc": "device PLOC builder (pt_build_bvh_device_ploc, radius 16)",
+                               "sah": "device top-down binned SAH builder (pt_build_bvh_device_sah)"}.get(
                            args.builder, "own SBVH builder (host, all cores)") + f", {args.bvh} layout",
-                       "bvh_build_kernels_ms": float(r.bvh_stats.build_ms) if args.builder in ("device", "ploc") else None,
+                       "bvh_build_kernels_ms": float(r.bvh_stats.build_ms) if args.builder in ("device", "ploc", "sah") else None,
                        "l2": "256 MB flush between timed launches"},
             "bvh_build_ms": {**dev, "ours_host_all_cores_best_of_3": min(builds), "nodes": int(r.bvh_stats.n_nodes), "refs": int(r.bvh_stats.n_refs),
                              "sah_cost": float(r.bvh_stats.sah_cost)},
@@ -906,9 +909,9 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="default command only: skip the short runs of the other BASELINE.json configs")
     ap.add_argument("--spp", type=int, default=0, help="path-tracing workloads: render a FIXED total of samples per pixel split over the GPUs "
                     "(64-frame batches per GPU, one reduce per batch) and report time-to-image (BASELINE.json configs[4] as written: --workload 4k --spp 4096)")
-    ap.add_argument("--builder", default="host", choices=["host", "device", "ploc", "split", "split_lbvh"],
+    ap.add_argument("--builder", default="host", choices=["host", "device", "ploc", "sah", "split", "split_lbvh"],
                     help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels; ploc: the same with a "
-                         "PLOC hierarchy (pt_build_bvh_device_ploc)")
+                         "PLOC hierarchy (pt_build_bvh_device_ploc); sah: top-down binned SAH on the device (pt_build_bvh_device_sah)")
     ap.add_argument("--bvh", default="reference", choices=["reference", "wide", "wide4"],
                     help="device BVH layout: the reference's binary fp32 tree (bit-exact) or the compressed 8-/4-wide collapse of it")
     args = ap.parse_args()

@@ -359,3 +359,44 @@ def test_device_built_bvh_with_spatial_splits(name, builder, monkeypatch):
     assert same.mean() > 1 - 1e-4
     assert np.array_equal(got[same, :3].view(np.uint32), other[same, :3].view(np.uint32))
     assert (gflag == o_ref.trace_any(anyr)[0]).mean() > 1 - 1e-4
+
+
+def _degenerate_soups():
+    import dataclasses
+    from gpupathtracer_b200 import scenes
+    base = scenes.random_soup(600, seed=21)
+    out = {}
+    for n in (2, 3, 16, 17, 18, 33):                              # around the builder's small-subtree threshold (16)
+        ids = base.mat_ids[:n].copy(); ids[0] = 6                 # material 3 of the soup is its emitter: a scene needs one
+        out[f"n{n}"] = dataclasses.replace(base, verts=base.verts[:n].copy(), mat_ids=ids)
+    same = base.verts.copy(); same[:500] = same[0]                # 500 copies of one triangle: every centroid in one bin on all axes
+    out["copies"] = dataclasses.replace(base, verts=same)
+    flat = base.verts.copy(); flat[:, :, 1] = 0.25                # everything in the plane y = 0.25: one axis has zero extent
+    out["coplanar"] = dataclasses.replace(base, verts=flat)
+    return out
+
+
+@pytest.mark.parametrize("case", ["n2", "n3", "n16", "n17", "n18", "n33", "copies", "coplanar"])
+def test_device_sah_builder_on_degenerate_input(case):
+    """pt_build_bvh_device_sah where the binned search has nothing to choose from: tiny scenes around the small-subtree
+    threshold, hundreds of identical triangles (no plane separates them: halved by position), a scene with no extent on one
+    axis. The tree must still reference every triangle once, parents must contain children, and the CUDA walk of it must equal
+    the oracle's walk of the same tree bit for bit."""
+    from common import mixed_rays
+    s = Scene(_degenerate_soups()[case])
+    r = Renderer().Initialize(64, 64, s, bvh="sah")
+    nodes, refs = s.nodes, s.refs
+    n = s.tris.shape[0]
+    assert nodes.shape[0] == 2 * n - 1 and refs.shape[0] == n and (refs <= 0).all()
+    assert np.array_equal(np.sort(np.abs(refs)), np.arange(n))
+    d0 = nodes[:, 3].copy().view(np.int32)
+    inner = np.nonzero(d0 > 0)[0]
+    for c in (0, 1):
+        ch = d0[inner] + c
+        assert (nodes[ch, 0:3] >= nodes[inner, 0:3]).all() and (nodes[ch, 4:7] <= nodes[inner, 4:7]).all()
+    assert r.bvh_stats.max_depth < 96
+    rays = mixed_rays(s, 20000, seed=5)
+    got = r.TraceClosest(rays)
+    r.CleanUp()
+    want, _ = oracle.Oracle(s).trace_closest(rays)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
