@@ -96,6 +96,13 @@ int pt_create(const pt_config* cfg, pt_context** out) {
         if (want > 16) want = 16;
         size_t sz = (npx + want - 1) / want;
         sz = (sz + 63) / 64 * 64;                               // whole 8x8 Morton tiles (Iterative.comp:163-172)
+        if (cfg->width % 8 == 0) {
+            // whole tile ROWS (8 pixel rows): a slice is then one contiguous band of the accumulator, which is what lets a slice
+            // clear and reduce its own pixels without waiting for the others (pt_comm.cu). 1080p and 4K split this way anyway.
+            const size_t band = (size_t)cfg->width * 8;
+            sz = (sz + band - 1) / band * band;
+            c->slices_banded = true;
+        }
         c->slice_size = (int)sz;
         c->n_slices = (int)((npx + sz - 1) / sz);
         c->slice_streams.resize(c->n_slices); c->slice_done.resize(2 * c->n_slices);
@@ -798,12 +805,25 @@ static FrameParams frame_params(pt_context* c, int first = 0, int count = -1, in
 // `g` consecutive frames of every slice between a fork from and a join into the main stream. Slices advance through
 // their frames independently; stream-capturable (every cross-stream edge is an event).
 static int join_impl(pt_context* c, bool mark_time);
-static int enqueue_frames_impl(pt_context* c, int g, bool join) {
+static int enqueue_frames_impl(pt_context* c, int g, bool join, cudaEvent_t accum_free = nullptr, bool clear_accum = false) {
     const int npx = c->cfg.width * c->cfg.height;
     int launches = 0;
     const bool chained = c->pending_join;          // the previous frame of every slice is still on its streams, not joined
     cudaEventRecord(c->ev_fork, c->stream);
-    for (int s = 0; s < c->n_slices; s++) cudaStreamWaitEvent(c->slice_streams[s].a, c->ev_fork, 0);
+    for (int s = 0; s < c->n_slices; s++) {
+        cudaStream_t a = c->slice_streams[s].a;
+        cudaStreamWaitEvent(a, c->ev_fork, 0);
+        if (accum_free) cudaStreamWaitEvent(a, accum_free, 0);
+        if (clear_accum) {
+            // a banded slice's pixels are the accumulator range of its ray indices. The caller alternates between two accumulators
+            // (pt_comm.cu): the frames still in flight on stream b write the OTHER one, and stream a is behind everything that
+            // wrote this one (its own kernels; the shadow kernels of two batches ago through the ev_shadow wait of the last
+            // batch's first shade).
+            const int first = s * c->slice_size;
+            const int count = npx - first < c->slice_size ? npx - first : c->slice_size;
+            cudaMemsetAsync(c->d_accum + first, 0, (size_t)count * sizeof(float4), a);
+        }
+    }
     for (int f = 0; f < g; f++, c->frame_seq++)
         for (int s = 0; s < c->n_slices; s++) {
             int first = s * c->slice_size;
@@ -820,6 +840,9 @@ static int enqueue_frames_impl(pt_context* c, int g, bool join) {
     return launches;
 }
 int pt_enqueue_frames(pt_context* c, int g) { return enqueue_frames_impl(c, g, true); }
+int pt_enqueue_frames_chained(pt_context* c, int g, cudaEvent_t accum_free, bool clear_accum) {
+    return enqueue_frames_impl(c, g, false, accum_free, clear_accum && c->slices_banded);
+}
 
 static int join_impl(pt_context* c, bool mark_time) {
     if (!c->pending_join) return PT_OK;

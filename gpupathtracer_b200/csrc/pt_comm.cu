@@ -136,22 +136,34 @@ void pt_comm_release(pt_context* c) {
 }
 
 // phase 1 of a batch: n frames into this rank's current batch accumulator (zeroed first), on the render streams
+// Chained batches: every slice clears and renders its own band of the batch's accumulator behind its previous frame, nothing is
+// joined into the main stream, and the reduce below takes the bands one by one as they finish -- no drain of the GPU between
+// batches (what per-slice present is to a single GPU). Needs banded slices; stage timing keeps the joined form.
+static bool batch_chained(pt_context* c) { return c->lazy_join && c->slices_banded && !c->stage_timing; }
 static int batch_render(pt_context* c, int n_frames) {
     pt_comm_state* s = c->comm;
     CK(cudaSetDevice(c->cfg.device));
     int rc = pt_check_scene(c, "pt_render_batch", true);
-    if (rc == PT_OK) rc = pt_join_slices(c);
     if (rc != PT_OK) return rc;
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
     const int k = s->turn;
     float4* A = batch_accum(c, k);
-    CK(cudaEventRecord(c->ev0, c->stream));
-    CK(cudaStreamWaitEvent(c->stream, s->ev_reduced[k], 0));            // the reduce that last read this accumulator (two batches ago)
-    CK(cudaMemsetAsync(A, 0, npx * sizeof(float4), c->stream));
-    c->d_accum = A;
-    c->counters.kernel_launches += pt_enqueue_frames(c, n_frames);
-    CK(cudaEventRecord(c->ev1, c->stream));
-    CK(cudaEventRecord(s->ev_rendered[k], c->stream));
+    if (batch_chained(c)) {
+        if (c->slices_presenting && (rc = pt_join_slices(c)) != PT_OK) return rc;      // a single-GPU present is still resolving
+        if (!c->pending_join) CK(cudaEventRecord(c->ev0, c->stream));
+        c->d_accum = A;
+        // ev_reduced[k]: the reduce that last read this accumulator (two batches ago)
+        c->counters.kernel_launches += pt_enqueue_frames_chained(c, n_frames, s->ev_reduced[k], true);
+    } else {
+        if ((rc = pt_join_slices(c)) != PT_OK) return rc;
+        CK(cudaEventRecord(c->ev0, c->stream));
+        CK(cudaStreamWaitEvent(c->stream, s->ev_reduced[k], 0));
+        CK(cudaMemsetAsync(A, 0, npx * sizeof(float4), c->stream));
+        c->d_accum = A;
+        c->counters.kernel_launches += pt_enqueue_frames(c, n_frames);
+        CK(cudaEventRecord(c->ev1, c->stream));
+        CK(cudaEventRecord(s->ev_rendered[k], c->stream));
+    }
     CK(cudaGetLastError());
     c->num_samples += n_frames;
     c->counters.frames += n_frames;
@@ -164,9 +176,22 @@ static int batch_reduce(pt_context* c, int n_frames) {
     CK(cudaSetDevice(c->cfg.device));
     const size_t npx = (size_t)c->cfg.width * c->cfg.height;
     const int k = s->turn;
+    float4* A = batch_accum(c, k);
+    if (batch_chained(c)) {
+        // one reduce per band, each behind its own slice only (every rank issues them in slice order). Inside an NCCL group
+        // (one thread driving several ranks) the waits all land before the grouped launch: still correct, just not staggered.
+        for (int sl = 0; sl < c->n_slices; sl++) {
+            const size_t first = (size_t)sl * c->slice_size;
+            const size_t count = npx - first < (size_t)c->slice_size ? npx - first : (size_t)c->slice_size;
+            CK(cudaStreamWaitEvent(s->stream, c->slice_done[2 * sl + 1], 0));
+            if (sl == 0) CK(cudaEventRecord(s->ev_r0, s->stream));
+            NK(n->Reduce(A + first, s->rank == 0 ? s->reduced.p + first : nullptr, count * 4, ncclFloat32, ncclSum, 0, s->comm, s->stream));
+        }
+        return PT_OK;
+    }
     CK(cudaStreamWaitEvent(s->stream, s->ev_rendered[k], 0));
     CK(cudaEventRecord(s->ev_r0, s->stream));
-    NK(n->Reduce(batch_accum(c, k), s->rank == 0 ? s->reduced.p : nullptr, npx * 4, ncclFloat32, ncclSum, 0, s->comm, s->stream));
+    NK(n->Reduce(A, s->rank == 0 ? s->reduced.p : nullptr, npx * 4, ncclFloat32, ncclSum, 0, s->comm, s->stream));
     return PT_OK;
 }
 // phase 3: rank 0 folds the batch into the running total; everybody marks the accumulator free
@@ -270,6 +295,7 @@ int pt_comm_synchronize(pt_context* c) {
     int rc = need_comm(c, "pt_comm_synchronize");
     if (rc != PT_OK) return rc;
     CK(cudaSetDevice(c->cfg.device));
+    if ((rc = pt_join_slices(c)) != PT_OK) return rc;                   // chained batches: the slices' streams into the main one
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaStreamSynchronize(c->comm->stream));
     CK(cudaStreamSynchronize(c->copy_stream));
@@ -292,6 +318,7 @@ int pt_comm_download_batch(pt_context* c, float* rgba) {
     if (rc != PT_OK) return rc;
     if (!rgba || c->comm->last_turn < 0) return fail(PT_ERR_INVALID, "pt_comm_download_batch: no batch rendered yet");
     CK(cudaSetDevice(c->cfg.device));
+    if ((rc = pt_join_slices(c)) != PT_OK) return rc;
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaMemcpy(rgba, batch_accum(c, c->comm->last_turn), (size_t)c->cfg.width * c->cfg.height * 16, cudaMemcpyDeviceToHost));
     return PT_OK;

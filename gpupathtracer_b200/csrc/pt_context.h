@@ -42,6 +42,7 @@ struct pt_context {
     // Inside a slice, shadow(b) and extend(b+1) run concurrently on two streams (enqueue_frame_dag). The whole
     // fork/join structure of `g` consecutive frames is captured once into a CUDA graph and replayed.
     int n_slices = 1, slice_size = 0;
+    bool slices_banded = false;                    // every slice is a whole number of 8-row tile bands: a contiguous range of the accumulator
     std::vector<SliceStreams> slice_streams;
     std::vector<cudaEvent_t> slice_done;      // 2 per slice (streams a and b)
     cudaEvent_t ev_fork = nullptr;
@@ -140,6 +141,10 @@ pt::SceneDev pt_scene_dev(pt_context* c);
 extern "C" int pt_check_scene(pt_context* c, const char* who, bool need_shading);
 extern "C" int pt_join_slices(pt_context* c);   // c->stream waits for everything the slices have been given (device-side wait)
 #define PT_CAM_RING 64
+// n frames of every slice chained behind whatever the slice streams hold, no join (pending_join stays set). accum_free (may be
+// null): waited for by every slice before it touches c->d_accum; clear_accum: every slice zeroes its own band first (needs
+// c->slices_banded). Slice s is complete when c->slice_done[2 * s + 1] fires.
+extern "C" int pt_enqueue_frames_chained(pt_context* c, int n_frames, cudaEvent_t accum_free, bool clear_accum);
 extern "C" int pt_enqueue_frames(pt_context* c, int n_frames);            // n frames of every slice between a fork from and a join into c->stream
 extern "C" int pt_ensure_host_bvh(pt_context* c);
 void pt_comm_release(pt_context* c);                          // pt_comm.cu; called by pt_destroy
