@@ -549,6 +549,7 @@ def pathtrace_line(args, name, wl, d, scene, r, cam, m):
                          "RenderFrame + PresentAsync per step through the C ABI: camera in, tonemapped 8-bit frame out to pinned host "
                          "memory; slices chain frame to frame (no per-frame drain), each slice resolves its own pixels")},
         "gpu_launches": m["launches"], "clocks": m["clocks"], "ms_reduce": m["ms_reduce"],
+        "ms_reduce_note": "first band's ncclReduce to the last band's on the communication stream: includes waiting for the later slices (chained batches)" if world > 1 else None,
     }
     stage, stage_frames, visits = m["stage"], m["stage_frames"], m["visits"]
     line["stage_ms_per_step"] = {k: v / stage_frames for k, v in stage.items()}
