@@ -108,6 +108,9 @@ __device__ __forceinline__ bool tri_test(const LeafTri* __restrict__ rec, V3 o, 
     return false;
 }
 
+#ifndef PT_PAIR_FETCH_MIN
+#define PT_PAIR_FETCH_MIN 12          // lanes that want a pair record before the warp fetches cooperatively (below: solo loads)
+#endif
 // Per-lane traversal state machine. `current` >= 0: pair record to test next (inner step);
 // `current` < 0: ~current = next record of the leaf triangle stream to test (leaf step).
 struct Traverser {
@@ -169,6 +172,43 @@ struct Traverser {
         current = stack_at(stack, --sp);
         return false;
     }
+    // ---- pair-record fetch. Solo: the lane's own record with two 256-bit loads. Cooperative (kPairFetch, called by a CONVERGED
+    // warp): lanes 2k / 2k+1 fetch the record of lane 2k by halves with one load instruction, then the record of lane 2k+1
+    // with a second one, and swap the halves they do not need with 7 SHFL.BFLY. The L1 cost of a scattered fetch is one tag
+    // look-up per (instruction, 128-B line), so a record costs one look-up instead of two: tools/l1_microbench.cu measures
+    // 1.41 instead of 2.33 SM-cycles per record at 32 lanes, 1.68 / 2.32 at 20, 2.34 / 2.18 at 10 (profiles/r08_l1_microbench.log).
+    // MEASURED AND NOT ADOPTED (profiles/r08_pair_fetch.md): in the traversal kernels the tag accesses do drop by 30 %, but SHFL runs on
+    // the same LSU data pipe (counted there as shared-memory wavefronts), so the binding pipe carries as many wavefronts as before,
+    // and the warp-uniform loop + selects + shuffles double the warp instructions: 3284 -> 2438 Mrays/s on the headline (lane pairs
+    // in lockstep instead of the whole warp, -DPT_PAIR_FETCH_MIN=0: 2222). Build with PT_NVCC_EXTRA=-DPT_PAIR_FETCH to reproduce.
+#ifdef PT_PAIR_FETCH
+    static const bool kPairFetch = true;
+#else
+    static const bool kPairFetch = false;
+#endif
+    static __device__ __forceinline__ void fetch_solo(const SceneDev& s, int cur, float4& a0, float4& a1, float4& b0, float4& b1) {
+        const float4* q = s.pairs[cur].q;
+        F8 ca = ldg256(q), cb = ldg256(q + 2);
+        a0 = ca.lo; a1 = ca.hi; b0 = cb.lo; b1 = cb.hi;
+    }
+    static __device__ __forceinline__ void fetch_coop(const SceneDev& s, unsigned FULL /* lanes that call together: the warp, or the lane pair */,
+                                                      int cur /* < 0: this lane wants nothing */, int other /* the partner's cur */,
+                                                      float4& a0, float4& a1, float4& b0, float4& b1) {
+        const int half = threadIdx.x & 1;
+        const int even_cur = half ? other : cur, odd_cur = half ? cur : other;
+        F8 e, o;
+        e.lo = e.hi = o.lo = o.hi = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (even_cur >= 0) e = ldg256(s.pairs[even_cur].q + 2 * half);     // lane 2k: child 0 of its record, lane 2k+1: child 1 of it
+        if (odd_cur >= 0) o = ldg256(s.pairs[odd_cur].q + 2 * half);       // the record of lane 2k+1 likewise
+        // the even lane keeps e and needs the partner's e (its child 1); the odd lane keeps o and needs the partner's o (its child 0)
+        const float4 g0 = half ? e.lo : o.lo, g1 = half ? e.hi : o.hi;
+        float4 r0, r1;
+        r0.x = __shfl_xor_sync(FULL, g0.x, 1); r0.y = __shfl_xor_sync(FULL, g0.y, 1); r0.z = __shfl_xor_sync(FULL, g0.z, 1);
+        r0.w = __shfl_xor_sync(FULL, g0.w, 1);
+        r1.x = __shfl_xor_sync(FULL, g1.x, 1); r1.y = __shfl_xor_sync(FULL, g1.y, 1); r1.z = __shfl_xor_sync(FULL, g1.z, 1);
+        r1.w = 0.0f;                                                        // padding word of the record
+        if (half) { a0 = r0; a1 = r1; b0 = o.lo; b1 = o.hi; } else { a0 = e.lo; a1 = e.hi; b0 = r0; b1 = r1; }
+    }
     template <bool ANY>
     __device__ __forceinline__ bool inner_step(const SceneDev& s, int* stack) {
         float4 a0, a1, b0, b1;
@@ -179,11 +219,12 @@ struct Traverser {
             a0 = q[0]; a1 = q[1]; b0 = q[2]; b1 = q[3];
         } else
 #endif
-        {
-            const float4* q = s.pairs[current].q;
-            F8 ca = ldg256(q), cb = ldg256(q + 2);
-            a0 = ca.lo; a1 = ca.hi; b0 = cb.lo; b1 = cb.hi;
-        }
+        fetch_solo(s, current, a0, a1, b0, b1);
+        return inner_apply<ANY>(s, stack, a0, a1, b0, b1);
+    }
+    // the pair test proper on a fetched record: both boxes, near child next, far child pushed
+    template <bool ANY>
+    __device__ __forceinline__ bool inner_apply(const SceneDev& s, int* stack, float4 a0, float4 a1, float4 b0, float4 b1) {
         bool hit0, hit1;
         float d0 = slab_test(a0, a1, inv, oinv, h.t, hit0);
         float d1 = slab_test(b0, b1, inv, oinv, h.t, hit1);
@@ -233,6 +274,10 @@ struct CountingTraverser : Traverser {
     unsigned long long n_pairs = 0, n_tris = 0;
     template <bool ANY>
     __device__ __forceinline__ bool inner_step(const SceneDev& s, int* stack) { n_pairs++; return Traverser::inner_step<ANY>(s, stack); }
+    template <bool ANY>
+    __device__ __forceinline__ bool inner_apply(const SceneDev& s, int* stack, float4 a0, float4 a1, float4 b0, float4 b1) {
+        n_pairs++; return Traverser::inner_apply<ANY>(s, stack, a0, a1, b0, b1);
+    }
     template <bool ANY>
     __device__ __forceinline__ bool leaf_step(const SceneDev& s, const int* stack) { n_tris++; return Traverser::leaf_step<ANY>(s, stack); }
     __device__ __forceinline__ void epilogue(unsigned long long* out) {
@@ -292,7 +337,40 @@ __device__ __forceinline__ void trace_persistent(const SceneDev& s, const IO& io
         unsigned m_inner = m_active & ~m_leaf;
         bool done = false;
         if (m_inner != 0 && __popc(m_leaf) < leaf_thresh) {
-            if (active && !at_leaf) {
+            if constexpr (TR::kPairFetch) {
+#if PT_PAIR_FETCH_MIN > 0
+                // the burst as a warp-uniform loop, so that lane pairs can share the loads of a step (fetch_coop)
+                bool go = active && !at_leaf;
+                for (int k = 0; k < burst; k++) {
+                    const unsigned m_go = __ballot_sync(FULL, go);
+                    if (m_go == 0) break;
+                    float4 a0, a1, b0, b1;
+                    if (__popc(m_go) >= PT_PAIR_FETCH_MIN) {
+                        const int cur = go ? tr.current : -1;
+                        TR::fetch_coop(s, FULL, cur, __shfl_xor_sync(FULL, cur, 1), a0, a1, b0, b1);
+                    } else if (go) TR::fetch_solo(s, tr.current, a0, a1, b0, b1);
+                    if (go) {
+                        done = tr.template inner_apply<ANY>(s, stack, a0, a1, b0, b1);
+                        go = !done && !tr.at_leaf();
+                    }
+                }
+#else
+                // lane PAIRS in lockstep, the warp is not: a lane whose partner still has steps to take stays as its helper
+                bool go = active && !at_leaf;
+                const unsigned pm = 3u << (lane & ~1);
+                for (int k = 0; k < burst; k++) {
+                    const int cur = go ? tr.current : -1;
+                    const int other = __shfl_xor_sync(pm, cur, 1);
+                    if (cur < 0 && other < 0) break;
+                    float4 a0, a1, b0, b1;
+                    TR::fetch_coop(s, pm, cur, other, a0, a1, b0, b1);
+                    if (go) {
+                        done = tr.template inner_apply<ANY>(s, stack, a0, a1, b0, b1);
+                        go = !done && !tr.at_leaf();
+                    }
+                }
+#endif
+            } else if (active && !at_leaf) {
                 done = tr.template inner_step<ANY>(s, stack);
                 for (int k = 1; k < burst && !done && !tr.at_leaf(); k++) done = tr.template inner_step<ANY>(s, stack);
             }

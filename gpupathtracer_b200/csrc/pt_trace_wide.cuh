@@ -53,6 +53,7 @@ template <int N>
 struct WideTraverser {
     typedef uint2 StackEntry;
     static const int kStack = 32;
+    static const bool kPairFetch = false;      // the cooperative record fetch of pt_trace.cuh is for the 64-B pair records
     __device__ __forceinline__ void epilogue(unsigned long long*) {}
     V3 o, d, inv;
     HitRec h;

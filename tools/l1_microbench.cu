@@ -53,8 +53,23 @@ __global__ void __launch_bounds__(128) k(const Rec* __restrict__ t, int n, int s
             if (act) { a = __ldg(&t[idx].q[0]); b = a; c = a; d = a; }
         } else if (MODE == 5) {     // 1 x LDG.256 per lane (32 B only)
             if (act) { ld256(&t[idx].q[0], a, b); c = a; d = b; }
+        } else if (MODE == 6) {     // lane pairs: two LDG.256, each fetching ONE record of the pair by halves (one line per pair per
+                                    // instruction instead of two), then 8 SHFL.BFLY to hand the halves over
+            const unsigned even_idx = __shfl_sync(0xffffffffu, idx, lane & ~1), odd_idx = __shfl_sync(0xffffffffu, idx, lane | 1);
+            const bool even_act = (lane & ~1) < active_lanes, odd_act = (lane | 1) < active_lanes;
+            const int half = lane & 1;
+            float4 e0 = make_float4(0, 0, 0, 0), e1 = e0, o0 = e0, o1 = e0;
+            if (even_act) ld256(&t[even_idx].q[2 * half], e0, e1);       // even lane's record: lane 2k its first half, lane 2k+1 its second
+            if (odd_act) ld256(&t[odd_idx].q[2 * half], o0, o1);         // odd lane's record likewise
+            // the even lane keeps e (first half) and needs the partner's e (second half); the odd lane keeps o (second half) and needs the partner's o
+            float4 give0 = half ? e0 : o0, give1 = half ? e1 : o1, got0, got1;
+            got0.x = __shfl_xor_sync(0xffffffffu, give0.x, 1); got0.y = __shfl_xor_sync(0xffffffffu, give0.y, 1);
+            got0.z = __shfl_xor_sync(0xffffffffu, give0.z, 1); got0.w = __shfl_xor_sync(0xffffffffu, give0.w, 1);
+            got1.x = __shfl_xor_sync(0xffffffffu, give1.x, 1); got1.y = __shfl_xor_sync(0xffffffffu, give1.y, 1);
+            got1.z = __shfl_xor_sync(0xffffffffu, give1.z, 1); got1.w = __shfl_xor_sync(0xffffffffu, give1.w, 1);
+            if (half) { a = got0; b = got1; c = o0; d = o1; } else { a = e0; b = e1; c = got0; d = got1; }
         }
-        if (act || MODE == 2 || MODE == 3) {
+        if (act || MODE == 2 || MODE == 3 || MODE == 6) {
             acc += a.x + b.y + c.z + d.x;
             idx = (__float_as_uint(a.w) + (unsigned)s * 7919u + lane * 104729u) % n;   // dependent next index
         }
@@ -76,9 +91,9 @@ int main(int argc, char** argv) {
     cudaMemcpy(d, h.data(), sizeof(Rec) * n, cudaMemcpyHostToDevice);
     cudaDeviceProp p; cudaGetDeviceProperties(&p, 0);
     int blocks = p.multiProcessorCount * 10;
-    const char* names[] = {"4xLDG.128/lane", "2xLDG.256/lane", "coop 4 lanes/rec + 16 SHFL", "quad (8 rays/warp) 1xLDG.128", "1xLDG.128 (16B)", "1xLDG.256 (32B)"};
+    const char* names[] = {"4xLDG.128/lane", "2xLDG.256/lane", "coop 4 lanes/rec + 16 SHFL", "quad (8 rays/warp) 1xLDG.128", "1xLDG.128 (16B)", "1xLDG.256 (32B)", "lane pairs: 2xLDG.256 by halves + 8 SHFL"};
     for (int lanes : {32, 20, 10}) {
-        for (int mode = 0; mode < 6; mode++) {
+        for (int mode = 0; mode < 7; mode++) {
             cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
             for (int rep = 0; rep < 2; rep++) {
                 cudaEventRecord(e0);
@@ -89,6 +104,7 @@ int main(int argc, char** argv) {
                     case 3: k<3><<<blocks, 128>>>(d, n, steps, out, lanes); break;
                     case 4: k<4><<<blocks, 128>>>(d, n, steps, out, lanes); break;
                     case 5: k<5><<<blocks, 128>>>(d, n, steps, out, lanes); break;
+                    case 6: k<6><<<blocks, 128>>>(d, n, steps, out, lanes); break;
                 }
                 cudaEventRecord(e1); cudaEventSynchronize(e1);
             }
