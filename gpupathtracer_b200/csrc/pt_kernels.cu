@@ -64,7 +64,8 @@ __device__ __forceinline__ unsigned spread3(unsigned v) {      // 10 bits -> eve
     v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
-__global__ void k_ray_bin(SceneDev s, const float4* __restrict__ rays, int n, int bits, unsigned* counts, unsigned* ray_bin) {
+__global__ void k_ray_bin(SceneDev s, const float4* __restrict__ rays, int n, int bits, int dbits /* > 0: octahedral direction cells of 2^dbits per axis
+                          instead of the octant; < 0: the same, direction-major */, unsigned* counts, unsigned* ray_bin) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const float4* q = s.pairs[0].q;
@@ -84,6 +85,19 @@ __global__ void k_ray_bin(SceneDev s, const float4* __restrict__ rays, int n, in
     unsigned morton = spread3(c[0]) | (spread3(c[1]) << 1) | (spread3(c[2]) << 2);
     unsigned oct = (rd.x < 0.0f ? 1u : 0u) | (rd.y < 0.0f ? 2u : 0u) | (rd.z < 0.0f ? 4u : 0u);
     unsigned bin = (morton << 3) | oct;
+    if (dbits != 0) {
+        // experiment (PT_RAY_ORDER_DIR_BITS): octahedral map of the direction, 2^|dbits| cells per axis
+        const int db = dbits < 0 ? -dbits : dbits;
+        const float l1 = fabsf(rd.x) + fabsf(rd.y) + fabsf(rd.z);
+        float u = l1 > 0.0f ? rd.x / l1 : 0.0f, v = l1 > 0.0f ? rd.y / l1 : 0.0f;
+        if (rd.z < 0.0f) { const float uu = (1.0f - fabsf(v)) * (u >= 0.0f ? 1.0f : -1.0f), vv = (1.0f - fabsf(u)) * (v >= 0.0f ? 1.0f : -1.0f); u = uu; v = vv; }
+        const int dc = 1 << db;
+        int iu = (int)((u * 0.5f + 0.5f) * (float)dc), iv = (int)((v * 0.5f + 0.5f) * (float)dc);
+        iu = iu < 0 ? 0 : (iu >= dc ? dc - 1 : iu); iv = iv < 0 ? 0 : (iv >= dc ? dc - 1 : iv);
+        unsigned dkey = 0;                                       // the two cell indices interleaved: 2 * db bits
+        for (int b = 0; b < db; b++) dkey |= (((unsigned)iu >> b) & 1u) << (2 * b) | (((unsigned)iv >> b) & 1u) << (2 * b + 1);
+        bin = dbits > 0 ? (morton << (2 * db)) | dkey : (dkey << (3 * bits)) | morton;
+    }
     ray_bin[i] = bin;
     atomicAdd(counts + bin, 1u);
 }
@@ -152,12 +166,19 @@ int launch_ray_order(const SceneDev& s, const float4* rays, long long n, unsigne
     if (per_bin < 1) per_bin = 1;
     while (bits < max_bits && (n >> (3 * (bits + 1) + 3)) >= per_bin) bits++;
     int n_bins = 1 << (3 * bits + 3);
+    int dbits = 0;
+    if (const char* e = getenv("PT_RAY_ORDER_DIR_BITS")) dbits = atoi(e);
+    if (dbits != 0) {
+        // same number of bins, split differently between origin cells and direction cells
+        const int total = 3 * bits + 3, db = dbits < 0 ? -dbits : dbits;
+        if (2 * db + 3 <= total) { bits = (total - 2 * db) / 3; n_bins = 1 << (3 * bits + 2 * db); } else dbits = 0;
+    }
     if (n_bins < 1024) n_bins = 1024;
     const int tiles = n_bins / 1024;
     unsigned* tile_sums = bins + n_bins;
     cudaMemsetAsync(bins, 0, sizeof(unsigned) * n_bins, st);
     const int blocks = (int)((n + 255) / 256);
-    k_ray_bin<<<blocks, 256, 0, st>>>(s, rays, (int)n, bits, bins, ray_bin);
+    k_ray_bin<<<blocks, 256, 0, st>>>(s, rays, (int)n, bits, dbits, bins, ray_bin);
     k_ray_bin_tile_sums<<<tiles, 1024, 0, st>>>(bins, tile_sums);
     k_ray_bin_scan<<<tiles, 1024, 0, st>>>(bins, tile_sums);
     k_ray_bin_scatter<<<blocks, 256, 0, st>>>(ray_bin, (int)n, bins, perm);
