@@ -32,6 +32,9 @@ namespace pt {
 
 #define PT_STREAM_THREADS 256
 #define PT_SHADE_THREADS 128
+#ifndef PT_SHADE_MIN_BLOCKS
+#define PT_SHADE_MIN_BLOCKS 6        // register cap of k_shade: 85 (80 used)
+#endif
 #define PT_RAY_ORDER_MAX_BITS 6      // 64^3 cells x 8 octants = 2097152 bins = 2048 scan tiles
 #define PT_RAY_ORDER_PER_BIN 64
 
@@ -279,7 +282,7 @@ static void launch_extend(const FrameParams& p, int b, int qi, const LaunchDims&
 
 // ------------------------------------------------------------------ shade
 template <int MODEL, bool SUN>
-__global__ void __launch_bounds__(PT_SHADE_THREADS, 6)
+__global__ void __launch_bounds__(PT_SHADE_THREADS, PT_SHADE_MIN_BLOCKS)
 k_shade(FrameParams p, int bounce, int qi) {
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
