@@ -152,7 +152,7 @@ void pt_destroy(pt_context* c) {
     pt_comm_release(c);
     cudaSetDevice(c->cfg.device);
     cudaStreamSynchronize(c->stream);
-    c->d_wide.release(); c->d_wide_tris.release(); c->d_ser_nodes.release(); c->d_ser_refs.release();
+    c->d_wide.release(); c->d_wide_tris.release(); c->d_ser_nodes.release(); c->d_ser_refs.release(); c->d_build_ws.release();
     c->d_tris.release(); c->d_pairs.release(); c->d_leaf.release(); c->d_mats.release(); c->d_texrec.release();
     for (float4* t : c->d_texels) cudaFree(t);
     c->d_lights.release(); c->d_env.release(); c->d_rng.release(); c->d_accum_own.release();
@@ -599,10 +599,12 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
     CK(c->d_ser_refs.alloc((size_t)m));
     CK(c->d_pairs.alloc((size_t)(m - 1)));
     CK(c->d_leaf.alloc((size_t)m));
-    float kernel_ms = 0.0f; int depth = 0;
+    float kernel_ms = 0.0f; int depth = 0, leaves = (int)m;      // the SAH builder makes leaves of several triangles: fewer leaves than references
     const RefSet* rs = split_grid > 0 ? &refset : nullptr;
+    // scratch kept in the context: a rebuild per frame pays for kernels, not for ~40 cudaMalloc / cudaFree (if it cannot be had, the builder allocates)
+    if (c->d_build_ws.alloc(build_lbvh_workspace_bytes(m)) != cudaSuccess) { c->d_build_ws.release(); cudaGetLastError(); }
     int launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
-                                     c->stream, &kernel_ms, ploc_radius, rs);
+                                     c->stream, &kernel_ms, ploc_radius, rs, &leaves, c->d_build_ws.p, c->d_build_ws.n);
     if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
     c->counters.kernel_launches += launches;
     kernel_ms += split_ms;
@@ -612,7 +614,7 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
         fail(PT_OK, "pt_build_bvh_device_%s tree depth %d exceeds the traversal stack (%d); Morton hierarchy used instead", ploc_radius > 0 ? "ploc: PLOC" : "sah: SAH", depth, PT_MAX_TREE_DEPTH);
         float ms2 = 0.0f;
         launches = build_lbvh_device(c->d_tris.p, (int)n, c->d_ser_nodes.p, c->d_ser_refs.p, c->d_pairs.p, c->d_leaf.p, &depth,
-                                     c->stream, &ms2, 0, rs);
+                                     c->stream, &ms2, 0, rs, &leaves, c->d_build_ws.p, c->d_build_ws.n);
         if (launches < 0) return fail(PT_ERR_CUDA, "pt_build_bvh_device: %s", cudaGetErrorString((cudaError_t)(-launches)));
         c->counters.kernel_launches += launches;
         kernel_ms += ms2;
@@ -621,18 +623,19 @@ static int build_bvh_on_device(pt_context* c, pt_bvh_stats* stats, int ploc_radi
         c->d_pairs.release(); c->d_leaf.release();
         return fail(PT_ERR_LIMIT, "pt_build_bvh_device: tree depth %d exceeds the traversal stack (%d); use pt_build_bvh", depth, PT_MAX_TREE_DEPTH);
     }
+    if (c->d_build_ws.n > ((size_t)512 << 20)) c->d_build_ws.release();      // big one-off builds do not keep gigabytes of scratch
     c->n_leaf = (int)m;
     c->top_pairs = 0;                                             // Karras order: the top levels are not contiguous
     c->h_bvh = HostBvh();
-    c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = (int)m;
-    c->host_bvh_stale = true; c->ser_nodes = 2 * m - 1; c->ser_refs = m;
+    c->h_bvh.max_depth = depth; c->h_bvh.n_leaves = leaves;
+    c->host_bvh_stale = true; c->ser_nodes = 2 * (int64_t)leaves - 1; c->ser_refs = m;
     if (c->cfg.bvh_layout != PT_BVH_REFERENCE) {                 // the wide collapse runs on the host
         int rc = pt_ensure_host_bvh(c);
         if (rc != PT_OK) return rc;
         if ((rc = upload_wide(c)) != PT_OK) return rc;
     }
     if (stats) {
-        stats->n_nodes = (int)(2 * m - 1); stats->n_refs = (int)m; stats->n_leaves = (int)m; stats->max_depth = depth;
+        stats->n_nodes = 2 * leaves - 1; stats->n_refs = (int)m; stats->n_leaves = leaves; stats->max_depth = depth;
         stats->sah_cost = c->host_bvh_stale ? 0.0f : c->h_bvh.sah_cost;     // known once the tree has been read back
         stats->build_ms = kernel_ms;        // CUDA-event time of the build kernels (the tree is usable at that point)
         stats->total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();

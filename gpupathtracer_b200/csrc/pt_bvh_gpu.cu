@@ -375,11 +375,14 @@ __device__ __forceinline__ float box_area(float4 lo, float4 hi) {
 __global__ void k_emit(const int* __restrict__ vals, int n, const int2* __restrict__ children, const float4* __restrict__ leaf_lo,
                        const float4* __restrict__ leaf_hi, const float4* __restrict__ inner_lo, const float4* __restrict__ inner_hi,
                        float4* nodes /* 2 float4 per node */, int* refs, const float4* __restrict__ tris, BvhPair* pairs, LeafTri* leaf,
-                       const int* __restrict__ remap /* optional: inner node id -> position */, const int* __restrict__ ref_tri) {
+                       const int* __restrict__ remap /* optional: inner node id -> position */, const int* __restrict__ ref_tri,
+                       const unsigned char* __restrict__ leaf_end = nullptr /* optional: 1 where a position ends its leaf (null: everywhere) */,
+                       const int* __restrict__ live = nullptr /* optional: parent of every inner id, < -1 for ids that were never used */) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int tri_of_leaf = ref_tri ? ref_tri[vals[i]] : vals[i];
-    refs[i] = -tri_of_leaf;
+    const bool ends = leaf_end ? leaf_end[i] != 0 : true;
+    refs[i] = ends ? -tri_of_leaf : tri_of_leaf;
     if (leaf) {
         // what upload_leaf_stream does on the host: intersection record of the leaf's triangle. The stream marks the end of a
         // leaf with ~index, which triangle 0 can carry too -- unlike the reference list's -0 == 0 (BVH.cpp:2117), whose
@@ -389,10 +392,11 @@ __global__ void k_emit(const int* __restrict__ vals, int n, const int2* __restri
         const float4* t = tris + 5 * (size_t)tri;
         float4 t0 = t[0], t1 = t[1], t2 = t[2];
         leaf[i].r[0] = t0; leaf[i].r[1] = t1;
-        leaf[i].r[2] = make_float4(t2.x, __int_as_float(~tri), 0.0f, 0.0f);
+        leaf[i].r[2] = make_float4(t2.x, __int_as_float(ends ? ~tri : tri), 0.0f, 0.0f);
         leaf[i].r[3] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
     if (i >= n - 1) return;
+    if (live && live[i] < -1) return;
     int2 c = children[i];
     float4 lo0 = c.x < 0 ? leaf_lo[~c.x] : inner_lo[c.x], hi0 = c.x < 0 ? leaf_hi[~c.x] : inner_hi[c.x];
     float4 lo1 = c.y < 0 ? leaf_lo[~c.y] : inner_lo[c.y], hi1 = c.y < 0 ? leaf_hi[~c.y] : inner_hi[c.y];
@@ -443,8 +447,12 @@ __global__ void k_depth(const int* __restrict__ parent_inner, const int* __restr
 // are partitioned into the other index buffer; subtrees of <= SAH_SMALL primitives are finished by ONE thread each with an exact
 // sweep. One primitive per leaf, as the other device builders; inner ids are handed out by an atomic counter (root = 0) and made
 // depth-first by k_ploc_relabel, so the emitted tree does not depend on the order atomics happened to land in.
+#ifndef SAH_BINS
 #define SAH_BINS 16
-#define SAH_SMALL 16
+#endif
+#ifndef SAH_SMALL
+#define SAH_SMALL 16              // <= 32: one lane per primitive in k_sah_small
+#endif
 struct SahNode { int begin, end; };                            // position range of an inner node in the index buffer
 struct SahSplit { int axis, plane, nl; int left, right; };     // axis < 0: median by position; children: inner id, or ~leaf position
 
@@ -547,11 +555,17 @@ __global__ void k_sah_box_init(unsigned* box, size_t count) {
 // children of node `nd` after a split that puts nl primitives on the left: ids, ranges, boxes, parents; appended to the next lists
 __device__ void sah_make_children(int nd, int begin, int end, int nl, const float llo[3], const float lhi[3], const float rlo[3], const float rhi[3],
                                   SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf,
-                                  int* subtree, int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, unsigned* cb, int& left, int& right) {
+                                  int* subtree, int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, unsigned* cb,
+                                  float4* leaf_lo, float4* leaf_hi, unsigned char* leaf_end, int& left, int& right) {
     const int cnts[2] = {nl, end - begin - nl}, begins[2] = {begin, begin + nl};
     int link[2];
     for (int k = 0; k < 2; k++) {
-        if (cnts[k] == 1) { link[k] = ~begins[k]; parent_leaf[begins[k]] = nd; continue; }
+        if (cnts[k] == 1) {
+            link[k] = ~begins[k]; parent_leaf[begins[k]] = nd; leaf_end[begins[k]] = 1;
+            const float* lo = k ? rlo : llo; const float* hi = k ? rhi : lhi;
+            leaf_lo[begins[k]] = make_float4(lo[0], lo[1], lo[2], 0.0f); leaf_hi[begins[k]] = make_float4(hi[0], hi[1], hi[2], 0.0f);
+            continue;
+        }
         const int id = atomicAdd(alloc, 1);
         link[k] = id;
         nodes[id].begin = begins[k]; nodes[id].end = begins[k] + cnts[k];
@@ -562,8 +576,12 @@ __device__ void sah_make_children(int nd, int begin, int end, int nl, const floa
         if (cnts[k] > SAH_SMALL) { const int s = atomicAdd(&next_lists[0], 1); next_large[s] = id; slot_of[id] = s; }
         else { const int s = atomicAdd(&next_lists[1], 1); next_small[s] = id; slot_of[id] = -1; }
     }
-    children[nd] = make_int2(link[0], link[1]);
     left = link[0]; right = link[1];
+    // the child with the larger surface goes first, as in the reference's serialised form (BVH.cpp:2240-2247): k_emit orders the pair
+    // that way whatever stands here, but the depth-first relabel follows THIS order, and the host builder's layout has the larger
+    // child's subtree right behind its parent
+    if (half_area(rlo, rhi) > half_area(llo, lhi)) { const int t = link[0]; link[0] = link[1]; link[1] = t; }
+    children[nd] = make_int2(link[0], link[1]);
 }
 
 // one WARP per large node: the 3 x (SAH_BINS - 1) planes are spread over the lanes, each summing its two sides from the node's bins
@@ -581,7 +599,8 @@ __device__ __forceinline__ void sah_side(const unsigned* c, const unsigned* x, i
 __global__ void __launch_bounds__(32 * SAH_SPLIT_WARPS)
 k_sah_split(const int* __restrict__ large, int n_large, const unsigned* __restrict__ cnt, const unsigned* __restrict__ box,
             SahNode* nodes, float4* inner_lo, float4* inner_hi, int2* children, int* parent_inner, int* parent_leaf, int* subtree,
-            int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, SahSplit* splits, unsigned* part_cnt /* 2 per slot */, unsigned* cb) {
+            int* slot_of, int* next_lists, int* next_large, int* next_small, int* alloc, SahSplit* splits, unsigned* part_cnt /* 2 per slot */, unsigned* cb,
+            float4* leaf_lo, float4* leaf_hi, unsigned char* leaf_end) {
     __shared__ unsigned s_cnt[SAH_SPLIT_WARPS][3 * SAH_BINS], s_box[SAH_SPLIT_WARPS][3 * SAH_BINS * 6];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int slot = blockIdx.x * SAH_SPLIT_WARPS + w;
@@ -622,7 +641,7 @@ k_sah_split(const int* __restrict__ large, int n_large, const unsigned* __restri
         bl[0] = br[0] = a.x; bl[1] = br[1] = a.y; bl[2] = br[2] = a.z; bl[3] = br[3] = b.x; bl[4] = br[4] = b.y; bl[5] = br[5] = b.z;
     }
     sah_make_children(nd, begin, end, sp.nl, bl, bl + 3, br, br + 3, nodes, inner_lo, inner_hi, children, parent_inner, parent_leaf, subtree, slot_of,
-                      next_lists, next_large, next_small, alloc, cb, sp.left, sp.right);
+                      next_lists, next_large, next_small, alloc, cb, leaf_lo, leaf_hi, leaf_end, sp.left, sp.right);
     splits[slot] = sp;
     part_cnt[2 * slot] = 0u; part_cnt[2 * slot + 1] = 0u;
 }
@@ -672,14 +691,21 @@ k_sah_partition(const int* __restrict__ idx, const int* __restrict__ node_of, in
 }
 
 // one WARP finishes the whole subtree of a node with <= SAH_SMALL primitives: exact SAH over every centroid plane of every axis
-// (3c candidates, up to two per lane, each an O(c) pass over the node's primitives in shared memory), stable partition by ballot
+// (3c candidates, up to two per lane, each an O(c) pass over the node's primitives in shared memory), stable partition by ballot.
+// This is also where LEAVES of several triangles are made, by the reference's rule (AdjustSAH + the leaf test, BVH.cpp:2123-2131, as
+// pt_bvh_build.cpp applies it): a node becomes a leaf unless  Ct + Ci * (A_l n_l + A_r n_r) / A  <  Ci * n  -- triangles that share a
+// box (the two halves of a quad) stay together instead of hanging under an inner node of the very same box.
 #define SAH_SMALL_WARPS 4
+#define SAH_CT 1.23f
+#define SAH_CI 5.33f
+#define SAH_DEAD (-2)             // parent_inner of an inner id that was handed out but not used
 __global__ void __launch_bounds__(32 * SAH_SMALL_WARPS)
 k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ idx, const SahNode* __restrict__ nodes_in,
             const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, float4* inner_lo, float4* inner_hi, int2* children,
-            int* parent_inner, int* parent_leaf, int* subtree, int* alloc, int* idx_out, int* node_out) {
+            int* parent_inner, int* parent_leaf, int* alloc, int* idx_out, int* node_out, float4* leaf_lo, float4* leaf_hi,
+            unsigned char* leaf_end, int multi_leaf) {
     __shared__ float s_lo[SAH_SMALL_WARPS][SAH_SMALL][3], s_hi[SAH_SMALL_WARPS][SAH_SMALL][3];
-    __shared__ int s_id[SAH_SMALL_WARPS][SAH_SMALL], s_stack[SAH_SMALL_WARPS][SAH_SMALL][3];
+    __shared__ int s_id[SAH_SMALL_WARPS][SAH_SMALL], s_stack[SAH_SMALL_WARPS][SAH_SMALL][4];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int t = blockIdx.x * SAH_SMALL_WARPS + w;
     if (t >= n_small) return;                                     // whole warps leave
@@ -692,15 +718,25 @@ k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ 
         const float4 a = prim_lo[prim], b = prim_hi[prim];
         ids[lane] = prim; lo[lane][0] = a.x; lo[lane][1] = a.y; lo[lane][2] = a.z; hi[lane][0] = b.x; hi[lane][1] = b.y; hi[lane][2] = b.z;
     }
-    int next_id = 0;                                              // the subtree has cnt0 - 1 inner nodes; `root` is one of them
+    int next_id = 0;                                              // the subtree has at most cnt0 - 1 inner nodes; `root` is one of them
     if (cnt0 > 2) { if (lane == 0) next_id = atomicAdd(alloc, cnt0 - 2); next_id = __shfl_sync(full, next_id, 0); }
-    if (lane == 0) { s_stack[w][0][0] = root; s_stack[w][0][1] = 0; s_stack[w][0][2] = cnt0; }
+    // stack of open nodes: (parent id, side of the parent's child pair, first, count); parent -1 = the subtree's root, whose id exists
+    if (lane == 0) { s_stack[w][0][0] = -1; s_stack[w][0][1] = 0; s_stack[w][0][2] = 0; s_stack[w][0][3] = cnt0; }
     int sp = 1;
     __syncwarp();
     while (sp > 0) {
         sp--;
-        const int nd = s_stack[w][sp][0], f = s_stack[w][sp][1], c = s_stack[w][sp][2];
+        const int par = s_stack[w][sp][0], side = s_stack[w][sp][1], f = s_stack[w][sp][2], c = s_stack[w][sp][3];
         __syncwarp();
+        const bool mine = lane < c;
+        const int i = f + (mine ? lane : 0);
+        // the node's own box
+        float nlo[3], nhi[3];
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            nlo[q] = ord2f(__reduce_min_sync(full, mine ? f2ord(lo[i][q]) : 0xffffffffu));
+            nhi[q] = ord2f(__reduce_max_sync(full, mine ? f2ord(hi[i][q]) : 0u));
+        }
         float best = 3.4e38f; int bc = 0x7fffffff;
         for (int cand = lane; cand < 3 * c; cand += 32) {
             // plane at primitive j's centroid: left = centroids below it (ties by slot), j itself goes right
@@ -708,11 +744,11 @@ k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ 
             const float cj = 0.5f * (lo[j][ax] + hi[j][ax]);
             float llo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, lhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f}, rlo[3] = {3.4e38f, 3.4e38f, 3.4e38f}, rhi[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
             int nl = 0;
-            for (int i = f; i < f + c; i++) {
-                const float ci = 0.5f * (lo[i][ax] + hi[i][ax]);
-                const bool left = ci < cj || (ci == cj && i < j);
-                if (left) { nl++; for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], lo[i][q]); lhi[q] = fmaxf(lhi[q], hi[i][q]); } }
-                else for (int q = 0; q < 3; q++) { rlo[q] = fminf(rlo[q], lo[i][q]); rhi[q] = fmaxf(rhi[q], hi[i][q]); }
+            for (int k = f; k < f + c; k++) {
+                const float ck = 0.5f * (lo[k][ax] + hi[k][ax]);
+                const bool left = ck < cj || (ck == cj && k < j);
+                if (left) { nl++; for (int q = 0; q < 3; q++) { llo[q] = fminf(llo[q], lo[k][q]); lhi[q] = fmaxf(lhi[q], hi[k][q]); } }
+                else for (int q = 0; q < 3; q++) { rlo[q] = fminf(rlo[q], lo[k][q]); rhi[q] = fmaxf(rhi[q], hi[k][q]); }
             }
             if (nl == 0) continue;
             const float cost = half_area(llo, lhi) * (float)nl + half_area(rlo, rhi) * (float)(c - nl);
@@ -723,12 +759,31 @@ k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ 
             const float ob = __shfl_xor_sync(full, best, off); const int oc = __shfl_xor_sync(full, bc, off);
             if (ob < best || (ob == best && oc < bc)) { best = ob; bc = oc; }
         }
-        // there always is a plane for c >= 2 (every centroid but an axis' smallest has somebody on its left) unless boxes hold NaN: halve then
+        // there always is a plane for c >= 2 (every centroid but an axis' smallest has somebody on its left) unless boxes hold NaN
         const bool have = best < 3.4e38f;
+        const float node_area = half_area(nlo, nhi);
+        const bool whole_tree_root = par < 0 && root == 0;       // inner node 0 must stay an inner node (k_emit: nodes[0])
+        const bool as_leaf = !whole_tree_root && (!have || (multi_leaf && (!(node_area > 0.0f) || !(SAH_CT + SAH_CI * best / node_area < SAH_CI * (float)c))));
+        if (as_leaf) {
+            if (lane == 0) {
+                const int first = rb + f;
+                if (par < 0) {                                    // the subtree's root: its parent (a binned node) already links to it as an inner node
+                    const int p = parent_inner[root];
+                    const int2 ch = children[p];
+                    reinterpret_cast<int*>(&children[p])[ch.y == root ? 1 : 0] = ~first;
+                    parent_leaf[first] = p; parent_inner[root] = SAH_DEAD;
+                } else { reinterpret_cast<int*>(&children[par])[side] = ~first; parent_leaf[first] = par; }
+                leaf_lo[first] = make_float4(nlo[0], nlo[1], nlo[2], 0.0f); leaf_hi[first] = make_float4(nhi[0], nhi[1], nhi[2], 0.0f);
+                leaf_end[first + c - 1] = 1;
+                // the reference list marks the end of a leaf by the sign of its last entry, which triangle 0 cannot carry
+                if (c > 1 && ids[f + c - 1] == 0) { ids[f + c - 1] = ids[f + c - 2]; ids[f + c - 2] = 0; }
+            }
+            __syncwarp();
+            continue;
+        }
+        const int nd = par < 0 ? root : next_id++;
         const int ax = have ? bc / c : 0, bj = have ? f + bc % c : f;
         const float pivot = 0.5f * (lo[bj][ax] + hi[bj][ax]);
-        const bool mine = lane < c;
-        const int i = f + (mine ? lane : 0);
         const float ci = 0.5f * (lo[i][ax] + hi[i][ax]);
         const bool left = mine && (have ? (ci < pivot || (ci == pivot && i < bj)) : lane < c / 2);
         const unsigned bl = __ballot_sync(full, left), br = __ballot_sync(full, mine && !left);
@@ -746,32 +801,53 @@ k_sah_small(const int* __restrict__ small, int n_small, const int* __restrict__ 
         __syncwarp();
         if (mine) { ids[at] = my_id; for (int q = 0; q < 3; q++) { lo[at][q] = ml[q]; hi[at][q] = mh[q]; } }
         const int cnts[2] = {nl, c - nl}, firsts[2] = {f, f + nl};
-        int child_id[2];
-        for (int k = 0; k < 2; k++) child_id[k] = cnts[k] > 1 ? next_id++ : -1;
+        // the child with the larger surface takes side 0 (see sah_make_children)
+        const int swap = half_area(cr, crh) > half_area(cl, chh) ? 1 : 0;
         if (lane == 0) {
-            int link[2], push = sp;
-            for (int k = 0; k < 2; k++) {
-                if (cnts[k] == 1) { link[k] = ~(rb + firsts[k]); parent_leaf[rb + firsts[k]] = nd; continue; }
-                const int id = child_id[k];
-                link[k] = id;
-                inner_lo[id] = k ? make_float4(cr[0], cr[1], cr[2], 0.0f) : make_float4(cl[0], cl[1], cl[2], 0.0f);
-                inner_hi[id] = k ? make_float4(crh[0], crh[1], crh[2], 0.0f) : make_float4(chh[0], chh[1], chh[2], 0.0f);
-                parent_inner[id] = nd; subtree[id] = cnts[k] - 1;
-                s_stack[w][push][0] = id; s_stack[w][push][1] = firsts[k]; s_stack[w][push][2] = cnts[k]; push++;
+            if (par >= 0) {
+                reinterpret_cast<int*>(&children[par])[side] = nd; parent_inner[nd] = par;
+                inner_lo[nd] = make_float4(nlo[0], nlo[1], nlo[2], 0.0f); inner_hi[nd] = make_float4(nhi[0], nhi[1], nhi[2], 0.0f);
             }
-            children[nd] = make_int2(link[0], link[1]);
+            int push = sp;
+            for (int k = 0; k < 2; k++) {
+                const int sd = k ^ swap;
+                if (cnts[k] == 1) {
+                    const int pos = rb + firsts[k];
+                    reinterpret_cast<int*>(&children[nd])[sd] = ~pos; parent_leaf[pos] = nd; leaf_end[pos] = 1;
+                    leaf_lo[pos] = k ? make_float4(cr[0], cr[1], cr[2], 0.0f) : make_float4(cl[0], cl[1], cl[2], 0.0f);
+                    leaf_hi[pos] = k ? make_float4(crh[0], crh[1], crh[2], 0.0f) : make_float4(chh[0], chh[1], chh[2], 0.0f);
+                    continue;
+                }
+                s_stack[w][push][0] = nd; s_stack[w][push][1] = sd; s_stack[w][push][2] = firsts[k]; s_stack[w][push][3] = cnts[k]; push++;
+            }
         }
         sp += (cnts[0] > 1 ? 1 : 0) + (cnts[1] > 1 ? 1 : 0);
         __syncwarp();
     }
     if (lane < cnt0) { idx_out[rb + lane] = ids[lane]; node_out[rb + lane] = -1; }
 }
-__global__ void k_sah_leaves(const int* __restrict__ idx, int n, const float4* __restrict__ prim_lo, const float4* __restrict__ prim_hi, int* vals,
-                             float4* leaf_lo, float4* leaf_hi) {
+// leaves below every inner node (subtree[] starts at -1: leaves - 1 = inner nodes of the subtree). Every leaf climbs to the root; lanes
+// of a warp that meet at the same ancestor merge into one climber carrying their sum, so the top of the tree sees one atomic per warp
+__global__ void k_sah_count(const unsigned char* __restrict__ leaf_end, int n, const int* __restrict__ parent_inner, const int* __restrict__ parent_leaf,
+                            int* subtree, int* n_leaves) {
+    const unsigned full = 0xffffffffu;
+    const int l = blockIdx.x * blockDim.x + threadIdx.x, lane = threadIdx.x & 31;
+    const bool first = l < n && (l == 0 || leaf_end[l - 1] != 0);
+    const unsigned m = __ballot_sync(full, first);
+    if (lane == 0 && m) atomicAdd(n_leaves, __popc(m));
+    int cur = first ? parent_leaf[l] : -1, w = first ? 1 : 0;
+    while (__any_sync(full, cur >= 0)) {
+        const unsigned peers = __match_any_sync(full, cur);
+        const int total = __reduce_add_sync(peers, w);
+        if (cur >= 0) {
+            if (lane == __ffs(peers) - 1) { atomicAdd(&subtree[cur], total); w = total; cur = parent_inner[cur]; }
+            else { cur = -1; w = 0; }
+        }
+    }
+}
+__global__ void k_sah_leaves(const int* __restrict__ idx, int n, int* vals) {
     int l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l >= n) return;
-    const int prim = idx[l];
-    vals[l] = prim; leaf_lo[l] = prim_lo[prim]; leaf_hi[l] = prim_hi[prim];
+    if (l < n) vals[l] = idx[l];
 }
 
 // ---------------------------------------------------------------- triangle pre-splitting (spatial splits for the device builders)
@@ -1015,7 +1091,17 @@ done:
 // Returns the number of kernels launched (> 0) or -(cudaError) on failure; *kernel_ms = device time of the build.
 // ploc_radius > 0: the hierarchy is built by PLOC with that search radius instead of Karras' Morton-bit splits.
 int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
-                      cudaStream_t st, float* kernel_ms, int ploc_radius, const RefSet* refset) {
+                      cudaStream_t st, float* kernel_ms, int ploc_radius, const RefSet* refset, int* n_leaves_out, void* workspace, size_t workspace_bytes) {
+    // scratch comes out of the caller's workspace while it lasts (a rebuild per frame should not pay ~40 cudaMalloc / cudaFree), else from cudaMalloc
+    struct Arena {
+        char* base; size_t cap, off;
+        cudaError_t get(void** p, size_t bytes) {
+            const size_t need = (bytes + 255) & ~(size_t)255;
+            if (base && off + need <= cap) { *p = base + off; off += need; return cudaSuccess; }
+            return cudaMalloc(p, bytes);
+        }
+        void put(void* p) { if (p && !(base && (char*)p >= base && (char*)p < base + cap)) cudaFree(p); }
+    } ws{(char*)workspace, workspace ? workspace_bytes : 0, 0};
     cudaError_t err = cudaSuccess;
     int launches = 0;
     // with a reference set the leaves are its m references (n becomes m below); d_nodes / d_refs / d_pairs / d_leaf are sized by m
@@ -1033,45 +1119,52 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
     int *sah_idx[2] = {nullptr, nullptr}, *sah_node_of[2] = {nullptr, nullptr}, *sah_slot_of = nullptr, *sah_large[2] = {nullptr, nullptr}, *sah_small[2] = {nullptr, nullptr};
     int *sah_lists = nullptr, *sah_alloc = nullptr;
     unsigned *sah_cnt = nullptr, *sah_box = nullptr, *sah_part = nullptr, *sah_cb = nullptr;
+    unsigned char* sah_leaf_end = nullptr;
+    int n_leaves = 0, sah_multi_leaf = 1;
     SahNode* sah_nodes = nullptr; SahSplit* sah_splits = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     const unsigned init_bounds[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     BCK(cudaEventCreate(&e0)); BCK(cudaEventCreate(&e1));
-    BCK(cudaMalloc((void**)&bounds, 6 * sizeof(unsigned)));
-    for (int k = 0; k < 2; k++) { BCK(cudaMalloc((void**)&keys[k], (size_t)n * 4)); BCK(cudaMalloc((void**)&vals[k], (size_t)n * 4)); }
-    BCK(cudaMalloc((void**)&hist, (size_t)256 * n_blocks * 4));
-    BCK(cudaMalloc((void**)&flags, (size_t)n * 4));
-    BCK(cudaMalloc((void**)&parent_inner, (size_t)n * 4)); BCK(cudaMalloc((void**)&parent_leaf, (size_t)n * 4));
-    BCK(cudaMalloc((void**)&children, (size_t)n * sizeof(int2)));
-    BCK(cudaMalloc((void**)&leaf_lo, (size_t)n * 16)); BCK(cudaMalloc((void**)&leaf_hi, (size_t)n * 16));
-    BCK(cudaMalloc((void**)&inner_lo, (size_t)n * 16)); BCK(cudaMalloc((void**)&inner_hi, (size_t)n * 16));
+    BCK(ws.get((void**)&bounds, 6 * sizeof(unsigned)));
+    for (int k = 0; k < 2; k++) { BCK(ws.get((void**)&keys[k], (size_t)n * 4)); BCK(ws.get((void**)&vals[k], (size_t)n * 4)); }
+    BCK(ws.get((void**)&hist, (size_t)256 * n_blocks * 4));
+    BCK(ws.get((void**)&flags, (size_t)n * 4));
+    BCK(ws.get((void**)&parent_inner, (size_t)n * 4)); BCK(ws.get((void**)&parent_leaf, (size_t)n * 4));
+    BCK(ws.get((void**)&children, (size_t)n * sizeof(int2)));
+    BCK(ws.get((void**)&leaf_lo, (size_t)n * 16)); BCK(ws.get((void**)&leaf_hi, (size_t)n * 16));
+    BCK(ws.get((void**)&inner_lo, (size_t)n * 16)); BCK(ws.get((void**)&inner_hi, (size_t)n * 16));
     BCK(cudaMemcpyAsync(bounds, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice, st));
     BCK(cudaMemsetAsync(flags, 0, (size_t)n * 4, st));
-    BCK(cudaMalloc((void**)&d_depth, 4));
+    BCK(ws.get((void**)&d_depth, 4));
     BCK(cudaMemsetAsync(d_depth, 0, 4, st));
     if (ploc_radius > 0) {
         for (int k = 0; k < 2; k++) {
-            BCK(cudaMalloc((void**)&cid[k], (size_t)n * 4)); BCK(cudaMalloc((void**)&clo[k], (size_t)n * 16)); BCK(cudaMalloc((void**)&chi[k], (size_t)n * 16));
+            BCK(ws.get((void**)&cid[k], (size_t)n * 4)); BCK(ws.get((void**)&clo[k], (size_t)n * 16)); BCK(ws.get((void**)&chi[k], (size_t)n * 16));
         }
-        BCK(cudaMalloc((void**)&nn, (size_t)n * 4)); BCK(cudaMalloc((void**)&valid, (size_t)n * 4));
-        BCK(cudaMalloc((void**)&block_counts, (size_t)grid_n * 4));
-        BCK(cudaMalloc((void**)&subtree, (size_t)n * 4)); BCK(cudaMalloc((void**)&remap, (size_t)n * 4));
-        BCK(cudaMalloc((void**)&d_m, 8));
+        BCK(ws.get((void**)&nn, (size_t)n * 4)); BCK(ws.get((void**)&valid, (size_t)n * 4));
+        BCK(ws.get((void**)&block_counts, (size_t)grid_n * 4));
+        BCK(ws.get((void**)&subtree, (size_t)n * 4)); BCK(ws.get((void**)&remap, (size_t)n * 4));
+        BCK(ws.get((void**)&d_m, 8));
         BCK(cudaMemsetAsync(d_m, 0, 8, st));                     // [0] = cluster count of the round, [1] = inner nodes created
     }
     if (ploc_radius < 0) {
         // ---- top-down binned SAH (kernels above). Level loop on the host: one 8-byte read-back per level sizes the launches.
         const int max_slots = n / (SAH_SMALL + 1) + 2;
-        BCK(cudaMalloc((void**)&sah_prim_lo, (size_t)n * 16)); BCK(cudaMalloc((void**)&sah_prim_hi, (size_t)n * 16));
-        for (int k = 0; k < 2; k++) { BCK(cudaMalloc((void**)&sah_idx[k], (size_t)n * 4)); BCK(cudaMalloc((void**)&sah_node_of[k], (size_t)n * 4)); }
-        BCK(cudaMalloc((void**)&sah_nodes, (size_t)n * sizeof(SahNode))); BCK(cudaMalloc((void**)&sah_slot_of, (size_t)n * 4));
-        BCK(cudaMalloc((void**)&subtree, (size_t)n * 4)); BCK(cudaMalloc((void**)&remap, (size_t)n * 4));
-        for (int k = 0; k < 2; k++) { BCK(cudaMalloc((void**)&sah_large[k], (size_t)max_slots * 4)); BCK(cudaMalloc((void**)&sah_small[k], (size_t)(n / 2 + 2) * 4)); }
-        BCK(cudaMalloc((void**)&sah_lists, 4 * 4)); BCK(cudaMalloc((void**)&sah_alloc, 4));
-        BCK(cudaMalloc((void**)&sah_cb, (size_t)n * 6 * 4));
+        BCK(ws.get((void**)&sah_prim_lo, (size_t)n * 16)); BCK(ws.get((void**)&sah_prim_hi, (size_t)n * 16));
+        for (int k = 0; k < 2; k++) { BCK(ws.get((void**)&sah_idx[k], (size_t)n * 4)); BCK(ws.get((void**)&sah_node_of[k], (size_t)n * 4)); }
+        BCK(ws.get((void**)&sah_nodes, (size_t)n * sizeof(SahNode))); BCK(ws.get((void**)&sah_slot_of, (size_t)n * 4));
+        BCK(ws.get((void**)&subtree, (size_t)n * 4)); BCK(ws.get((void**)&remap, (size_t)n * 4));
+        for (int k = 0; k < 2; k++) { BCK(ws.get((void**)&sah_large[k], (size_t)max_slots * 4)); BCK(ws.get((void**)&sah_small[k], (size_t)(n / 2 + 2) * 4)); }
+        BCK(ws.get((void**)&sah_lists, 4 * 4)); BCK(ws.get((void**)&sah_alloc, 4));
+        BCK(ws.get((void**)&sah_cb, (size_t)n * 6 * 4));
+        BCK(ws.get((void**)&sah_leaf_end, (size_t)n));
+        BCK(cudaMemsetAsync(sah_leaf_end, 0, (size_t)n, st));
+        BCK(cudaMemsetAsync(parent_inner, 0xfe, (size_t)n * 4, st));       // every inner id starts out unused (< -1)
+        BCK(cudaMemsetAsync(parent_leaf, 0xff, (size_t)n * 4, st));        // -1: only the first position of a leaf gets a parent
+        if (const char* e = getenv("PT_SAH_SINGLE_LEAF")) sah_multi_leaf = atoi(e) ? 0 : 1;
         BCK(cudaMemcpyAsync(sah_cb, init_bounds, sizeof(init_bounds), cudaMemcpyHostToDevice, st));
-        BCK(cudaMalloc((void**)&sah_cnt, (size_t)max_slots * 3 * SAH_BINS * 4)); BCK(cudaMalloc((void**)&sah_box, (size_t)max_slots * 3 * SAH_BINS * 6 * 4));
-        BCK(cudaMalloc((void**)&sah_splits, (size_t)max_slots * sizeof(SahSplit))); BCK(cudaMalloc((void**)&sah_part, (size_t)max_slots * 2 * 4));
+        BCK(ws.get((void**)&sah_cnt, (size_t)max_slots * 3 * SAH_BINS * 4)); BCK(ws.get((void**)&sah_box, (size_t)max_slots * 3 * SAH_BINS * 6 * 4));
+        BCK(ws.get((void**)&sah_splits, (size_t)max_slots * sizeof(SahSplit))); BCK(ws.get((void**)&sah_part, (size_t)max_slots * 2 * 4));
         const int one = 1;
         BCK(cudaMemcpyAsync(sah_alloc, &one, 4, cudaMemcpyHostToDevice, st));             // inner id 0 is the root
     }
@@ -1096,18 +1189,23 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
                 k_sah_box_init<<<(unsigned)((bins * 6 + BVH_THREADS - 1) / BVH_THREADS), BVH_THREADS, 0, st>>>(sah_box, bins * 6); launches++;
                 k_sah_bin<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_prim_lo, sah_prim_hi, sah_cb, sah_cnt, sah_box); launches++;
                 k_sah_split<<<(counts[0] + SAH_SPLIT_WARPS - 1) / SAH_SPLIT_WARPS, 32 * SAH_SPLIT_WARPS, 0, st>>>(sah_large[lv], counts[0], sah_cnt, sah_box, sah_nodes, inner_lo, inner_hi, children, parent_inner,
-                                                                      parent_leaf, subtree, sah_slot_of, next_lists, sah_large[nx], sah_small[nx], sah_alloc, sah_splits, sah_part, sah_cb); launches++;
+                                                                      parent_leaf, subtree, sah_slot_of, next_lists, sah_large[nx], sah_small[nx], sah_alloc, sah_splits, sah_part, sah_cb, leaf_lo, leaf_hi, sah_leaf_end); launches++;
             }
             // copy-through + partition of the large nodes, then the small subtrees (disjoint positions of the other buffer)
             k_sah_partition<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], sah_node_of[cur], n, sah_slot_of, sah_nodes, sah_splits, sah_prim_lo, sah_prim_hi, sah_cb,
                                                             sah_part, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
             if (counts[1] > 0) {
                 k_sah_small<<<(counts[1] + SAH_SMALL_WARPS - 1) / SAH_SMALL_WARPS, 32 * SAH_SMALL_WARPS, 0, st>>>(sah_small[lv], counts[1], sah_idx[cur], sah_nodes, sah_prim_lo, sah_prim_hi, inner_lo, inner_hi, children,
-                                                                  parent_inner, parent_leaf, subtree, sah_alloc, sah_idx[cur ^ 1], sah_node_of[cur ^ 1]); launches++;
+                                                                  parent_inner, parent_leaf, sah_alloc, sah_idx[cur ^ 1], sah_node_of[cur ^ 1], leaf_lo, leaf_hi, sah_leaf_end,
+                                                                  sah_multi_leaf); launches++;
             }
             cur ^= 1;
         }
-        k_sah_leaves<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], n, sah_prim_lo, sah_prim_hi, vals[0], leaf_lo, leaf_hi); launches++;
+        k_sah_leaves<<<grid_n, BVH_THREADS, 0, st>>>(sah_idx[cur], n, vals[0]); launches++;
+        BCK(cudaMemsetAsync(subtree, 0xff, (size_t)n * 4, st));            // -1 + the leaves below = inner nodes of the subtree
+        BCK(cudaMemsetAsync(sah_lists, 0, 4, st));
+        k_sah_count<<<grid_n, BVH_THREADS, 0, st>>>(sah_leaf_end, n, parent_inner, parent_leaf, subtree, sah_lists); launches++;
+        BCK(cudaMemcpyAsync(&n_leaves, sah_lists, 4, cudaMemcpyDeviceToHost, st));
         k_ploc_relabel<<<grid_n, BVH_THREADS, 0, st>>>(children, parent_inner, subtree, n - 1, remap); launches++;
         goto emit;
     }
@@ -1143,22 +1241,24 @@ int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs,
         k_fit<<<grid_n, BVH_THREADS, 0, st>>>(src, vals[0], n, children, parent_inner, parent_leaf, leaf_lo, leaf_hi, inner_lo, inner_hi, flags); launches++;
     }
 emit:
-    k_emit<<<grid_n, BVH_THREADS, 0, st>>>(vals[0], n, children, leaf_lo, leaf_hi, inner_lo, inner_hi, d_nodes, d_refs, d_tris, d_pairs, d_leaf, ploc_radius != 0 ? remap : nullptr, src.ref_tri); launches++;
+    k_emit<<<grid_n, BVH_THREADS, 0, st>>>(vals[0], n, children, leaf_lo, leaf_hi, inner_lo, inner_hi, d_nodes, d_refs, d_tris, d_pairs, d_leaf, ploc_radius != 0 ? remap : nullptr, src.ref_tri,
+                                            sah_leaf_end, ploc_radius < 0 ? parent_inner : nullptr); launches++;
     k_depth<<<grid_n, BVH_THREADS, 0, st>>>(parent_inner, parent_leaf, n, d_depth); launches++;
     BCK(cudaEventRecord(e1, st));
     if (depth) BCK(cudaMemcpyAsync(depth, d_depth, 4, cudaMemcpyDeviceToHost, st));
     BCK(cudaGetLastError());
     BCK(cudaStreamSynchronize(st));
     if (kernel_ms) BCK(cudaEventElapsedTime(kernel_ms, e0, e1));
+    if (n_leaves_out) *n_leaves_out = ploc_radius < 0 ? n_leaves : n;
 done:
-    cudaFree(bounds); cudaFree(keys[0]); cudaFree(keys[1]); cudaFree(vals[0]); cudaFree(vals[1]); cudaFree(hist); cudaFree(flags);
-    cudaFree(parent_inner); cudaFree(parent_leaf); cudaFree(children); cudaFree(d_depth);
-    cudaFree(leaf_lo); cudaFree(leaf_hi); cudaFree(inner_lo); cudaFree(inner_hi);
-    for (int k = 0; k < 2; k++) { cudaFree(cid[k]); cudaFree(clo[k]); cudaFree(chi[k]); }
-    cudaFree(nn); cudaFree(valid); cudaFree(block_counts); cudaFree(d_m); cudaFree(subtree); cudaFree(remap);
-    cudaFree(sah_prim_lo); cudaFree(sah_prim_hi); cudaFree(sah_slot_of); cudaFree(sah_lists); cudaFree(sah_alloc); cudaFree(sah_cnt); cudaFree(sah_box);
-    cudaFree(sah_part); cudaFree(sah_nodes); cudaFree(sah_splits); cudaFree(sah_cb);
-    for (int k = 0; k < 2; k++) { cudaFree(sah_idx[k]); cudaFree(sah_node_of[k]); cudaFree(sah_large[k]); cudaFree(sah_small[k]); }
+    ws.put(bounds); ws.put(keys[0]); ws.put(keys[1]); ws.put(vals[0]); ws.put(vals[1]); ws.put(hist); ws.put(flags);
+    ws.put(parent_inner); ws.put(parent_leaf); ws.put(children); ws.put(d_depth);
+    ws.put(leaf_lo); ws.put(leaf_hi); ws.put(inner_lo); ws.put(inner_hi);
+    for (int k = 0; k < 2; k++) { ws.put(cid[k]); ws.put(clo[k]); ws.put(chi[k]); }
+    ws.put(nn); ws.put(valid); ws.put(block_counts); ws.put(d_m); ws.put(subtree); ws.put(remap);
+    ws.put(sah_prim_lo); ws.put(sah_prim_hi); ws.put(sah_slot_of); ws.put(sah_lists); ws.put(sah_alloc); ws.put(sah_cnt); ws.put(sah_box);
+    ws.put(sah_part); ws.put(sah_nodes); ws.put(sah_splits); ws.put(sah_cb); ws.put(sah_leaf_end);
+    for (int k = 0; k < 2; k++) { ws.put(sah_idx[k]); ws.put(sah_node_of[k]); ws.put(sah_large[k]); ws.put(sah_small[k]); }
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
     return err == cudaSuccess ? launches : -(int)err;

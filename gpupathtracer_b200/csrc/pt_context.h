@@ -88,6 +88,7 @@ struct pt_context {
     WideBvh h_wide;
     // device builder: serialised tree kept on the device, host mirror fetched on demand
     DevBuf<float4> d_ser_nodes; DevBuf<int> d_ser_refs;
+    DevBuf<unsigned char> d_build_ws;          // scratch of the device builders, kept between rebuilds
     bool host_bvh_stale = false; int64_t ser_nodes = 0, ser_refs = 0;
     float wide_ms = 0.0f;
     DevBuf<MaterialRec> d_mats;

@@ -64,7 +64,10 @@ struct RefSet { int m = 0; int* tri = nullptr; float4* lo = nullptr; float4* hi 
 int presplit_device(const float4* d_tris, int n, int grid, RefSet* out, cudaStream_t st, float* kernel_ms);   // launches, or -(cudaError)
 void free_refset(RefSet* r);
 int build_lbvh_device(const float4* d_tris, int n, float4* d_nodes, int* d_refs, BvhPair* d_pairs, LeafTri* d_leaf, int* depth,
-                      cudaStream_t st, float* kernel_ms, int ploc_radius = 0, const RefSet* refset = nullptr);
+                      cudaStream_t st, float* kernel_ms, int ploc_radius = 0, const RefSet* refset = nullptr, int* n_leaves = nullptr,
+                      void* workspace = nullptr, size_t workspace_bytes = 0);
+// bytes of scratch a build over n leaves takes at most (the workspace argument above; a smaller one is used as far as it goes)
+inline size_t build_lbvh_workspace_bytes(long long n) { return (size_t)n * 352 + ((size_t)4 << 20); }
 
 int launch_primary(const FrameParams& p, const LaunchDims& dims, float4* by_pixel, cudaStream_t st);
 void launch_raygen_probe(const FrameParams& p, long long first, long long n, float4* out3, cudaStream_t st);

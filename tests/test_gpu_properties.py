@@ -109,11 +109,22 @@ def test_device_built_bvh(name, builder):
     st = r.bvh_stats
     nodes, refs = s.nodes, s.refs
     n = s.tris.shape[0]
-    assert nodes.shape[0] == 2 * n - 1 and refs.shape[0] == n and st.n_leaves == n
-    assert np.array_equal(np.sort(np.abs(refs)), np.arange(n))
-    assert (refs <= 0).all()                                     # one triangle per leaf: every entry ends its leaf
-    # boxes: every node's box contains both children's boxes
     d0 = nodes[:, 3].copy().view(np.int32)
+    assert refs.shape[0] == n and np.array_equal(np.sort(np.abs(refs)), np.arange(n))
+    if builder == "sah":
+        # leaves of several triangles where the SAH says so: a leaf per end-of-leaf marker (triangle 0 cannot carry one), every
+        # leaf node points at the first entry of its run, the runs tile the reference list
+        leaves = int((d0[1:] <= 0).sum())
+        assert nodes.shape[0] == 2 * leaves - 1 and st.n_leaves == leaves and leaves <= n
+        starts = np.sort(-d0[1:][d0[1:] <= 0])
+        ends = np.nonzero((refs < 0) | ((refs == 0) & np.isin(np.arange(n) + 1, np.append(starts, n))))[0]
+        assert starts[0] == 0 and np.array_equal(starts[1:], ends[:-1] + 1) and ends[-1] == n - 1
+        if name != "soup":
+            assert leaves < n                                    # quads and coplanar fans stay together
+    else:
+        assert nodes.shape[0] == 2 * n - 1 and st.n_leaves == n
+        assert (refs <= 0).all()                                 # one triangle per leaf: every entry ends its leaf
+    # boxes: every node's box contains both children's boxes
     inner = np.nonzero(d0 > 0)[0]
     for c in (0, 1):
         ch = d0[inner] + c
@@ -387,9 +398,12 @@ def test_device_sah_builder_on_degenerate_input(case):
     r = Renderer().Initialize(64, 64, s, bvh="sah")
     nodes, refs = s.nodes, s.refs
     n = s.tris.shape[0]
-    assert nodes.shape[0] == 2 * n - 1 and refs.shape[0] == n and (refs <= 0).all()
-    assert np.array_equal(np.sort(np.abs(refs)), np.arange(n))
     d0 = nodes[:, 3].copy().view(np.int32)
+    leaves = int((d0[1:] <= 0).sum())
+    assert nodes.shape[0] == 2 * leaves - 1 and refs.shape[0] == n and 2 <= leaves <= n and r.bvh_stats.n_leaves == leaves
+    assert np.array_equal(np.sort(np.abs(refs)), np.arange(n))
+    if case == "copies":
+        assert leaves < n - 400                                  # identical triangles share leaves (up to 16 each)
     inner = np.nonzero(d0 > 0)[0]
     for c in (0, 1):
         ch = d0[inner] + c

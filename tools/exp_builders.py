@@ -14,6 +14,8 @@ cam = bench.make_camera(base, W, H)
 cases = [("host SBVH", "build", None), ("device LBVH", "device", None), ("device PLOC", "ploc", None), ("device SAH", "sah", None)]
 for g in grids:
     cases += [(f"split {g} + PLOC", "split", g), (f"split {g} + LBVH", "split_lbvh", g)]
+if os.environ.get('EXP_ONLY'):
+    cases = [c for c in cases if c[1] in os.environ['EXP_ONLY'].split(',')]
 for label, how, g in cases:
     if g:
         os.environ["PT_SPLIT_GRID"] = str(g)

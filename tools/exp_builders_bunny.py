@@ -9,6 +9,8 @@ cam = bench.make_camera(base, W, H)
 n = W * H
 cases = [("host SBVH", "build", None, None), ("device LBVH", "device", None, None), ("device SAH", "sah", None, None)] + [(f"PLOC r={r}", "ploc", None, r) for r in (16, 32)] + \
         [(f"split {g} + PLOC", "split", g, 16) for g in (32,)] + [(f"split {g} + LBVH", "split_lbvh", g, 16) for g in ()]
+if os.environ.get('EXP_ONLY'):
+    cases = [c for c in cases if c[1] in os.environ['EXP_ONLY'].split(',')]
 for label, how, g, rad in cases:
     if g: os.environ["PT_SPLIT_GRID"] = str(g)
     if rad: os.environ["PT_PLOC_RADIUS"] = str(rad)
