@@ -316,6 +316,17 @@ LAYOUTS = {"reference": 0, "wide": 1, "wide4": 2}
 BUILDERS = {"device": "device", "ploc": "ploc", "sah": "sah", "split": "split", "split_lbvh": "split_lbvh"}
 
 
+def optimize_setting(args, path_tracing):
+    """(iterations, fraction) of the reinsertion pass for this run, or None."""
+    v = getattr(args, "optimize_bvh", "auto")
+    if v == "off" or (v == "auto" and not path_tracing):
+        return None
+    if v == "auto":
+        return 4, 0.1
+    it, fr = v.split(",")
+    return int(it), float(fr)
+
+
 def make_renderer(d, scene, W, H, wl, args, **kw):
     """One context per rank. N > 1: the tree is built ONCE, on rank 0, and reaches the other ranks through the library's
     broadcast (pt_comm_broadcast_bvh); RNG tables are seeded per rank by the library (pt_comm_seed_rng)."""
@@ -326,6 +337,9 @@ def make_renderer(d, scene, W, H, wl, args, **kw):
         how = "none"
     r = Renderer().Initialize(W, H, scene, max_depth=wl["depth"], microfacet_model=wl["model"], device=d.local, bvh=how,
                               bvh_layout=LAYOUTS[args.bvh], **kw)
+    opt = optimize_setting(args, True)
+    if opt and how != "none" and LAYOUTS[args.bvh] == 0:
+        r.OptimizeBVH(*opt)                       # on the rank that built the tree; the others receive the optimised tree below
     if d.world > 1:
         init_comm(r, d.dist)
         if LAYOUTS[args.bvh] == 0:
@@ -536,6 +550,10 @@ def pathtrace_line(args, name, wl, d, scene, r, cam, m):
                    "microfacet": "beckmann" if wl["model"] else "ggx", "lens_radius": float(cam.plane.lens_radius),
                    "bvh": f"{ {'device': 'device LBVH', 'ploc': 'device PLOC', 'sah': 'device top-down SAH', 'split': 'device pre-split + PLOC', 'split_lbvh': 'device pre-split + LBVH'}.get(args.builder, 'own SBVH') } builder, {args.bvh} layout",
                    "bvh_total_ms": float(r.bvh_stats.total_ms), "bvh_sah_cost": float(r.bvh_stats.sah_cost), "bvh_build_ms": float(r.bvh_stats.build_ms),
+                   "bvh_optimized": ({"what": "pt_optimize_bvh: reinsertion pass over the built tree (host), same leaves, same hits",
+                                      "iterations_fraction": list(optimize_setting(args, True)), "sah_cost": float(r.opt_stats.sah_cost),
+                                      "ms": float(r.opt_stats.total_ms), "depth": int(r.opt_stats.max_depth)}
+                                     if getattr(r, "opt_stats", None) is not None else None),
                    "slices": "each frame = 3 pixel-disjoint slices on concurrent streams, shadow(b) || extend(b+1) inside a slice (pt_config.n_slices)",
                    "l2": "per-step working set (path state + queues + accum, ~0.5 GB at 1080p) exceeds the 126 MB L2",
                    "parallelism": (f"samples split over {world} GPUs inside the library (pt_comm_init): BVH built on rank 0 and broadcast, "
@@ -660,6 +678,8 @@ def run_micro(args, name, wl, d, sub=False):
     t0 = time.perf_counter()
     r = Renderer().Initialize(64, 64, scene, max_depth=5, device=local, seed=1, bvh=BUILDERS.get(args.builder, "build"),
                               bvh_layout=LAYOUTS[args.bvh])
+    if optimize_setting(args, False) and LAYOUTS[args.bvh] == 0:
+        r.OptimizeBVH(*optimize_setting(args, False))
     init_s = time.perf_counter() - t0
     d_closest = torch.from_numpy(closest).cuda()
     d_any = torch.from_numpy(anyr).cuda()
@@ -910,6 +930,9 @@ def main():
     ap.add_argument("--no-configs", action="store_true", help="default command only: skip the short runs of the other BASELINE.json configs")
     ap.add_argument("--spp", type=int, default=0, help="path-tracing workloads: render a FIXED total of samples per pixel split over the GPUs "
                     "(64-frame batches per GPU, one reduce per batch) and report time-to-image (BASELINE.json configs[4] as written: --workload 4k --spp 4096)")
+    ap.add_argument("--optimize-bvh", default="auto", metavar="ITERATIONS,FRACTION",
+                    help="reinsertion optimisation of the built tree (pt_optimize_bvh) before rendering: 'auto' = 4,0.1 for the path-tracing "
+                         "workloads (measured +2-3 %% frames), off for primary-ray / random-ray batches (measured none); 'off'; or e.g. 8,0.3")
     ap.add_argument("--builder", default="host", choices=["host", "device", "ploc", "sah", "split", "split_lbvh"],
                     help="host: own multi-threaded SBVH builder (default); device: Morton LBVH built by CUDA kernels; ploc: the same with a "
                          "PLOC hierarchy (pt_build_bvh_device_ploc); sah: top-down binned SAH on the device (pt_build_bvh_device_sah)")

@@ -85,6 +85,8 @@ SYMBOLS = [
     ("pt_build_bvh_device_ploc", C.c_int, [_P, C.c_int32, C.POINTER(pt_bvh_stats)]),
     ("pt_build_bvh_device_split", C.c_int, [_P, C.c_int32, C.c_int32, C.POINTER(pt_bvh_stats)]),
     ("pt_build_bvh_device_sah", C.c_int, [_P, C.POINTER(pt_bvh_stats)]),
+    ("pt_optimize_bvh", C.c_int, [_P, C.c_int32, C.c_float, C.POINTER(pt_bvh_stats)]),
+    ("pt_bvh_optimize_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, C.c_float, _F, _F]),
     ("pt_bvh_build_host", C.c_int, [_P, C.c_int64, C.c_int32, C.POINTER(_F), C.POINTER(C.c_int32), C.POINTER(C.POINTER(C.c_int32)), C.POINTER(C.c_int32), C.POINTER(pt_bvh_stats)]),
     ("pt_free", None, [_P]),
     ("pt_bvh_collapse_host", C.c_int, [_P, C.c_int32, _P, C.c_int32, _P, C.c_int64, C.c_int32, C.POINTER(C.POINTER(C.c_uint8)),
@@ -520,6 +522,15 @@ class Renderer:
         refs = np.zeros(nr.value, dtype=np.int32)
         _check(self.lib.pt_get_bvh(self.ctx, _ptr(nodes), C.byref(nn), _ptr(refs), C.byref(nr)))
         return nodes, refs
+
+    def OptimizeBVH(self, iterations=4, batch_fraction=0.1):
+        """pt_optimize_bvh: reinsertion optimisation of the installed tree (host pass); the scene object follows the new tree."""
+        stats = pt_bvh_stats()
+        _check(self.lib.pt_optimize_bvh(self.ctx, int(iterations), float(batch_fraction), C.byref(stats)))
+        if getattr(self, "scene", None) is not None:
+            self.scene.set_bvh(*self.GetBVH())
+        self.opt_stats = stats
+        return stats
 
     def SetRNG(self, state):
         state = np.ascontiguousarray(state, dtype=np.uint32)

@@ -10,7 +10,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libb200pt.so")
-SOURCES = ["pt_api.cu", "pt_comm.cu", "pt_noalloc.cu", "pt_kernels.cu", "pt_bvh_gpu.cu", "pt_host.cpp", "pt_bvh_build.cpp", "pt_bvh_wide.cpp", "pt_obj.cpp", "pt_image.cpp"]
+SOURCES = ["pt_api.cu", "pt_comm.cu", "pt_noalloc.cu", "pt_kernels.cu", "pt_bvh_gpu.cu", "pt_host.cpp", "pt_bvh_build.cpp", "pt_bvh_wide.cpp", "pt_bvh_opt.cpp", "pt_obj.cpp", "pt_image.cpp"]
 
 # Float mode of the parity contract: no FMA contraction, IEEE division and square root.
 NVCC_FLAGS = [

@@ -536,6 +536,39 @@ int pt_set_bvh(pt_context* c, const float* nodes, int32_t n_nodes, const int32_t
     return install_bvh(c);
 }
 
+// Reinsertion optimisation of whatever tree the context holds (host or device built, or injected): read back if need be, optimised on
+// the host, installed again. stats: n_nodes / n_refs / n_leaves / max_depth / sah_cost of the result, build_ms = time of the pass.
+int pt_optimize_bvh(pt_context* c, int32_t iterations, float batch_fraction, pt_bvh_stats* stats) {
+    if (!c) return fail(PT_ERR_INVALID, "pt_optimize_bvh: null context");
+    if (iterations < 1 || iterations > 64 || !(batch_fraction > 0.0f) || batch_fraction > 1.0f)
+        return fail(PT_ERR_INVALID, "pt_optimize_bvh: iterations 1 .. 64, batch_fraction in (0, 1]");
+    PT_ENTER(c);
+    int rc = pt_check_scene(c, "pt_optimize_bvh", false);
+    if (rc == PT_OK) rc = pt_ensure_host_bvh(c);
+    if (rc != PT_OK) return rc;
+    auto t0 = std::chrono::steady_clock::now();
+    float before = 0.0f, after = 0.0f;
+    HostBvh& b = c->h_bvh;
+    const int moved = optimize_bvh_reinsertion(b.nodes.data(), (int)(b.nodes.size() / 8), iterations, batch_fraction, PT_MAX_TREE_DEPTH, &before, &after,
+                                               b.refs.data(), (int)b.refs.size());
+    if (moved < 0) return fail(PT_ERR_LIMIT, "pt_optimize_bvh: the optimised tree would exceed the traversal stack (%d); tree left as it was", PT_MAX_TREE_DEPTH);
+    auto t1 = std::chrono::steady_clock::now();
+    if (moved > 0) {
+        std::string msg; int n_leaves = 0;
+        int depth = validate_bvh(b.nodes.data(), (int)(b.nodes.size() / 8), b.refs.data(), (int)b.refs.size(), (int64_t)(c->h_tris.size() / 20), msg, &n_leaves);
+        if (depth < 0) return fail(PT_ERR_INVALID, "pt_optimize_bvh: internal error, %s", msg.c_str());
+        b.max_depth = depth; b.n_leaves = n_leaves; b.sah_cost = after;
+        if ((rc = install_bvh(c)) != PT_OK) return rc;
+    }
+    if (stats) {
+        stats->n_nodes = (int)(b.nodes.size() / 8); stats->n_refs = (int)b.refs.size(); stats->n_leaves = b.n_leaves; stats->max_depth = b.max_depth;
+        stats->sah_cost = moved > 0 ? after : before;
+        stats->build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+        stats->total_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return PT_OK;
+}
+
 int pt_build_bvh(pt_context* c, pt_bvh_stats* stats) {
     if (!c) return fail(PT_ERR_INVALID, "pt_build_bvh: null context");
     if (c->h_tris.empty()) return fail(PT_ERR_INVALID, "pt_build_bvh: call pt_set_triangles first");

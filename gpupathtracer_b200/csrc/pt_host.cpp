@@ -3,6 +3,7 @@
 // SAH cost (BVH.cpp:2174-2195) and the headless image writers that stand in for
 // Renderer::SaveScreenshot (Renderer.cpp:697-705).
 #include "pt_host.h"
+#include "pt_layout.h"
 #include <cmath>
 #include <cstring>
 #include <cstdio>
@@ -175,6 +176,12 @@ void pt_camera_image_plane(float aspect, float fov, float focus, float aperture,
 
 }  // extern "C"
 
+extern "C" int pt_bvh_optimize_host(float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs, int32_t iterations, float batch_fraction,
+                                    float* sah_before, float* sah_after) {
+    if (!nodes || !refs || n_nodes < 3 || iterations < 1 || !(batch_fraction > 0.0f) || batch_fraction > 1.0f) return PT_ERR_INVALID;
+    const int moved = pt::optimize_bvh_reinsertion(nodes, n_nodes, iterations, batch_fraction, PT_MAX_TREE_DEPTH, sah_before, sah_after, refs, n_refs);
+    return moved < 0 ? PT_ERR_LIMIT : moved;
+}
 extern "C" float pt_bvh_sah_cost(const float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs) {
     if (!nodes || !refs || n_nodes < 1) return -1.0f;
     return pt::bvh_sah_cost(nodes, n_nodes, refs, n_refs);

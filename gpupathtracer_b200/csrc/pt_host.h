@@ -22,6 +22,11 @@ int validate_bvh(const float* nodes, int n_nodes, const int32_t* refs, int n_ref
 // SAH cost as BVH.cpp:2174-2195 (CalculateCost) evaluated on the serialised tree.
 float bvh_sah_cost(const float* nodes, int n_nodes, const int32_t* refs, int n_refs);
 
+// Reinsertion optimisation of a reference-form tree in place (pt_bvh_opt.cpp). Returns the subtrees moved, -1 if the result would
+// be max_depth deep or deeper (input untouched).
+int optimize_bvh_reinsertion(float* nodes, int n_nodes, int iterations, float batch_fraction, int max_depth, float* sah_before, float* sah_after,
+                             const int32_t* refs, int n_refs);
+
 // Own builder (pt_bvh_build.cpp): tris_pre = n x 20 floats with pre-subtracted edges.
 bool build_sbvh(const float* tris_pre, int64_t n, int n_threads, HostBvh& out, std::string& msg);
 

@@ -187,6 +187,16 @@ int pt_build_bvh_device_split(pt_context* ctx, int32_t ploc_radius, int32_t spli
  * pt_last_error()) should the tree come out deeper than the traversal stack. The builders' scratch stays in the context (<= 512 MB),
  * so a rebuild per frame costs its kernels only. */
 int pt_build_bvh_device_sah(pt_context* ctx, pt_bvh_stats* stats);
+/* Reinsertion optimisation of the tree the context holds, whoever built it (Bittner, Hapala, Havran 2013, batched: the nodes with the
+ * largest surface look -- branch and bound -- for the place in the tree where their subtree adds the least surface area, and move there).
+ * The reference carries such a pass, ReinsertionOptimize, and never calls it (BVH.cpp; SURVEY.md 2 lists it as dead code). Leaves and
+ * reference list are untouched, the serialised form is kept; `iterations` passes (1 .. 64) over the `batch_fraction` (0 .. 1] of nodes
+ * with the largest surface. Host work (seconds at 1 M triangles); the tree is read back from the device if it was built there.
+ * PT_ERR_LIMIT (tree unchanged) if the result would be deeper than the traversal stack. */
+int pt_optimize_bvh(pt_context* ctx, int32_t iterations, float batch_fraction, pt_bvh_stats* stats);
+/* The same on arrays, in place, no context: returns the number of subtrees moved (>= 0) or an error code (< 0). */
+int pt_bvh_optimize_host(float* nodes, int32_t n_nodes, const int32_t* refs, int32_t n_refs, int32_t iterations, float batch_fraction,
+                         float* sah_before, float* sah_after);
 /* The same builder without a context or a device (pure host work): arrays are malloc()ed, release with pt_free. */
 int pt_bvh_build_host(const float* tris, int64_t n, int32_t n_threads, float** nodes, int32_t* n_nodes,
                       int32_t** refs, int32_t* n_refs, pt_bvh_stats* stats);

@@ -163,3 +163,53 @@ def test_no_reference_text_is_left_in_the_tree():
         pytest.skip("oracle/_ref not built")
     left = [f for f in os.listdir(d) if not f.endswith(".so")]
     assert left == [], left
+
+
+@pytest.mark.parametrize("name,tree", [("atrium_small", "own"), ("soup", "own"), ("cornell", "reference")])
+def test_reinsertion_optimisation_keeps_the_tree_valid_and_the_hits(name, tree):
+    """pt_bvh_optimize_host (the pass the reference carries as dead code, ReinsertionOptimize): subtrees move, leaves and reference
+    list do not. The result is still the reference's serialised form (every node referenced once, children adjacent at an odd index,
+    larger child first, boxes nested), it has the same leaves, a SAH cost that is no higher, and the ORACLE walking it returns the same
+    hits bit for bit with fewer node visits."""
+    import ctypes as C
+    from gpupathtracer_b200 import load_library
+    from gpupathtracer_b200.api import _ptr
+    lib = load_library()
+    s = Scene(SCENES[name]())
+    if tree == "reference":
+        if not oracle.have_ref():
+            pytest.skip("oracle/_ref not built")
+        nodes, refs = oracle.ref_build_sbvh(s.tris_abs)
+    else:
+        nodes, refs, _ = build_bvh_host(s.tris, n_threads=4)
+    rays = scenes.random_rays(40000, *s.bounds(), seed=21)
+    s.set_bvh(nodes.copy(), refs.copy())
+    want, c0 = oracle.Oracle(s).trace_closest(rays)
+    opt = np.ascontiguousarray(nodes.copy())
+    before, after = C.c_float(), C.c_float()
+    moved = lib.pt_bvh_optimize_host(_ptr(opt), opt.shape[0], _ptr(refs), refs.shape[0], 4, 0.25, C.byref(before), C.byref(after))
+    assert moved > 0 and after.value <= before.value
+    n = opt.shape[0]
+    d0, d0_in = opt[:, 3].copy().view(np.int32), nodes[:, 3].copy().view(np.int32)
+    inner = d0 > 0
+    assert n == nodes.shape[0] and d0[0] == 1 and np.all(d0[inner] % 2 == 1)
+    assert np.array_equal(np.sort(np.concatenate([d0[inner], d0[inner] + 1])), np.arange(1, n))
+    assert np.array_equal(np.sort(d0[~inner]), np.sort(d0_in[d0_in <= 0]))                     # the same leaves
+    leaf_boxes = lambda a, d: a[d <= 0][np.argsort(d[d <= 0], kind="stable")]
+    assert np.array_equal(leaf_boxes(opt, d0)[:, [0, 1, 2, 4, 5, 6]], leaf_boxes(nodes, d0_in)[:, [0, 1, 2, 4, 5, 6]])
+    for k in (0, 1):
+        c = d0[inner] + k
+        assert np.all(opt[c, 0:3] >= opt[inner, 0:3]) and np.all(opt[c, 4:7] <= opt[inner, 4:7])
+    ext = opt[:, 4:7] - opt[:, 0:3]
+    area = ext[:, 0] * (ext[:, 1] + ext[:, 2]) + ext[:, 1] * ext[:, 2]
+    assert np.all(area[d0[inner]] >= area[d0[inner] + 1])                                       # BVH.cpp:2240-2247
+    s.set_bvh(opt, refs.copy())
+    got, c1 = oracle.Oracle(s).trace_closest(rays)
+    ids_same = got[:, 3].view(np.int32) == want[:, 3].view(np.int32)
+    assert ids_same.mean() > 1 - 1e-4                        # a different tree: only ties / box-grazing rays may differ
+    assert np.array_equal(got[ids_same].view(np.uint32), want[ids_same].view(np.uint32))
+    assert c1["node_pairs"] <= c0["node_pairs"]
+    # doing nothing is allowed too: a tree below 7 nodes is returned as it is
+    tiny = np.ascontiguousarray(nodes[:3].copy())
+    assert lib.pt_bvh_optimize_host(_ptr(tiny), 3, _ptr(refs), refs.shape[0], 1, 0.5, None, None) == 0
+    assert lib.pt_bvh_optimize_host(_ptr(opt), n, _ptr(refs), refs.shape[0], 0, 0.5, None, None) < 0      # bad argument

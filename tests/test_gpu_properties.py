@@ -414,3 +414,39 @@ def test_device_sah_builder_on_degenerate_input(case):
     r.CleanUp()
     want, _ = oracle.Oracle(s).trace_closest(rays)
     assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("builder", ["build", "sah"])
+def test_reinsertion_optimised_tree_on_the_device(builder):
+    """pt_optimize_bvh on a tree built by the host builder / by the device SAH builder (read back, optimised on the host, installed
+    again): the CUDA walk of the new tree equals the oracle's walk of it bit for bit, it finds the same surfaces as before with no
+    more pair visits (device counters), and whole frames under the parity libm are still bit-identical to the oracle on that tree."""
+    from common import mixed_rays
+    s = Scene(get_scene("atrium_small").data)
+    w, h = 64, 48
+    rng = make_rng_table(w * h, 5)
+    r = Renderer().Initialize(w, h, s, max_depth=5, rng_state=rng, bvh=builder, parity_libm=True)
+    rays = mixed_rays(s, 150000, seed=17)
+    r.SetVisitCounting(True)
+    before = r.TraceClosest(rays)
+    v0 = r.Counters()
+    sah0 = float(r.bvh_stats.sah_cost)
+    st = r.OptimizeBVH(4, 0.25)
+    assert st.sah_cost < sah0 and st.max_depth < 96 and st.n_refs == s.refs.shape[0]
+    got = r.TraceClosest(rays)
+    v1 = r.Counters()
+    r.SetVisitCounting(False)
+    want, _ = oracle.Oracle(s).trace_closest(rays)               # the scene object follows the installed tree
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+    same = got[:, 3].view(np.int32) == before[:, 3].view(np.int32)
+    assert same.mean() > 1 - 1e-4 and np.array_equal(got[same].view(np.uint32), before[same].view(np.uint32))
+    pairs0 = v0["closest_pair_tests"]; pairs1 = v1["closest_pair_tests"] - v0["closest_pair_tests"]
+    assert pairs1 <= pairs0
+    cam = make_camera(s.data, w, h, aperture=0.1)
+    r.RenderFrame(cam, 2)
+    img, rng_got = r.DownloadAccum(), r.GetRNG()
+    r.CleanUp()
+    rng_o, ref = rng.copy(), np.zeros((h, w, 4), np.float32)
+    oracle.Oracle(s).render(cam.as_array(), w, h, rng_o, ref, n_frames=2, max_depth=5, parity_libm=True)
+    eq = (img.view(np.uint32) == ref.view(np.uint32)) | (np.isnan(img) & np.isnan(ref))
+    assert eq.all() and np.array_equal(rng_got, rng_o)

@@ -22,6 +22,9 @@ for label, how, g in cases:
     s = Scene(base.data)
     r = Renderer().Initialize(W, H, s, max_depth=wl["depth"], microfacet_model=wl["model"], seed=1, bvh=how)
     st = r.bvh_stats
+    if os.environ.get("EXP_OPT"):
+        it, fr = os.environ["EXP_OPT"].split(","); o = r.OptimizeBVH(int(it), float(fr))
+        label = label + f" + opt {it}x{fr}"; st.sah_cost = o.sah_cost; st.max_depth = o.max_depth; st.total_ms += o.total_ms
     for _ in range(3):
         r.RenderFrame(cam, 8); r.Synchronize()
     ms = []

@@ -16,6 +16,9 @@ for label, how, g, rad in cases:
     if rad: os.environ["PT_PLOC_RADIUS"] = str(rad)
     s = Scene(base.data)
     r = Renderer().Initialize(W, H, s, max_depth=1, seed=1, bvh=how)
+    if os.environ.get("EXP_OPT"):
+        it, fr = os.environ["EXP_OPT"].split(","); o = r.OptimizeBVH(int(it), float(fr))
+        label = label + f" + opt {it}x{fr}"; r.bvh_stats.sah_cost = o.sah_cost; r.bvh_stats.max_depth = o.max_depth
     r.lib.pt_set_camera(r.ctx, cam.plane)
     pr = r.RaygenProbe(0, n)
     rays = np.zeros((n, 8), np.float32); rays[:, 0:3] = pr[:, 2:5]; rays[:, 4:7] = pr[:, 5:8]; rays[:, 7] = 1e20
