@@ -440,12 +440,13 @@ __global__ void k_depth(const int* __restrict__ parent_inner, const int* __restr
 // ---------------------------------------------------------------- top-down binned SAH on the device (pt_build_bvh_device_sah)
 // The reference's builder is a top-down SAH search (FindBestObjectSplit, BVH.cpp:1619-1763: 8 bins per axis, sweep below 8
 // references); its spatial splits are worth 2 % of SAH cost on the atrium and nothing on the bunny scene, the
-// top-down search itself is worth the 8-10 % that separate it from Morton / PLOC trees. Here the same search runs on the device,
+// top-down search and the multi-triangle leaves are worth the 8-10 % that separate it from Morton / PLOC trees. Here the same search runs on the device,
 // breadth first: every level bins the primitives of all nodes larger than SAH_SMALL at once (SAH_BINS bins per axis over the
 // node's CENTROID box, counts + boxes accumulated with atomics: block-private in shared memory for the node a block starts in, global for
 // the rest), one thread per node picks the cheapest of the 3 x (SAH_BINS - 1) planes and creates the children, and the primitives
 // are partitioned into the other index buffer; subtrees of <= SAH_SMALL primitives are finished by ONE thread each with an exact
-// sweep. One primitive per leaf, as the other device builders; inner ids are handed out by an atomic counter (root = 0) and made
+// sweep, which is also where leaves of SEVERAL triangles are made by the reference's SAH leaf rule (k_sah_small; the LBVH / PLOC builders
+// keep one primitive per leaf). Inner ids are handed out by an atomic counter (root = 0; ids of nodes that turned into leaves stay unused) and made
 // depth-first by k_ploc_relabel, so the emitted tree does not depend on the order atomics happened to land in.
 #ifndef SAH_BINS
 #define SAH_BINS 16
